@@ -1,0 +1,40 @@
+"""tcgen05 GEMM binding (csrc/gemm_tcgen05.cu)."""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from . import _lib
+
+BIAS, RELU, ATOMIC_ADD = 1, 2, 4
+
+
+def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False, bias=None, relu=False,
+              out: torch.Tensor | None = None, out_dtype=torch.bfloat16, accumulate: bool = False, splits: int = 0):
+    """D[M,N] = opA(a) @ opB(b)^T on the tensor cores.
+
+    ``a`` is [M,K] (or [K,M] when ``a_mn``), ``b`` is [N,K] (or [K,N] when ``b_mn``); both bf16, 2-D, unit inner
+    stride (row pitch may exceed the row length: channel slices of a wider NHWC tensor are fine).
+    ``accumulate`` adds into an fp32 ``out`` with red.global.add (split-K is chosen automatically).
+    """
+    lib = _lib.cuda_lib()
+    assert lib is not None, "gemm_bf16 needs a CUDA device"
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.dim() == 2 and b.dim() == 2
+    assert a.stride(1) == 1 and b.stride(1) == 1
+    M, K = (a.shape[1], a.shape[0]) if a_mn else (a.shape[0], a.shape[1])
+    N, Kb = (b.shape[1], b.shape[0]) if b_mn else (b.shape[0], b.shape[1])
+    assert K == Kb, f"contraction mismatch {K} vs {Kb}"
+    if out is None:
+        out = torch.empty((M, N), device=a.device, dtype=out_dtype)
+    assert out.shape == (M, N) and out.stride(1) == 1
+    flags = (BIAS if bias is not None else 0) | (RELU if relu else 0) | (ATOMIC_ADD if accumulate else 0)
+    if bias is not None:
+        assert bias.dtype == torch.float32 and bias.is_contiguous()
+    rc = lib.bdl_gemm_bf16(_lib.ptr(a), _lib.ptr(b), _lib.ptr(out), _lib.ptr(bias), M, N, K,
+                           ctypes.c_longlong(a.stride(0)), ctypes.c_longlong(b.stride(0)),
+                           ctypes.c_longlong(out.stride(0)), int(a_mn), int(b_mn),
+                           int(out.dtype == torch.float32), flags, splits, _lib.stream_ptr())
+    _lib.check(rc, "bdl_gemm_bf16")
+    _lib.count_launch()
+    return out

@@ -1,0 +1,85 @@
+#include "host_common.h"
+
+#include <mutex>
+#include <stdio.h>
+#include <string.h>
+
+#include "bigdl_b200.h"
+
+static thread_local char g_err[512] = "";
+
+int bdl_fail(const char* msg) {
+  snprintf(g_err, sizeof(g_err), "%s", msg);
+  return BDL_ERR_INVALID;
+}
+int bdl_fail_cuda(const char* what, cudaError_t e) {
+  snprintf(g_err, sizeof(g_err), "%s: %s", what, cudaGetErrorString(e));
+  return BDL_ERR_CUDA;
+}
+int bdl_check_launch(const char* kernel_name) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return bdl_fail_cuda(kernel_name, e);
+  return BDL_OK;
+}
+extern "C" const char* bdl_last_error() { return g_err; }
+extern "C" int bdl_version() { return 100; }
+
+int bdl_num_sms() {
+  static int cache[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (cache[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cache[dev] = n;
+  }
+  return cache[dev];
+}
+extern "C" int bdl_sm_count() { return bdl_num_sms(); }
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_tiled() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+static int make_tmap_2d(CUtensorMap* out, CUtensorMapDataType dt, int esize, const void* base, uint64_t dim0,
+                        uint64_t dim1, long long ld, uint32_t box0, uint32_t box1) {
+  EncodeTiledFn fn = get_encode_tiled();
+  if (!fn) return bdl_fail("cuTensorMapEncodeTiled entry point not available (no CUDA driver?)");
+  cuuint64_t dims[2] = {dim0, dim1};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * esize};
+  cuuint32_t box[2] = {box0, box1};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    char buf[256];
+    snprintf(buf, sizeof(buf),
+             "cuTensorMapEncodeTiled failed (CUresult %d) dims=(%llu,%llu) ld=%lld box=(%u,%u) base=%p", (int)r,
+             (unsigned long long)dim0, (unsigned long long)dim1, ld, box0, box1, base);
+    return bdl_fail(buf);
+  }
+  return BDL_OK;
+}
+
+int bdl_make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t dim0, uint64_t dim1, long long ld, uint32_t box0,
+                          uint32_t box1) {
+  return make_tmap_2d(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dim0, dim1, ld, box0, box1);
+}
+int bdl_make_tmap_2d_u8(CUtensorMap* out, const void* base, uint64_t dim0, uint64_t dim1, long long ld, uint32_t box0,
+                        uint32_t box1) {
+  return make_tmap_2d(out, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, base, dim0, dim1, ld, box0, box1);
+}

@@ -1,0 +1,18 @@
+// Host-side helpers shared by every .cu translation unit: error reporting, device properties,
+// TMA tensor-map construction through the driver entry point (no link-time dependency on libcuda).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+int bdl_fail(const char* msg);                       // records msg, returns BDL_ERR_INVALID
+int bdl_fail_cuda(const char* what, cudaError_t e);  // records "what: cudaGetErrorString(e)", returns BDL_ERR_CUDA
+int bdl_check_launch(const char* kernel_name);       // cudaGetLastError() after a launch
+int bdl_num_sms();                                   // SM count of the current device (cached per device)
+
+// 2-D bf16 tensor map with 128-byte swizzle. dim0 is the contiguous dimension; ld is the row pitch in elements.
+int bdl_make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t dim0, uint64_t dim1, long long ld, uint32_t box0,
+                          uint32_t box1);
+// Same for 1-byte elements (fp8): box0 is in elements (= bytes), at most 128.
+int bdl_make_tmap_2d_u8(CUtensorMap* out, const void* base, uint64_t dim0, uint64_t dim1, long long ld, uint32_t box0,
+                        uint32_t box1);

@@ -1,0 +1,61 @@
+"""tcgen05 GEMM vs a plain fp32 PyTorch reference (all four operand-major combinations, ragged shapes, split-K)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _ref(a, b, a_mn, b_mn):
+    A = a.float().t() if a_mn else a.float()
+    B = b.float() if b_mn else b.float().t()
+    return A @ B
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, False), (True, True)])
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (256, 512, 256), (384, 200, 136), (1000, 96, 72), (130, 1000, 1024),
+                                   (4096, 2048, 512)])
+def test_gemm_majors(a_mn, b_mn, M, N, K):
+    from bigdl_b200.ops.gemm import gemm_bf16
+    torch.manual_seed(0)
+    dev = "cuda"
+    # leading dims must be multiples of 8 elements: pad the storage, slice the view
+    def mk(rows, cols):
+        ld = (cols + 7) // 8 * 8
+        return torch.randn(rows, ld, device=dev).to(torch.bfloat16)[:, :cols]
+    a = mk(K, M) if a_mn else mk(M, K)
+    b = mk(K, N) if b_mn else mk(N, K)
+    out = gemm_bf16(a, b, a_mn=a_mn, b_mn=b_mn, out_dtype=torch.float32)
+    torch.cuda.synchronize()
+    ref = _ref(a, b, a_mn, b_mn)
+    err = (out - ref).abs().max().item()
+    scale = ref.abs().max().item()
+    assert err <= 2e-3 * scale + 1e-3, (err, scale)
+
+
+def test_gemm_bias_relu_bf16_out():
+    from bigdl_b200.ops.gemm import gemm_bf16
+    torch.manual_seed(1)
+    a = torch.randn(512, 320, device="cuda").bfloat16()
+    b = torch.randn(192, 320, device="cuda").bfloat16()
+    bias = torch.randn(192, device="cuda")
+    wide = torch.zeros(512, 256, device="cuda", dtype=torch.bfloat16)
+    out = gemm_bf16(a, b, bias=bias, relu=True, out=wide[:, 32:224])
+    torch.cuda.synchronize()
+    ref = torch.relu(a.float() @ b.float().t() + bias)
+    assert torch.allclose(out.float(), ref, rtol=2e-2, atol=2e-1)
+    assert wide[:, :32].abs().max().item() == 0 and wide[:, 224:].abs().max().item() == 0
+
+
+def test_gemm_splitk_accumulate():
+    from bigdl_b200.ops.gemm import gemm_bf16
+    torch.manual_seed(2)
+    # wgrad shape: dW[Cout, K] = dY[M, Cout]^T X[M, K]; tiny output, huge contraction -> split-K with red.add
+    M, Cout, Kd = 128 * 196, 64, 576
+    dy = torch.randn(M, Cout, device="cuda").bfloat16()
+    x = torch.randn(M, Kd, device="cuda").bfloat16()
+    acc = torch.ones(Cout, Kd, device="cuda")
+    gemm_bf16(dy, x, a_mn=True, b_mn=True, out=acc, accumulate=True)
+    torch.cuda.synchronize()
+    ref = 1.0 + dy.float().t() @ x.float()
+    err = (acc - ref).abs().max().item()
+    assert err <= 2e-3 * ref.abs().max().item() + 1e-2, err

@@ -1,0 +1,364 @@
+"""Sample / MiniBatch / DataSet / Transformer (reference: S/dataset/Sample.scala, MiniBatch.scala, DataSet.scala,
+Transformer.scala).
+
+* ``Sample(features, labels)`` — one record; features/labels are tensors (or lists of tensors).
+* ``MiniBatch`` — batched features/labels with 1-based ``slice(offset, length)``.
+* ``DataSet.array(...)`` → ``LocalArrayDataSet``; ``DataSet.rdd(...)`` → ``DistributedDataSet`` which shards the
+  records over ranks (one process per GPU replaces one Spark partition per node) and, like
+  ``CachedDistriDataSet`` (DataSet.scala:247-322), serves an *infinite* shuffled training iterator that starts at a
+  random offset.
+* ``Transformer`` objects chain with ``->`` in Scala; here with ``>>`` (or ``.chain``).
+"""
+from __future__ import annotations
+
+import math
+from typing import Callable, Iterable, Iterator, Sequence
+
+import numpy as np
+import torch
+
+from ..utils.random_generator import RNG
+from ..utils.table import Table
+
+
+def _t(x) -> torch.Tensor:
+    if isinstance(x, torch.Tensor):
+        return x
+    a = np.asarray(x)
+    if a.dtype == np.float64:
+        a = a.astype(np.float32)
+    return torch.from_numpy(np.ascontiguousarray(a))
+
+
+class Sample:
+    """One training record (S/dataset/Sample.scala ArraySample/TensorSample; Python P/util/common.py:294)."""
+
+    def __init__(self, features, labels=None):
+        self.features = [_t(f) for f in features] if isinstance(features, (list, tuple)) else [_t(features)]
+        if labels is None:
+            self.labels = []
+        else:
+            self.labels = [_t(l) for l in labels] if isinstance(labels, (list, tuple)) else [_t(labels)]
+
+    @classmethod
+    def from_ndarray(cls, features, labels=None):
+        return cls(features, labels)
+
+    def feature(self, index: int = 0) -> torch.Tensor:
+        return self.features[index]
+
+    def label(self, index: int = 0) -> torch.Tensor:
+        return self.labels[index]
+
+    def numFeature(self) -> int:
+        return len(self.features)
+
+    def numLabel(self) -> int:
+        return len(self.labels)
+
+    def __repr__(self):
+        return f"Sample: features: {[tuple(f.shape) for f in self.features]}, labels: {[tuple(l.shape) for l in self.labels]}"
+
+
+class PaddingParam:
+    """Variable-length padding policy (S/dataset/MiniBatch.scala:523): pad each feature to the longest in the batch
+    (``FixedLength`` pads to a given size) with ``padding_tensor`` values (default 0)."""
+
+    def __init__(self, padding_tensor=None, padding_strategy=None, fixed_length=None):
+        self.padding_tensor = padding_tensor
+        self.fixed_length = fixed_length if fixed_length is not None else padding_strategy
+
+
+def _stack(tensors: Sequence[torch.Tensor], pad: PaddingParam | None, idx: int) -> torch.Tensor:
+    shapes = {tuple(t.shape) for t in tensors}
+    if len(shapes) == 1 and (pad is None or pad.fixed_length is None):
+        return torch.stack(list(tensors))
+    if pad is None:
+        raise ValueError("samples have different sizes; pass a PaddingParam to pad them")
+    nd = tensors[0].dim()
+    target = [max(t.shape[d] for t in tensors) for d in range(nd)]
+    if pad.fixed_length is not None:
+        fl = pad.fixed_length[idx] if isinstance(pad.fixed_length, (list, tuple)) else pad.fixed_length
+        if fl is not None and fl > 0:
+            target[0] = max(target[0], fl)
+    value = 0.0
+    if pad.padding_tensor is not None:
+        pt = pad.padding_tensor[idx] if isinstance(pad.padding_tensor, (list, tuple)) else pad.padding_tensor
+        value = float(_t(pt).reshape(-1)[0])
+    out = torch.full([len(tensors)] + target, value, dtype=tensors[0].dtype)
+    for i, t in enumerate(tensors):
+        out[(i,) + tuple(slice(0, s) for s in t.shape)] = t
+    return out
+
+
+class MiniBatch:
+    """Batched activity pair (S/dataset/MiniBatch.scala:34). ``getInput``/``getTarget`` return a Tensor, or a Table
+    when there are several feature/label tensors."""
+
+    def __init__(self, inputs, targets=None):
+        self.inputs = list(inputs) if isinstance(inputs, (list, tuple)) else [inputs]
+        self.targets = [] if targets is None else (list(targets) if isinstance(targets, (list, tuple)) else [targets])
+
+    def size(self) -> int:
+        return self.inputs[0].shape[0]
+
+    def getInput(self):
+        return self.inputs[0] if len(self.inputs) == 1 else Table(*self.inputs)
+
+    def getTarget(self):
+        if not self.targets:
+            return None
+        return self.targets[0] if len(self.targets) == 1 else Table(*self.targets)
+
+    get_input, get_target = getInput, getTarget
+
+    def slice(self, offset: int, length: int) -> "MiniBatch":
+        """1-based offset, like the reference."""
+        s = slice(offset - 1, offset - 1 + length)
+        return MiniBatch([t[s] for t in self.inputs], [t[s] for t in self.targets])
+
+    def to(self, device, non_blocking: bool = True) -> "MiniBatch":
+        return MiniBatch([t.to(device, non_blocking=non_blocking) for t in self.inputs],
+                         [t.to(device, non_blocking=non_blocking) for t in self.targets])
+
+    def pin(self) -> "MiniBatch":
+        if torch.cuda.is_available():
+            return MiniBatch([t.pin_memory() for t in self.inputs], [t.pin_memory() for t in self.targets])
+        return self
+
+    @staticmethod
+    def from_samples(samples: Sequence[Sample], feature_padding: PaddingParam | None = None,
+                     label_padding: PaddingParam | None = None) -> "MiniBatch":
+        nf, nl = samples[0].numFeature(), samples[0].numLabel()
+        ins = [_stack([s.features[i] for s in samples], feature_padding, i) for i in range(nf)]
+        tgs = [_stack([s.labels[i] for s in samples], label_padding, i) for i in range(nl)]
+        return MiniBatch(ins, tgs)
+
+
+# ====================================================================== transformers
+class Transformer:
+    """Iterator → iterator stage (S/dataset/Transformer.scala). ``a >> b`` chains (Scala ``a -> b``)."""
+
+    def __call__(self, prev: Iterator) -> Iterator:  # pragma: no cover
+        raise NotImplementedError
+
+    def chain(self, other: "Transformer") -> "Transformer":
+        return ChainedTransformer(self, other)
+
+    __rshift__ = chain
+
+    def cloneTransformer(self):
+        import copy
+
+        return copy.deepcopy(self)
+
+
+class ChainedTransformer(Transformer):
+    def __init__(self, first: Transformer, last: Transformer):
+        self.first, self.last = first, last
+
+    def __call__(self, prev):
+        return self.last(self.first(prev))
+
+
+class Identity(Transformer):
+    def __call__(self, prev):
+        return prev
+
+
+class FuncTransformer(Transformer):
+    def __init__(self, fn: Callable):
+        self.fn = fn
+
+    def __call__(self, prev):
+        return (self.fn(x) for x in prev)
+
+
+class SampleToMiniBatch(Transformer):
+    """Group ``batch_size`` samples into a MiniBatch (S/dataset/Transformer.scala:309). ``batch_size`` is the batch of
+    THIS process; ``partition_num`` divides a global batch like the reference's totalBatch/partitionNum."""
+
+    def __init__(self, batch_size: int, feature_padding=None, label_padding=None, partition_num: int | None = None,
+                 drop_remainder: bool = False):
+        self.batch_size = batch_size // partition_num if partition_num else batch_size
+        self.feature_padding, self.label_padding, self.drop_remainder = feature_padding, label_padding, drop_remainder
+
+    def __call__(self, prev):
+        buf = []
+        for s in prev:
+            buf.append(s)
+            if len(buf) == self.batch_size:
+                yield MiniBatch.from_samples(buf, self.feature_padding, self.label_padding)
+                buf = []
+        if buf and not self.drop_remainder:
+            yield MiniBatch.from_samples(buf, self.feature_padding, self.label_padding)
+
+
+# ====================================================================== datasets
+class AbstractDataSet:
+    def data(self, train: bool) -> Iterator:  # pragma: no cover
+        raise NotImplementedError
+
+    def size(self) -> int:  # pragma: no cover
+        raise NotImplementedError
+
+    def shuffle(self):
+        return self
+
+    def transform(self, transformer: Transformer) -> "AbstractDataSet":
+        return TransformedDataSet(self, transformer)
+
+    def __rshift__(self, transformer: Transformer):
+        return self.transform(transformer)
+
+    def toLocal(self):
+        return self
+
+    def toDistributed(self):
+        return self
+
+    def is_distributed(self) -> bool:
+        return False
+
+
+class TransformedDataSet(AbstractDataSet):
+    def __init__(self, base: AbstractDataSet, transformer: Transformer):
+        self.base, self.transformer = base, transformer
+
+    def data(self, train: bool):
+        return self.transformer(self.base.data(train))
+
+    def size(self):
+        return self.base.size()
+
+    def shuffle(self):
+        self.base.shuffle()
+        return self
+
+    def is_distributed(self):
+        return self.base.is_distributed()
+
+    def originRDD(self):
+        return self.base
+
+
+class LocalArrayDataSet(AbstractDataSet):
+    """In-memory records; the training iterator is infinite and walks a shuffled index (DataSet.scala:135-169)."""
+
+    def __init__(self, buffer: Sequence):
+        self.buffer = list(buffer)
+        self.index = list(range(len(self.buffer)))
+
+    def shuffle(self):
+        RNG.shuffle(self.index)
+        return self
+
+    def size(self):
+        return len(self.buffer)
+
+    def data(self, train: bool):
+        n = len(self.buffer)
+        if not train:
+            return iter(self.buffer)
+
+        def gen():
+            i = 0
+            while True:
+                yield self.buffer[self.index[i % n]]
+                i += 1
+
+        return gen()
+
+
+class DistributedDataSet(LocalArrayDataSet):
+    """Records sharded over ranks: rank r keeps records r, r+W, r+2W, … (the analogue of ``coalesce(nodeNumber)``);
+    ``size()`` is the GLOBAL record count; the training iterator is infinite with a random start offset
+    (CachedDistriDataSet, DataSet.scala:268-283)."""
+
+    def __init__(self, buffer: Sequence, rank: int | None = None, world_size: int | None = None):
+        from ..utils.engine import Engine
+
+        self.rank = Engine.ensure().rank if rank is None else rank
+        self.world_size = Engine.world_size if world_size is None else world_size
+        self.global_size = len(buffer)
+        super().__init__([b for i, b in enumerate(buffer) if i % self.world_size == self.rank])
+
+    def size(self):
+        return self.global_size
+
+    def local_size(self):
+        return len(self.buffer)
+
+    def is_distributed(self):
+        return True
+
+    def data(self, train: bool):
+        n = len(self.buffer)
+        if not train:
+            return iter(self.buffer)
+        start = int(RNG.uniform(0, n)) if n > 0 else 0
+
+        def gen():
+            i = start
+            while True:
+                yield self.buffer[self.index[i % n]]
+                i += 1
+
+        return gen()
+
+
+class DataSet:
+    """Factory namespace (S/dataset/DataSet.scala:324-669)."""
+
+    @staticmethod
+    def array(data: Sequence, distributed: bool = False) -> AbstractDataSet:
+        return DistributedDataSet(data) if distributed else LocalArrayDataSet(data)
+
+    @staticmethod
+    def rdd(data: Iterable, partition_num: int | None = None) -> AbstractDataSet:
+        """A Python iterable stands in for an RDD; it is materialised and sharded across ranks."""
+        return DistributedDataSet(list(data))
+
+    @staticmethod
+    def from_ndarrays(x: np.ndarray, y: np.ndarray | None = None, distributed: bool = False) -> AbstractDataSet:
+        samples = [Sample(x[i], None if y is None else y[i]) for i in range(len(x))]
+        return DataSet.array(samples, distributed)
+
+    @staticmethod
+    def imageFrame(frame):
+        return frame.toDataSet() if hasattr(frame, "toDataSet") else DataSet.array(list(frame))
+
+    @staticmethod
+    def ImageFolder(path: str, scale_to: int = 256, distributed: bool = False):
+        from .image import image_folder_dataset
+
+        return image_folder_dataset(path, scale_to, distributed)
+
+    @staticmethod
+    def SeqFileFolder(path: str, class_num: int = 1000, distributed: bool = True):
+        from .seqfile import seq_file_dataset
+
+        return seq_file_dataset(path, class_num, distributed)
+
+
+class FixedMiniBatchDataSet(AbstractDataSet):
+    """One fixed MiniBatch served forever — the synthetic-data mode of the perf harnesses
+    (S/models/utils/DistriOptimizerPerf.scala:100-120)."""
+
+    def __init__(self, batch: MiniBatch, epoch_size: int | None = None, distributed: bool = True):
+        self.batch, self._size, self._dist = batch, epoch_size or batch.size(), distributed
+
+    def size(self):
+        return self._size
+
+    def is_distributed(self):
+        return self._dist
+
+    def data(self, train: bool):
+        if train:
+            def gen():
+                while True:
+                    yield self.batch
+            return gen()
+        n = max(1, math.ceil(self._size / max(self.batch.size(), 1)))
+        return iter([self.batch] * n)

@@ -1,0 +1,7 @@
+"""``bigdl_b200.nn.layer`` — every layer under one roof, mirroring P/nn/layer.py of the reference."""
+from .module import *            # noqa: F401,F403
+from .module import Module as Layer   # noqa: F401  (P/nn/layer.py:117 calls the base class ``Layer``)
+from .layers_core import *       # noqa: F401,F403
+from .layers_table import *      # noqa: F401,F403
+from .layers_activation import * # noqa: F401,F403
+from .initialization_method import *  # noqa: F401,F403

@@ -44,7 +44,65 @@ def cuda_lib():
             return None
         _cuda = _load("libbigdl_b200.so")
         _cuda.bdl_last_error.restype = ctypes.c_char_p
+        _declare(_cuda)
     return _cuda
+
+
+_P, _I, _L, _F, _Z, _U64 = (ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_float, ctypes.c_size_t,
+                            ctypes.c_ulonglong)
+
+# argument types of every exported function (include/bigdl_b200.h); keeps 64-bit values intact through ctypes
+_SIGNATURES = {
+    "bdl_gemm_bf16": [_P, _P, _P, _P, _I, _I, _I, _L, _L, _L, _I, _I, _I, _I, _I, _P],
+    "bdl_gemm_fp8": [_P, _P, _P, _P, _P, _P, _I, _I, _I, _L, _L, _L, _I, _I, _P],
+    "bdl_cast_f32_to_bf16": [_P, _P, _Z, _I, _P],
+    "bdl_cast_bf16_to_f32": [_P, _P, _Z, _P],
+    "bdl_bf16_trunc_add": [_P, _P, _P, _Z, _P],
+    "bdl_eltwise_bf16": [_I, _P, _P, _P, _Z, _F, _P],
+    "bdl_colsum_bf16": [_P, _P, _P, _P, _L, _I, _L, _L, _L, _P],
+    "bdl_dropout_fwd_bf16": [_P, _P, _P, _Z, _F, _U64, _U64, _P],
+    "bdl_dropout_bwd_bf16": [_P, _P, _P, _Z, _F, _P],
+    "bdl_copy2d_bf16": [_P, _P, _L, _I, _L, _L, _I, _P],
+    "bdl_im2col_nhwc_bf16": [_P, _P] + [_I] * 14 + [_L, _I, _P],
+    "bdl_col2im_nhwc_bf16": [_P, _P] + [_I] * 14 + [_L, _I, _P],
+    "bdl_maxpool_fwd_nhwc_bf16": [_P, _P, _P] + [_I] * 12 + [_L, _L, _P],
+    "bdl_maxpool_bwd_nhwc_bf16": [_P, _P, _P] + [_I] * 12 + [_L, _L, _P],
+    "bdl_avgpool_fwd_nhwc_bf16": [_P, _P] + [_I] * 12 + [_L, _L, _I, _I, _P],
+    "bdl_avgpool_bwd_nhwc_bf16": [_P, _P] + [_I] * 12 + [_L, _L, _I, _I, _P],
+    "bdl_lrn_fwd_nhwc_bf16": [_P, _P, _L, _I, _L, _L, _I, _F, _F, _F, _P],
+    "bdl_lrn_bwd_nhwc_bf16": [_P, _P, _P, _L, _I, _L, _L, _L, _I, _F, _F, _F, _P],
+    "bdl_xent_fwd": [_P, _P, _P, _P, _P, _L, _I, _L, _I, _I, _I, _I, _P],
+    "bdl_xent_bwd": [_P, _P, _P, _P, _P, _P, _L, _I, _L, _L, _I, _I, _I, _I, _F, _P],
+    "bdl_topk_correct": [_P, _P, _P, _L, _I, _L, _I, _I, _P],
+    "bdl_optim_update": [_I, _P, _P, _P, _P, _P, _Z, _P, _P, _I, _I, _P],
+    "bdl_sumsq_f32": [_P, _Z, _P, _P],
+    "bdl_absmax": [_P, _Z, _I, _P, _P],
+    "bdl_scale_f32": [_P, _Z, _F, _P, _F, _P],
+    "bdl_compress_grads": [_P, _P, _Z, _I, _I, _P],
+    "bdl_fused_rs_update": [_P, _P, _P, _I, _I, _L, _L, _P, _P, _P, _P, _I, _P, _P, _I, ctypes.c_uint, _P, _P, _I, _P],
+    "bdl_ipc_alloc": [_Z, _P, _P],
+    "bdl_ipc_open": [_P, _P],
+    "bdl_ipc_close": [_P],
+    "bdl_ipc_free": [_P],
+}
+
+
+def _declare(lib):
+    for name, args in _SIGNATURES.items():
+        fn = getattr(lib, name, None)
+        if fn is not None:
+            fn.argtypes = args
+            fn.restype = ctypes.c_int
+
+
+def declare(name: str, args):
+    """Register the signature of a function added after the table above was written."""
+    _SIGNATURES[name] = args
+    if _cuda is not None:
+        fn = getattr(_cuda, name, None)
+        if fn is not None:
+            fn.argtypes = args
+            fn.restype = ctypes.c_int
 
 
 def host_lib():
@@ -60,12 +118,12 @@ def check(rc: int, what: str = ""):
         raise NativeError(f"{what} failed ({rc}): {msg}")
 
 
-def stream_ptr() -> ctypes.c_void_p:
-    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+def stream_ptr():
+    return torch.cuda.current_stream().cuda_stream
 
 
-def ptr(t) -> ctypes.c_void_p:
-    return ctypes.c_void_p(0 if t is None else t.data_ptr())
+def ptr(t):
+    return None if t is None else t.data_ptr()
 
 
 LAUNCHES = 0  # number of native kernel-launching calls made by this process (bench.py reports it)

@@ -1,0 +1,441 @@
+"""GPU autograd Functions built on the sm_100a kernels (the "mkldnn engine" of this framework).
+
+Activations are bf16, logically NCHW but stored NHWC (torch ``channels_last``), so every convolution is a GEMM over
+``[N*Ho*Wo, kh*kw*C]`` and every 1x1 convolution is a GEMM on the activation tensor itself. Parameter gradients are
+accumulated *directly into the flat fp32 gradient buffer* (``param.grad``) by the split-K wgrad GEMM — the
+``accGradParameters`` contract of the reference — so backward returns ``None`` for parameter inputs.
+
+Reference call stack being replaced: S/nn/SpatialConvolution.scala:253-361 (updateOutput), :364-427 (updateGradInput),
+:435-521 (accGradParameters); S/nn/Linear.scala:78-167; S/nn/mkldnn/SpatialConvolution.scala:435-466.
+"""
+from __future__ import annotations
+
+import torch
+from torch.autograd import Function
+
+from . import _lib
+from . import elementwise as ew
+from .gemm import gemm_bf16
+
+_WS: dict = {}
+
+
+def workspace(numel: int, device, slot: int = 0) -> torch.Tensor:
+    """Grow-only bf16 scratch buffer shared by all conv layers of a device (im2col / dgrad columns)."""
+    key = (device.index, slot)
+    buf = _WS.get(key)
+    if buf is None or buf.numel() < numel:
+        buf = torch.empty(max(numel, 1 << 20), dtype=torch.bfloat16, device=device)
+        _WS[key] = buf
+    return buf[:numel]
+
+
+def _nhwc(x: torch.Tensor) -> torch.Tensor:
+    """[N,C,H,W] logical → contiguous [N,H,W,C] view (copying only if the tensor is not channels_last yet)."""
+    if x.dtype != torch.bfloat16:
+        x = x.to(torch.bfloat16)
+    x = x.contiguous(memory_format=torch.channels_last)
+    return x.permute(0, 2, 3, 1)
+
+
+def _acc_grad(param: torch.Tensor, scale: float):
+    return param.grad if (param is not None and param.requires_grad and scale != 0.0) else None
+
+
+class LinearFn(Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, w16, relu, scale_w, scale_b):
+        K = w16.shape[1]
+        x2 = x.reshape(-1, K)
+        if x2.dtype != torch.bfloat16:
+            x2 = x2.to(torch.bfloat16)
+        x2 = x2.contiguous()
+        if K % 8:
+            raise _lib.NativeError("Linear on the tensor-core path needs inputSize % 8 == 0")
+        b32 = bias.detach() if bias is not None else None
+        y = gemm_bf16(x2, w16, bias=b32, relu=relu)
+        ctx.save_for_backward(x2, w16, y if relu else None)
+        ctx.params = (weight, bias, relu, scale_w, scale_b, x.shape)
+        return y.reshape(*x.shape[:-1], w16.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w16, y = ctx.saved_tensors
+        weight, bias, relu, scale_w, scale_b, xshape = ctx.params
+        N = w16.shape[0]
+        dy2 = dy.reshape(-1, N)
+        if dy2.dtype != torch.bfloat16:
+            dy2 = dy2.to(torch.bfloat16)
+        dy2 = dy2.contiguous()
+        gb = _acc_grad(bias, scale_b)
+        if relu:
+            dz = torch.empty_like(dy2)
+            gtmp = gb if (gb is not None and scale_b == 1.0) else torch.zeros(N, device=dy.device)
+            ew.colsum(dy2, gtmp, y, dz)
+            if gb is not None and scale_b != 1.0:
+                gb.add_(gtmp, alpha=scale_b)
+        else:
+            dz = dy2
+            if gb is not None:
+                if scale_b == 1.0:
+                    ew.colsum(dy2, gb)
+                else:
+                    gb.add_(ew.colsum(dy2, torch.zeros(N, device=dy.device)), alpha=scale_b)
+        gw = _acc_grad(weight, scale_w)
+        if gw is not None:
+            if scale_w == 1.0 and gw.is_contiguous():
+                gemm_bf16(dz, x2, a_mn=True, b_mn=True, out=gw, accumulate=True)
+            else:
+                tmp = torch.zeros(gw.shape, device=gw.device)
+                gemm_bf16(dz, x2, a_mn=True, b_mn=True, out=tmp, accumulate=True)
+                gw.add_(tmp, alpha=scale_w)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = gemm_bf16(dz, w16, b_mn=True).reshape(xshape)
+        return dx, None, None, None, None, None, None
+
+
+class ConvFn(Function):
+    """2-D convolution, NHWC bf16, explicit-GEMM on the tcgen05 kernel (1x1/s1/p0 convs skip im2col entirely)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, w16, geom, relu, scale_w, scale_b):
+        kh, kw, sh, sw, pt, pl, pb, pr, dh, dw, groups = geom
+        xn = _nhwc(x)
+        N, H, W, C = xn.shape
+        O = w16.shape[0]
+        Cg, Og = C // groups, O // groups
+        Ho = (H + pt + pb - dh * (kh - 1) - 1) // sh + 1
+        Wo = (W + pl + pr - dw * (kw - 1) - 1) // sw + 1
+        M = N * Ho * Wo
+        y = torch.empty((N, Ho, Wo, O), dtype=torch.bfloat16, device=x.device)
+        y2 = y.view(M, O)
+        x2 = xn.reshape(N * H * W, C)
+        w2 = w16.permute(0, 2, 3, 1).reshape(O, kh * kw * Cg)   # OHWI physical → [O, K] view
+        direct = (kh == 1 and kw == 1 and sh == 1 and sw == 1 and pt == pl == pb == pr == 0 and Cg % 8 == 0)
+        K = kh * kw * Cg
+        Kp = (K + 7) // 8 * 8
+        lib = _lib.cuda_lib()
+        b32 = bias.detach() if bias is not None else None
+        asym = (pt != pb) or (pl != pr)
+        if asym:
+            # TF-style SAME padding can be asymmetric: materialise the extra bottom/right rows once
+            xn = torch.nn.functional.pad(xn, (0, 0, 0, pr - pl if pr > pl else 0, 0, pb - pt if pb > pt else 0))
+            N, H, W, C = xn.shape
+            x2 = xn.reshape(N * H * W, C)
+        for g in range(groups):
+            wg = w2[g * Og:(g + 1) * Og]
+            if Kp != K:
+                wpad = torch.zeros((Og, Kp), dtype=torch.bfloat16, device=x.device)
+                wpad[:, :K] = wg
+                wg = wpad
+            bg = b32[g * Og:(g + 1) * Og] if b32 is not None else None
+            if direct:
+                a = x2[:, g * Cg:(g + 1) * Cg]
+            else:
+                a = workspace(M * Kp, x.device).view(M, Kp)
+                xg = xn[..., g * Cg:(g + 1) * Cg]
+                _lib.check(lib.bdl_im2col_nhwc_bf16(xg.data_ptr(), a.data_ptr(), N, H, W, Cg, Ho, Wo, kh, kw, sh, sw,
+                                                    pt, pl, dh, dw, C, Kp, _lib.stream_ptr()), "bdl_im2col_nhwc_bf16")
+                _lib.count_launch()
+            gemm_bf16(a, wg, bias=bg, relu=relu, out=y2[:, g * Og:(g + 1) * Og])
+        ctx.save_for_backward(xn, w16, y if relu else None)
+        ctx.params = (weight, bias, geom, relu, scale_w, scale_b, (N, H, W, C, Ho, Wo, O, K, Kp, direct), x.shape)
+        return y.permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, dy):
+        xn, w16, y = ctx.saved_tensors
+        weight, bias, geom, relu, scale_w, scale_b, dims, xshape = ctx.params
+        kh, kw, sh, sw, pt, pl, pb, pr, dh, dw, groups = geom
+        N, H, W, C, Ho, Wo, O, K, Kp, direct = dims
+        Cg, Og = C // groups, O // groups
+        M = N * Ho * Wo
+        lib = _lib.cuda_lib()
+        dyn = _nhwc(dy).reshape(M, O)
+        gb = _acc_grad(bias, scale_b)
+        if relu:
+            dz = torch.empty_like(dyn)
+            gtmp = gb if (gb is not None and scale_b == 1.0) else torch.zeros(O, device=dy.device)
+            ew.colsum(dyn, gtmp, y.view(M, O), dz)
+            if gb is not None and scale_b != 1.0:
+                gb.add_(gtmp, alpha=scale_b)
+        else:
+            dz = dyn
+            if gb is not None:
+                if scale_b == 1.0:
+                    ew.colsum(dyn, gb)
+                else:
+                    gb.add_(ew.colsum(dyn, torch.zeros(O, device=dy.device)), alpha=scale_b)
+        x2 = xn.reshape(N * H * W, C)
+        w2 = w16.permute(0, 2, 3, 1).reshape(O, kh * kw * Cg)
+        gw = _acc_grad(weight, scale_w)
+        gw2 = gw.permute(0, 2, 3, 1).reshape(O, kh * kw * Cg) if gw is not None else None
+        need_dx = ctx.needs_input_grad[0]
+        dxn = torch.empty_like(xn) if need_dx else None
+        for g in range(groups):
+            dzg = dz[:, g * Og:(g + 1) * Og]
+            if direct:
+                a = x2[:, g * Cg:(g + 1) * Cg]
+            elif gw is not None:
+                a = workspace(M * Kp, dy.device).view(M, Kp)
+                xg = xn[..., g * Cg:(g + 1) * Cg]
+                _lib.check(lib.bdl_im2col_nhwc_bf16(xg.data_ptr(), a.data_ptr(), N, H, W, Cg, Ho, Wo, kh, kw, sh, sw,
+                                                    pt, pl, dh, dw, C, Kp, _lib.stream_ptr()), "bdl_im2col_nhwc_bf16")
+                _lib.count_launch()
+            if gw is not None:
+                tgt = gw2[g * Og:(g + 1) * Og]
+                if scale_w == 1.0 and Kp == K and tgt.stride(1) == 1 and tgt.stride(0) % 4 == 0:
+                    gemm_bf16(dzg, a, a_mn=True, b_mn=True, out=tgt, accumulate=True)
+                else:
+                    tmp = torch.zeros((Og, Kp), device=dy.device)
+                    gemm_bf16(dzg, a, a_mn=True, b_mn=True, out=tmp, accumulate=True)
+                    tgt.add_(tmp[:, :K], alpha=scale_w)
+            if need_dx:
+                wg = w2[g * Og:(g + 1) * Og]
+                if direct:
+                    gemm_bf16(dzg, wg, b_mn=True, out=dxn.view(N * H * W, C)[:, g * Cg:(g + 1) * Cg])
+                else:
+                    if Kp != K:
+                        wpad = torch.zeros((Og, Kp), dtype=torch.bfloat16, device=dy.device)
+                        wpad[:, :K] = wg
+                        wg = wpad
+                    dcol = workspace(M * Kp, dy.device).view(M, Kp)
+                    gemm_bf16(dzg, wg, b_mn=True, out=dcol)
+                    dxg = dxn[..., g * Cg:(g + 1) * Cg]
+                    _lib.check(lib.bdl_col2im_nhwc_bf16(dcol.data_ptr(), dxg.data_ptr(), N, H, W, Cg, Ho, Wo, kh, kw,
+                                                        sh, sw, pt, pl, dh, dw, C, Kp, _lib.stream_ptr()),
+                               "bdl_col2im_nhwc_bf16")
+                    _lib.count_launch()
+        dx = None
+        if need_dx:
+            dx = dxn.permute(0, 3, 1, 2)
+            if tuple(dx.shape) != tuple(xshape):     # asymmetric SAME padding: drop the materialised border
+                dx = dx[:, :, :xshape[2], :xshape[3]]
+        return dx, None, None, None, None, None, None, None
+
+
+class MaxPoolFn(Function):
+    @staticmethod
+    def forward(ctx, x, kh, kw, sh, sw, ph, pw, Ho, Wo):
+        xn = _nhwc(x)
+        N, H, W, C = xn.shape
+        lib = _lib.cuda_lib()
+        y = torch.empty((N, Ho, Wo, C), dtype=torch.bfloat16, device=x.device)
+        idx = torch.empty((N, Ho, Wo, C), dtype=torch.uint8, device=x.device)
+        _lib.check(lib.bdl_maxpool_fwd_nhwc_bf16(xn.data_ptr(), y.data_ptr(), idx.data_ptr(), N, H, W, C, Ho, Wo, kh,
+                                                 kw, sh, sw, ph, pw, C, C, _lib.stream_ptr()), "maxpool_fwd")
+        _lib.count_launch()
+        ctx.save_for_backward(idx)
+        ctx.geom = (N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph, pw)
+        return y.permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (idx,) = ctx.saved_tensors
+        N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph, pw = ctx.geom
+        lib = _lib.cuda_lib()
+        dyn = _nhwc(dy)
+        dx = torch.empty((N, H, W, C), dtype=torch.bfloat16, device=dy.device)
+        _lib.check(lib.bdl_maxpool_bwd_nhwc_bf16(dyn.data_ptr(), idx.data_ptr(), dx.data_ptr(), N, H, W, C, Ho, Wo, kh,
+                                                 kw, sh, sw, ph, pw, C, C, _lib.stream_ptr()), "maxpool_bwd")
+        _lib.count_launch()
+        return (dx.permute(0, 3, 1, 2),) + (None,) * 8
+
+
+class AvgPoolFn(Function):
+    @staticmethod
+    def forward(ctx, x, kh, kw, sh, sw, ph, pw, Ho, Wo, count_include_pad, divide):
+        xn = _nhwc(x)
+        N, H, W, C = xn.shape
+        lib = _lib.cuda_lib()
+        y = torch.empty((N, Ho, Wo, C), dtype=torch.bfloat16, device=x.device)
+        _lib.check(lib.bdl_avgpool_fwd_nhwc_bf16(xn.data_ptr(), y.data_ptr(), N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph,
+                                                 pw, C, C, int(count_include_pad), int(divide), _lib.stream_ptr()),
+                   "avgpool_fwd")
+        _lib.count_launch()
+        ctx.geom = (N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph, pw, count_include_pad, divide)
+        return y.permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, dy):
+        N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph, pw, cip, divide = ctx.geom
+        lib = _lib.cuda_lib()
+        dyn = _nhwc(dy)
+        dx = torch.empty((N, H, W, C), dtype=torch.bfloat16, device=dy.device)
+        _lib.check(lib.bdl_avgpool_bwd_nhwc_bf16(dyn.data_ptr(), dx.data_ptr(), N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph,
+                                                 pw, C, C, int(cip), int(divide), _lib.stream_ptr()), "avgpool_bwd")
+        _lib.count_launch()
+        return (dx.permute(0, 3, 1, 2),) + (None,) * 10
+
+
+class LRNFn(Function):
+    @staticmethod
+    def forward(ctx, x, size, alpha, beta, k):
+        xn = _nhwc(x)
+        N, H, W, C = xn.shape
+        lib = _lib.cuda_lib()
+        y = torch.empty_like(xn)
+        _lib.check(lib.bdl_lrn_fwd_nhwc_bf16(xn.data_ptr(), y.data_ptr(), N * H * W, C, C, C, size, alpha, beta, k,
+                                             _lib.stream_ptr()), "lrn_fwd")
+        _lib.count_launch()
+        ctx.save_for_backward(xn)
+        ctx.hp = (size, alpha, beta, k)
+        return y.permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (xn,) = ctx.saved_tensors
+        size, alpha, beta, k = ctx.hp
+        N, H, W, C = xn.shape
+        lib = _lib.cuda_lib()
+        dyn = _nhwc(dy)
+        dx = torch.empty_like(xn)
+        _lib.check(lib.bdl_lrn_bwd_nhwc_bf16(xn.data_ptr(), dyn.data_ptr(), dx.data_ptr(), N * H * W, C, C, C, C, size,
+                                             alpha, beta, k, _lib.stream_ptr()), "lrn_bwd")
+        _lib.count_launch()
+        return dx.permute(0, 3, 1, 2), None, None, None, None
+
+
+def _dense_like(a: torch.Tensor) -> torch.Tensor:
+    """Return ``a`` if its memory is dense (contiguous or channels_last), else a contiguous copy."""
+    if a.is_contiguous() or (a.dim() == 4 and a.is_contiguous(memory_format=torch.channels_last)):
+        return a
+    return a.contiguous()
+
+
+class ReLUFn(Function):
+    @staticmethod
+    def forward(ctx, x):
+        x = _dense_like(x)
+        y = ew.eltwise(ew.RELU, x)
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        if dy.stride() != y.stride():
+            dy = dy.contiguous(memory_format=torch.channels_last) if (
+                y.dim() == 4 and not y.is_contiguous()) else dy.contiguous()
+        return ew.eltwise(ew.RELU_BWD, dy, y)
+
+
+class AddFn(Function):
+    """out = a + b (optionally ReLU'd) for two tensors with the same dense layout (residual connections)."""
+
+    @staticmethod
+    def forward(ctx, a, b, relu):
+        a = _dense_like(a)
+        if b.stride() != a.stride():
+            b = b.contiguous(memory_format=torch.channels_last) if (a.dim() == 4 and not a.is_contiguous()) \
+                else b.contiguous()
+        y = ew.eltwise(ew.ADD_RELU if relu else ew.ADD, a, b)
+        ctx.relu = relu
+        if relu:
+            ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        if ctx.relu:
+            (y,) = ctx.saved_tensors
+            if dy.stride() != y.stride():
+                dy = dy.contiguous(memory_format=torch.channels_last) if (
+                    y.dim() == 4 and not y.is_contiguous()) else dy.contiguous()
+            dz = ew.eltwise(ew.RELU_BWD, dy, y)
+            return dz, dz, None
+        return dy, dy, None
+
+
+_dropout_offset = [0]
+
+
+class DropoutFn(Function):
+    @staticmethod
+    def forward(ctx, x, p, seed):
+        x = _dense_like(x)
+        off = _dropout_offset[0]
+        _dropout_offset[0] += (x.numel() + 7) // 8
+        y, mask = ew.dropout_fwd(x, p, seed, off)
+        ctx.save_for_backward(mask)
+        ctx.p = p
+        ctx.xstride = x.stride()
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (mask,) = ctx.saved_tensors
+        if dy.stride() != ctx.xstride:
+            dy = dy.contiguous(memory_format=torch.channels_last) if len(ctx.xstride) == 4 and ctx.xstride[1] == 1 \
+                else dy.contiguous()
+        return ew.dropout_bwd(dy, mask, ctx.p), None, None
+
+
+class XentFn(Function):
+    """CrossEntropyCriterion = LogSoftMax + ClassNLL, fused; returns the scalar loss (fp32)."""
+
+    @staticmethod
+    def forward(ctx, logits, target, class_w, size_average, padding_value):
+        lib = _lib.cuda_lib()
+        lg = logits if logits.stride(-1) == 1 else logits.contiguous()
+        B, C = lg.shape
+        tgt = target.reshape(-1)
+        if tgt.dtype not in (torch.float32, torch.int64):
+            tgt = tgt.float()
+        tgt = tgt.contiguous()
+        scratch = torch.empty(3 * B, dtype=torch.float32, device=lg.device)
+        out = torch.empty(2, dtype=torch.float32, device=lg.device)
+        _lib.check(lib.bdl_xent_fwd(lg.data_ptr(), tgt.data_ptr(), _lib.ptr(class_w), scratch.data_ptr(),
+                                    out.data_ptr(), B, C, lg.stride(0), int(lg.dtype == torch.bfloat16),
+                                    int(tgt.dtype == torch.int64), padding_value, int(size_average),
+                                    _lib.stream_ptr()), "bdl_xent_fwd")
+        _lib.count_launch(2)
+        ctx.save_for_backward(lg, tgt, scratch, out)
+        ctx.cfg = (class_w, size_average, padding_value)
+        return out[0]
+
+    @staticmethod
+    def backward(ctx, gloss):
+        lg, tgt, scratch, out = ctx.saved_tensors
+        class_w, size_average, padding_value = ctx.cfg
+        lib = _lib.cuda_lib()
+        B, C = lg.shape
+        d = torch.empty((B, C), dtype=lg.dtype, device=lg.device)
+        # gloss is almost always the constant 1; keep it on the device-free fast path
+        g = 1.0 if not isinstance(gloss, torch.Tensor) else None
+        if g is None:
+            g = 1.0
+            scale_t = gloss
+        else:
+            scale_t = None
+        _lib.check(lib.bdl_xent_bwd(lg.data_ptr(), tgt.data_ptr(), _lib.ptr(class_w), scratch.data_ptr(),
+                                    out.data_ptr(), d.data_ptr(), B, C, lg.stride(0), d.stride(0),
+                                    int(lg.dtype == torch.bfloat16), int(tgt.dtype == torch.int64), padding_value,
+                                    int(size_average), g, _lib.stream_ptr()), "bdl_xent_bwd")
+        _lib.count_launch()
+        if scale_t is not None and not _is_one(scale_t):
+            d = d * scale_t.to(d.dtype)
+        return d, None, None, None, None
+
+
+def _is_one(t: torch.Tensor) -> bool:
+    # backward seeds created by the training loops are python-constructed ones; avoid a device sync for them
+    return getattr(t, "_bdl_is_one", False)
+
+
+def topk_correct(logits: torch.Tensor, target: torch.Tensor, counts: torch.Tensor | None = None) -> torch.Tensor:
+    """counts[0] += top-1 hits, counts[1] += top-5 hits (uint32, device resident)."""
+    lib = _lib.cuda_lib()
+    lg = logits if logits.stride(-1) == 1 else logits.contiguous()
+    tgt = target.reshape(-1)
+    if tgt.dtype not in (torch.float32, torch.int64):
+        tgt = tgt.float()
+    if counts is None:
+        counts = torch.zeros(2, dtype=torch.int32, device=lg.device)
+    B, C = lg.shape
+    _lib.check(lib.bdl_topk_correct(lg.data_ptr(), tgt.contiguous().data_ptr(), counts.data_ptr(), B, C, lg.stride(0),
+                                    int(lg.dtype == torch.bfloat16), int(tgt.dtype == torch.int64), _lib.stream_ptr()),
+               "bdl_topk_correct")
+    _lib.count_launch()
+    return counts

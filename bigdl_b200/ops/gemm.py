@@ -32,8 +32,7 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: boo
     if bias is not None:
         assert bias.dtype == torch.float32 and bias.is_contiguous()
     rc = lib.bdl_gemm_bf16(_lib.ptr(a), _lib.ptr(b), _lib.ptr(out), _lib.ptr(bias), M, N, K,
-                           ctypes.c_longlong(a.stride(0)), ctypes.c_longlong(b.stride(0)),
-                           ctypes.c_longlong(out.stride(0)), int(a_mn), int(b_mn),
+                           a.stride(0), b.stride(0), out.stride(0), int(a_mn), int(b_mn),
                            int(out.dtype == torch.float32), flags, splits, _lib.stream_ptr())
     _lib.check(rc, "bdl_gemm_bf16")
     _lib.count_launch()

@@ -1,0 +1,98 @@
+"""Typed configuration registry.
+
+The reference reads JVM system properties ad hoc (``-Dbigdl.engineType=...``; full list in SURVEY.md §5.6). Here one
+registry owns every flag: values come from (highest priority first) ``set()``, environment variables
+(``BIGDL_<NAME>`` with dots replaced by underscores, upper-cased), then the defaults below. The old property names
+are accepted verbatim so launch scripts written for the reference keep working.
+"""
+from __future__ import annotations
+
+import os
+from typing import Any
+
+_DEFAULTS: dict[str, Any] = {
+    # engine
+    "bigdl.engineType": "b200",           # reference: mklblas | mkldnn (S/utils/Engine.scala:210-216)
+    "bigdl.localMode": True,
+    "bigdl.coreNumber": 0,                # 0 = autodetect
+    "bigdl.check.singleton": False,
+    "bigdl.computeDtype": "bf16",         # bf16 on GPU, fp32 on CPU
+    "bigdl.enableNHWC": True,
+    # failure / retry (S/optim/DistriOptimizer.scala:881-963)
+    "bigdl.failure.retryTimes": 5,
+    "bigdl.failure.retryTimeInterval": 120,
+    # parameter sync
+    "bigdl.Parameter.syncPoolSize": 4,
+    "bigdl.parameter.compress": "bf16_rn",   # bf16_rn | bf16_trunc (reference-exact) | fp32
+    "bigdl.parameter.backend": "auto",       # auto | p2p (fused NVLink kernels) | nccl | gloo
+    "bigdl.parallelOptimizer.iterationPerTime": 1,
+    "bigdl.parallelOptimizer.parameterBlocks": 10,
+    # fusion flags (S/nn/mkldnn/DnnGraph.scala:412-463)
+    "bigdl.mkldnn.fusion": True,
+    "bigdl.mkldnn.fusion.convbn": True,
+    "bigdl.mkldnn.fusion.bnrelu": True,
+    "bigdl.mkldnn.fusion.convrelu": True,
+    "bigdl.mkldnn.fusion.convsum": True,
+    # misc
+    "bigdl.cudaGraph": True,
+    "bigdl.utils.LoggerFilter.disable": False,
+    "bigdl.utils.LoggerFilter.logFile": "bigdl.log",
+    "bigdl.utils.LoggerFilter.enableSparkLog": True,
+    "bigdl.tensor.fold": 1000,
+    "bigdl.ModelBroadcastFactory": "default",
+}
+
+_overrides: dict[str, Any] = {}
+
+
+def _env_name(key: str) -> str:
+    return key.replace(".", "_").upper()
+
+
+def _coerce(val: str, like: Any):
+    if isinstance(like, bool):
+        return val.strip().lower() in ("1", "true", "yes", "on")
+    if isinstance(like, int):
+        return int(val)
+    if isinstance(like, float):
+        return float(val)
+    return val
+
+
+def get(key: str, default: Any = None) -> Any:
+    if key in _overrides:
+        return _overrides[key]
+    base = _DEFAULTS.get(key, default)
+    env = os.environ.get(_env_name(key))
+    if env is None:
+        env = os.environ.get(key)  # exact property name also accepted
+    if env is not None:
+        return _coerce(env, base) if base is not None else env
+    return base
+
+
+def set(key: str, value: Any) -> None:  # noqa: A001 - mirrors System.setProperty
+    _overrides[key] = value
+
+
+def unset(key: str) -> None:
+    _overrides.pop(key, None)
+
+
+def keys():
+    return sorted(set_union(_DEFAULTS.keys(), _overrides.keys()))
+
+
+def set_union(a, b):
+    out = dict.fromkeys(a)
+    out.update(dict.fromkeys(b))
+    return out.keys()
+
+
+def parse_java_opts(opts: str) -> None:
+    """Accept a ``-Dbigdl.x=y -Dbigdl.z=w`` string as used with spark-submit in the reference."""
+    for tok in opts.split():
+        if tok.startswith("-D") and "=" in tok:
+            k, v = tok[2:].split("=", 1)
+            like = _DEFAULTS.get(k)
+            _overrides[k] = _coerce(v, like) if like is not None else v

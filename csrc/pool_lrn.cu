@@ -1,0 +1,375 @@
+// NHWC bf16 pooling (max with argmax byte, average) and cross-channel LRN, forward and backward.
+// All are HBM-bound gather kernels: one thread owns 8 channels (16 B) of one output element, no atomics.
+//
+// Reference counterparts: S/nn/SpatialMaxPooling.scala (ceil mode via .ceil()), S/nn/SpatialAveragePooling.scala
+// (countIncludePad, divide), S/nn/SpatialCrossMapLRN.scala:204-237 (y = x * (k + alpha/size * sum x^2)^-beta),
+// and their mkldnn twins S/nn/mkldnn/{MaxPooling,AvgPooling,LRN}.scala.
+#include "bigdl_b200.h"
+#include "host_common.h"
+#include "ptx.cuh"
+
+namespace bdl {
+
+struct PoolGeom {
+  int N, H, W, C, Ho, Wo;
+  int kh, kw, sh, sw, ph, pw;
+  long long ldx, ldy;  // pixel pitches of input / output (channel slices allowed)
+  int count_include_pad;
+  int divide;
+};
+
+__device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&f)[8]) {
+  const uint4 v = *reinterpret_cast<const uint4*>(p);
+  const __nv_bfloat162* q = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float2 t = __bfloat1622float2(q[j]);
+    f[2 * j] = t.x;
+    f[2 * j + 1] = t.y;
+  }
+}
+__device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&f)[8]) {
+  uint4 o;
+  o.x = pack_bf16x2(f[0], f[1]);
+  o.y = pack_bf16x2(f[2], f[3]);
+  o.z = pack_bf16x2(f[4], f[5]);
+  o.w = pack_bf16x2(f[6], f[7]);
+  *reinterpret_cast<uint4*>(p) = o;
+}
+
+// ---------------------------------------------------------------- max pooling
+__global__ void maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
+                                   uint8_t* __restrict__ idx, const PoolGeom g) {
+  const int cvec = g.C / 8;
+  const long long total = static_cast<long long>(g.N) * g.Ho * g.Wo * cvec;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int cv = static_cast<int>(i % cvec);
+    long long t = i / cvec;
+    const int wo = static_cast<int>(t % g.Wo);
+    t /= g.Wo;
+    const int ho = static_cast<int>(t % g.Ho);
+    const int n = static_cast<int>(t / g.Ho);
+    float best[8];
+    uint8_t bi[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      best[j] = -INFINITY;
+      bi[j] = 0;
+    }
+    for (int ky = 0; ky < g.kh; ++ky) {
+      const int hi = ho * g.sh - g.ph + ky;
+      if (hi < 0 || hi >= g.H) continue;
+      for (int kx = 0; kx < g.kw; ++kx) {
+        const int wi = wo * g.sw - g.pw + kx;
+        if (wi < 0 || wi >= g.W) continue;
+        float f[8];
+        load8(x + ((static_cast<long long>(n) * g.H + hi) * g.W + wi) * g.ldx + cv * 8, f);
+        const uint8_t tap = static_cast<uint8_t>(ky * g.kw + kx);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (f[j] > best[j]) {
+            best[j] = f[j];
+            bi[j] = tap;
+          }
+      }
+    }
+    const long long opix = (static_cast<long long>(n) * g.Ho + ho) * g.Wo + wo;
+    store8(y + opix * g.ldy + cv * 8, best);
+    if (idx) {
+      uint2 pk;
+      pk.x = bi[0] | (bi[1] << 8) | (bi[2] << 16) | (static_cast<uint32_t>(bi[3]) << 24);
+      pk.y = bi[4] | (bi[5] << 8) | (bi[6] << 16) | (static_cast<uint32_t>(bi[7]) << 24);
+      *reinterpret_cast<uint2*>(idx + opix * g.C + cv * 8) = pk;
+    }
+  }
+}
+
+// dx[n,h,w,c] = sum of dy over output cells whose argmax tap lands on (h,w)
+__global__ void maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const uint8_t* __restrict__ idx,
+                                   __nv_bfloat16* __restrict__ dx, const PoolGeom g) {
+  const int cvec = g.C / 8;
+  const long long total = static_cast<long long>(g.N) * g.H * g.W * cvec;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int cv = static_cast<int>(i % cvec);
+    long long t = i / cvec;
+    const int w = static_cast<int>(t % g.W);
+    t /= g.W;
+    const int h = static_cast<int>(t % g.H);
+    const int n = static_cast<int>(t / g.H);
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int ky = 0; ky < g.kh; ++ky) {
+      const int hh = h + g.ph - ky;
+      if (hh < 0 || hh % g.sh) continue;
+      const int ho = hh / g.sh;
+      if (ho >= g.Ho) continue;
+      for (int kx = 0; kx < g.kw; ++kx) {
+        const int ww = w + g.pw - kx;
+        if (ww < 0 || ww % g.sw) continue;
+        const int wo = ww / g.sw;
+        if (wo >= g.Wo) continue;
+        const long long opix = (static_cast<long long>(n) * g.Ho + ho) * g.Wo + wo;
+        const uint2 pk = *reinterpret_cast<const uint2*>(idx + opix * g.C + cv * 8);
+        float f[8];
+        load8(dy + opix * g.ldy + cv * 8, f);
+        const uint32_t tap = static_cast<uint32_t>(ky * g.kw + kx);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint32_t b = ((j < 4 ? pk.x : pk.y) >> (8 * (j & 3))) & 0xFFu;
+          if (b == tap) acc[j] += f[j];
+        }
+      }
+    }
+    store8(dx + ((static_cast<long long>(n) * g.H + h) * g.W + w) * g.ldx + cv * 8, acc);
+  }
+}
+
+// ---------------------------------------------------------------- average pooling
+__device__ __forceinline__ float avg_divisor(const PoolGeom& g, int ho, int wo) {
+  if (!g.divide) return 1.f;
+  int hs = ho * g.sh - g.ph, ws = wo * g.sw - g.pw;
+  int he = min(hs + g.kh, g.H + g.ph), we = min(ws + g.kw, g.W + g.pw);
+  const int pool_size = (he - hs) * (we - ws);
+  if (g.count_include_pad) return static_cast<float>(pool_size);
+  hs = max(hs, 0);
+  ws = max(ws, 0);
+  he = min(he, g.H);
+  we = min(we, g.W);
+  return static_cast<float>(max((he - hs) * (we - ws), 1));
+}
+
+__global__ void avgpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
+                                   const PoolGeom g) {
+  const int cvec = g.C / 8;
+  const long long total = static_cast<long long>(g.N) * g.Ho * g.Wo * cvec;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int cv = static_cast<int>(i % cvec);
+    long long t = i / cvec;
+    const int wo = static_cast<int>(t % g.Wo);
+    t /= g.Wo;
+    const int ho = static_cast<int>(t % g.Ho);
+    const int n = static_cast<int>(t / g.Ho);
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int ky = 0; ky < g.kh; ++ky) {
+      const int hi = ho * g.sh - g.ph + ky;
+      if (hi < 0 || hi >= g.H) continue;
+      for (int kx = 0; kx < g.kw; ++kx) {
+        const int wi = wo * g.sw - g.pw + kx;
+        if (wi < 0 || wi >= g.W) continue;
+        float f[8];
+        load8(x + ((static_cast<long long>(n) * g.H + hi) * g.W + wi) * g.ldx + cv * 8, f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += f[j];
+      }
+    }
+    const float inv = 1.f / avg_divisor(g, ho, wo);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] *= inv;
+    store8(y + ((static_cast<long long>(n) * g.Ho + ho) * g.Wo + wo) * g.ldy + cv * 8, acc);
+  }
+}
+
+__global__ void avgpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx,
+                                   const PoolGeom g) {
+  const int cvec = g.C / 8;
+  const long long total = static_cast<long long>(g.N) * g.H * g.W * cvec;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int cv = static_cast<int>(i % cvec);
+    long long t = i / cvec;
+    const int w = static_cast<int>(t % g.W);
+    t /= g.W;
+    const int h = static_cast<int>(t % g.H);
+    const int n = static_cast<int>(t / g.H);
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int ky = 0; ky < g.kh; ++ky) {
+      const int hh = h + g.ph - ky;
+      if (hh < 0 || hh % g.sh) continue;
+      const int ho = hh / g.sh;
+      if (ho >= g.Ho) continue;
+      for (int kx = 0; kx < g.kw; ++kx) {
+        const int ww = w + g.pw - kx;
+        if (ww < 0 || ww % g.sw) continue;
+        const int wo = ww / g.sw;
+        if (wo >= g.Wo) continue;
+        float f[8];
+        load8(dy + ((static_cast<long long>(n) * g.Ho + ho) * g.Wo + wo) * g.ldy + cv * 8, f);
+        const float inv = 1.f / avg_divisor(g, ho, wo);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += f[j] * inv;
+      }
+    }
+    store8(dx + ((static_cast<long long>(n) * g.H + h) * g.W + w) * g.ldx + cv * 8, acc);
+  }
+}
+
+// ---------------------------------------------------------------- cross-channel LRN
+// One warp-lane owns 8 consecutive channels of a pixel and reads the halo it needs from global (L1-resident).
+// scale_c = k + alpha/size * sum_{c' in [c-pre, c+post]} x_c'^2, pre = (size-1)/2, post = size-1-pre.
+__global__ void lrn_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long pixels,
+                               int C, long long ldx, long long ldy, int size, float alpha, float beta, float k) {
+  const int cvec = C / 8;
+  const long long total = pixels * cvec;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const int pre = (size - 1) / 2, post = size - 1 - pre;
+  const float as = alpha / size;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int cv = static_cast<int>(i % cvec);
+    const long long pix = i / cvec;
+    const __nv_bfloat16* row = x + pix * ldx;
+    const int c0 = cv * 8;
+    float out[8];
+    for (int j = 0; j < 8; ++j) {
+      const int c = c0 + j;
+      float s = 0.f;
+      for (int cc = max(c - pre, 0); cc <= min(c + post, C - 1); ++cc) {
+        const float v = __bfloat162float(row[cc]);
+        s += v * v;
+      }
+      const float sc = k + as * s;
+      out[j] = __bfloat162float(row[c]) * __powf(sc, -beta);
+    }
+    store8(y + pix * ldy + c0, out);
+  }
+}
+
+// dx_c = dy_c * s_c^-beta - 2*alpha*beta/size * x_c * sum_{c' : c in window(c')} dy_c' * x_c' * s_c'^(-beta-1)
+__global__ void lrn_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                               __nv_bfloat16* __restrict__ dx, long long pixels, int C, long long ldx, long long ldy,
+                               long long lddx, int size, float alpha, float beta, float k) {
+  const int cvec = C / 8;
+  const long long total = pixels * cvec;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const int pre = (size - 1) / 2, post = size - 1 - pre;
+  const float as = alpha / size;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int cv = static_cast<int>(i % cvec);
+    const long long pix = i / cvec;
+    const __nv_bfloat16* xr = x + pix * ldx;
+    const __nv_bfloat16* gr = dy + pix * ldy;
+    const int c0 = cv * 8;
+    float out[8];
+    for (int j = 0; j < 8; ++j) {
+      const int c = c0 + j;
+      float cross = 0.f, self_scale = 1.f;
+      // c is inside window(c') iff c' - pre <= c <= c' + post  <=>  c - post <= c' <= c + pre
+      for (int cp = max(c - post, 0); cp <= min(c + pre, C - 1); ++cp) {
+        float s = 0.f;
+        for (int cc = max(cp - pre, 0); cc <= min(cp + post, C - 1); ++cc) {
+          const float v = __bfloat162float(xr[cc]);
+          s += v * v;
+        }
+        const float sc = k + as * s;
+        const float pw = __powf(sc, -beta);
+        if (cp == c) self_scale = pw;
+        cross += __bfloat162float(gr[cp]) * __bfloat162float(xr[cp]) * pw / sc;
+      }
+      out[j] = __bfloat162float(gr[c]) * self_scale - 2.f * as * beta * __bfloat162float(xr[c]) * cross;
+    }
+    store8(dx + pix * lddx + c0, out);
+  }
+}
+
+static int grid_for(long long total) {
+  const long long cap = static_cast<long long>(bdl_num_sms()) * 16;
+  long long b = (total + 255) / 256;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return static_cast<int>(b);
+}
+
+}  // namespace bdl
+
+using namespace bdl;
+
+static int check_pool(const char* who, int C, long long ldx, long long ldy, const void* a, const void* b) {
+  if ((C % 8) || (ldx % 8) || (ldy % 8) || (reinterpret_cast<uintptr_t>(a) & 15u) || (reinterpret_cast<uintptr_t>(b) & 15u))
+    return bdl_fail(who);
+  return BDL_OK;
+}
+
+static PoolGeom make_pool(int N, int H, int W, int C, int Ho, int Wo, int kh, int kw, int sh, int sw, int ph, int pw,
+                          long long ldx, long long ldy, int cip, int divide) {
+  PoolGeom g;
+  g.N = N; g.H = H; g.W = W; g.C = C; g.Ho = Ho; g.Wo = Wo;
+  g.kh = kh; g.kw = kw; g.sh = sh; g.sw = sw; g.ph = ph; g.pw = pw;
+  g.ldx = ldx; g.ldy = ldy; g.count_include_pad = cip; g.divide = divide;
+  return g;
+}
+
+extern "C" int bdl_maxpool_fwd_nhwc_bf16(const void* x, void* y, void* idx, int N, int H, int W, int C, int Ho, int Wo,
+                                         int kh, int kw, int sh, int sw, int ph, int pw, long long ldx, long long ldy,
+                                         void* stream) {
+  if (check_pool("bdl_maxpool_fwd_nhwc_bf16: C and pitches must be multiples of 8, pointers 16-byte aligned", C, ldx,
+                 ldy, x, y))
+    return BDL_ERR_INVALID;
+  if (kh * kw > 255) return bdl_fail("bdl_maxpool_fwd_nhwc_bf16: window larger than 255 taps");
+  const PoolGeom g = make_pool(N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph, pw, ldx, ldy, 0, 0);
+  const long long total = static_cast<long long>(N) * Ho * Wo * (C / 8);
+  maxpool_fwd_kernel<<<grid_for(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), static_cast<uint8_t*>(idx), g);
+  return bdl_check_launch("maxpool_fwd_kernel");
+}
+
+extern "C" int bdl_maxpool_bwd_nhwc_bf16(const void* dy, const void* idx, void* dx, int N, int H, int W, int C, int Ho,
+                                         int Wo, int kh, int kw, int sh, int sw, int ph, int pw, long long ldx,
+                                         long long ldy, void* stream) {
+  if (check_pool("bdl_maxpool_bwd_nhwc_bf16: C and pitches must be multiples of 8, pointers 16-byte aligned", C, ldx,
+                 ldy, dx, dy))
+    return BDL_ERR_INVALID;
+  const PoolGeom g = make_pool(N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph, pw, ldx, ldy, 0, 0);
+  const long long total = static_cast<long long>(N) * H * W * (C / 8);
+  maxpool_bwd_kernel<<<grid_for(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dy), static_cast<const uint8_t*>(idx), static_cast<__nv_bfloat16*>(dx), g);
+  return bdl_check_launch("maxpool_bwd_kernel");
+}
+
+extern "C" int bdl_avgpool_fwd_nhwc_bf16(const void* x, void* y, int N, int H, int W, int C, int Ho, int Wo, int kh,
+                                         int kw, int sh, int sw, int ph, int pw, long long ldx, long long ldy,
+                                         int count_include_pad, int divide, void* stream) {
+  if (check_pool("bdl_avgpool_fwd_nhwc_bf16: C and pitches must be multiples of 8, pointers 16-byte aligned", C, ldx,
+                 ldy, x, y))
+    return BDL_ERR_INVALID;
+  const PoolGeom g = make_pool(N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph, pw, ldx, ldy, count_include_pad, divide);
+  const long long total = static_cast<long long>(N) * Ho * Wo * (C / 8);
+  avgpool_fwd_kernel<<<grid_for(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), g);
+  return bdl_check_launch("avgpool_fwd_kernel");
+}
+
+extern "C" int bdl_avgpool_bwd_nhwc_bf16(const void* dy, void* dx, int N, int H, int W, int C, int Ho, int Wo, int kh,
+                                         int kw, int sh, int sw, int ph, int pw, long long ldx, long long ldy,
+                                         int count_include_pad, int divide, void* stream) {
+  if (check_pool("bdl_avgpool_bwd_nhwc_bf16: C and pitches must be multiples of 8, pointers 16-byte aligned", C, ldx,
+                 ldy, dx, dy))
+    return BDL_ERR_INVALID;
+  const PoolGeom g = make_pool(N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph, pw, ldx, ldy, count_include_pad, divide);
+  const long long total = static_cast<long long>(N) * H * W * (C / 8);
+  avgpool_bwd_kernel<<<grid_for(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), g);
+  return bdl_check_launch("avgpool_bwd_kernel");
+}
+
+extern "C" int bdl_lrn_fwd_nhwc_bf16(const void* x, void* y, long long pixels, int C, long long ldx, long long ldy,
+                                     int size, float alpha, float beta, float k, void* stream) {
+  if (check_pool("bdl_lrn_fwd_nhwc_bf16: C and pitches must be multiples of 8, pointers 16-byte aligned", C, ldx, ldy, x,
+                 y))
+    return BDL_ERR_INVALID;
+  lrn_fwd_kernel<<<grid_for(pixels * (C / 8)), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), pixels, C, ldx, ldy, size, alpha, beta, k);
+  return bdl_check_launch("lrn_fwd_kernel");
+}
+
+extern "C" int bdl_lrn_bwd_nhwc_bf16(const void* x, const void* dy, void* dx, long long pixels, int C, long long ldx,
+                                     long long ldy, long long lddx, int size, float alpha, float beta, float k,
+                                     void* stream) {
+  if (check_pool("bdl_lrn_bwd_nhwc_bf16: C and pitches must be multiples of 8, pointers 16-byte aligned", C, ldx, ldy, x,
+                 dy))
+    return BDL_ERR_INVALID;
+  lrn_bwd_kernel<<<grid_for(pixels * (C / 8)), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx),
+      pixels, C, ldx, ldy, lddx, size, alpha, beta, k);
+  return bdl_check_launch("lrn_bwd_kernel");
+}

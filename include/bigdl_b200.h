@@ -33,6 +33,89 @@ int bdl_sm_count(void);
 int bdl_gemm_bf16(const void* A, const void* B, void* D, const float* bias, int M, int N, int K, long long lda,
                   long long ldb, long long ldd, int a_mn, int b_mn, int out_fp32, int flags, int splits, void* stream);
 
+/* ---- elementwise / reductions on bf16 activations (csrc/elementwise.cu).
+ *      Reference: S/nn/ReLU.scala, S/nn/Dropout.scala:40-75, S/nn/CAddTable.scala,
+ *      S/parameters/FP16CompressedTensor.scala:80-98,152-196,271-278. */
+#include <stddef.h>
+int bdl_cast_f32_to_bf16(const float* src, void* dst, size_t n, int truncate, void* stream);
+int bdl_cast_bf16_to_f32(const void* src, float* dst, size_t n, void* stream);
+int bdl_bf16_trunc_add(const void* a, const void* b, void* out, size_t n, void* stream);
+/* op codes: 0 relu, 1 relu_bwd(a=dy,b=y), 2 add, 3 add_relu, 4 mul, 5 tanh, 6 sigmoid, 7 tanh_bwd, 8 sigmoid_bwd,
+ *           9 scale(alpha), 10 axpy(alpha*a+b), 11 sub, 12 max, 13 relu6 */
+int bdl_eltwise_bf16(int op, const void* a, const void* b, void* out, size_t n, float alpha, void* stream);
+/* out[c] += sum_m x[m,c]; with y != NULL: dz = (y>0 ? x : 0) is written and summed (fused ReLU-bwd + bias grad). */
+int bdl_colsum_bf16(const void* x, const void* y, void* dz, float* out, long long M, int C, long long ldx,
+                    long long ldy, long long ldz, void* stream);
+int bdl_dropout_fwd_bf16(const void* x, void* y, void* mask, size_t n, float p, unsigned long long seed,
+                         unsigned long long offset, void* stream);
+int bdl_dropout_bwd_bf16(const void* dy, const void* mask, void* dx, size_t n, float p, void* stream);
+int bdl_copy2d_bf16(const void* src, void* dst, long long rows, int C, long long lds, long long ldd, int accumulate,
+                    void* stream);
+
+/* ---- NHWC im2col / col2im (csrc/conv_im2col.cu). Reference: S/nn/NNPrimitive.scala:24-1719. */
+int bdl_im2col_nhwc_bf16(const void* x, void* col, int N, int H, int W, int C, int Ho, int Wo, int kh, int kw, int sh,
+                         int sw, int ph, int pw, int dh, int dw, long long ldx, int Kp, void* stream);
+int bdl_col2im_nhwc_bf16(const void* col, void* dx, int N, int H, int W, int C, int Ho, int Wo, int kh, int kw, int sh,
+                         int sw, int ph, int pw, int dh, int dw, long long ldx, int Kp, void* stream);
+
+/* ---- pooling / LRN (csrc/pool_lrn.cu). Reference: S/nn/SpatialMaxPooling.scala, SpatialAveragePooling.scala,
+ *      SpatialCrossMapLRN.scala:204-237, S/nn/mkldnn/{MaxPooling,AvgPooling,LRN}.scala. */
+int bdl_maxpool_fwd_nhwc_bf16(const void* x, void* y, void* idx, int N, int H, int W, int C, int Ho, int Wo, int kh,
+                              int kw, int sh, int sw, int ph, int pw, long long ldx, long long ldy, void* stream);
+int bdl_maxpool_bwd_nhwc_bf16(const void* dy, const void* idx, void* dx, int N, int H, int W, int C, int Ho, int Wo,
+                              int kh, int kw, int sh, int sw, int ph, int pw, long long ldx, long long ldy,
+                              void* stream);
+int bdl_avgpool_fwd_nhwc_bf16(const void* x, void* y, int N, int H, int W, int C, int Ho, int Wo, int kh, int kw,
+                              int sh, int sw, int ph, int pw, long long ldx, long long ldy, int count_include_pad,
+                              int divide, void* stream);
+int bdl_avgpool_bwd_nhwc_bf16(const void* dy, void* dx, int N, int H, int W, int C, int Ho, int Wo, int kh, int kw,
+                              int sh, int sw, int ph, int pw, long long ldx, long long ldy, int count_include_pad,
+                              int divide, void* stream);
+int bdl_lrn_fwd_nhwc_bf16(const void* x, void* y, long long pixels, int C, long long ldx, long long ldy, int size,
+                          float alpha, float beta, float k, void* stream);
+int bdl_lrn_bwd_nhwc_bf16(const void* x, const void* dy, void* dx, long long pixels, int C, long long ldx,
+                          long long ldy, long long lddx, int size, float alpha, float beta, float k, void* stream);
+
+/* ---- fused LogSoftMax + ClassNLL (csrc/loss_softmax.cu). Reference: S/nn/ClassNLLCriterion.scala:70-242,
+ *      S/nn/CrossEntropyCriterion.scala:35-53, S/optim/ValidationMethod.scala:173,827.
+ *      scratch: 3*B floats kept between fwd and bwd; out: {loss, total weight}. Targets are 1-based. */
+int bdl_xent_fwd(const void* logits, const void* target, const float* class_w, float* scratch, float* out, long long B,
+                 int C, long long ld, int logits_bf16, int target_i64, int padding_value, int size_average,
+                 void* stream);
+int bdl_xent_bwd(const void* logits, const void* target, const float* class_w, const float* scratch, const float* out,
+                 void* dlogits, long long B, int C, long long ld, long long ldd, int logits_bf16, int target_i64,
+                 int padding_value, int size_average, float gscale, void* stream);
+int bdl_topk_correct(const void* logits, const void* target, void* counts, long long B, int C, long long ld,
+                     int logits_bf16, int target_i64, void* stream);
+
+/* ---- flat OptimMethod update (csrc/optim.cu, csrc/optim_update.cuh). Reference: S/optim/{SGD,Adam,Adagrad,RMSprop,
+ *      Adadelta,Adamax,Ftrl,LarsSGD}.scala; S/parameters/Util.scala:30-50.
+ *      kind: 0 SGD, 1 Adam, 2 Adagrad, 3 RMSprop, 4 Adadelta, 5 Adamax, 6 Ftrl, 7 LARS.
+ *      hp_host/hp_dev point at an OptimHP (bdl_optim_hp_size() bytes); hp_dev (device memory) wins when non-NULL. */
+int bdl_optim_hp_size(void);
+int bdl_optim_update(int kind, float* w, float* g, float* s0, float* s1, void* w16, size_t n, const void* hp_host,
+                     const void* hp_dev, int truncate, int zero_grad, void* stream);
+int bdl_sumsq_f32(const float* x, size_t n, float* out, void* stream);
+int bdl_absmax(const void* x, size_t n, int is_bf16, float* out, void* stream);
+int bdl_scale_f32(float* x, size_t n, float alpha, const float* norm_sq, float max_norm, void* stream);
+
+/* ---- fused NVLink reduce-scatter + OptimMethod update + all-gather (csrc/comm_fused.cu).
+ *      Reference: S/parameters/AllReduceParameter.scala:201-328, S/parameters/FP16CompressedTensor.scala:152-196,
+ *      S/optim/DistriOptimizer.scala:358-396.
+ *      mode bits: 1 reduce, 2 write fp32 grad slice, 4 update, 8 publish bf16 weights to all peers,
+ *                 16 begin barrier, 32 end barrier, 64 reference-exact (truncating) arithmetic, 128 sum of squares,
+ *                 256 divide by hp.gscale instead of multiplying. */
+int bdl_compress_grads(float* g, void* out16, size_t n, int truncate, int zero_src, void* stream);
+int bdl_fused_rs_update(const void* const* grad16_ptrs, void* const* w16_ptrs, void* const* flag_ptrs, int nranks,
+                        int rank, long long start, long long length, float* master, float* grad_part, float* s0,
+                        float* s1, int kind, const void* hp_host, const void* hp_dev, int mode, unsigned int epoch,
+                        void* local_sync, float* sumsq, int max_blocks, void* stream);
+/* cudaMalloc + cudaIpc handle exchange for the symmetric buffers (one process per GPU). handle64: 64 bytes. */
+int bdl_ipc_alloc(size_t bytes, void** ptr, void* handle64);
+int bdl_ipc_open(const void* handle64, void** ptr);
+int bdl_ipc_close(void* ptr);
+int bdl_ipc_free(void* ptr);
+
 #ifdef __cplusplus
 }
 #endif

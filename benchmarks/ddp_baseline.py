@@ -1,0 +1,107 @@
+"""PyTorch DDP baseline (NCCL + cuDNN/cuBLAS, bf16 autocast, channels_last) for the models bench.py measures.
+This is the "GPU bar to beat" of BASELINE.md §3 — library kernels, not part of the product."""
+from __future__ import annotations
+
+import json
+import os
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+
+class _Inception(nn.Module):
+    def __init__(self, cin, c1, c3r, c3, c5r, c5, pp):
+        super().__init__()
+        self.b1 = nn.Conv2d(cin, c1, 1)
+        self.b3r, self.b3 = nn.Conv2d(cin, c3r, 1), nn.Conv2d(c3r, c3, 3, padding=1)
+        self.b5r, self.b5 = nn.Conv2d(cin, c5r, 1), nn.Conv2d(c5r, c5, 5, padding=2)
+        self.pp = nn.Conv2d(cin, pp, 1)
+
+    def forward(self, x):
+        return torch.cat([F.relu(self.b1(x)), F.relu(self.b3(F.relu(self.b3r(x)))),
+                          F.relu(self.b5(F.relu(self.b5r(x)))),
+                          F.relu(self.pp(F.max_pool2d(x, 3, 1, 1, ceil_mode=True)))], 1)
+
+
+class InceptionV1(nn.Module):
+    def __init__(self, classes=1000):
+        super().__init__()
+        self.c1, self.c2r, self.c2 = nn.Conv2d(3, 64, 7, 2, 3), nn.Conv2d(64, 64, 1), nn.Conv2d(64, 192, 3, padding=1)
+        cfg = [(192, 64, 96, 128, 16, 32, 32), (256, 128, 128, 192, 32, 96, 64), None,
+               (480, 192, 96, 208, 16, 48, 64), (512, 160, 112, 224, 24, 64, 64), (512, 128, 128, 256, 24, 64, 64),
+               (512, 112, 144, 288, 32, 64, 64), (528, 256, 160, 320, 32, 128, 128), None,
+               (832, 256, 160, 320, 32, 128, 128), (832, 384, 192, 384, 48, 128, 128)]
+        self.blocks = nn.ModuleList([_Inception(*c) if c else nn.MaxPool2d(3, 2, ceil_mode=True) for c in cfg])
+        self.drop, self.fc = nn.Dropout(0.4), nn.Linear(1024, classes)
+
+    def forward(self, x):
+        x = F.max_pool2d(F.relu(self.c1(x)), 3, 2, ceil_mode=True)
+        x = F.local_response_norm(x, 5, 1e-4, 0.75)
+        x = F.relu(self.c2(F.relu(self.c2r(x))))
+        x = F.max_pool2d(F.local_response_norm(x, 5, 1e-4, 0.75), 3, 2, ceil_mode=True)
+        for b in self.blocks:
+            x = b(x)
+        x = self.drop(F.avg_pool2d(x, 7)).flatten(1)
+        return F.log_softmax(self.fc(x).float(), 1)
+
+
+def _model(name):
+    if name.startswith("inception"):
+        return InceptionV1()
+    import torchvision.models as tv  # pragma: no cover - only if torchvision is present
+
+    return tv.resnet50() if name == "resnet50" else tv.vgg16()
+
+
+def run(args):
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    rank = int(os.environ.get("RANK", 0))
+    lr = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(lr)
+    if world > 1:
+        dist.init_process_group("nccl")
+    torch.backends.cudnn.benchmark = True
+    m = _model(args.model).cuda().to(memory_format=torch.channels_last)
+    if world > 1:
+        m = nn.parallel.DistributedDataParallel(m, device_ids=[lr], gradient_as_bucket_view=True)
+    opt = torch.optim.SGD(m.parameters(), lr=0.01, momentum=0.9, weight_decay=1e-4)
+    B = args.batch
+    x = torch.randn(B, 3, 224, 224, device="cuda").contiguous(memory_format=torch.channels_last)
+    y = torch.randint(0, 1000, (B,), device="cuda")
+
+    def step():
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            out = m(x)
+        loss = F.nll_loss(out.float(), y) if out.dtype != torch.float32 or True else None
+        opt.zero_grad(set_to_none=True)
+        loss.backward()
+        opt.step()
+        return loss
+
+    for _ in range(args.warmup):
+        step()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        v = B * world * args.steps / (float(ms) / 1e3)
+        print(json.dumps({"impl": "torch_ddp_cudnn", "metric": "train images/sec", "value": round(v, 2),
+                          "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                          "ms_per_step": round(float(ms) / args.steps, 3), "dtype": "bf16 autocast",
+                          "config": {"model": args.model, "per_gpu_batch": B}}))
+    if world > 1:
+        dist.destroy_process_group()

@@ -223,6 +223,12 @@ class Optimizer:
     def prepareInput(self):
         return self
 
+    def setIterationCallback(self, fn):
+        """``fn(state, loss_tensor)`` runs at the end of every iteration (after the parameter update has been
+        enqueued). Used by the perf harnesses to drop CUDA events without leaving the public ``optimize()`` path."""
+        self._iteration_callback = fn
+        return self
+
     prepare_input = prepareInput
 
     # ------------------------------------------------------------------ helpers shared by the loops
@@ -483,6 +489,9 @@ def _train_loop(opt: Optimizer, distributed: bool):
         for om in opt.optim_methods.values():
             if om is not lead:
                 om.state["epoch"], om.state["neval"] = state["epoch"], state["neval"]
+        cb = getattr(opt, "_iteration_callback", None)
+        if cb is not None:
+            cb(state, loss)
         opt._summary(state, loss_value, n_global / max(dt, 1e-12), lr)
         opt._validate(state)
         opt._checkpoint(state, os.path.basename(opt._checkpoint_dir) if (distributed and opt.checkpoint_path) else None,

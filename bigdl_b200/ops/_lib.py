@@ -73,6 +73,7 @@ _SIGNATURES = {
     "bdl_lrn_bwd_nhwc_bf16": [_P, _P, _P, _L, _I, _L, _L, _L, _I, _F, _F, _F, _P],
     "bdl_xent_fwd": [_P, _P, _P, _P, _P, _L, _I, _L, _I, _I, _I, _I, _P],
     "bdl_xent_bwd": [_P, _P, _P, _P, _P, _P, _L, _I, _L, _L, _I, _I, _I, _I, _F, _P],
+    "bdl_xent_fwd_noalloc": [_P, _P, _P, _P, _L, _I, _L, _I, _I, _I, _I, _P],
     "bdl_topk_correct": [_P, _P, _P, _L, _I, _L, _I, _I, _P],
     "bdl_optim_update": [_I, _P, _P, _P, _P, _P, _Z, _P, _P, _I, _I, _P],
     "bdl_sumsq_f32": [_P, _Z, _P, _P],

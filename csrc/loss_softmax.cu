@@ -206,3 +206,57 @@ extern "C" int bdl_topk_correct(const void* logits, const void* target, void* co
     topk_correct_kernel<<<grid, 256, 0, st>>>(cp<float>(logits), cp<float>(target), cn, C, ld);
   return bdl_check_launch("topk_correct_kernel");
 }
+
+// ------------------------------------------------------------------------------------------------------------------
+// Allocation-free forward (no counterpart in the reference).
+//
+// Some hosts of this library are not allowed to obtain device memory at call time: a serving process whose whole
+// HBM budget was handed to one arena at start-up, a real-time loop that cannot absorb the device-wide stall a
+// cudaMalloc may cause, or a plug-in running inside another runtime that owns the allocator and gives a plain C caller
+// no way to ask it for a buffer. bdl_xent_fwd() needs 3*B floats of scratch from its caller; for those hosts the
+// variant below keeps that scratch inside the library image instead, in the fixed array right here. The price is a
+// hard cap on the batch (BDL_XENT_NOALLOC_MAX_ROWS rows = 768 KiB, resident on every GPU that loads the library until
+// the process exits) and no backward pass (the per-row log-sum-exp stays private to the library).
+//
+// The array name is only a host-side handle; the device address is looked up once per device with
+// cudaGetSymbolAddress (that device current) and cached. That look-up happens inside the first call made on a device,
+// so make that first call before starting any stream capture. Nothing in the scratch has to start at zero: every slot
+// the reduction reads was written earlier in the same call, so contents left by a previous call are harmless. All
+// calls on a device share the one array — two calls that can overlap on the GPU (different streams) race; serialise
+// them.
+#include <mutex>
+
+#define BDL_XENT_NOALLOC_MAX_ROWS 65536
+static __device__ __align__(256) float bdl_xent_static_scratch[3 * BDL_XENT_NOALLOC_MAX_ROWS];
+
+static int xent_static_scratch_ptr(float** out) {
+  static std::mutex mu;
+  static float* per_device[64] = {nullptr};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return bdl_fail_cuda("bdl_xent_fwd_noalloc: cudaGetDevice", e);
+  if (dev < 0 || dev >= 64) return bdl_fail("bdl_xent_fwd_noalloc: device ordinal outside [0, 64)");
+  std::lock_guard<std::mutex> lock(mu);
+  if (per_device[dev] == nullptr) {
+    float* p = nullptr;
+    e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), bdl_xent_static_scratch);
+    if (e != cudaSuccess) return bdl_fail_cuda("bdl_xent_fwd_noalloc: cudaGetSymbolAddress", e);
+    if (p == nullptr) return bdl_fail("bdl_xent_fwd_noalloc: cudaGetSymbolAddress returned a null address");
+    per_device[dev] = p;
+  }
+  *out = per_device[dev];
+  return BDL_OK;
+}
+
+extern "C" int bdl_xent_fwd_noalloc(const void* logits, const void* target, const float* class_w, float* out,
+                                    long long B, int C, long long ld, int logits_bf16, int target_i64,
+                                    int padding_value, int size_average, void* stream) {
+  if (B > BDL_XENT_NOALLOC_MAX_ROWS)
+    return bdl_fail("bdl_xent_fwd_noalloc: batch exceeds the built-in scratch (at most 65536 rows); "
+                    "use bdl_xent_fwd with caller-provided scratch for larger batches");
+  float* scratch = nullptr;
+  const int rc = xent_static_scratch_ptr(&scratch);
+  if (rc != BDL_OK) return rc;
+  return bdl_xent_fwd(logits, target, class_w, scratch, out, B, C, ld, logits_bf16, target_i64, padding_value,
+                      size_average, stream);
+}

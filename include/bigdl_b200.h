@@ -85,6 +85,14 @@ int bdl_xent_fwd(const void* logits, const void* target, const float* class_w, f
 int bdl_xent_bwd(const void* logits, const void* target, const float* class_w, const float* scratch, const float* out,
                  void* dlogits, long long B, int C, long long ld, long long ldd, int logits_bf16, int target_i64,
                  int padding_value, int size_average, float gscale, void* stream);
+/* Allocation-free variant of bdl_xent_fwd: no counterpart in the reference. For hosts that may not allocate device
+ * memory at call time (pre-reserved arenas, real-time loops, plug-ins without access to the owner's allocator): the
+ * 3*B-float scratch lives in a fixed array inside the library, so B is capped at 65536 rows (larger B is rejected) and
+ * there is no backward. The first call on each device resolves the array's device address — make it before any stream
+ * capture. All calls on a device share that array: calls that can overlap on the GPU race. out: {loss, total weight}. */
+int bdl_xent_fwd_noalloc(const void* logits, const void* target, const float* class_w, float* out, long long B, int C,
+                         long long ld, int logits_bf16, int target_i64, int padding_value, int size_average,
+                         void* stream);
 int bdl_topk_correct(const void* logits, const void* target, void* counts, long long B, int C, long long ld,
                      int logits_bf16, int target_i64, void* stream);
 

@@ -253,8 +253,10 @@ class AllReduceParameter:
         else:
             bits = _trunc_to_bf16_bits(fl.grads) if self.truncate else \
                 fl.grads.to(torch.bfloat16).view(torch.int16)
-            gathered = [torch.empty_like(bits) for _ in range(self.world)]
-            dist.all_gather(gathered, bits, group=self.group)
+            raw = bits.contiguous().view(torch.uint8)          # gloo has no int16: ship the payload as bytes
+            gathered_raw = [torch.empty_like(raw) for _ in range(self.world)]
+            dist.all_gather(gathered_raw, raw, group=self.group)
+            gathered = [t.view(torch.int16) for t in gathered_raw]
             if self.truncate:
                 acc = _bits_to_f32(gathered[0][s:s + l])
                 for r in range(1, self.world):      # left fold in partition order, re-truncating after every add

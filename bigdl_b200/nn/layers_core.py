@@ -185,6 +185,11 @@ class SpatialConvolution(Module):
             geom = (self.kernel_h, self.kernel_w, self.stride_h, self.stride_w, pt, pl, pb, pr, self.dilation_h,
                     self.dilation_w, self.n_group)
             xin = x if self.propagate_back else x.detach()
+            hint = self.__dict__.pop("_next_out_hint", None)
+            if hint is not None:
+                from ..ops.functions import set_out_hint
+
+                set_out_hint(hint)
             y = ConvFn.apply(xin, self.weight, bias, w16, geom, self._fuse_relu, self.scaleW, self.scaleB)
         else:
             w = self.weight
@@ -379,6 +384,8 @@ class ReLU(Module):
         self.inplace = ip
 
     def updateOutput(self, input):
+        if getattr(self, "_fused", False):      # folded into the producer's epilogue (nn/fusion.py)
+            return input
         if native(input) and input.dtype == torch.bfloat16:
             from ..ops.functions import ReLUFn
 
@@ -457,6 +464,8 @@ class BatchNormalization(Module):
         return self
 
     def updateOutput(self, input):
+        if getattr(self, "_folded", False):     # folded into the preceding convolution (nn/fusion.py fold_bn)
+            return F.relu(input) if self._fuse_relu else input
         x = input
         if self.data_format == "NHWC" and x.dim() == 4:
             x = x.permute(0, 3, 1, 2)

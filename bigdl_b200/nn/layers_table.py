@@ -39,9 +39,57 @@ class Concat(Container):
         super().__init__()
         self.dimension = dimension
 
+    def _tail_conv(self, branch):
+        """The convolution that produces ``branch``'s final activation (ReLUs folded into it are skipped), or None."""
+        from .layers_core import ReLU, SpatialConvolution
+
+        m = branch
+        while isinstance(m, Container) and type(m).__name__ == "Sequential" and m.modules:
+            last = m.modules[-1]
+            if type(last) is ReLU and getattr(last, "_fused", False) and len(m.modules) >= 2:
+                last = m.modules[-2]
+            m = last
+        return m if isinstance(m, SpatialConvolution) and m.data_format == "NCHW" else None
+
     def updateOutput(self, input):
+        from .layers_core import native
+
+        if (self.dimension == 2 and isinstance(input, torch.Tensor) and input.dim() == 4 and native(input)
+                and input.dtype == torch.bfloat16 and getattr(self, "_zero_copy", True)):
+            out = self._zero_copy_forward(input)
+            if out is not None:
+                return out
         outs = [m._call(input) for m in self.modules]
         return torch.cat(outs, dim=self.dimension - 1)
+
+    def _zero_copy_forward(self, input):
+        """Channel concat without the copy: every branch's last convolution writes straight into its channel slice of
+        one NHWC buffer (the analogue of the reference's mkldnn JoinTable fusion, S/nn/mkldnn/Fusion.scala)."""
+        from ..ops import functions as Fn
+
+        tails = [self._tail_conv(b) for b in self.modules]
+        if any(t is None for t in tails) or any(t.n_output_plane % 8 for t in tails):
+            self._zero_copy = False
+            return None
+        key = tuple(input.shape)
+        cache = self.__dict__.setdefault("_out_hw", {})
+        if key not in cache:
+            # first call with this input shape: run normally once to learn the output spatial size
+            outs = [m._call(input) for m in self.modules]
+            if len({tuple(o.shape[2:]) for o in outs}) != 1:
+                self._zero_copy = False
+            else:
+                cache[key] = tuple(outs[0].shape[2:])
+            return torch.cat(outs, dim=1)
+        Ho, Wo = cache[key]
+        ctot = sum(t.n_output_plane for t in tails)
+        big = torch.empty((input.shape[0], Ho, Wo, ctot), dtype=torch.bfloat16, device=input.device)
+        outs, c = [], 0
+        for branch, tail in zip(self.modules, tails):
+            tail._next_out_hint = big[..., c:c + tail.n_output_plane]
+            outs.append(branch._call(input))
+            c += tail.n_output_plane
+        return Fn.ConcatViewFn.apply(big, *outs)
 
 
 class ConcatTable(Container):

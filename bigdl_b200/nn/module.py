@@ -349,6 +349,9 @@ class Module:
             m._on_device_change(device)
         if device.type == "cuda":
             self.getParameters()
+            from .fusion import fuse
+
+            fuse(self)
         return self
 
     def cuda(self, index: int | None = None):

@@ -38,6 +38,60 @@ def _nhwc(x: torch.Tensor) -> torch.Tensor:
     return x.permute(0, 2, 3, 1)
 
 
+def nhwc_pitched(x: torch.Tensor):
+    """[N,C,H,W] logical → ([N,H,W,C] view, pixel pitch). A channel slice of a dense NHWC tensor (what autograd hands
+    back for one branch of a channel concat) is used in place — the kernels take the pitch — instead of being copied."""
+    if x.dtype != torch.bfloat16:
+        x = x.to(torch.bfloat16)
+    xp = x.permute(0, 2, 3, 1)
+    N, H, W, C = xp.shape
+    st = xp.stride()
+    ld = st[2] if W > 1 else (st[1] if H > 1 else (st[0] if N > 1 else C))
+    ok = (st[3] == 1 or C == 1) and ld >= C and ld % 8 == 0 and (W == 1 or st[2] == ld) and \
+        (H == 1 or st[1] == W * ld) and (N == 1 or st[0] == H * W * ld) and xp.data_ptr() % 16 == 0
+    if ok:
+        return xp, ld
+    return x.contiguous(memory_format=torch.channels_last).permute(0, 2, 3, 1), C
+
+
+def rows2d(xp: torch.Tensor, ld: int) -> torch.Tensor:
+    """[N,H,W,C] (pixel pitch ld) → [N*H*W, C] view with row pitch ld."""
+    N, H, W, C = xp.shape
+    return torch.as_strided(xp, (N * H * W, C), (ld, 1), xp.storage_offset())
+
+
+_OUT_HINT: list = [None]
+
+
+def set_out_hint(buf: torch.Tensor | None):
+    """The next ConvFn.forward writes its output into ``buf`` ([N,Ho,Wo,O] view, e.g. a channel slice of a concat
+    buffer) instead of allocating — how Concat/JoinTable become zero-copy (cf. S/nn/mkldnn/Fusion.scala JoinTable)."""
+    _OUT_HINT[0] = buf
+
+
+def _take_out_hint():
+    h, _OUT_HINT[0] = _OUT_HINT[0], None
+    return h
+
+
+class ConcatViewFn(Function):
+    """The branches already wrote into channel slices of ``big`` ([N,H,W,Ctot]); expose it as one NCHW tensor whose
+    gradient is handed back to the branches as (pitched) channel slices — no copies in either direction."""
+
+    @staticmethod
+    def forward(ctx, big, *outs):
+        ctx.sizes = [o.shape[1] for o in outs]
+        return big.permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, g):
+        grads, c = [], 0
+        for n in ctx.sizes:
+            grads.append(g[:, c:c + n])
+            c += n
+        return (None, *grads)
+
+
 def _acc_grad(param: torch.Tensor, scale: float):
     return param.grad if (param is not None and param.requires_grad and scale != 0.0) else None
 
@@ -101,28 +155,39 @@ class ConvFn(Function):
     @staticmethod
     def forward(ctx, x, weight, bias, w16, geom, relu, scale_w, scale_b):
         kh, kw, sh, sw, pt, pl, pb, pr, dh, dw, groups = geom
-        xn = _nhwc(x)
+        xn, ldx = nhwc_pitched(x)
         N, H, W, C = xn.shape
         O = w16.shape[0]
-        Cg, Og = C // groups, O // groups
         Ho = (H + pt + pb - dh * (kh - 1) - 1) // sh + 1
         Wo = (W + pl + pr - dw * (kw - 1) - 1) // sw + 1
         M = N * Ho * Wo
-        y = torch.empty((N, Ho, Wo, O), dtype=torch.bfloat16, device=x.device)
-        y2 = y.view(M, O)
-        x2 = xn.reshape(N * H * W, C)
-        w2 = w16.permute(0, 2, 3, 1).reshape(O, kh * kw * Cg)   # OHWI physical → [O, K] view
-        direct = (kh == 1 and kw == 1 and sh == 1 and sw == 1 and pt == pl == pb == pr == 0 and Cg % 8 == 0)
-        K = kh * kw * Cg
-        Kp = (K + 7) // 8 * 8
-        lib = _lib.cuda_lib()
-        b32 = bias.detach() if bias is not None else None
+        c_real = C
+        w4 = w16.permute(0, 2, 3, 1)                        # OHWI physical order
+        if groups == 1 and C % 8 != 0 and C < 8:
+            # tiny channel counts (the RGB stem): pad to 8 channels so the 16-byte vector im2col path applies
+            xn = torch.nn.functional.pad(xn, (0, 8 - C))
+            w4 = torch.nn.functional.pad(w4, (0, 8 - C))
+            C, ldx = 8, 8
         asym = (pt != pb) or (pl != pr)
         if asym:
             # TF-style SAME padding can be asymmetric: materialise the extra bottom/right rows once
             xn = torch.nn.functional.pad(xn, (0, 0, 0, pr - pl if pr > pl else 0, 0, pb - pt if pb > pt else 0))
             N, H, W, C = xn.shape
-            x2 = xn.reshape(N * H * W, C)
+            ldx = C
+        Cg, Og = C // groups, O // groups
+        hint = _take_out_hint()
+        if hint is not None and tuple(hint.shape) == (N, Ho, Wo, O):
+            y, ldy = hint, hint.stride(2)
+        else:
+            y, ldy = torch.empty((N, Ho, Wo, O), dtype=torch.bfloat16, device=x.device), O
+        y2 = rows2d(y, ldy)
+        x2 = rows2d(xn, ldx)
+        w2 = w4.reshape(O, kh * kw * Cg)                     # [O, K]
+        direct = (kh == 1 and kw == 1 and sh == 1 and sw == 1 and pt == pl == pb == pr == 0 and Cg % 8 == 0)
+        K = kh * kw * Cg
+        Kp = (K + 7) // 8 * 8
+        lib = _lib.cuda_lib()
+        b32 = bias.detach() if bias is not None else None
         for g in range(groups):
             wg = w2[g * Og:(g + 1) * Og]
             if Kp != K:
@@ -136,28 +201,30 @@ class ConvFn(Function):
                 a = workspace(M * Kp, x.device).view(M, Kp)
                 xg = xn[..., g * Cg:(g + 1) * Cg]
                 _lib.check(lib.bdl_im2col_nhwc_bf16(xg.data_ptr(), a.data_ptr(), N, H, W, Cg, Ho, Wo, kh, kw, sh, sw,
-                                                    pt, pl, dh, dw, C, Kp, _lib.stream_ptr()), "bdl_im2col_nhwc_bf16")
+                                                    pt, pl, dh, dw, ldx, Kp, _lib.stream_ptr()), "bdl_im2col_nhwc_bf16")
                 _lib.count_launch()
             gemm_bf16(a, wg, bias=bg, relu=relu, out=y2[:, g * Og:(g + 1) * Og])
-        ctx.save_for_backward(xn, w16, y if relu else None)
-        ctx.params = (weight, bias, geom, relu, scale_w, scale_b, (N, H, W, C, Ho, Wo, O, K, Kp, direct), x.shape)
+        ctx.save_for_backward(xn, w4, y if relu else None)
+        ctx.params = (weight, bias, geom, relu, scale_w, scale_b,
+                      (N, H, W, C, Ho, Wo, O, K, Kp, direct, ldx, ldy, c_real), x.shape)
         return y.permute(0, 3, 1, 2)
 
     @staticmethod
     def backward(ctx, dy):
-        xn, w16, y = ctx.saved_tensors
+        xn, w4, y = ctx.saved_tensors
         weight, bias, geom, relu, scale_w, scale_b, dims, xshape = ctx.params
         kh, kw, sh, sw, pt, pl, pb, pr, dh, dw, groups = geom
-        N, H, W, C, Ho, Wo, O, K, Kp, direct = dims
+        N, H, W, C, Ho, Wo, O, K, Kp, direct, ldx, ldy, c_real = dims
         Cg, Og = C // groups, O // groups
         M = N * Ho * Wo
         lib = _lib.cuda_lib()
-        dyn = _nhwc(dy).reshape(M, O)
+        dy4, ldd = nhwc_pitched(dy)
+        dyn = rows2d(dy4, ldd)
         gb = _acc_grad(bias, scale_b)
         if relu:
-            dz = torch.empty_like(dyn)
+            dz = torch.empty((M, O), dtype=torch.bfloat16, device=dy.device)
             gtmp = gb if (gb is not None and scale_b == 1.0) else torch.zeros(O, device=dy.device)
-            ew.colsum(dyn, gtmp, y.view(M, O), dz)
+            ew.colsum(dyn, gtmp, rows2d(y, ldy), dz)
             if gb is not None and scale_b != 1.0:
                 gb.add_(gtmp, alpha=scale_b)
         else:
@@ -167,12 +234,15 @@ class ConvFn(Function):
                     ew.colsum(dyn, gb)
                 else:
                     gb.add_(ew.colsum(dyn, torch.zeros(O, device=dy.device)), alpha=scale_b)
-        x2 = xn.reshape(N * H * W, C)
-        w2 = w16.permute(0, 2, 3, 1).reshape(O, kh * kw * Cg)
+        x2 = rows2d(xn, ldx)
+        w2 = w4.reshape(O, kh * kw * Cg)
         gw = _acc_grad(weight, scale_w)
-        gw2 = gw.permute(0, 2, 3, 1).reshape(O, kh * kw * Cg) if gw is not None else None
+        padded_c = c_real != C and groups == 1 and C == 8 and c_real < 8
+        gw2 = None
+        if gw is not None and not padded_c:
+            gw2 = gw.permute(0, 2, 3, 1).reshape(O, kh * kw * Cg)
         need_dx = ctx.needs_input_grad[0]
-        dxn = torch.empty_like(xn) if need_dx else None
+        dxn = torch.empty((N, H, W, C), dtype=torch.bfloat16, device=dy.device) if need_dx else None
         for g in range(groups):
             dzg = dz[:, g * Og:(g + 1) * Og]
             if direct:
@@ -181,16 +251,21 @@ class ConvFn(Function):
                 a = workspace(M * Kp, dy.device).view(M, Kp)
                 xg = xn[..., g * Cg:(g + 1) * Cg]
                 _lib.check(lib.bdl_im2col_nhwc_bf16(xg.data_ptr(), a.data_ptr(), N, H, W, Cg, Ho, Wo, kh, kw, sh, sw,
-                                                    pt, pl, dh, dw, C, Kp, _lib.stream_ptr()), "bdl_im2col_nhwc_bf16")
+                                                    pt, pl, dh, dw, ldx, Kp, _lib.stream_ptr()), "bdl_im2col_nhwc_bf16")
                 _lib.count_launch()
             if gw is not None:
-                tgt = gw2[g * Og:(g + 1) * Og]
-                if scale_w == 1.0 and Kp == K and tgt.stride(1) == 1 and tgt.stride(0) % 4 == 0:
-                    gemm_bf16(dzg, a, a_mn=True, b_mn=True, out=tgt, accumulate=True)
-                else:
-                    tmp = torch.zeros((Og, Kp), device=dy.device)
+                if padded_c:
+                    tmp = torch.zeros((O, Kp), device=dy.device)
                     gemm_bf16(dzg, a, a_mn=True, b_mn=True, out=tmp, accumulate=True)
-                    tgt.add_(tmp[:, :K], alpha=scale_w)
+                    gw.permute(0, 2, 3, 1).add_(tmp.view(O, kh, kw, C)[..., :c_real], alpha=scale_w)
+                else:
+                    tgt = gw2[g * Og:(g + 1) * Og]
+                    if scale_w == 1.0 and Kp == K and tgt.stride(1) == 1:
+                        gemm_bf16(dzg, a, a_mn=True, b_mn=True, out=tgt, accumulate=True)
+                    else:
+                        tmp = torch.zeros((Og, Kp), device=dy.device)
+                        gemm_bf16(dzg, a, a_mn=True, b_mn=True, out=tmp, accumulate=True)
+                        tgt.add_(tmp[:, :K], alpha=scale_w)
             if need_dx:
                 wg = w2[g * Og:(g + 1) * Og]
                 if direct:
@@ -210,6 +285,8 @@ class ConvFn(Function):
         dx = None
         if need_dx:
             dx = dxn.permute(0, 3, 1, 2)
+            if dx.shape[1] != xshape[1]:
+                dx = dx[:, :xshape[1]]
             if tuple(dx.shape) != tuple(xshape):     # asymmetric SAME padding: drop the materialised border
                 dx = dx[:, :, :xshape[2], :xshape[3]]
         return dx, None, None, None, None, None, None, None
@@ -218,13 +295,13 @@ class ConvFn(Function):
 class MaxPoolFn(Function):
     @staticmethod
     def forward(ctx, x, kh, kw, sh, sw, ph, pw, Ho, Wo):
-        xn = _nhwc(x)
+        xn, ldx = nhwc_pitched(x)
         N, H, W, C = xn.shape
         lib = _lib.cuda_lib()
         y = torch.empty((N, Ho, Wo, C), dtype=torch.bfloat16, device=x.device)
         idx = torch.empty((N, Ho, Wo, C), dtype=torch.uint8, device=x.device)
         _lib.check(lib.bdl_maxpool_fwd_nhwc_bf16(xn.data_ptr(), y.data_ptr(), idx.data_ptr(), N, H, W, C, Ho, Wo, kh,
-                                                 kw, sh, sw, ph, pw, C, C, _lib.stream_ptr()), "maxpool_fwd")
+                                                 kw, sh, sw, ph, pw, ldx, C, _lib.stream_ptr()), "maxpool_fwd")
         _lib.count_launch()
         ctx.save_for_backward(idx)
         ctx.geom = (N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph, pw)
@@ -235,10 +312,10 @@ class MaxPoolFn(Function):
         (idx,) = ctx.saved_tensors
         N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph, pw = ctx.geom
         lib = _lib.cuda_lib()
-        dyn = _nhwc(dy)
+        dyn, ldy = nhwc_pitched(dy)
         dx = torch.empty((N, H, W, C), dtype=torch.bfloat16, device=dy.device)
         _lib.check(lib.bdl_maxpool_bwd_nhwc_bf16(dyn.data_ptr(), idx.data_ptr(), dx.data_ptr(), N, H, W, C, Ho, Wo, kh,
-                                                 kw, sh, sw, ph, pw, C, C, _lib.stream_ptr()), "maxpool_bwd")
+                                                 kw, sh, sw, ph, pw, C, ldy, _lib.stream_ptr()), "maxpool_bwd")
         _lib.count_launch()
         return (dx.permute(0, 3, 1, 2),) + (None,) * 8
 

@@ -206,8 +206,26 @@ __global__ void avgpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bf
 }
 
 // ---------------------------------------------------------------- cross-channel LRN
-// One warp-lane owns 8 consecutive channels of a pixel and reads the halo it needs from global (L1-resident).
+// One thread owns 8 consecutive channels of a pixel. It loads the 24-channel neighbourhood [c0-8, c0+16) with three
+// 16-byte loads, builds squared values once, and derives every window sum from registers (window <= 9 wide), so each
+// input element is read from L1/L2 a constant three times regardless of the window size.
 // scale_c = k + alpha/size * sum_{c' in [c-pre, c+post]} x_c'^2, pre = (size-1)/2, post = size-1-pre.
+__device__ __forceinline__ void lrn_load24(const __nv_bfloat16* row, int c0, int C, float (&v)[24]) {
+#pragma unroll
+  for (int blk = 0; blk < 3; ++blk) {
+    const int cb = c0 - 8 + 8 * blk;
+    if (cb >= 0 && cb + 8 <= C) {
+      float f[8];
+      load8(row + cb, f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[8 * blk + j] = f[j];
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[8 * blk + j] = 0.f;
+    }
+  }
+}
+
 __global__ void lrn_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long pixels,
                                int C, long long ldx, long long ldy, int size, float alpha, float beta, float k) {
   const int cvec = C / 8;
@@ -218,24 +236,28 @@ __global__ void lrn_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat1
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
     const int cv = static_cast<int>(i % cvec);
     const long long pix = i / cvec;
-    const __nv_bfloat16* row = x + pix * ldx;
     const int c0 = cv * 8;
+    float v[24];
+    lrn_load24(x + pix * ldx, c0, C, v);
+    float sq[24];
+#pragma unroll
+    for (int j = 0; j < 24; ++j) sq[j] = v[j] * v[j];
     float out[8];
+#pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const int c = c0 + j;
       float s = 0.f;
-      for (int cc = max(c - pre, 0); cc <= min(c + post, C - 1); ++cc) {
-        const float v = __bfloat162float(row[cc]);
-        s += v * v;
-      }
-      const float sc = k + as * s;
-      out[j] = __bfloat162float(row[c]) * __powf(sc, -beta);
+#pragma unroll
+      for (int d = -8; d <= 8; ++d)
+        if (d >= -pre && d <= post) s += sq[8 + j + d];
+      out[j] = v[8 + j] * __powf(k + as * s, -beta);
     }
     store8(y + pix * ldy + c0, out);
   }
 }
 
 // dx_c = dy_c * s_c^-beta - 2*alpha*beta/size * x_c * sum_{c' : c in window(c')} dy_c' * x_c' * s_c'^(-beta-1)
+// c is inside window(c') iff c - post <= c' <= c + pre; s_c' needs x over [c'-pre, c'+post], so the 24-wide
+// neighbourhood covers everything for windows up to 9 (pre, post <= 4).
 __global__ void lrn_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                                __nv_bfloat16* __restrict__ dx, long long pixels, int C, long long ldx, long long ldy,
                                long long lddx, int size, float alpha, float beta, float k) {
@@ -247,28 +269,92 @@ __global__ void lrn_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_b
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
     const int cv = static_cast<int>(i % cvec);
     const long long pix = i / cvec;
-    const __nv_bfloat16* xr = x + pix * ldx;
-    const __nv_bfloat16* gr = dy + pix * ldy;
     const int c0 = cv * 8;
-    float out[8];
-    for (int j = 0; j < 8; ++j) {
-      const int c = c0 + j;
-      float cross = 0.f, self_scale = 1.f;
-      // c is inside window(c') iff c' - pre <= c <= c' + post  <=>  c - post <= c' <= c + pre
-      for (int cp = max(c - post, 0); cp <= min(c + pre, C - 1); ++cp) {
-        float s = 0.f;
-        for (int cc = max(cp - pre, 0); cc <= min(cp + post, C - 1); ++cc) {
-          const float v = __bfloat162float(xr[cc]);
-          s += v * v;
-        }
-        const float sc = k + as * s;
-        const float pw = __powf(sc, -beta);
-        if (cp == c) self_scale = pw;
-        cross += __bfloat162float(gr[cp]) * __bfloat162float(xr[cp]) * pw / sc;
+    float v[24], g[24];
+    lrn_load24(x + pix * ldx, c0, C, v);
+    lrn_load24(dy + pix * ldy, c0, C, g);
+    float sq[24];
+#pragma unroll
+    for (int j = 0; j < 24; ++j) sq[j] = v[j] * v[j];
+    // ratio[c'] = dy_c' * x_c' * s_c'^(-beta-1) and pw[c'] = s_c'^-beta for c' in [c0-4, c0+12)  (index t = c' - c0 + 4)
+    float ratio[16], pw[16];
+#pragma unroll
+    for (int t = 0; t < 16; ++t) {
+      const int cp = c0 - 4 + t;
+      if (cp < 0 || cp >= C) {   // outside the tensor: contributes nothing (and k may be 0)
+        ratio[t] = 0.f;
+        pw[t] = 0.f;
+        continue;
       }
-      out[j] = __bfloat162float(gr[c]) * self_scale - 2.f * as * beta * __bfloat162float(xr[c]) * cross;
+      float s = 0.f;
+#pragma unroll
+      for (int d = -4; d <= 4; ++d)
+        if (d >= -pre && d <= post) s += sq[4 + t + d];
+      const float sc = k + as * s;
+      const float p = __powf(sc, -beta);
+      pw[t] = p;
+      ratio[t] = g[4 + t] * v[4 + t] * p / sc;
+    }
+    float out[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float cross = 0.f;
+#pragma unroll
+      for (int d = -4; d <= 4; ++d)
+        if (d >= -post && d <= pre) cross += ratio[4 + j + d];
+      out[j] = g[8 + j] * pw[4 + j] - 2.f * as * beta * v[8 + j] * cross;
     }
     store8(dx + pix * lddx + c0, out);
+  }
+}
+
+// generic fallback for windows wider than 9 (never used by the model zoo)
+__global__ void lrn_fwd_wide_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
+                                    long long pixels, int C, long long ldx, long long ldy, int size, float alpha,
+                                    float beta, float k) {
+  const long long total = pixels * C;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const int pre = (size - 1) / 2, post = size - 1 - pre;
+  const float as = alpha / size;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int c = static_cast<int>(i % C);
+    const long long pix = i / C;
+    const __nv_bfloat16* row = x + pix * ldx;
+    float s = 0.f;
+    for (int cc = max(c - pre, 0); cc <= min(c + post, C - 1); ++cc) {
+      const float t = __bfloat162float(row[cc]);
+      s += t * t;
+    }
+    y[pix * ldy + c] = __float2bfloat16_rn(__bfloat162float(row[c]) * __powf(k + as * s, -beta));
+  }
+}
+
+__global__ void lrn_bwd_wide_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                                    __nv_bfloat16* __restrict__ dx, long long pixels, int C, long long ldx,
+                                    long long ldy, long long lddx, int size, float alpha, float beta, float k) {
+  const long long total = pixels * C;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const int pre = (size - 1) / 2, post = size - 1 - pre;
+  const float as = alpha / size;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int c = static_cast<int>(i % C);
+    const long long pix = i / C;
+    const __nv_bfloat16* xr = x + pix * ldx;
+    const __nv_bfloat16* gr = dy + pix * ldy;
+    float cross = 0.f, self_scale = 1.f;
+    for (int cp = max(c - post, 0); cp <= min(c + pre, C - 1); ++cp) {
+      float s = 0.f;
+      for (int cc = max(cp - pre, 0); cc <= min(cp + post, C - 1); ++cc) {
+        const float t = __bfloat162float(xr[cc]);
+        s += t * t;
+      }
+      const float sc = k + as * s;
+      const float p = __powf(sc, -beta);
+      if (cp == c) self_scale = p;
+      cross += __bfloat162float(gr[cp]) * __bfloat162float(xr[cp]) * p / sc;
+    }
+    dx[pix * lddx + c] = __float2bfloat16_rn(__bfloat162float(gr[c]) * self_scale -
+                                             2.f * as * beta * __bfloat162float(xr[c]) * cross);
   }
 }
 
@@ -357,8 +443,14 @@ extern "C" int bdl_lrn_fwd_nhwc_bf16(const void* x, void* y, long long pixels, i
   if (check_pool("bdl_lrn_fwd_nhwc_bf16: C and pitches must be multiples of 8, pointers 16-byte aligned", C, ldx, ldy, x,
                  y))
     return BDL_ERR_INVALID;
-  lrn_fwd_kernel<<<grid_for(pixels * (C / 8)), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), pixels, C, ldx, ldy, size, alpha, beta, k);
+  if (size <= 9)
+    lrn_fwd_kernel<<<grid_for(pixels * (C / 8)), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), pixels, C, ldx, ldy, size, alpha, beta,
+        k);
+  else
+    lrn_fwd_wide_kernel<<<grid_for(pixels * C), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), pixels, C, ldx, ldy, size, alpha, beta,
+        k);
   return bdl_check_launch("lrn_fwd_kernel");
 }
 
@@ -368,8 +460,13 @@ extern "C" int bdl_lrn_bwd_nhwc_bf16(const void* x, const void* dy, void* dx, lo
   if (check_pool("bdl_lrn_bwd_nhwc_bf16: C and pitches must be multiples of 8, pointers 16-byte aligned", C, ldx, ldy, x,
                  dy))
     return BDL_ERR_INVALID;
-  lrn_bwd_kernel<<<grid_for(pixels * (C / 8)), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx),
-      pixels, C, ldx, ldy, lddx, size, alpha, beta, k);
+  if (size <= 9)
+    lrn_bwd_kernel<<<grid_for(pixels * (C / 8)), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx),
+        pixels, C, ldx, ldy, lddx, size, alpha, beta, k);
+  else
+    lrn_bwd_wide_kernel<<<grid_for(pixels * C), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx),
+        pixels, C, ldx, ldy, lddx, size, alpha, beta, k);
   return bdl_check_launch("lrn_bwd_kernel");
 }

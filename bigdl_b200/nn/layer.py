@@ -4,4 +4,10 @@ from .module import Module as Layer   # noqa: F401  (P/nn/layer.py:117 calls the
 from .layers_core import *       # noqa: F401,F403
 from .layers_table import *      # noqa: F401,F403
 from .layers_activation import * # noqa: F401,F403
+from .layers_linear import *     # noqa: F401,F403
+from .layers_conv_extra import * # noqa: F401,F403
+from .layers_recurrent import *  # noqa: F401,F403
+from .layers_attention import *  # noqa: F401,F403
+from .layers_detection import *  # noqa: F401,F403
 from .initialization_method import *  # noqa: F401,F403
+from .layers_recurrent import RnnCell as RNN  # noqa: F401  (Python API name, P/nn/layer.py)

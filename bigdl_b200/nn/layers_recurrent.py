@@ -349,6 +349,15 @@ class BiRecurrent(Container):
         self.bwd.add(c2)
         return self
 
+    # serializer hooks: the two cells are the only state that the constructor cannot rebuild
+    def _ser_children(self):
+        return [self.fwd.cell, self.bwd.cell] if self.fwd.modules else []
+
+    def _deser_children(self, mods):
+        if len(mods) == 2:
+            self.fwd.add(mods[0])
+            self.bwd.add(mods[1])
+
     def updateOutput(self, input):
         if self.is_split_input:
             half = input.shape[-1] // 2

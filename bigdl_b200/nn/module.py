@@ -53,8 +53,47 @@ def _detach(x):
     return map_activity(lambda t: t.detach(), x)
 
 
+def _capture_ctor(cls):
+    """Wrap ``cls.__init__`` so every instance remembers its constructor arguments (``_ctor_args``) and whether the
+    constructor itself created sub-modules (``_children_from_ctor``) — the Python stand-in for the constructor
+    reflection the reference's serializer relies on (S/utils/ReflectionUtils.scala, ModuleSerializable.scala:150-200)."""
+    import functools
+    import inspect
+
+    init = cls.__dict__.get("__init__")
+    if init is None or getattr(init, "_captures", False):
+        return
+    try:
+        sig = inspect.signature(init)
+    except (TypeError, ValueError):
+        return
+
+    @functools.wraps(init)
+    def wrapped(self, *a, **k):
+        outermost = "_ctor_args" not in self.__dict__
+        if outermost:
+            try:
+                bound = sig.bind(self, *a, **k)
+                bound.apply_defaults()
+                self.__dict__["_ctor_args"] = dict(list(bound.arguments.items())[1:])
+                self.__dict__["_ctor_cls"] = cls
+            except TypeError:
+                self.__dict__["_ctor_args"] = {}
+                self.__dict__["_ctor_cls"] = cls
+        init(self, *a, **k)
+        if outermost:
+            self.__dict__["_children_from_ctor"] = len(self.__dict__.get("modules", [])) > 0
+
+    wrapped._captures = True
+    cls.__init__ = wrapped
+
+
 class Module:
     """Base class of every layer (reference: AbstractModule[A, B, T])."""
+
+    def __init_subclass__(cls, **kw):
+        super().__init_subclass__(**kw)
+        _capture_ctor(cls)
 
     def __init__(self):
         self._uid = next(_uid)

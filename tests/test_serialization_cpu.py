@@ -1,0 +1,115 @@
+"""``.bigdl`` protobuf round trips (every layer family), the separate big-weights file, snapshots, and byte-level
+checks of the format rules (T/utils/serializer/ModuleSerializationTest and friends)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from bigdl_b200.models.inception import Inception_Layer_v1
+from bigdl_b200.models.lenet import LeNet5, LeNet5_graph
+from bigdl_b200.nn import layer as L
+from bigdl_b200.nn.module import Module
+from bigdl_b200.serialization import bigdl_pb as pb
+from bigdl_b200.serialization.module_io import load_module, save_module
+from bigdl_b200.utils.random_generator import RNG
+from bigdl_b200.utils.table import T
+
+
+def _roundtrip(m, x, tmp_path, weight_file=False):
+    m.evaluate()
+    y = m.forward(x)
+    path = str(tmp_path / "m.bigdl")
+    wpath = str(tmp_path / "m.bin") if weight_file else None
+    m.saveModule(path, wpath, True)
+    m2 = Module.loadModule(path, wpath)
+    m2.evaluate()
+    y2 = m2.forward(x)
+    ya = y.to_list() if hasattr(y, "to_list") else [y]
+    yb = y2.to_list() if hasattr(y2, "to_list") else [y2]
+    for a, b in zip(ya, yb):
+        assert torch.allclose(a, b, atol=1e-6), type(m).__name__
+    return m2
+
+
+def test_lenet_roundtrip_and_format(tmp_path):
+    RNG.setSeed(1)
+    m = LeNet5(10)
+    x = torch.randn(2, 28, 28)
+    m2 = _roundtrip(m, x, tmp_path)
+    assert [type(a).__name__ for a in m2.modules] == [type(a).__name__ for a in m.modules]
+    root = pb.BigDLModule.FromString(open(tmp_path / "m.bigdl", "rb").read())
+    assert root.moduleType == "com.intel.analytics.bigdl.nn.Sequential"
+    conv = root.subModules[1]
+    assert conv.moduleType == "com.intel.analytics.bigdl.nn.SpatialConvolution" and conv.name == "conv1_5x5"
+    assert conv.attr["nInputPlane"].int32Value == 1 and conv.attr["nOutputPlane"].int32Value == 6
+    assert conv.attr["kernelW"].int32Value == 5
+    w = conv.parameters[0]
+    assert list(w.size) == [1, 6, 1, 5, 5] and w.offset == 1            # (nGroup, out/g, in/g, kH, kW), 1-based offset
+    assert len(w.storage.float_data) == 0                               # data lives once in global_storage
+    gs = root.attr["global_storage"].nameAttrListValue
+    assert str(w.id) in gs.attr and len(gs.attr[str(w.id)].tensorValue.storage.float_data) == 150
+
+
+def test_weight_file_variant_and_checksum(tmp_path):
+    RNG.setSeed(2)
+    m = LeNet5(10)
+    x = torch.randn(2, 28, 28)
+    _roundtrip(m, x, tmp_path, weight_file=True)
+    raw = bytearray(open(tmp_path / "m.bin", "rb").read())
+    assert int.from_bytes(raw[:4], "big") == 3721
+    raw[40] ^= 0xFF
+    open(tmp_path / "bad.bin", "wb").write(raw)
+    with pytest.raises(ValueError):
+        Module.loadModule(str(tmp_path / "m.bigdl"), str(tmp_path / "bad.bin"))
+    with pytest.raises(FileExistsError):
+        m.saveModule(str(tmp_path / "m.bigdl"))
+
+
+def test_graph_and_many_layers_roundtrip(tmp_path):
+    RNG.setSeed(3)
+    _roundtrip(LeNet5_graph(10), torch.randn(2, 28, 28), tmp_path)
+    img = torch.randn(2, 8, 12, 12)
+    _roundtrip(Inception_Layer_v1(8, ((8,), (8, 16), (8, 8), (8,)), "x/"), img, tmp_path)
+    seq = L.Sequential().add(L.SpatialConvolution(8, 8, 3, 3, 1, 1, 1, 1, 2)).add(L.SpatialBatchNormalization(8)) \
+        .add(L.ReLU()).add(L.SpatialMaxPooling(3, 3, 2, 2).ceil()).add(L.SpatialCrossMapLRN(3, 0.1, 0.5, 2.0)) \
+        .add(L.Dropout(0.3)).add(L.View(8 * 6 * 6).setNumInputDims(3)).add(L.Linear(288, 5)).add(L.LogSoftMax())
+    seq.forward(img)          # populate BN running stats
+    m2 = _roundtrip(seq, img, tmp_path)
+    assert m2.modules[3].ceil_mode is True
+    assert torch.allclose(m2.modules[1].runningMean, seq.modules[1].runningMean)
+    seqs = torch.randn(2, 5, 4)
+    _roundtrip(L.Recurrent().add(L.LSTM(4, 6)), seqs, tmp_path)
+    _roundtrip(L.Recurrent().add(L.GRU(4, 6)), seqs, tmp_path)
+    _roundtrip(L.BiRecurrent(L.JoinTable(3)).add(L.LSTM(4, 3)), seqs, tmp_path)
+    _roundtrip(L.TimeDistributed(L.Linear(4, 3)), seqs, tmp_path)
+    _roundtrip(L.Sequential().add(L.LookupTable(10, 4)).add(L.Mean(2)), torch.randint(1, 11, (2, 5)).float(), tmp_path)
+    _roundtrip(L.Scale([1, 8, 1, 1]), img, tmp_path)
+    _roundtrip(L.Attention(8, 2, 0.0), T(torch.randn(2, 3, 8), torch.randn(2, 3, 8)), tmp_path)
+    _roundtrip(L.Transformer(12, 8, 2, 16, 1, 0.0, 0.0, 0.0), torch.randint(1, 13, (2, 4)).float(), tmp_path)
+    ct = L.Sequential().add(L.ConcatTable().add(L.Linear(4, 3)).add(L.Linear(4, 3))).add(L.CAddTable())
+    _roundtrip(ct, torch.randn(2, 4), tmp_path)
+    _roundtrip(L.SpatialFullConvolution(8, 4, 3, 3, 2, 2, 1, 1, 1, 1), img, tmp_path)
+    _roundtrip(L.Sequential().add(L.Reshape([8, 144])).add(L.Transpose([(2, 3)])).add(L.Narrow(2, 1, 10)), img, tmp_path)
+    _roundtrip(L.PReLU(8), img, tmp_path)
+    _roundtrip(L.Bilinear(4, 3, 2), T(torch.randn(2, 4), torch.randn(2, 3)), tmp_path)
+
+
+def test_snapshot_and_optim_method_files(tmp_path):
+    from bigdl_b200.optim.optim_method import SGD, OptimMethod
+
+    RNG.setSeed(4)
+    m = LeNet5(10)
+    x = torch.randn(2, 28, 28)
+    y = m.forward(x)
+    m.save(str(tmp_path / "model.5"))
+    m2 = Module.load(str(tmp_path / "model.5"))
+    assert torch.allclose(m2.forward(x), y)
+    om = SGD(0.1, momentum=0.9)
+    w = torch.zeros(8)
+    om.update(w, torch.ones(8))
+    om.state["epoch"], om.state["neval"] = 3, 77
+    om.save(str(tmp_path / "optimMethod-LeNet.77"))
+    om2 = OptimMethod.load(str(tmp_path / "optimMethod-LeNet.77"))
+    assert om2.state["neval"] == 77 and om2.state["epoch"] == 3 and om2.momentum == 0.9
+    assert om2._hist == {}            # history is dropped on save (S/optim/OptimMethod.scala:92-96)

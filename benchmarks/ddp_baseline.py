@@ -51,7 +51,17 @@ def _model(name):
         return InceptionV1()
     import torchvision.models as tv  # pragma: no cover - only if torchvision is present
 
-    return tv.resnet50() if name == "resnet50" else tv.vgg16()
+    m = tv.resnet50() if name == "resnet50" else tv.vgg16()
+
+    class _LS(nn.Module):
+        def __init__(self, body):
+            super().__init__()
+            self.body = body
+
+        def forward(self, x):
+            return F.log_softmax(self.body(x).float(), 1)
+
+    return _LS(m)
 
 
 def run(args):

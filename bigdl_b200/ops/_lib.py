@@ -79,6 +79,14 @@ _SIGNATURES = {
     "bdl_sumsq_f32": [_P, _Z, _P, _P],
     "bdl_absmax": [_P, _Z, _I, _P, _P],
     "bdl_scale_f32": [_P, _Z, _F, _P, _F, _P],
+    "bdl_bn_stats": [_P, _P, _L, _I, _L, _P],
+    "bdl_bn_finalize": [_P, _F, _I, _F, _F, _P, _P, _P, _P, _P],
+    "bdl_bn_apply": [_P, _P, _P, _P, _P, _P, _L, _I, _L, _L, _F, _I, _I, _P],
+    "bdl_bn_bwd_reduce": [_P, _P, _P, _P, _P, _P, _L, _I, _L, _L, _L, _P],
+    "bdl_bn_bwd_apply": [_P, _P, _P, _P, _P, _P, _P, _P, _L, _F, _I, _L, _L, _L, _L, _P],
+    "bdl_bn_param_grad": [_P, _P, _P, _I, _F, _F, _P],
+    "bdl_lstm_gates_fwd": [_P, _P, _P, _P, _P, _L, _I, _L, _P],
+    "bdl_lstm_gates_bwd": [_P, _P, _P, _P, _P, _P, _P, _L, _I, _P],
     "bdl_compress_grads": [_P, _P, _Z, _I, _I, _P],
     "bdl_fused_rs_update": [_P, _P, _P, _I, _I, _L, _L, _P, _P, _P, _P, _I, _P, _P, _I, ctypes.c_uint, _P, _P, _I, _P],
     "bdl_ipc_alloc": [_Z, _P, _P],

@@ -1,0 +1,298 @@
+// Batch normalisation for NHWC bf16 activations (rows = N*H*W pixels, columns = channels), training and inference,
+// with optional fused ReLU in both directions. All kernels are HBM-bound: every thread owns 8 channels (one 16-byte
+// vector) and walks rows; per-channel partial sums are combined through shared memory and one fp32 atomic per
+// channel per block. The statistics buffer is separate from the apply step so that the [2, C] sums can be
+// all-reduced across ranks in between (sync-BN, the cross-replica variant of S/nn/BatchNormalization.scala:65-76,
+// 224-235 built on S/utils/ParameterSynchronizer.scala).
+//
+// Semantics follow S/nn/BatchNormalization.scala:40-110 and SpatialBatchNormalization.scala:485-494:
+//   y = gamma * (x - mean) / sqrt(var_biased + eps) + beta
+//   running = (1 - momentum) * running + momentum * batch, with the UNBIASED batch variance for runningVar.
+// mkldnn twin: S/nn/mkldnn/SpatialBatchNormalization.scala (fused ReLU :44-83).
+#include "bigdl_b200.h"
+#include "host_common.h"
+#include "ptx.cuh"
+
+namespace bdl {
+
+__device__ __forceinline__ void bn_load8(const __nv_bfloat16* p, float (&f)[8]) {
+  const uint4 v = *reinterpret_cast<const uint4*>(p);
+  const __nv_bfloat162* q = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float2 t = __bfloat1622float2(q[j]);
+    f[2 * j] = t.x;
+    f[2 * j + 1] = t.y;
+  }
+}
+__device__ __forceinline__ void bn_store8(__nv_bfloat16* p, const float (&f)[8]) {
+  uint4 o;
+  o.x = pack_bf16x2(f[0], f[1]);
+  o.y = pack_bf16x2(f[2], f[3]);
+  o.z = pack_bf16x2(f[4], f[5]);
+  o.w = pack_bf16x2(f[6], f[7]);
+  *reinterpret_cast<uint4*>(p) = o;
+}
+
+// Thread layout shared by the reductions: vcols = min(C/8, 256) vector columns across, rif = 256/vcols rows in flight.
+// acc0/acc1 are two per-channel accumulators (sum & sum of squares, or dbeta & dgamma).
+template <int kMode>  // 0: forward stats (x)   1: backward sums (dy, x̂, optional ReLU mask from y)
+__global__ void bn_reduce_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ x,
+                                 const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean,
+                                 const float* __restrict__ invstd, float* __restrict__ out, long long M, int C,
+                                 long long lda, long long ldx, long long ldy, int rows_per_block) {
+  extern __shared__ float red[];  // [rif][vcols*16]
+  const int cvec = C / 8;
+  const int vcols = cvec < static_cast<int>(blockDim.x) ? cvec : blockDim.x;
+  const int rif = blockDim.x / vcols;
+  const int tc = threadIdx.x % vcols;
+  const int tr = threadIdx.x / vcols;
+  const long long r0 = static_cast<long long>(blockIdx.x) * rows_per_block;
+  long long r1 = r0 + rows_per_block;
+  if (r1 > M) r1 = M;
+  for (int cv = tc; cv < cvec; cv += vcols) {
+    float s0[8] = {0, 0, 0, 0, 0, 0, 0, 0}, s1[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    float mu[8], is[8];
+    if (kMode == 1) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        mu[j] = mean[cv * 8 + j];
+        is[j] = invstd[cv * 8 + j];
+      }
+    }
+    if (tr < rif) {
+      for (long long r = r0 + tr; r < r1; r += rif) {
+        float fa[8];
+        bn_load8(a + r * lda + cv * 8, fa);
+        if (kMode == 0) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            s0[j] += fa[j];
+            s1[j] += fa[j] * fa[j];
+          }
+        } else {
+          float fx[8];
+          bn_load8(x + r * ldx + cv * 8, fx);
+          if (y) {
+            float fy[8];
+            bn_load8(y + r * ldy + cv * 8, fy);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) fa[j] = fy[j] > 0.f ? fa[j] : 0.f;
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            s0[j] += fa[j];
+            s1[j] += fa[j] * (fx[j] - mu[j]) * is[j];
+          }
+        }
+      }
+    }
+    __syncthreads();
+    if (tr < rif) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        red[(tr * vcols + tc) * 16 + j] = s0[j];
+        red[(tr * vcols + tc) * 16 + 8 + j] = s1[j];
+      }
+    }
+    __syncthreads();
+    if (tr == 0) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float t0 = 0.f, t1 = 0.f;
+        for (int t = 0; t < rif; ++t) {
+          t0 += red[(t * vcols + tc) * 16 + j];
+          t1 += red[(t * vcols + tc) * 16 + 8 + j];
+        }
+        atomicAdd(out + cv * 8 + j, t0);
+        atomicAdd(out + C + cv * 8 + j, t1);
+      }
+    }
+  }
+}
+
+// mean / invstd from the (possibly all-reduced) sums; running statistics update. One thread per channel.
+__global__ void bn_finalize_kernel(const float* __restrict__ sums, float count, int C, float eps, float momentum,
+                                   float* __restrict__ save_mean, float* __restrict__ save_invstd,
+                                   float* __restrict__ running_mean, float* __restrict__ running_var) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float mean = sums[c] / count;
+  float var = sums[C + c] / count - mean * mean;
+  var = fmaxf(var, 0.f);
+  save_mean[c] = mean;
+  save_invstd[c] = rsqrtf(var + eps);
+  if (running_mean) {
+    const float unbiased = count > 1.f ? var * count / (count - 1.f) : var;
+    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+    running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+  }
+}
+
+// y = (x - mean) * invstd * gamma + beta (+ReLU). For inference pass mean = running mean and invstd computed from
+// the running variance (use_var = 1 makes the kernel derive invstd = rsqrt(var + eps) itself).
+__global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
+                                const float* __restrict__ mean, const float* __restrict__ invstd_or_var,
+                                const float* __restrict__ gamma, const float* __restrict__ beta, long long M, int C,
+                                long long ldx, long long ldy, float eps, int use_var, int relu) {
+  const int cvec = C / 8;
+  const long long total = M * cvec;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int cv = static_cast<int>(i % cvec);
+    const long long r = i / cvec;
+    float f[8];
+    bn_load8(x + r * ldx + cv * 8, f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = cv * 8 + j;
+      const float is = use_var ? rsqrtf(invstd_or_var[c] + eps) : invstd_or_var[c];
+      const float g = gamma ? gamma[c] : 1.f;
+      const float b = beta ? beta[c] : 0.f;
+      float v = (f[j] - mean[c]) * is * g + b;
+      f[j] = relu ? fmaxf(v, 0.f) : v;
+    }
+    bn_store8(y + r * ldy + cv * 8, f);
+  }
+}
+
+// dx = gamma * invstd * (dy' - dbeta/count - x̂ * dgamma/count), dy' = dy masked by (y > 0) when ReLU was fused.
+__global__ void bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                                    const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean,
+                                    const float* __restrict__ invstd, const float* __restrict__ gamma,
+                                    const float* __restrict__ sums, __nv_bfloat16* __restrict__ dx, long long M,
+                                    float count, int C, long long lddy, long long ldx, long long ldy,
+                                    long long lddx) {
+  const int cvec = C / 8;
+  const long long total = M * cvec;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const float inv_count = 1.f / count;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int cv = static_cast<int>(i % cvec);
+    const long long r = i / cvec;
+    float g[8], fx[8];
+    bn_load8(dy + r * lddy + cv * 8, g);
+    bn_load8(x + r * ldx + cv * 8, fx);
+    if (y) {
+      float fy[8];
+      bn_load8(y + r * ldy + cv * 8, fy);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) g[j] = fy[j] > 0.f ? g[j] : 0.f;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = cv * 8 + j;
+      const float is = invstd[c];
+      const float xh = (fx[j] - mean[c]) * is;
+      const float gm = gamma ? gamma[c] : 1.f;
+      g[j] = gm * is * (g[j] - sums[c] * inv_count - xh * sums[C + c] * inv_count);
+    }
+    bn_store8(dx + r * lddx + cv * 8, g);
+  }
+}
+
+// gradWeight += scale_w * dgamma ; gradBias += scale_b * dbeta
+__global__ void bn_param_grad_kernel(const float* __restrict__ sums, float* __restrict__ gw, float* __restrict__ gb,
+                                     int C, float scale_w, float scale_b) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  if (gb) gb[c] += scale_b * sums[c];
+  if (gw) gw[c] += scale_w * sums[C + c];
+}
+
+static int bn_grid(long long total) {
+  const long long cap = static_cast<long long>(bdl_num_sms()) * 16;
+  long long b = (total + 255) / 256;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return static_cast<int>(b);
+}
+
+static int bn_check(const char* who, int C, long long l0, long long l1, const void* p0, const void* p1) {
+  if ((C % 8) || (l0 % 8) || (l1 % 8) || (reinterpret_cast<uintptr_t>(p0) & 15u) ||
+      (reinterpret_cast<uintptr_t>(p1) & 15u))
+    return bdl_fail(who);
+  return BDL_OK;
+}
+
+}  // namespace bdl
+
+using namespace bdl;
+
+static void reduce_geometry(long long M, int C, int* grid, int* rpb, size_t* smem) {
+  const int sms = bdl_num_sms();
+  long long r = (M + sms * 4 - 1) / (sms * 4);
+  if (r < 32) r = 32;
+  *rpb = static_cast<int>(r);
+  *grid = static_cast<int>((M + r - 1) / r);
+  const int cvec = C / 8;
+  const int vcols = cvec < 256 ? cvec : 256;
+  const int rif = 256 / vcols;
+  *smem = static_cast<size_t>(rif) * vcols * 16 * sizeof(float);
+}
+
+// sums: [2*C] fp32, must be zero on entry (sum, sum of squares)
+extern "C" int bdl_bn_stats(const void* x, float* sums, long long M, int C, long long ldx, void* stream) {
+  if (bn_check("bdl_bn_stats: C and pitch must be multiples of 8, pointer 16-byte aligned", C, ldx, ldx, x, x))
+    return BDL_ERR_INVALID;
+  int grid, rpb;
+  size_t smem;
+  reduce_geometry(M, C, &grid, &rpb, &smem);
+  bn_reduce_kernel<0><<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), nullptr, nullptr, nullptr, nullptr, sums, M, C, ldx, 0, 0, rpb);
+  return bdl_check_launch("bn_reduce_kernel<0>");
+}
+
+extern "C" int bdl_bn_finalize(const float* sums, float count, int C, float eps, float momentum, float* save_mean,
+                               float* save_invstd, float* running_mean, float* running_var, void* stream) {
+  bn_finalize_kernel<<<(C + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      sums, count, C, eps, momentum, save_mean, save_invstd, running_mean, running_var);
+  return bdl_check_launch("bn_finalize_kernel");
+}
+
+extern "C" int bdl_bn_apply(const void* x, void* y, const float* mean, const float* invstd_or_var, const float* gamma,
+                            const float* beta, long long M, int C, long long ldx, long long ldy, float eps,
+                            int use_var, int relu, void* stream) {
+  if (bn_check("bdl_bn_apply: C and pitches must be multiples of 8, pointers 16-byte aligned", C, ldx, ldy, x, y))
+    return BDL_ERR_INVALID;
+  bn_apply_kernel<<<bn_grid(M * (C / 8)), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), mean, invstd_or_var, gamma, beta, M, C,
+      ldx, ldy, eps, use_var, relu);
+  return bdl_check_launch("bn_apply_kernel");
+}
+
+// sums: [2*C] fp32, zero on entry; receives (dbeta, dgamma)
+extern "C" int bdl_bn_bwd_reduce(const void* dy, const void* x, const void* y, const float* mean, const float* invstd,
+                                 float* sums, long long M, int C, long long lddy, long long ldx, long long ldy,
+                                 void* stream) {
+  if (bn_check("bdl_bn_bwd_reduce: C and pitches must be multiples of 8, pointers 16-byte aligned", C, lddy, ldx, dy,
+               x))
+    return BDL_ERR_INVALID;
+  int grid, rpb;
+  size_t smem;
+  reduce_geometry(M, C, &grid, &rpb, &smem);
+  bn_reduce_kernel<1><<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
+      static_cast<const __nv_bfloat16*>(y), mean, invstd, sums, M, C, lddy, ldx, ldy, rpb);
+  return bdl_check_launch("bn_reduce_kernel<1>");
+}
+
+extern "C" int bdl_bn_bwd_apply(const void* dy, const void* x, const void* y, const float* mean, const float* invstd,
+                                const float* gamma, const float* sums, void* dx, long long M, float count, int C,
+                                long long lddy, long long ldx, long long ldy, long long lddx, void* stream) {
+  if (bn_check("bdl_bn_bwd_apply: C and pitches must be multiples of 8, pointers 16-byte aligned", C, lddy, lddx, dy,
+               dx))
+    return BDL_ERR_INVALID;
+  bn_bwd_apply_kernel<<<bn_grid(M * (C / 8)), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
+      static_cast<const __nv_bfloat16*>(y), mean, invstd, gamma, sums, static_cast<__nv_bfloat16*>(dx), M, count, C,
+      lddy, ldx, ldy, lddx);
+  return bdl_check_launch("bn_bwd_apply_kernel");
+}
+
+extern "C" int bdl_bn_param_grad(const float* sums, float* gw, float* gb, int C, float scale_w, float scale_b,
+                                 void* stream) {
+  bn_param_grad_kernel<<<(C + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(sums, gw, gb, C, scale_w,
+                                                                                        scale_b);
+  return bdl_check_launch("bn_param_grad_kernel");
+}

@@ -124,6 +124,30 @@ int bdl_ipc_open(const void* handle64, void** ptr);
 int bdl_ipc_close(void* ptr);
 int bdl_ipc_free(void* ptr);
 
+/* ---- batch normalisation, NHWC bf16 (csrc/batchnorm.cu). Reference: S/nn/BatchNormalization.scala:40-110,
+ *      SpatialBatchNormalization.scala:485-494, S/nn/mkldnn/SpatialBatchNormalization.scala:44-83.
+ *      sums buffers are [2*C] fp32 and must be zero on entry; between bdl_bn_stats and bdl_bn_finalize they may be
+ *      all-reduced across ranks (sync-BN). */
+int bdl_bn_stats(const void* x, float* sums, long long M, int C, long long ldx, void* stream);
+int bdl_bn_finalize(const float* sums, float count, int C, float eps, float momentum, float* save_mean,
+                    float* save_invstd, float* running_mean, float* running_var, void* stream);
+int bdl_bn_apply(const void* x, void* y, const float* mean, const float* invstd_or_var, const float* gamma,
+                 const float* beta, long long M, int C, long long ldx, long long ldy, float eps, int use_var, int relu,
+                 void* stream);
+int bdl_bn_bwd_reduce(const void* dy, const void* x, const void* y, const float* mean, const float* invstd,
+                      float* sums, long long M, int C, long long lddy, long long ldx, long long ldy, void* stream);
+int bdl_bn_bwd_apply(const void* dy, const void* x, const void* y, const float* mean, const float* invstd,
+                     const float* gamma, const float* sums, void* dx, long long M, float count, int C, long long lddy,
+                     long long ldx, long long ldy, long long lddx, void* stream);
+int bdl_bn_param_grad(const float* sums, float* gw, float* gb, int C, float scale_w, float scale_b, void* stream);
+
+/* ---- fused LSTM gate math (csrc/recurrent.cu). Reference: S/nn/LSTM.scala:150-175, S/nn/mkldnn/RNN.scala.
+ *      Gate order along 4H: input, candidate, forget, output. c is kept in fp32. */
+int bdl_lstm_gates_fwd(const void* g, const float* c_prev, void* h, float* c, void* gates, long long B, int H,
+                       long long ldg, void* stream);
+int bdl_lstm_gates_bwd(const void* dh, const float* dc_in, const void* gates, const float* c, const float* c_prev,
+                       void* dg, float* dc_prev, long long B, int H, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -218,3 +218,76 @@ def test_optim_kernels_match_cpu(name):
         b.update(xg, g.to(DEV), w16=w16)
     _close(xg.cpu(), xc, 1e-5, 1e-6)
     assert torch.equal(w16, xg.to(torch.bfloat16))
+
+
+@pytest.mark.parametrize("relu", [False, True])
+@pytest.mark.parametrize("train", [True, False])
+def test_batchnorm_fwd_bwd(relu, train):
+    from bigdl_b200.nn.layers_core import SpatialBatchNormalization
+    from bigdl_b200.utils.random_generator import RNG
+    RNG.setSeed(11)
+    torch.manual_seed(11)
+    bn = SpatialBatchNormalization(32, 1e-3)
+    bn._fuse_relu = relu
+    ref = bn.cloneModule()
+    ref._fuse_relu = relu
+    if not train:
+        bn.evaluate()
+        ref.evaluate()
+        with torch.no_grad():
+            for m in (bn, ref):
+                m._buffers["runningMean"].copy_(torch.linspace(-1, 1, 32))
+                m._buffers["runningVar"].copy_(torch.linspace(0.5, 2, 32))
+    bn.cuda()
+    x = (torch.randn(8, 32, 14, 14) * 2 + 0.5)
+    xb = x.cuda().to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    y = bn.forward(xb)
+    yr = ref.forward(xb.float().cpu())
+    _close(y.cpu(), yr, 2e-2, 2e-2)
+    if train:
+        _close(bn.runningMean.cpu(), ref.runningMean, 1e-3, 1e-3)
+        _close(bn.runningVar.cpu(), ref.runningVar, 1e-3, 1e-3)
+    go = torch.randn_like(yr).to(torch.bfloat16)
+    gx = bn.backward(xb, go.cuda())
+    gr = ref.backward(xb.float().cpu(), go.float())
+    _close(gx.cpu(), gr, 5e-2, 5e-2)
+    _close(bn.gradWeight.cpu(), ref.gradWeight, 3e-2, 0.5)
+    _close(bn.gradBias.cpu(), ref.gradBias, 3e-2, 0.5)
+
+
+def test_lstm_gates_kernel():
+    from bigdl_b200.ops.recurrent import lstm_gates
+    torch.manual_seed(12)
+    B, H = 64, 96
+    g = torch.randn(B, 4 * H, device=DEV).to(torch.bfloat16).requires_grad_(True)
+    c0 = torch.randn(B, H, device=DEV).requires_grad_(True)
+    h, c = lstm_gates(g, c0)
+    gf = g.detach().float().requires_grad_(True)
+    cf = c0.detach().clone().requires_grad_(True)
+    i, z, f, o = torch.sigmoid(gf[:, :H]), torch.tanh(gf[:, H:2 * H]), torch.sigmoid(gf[:, 2 * H:3 * H]), torch.sigmoid(gf[:, 3 * H:])
+    cr = i * z + f * cf
+    hr = torch.tanh(cr) * o
+    _close(h, hr, 2e-2, 2e-2)
+    _close(c, cr, 2e-2, 2e-2)
+    dh, dc = torch.randn_like(hr), torch.randn_like(cr)
+    torch.autograd.backward([h, c], [dh.to(torch.bfloat16), dc])
+    torch.autograd.backward([hr, cr], [dh.to(torch.bfloat16).float(), dc])
+    _close(g.grad, gf.grad, 4e-2, 4e-2)
+    _close(c0.grad, cf.grad, 4e-2, 4e-2)
+
+
+def test_recurrent_lstm_on_gpu_matches_cpu():
+    from bigdl_b200.nn.layer import LSTM, Recurrent
+    from bigdl_b200.utils.random_generator import RNG
+    RNG.setSeed(13)
+    r = Recurrent().add(LSTM(64, 128))
+    ref = r.cloneModule()
+    r.cuda()
+    x = torch.randn(4, 6, 64)
+    y = r.forward(x.cuda().to(torch.bfloat16))
+    yr = ref.forward(x)
+    _close(y.cpu(), yr, 5e-2, 5e-2)
+    go = torch.randn_like(yr)
+    gx = r.backward(x.cuda().to(torch.bfloat16), go.cuda().to(torch.bfloat16))
+    gr = ref.backward(x, go)
+    _close(gx.cpu(), gr, 8e-2, 8e-2)

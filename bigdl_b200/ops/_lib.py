@@ -54,6 +54,7 @@ _P, _I, _L, _F, _Z, _U64 = (ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ct
 # argument types of every exported function (include/bigdl_b200.h); keeps 64-bit values intact through ctypes
 _SIGNATURES = {
     "bdl_gemm_bf16": [_P, _P, _P, _P, _I, _I, _I, _L, _L, _L, _I, _I, _I, _I, _I, _P],
+    "bdl_conv_igemm_bf16": [_I, _P, _I, _I, _I, _I, _L, _P, _L, _P, _L, _P] + [_I] * 14 + [_P],
     "bdl_gemm_fp8": [_P, _P, _P, _P, _P, _P, _I, _I, _I, _L, _L, _L, _I, _I, _P],
     "bdl_cast_f32_to_bf16": [_P, _P, _Z, _I, _P],
     "bdl_cast_bf16_to_f32": [_P, _P, _Z, _P],

@@ -15,7 +15,7 @@ from torch.autograd import Function
 
 from . import _lib
 from . import elementwise as ew
-from .gemm import gemm_bf16
+from .gemm import conv_igemm, gemm_bf16
 
 _WS: dict = {}
 
@@ -61,6 +61,7 @@ def rows2d(xp: torch.Tensor, ld: int) -> torch.Tensor:
 
 
 _OUT_HINT: list = [None]
+_IGEMM: list = [True]      # implicit-GEMM (TMA im2col) convolution path; False forces the explicit im2col path
 
 
 def set_out_hint(buf: torch.Tensor | None):
@@ -188,7 +189,10 @@ class ConvFn(Function):
         Kp = (K + 7) // 8 * 8
         lib = _lib.cuda_lib()
         b32 = bias.detach() if bias is not None else None
-        for g in range(groups):
+        implicit = (not direct) and groups == 1 and C % 8 == 0 and C >= 32 and O % 8 == 0 and _IGEMM[0]
+        if implicit:
+            conv_igemm(0, xn, ldx, w2, y2, O, Ho, Wo, kh, kw, sh, sw, pt, pl, dh, dw, bias=b32, relu=relu)
+        for g in range(groups if not implicit else 0):
             wg = w2[g * Og:(g + 1) * Og]
             if Kp != K:
                 wpad = torch.zeros((Og, Kp), dtype=torch.bfloat16, device=x.device)
@@ -206,7 +210,7 @@ class ConvFn(Function):
             gemm_bf16(a, wg, bias=bg, relu=relu, out=y2[:, g * Og:(g + 1) * Og])
         ctx.save_for_backward(xn, w4, y if relu else None)
         ctx.params = (weight, bias, geom, relu, scale_w, scale_b,
-                      (N, H, W, C, Ho, Wo, O, K, Kp, direct, ldx, ldy, c_real), x.shape)
+                      (N, H, W, C, Ho, Wo, O, K, Kp, direct, ldx, ldy, c_real, implicit), x.shape)
         return y.permute(0, 3, 1, 2)
 
     @staticmethod
@@ -214,7 +218,7 @@ class ConvFn(Function):
         xn, w4, y = ctx.saved_tensors
         weight, bias, geom, relu, scale_w, scale_b, dims, xshape = ctx.params
         kh, kw, sh, sw, pt, pl, pb, pr, dh, dw, groups = geom
-        N, H, W, C, Ho, Wo, O, K, Kp, direct, ldx, ldy, c_real = dims
+        N, H, W, C, Ho, Wo, O, K, Kp, direct, ldx, ldy, c_real, implicit = dims
         Cg, Og = C // groups, O // groups
         M = N * Ho * Wo
         lib = _lib.cuda_lib()
@@ -243,17 +247,30 @@ class ConvFn(Function):
             gw2 = gw.permute(0, 2, 3, 1).reshape(O, kh * kw * Cg)
         need_dx = ctx.needs_input_grad[0]
         dxn = torch.empty((N, H, W, C), dtype=torch.bfloat16, device=dy.device) if need_dx else None
+        done_w = done_x = False
+        if implicit:
+            ldz = dz.stride(0)
+            if gw is not None and not padded_c and C % 64 == 0 and scale_w == 1.0 and gw2.stride(1) == 1:
+                conv_igemm(2, xn, ldx, dz, gw2, O, Ho, Wo, kh, kw, sh, sw, pt, pl, dh, dw, accumulate=True)
+                done_w = True
+            if need_dx and sh == 1 and sw == 1 and dh * (kh - 1) - pt >= 0 and dw * (kw - 1) - pl >= 0:
+                dz_nhwc = torch.as_strided(dz, (N, Ho, Wo, O), (Ho * Wo * ldz, Wo * ldz, ldz, 1), dz.storage_offset())
+                conv_igemm(1, dz_nhwc, ldz, w2, dxn.view(N * H * W, C), C, H, W, kh, kw, 1, 1, dh * (kh - 1) - pt,
+                           dw * (kw - 1) - pl, dh, dw)
+                done_x = True
         for g in range(groups):
+            if (gw is None or done_w) and (not need_dx or done_x):
+                break
             dzg = dz[:, g * Og:(g + 1) * Og]
             if direct:
                 a = x2[:, g * Cg:(g + 1) * Cg]
-            elif gw is not None:
+            elif gw is not None and not done_w:
                 a = workspace(M * Kp, dy.device).view(M, Kp)
                 xg = xn[..., g * Cg:(g + 1) * Cg]
                 _lib.check(lib.bdl_im2col_nhwc_bf16(xg.data_ptr(), a.data_ptr(), N, H, W, Cg, Ho, Wo, kh, kw, sh, sw,
                                                     pt, pl, dh, dw, ldx, Kp, _lib.stream_ptr()), "bdl_im2col_nhwc_bf16")
                 _lib.count_launch()
-            if gw is not None:
+            if gw is not None and not done_w:
                 if padded_c:
                     tmp = torch.zeros((O, Kp), device=dy.device)
                     gemm_bf16(dzg, a, a_mn=True, b_mn=True, out=tmp, accumulate=True)
@@ -266,7 +283,7 @@ class ConvFn(Function):
                         tmp = torch.zeros((Og, Kp), device=dy.device)
                         gemm_bf16(dzg, a, a_mn=True, b_mn=True, out=tmp, accumulate=True)
                         tgt.add_(tmp[:, :K], alpha=scale_w)
-            if need_dx:
+            if need_dx and not done_x:
                 wg = w2[g * Og:(g + 1) * Og]
                 if direct:
                     gemm_bf16(dzg, wg, b_mn=True, out=dxn.view(N * H * W, C)[:, g * Cg:(g + 1) * Cg])

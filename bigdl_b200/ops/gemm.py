@@ -37,3 +37,19 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: boo
     _lib.check(rc, "bdl_gemm_bf16")
     _lib.count_launch()
     return out
+
+
+def conv_igemm(mode: int, act: torch.Tensor, ld_act: int, other: torch.Tensor, out: torch.Tensor, O: int, Ho: int,
+               Wo: int, kh: int, kw: int, sh: int, sw: int, ph: int, pw: int, dh: int, dw: int, bias=None, relu=False,
+               accumulate=False, splits: int = 0):
+    """Implicit-GEMM convolution (csrc/gemm_tcgen05.cu, TMA im2col). ``act`` is an NHWC view [N,H,W,C] with pixel
+    pitch ``ld_act``; ``other`` is the 2-D weight matrix (modes 0/1) or dY [N*Ho*Wo, O] (mode 2); ``out`` is 2-D."""
+    lib = _lib.cuda_lib()
+    N, H, W, C = act.shape
+    flags = (BIAS if bias is not None else 0) | (RELU if relu else 0) | (ATOMIC_ADD if accumulate else 0)
+    rc = lib.bdl_conv_igemm_bf16(mode, act.data_ptr(), N, H, W, C, ld_act, other.data_ptr(), other.stride(0),
+                                 out.data_ptr(), out.stride(0), _lib.ptr(bias), O, Ho, Wo, kh, kw, sh, sw, ph, pw, dh,
+                                 dw, int(out.dtype == torch.float32), flags, splits, _lib.stream_ptr())
+    _lib.check(rc, "bdl_conv_igemm_bf16")
+    _lib.count_launch()
+    return out

@@ -39,9 +39,22 @@ struct GemmParams {
   int flags;
   void* D;
   const float* bias;
+  // implicit-GEMM convolution (kConv != 0): the A (fprop/dgrad) or B (wgrad) operand is gathered from an NHWC
+  // activation tensor by TMA im2col loads instead of being read from a materialised column matrix.
+  int cv_Ho, cv_Wo;          // output spatial size of the traversal
+  int cv_sh, cv_sw;          // traversal strides
+  int cv_ph, cv_pw;          // lower padding (first base position = -pad)
+  int cv_dh, cv_dw;          // dilation
+  int cv_kh, cv_kw;          // filter size
+  int cv_C;                  // channels of the gathered tensor
+  int cv_cblocks;            // ceil(C / 64)
+  int cv_flip;               // dgrad: B uses the spatially flipped tap
+  int cv_num_kb;             // number of 64-wide k blocks (taps * cblocks for fprop/dgrad, ceil(M/64) for wgrad)
+  int cv_nimg;               // batch size of the gathered tensor (first out-of-bounds image index)
 };
 
-template <bool kAMN, bool kBMN>
+// kConv: 0 plain GEMM; 1 A operand via im2col TMA (conv fprop, and dgrad when kBMN); 2 B operand via im2col TMA (wgrad)
+template <bool kAMN, bool kBMN, int kConv>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                          const GemmParams p) {
@@ -78,7 +91,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
 
-  const int num_kb = (p.K + BK - 1) / BK;
+  const int num_kb = kConv ? p.cv_num_kb : (p.K + BK - 1) / BK;
   const int tiles_mn = p.tiles_m * p.tiles_n;
   const int total_work = tiles_mn * p.splits;
 
@@ -103,6 +116,46 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           const uint32_t sb = sa + a_bytes;
           mbar_expect_tx(fb, stage_bytes);
           const int k0 = kb * BK;
+          if (kConv == 1) {
+            // k block = (filter tap, 64-channel block); A tile = 128 consecutive output pixels of that tap
+            const int tap = kb / p.cv_cblocks;
+            const int cb = kb - tap * p.cv_cblocks;
+            const int r = tap / p.cv_kw, sx = tap - r * p.cv_kw;
+            const int hw = p.cv_Ho * p.cv_Wo;
+            const int img = m0 / hw;
+            const int rem = m0 - img * hw;
+            const int ho = rem / p.cv_Wo, wo = rem - ho * p.cv_Wo;
+            tma_load_im2col_4d(sa, &tmA, fb, cb * 64, wo * p.cv_sw - p.cv_pw, ho * p.cv_sh - p.cv_ph, img,
+                               static_cast<uint16_t>(sx * p.cv_dw), static_cast<uint16_t>(r * p.cv_dh));
+            if (kBMN) {
+              // dgrad: B[k = cout block][n = cin] is the (flipped) tap's [Cout, Cin] slice of the OHWI weights
+              const int btap = p.cv_flip ? (p.cv_kh - 1 - r) * p.cv_kw + (p.cv_kw - 1 - sx) : tap;
+              for (int j = 0; j < p.b_rows / 64; ++j)
+                tma_load_2d(sb + j * 8192u, &tmB, fb, btap * p.N + n0 + 64 * j, cb * 64);
+            } else {
+              tma_load_2d(sb, &tmB, fb, tap * p.cv_C + cb * 64, n0);
+            }
+          } else if (kConv == 2) {
+            // wgrad: k block = 64 consecutive output pixels; A = dY^T (MN-major), B atoms = im2col gathers
+            tma_load_2d(sa, &tmA, fb, m0, k0);
+            tma_load_2d(sa + 8192u, &tmA, fb, m0 + 64, k0);
+            const int hw = p.cv_Ho * p.cv_Wo;
+            const int img = k0 / hw;
+            const int rem = k0 - img * hw;
+            const int ho = rem / p.cv_Wo, wo = rem - ho * p.cv_Wo;
+            for (int j = 0; j < p.b_rows / 64; ++j) {
+              const int ncol = n0 + 64 * j;            // column in the [taps * C] space (C % 64 == 0)
+              const int tap = ncol / p.cv_C;
+              const int c0 = ncol - tap * p.cv_C;
+              const int r = tap / p.cv_kw, sx = tap - r * p.cv_kw;
+              if (tap < p.cv_kh * p.cv_kw)
+                tma_load_im2col_4d(sb + j * 8192u, &tmB, fb, c0, wo * p.cv_sw - p.cv_pw, ho * p.cv_sh - p.cv_ph, img,
+                                   static_cast<uint16_t>(sx * p.cv_dw), static_cast<uint16_t>(r * p.cv_dh));
+              else
+                tma_load_im2col_4d(sb + j * 8192u, &tmB, fb, 0, -p.cv_pw, -p.cv_ph, p.cv_nimg, 0,
+                                   0);   // past the last tap: a box that starts after the last image (zero fill)
+            }
+          } else {
           if (kAMN) {
             // A stored [K, M]: two boxes of {64 m, 64 k}
             tma_load_2d(sa, &tmA, fb, m0, k0);
@@ -114,6 +167,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             for (int j = 0; j < p.b_rows / 64; ++j) tma_load_2d(sb + j * 8192u, &tmB, fb, n0 + 64 * j, k0);
           } else {
             tma_load_2d(sb, &tmB, fb, k0, n0);  // box {64 k, block_n}
+          }
           }
           if (++stage == p.num_stages) {
             stage = 0;
@@ -344,7 +398,7 @@ extern "C" int bdl_gemm_bf16(const void* A, const void* B, void* D, const float*
   const int grid = static_cast<int>(total < num_sms ? total : num_sms);
 #define BDL_LAUNCH_GEMM(AMN, BMN)                                                                                 \
   do {                                                                                                            \
-    auto kfn = gemm_bf16_tcgen05_kernel<AMN, BMN>;                                                                \
+    auto kfn = gemm_bf16_tcgen05_kernel<AMN, BMN, 0>;                                                                \
     cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 256);     \
     if (e != cudaSuccess) return bdl_fail_cuda("cudaFuncSetAttribute(gemm)", e);                                  \
     kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, p);                                                       \
@@ -359,4 +413,113 @@ extern "C" int bdl_gemm_bf16(const void* A, const void* B, void* D, const float*
     BDL_LAUNCH_GEMM(false, false);
 #undef BDL_LAUNCH_GEMM
   return bdl_check_launch("gemm_bf16_tcgen05_kernel");
+}
+
+
+// ------------------------------------------------------------------------------------------------ implicit-GEMM conv
+// mode 0 (fprop):  D[N*Ho*Wo, O]      = im2col(act)[., (tap, c)] * Wt[O, (tap, c)]^T          (+bias)(ReLU)
+// mode 1 (dgrad):  D[N*Ho*Wo, O]      = im2col(act)[., (tap, c)] * Wt[c, (flip(tap), o)]       act = dY, O = Cin; the caller
+//                  passes the transposed-convolution geometry (Ho/Wo = input size, pad' = dil*(k-1) - pad, stride 1)
+// mode 2 (wgrad):  D[O, (tap, c)]    += other[N*Ho*Wo, O]^T * im2col(act)[., (tap, c)]          other = dY, fp32 red.add
+// act is an NHWC tensor [N, H, W, C] with pixel pitch ld_act; `other` is the weight matrix (modes 0/1, row pitch
+// ld_other) or dY (mode 2). Reference: S/nn/SpatialConvolution.scala:253-521, S/nn/mkldnn/SpatialConvolution.scala.
+extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int W, int C, long long ld_act,
+                                   const void* other, long long ld_other, void* D, long long ldd, const float* bias,
+                                   int O, int Ho, int Wo, int kh, int kw, int sh, int sw, int ph, int pw, int dh,
+                                   int dw, int out_fp32, int flags, int splits, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (mode < 0 || mode > 2) return bdl_fail("bdl_conv_igemm_bf16: mode must be 0 (fprop), 1 (dgrad) or 2 (wgrad)");
+  if ((reinterpret_cast<uintptr_t>(act) & 15u) || (reinterpret_cast<uintptr_t>(other) & 15u) || (ld_act % 8) ||
+      (ld_other % 8))
+    return bdl_fail("bdl_conv_igemm_bf16: operands must be 16-byte aligned with pitches that are multiples of 8");
+  if (mode == 2 && (C % 64)) return bdl_fail("bdl_conv_igemm_bf16: wgrad needs C % 64 == 0");
+  if (mode == 2 && !(flags & BDL_GEMM_ATOMIC_ADD)) return bdl_fail("bdl_conv_igemm_bf16: wgrad accumulates (ATOMIC_ADD)");
+  const int num_sms = bdl_num_sms();
+  const long long Mpix = static_cast<long long>(N) * Ho * Wo;
+  if (Mpix >= (1ll << 31)) return bdl_fail("bdl_conv_igemm_bf16: too many output pixels");
+  const int taps = kh * kw;
+  GemmParams p{};
+  p.cv_Ho = Ho; p.cv_Wo = Wo; p.cv_sh = sh; p.cv_sw = sw; p.cv_ph = ph; p.cv_pw = pw; p.cv_dh = dh; p.cv_dw = dw;
+  p.cv_kh = kh; p.cv_kw = kw; p.cv_C = C; p.cv_cblocks = (C + 63) / 64; p.cv_flip = (mode == 1); p.cv_nimg = N;
+  int gm, gn;
+  if (mode == 2) {
+    gm = O;
+    gn = taps * C;
+    p.K = static_cast<int>(Mpix);
+    p.cv_num_kb = static_cast<int>((Mpix + 63) / 64);
+  } else {
+    gm = static_cast<int>(Mpix);
+    gn = O;
+    p.K = taps * p.cv_cblocks * 64;
+    p.cv_num_kb = taps * p.cv_cblocks;
+  }
+  p.M = gm;
+  p.N = gn;
+  p.block_n = pick_block_n(gm, gn, num_sms);
+  const bool b_mn = (mode != 0);
+  p.b_rows = b_mn ? ((p.block_n + 63) / 64) * 64 : p.block_n;
+  p.tiles_m = (gm + BM - 1) / BM;
+  p.tiles_n = (gn + p.block_n - 1) / p.block_n;
+  const long long tiles_mn = static_cast<long long>(p.tiles_m) * p.tiles_n;
+  if (splits <= 0) {
+    splits = 1;
+    if ((flags & BDL_GEMM_ATOMIC_ADD) && tiles_mn < num_sms) {
+      splits = static_cast<int>(num_sms / tiles_mn);
+      const int max_by_k = p.cv_num_kb / 4 > 0 ? p.cv_num_kb / 4 : 1;
+      if (splits > max_by_k) splits = max_by_k;
+    }
+  }
+  if (splits > 1 && !(flags & BDL_GEMM_ATOMIC_ADD)) return bdl_fail("bdl_conv_igemm_bf16: split-K needs ATOMIC_ADD");
+  if (splits > p.cv_num_kb) splits = p.cv_num_kb;
+  p.splits = splits;
+  p.ldd = ldd;
+  p.out_fp32 = out_fp32;
+  p.flags = flags;
+  p.D = D;
+  p.bias = bias;
+  const size_t stage_bytes = static_cast<size_t>(BM) * BK * 2 + static_cast<size_t>(p.b_rows) * BK * 2;
+  const size_t budget = 227 * 1024 - 1024 - 256;
+  int stages = static_cast<int>(budget / stage_bytes);
+  if (stages > kMaxStages) stages = kMaxStages;
+  if (stages < 2) return bdl_fail("bdl_conv_igemm_bf16: tile does not fit in shared memory");
+  p.num_stages = stages;
+  const size_t smem = stages * stage_bytes + 1024;
+
+  // bounding box of base pixel positions: [-pad, dim - 1 + pad - dil*(k-1)] (inclusive), traversal stride = conv stride
+  const int up_w = pw - dw * (kw - 1), up_h = ph - dh * (kh - 1);
+  CUtensorMap tmA, tmB;
+  int rc;
+  if (mode == 2) {
+    rc = bdl_make_tmap_2d_bf16(&tmA, other, static_cast<uint64_t>(O), static_cast<uint64_t>(Mpix), ld_other, 64, 64);
+    if (rc) return rc;
+    rc = bdl_make_tmap_im2col_bf16(&tmB, act, C, W, H, N, ld_act, -pw, -ph, up_w, up_h, 64, 64, sw, sh);
+    if (rc) return rc;
+  } else {
+    rc = bdl_make_tmap_im2col_bf16(&tmA, act, C, W, H, N, ld_act, -pw, -ph, up_w, up_h, 64, BM, sw, sh);
+    if (rc) return rc;
+    if (mode == 0)
+      rc = bdl_make_tmap_2d_bf16(&tmB, other, static_cast<uint64_t>(taps) * C, static_cast<uint64_t>(O), ld_other, 64,
+                                 p.block_n);
+    else  // weights [Cact rows, taps*O cols]
+      rc = bdl_make_tmap_2d_bf16(&tmB, other, static_cast<uint64_t>(taps) * O, static_cast<uint64_t>(C), ld_other, 64,
+                                 64);
+    if (rc) return rc;
+  }
+  const long long total = tiles_mn * splits;
+  const int grid = static_cast<int>(total < num_sms ? total : num_sms);
+#define BDL_LAUNCH_CONV(AMN, BMN, CV)                                                                             \
+  do {                                                                                                            \
+    auto kfn = gemm_bf16_tcgen05_kernel<AMN, BMN, CV>;                                                            \
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 256);     \
+    if (e != cudaSuccess) return bdl_fail_cuda("cudaFuncSetAttribute(conv gemm)", e);                             \
+    kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, p);                                                       \
+  } while (0)
+  if (mode == 0)
+    BDL_LAUNCH_CONV(false, false, 1);
+  else if (mode == 1)
+    BDL_LAUNCH_CONV(false, true, 1);
+  else
+    BDL_LAUNCH_CONV(true, true, 2);
+#undef BDL_LAUNCH_CONV
+  return bdl_check_launch("gemm_bf16_tcgen05_kernel<conv>");
 }

@@ -83,3 +83,49 @@ int bdl_make_tmap_2d_u8(CUtensorMap* out, const void* base, uint64_t dim0, uint6
                         uint32_t box1) {
   return make_tmap_2d(out, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, base, dim0, dim1, ld, box0, box1);
 }
+
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const int*, const int*, cuuint32_t, cuuint32_t,
+                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeIm2colFn get_encode_im2col() {
+  static EncodeIm2colFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeIm2colFn>(p);
+  });
+  return fn;
+}
+
+int bdl_make_tmap_im2col_bf16(CUtensorMap* out, const void* base, int C, int W, int H, int N, long long ld_pixel,
+                              int lower_w, int lower_h, int upper_w, int upper_h, int channels_per_pixel,
+                              int pixels_per_column, int stride_w, int stride_h) {
+  EncodeIm2colFn fn = get_encode_im2col();
+  if (!fn) return bdl_fail("cuTensorMapEncodeIm2col entry point not available (no CUDA driver?)");
+  cuuint64_t dims[4] = {static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H),
+                        static_cast<cuuint64_t>(N)};
+  cuuint64_t strides[3] = {static_cast<cuuint64_t>(ld_pixel) * 2, static_cast<cuuint64_t>(ld_pixel) * 2 * W,
+                           static_cast<cuuint64_t>(ld_pixel) * 2 * W * H};
+  int lower[2] = {lower_w, lower_h};
+  int upper[2] = {upper_w, upper_h};
+  cuuint32_t estr[4] = {1, static_cast<cuuint32_t>(stride_w), static_cast<cuuint32_t>(stride_h), 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, lower, upper,
+                  static_cast<cuuint32_t>(channels_per_pixel), static_cast<cuuint32_t>(pixels_per_column), estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    char buf[320];
+    snprintf(buf, sizeof(buf),
+             "cuTensorMapEncodeIm2col failed (CUresult %d) dims=(C%d,W%d,H%d,N%d) ld=%lld lower=(%d,%d) upper=(%d,%d) "
+             "cpp=%d ppc=%d stride=(%d,%d)",
+             (int)r, C, W, H, N, ld_pixel, lower_w, lower_h, upper_w, upper_h, channels_per_pixel, pixels_per_column,
+             stride_w, stride_h);
+    return bdl_fail(buf);
+  }
+  return BDL_OK;
+}

@@ -16,3 +16,9 @@ int bdl_make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t dim0, uin
 // Same for 1-byte elements (fp8): box0 is in elements (= bytes), at most 128.
 int bdl_make_tmap_2d_u8(CUtensorMap* out, const void* base, uint64_t dim0, uint64_t dim1, long long ld, uint32_t box0,
                         uint32_t box1);
+
+// 4-D NHWC im2col tensor map (dims {C, W, H, N}, pixel pitch ld elements): bounding box corners for W/H, number of
+// channels and pixels fetched per instruction, traversal strides. 128-byte swizzle, zero fill outside the tensor.
+int bdl_make_tmap_im2col_bf16(CUtensorMap* out, const void* base, int C, int W, int H, int N, long long ld_pixel,
+                              int lower_w, int lower_h, int upper_w, int upper_h, int channels_per_pixel,
+                              int pixels_per_column, int stride_w, int stride_h);

@@ -32,6 +32,14 @@ int bdl_sm_count(void);
 #define BDL_GEMM_ATOMIC_ADD 4
 int bdl_gemm_bf16(const void* A, const void* B, void* D, const float* bias, int M, int N, int K, long long lda,
                   long long ldb, long long ldd, int a_mn, int b_mn, int out_fp32, int flags, int splits, void* stream);
+/* Implicit-GEMM convolution on the same kernel: the gathered operand is fetched from the NHWC activation tensor by
+ * TMA im2col loads (no column matrix). mode 0 fprop, 1 dgrad (caller passes the transposed-conv geometry, stride 1),
+ * 2 wgrad (C % 64 == 0, accumulates with red.add). Reference: S/nn/SpatialConvolution.scala:253-521,
+ * S/nn/NNPrimitive.scala im2col/col2im, S/nn/mkldnn/SpatialConvolution.scala:435-633. */
+int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int W, int C, long long ld_act, const void* other,
+                        long long ld_other, void* D, long long ldd, const float* bias, int O, int Ho, int Wo, int kh,
+                        int kw, int sh, int sw, int ph, int pw, int dh, int dw, int out_fp32, int flags, int splits,
+                        void* stream);
 
 /* ---- elementwise / reductions on bf16 activations (csrc/elementwise.cu).
  *      Reference: S/nn/ReLU.scala, S/nn/Dropout.scala:40-75, S/nn/CAddTable.scala,

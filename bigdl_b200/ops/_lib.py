@@ -88,8 +88,12 @@ _SIGNATURES = {
     "bdl_bn_param_grad": [_P, _P, _P, _I, _F, _F, _P],
     "bdl_lstm_gates_fwd": [_P, _P, _P, _P, _P, _L, _I, _L, _P],
     "bdl_lstm_gates_bwd": [_P, _P, _P, _P, _P, _P, _P, _L, _I, _P],
+    "bdl_stream_capture_status": [_P],
     "bdl_compress_grads": [_P, _P, _Z, _I, _I, _P],
-    "bdl_fused_rs_update": [_P, _P, _P, _I, _I, _L, _L, _P, _P, _P, _P, _I, _P, _P, _I, ctypes.c_uint, _P, _P, _I, _P],
+    "bdl_fused_rs_update": [_P, _P, _P, _I, _I, _L, _L, _P, _P, _P, _P, _I, _P, _P, _I, ctypes.c_uint, _P, _P, _I, _P,
+                            _P],
+    "bdl_dropout_fwd_bf16_ctr": [_P, _P, _P, _Z, _F, _U64, _P, _P],
+    "bdl_counter_add": [_P, _U64, _P],
     "bdl_ipc_alloc": [_Z, _P, _P],
     "bdl_ipc_open": [_P, _P],
     "bdl_ipc_close": [_P],

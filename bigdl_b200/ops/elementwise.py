@@ -91,13 +91,31 @@ def copy2d(src2d: torch.Tensor, dst2d: torch.Tensor, accumulate: bool = False):
     return dst2d
 
 
-def dropout_fwd(x: torch.Tensor, p: float, seed: int, offset: int):
+_DROPOUT_CTR: dict = {}
+
+
+def dropout_counter(device) -> torch.Tensor:
+    """Per-device Philox stream position kept in device memory so that CUDA-graph replays draw fresh masks."""
+    c = _DROPOUT_CTR.get(device.index)
+    if c is None:
+        c = torch.zeros(1, dtype=torch.int64, device=device)
+        _DROPOUT_CTR[device.index] = c
+    return c
+
+
+def dropout_fwd(x: torch.Tensor, p: float, seed: int, offset: int | None = None):
     lib = _lib.cuda_lib()
     y = torch.empty_like(x)
     mask = torch.empty((x.numel() + 7) // 8, dtype=torch.uint8, device=x.device)
-    _lib.check(lib.bdl_dropout_fwd_bf16(x.data_ptr(), y.data_ptr(), mask.data_ptr(), x.numel(), float(p), seed, offset,
-                                        _lib.stream_ptr()), "bdl_dropout_fwd_bf16")
-    _lib.count_launch()
+    if offset is None:
+        _lib.check(lib.bdl_dropout_fwd_bf16_ctr(x.data_ptr(), y.data_ptr(), mask.data_ptr(), x.numel(), float(p), seed,
+                                                dropout_counter(x.device).data_ptr(), _lib.stream_ptr()),
+                   "bdl_dropout_fwd_bf16_ctr")
+        _lib.count_launch(2)
+    else:
+        _lib.check(lib.bdl_dropout_fwd_bf16(x.data_ptr(), y.data_ptr(), mask.data_ptr(), x.numel(), float(p), seed,
+                                            offset, _lib.stream_ptr()), "bdl_dropout_fwd_bf16")
+        _lib.count_launch()
     return y, mask
 
 

@@ -449,9 +449,7 @@ class DropoutFn(Function):
     @staticmethod
     def forward(ctx, x, p, seed):
         x = _dense_like(x)
-        off = _dropout_offset[0]
-        _dropout_offset[0] += (x.numel() + 7) // 8
-        y, mask = ew.dropout_fwd(x, p, seed, off)
+        y, mask = ew.dropout_fwd(x, p, seed)          # stream position lives on the device (graph-replay safe)
         ctx.save_for_backward(mask)
         ctx.p = p
         ctx.xstride = x.stride()

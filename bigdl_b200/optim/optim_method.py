@@ -260,15 +260,17 @@ def pack_hp(lr=0.0, wd=0.0, momentum=0.0, dampening=0.0, eps=0.0, gscale=1.0, cl
                        int(first_step), lr_power, l1, l2, l2_shrink)
 
 
-def native_update(kind: int, w: torch.Tensor, g: torch.Tensor, s0, s1, hp: bytes, w16=None, truncate=False,
-                  zero_grad=False):
+def native_update(kind: int, w: torch.Tensor, g: torch.Tensor, s0, s1, hp: bytes | None, w16=None, truncate=False,
+                  zero_grad=False, hp_dev: int | None = None):
+    """Flat fused update. ``hp`` (host bytes) is passed by value; ``hp_dev`` (device address of an OptimHP) wins when
+    given — that is what a captured CUDA graph uses so the schedule can change between replays."""
     from ..ops import _lib
 
     lib = _lib.cuda_lib()
-    buf = ctypes.create_string_buffer(hp, len(hp))
+    buf = ctypes.create_string_buffer(hp, len(hp)) if hp is not None else None
     _lib.check(lib.bdl_optim_update(kind, w.data_ptr(), g.data_ptr(), _lib.ptr(s0), _lib.ptr(s1), _lib.ptr(w16),
-                                    w.numel(), ctypes.cast(buf, ctypes.c_void_p), None, int(truncate), int(zero_grad),
-                                    _lib.stream_ptr()), "bdl_optim_update")
+                                    w.numel(), ctypes.cast(buf, ctypes.c_void_p) if buf is not None else None, hp_dev,
+                                    int(truncate), int(zero_grad), _lib.stream_ptr()), "bdl_optim_update")
     _lib.count_launch()
 
 
@@ -402,7 +404,8 @@ class SGD(OptimMethod):
 
     def _advance(self):
         self.learningRateSchedule.updateHyperParameter(self)
-        return -self.learningRateSchedule.currentRate, ("v" not in self._hist)
+        first = ("v" not in self._hist) or bool(self.__dict__.pop("_hist_fresh", False))
+        return -self.learningRateSchedule.currentRate, first
 
     def native_plan(self, x, g=None):
         if self.learningRates is not None or self.weightDecays is not None:

@@ -431,37 +431,55 @@ def _train_loop(opt: Optimizer, distributed: bool):
     pending_loss = None        # GPU: the loss is read back one iteration late so the host never stalls the stream
     loss_value = float("nan")
     use_fused_loss = device.type == "cuda"
+    graphs: dict = {}
+    graph_ok = (device.type == "cuda" and bool(config.get("bigdl.cudaGraph")) and single is not None
+                and clip.l2norm is None and sync.backend in ("local", "p2p") and config.get("bigdl.engineType") == "b200")
 
     while not opt.end_when(state):
         t0 = time.time()
         batch = next(data_iter)
         if not isinstance(batch, MiniBatch):
             raise TypeError("the training dataset must yield MiniBatch (use SampleToMiniBatch or pass batch_size)")
-        batch = opt._to_device(batch, device)
-        x, y = batch.getInput(), batch.getTarget()
         n_local = batch.size()
-        with torch.enable_grad():
-            out = model._call(x)
-            loss = criterion._call(out, y)
-        seed = torch.ones((), dtype=loss.dtype, device=loss.device)
-        seed._bdl_is_one = True
-        torch.autograd.backward(loss, seed)
-        model._apply_regularizers()
-
         for om in opt.optim_methods.values():
             om.clip_range = clip.constant
-        if single is not None:
-            sync.step(single, avg_numbers=world, l2_clip=clip.l2norm)
-        else:
-            _multi_method_step(opt, sync, flat, ranges, world, clip)
+        loss = None
+        if graph_ok and len(batch.inputs) == 1 and len(batch.targets) == 1:
+            loss = _graph_step(opt, graphs, model, criterion, sync, single, batch, device, world)
+            if loss is None:
+                graph_ok = False
+        if loss is None:
+            batch = opt._to_device(batch, device)
+            x, y = batch.getInput(), batch.getTarget()
+            with torch.enable_grad():
+                out = model._call(x)
+                loss = criterion._call(out, y)
+            seed = torch.ones((), dtype=loss.dtype, device=loss.device)
+            seed._bdl_is_one = True
+            torch.autograd.backward(loss, seed)
+            model._apply_regularizers()
+            if single is not None:
+                sync.step(single, avg_numbers=world, l2_clip=clip.l2norm)
+            else:
+                _multi_method_step(opt, sync, flat, ranges, world, clip)
 
         # ---- bookkeeping (DistriOptimizer.scala:399-474)
         if device.type == "cuda":
-            prev, pending_loss = pending_loss, loss.detach()
+            # D2H read of the step's result, lagging one iteration so the host never stalls the stream it feeds
+            snap = torch.empty(1, dtype=torch.float32).pin_memory() if not hasattr(opt, "_loss_ring") else None
+            if snap is not None:
+                opt._loss_ring = [snap, torch.empty(1, dtype=torch.float32).pin_memory()]
+                opt._loss_events = [torch.cuda.Event(), torch.cuda.Event()]
+                opt._loss_slot = 0
+            slot = opt._loss_slot
+            opt._loss_ring[slot].copy_(loss.detach().reshape(1).float(), non_blocking=True)
+            opt._loss_events[slot].record()
+            prev, pending_loss = pending_loss, (slot,)
+            opt._loss_slot = 1 - slot
             if prev is not None:
-                loss_value = float(prev)
-            elif not use_fused_loss:
-                loss_value = float(pending_loss)
+                opt._loss_events[prev[0]].synchronize()
+                loss_value = float(opt._loss_ring[prev[0]][0])
+
         else:
             loss_value = float(loss.detach())
         if distributed and world > 1 and device.type != "cuda":
@@ -498,7 +516,8 @@ def _train_loop(opt: Optimizer, distributed: bool):
                         distri_names=distributed)
 
     if pending_loss is not None:
-        state["Loss"] = float(pending_loss)
+        opt._loss_events[pending_loss[0]].synchronize()
+        state["Loss"] = float(opt._loss_ring[pending_loss[0]][0])
     sync.gather_master_weights()
     if flat.compute is not None and sync.backend == "local":
         flat.dirty = True
@@ -508,6 +527,24 @@ def _train_loop(opt: Optimizer, distributed: bool):
         # keep the symmetric buffers alive while the model still points its compute weights at them
         model._param_sync_keepalive = sync
     return model
+
+
+def _graph_step(opt, graphs, model, criterion, sync, om, batch, device, world):
+    """Run one iteration through a captured CUDA graph (one graph per batch shape). Returns the loss tensor, or None
+    when this configuration cannot be captured (the caller then falls back to eager execution for good)."""
+    from .graph_step import GraphedTrainStep
+
+    x, y = batch.inputs[0], batch.targets[0]
+    key = (tuple(x.shape), x.dtype, tuple(y.shape), y.dtype)
+    gs = graphs.get(key)
+    if gs is None:
+        try:
+            gs = GraphedTrainStep(model, criterion, sync, om, x.to(device), y.to(device), world)
+        except NotImplementedError as e:
+            log.warning("CUDA-graph capture unavailable for this configuration (%s); running eagerly", e)
+            return None
+        graphs[key] = gs        # capture warm-ups were rolled back; fall through to the first real replay
+    return gs.run(x, y)
 
 
 def _multi_method_step(opt, sync, flat, ranges, world, clip):

@@ -119,6 +119,7 @@ class AllReduceParameter:
         w16 = self._sym.view(torch.bfloat16, self._off_w16, P)
         self._rebind_compute(w16)
         self._local_sync = torch.zeros(2, dtype=torch.int32, device=self.device)
+        self._epoch_dev = torch.zeros(1, dtype=torch.int64, device=self.device)   # barrier generation, device resident
         self._sumsq = torch.zeros(1, dtype=torch.float32, device=self.device)
         self._g16_ptrs = self._sym.peer_ptr_array(self._off_g16)
         self._w16_ptrs = self._sym.peer_ptr_array(self._off_w16)
@@ -160,6 +161,48 @@ class AllReduceParameter:
         if self.backend == "nccl":
             return self._step_nccl(optim_method, avg, l2_clip)
         return self._step_gloo(optim_method, avg, l2_clip)
+
+    # ---- graph-capturable form: every per-step scalar comes from device memory
+    def update_target(self) -> torch.Tensor:
+        """The fp32 vector the OptimMethod updates on this rank (whole vector locally, my slice when sharded)."""
+        return self.flat.weights if self.backend == "local" else self.weight_partition
+
+    def grad_scale_for(self, world: int) -> float:
+        if self.backend == "p2p" and self.truncate:
+            return float(world)          # parity mode divides (CM_DIVIDE)
+        return 1.0 / world
+
+    def step_device_hp(self, plan, hp_dev: int, epoch_dev: int):
+        """``step`` with the OptimHP read from ``hp_dev`` and the barrier generation from ``epoch_dev`` — safe to
+        capture in a CUDA graph. ``plan`` = (kind, _, s0, s1) from ``OptimMethod.native_plan``."""
+        from ..ops import _lib
+        from ..optim.optim_method import native_update
+
+        if not self._inited:
+            self.init()
+        kind, _, s0, s1 = plan
+        fl = self.flat
+        if self.backend == "local":
+            native_update(kind, fl.weights, fl.grads, s0, s1, None, fl.compute, self.truncate, zero_grad=True,
+                          hp_dev=hp_dev)
+            fl.dirty = False
+            return
+        if self.backend != "p2p":
+            raise NotImplementedError("graph-captured steps run on the local and p2p parameter backends")
+        lib = _lib.cuda_lib()
+        st = _lib.stream_ptr()
+        _lib.check(lib.bdl_compress_grads(fl.grads.data_ptr(), self.g16.data_ptr(), self.P, int(self.truncate), 1, st),
+                   "bdl_compress_grads")
+        parity = CM_PARITY | CM_DIVIDE if self.truncate else 0
+        mode = CM_REDUCE | CM_UPDATE | CM_PUBLISH | CM_BARRIER_BEGIN | CM_BARRIER_END | parity
+        _lib.check(lib.bdl_fused_rs_update(self._g16_ptrs, self._w16_ptrs, self._flag_ptrs, self.world, self.rank,
+                                           self.start, self.length, self.weight_partition.data_ptr(),
+                                           self.gradient_partition.data_ptr(), _lib.ptr(s0), _lib.ptr(s1), kind, None,
+                                           hp_dev, mode, 1, self._local_sync.data_ptr(), self._sumsq.data_ptr(), 0,
+                                           self._epoch_dev.data_ptr(), st), "bdl_fused_rs_update")
+        _lib.check(lib.bdl_counter_add(self._epoch_dev.data_ptr(), 1, st), "bdl_counter_add")
+        _lib.count_launch(3)
+        fl.dirty = False
 
     # ---- world size 1
     def _step_local(self, om, avg, l2_clip):
@@ -212,13 +255,16 @@ class AllReduceParameter:
         from ..ops import _lib
 
         buf = ctypes.create_string_buffer(hp, len(hp))
+        # generation = 1 + device counter; the counter is bumped after every launch so eager and graph-replayed steps
+        # share one monotone sequence on every rank
         _lib.check(lib.bdl_fused_rs_update(self._g16_ptrs, self._w16_ptrs, self._flag_ptrs, self.world, self.rank,
                                            self.start, self.length, self.weight_partition.data_ptr(),
                                            self.gradient_partition.data_ptr(), _lib.ptr(s0), _lib.ptr(s1), kind,
-                                           ctypes.cast(buf, ctypes.c_void_p), None, mode, self.epoch,
-                                           self._local_sync.data_ptr(), self._sumsq.data_ptr(), 0, st),
-                   "bdl_fused_rs_update")
-        _lib.count_launch()
+                                           ctypes.cast(buf, ctypes.c_void_p), None, mode, 1,
+                                           self._local_sync.data_ptr(), self._sumsq.data_ptr(), 0,
+                                           self._epoch_dev.data_ptr(), st), "bdl_fused_rs_update")
+        _lib.check(lib.bdl_counter_add(self._epoch_dev.data_ptr(), 1, st), "bdl_counter_add")
+        _lib.count_launch(2)
 
     # ---- NCCL baseline
     def _step_nccl(self, om, avg, l2_clip):

@@ -61,7 +61,28 @@ __global__ void bn_reduce_kernel(const __nv_bfloat16* __restrict__ a, const __nv
       }
     }
     if (tr < rif) {
-      for (long long r = r0 + tr; r < r1; r += rif) {
+      long long r = r0 + tr;
+      if (kMode == 0) {
+        // forward statistics: 4 independent 16-byte loads in flight per thread
+        for (; r + 3ll * rif < r1; r += 4ll * rif) {
+          uint4 v[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) v[u] = *reinterpret_cast<const uint4*>(a + (r + u * rif) * lda + cv * 8);
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const __nv_bfloat162* q = reinterpret_cast<const __nv_bfloat162*>(&v[u]);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const float2 t = __bfloat1622float2(q[j]);
+              s0[2 * j] += t.x;
+              s0[2 * j + 1] += t.y;
+              s1[2 * j] = fmaf(t.x, t.x, s1[2 * j]);
+              s1[2 * j + 1] = fmaf(t.y, t.y, s1[2 * j + 1]);
+            }
+          }
+        }
+      }
+      for (; r < r1; r += rif) {
         float fa[8];
         bn_load8(a + r * lda + cv * 8, fa);
         if (kMode == 0) {
@@ -131,63 +152,141 @@ __global__ void bn_finalize_kernel(const float* __restrict__ sums, float count, 
 
 // y = (x - mean) * invstd * gamma + beta (+ReLU). For inference pass mean = running mean and invstd computed from
 // the running variance (use_var = 1 makes the kernel derive invstd = rsqrt(var + eps) itself).
+// Thread layout: blockDim.x = vcols * rif; a thread owns ONE 8-channel vector column (its scale/shift live in
+// registers) and streams rows with 4 independent 16-byte loads in flight — no per-element index arithmetic.
 __global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
                                 const float* __restrict__ mean, const float* __restrict__ invstd_or_var,
                                 const float* __restrict__ gamma, const float* __restrict__ beta, long long M, int C,
-                                long long ldx, long long ldy, float eps, int use_var, int relu) {
+                                long long ldx, long long ldy, float eps, int use_var, int relu, int rows_per_block) {
   const int cvec = C / 8;
-  const long long total = M * cvec;
-  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int cv = static_cast<int>(i % cvec);
-    const long long r = i / cvec;
-    float f[8];
-    bn_load8(x + r * ldx + cv * 8, f);
+  const int vcols = cvec < static_cast<int>(blockDim.x) ? cvec : blockDim.x;
+  const int rif = blockDim.x / vcols;
+  const int tc = threadIdx.x % vcols;
+  const int tr = threadIdx.x / vcols;
+  if (tr >= rif) return;
+  const long long r0 = static_cast<long long>(blockIdx.x) * rows_per_block;
+  long long r1 = r0 + rows_per_block;
+  if (r1 > M) r1 = M;
+  for (int cv = tc; cv < cvec; cv += vcols) {
+    float sa[8], sb[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const int c = cv * 8 + j;
       const float is = use_var ? rsqrtf(invstd_or_var[c] + eps) : invstd_or_var[c];
-      const float g = gamma ? gamma[c] : 1.f;
-      const float b = beta ? beta[c] : 0.f;
-      float v = (f[j] - mean[c]) * is * g + b;
-      f[j] = relu ? fmaxf(v, 0.f) : v;
+      sa[j] = is * (gamma ? gamma[c] : 1.f);
+      sb[j] = (beta ? beta[c] : 0.f) - mean[c] * sa[j];
     }
-    bn_store8(y + r * ldy + cv * 8, f);
+    const __nv_bfloat16* xp = x + cv * 8;
+    __nv_bfloat16* yp = y + cv * 8;
+    long long r = r0 + tr;
+    for (; r + 3ll * rif < r1; r += 4ll * rif) {
+      uint4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = *reinterpret_cast<const uint4*>(xp + (r + u * rif) * ldx);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const __nv_bfloat162* q = reinterpret_cast<const __nv_bfloat162*>(&v[u]);
+        float f[8];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 t = __bfloat1622float2(q[j]);
+          f[2 * j] = fmaf(t.x, sa[2 * j], sb[2 * j]);
+          f[2 * j + 1] = fmaf(t.y, sa[2 * j + 1], sb[2 * j + 1]);
+        }
+        if (relu) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+        }
+        bn_store8(yp + (r + u * rif) * ldy, f);
+      }
+    }
+    for (; r < r1; r += rif) {
+      float f[8];
+      bn_load8(xp + r * ldx, f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        f[j] = fmaf(f[j], sa[j], sb[j]);
+        if (relu) f[j] = fmaxf(f[j], 0.f);
+      }
+      bn_store8(yp + r * ldy, f);
+    }
   }
 }
 
 // dx = gamma * invstd * (dy' - dbeta/count - x̂ * dgamma/count), dy' = dy masked by (y > 0) when ReLU was fused.
+// Rewritten per channel as dx = ka * dy' + kb * x + kc with
+//   ka = gamma*invstd, kb = -gamma*invstd^2*dgamma/count, kc = -ka*dbeta/count - kb*mean.
 __global__ void bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                                     const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean,
                                     const float* __restrict__ invstd, const float* __restrict__ gamma,
                                     const float* __restrict__ sums, __nv_bfloat16* __restrict__ dx, long long M,
                                     float count, int C, long long lddy, long long ldx, long long ldy,
-                                    long long lddx) {
+                                    long long lddx, int rows_per_block) {
   const int cvec = C / 8;
-  const long long total = M * cvec;
-  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const int vcols = cvec < static_cast<int>(blockDim.x) ? cvec : blockDim.x;
+  const int rif = blockDim.x / vcols;
+  const int tc = threadIdx.x % vcols;
+  const int tr = threadIdx.x / vcols;
+  if (tr >= rif) return;
+  const long long r0 = static_cast<long long>(blockIdx.x) * rows_per_block;
+  long long r1 = r0 + rows_per_block;
+  if (r1 > M) r1 = M;
   const float inv_count = 1.f / count;
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int cv = static_cast<int>(i % cvec);
-    const long long r = i / cvec;
-    float g[8], fx[8];
-    bn_load8(dy + r * lddy + cv * 8, g);
-    bn_load8(x + r * ldx + cv * 8, fx);
-    if (y) {
-      float fy[8];
-      bn_load8(y + r * ldy + cv * 8, fy);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) g[j] = fy[j] > 0.f ? g[j] : 0.f;
-    }
+  for (int cv = tc; cv < cvec; cv += vcols) {
+    float ka[8], kb[8], kc[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const int c = cv * 8 + j;
       const float is = invstd[c];
-      const float xh = (fx[j] - mean[c]) * is;
       const float gm = gamma ? gamma[c] : 1.f;
-      g[j] = gm * is * (g[j] - sums[c] * inv_count - xh * sums[C + c] * inv_count);
+      ka[j] = gm * is;
+      kb[j] = -gm * is * is * sums[C + c] * inv_count;
+      kc[j] = -ka[j] * sums[c] * inv_count - kb[j] * mean[c];
     }
-    bn_store8(dx + r * lddx + cv * 8, g);
+    long long r = r0 + tr;
+    for (; r + 1ll * rif < r1; r += 2ll * rif) {
+      uint4 vg[2], vx[2], vy[2];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        vg[u] = *reinterpret_cast<const uint4*>(dy + (r + u * rif) * lddy + cv * 8);
+        vx[u] = *reinterpret_cast<const uint4*>(x + (r + u * rif) * ldx + cv * 8);
+        if (y) vy[u] = *reinterpret_cast<const uint4*>(y + (r + u * rif) * ldy + cv * 8);
+      }
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const __nv_bfloat162* qg = reinterpret_cast<const __nv_bfloat162*>(&vg[u]);
+        const __nv_bfloat162* qx = reinterpret_cast<const __nv_bfloat162*>(&vx[u]);
+        const __nv_bfloat162* qy = reinterpret_cast<const __nv_bfloat162*>(&vy[u]);
+        float f[8];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          float2 g2 = __bfloat1622float2(qg[j]);
+          const float2 x2 = __bfloat1622float2(qx[j]);
+          if (y) {
+            const float2 y2 = __bfloat1622float2(qy[j]);
+            g2.x = y2.x > 0.f ? g2.x : 0.f;
+            g2.y = y2.y > 0.f ? g2.y : 0.f;
+          }
+          f[2 * j] = fmaf(ka[2 * j], g2.x, fmaf(kb[2 * j], x2.x, kc[2 * j]));
+          f[2 * j + 1] = fmaf(ka[2 * j + 1], g2.y, fmaf(kb[2 * j + 1], x2.y, kc[2 * j + 1]));
+        }
+        bn_store8(dx + (r + u * rif) * lddx + cv * 8, f);
+      }
+    }
+    for (; r < r1; r += rif) {
+      float g[8], fx[8];
+      bn_load8(dy + r * lddy + cv * 8, g);
+      bn_load8(x + r * ldx + cv * 8, fx);
+      if (y) {
+        float fy[8];
+        bn_load8(y + r * ldy + cv * 8, fy);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] = fy[j] > 0.f ? g[j] : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) g[j] = fmaf(ka[j], g[j], fmaf(kb[j], fx[j], kc[j]));
+      bn_store8(dx + r * lddx + cv * 8, g);
+    }
   }
 }
 
@@ -219,15 +318,29 @@ static int bn_check(const char* who, int C, long long l0, long long l1, const vo
 
 using namespace bdl;
 
-static void reduce_geometry(long long M, int C, int* grid, int* rpb, size_t* smem) {
+// streaming kernels: ~16 CTAs per SM so that every SM keeps 2048 threads x 4 loads in flight
+static void stream_geometry(long long M, int C, int* grid, int* rpb, size_t* smem) {
   const int sms = bdl_num_sms();
-  long long r = (M + sms * 4 - 1) / (sms * 4);
-  if (r < 32) r = 32;
-  *rpb = static_cast<int>(r);
-  *grid = static_cast<int>((M + r - 1) / r);
   const int cvec = C / 8;
   const int vcols = cvec < 256 ? cvec : 256;
   const int rif = 256 / vcols;
+  long long r = (M + sms * 16 - 1) / (sms * 16);
+  const long long min_rows = 4ll * rif;
+  if (r < min_rows) r = min_rows;
+  *rpb = static_cast<int>(r);
+  *grid = static_cast<int>((M + r - 1) / r);
+  *smem = 0;
+}
+
+static void reduce_geometry(long long M, int C, int* grid, int* rpb, size_t* smem) {
+  const int sms = bdl_num_sms();
+  const int cvec = C / 8;
+  const int vcols = cvec < 256 ? cvec : 256;
+  const int rif = 256 / vcols;
+  long long r = (M + sms * 8 - 1) / (sms * 8);
+  if (r < 4ll * rif) r = 4ll * rif;
+  *rpb = static_cast<int>(r);
+  *grid = static_cast<int>((M + r - 1) / r);
   *smem = static_cast<size_t>(rif) * vcols * 16 * sizeof(float);
 }
 
@@ -255,9 +368,12 @@ extern "C" int bdl_bn_apply(const void* x, void* y, const float* mean, const flo
                             int use_var, int relu, void* stream) {
   if (bn_check("bdl_bn_apply: C and pitches must be multiples of 8, pointers 16-byte aligned", C, ldx, ldy, x, y))
     return BDL_ERR_INVALID;
-  bn_apply_kernel<<<bn_grid(M * (C / 8)), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  int grid, rpb;
+  size_t smem_unused;
+  stream_geometry(M, C, &grid, &rpb, &smem_unused);
+  bn_apply_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), mean, invstd_or_var, gamma, beta, M, C,
-      ldx, ldy, eps, use_var, relu);
+      ldx, ldy, eps, use_var, relu, rpb);
   return bdl_check_launch("bn_apply_kernel");
 }
 
@@ -283,10 +399,13 @@ extern "C" int bdl_bn_bwd_apply(const void* dy, const void* x, const void* y, co
   if (bn_check("bdl_bn_bwd_apply: C and pitches must be multiples of 8, pointers 16-byte aligned", C, lddy, lddx, dy,
                dx))
     return BDL_ERR_INVALID;
-  bn_bwd_apply_kernel<<<bn_grid(M * (C / 8)), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  int grid, rpb;
+  size_t smem_unused;
+  stream_geometry(M, C, &grid, &rpb, &smem_unused);
+  bn_bwd_apply_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
       static_cast<const __nv_bfloat16*>(y), mean, invstd, gamma, sums, static_cast<__nv_bfloat16*>(dx), M, count, C,
-      lddy, ldx, ldy, lddx);
+      lddy, ldx, ldy, lddx, rpb);
   return bdl_check_launch("bn_bwd_apply_kernel");
 }
 

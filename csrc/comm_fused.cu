@@ -70,8 +70,10 @@ __global__ void __launch_bounds__(512)
 fused_rs_update_kernel(const PeerTable peers, int nranks, int rank, long long start, long long length,
                        float* __restrict__ master, float* __restrict__ grad_part, float* __restrict__ s0,
                        float* __restrict__ s1, int kind, OptimHP hp, const OptimHP* __restrict__ hp_dev, int mode,
-                       uint32_t epoch, uint32_t* __restrict__ local_sync, float* __restrict__ sumsq) {
+                       uint32_t epoch, uint32_t* __restrict__ local_sync, float* __restrict__ sumsq,
+                       const unsigned long long* __restrict__ epoch_dev) {
   if (hp_dev) hp = *hp_dev;
+  if (epoch_dev) epoch += static_cast<uint32_t>(*epoch_dev);   // graph replays: the step counter lives on the device
   const bool parity = (mode & CM_PARITY) != 0;
 
   // ---------------- begin barrier: every rank's compressed gradients are complete and visible
@@ -295,7 +297,7 @@ extern "C" int bdl_fused_rs_update(const void* const* grad16_ptrs, void* const* 
                                    int nranks, int rank, long long start, long long length, float* master,
                                    float* grad_part, float* s0, float* s1, int kind, const void* hp_host,
                                    const void* hp_dev, int mode, unsigned int epoch, void* local_sync, float* sumsq,
-                                   int max_blocks, void* stream) {
+                                   int max_blocks, const void* epoch_dev, void* stream) {
   if (nranks < 1 || nranks > kMaxPeers) return bdl_fail("bdl_fused_rs_update: nranks must be in [1,16]");
   if ((start % 8) || (length % 8)) return bdl_fail("bdl_fused_rs_update: slice must be 8-element aligned");
   if (length == 0 && !(mode & (CM_BARRIER_BEGIN | CM_BARRIER_END))) return BDL_OK;
@@ -317,7 +319,7 @@ extern "C" int bdl_fused_rs_update(const void* const* grad16_ptrs, void* const* 
   if (blocks < 1) blocks = 1;
   fused_rs_update_kernel<<<static_cast<int>(blocks), threads, 0, static_cast<cudaStream_t>(stream)>>>(
       pt, nranks, rank, start, length, master, grad_part, s0, s1, kind, hp, static_cast<const OptimHP*>(hp_dev), mode,
-      epoch, static_cast<uint32_t*>(local_sync), sumsq);
+      epoch, static_cast<uint32_t*>(local_sync), sumsq, static_cast<const unsigned long long*>(epoch_dev));
   return bdl_check_launch("fused_rs_update_kernel");
 }
 

@@ -251,7 +251,9 @@ __device__ __forceinline__ uint4 philox4x32(uint2 key, uint4 ctr) {
 // y = x * keep / (1-p); the keep mask is packed one byte per 8 elements for the backward pass.
 __global__ void dropout_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
                                    uint8_t* __restrict__ mask, size_t n, float p, float scale,
-                                   unsigned long long seed, unsigned long long offset) {
+                                   unsigned long long seed, unsigned long long offset,
+                                   const unsigned long long* __restrict__ offset_dev) {
+  if (offset_dev) offset += *offset_dev;   // device-resident stream position (CUDA-graph replays get fresh masks)
   const size_t nvec = (n + 7) / 8;
   const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
   const uint32_t thresh = static_cast<uint32_t>(fminf(p, 1.f) * 16777216.f);  // compare on 24 bits
@@ -321,9 +323,17 @@ __global__ void copy2d_bf16_kernel(const __nv_bfloat16* __restrict__ src, __nv_b
   }
 }
 
+__global__ void counter_add_kernel(unsigned long long* c, unsigned long long v) { *c += v; }
+
 }  // namespace bdl
 
 using namespace bdl;
+
+// *counter += v, stream ordered (device-side step counters for graph-captured training steps)
+extern "C" int bdl_counter_add(void* counter_dev, unsigned long long v, void* stream) {
+  counter_add_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<unsigned long long*>(counter_dev), v);
+  return bdl_check_launch("counter_add_kernel");
+}
 
 extern "C" int bdl_cast_f32_to_bf16(const float* src, void* dst, size_t n, int truncate, void* stream) {
   if (n == 0) return BDL_OK;
@@ -429,8 +439,22 @@ extern "C" int bdl_dropout_fwd_bf16(const void* x, void* y, void* mask, size_t n
   const float scale = p < 1.f ? 1.f / (1.f - p) : 0.f;
   dropout_fwd_kernel<<<ew_grid((n + 7) / 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), static_cast<uint8_t*>(mask), n, p, scale,
-      seed, offset);
+      seed, offset, nullptr);
   return bdl_check_launch("dropout_fwd_kernel");
+}
+
+// Same, but the Philox stream position is read from device memory and advanced afterwards by bdl_counter_add, so a
+// captured CUDA graph draws a new mask on every replay.
+extern "C" int bdl_dropout_fwd_bf16_ctr(const void* x, void* y, void* mask, size_t n, float p, unsigned long long seed,
+                                        void* counter_dev, void* stream) {
+  if (n == 0) return BDL_OK;
+  const float scale = p < 1.f ? 1.f / (1.f - p) : 0.f;
+  dropout_fwd_kernel<<<ew_grid((n + 7) / 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), static_cast<uint8_t*>(mask), n, p, scale,
+      seed, 0ull, static_cast<const unsigned long long*>(counter_dev));
+  int rc = bdl_check_launch("dropout_fwd_kernel");
+  if (rc) return rc;
+  return bdl_counter_add(counter_dev, (n + 7) / 8, stream);
 }
 
 extern "C" int bdl_dropout_bwd_bf16(const void* dy, const void* mask, void* dx, size_t n, float p, void* stream) {

@@ -27,6 +27,25 @@ constexpr int kGemmThreads = 192;
 constexpr int kTmemCols = 512;
 constexpr int kAccStride = 256;  // TMEM columns between the two accumulator stages
 
+// Division by a runtime constant without the ~100-cycle integer divide sequence: the single producer thread decodes
+// pixel / tap coordinates for every k block, so its divides sit on the critical path of the TMA issue rate.
+struct FastDiv {
+  uint32_t mul, shr, div;
+  __host__ void init(uint32_t d) {
+    div = d;
+    if (d <= 1) { mul = 0; shr = 0; return; }
+    uint32_t l = 0;
+    while ((1ull << l) < d) ++l;
+    mul = static_cast<uint32_t>(((1ull << 32) * ((1ull << l) - d)) / d + 1);
+    shr = l;
+  }
+  __device__ __forceinline__ uint32_t quot(uint32_t n) const {
+    if (div <= 1) return n;
+    const uint32_t t = __umulhi(n, mul);
+    return (t + ((n - t) >> 1)) >> (shr - 1);
+  }
+};
+
 struct GemmParams {
   int M, N, K;
   int block_n;     // UMMA N (multiple of 16, <= 256)
@@ -51,6 +70,7 @@ struct GemmParams {
   int cv_flip;               // dgrad: B uses the spatially flipped tap
   int cv_num_kb;             // number of 64-wide k blocks (taps * cblocks for fprop/dgrad, ceil(M/64) for wgrad)
   int cv_nimg;               // batch size of the gathered tensor (first out-of-bounds image index)
+  FastDiv fd_hw, fd_wo, fd_cblocks, fd_kw, fd_c;
 };
 
 // kConv: 0 plain GEMM; 1 A operand via im2col TMA (conv fprop, and dgrad when kBMN); 2 B operand via im2col TMA (wgrad)
@@ -109,6 +129,35 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         const int kb1 = static_cast<int>((static_cast<long long>(split + 1) * num_kb) / p.splits);
         const int m0 = m_blk * BM;
         const int n0 = n_blk * p.block_n;
+        // implicit-GEMM bookkeeping hoisted out of the k loop
+        int cv_img = 0, cv_h = 0, cv_w = 0, cv_r = 0, cv_s = 0, cv_cb = 0;
+        int at_c0[4] = {0, 0, 0, 0};
+        uint16_t at_ow[4] = {0, 0, 0, 0}, at_oh[4] = {0, 0, 0, 0};
+        bool at_ok[4] = {false, false, false, false};
+        if (kConv == 1) {
+          const uint32_t img = p.fd_hw.quot(static_cast<uint32_t>(m0));
+          const uint32_t rem = static_cast<uint32_t>(m0) - img * p.fd_hw.div;
+          const uint32_t ho = p.fd_wo.quot(rem);
+          const uint32_t wo = rem - ho * p.fd_wo.div;
+          cv_img = static_cast<int>(img);
+          cv_h = static_cast<int>(ho) * p.cv_sh - p.cv_ph;
+          cv_w = static_cast<int>(wo) * p.cv_sw - p.cv_pw;
+          const uint32_t tap = p.fd_cblocks.quot(static_cast<uint32_t>(kb0));
+          cv_cb = kb0 - static_cast<int>(tap) * p.cv_cblocks;
+          cv_r = static_cast<int>(p.fd_kw.quot(tap));
+          cv_s = static_cast<int>(tap) - cv_r * p.cv_kw;
+        } else if (kConv == 2) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const uint32_t ncol = static_cast<uint32_t>(n0 + 64 * j);
+            const uint32_t tap = p.fd_c.quot(ncol);
+            const uint32_t r = p.fd_kw.quot(tap);
+            at_c0[j] = static_cast<int>(ncol - tap * p.fd_c.div);
+            at_ow[j] = static_cast<uint16_t>((tap - r * p.fd_kw.div) * p.cv_dw);
+            at_oh[j] = static_cast<uint16_t>(r * p.cv_dh);
+            at_ok[j] = tap < static_cast<uint32_t>(p.cv_kh * p.cv_kw);
+          }
+        }
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
           const uint32_t fb = smem_u32(&full_bar[stage]);
@@ -118,42 +167,41 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           const int k0 = kb * BK;
           if (kConv == 1) {
             // k block = (filter tap, 64-channel block); A tile = 128 consecutive output pixels of that tap
-            const int tap = kb / p.cv_cblocks;
-            const int cb = kb - tap * p.cv_cblocks;
-            const int r = tap / p.cv_kw, sx = tap - r * p.cv_kw;
-            const int hw = p.cv_Ho * p.cv_Wo;
-            const int img = m0 / hw;
-            const int rem = m0 - img * hw;
-            const int ho = rem / p.cv_Wo, wo = rem - ho * p.cv_Wo;
-            tma_load_im2col_4d(sa, &tmA, fb, cb * 64, wo * p.cv_sw - p.cv_pw, ho * p.cv_sh - p.cv_ph, img,
-                               static_cast<uint16_t>(sx * p.cv_dw), static_cast<uint16_t>(r * p.cv_dh));
+            tma_load_im2col_4d(sa, &tmA, fb, cv_cb * 64, cv_w, cv_h, cv_img, static_cast<uint16_t>(cv_s * p.cv_dw),
+                               static_cast<uint16_t>(cv_r * p.cv_dh));
+            const int tap = cv_r * p.cv_kw + cv_s;
             if (kBMN) {
               // dgrad: B[k = cout block][n = cin] is the (flipped) tap's [Cout, Cin] slice of the OHWI weights
-              const int btap = p.cv_flip ? (p.cv_kh - 1 - r) * p.cv_kw + (p.cv_kw - 1 - sx) : tap;
+              const int btap = p.cv_flip ? (p.cv_kh - 1 - cv_r) * p.cv_kw + (p.cv_kw - 1 - cv_s) : tap;
               for (int j = 0; j < p.b_rows / 64; ++j)
-                tma_load_2d(sb + j * 8192u, &tmB, fb, btap * p.N + n0 + 64 * j, cb * 64);
+                tma_load_2d(sb + j * 8192u, &tmB, fb, btap * p.N + n0 + 64 * j, cv_cb * 64);
             } else {
-              tma_load_2d(sb, &tmB, fb, tap * p.cv_C + cb * 64, n0);
+              tma_load_2d(sb, &tmB, fb, tap * p.cv_C + cv_cb * 64, n0);
+            }
+            if (++cv_cb == p.cv_cblocks) {   // advance (tap, channel block) without dividing
+              cv_cb = 0;
+              if (++cv_s == p.cv_kw) {
+                cv_s = 0;
+                ++cv_r;
+              }
             }
           } else if (kConv == 2) {
             // wgrad: k block = 64 consecutive output pixels; A = dY^T (MN-major), B atoms = im2col gathers
             tma_load_2d(sa, &tmA, fb, m0, k0);
             tma_load_2d(sa + 8192u, &tmA, fb, m0 + 64, k0);
-            const int hw = p.cv_Ho * p.cv_Wo;
-            const int img = k0 / hw;
-            const int rem = k0 - img * hw;
-            const int ho = rem / p.cv_Wo, wo = rem - ho * p.cv_Wo;
-            for (int j = 0; j < p.b_rows / 64; ++j) {
-              const int ncol = n0 + 64 * j;            // column in the [taps * C] space (C % 64 == 0)
-              const int tap = ncol / p.cv_C;
-              const int c0 = ncol - tap * p.cv_C;
-              const int r = tap / p.cv_kw, sx = tap - r * p.cv_kw;
-              if (tap < p.cv_kh * p.cv_kw)
-                tma_load_im2col_4d(sb + j * 8192u, &tmB, fb, c0, wo * p.cv_sw - p.cv_pw, ho * p.cv_sh - p.cv_ph, img,
-                                   static_cast<uint16_t>(sx * p.cv_dw), static_cast<uint16_t>(r * p.cv_dh));
-              else
-                tma_load_im2col_4d(sb + j * 8192u, &tmB, fb, 0, -p.cv_pw, -p.cv_ph, p.cv_nimg, 0,
-                                   0);   // past the last tap: a box that starts after the last image (zero fill)
+            const uint32_t img = p.fd_hw.quot(static_cast<uint32_t>(k0));
+            const uint32_t rem = static_cast<uint32_t>(k0) - img * p.fd_hw.div;
+            const uint32_t ho = p.fd_wo.quot(rem);
+            const uint32_t wo = rem - ho * p.fd_wo.div;
+            const int w = static_cast<int>(wo) * p.cv_sw - p.cv_pw, h = static_cast<int>(ho) * p.cv_sh - p.cv_ph;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              if (j < p.b_rows / 64) {
+                if (at_ok[j])
+                  tma_load_im2col_4d(sb + j * 8192u, &tmB, fb, at_c0[j], w, h, static_cast<int>(img), at_ow[j], at_oh[j]);
+                else  // past the last tap: a box that starts after the last image (zero fill)
+                  tma_load_im2col_4d(sb + j * 8192u, &tmB, fb, 0, -p.cv_pw, -p.cv_ph, p.cv_nimg, 0, 0);
+              }
             }
           } else {
           if (kAMN) {
@@ -441,6 +489,11 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
   GemmParams p{};
   p.cv_Ho = Ho; p.cv_Wo = Wo; p.cv_sh = sh; p.cv_sw = sw; p.cv_ph = ph; p.cv_pw = pw; p.cv_dh = dh; p.cv_dw = dw;
   p.cv_kh = kh; p.cv_kw = kw; p.cv_C = C; p.cv_cblocks = (C + 63) / 64; p.cv_flip = (mode == 1); p.cv_nimg = N;
+  p.fd_hw.init(static_cast<uint32_t>(Ho) * Wo);
+  p.fd_wo.init(static_cast<uint32_t>(Wo));
+  p.fd_cblocks.init(static_cast<uint32_t>(p.cv_cblocks));
+  p.fd_kw.init(static_cast<uint32_t>(kw));
+  p.fd_c.init(static_cast<uint32_t>(C));
   int gm, gn;
   if (mode == 2) {
     gm = O;

@@ -129,3 +129,15 @@ int bdl_make_tmap_im2col_bf16(CUtensorMap* out, const void* base, int C, int W, 
   }
   return BDL_OK;
 }
+
+// 0 = not capturing, 1 = capture active, 2 = capture invalidated (an illegal call happened), <0 = query failed.
+// Diagnostic used when a graph capture of a training step fails: poll it after each op to find the offender.
+extern "C" int bdl_stream_capture_status(void* stream) {
+  cudaStreamCaptureStatus st;
+  cudaError_t e = cudaStreamIsCapturing(static_cast<cudaStream_t>(stream), &st);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return -static_cast<int>(e);
+  }
+  return static_cast<int>(st);
+}

@@ -38,14 +38,15 @@ __device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&f)[8]) {
 }
 
 // ---------------------------------------------------------------- max pooling
+template <typename I>
 __global__ void maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
                                    uint8_t* __restrict__ idx, const PoolGeom g) {
   const int cvec = g.C / 8;
-  const long long total = static_cast<long long>(g.N) * g.Ho * g.Wo * cvec;
-  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+  const I total = static_cast<I>(g.N) * g.Ho * g.Wo * cvec;
+  const I stride = static_cast<I>(gridDim.x) * blockDim.x;
+  for (I i = static_cast<I>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
     const int cv = static_cast<int>(i % cvec);
-    long long t = i / cvec;
+    I t = i / cvec;
     const int wo = static_cast<int>(t % g.Wo);
     t /= g.Wo;
     const int ho = static_cast<int>(t % g.Ho);
@@ -86,14 +87,15 @@ __global__ void maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfl
 }
 
 // dx[n,h,w,c] = sum of dy over output cells whose argmax tap lands on (h,w)
+template <typename I>
 __global__ void maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const uint8_t* __restrict__ idx,
                                    __nv_bfloat16* __restrict__ dx, const PoolGeom g) {
   const int cvec = g.C / 8;
-  const long long total = static_cast<long long>(g.N) * g.H * g.W * cvec;
-  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+  const I total = static_cast<I>(g.N) * g.H * g.W * cvec;
+  const I stride = static_cast<I>(gridDim.x) * blockDim.x;
+  for (I i = static_cast<I>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
     const int cv = static_cast<int>(i % cvec);
-    long long t = i / cvec;
+    I t = i / cvec;
     const int w = static_cast<int>(t % g.W);
     t /= g.W;
     const int h = static_cast<int>(t % g.H);
@@ -139,14 +141,15 @@ __device__ __forceinline__ float avg_divisor(const PoolGeom& g, int ho, int wo) 
   return static_cast<float>(max((he - hs) * (we - ws), 1));
 }
 
+template <typename I>
 __global__ void avgpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
                                    const PoolGeom g) {
   const int cvec = g.C / 8;
-  const long long total = static_cast<long long>(g.N) * g.Ho * g.Wo * cvec;
-  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+  const I total = static_cast<I>(g.N) * g.Ho * g.Wo * cvec;
+  const I stride = static_cast<I>(gridDim.x) * blockDim.x;
+  for (I i = static_cast<I>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
     const int cv = static_cast<int>(i % cvec);
-    long long t = i / cvec;
+    I t = i / cvec;
     const int wo = static_cast<int>(t % g.Wo);
     t /= g.Wo;
     const int ho = static_cast<int>(t % g.Ho);
@@ -171,14 +174,15 @@ __global__ void avgpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfl
   }
 }
 
+template <typename I>
 __global__ void avgpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx,
                                    const PoolGeom g) {
   const int cvec = g.C / 8;
-  const long long total = static_cast<long long>(g.N) * g.H * g.W * cvec;
-  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+  const I total = static_cast<I>(g.N) * g.H * g.W * cvec;
+  const I stride = static_cast<I>(gridDim.x) * blockDim.x;
+  for (I i = static_cast<I>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
     const int cv = static_cast<int>(i % cvec);
-    long long t = i / cvec;
+    I t = i / cvec;
     const int w = static_cast<int>(t % g.W);
     t /= g.W;
     const int h = static_cast<int>(t % g.H);
@@ -226,16 +230,17 @@ __device__ __forceinline__ void lrn_load24(const __nv_bfloat16* row, int c0, int
   }
 }
 
+template <typename I>
 __global__ void lrn_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long pixels,
                                int C, long long ldx, long long ldy, int size, float alpha, float beta, float k) {
   const int cvec = C / 8;
-  const long long total = pixels * cvec;
-  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const I total = static_cast<I>(pixels) * cvec;
+  const I stride = static_cast<I>(gridDim.x) * blockDim.x;
   const int pre = (size - 1) / 2, post = size - 1 - pre;
   const float as = alpha / size;
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+  for (I i = static_cast<I>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
     const int cv = static_cast<int>(i % cvec);
-    const long long pix = i / cvec;
+    const I pix = i / cvec;
     const int c0 = cv * 8;
     float v[24];
     lrn_load24(x + pix * ldx, c0, C, v);
@@ -258,17 +263,18 @@ __global__ void lrn_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat1
 // dx_c = dy_c * s_c^-beta - 2*alpha*beta/size * x_c * sum_{c' : c in window(c')} dy_c' * x_c' * s_c'^(-beta-1)
 // c is inside window(c') iff c - post <= c' <= c + pre; s_c' needs x over [c'-pre, c'+post], so the 24-wide
 // neighbourhood covers everything for windows up to 9 (pre, post <= 4).
+template <typename I>
 __global__ void lrn_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                                __nv_bfloat16* __restrict__ dx, long long pixels, int C, long long ldx, long long ldy,
                                long long lddx, int size, float alpha, float beta, float k) {
   const int cvec = C / 8;
-  const long long total = pixels * cvec;
-  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const I total = static_cast<I>(pixels) * cvec;
+  const I stride = static_cast<I>(gridDim.x) * blockDim.x;
   const int pre = (size - 1) / 2, post = size - 1 - pre;
   const float as = alpha / size;
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+  for (I i = static_cast<I>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
     const int cv = static_cast<int>(i % cvec);
-    const long long pix = i / cvec;
+    const I pix = i / cvec;
     const int c0 = cv * 8;
     float v[24], g[24];
     lrn_load24(x + pix * ldx, c0, C, v);
@@ -358,6 +364,14 @@ __global__ void lrn_bwd_wide_kernel(const __nv_bfloat16* __restrict__ x, const _
   }
 }
 
+#define BDL_IDX_DISPATCH(KERNEL, TOTAL, ...)                                      \
+  do {                                                                           \
+    if ((TOTAL) < (1ll << 31) - (1ll << 24))                                     \
+      KERNEL<unsigned int><<<grid_for(TOTAL), 256, 0, st_>>>(__VA_ARGS__);       \
+    else                                                                         \
+      KERNEL<long long><<<grid_for(TOTAL), 256, 0, st_>>>(__VA_ARGS__);          \
+  } while (0)
+
 static int grid_for(long long total) {
   const long long cap = static_cast<long long>(bdl_num_sms()) * 16;
   long long b = (total + 255) / 256;
@@ -394,8 +408,11 @@ extern "C" int bdl_maxpool_fwd_nhwc_bf16(const void* x, void* y, void* idx, int 
   if (kh * kw > 255) return bdl_fail("bdl_maxpool_fwd_nhwc_bf16: window larger than 255 taps");
   const PoolGeom g = make_pool(N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph, pw, ldx, ldy, 0, 0);
   const long long total = static_cast<long long>(N) * Ho * Wo * (C / 8);
-  maxpool_fwd_kernel<<<grid_for(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  {
+    cudaStream_t st_ = static_cast<cudaStream_t>(stream);
+    BDL_IDX_DISPATCH(maxpool_fwd_kernel, static_cast<long long>(total), 
       static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), static_cast<uint8_t*>(idx), g);
+  }
   return bdl_check_launch("maxpool_fwd_kernel");
 }
 
@@ -407,8 +424,11 @@ extern "C" int bdl_maxpool_bwd_nhwc_bf16(const void* dy, const void* idx, void* 
     return BDL_ERR_INVALID;
   const PoolGeom g = make_pool(N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph, pw, ldx, ldy, 0, 0);
   const long long total = static_cast<long long>(N) * H * W * (C / 8);
-  maxpool_bwd_kernel<<<grid_for(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  {
+    cudaStream_t st_ = static_cast<cudaStream_t>(stream);
+    BDL_IDX_DISPATCH(maxpool_bwd_kernel, static_cast<long long>(total), 
       static_cast<const __nv_bfloat16*>(dy), static_cast<const uint8_t*>(idx), static_cast<__nv_bfloat16*>(dx), g);
+  }
   return bdl_check_launch("maxpool_bwd_kernel");
 }
 
@@ -420,8 +440,11 @@ extern "C" int bdl_avgpool_fwd_nhwc_bf16(const void* x, void* y, int N, int H, i
     return BDL_ERR_INVALID;
   const PoolGeom g = make_pool(N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph, pw, ldx, ldy, count_include_pad, divide);
   const long long total = static_cast<long long>(N) * Ho * Wo * (C / 8);
-  avgpool_fwd_kernel<<<grid_for(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  {
+    cudaStream_t st_ = static_cast<cudaStream_t>(stream);
+    BDL_IDX_DISPATCH(avgpool_fwd_kernel, static_cast<long long>(total), 
       static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), g);
+  }
   return bdl_check_launch("avgpool_fwd_kernel");
 }
 
@@ -433,8 +456,11 @@ extern "C" int bdl_avgpool_bwd_nhwc_bf16(const void* dy, void* dx, int N, int H,
     return BDL_ERR_INVALID;
   const PoolGeom g = make_pool(N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph, pw, ldx, ldy, count_include_pad, divide);
   const long long total = static_cast<long long>(N) * H * W * (C / 8);
-  avgpool_bwd_kernel<<<grid_for(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  {
+    cudaStream_t st_ = static_cast<cudaStream_t>(stream);
+    BDL_IDX_DISPATCH(avgpool_bwd_kernel, static_cast<long long>(total), 
       static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), g);
+  }
   return bdl_check_launch("avgpool_bwd_kernel");
 }
 
@@ -444,9 +470,12 @@ extern "C" int bdl_lrn_fwd_nhwc_bf16(const void* x, void* y, long long pixels, i
                  y))
     return BDL_ERR_INVALID;
   if (size <= 9)
-    lrn_fwd_kernel<<<grid_for(pixels * (C / 8)), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+    {
+    cudaStream_t st_ = static_cast<cudaStream_t>(stream);
+    BDL_IDX_DISPATCH(lrn_fwd_kernel, static_cast<long long>(pixels * (C / 8)), 
         static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), pixels, C, ldx, ldy, size, alpha, beta,
         k);
+  }
   else
     lrn_fwd_wide_kernel<<<grid_for(pixels * C), 256, 0, static_cast<cudaStream_t>(stream)>>>(
         static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), pixels, C, ldx, ldy, size, alpha, beta,
@@ -461,9 +490,12 @@ extern "C" int bdl_lrn_bwd_nhwc_bf16(const void* x, const void* dy, void* dx, lo
                  dy))
     return BDL_ERR_INVALID;
   if (size <= 9)
-    lrn_bwd_kernel<<<grid_for(pixels * (C / 8)), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+    {
+    cudaStream_t st_ = static_cast<cudaStream_t>(stream);
+    BDL_IDX_DISPATCH(lrn_bwd_kernel, static_cast<long long>(pixels * (C / 8)), 
         static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx),
         pixels, C, ldx, ldy, lddx, size, alpha, beta, k);
+  }
   else
     lrn_bwd_wide_kernel<<<grid_for(pixels * C), 256, 0, static_cast<cudaStream_t>(stream)>>>(
         static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx),

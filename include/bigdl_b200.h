@@ -20,6 +20,8 @@ extern "C" {
 const char* bdl_last_error(void);
 int bdl_version(void);
 int bdl_sm_count(void);
+/* 0 none, 1 capturing, 2 invalidated; diagnostic for CUDA-graph capture of training steps. */
+int bdl_stream_capture_status(void* stream);
 
 /* ---- tcgen05 GEMM (csrc/gemm_tcgen05.cu). Reference: MKL sgemm JNI, core/mkl2017-xeon-blas/src/main/c/mkl.c;
  *      S/nn/Linear.scala:78-167. D[M,N] = opA(A) * opB(B)^T.
@@ -56,6 +58,10 @@ int bdl_colsum_bf16(const void* x, const void* y, void* dz, float* out, long lon
                     long long ldy, long long ldz, void* stream);
 int bdl_dropout_fwd_bf16(const void* x, void* y, void* mask, size_t n, float p, unsigned long long seed,
                          unsigned long long offset, void* stream);
+/* Graph-replay friendly variant: Philox position read from *counter_dev (u64) and advanced by the call. */
+int bdl_dropout_fwd_bf16_ctr(const void* x, void* y, void* mask, size_t n, float p, unsigned long long seed,
+                             void* counter_dev, void* stream);
+int bdl_counter_add(void* counter_dev, unsigned long long v, void* stream);
 int bdl_dropout_bwd_bf16(const void* dy, const void* mask, void* dx, size_t n, float p, void* stream);
 int bdl_copy2d_bf16(const void* src, void* dst, long long rows, int C, long long lds, long long ldd, int accumulate,
                     void* stream);
@@ -120,12 +126,14 @@ int bdl_scale_f32(float* x, size_t n, float alpha, const float* norm_sq, float m
  *      S/optim/DistriOptimizer.scala:358-396.
  *      mode bits: 1 reduce, 2 write fp32 grad slice, 4 update, 8 publish bf16 weights to all peers,
  *                 16 begin barrier, 32 end barrier, 64 reference-exact (truncating) arithmetic, 128 sum of squares,
- *                 256 divide by hp.gscale instead of multiplying. */
+ *                 256 divide by hp.gscale instead of multiplying.
+ *      epoch_dev (optional, u64 in device memory) is added to `epoch` so a captured graph can advance the barrier
+ *      generation between replays with bdl_counter_add. */
 int bdl_compress_grads(float* g, void* out16, size_t n, int truncate, int zero_src, void* stream);
 int bdl_fused_rs_update(const void* const* grad16_ptrs, void* const* w16_ptrs, void* const* flag_ptrs, int nranks,
                         int rank, long long start, long long length, float* master, float* grad_part, float* s0,
                         float* s1, int kind, const void* hp_host, const void* hp_dev, int mode, unsigned int epoch,
-                        void* local_sync, float* sumsq, int max_blocks, void* stream);
+                        void* local_sync, float* sumsq, int max_blocks, const void* epoch_dev, void* stream);
 /* cudaMalloc + cudaIpc handle exchange for the symmetric buffers (one process per GPU). handle64: 64 bytes. */
 int bdl_ipc_alloc(size_t bytes, void** ptr, void* handle64);
 int bdl_ipc_open(const void* handle64, void** ptr);

@@ -46,7 +46,7 @@ def _run(world, P, parity, kind_hp):
         mode = CM_REDUCE | CM_WRITE_GRAD | CM_UPDATE | CM_PUBLISH | (CM_PARITY | CM_DIVIDE if parity else 0)
         _lib.check(lib.bdl_fused_rs_update(g16, w16, None, world, r, s, l, m.data_ptr(), gp.data_ptr(), mom.data_ptr(),
                                            None, kind, ctypes.cast(buf, ctypes.c_void_p), None, mode, 1, None, None, 0,
-                                           st), "bdl_fused_rs_update")
+                                           None, st), "bdl_fused_rs_update")
         masters.append((s, l, m))
         gparts.append(gp)
     torch.cuda.synchronize()

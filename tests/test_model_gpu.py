@@ -90,3 +90,44 @@ def test_training_step_reduces_loss_on_gpu():
     opt.optimize()
     last = crit.forward(m.forward(x.cuda()), y.cuda())
     assert last < 0.3 * first, (first, last)
+
+
+def test_graphed_step_matches_eager():
+    """A CUDA-graph replayed training step must follow the same trajectory as eager execution (same seeds)."""
+    from bigdl_b200.dataset.base import FixedMiniBatchDataSet, MiniBatch
+    from bigdl_b200.nn.criterion import ClassNLLCriterion
+    from bigdl_b200.nn.layer import (Linear, LogSoftMax, ReLU, Sequential, SpatialBatchNormalization,
+                                     SpatialConvolution, SpatialMaxPooling, View)
+    from bigdl_b200.optim.optim_method import SGD, Poly
+    from bigdl_b200.optim.optimizer import Optimizer
+    from bigdl_b200.optim.trigger import MaxIteration
+    from bigdl_b200.utils import config
+    from bigdl_b200.utils.random_generator import RNG
+
+    def run(use_graph):
+        config.set("bigdl.cudaGraph", use_graph)
+        RNG.setSeed(21)
+        m = Sequential()
+        m.add(SpatialConvolution(8, 32, 3, 3, 1, 1, 1, 1)).add(SpatialBatchNormalization(32)).add(ReLU())
+        m.add(SpatialMaxPooling(2, 2, 2, 2)).add(SpatialConvolution(32, 64, 3, 3, 1, 1, 1, 1)).add(ReLU())
+        m.add(View(64 * 8 * 8).setNumInputDims(3)).add(Linear(64 * 8 * 8, 16)).add(LogSoftMax())
+        m.cuda()
+        g = torch.Generator().manual_seed(3)
+        x = torch.randn(32, 8, 16, 16, generator=g)
+        y = torch.randint(1, 17, (32,), generator=g).float()
+        opt = Optimizer(m, FixedMiniBatchDataSet(MiniBatch(x, y), 32, distributed=False), ClassNLLCriterion(),
+                        MaxIteration(12), 32, SGD(0.05, momentum=0.9, weightdecay=1e-4,
+                                                  learningrate_schedule=Poly(0.5, 100)))
+        opt.optimize()
+        torch.cuda.synchronize()
+        return m._flat.weights.clone(), float(opt.state["Loss"]), m.modules[1].runningMean.clone(), opt.state["neval"]
+
+    try:
+        w_e, l_e, rm_e, n_e = run(False)
+        w_g, l_g, rm_g, n_g = run(True)
+    finally:
+        config.unset("bigdl.cudaGraph")
+    assert n_e == n_g == 13
+    assert _rel(w_g, w_e) < 2e-3, _rel(w_g, w_e)
+    assert _rel(rm_g, rm_e) < 2e-3
+    assert abs(l_g - l_e) < 2e-2 * max(1.0, abs(l_e))

@@ -189,7 +189,7 @@ class ConvFn(Function):
         Kp = (K + 7) // 8 * 8
         lib = _lib.cuda_lib()
         b32 = bias.detach() if bias is not None else None
-        implicit = (not direct) and groups == 1 and C % 8 == 0 and C >= 32 and O % 8 == 0 and _IGEMM[0]
+        implicit = (not direct) and groups == 1 and C % 8 == 0 and C >= 16 and O % 8 == 0 and _IGEMM[0]
         if implicit:
             conv_igemm(0, xn, ldx, w2, y2, O, Ho, Wo, kh, kw, sh, sw, pt, pl, dh, dw, bias=b32, relu=relu)
         for g in range(groups if not implicit else 0):

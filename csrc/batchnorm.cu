@@ -82,6 +82,38 @@ __global__ void bn_reduce_kernel(const __nv_bfloat16* __restrict__ a, const __nv
           }
         }
       }
+      if (kMode == 1) {
+        // backward sums: two rows (six 16-byte loads) in flight per thread
+        for (; r + 1ll * rif < r1; r += 2ll * rif) {
+          uint4 va[2], vx[2], vy[2];
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            va[u] = *reinterpret_cast<const uint4*>(a + (r + u * rif) * lda + cv * 8);
+            vx[u] = *reinterpret_cast<const uint4*>(x + (r + u * rif) * ldx + cv * 8);
+            if (y) vy[u] = *reinterpret_cast<const uint4*>(y + (r + u * rif) * ldy + cv * 8);
+          }
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            const __nv_bfloat162* qa = reinterpret_cast<const __nv_bfloat162*>(&va[u]);
+            const __nv_bfloat162* qx = reinterpret_cast<const __nv_bfloat162*>(&vx[u]);
+            const __nv_bfloat162* qy = reinterpret_cast<const __nv_bfloat162*>(&vy[u]);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              float2 g2 = __bfloat1622float2(qa[j]);
+              const float2 x2 = __bfloat1622float2(qx[j]);
+              if (y) {
+                const float2 y2 = __bfloat1622float2(qy[j]);
+                g2.x = y2.x > 0.f ? g2.x : 0.f;
+                g2.y = y2.y > 0.f ? g2.y : 0.f;
+              }
+              s0[2 * j] += g2.x;
+              s0[2 * j + 1] += g2.y;
+              s1[2 * j] = fmaf(g2.x, (x2.x - mu[2 * j]) * is[2 * j], s1[2 * j]);
+              s1[2 * j + 1] = fmaf(g2.y, (x2.y - mu[2 * j + 1]) * is[2 * j + 1], s1[2 * j + 1]);
+            }
+          }
+        }
+      }
       for (; r < r1; r += rif) {
         float fa[8];
         bn_load8(a + r * lda + cv * 8, fa);
@@ -337,7 +369,10 @@ static void reduce_geometry(long long M, int C, int* grid, int* rpb, size_t* sme
   const int cvec = C / 8;
   const int vcols = cvec < 256 ? cvec : 256;
   const int rif = 256 / vcols;
-  long long r = (M + sms * 8 - 1) / (sms * 8);
+  // every block ends with 2*C atomics on the same addresses: keep the block count low for wide layers and let the
+  // unrolled loads (4 rows in flight per thread) provide the memory-level parallelism instead
+  long long blocks_target = static_cast<long long>(sms) * (C >= 1024 ? 1 : (C >= 256 ? 2 : 4));
+  long long r = (M + blocks_target - 1) / blocks_target;
   if (r < 4ll * rif) r = 4ll * rif;
   *rpb = static_cast<int>(r);
   *grid = static_cast<int>((M + r - 1) / r);

@@ -426,6 +426,7 @@ def _train_loop(opt: Optimizer, distributed: bool):
             if distributed else opt.checkpoint_path
     dataset.shuffle()
     data_iter = dataset.data(train=True)
+    prefetch = _Prefetcher(data_iter, device) if device.type == "cuda" else None
     wall_start = time.time()
     clip = opt.clipping
     pending_loss = None        # GPU: the loss is read back one iteration late so the host never stalls the stream
@@ -437,7 +438,7 @@ def _train_loop(opt: Optimizer, distributed: bool):
 
     while not opt.end_when(state):
         t0 = time.time()
-        batch = next(data_iter)
+        batch = next(prefetch) if prefetch is not None else next(data_iter)
         if not isinstance(batch, MiniBatch):
             raise TypeError("the training dataset must yield MiniBatch (use SampleToMiniBatch or pass batch_size)")
         n_local = batch.size()
@@ -502,6 +503,8 @@ def _train_loop(opt: Optimizer, distributed: bool):
             state["epoch"] = state["epoch"] + 1
             dataset.shuffle()
             data_iter = dataset.data(train=True)
+            if prefetch is not None:
+                prefetch.reset(data_iter)
             records_this_epoch = 0
             state["recordsProcessedThisEpoch"] = 0
         for om in opt.optim_methods.values():
@@ -527,6 +530,49 @@ def _train_loop(opt: Optimizer, distributed: bool):
         # keep the symmetric buffers alive while the model still points its compute weights at them
         model._param_sync_keepalive = sync
     return model
+
+
+class _Prefetcher:
+    """Pulls MiniBatches one step ahead and uploads them on a dedicated copy stream, so the host→device transfer of
+    batch k+1 overlaps the compute of batch k (the GPU analogue of the reference's multi-threaded batchers,
+    S/dataset/image/MTLabeledBGRImgToBatch.scala)."""
+
+    def __init__(self, it, device):
+        self.it, self.device = it, device
+        self.stream = torch.cuda.Stream(device)
+        self._next = None
+        self._preload()
+
+    def _preload(self):
+        try:
+            b = next(self.it)
+        except StopIteration:
+            self._next = None
+            return
+        if not isinstance(b, MiniBatch):
+            self._next = (b, None)
+            return
+        with torch.cuda.stream(self.stream):
+            dev = MiniBatch([t.to(self.device, non_blocking=True) for t in b.inputs],
+                            [t.to(self.device, non_blocking=True) for t in b.targets])
+            ev = torch.cuda.Event()
+            ev.record(self.stream)
+        self._next = (dev, ev)
+
+    def reset(self, it):
+        self.it = it
+        self._preload()
+
+    def __next__(self):
+        if self._next is None:
+            raise StopIteration
+        b, ev = self._next
+        if ev is not None:
+            torch.cuda.current_stream(self.device).wait_event(ev)
+            for t in b.inputs + b.targets:
+                t.record_stream(torch.cuda.current_stream(self.device))
+        self._preload()
+        return b
 
 
 def _graph_step(opt, graphs, model, criterion, sync, om, batch, device, world):

@@ -43,7 +43,7 @@ def fuse(model: Module) -> Module:
             continue
         if conv_relu and isinstance(a, (SpatialConvolution, Linear)) and not a._fuse_relu:
             a._fuse_relu, b._fused = True, True
-        elif bn_relu and isinstance(a, BatchNormalization) and not a._fuse_relu:
+        elif bn_relu and isinstance(a, BatchNormalization) and not a._fuse_relu and not getattr(a, "_folded", False):
             a._fuse_relu, b._fused = True, True
         elif conv_sum and isinstance(a, CAddTable) and not a._fuse_relu:
             a._fuse_relu, b._fused = True, True

@@ -576,7 +576,7 @@ class Module:
 
     def __deepcopy__(self, memo):
         cls = self.__class__
-        new = cls.__new__(cls)
+        new = object.__new__(cls)      # Input.__new__ returns a Node, so bypass class-level __new__
         memo[id(self)] = new
         for k, v in self.__dict__.items():
             if k in ("_flat", "_compute"):

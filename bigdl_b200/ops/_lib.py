@@ -55,7 +55,11 @@ _P, _I, _L, _F, _Z, _U64 = (ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ct
 _SIGNATURES = {
     "bdl_gemm_bf16": [_P, _P, _P, _P, _I, _I, _I, _L, _L, _L, _I, _I, _I, _I, _I, _P],
     "bdl_conv_igemm_bf16": [_I, _P, _I, _I, _I, _I, _L, _P, _L, _P, _L, _P] + [_I] * 14 + [_P],
-    "bdl_gemm_fp8": [_P, _P, _P, _P, _P, _P, _I, _I, _I, _L, _L, _L, _I, _I, _P],
+    "bdl_gemm_fp8": [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _L, _L, _L, _I, _I, _P],
+    "bdl_row_absmax": [_P, _P, _L, _L, _L, _I, _P],
+    "bdl_quantize_e4m3": [_P, _P, _P, _I, _L, _L, _L, _L, _I, _P],
+    "bdl_fp8_colscale": [_P, _P, _P, _I, _P],
+    "bdl_quantize_int8_rows": [_P, _P, _P, _L, _L, _P],
     "bdl_cast_f32_to_bf16": [_P, _P, _Z, _I, _P],
     "bdl_cast_bf16_to_f32": [_P, _P, _Z, _P],
     "bdl_bf16_trunc_add": [_P, _P, _P, _Z, _P],

@@ -1,0 +1,5 @@
+"""fp8 quantised inference (reference: S/nn/quantized/*, core/bigquant, S/nn/MklInt8Convertible.scala)."""
+from .layers import Linear, QuantizedModule, SpatialConvolution, SpatialDilatedConvolution
+from .quantizer import Quantizer
+
+__all__ = ["Linear", "QuantizedModule", "SpatialConvolution", "SpatialDilatedConvolution", "Quantizer"]

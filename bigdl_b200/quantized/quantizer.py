@@ -1,0 +1,162 @@
+"""Model quantiser (S/nn/quantized/Quantizer.scala:27-140, Quantizable.scala): walks containers, graphs and recurrent
+cells and swaps Linear / SpatialConvolution / SpatialDilatedConvolution for their fp8 versions. ``calibrate`` is the
+B200 form of ``MklInt8Convertible.calcScales`` (S/nn/MklInt8Convertible.scala:53-98): it runs sample batches, records the
+abs-max of every quantised layer's input, freezes those as static scales and links producer→consumer pairs so the
+producer's GEMM epilogue writes e4m3 for the consumer directly."""
+from __future__ import annotations
+
+import torch
+
+from ..nn import layers_core as LC
+from ..nn.module import Container, Graph, Module, Sequential
+from . import layers as QL
+
+
+class Quantizer:
+    _registry: dict[type, type] = {}
+
+    @classmethod
+    def register(cls, float_cls, quant_cls):
+        if float_cls in cls._registry:
+            raise ValueError(f"Module: {float_cls.__name__} has been registered.")
+        cls._registry[float_cls] = quant_cls
+
+    @classmethod
+    def quantize(cls, model: Module, fold_bn: bool = True) -> Module:
+        """Returns a quantised deep copy in evaluate mode (AbstractModule.quantize clones first, S/nn/abstractnn/
+        AbstractModule.scala:920-928)."""
+        from ..nn.fusion import fold_bn as do_fold, fuse
+
+        from ..nn.flat import unflatten_parameters
+
+        m = model.cloneModule().evaluate()
+        dev = m.device()
+        unflatten_parameters(m)
+        if fold_bn:
+            do_fold(m)
+        fuse(m)
+        _fuse_through_identities(m)
+        out = cls._convert(m)
+        out.evaluate()
+        if dev.type == "cuda" and out.torch_parameters():
+            out.getParameters()
+        return out
+
+    @classmethod
+    def _convert(cls, m: Module) -> Module:
+        q = cls._registry.get(type(m))
+        if q is not None:
+            return q.from_float(m)
+        if isinstance(m, Graph):
+            for n in m.exec_order:
+                new = cls._convert(n.element)
+                if new is not n.element:
+                    n.element = new
+            m._build()
+            return m
+        if isinstance(m, Container):
+            m.modules = [cls._convert(c) for c in m.modules]
+            if hasattr(m, "_after_children_replaced"):
+                m._after_children_replaced()
+            return m
+        cell = m.__dict__.get("cell")
+        if isinstance(cell, Module):           # Recurrent-style wrappers own a single cell (CellQuantizer)
+            m.cell = cls._convert(cell)
+        return m
+
+    # ---------------------------------------------------------------- calibration
+    @staticmethod
+    def quantized_layers(model: Module) -> list[QL.QuantizedModule]:
+        return [m for m in model.all_modules() if isinstance(m, QL.QuantizedModule)]
+
+    @classmethod
+    def calibrate(cls, model: Module, batches, chain: bool = True) -> Module:
+        """Run ``batches`` (iterable of inputs) through the quantised model recording input abs-max per layer, then
+        switch every layer to static scales and link requantising epilogues."""
+        qs = cls.quantized_layers(model)
+        for q in qs:
+            q._buffers["input_absmax"].zero_()
+            q.calibrating, q._emit_q = True, None
+        for b in batches:
+            model.forward(b)
+        for q in qs:
+            q.calibrating, q.static_scale, q._colscale = False, True, None
+            q.__dict__.pop("_in_qscale", None)
+        if chain:
+            cls.link_chains(model)
+        return model
+
+    @staticmethod
+    def link_chains(model: Module) -> int:
+        """producer._emit_q = consumer wherever the producer's only user is a statically-scaled quantised layer whose
+        input channel count needs no padding (so the e4m3 tensor can be consumed in place). Returns the link count."""
+        n = 0
+        for a, b in _effective_pairs(model):
+            if isinstance(a, QL.QuantizedModule) and isinstance(b, QL.QuantizedModule) and b.static_scale:
+                if isinstance(b, QL.SpatialConvolution):
+                    ok = isinstance(a, QL.SpatialConvolution) and a.n_output_plane == b.n_input_plane and \
+                        b.n_input_plane % 16 == 0 and b.n_group == 1 and b.data_format == a.data_format
+                else:
+                    ok = isinstance(a, QL.Linear) and a.output_size == b.input_size and b.input_size % 16 == 0
+                if ok:
+                    a._emit_q = b
+                    n += 1
+        # branches of a ConcatTable read the same tensor: give their first quantised layers ONE scale buffer so the
+        # second branch reuses the first one's quantised copy (layers.py caches it on the tensor)
+        from ..nn.layers_table import ConcatTable
+
+        for ct in model.all_modules():
+            if not isinstance(ct, ConcatTable):
+                continue
+            firsts = []
+            for br in ct.modules:
+                f = br
+                while isinstance(f, Sequential):
+                    mods = [c for c in f.modules if not _is_identity(c)]
+                    f = mods[0] if mods else None
+                if isinstance(f, QL.SpatialConvolution) and f.static_scale:
+                    firsts.append(f)
+            if len(firsts) >= 2:
+                shared = torch.stack([f._buffers["input_absmax"] for f in firsts]).amax(dim=0)
+                for f in firsts:
+                    f._buffers["input_absmax"] = shared
+                    f._colscale = None
+                    f.__dict__.pop("_in_qscale", None)
+        return n
+
+
+def _is_identity(m: Module) -> bool:
+    return (type(m) is LC.ReLU and getattr(m, "_fused", False)) or \
+        (isinstance(m, LC.BatchNormalization) and getattr(m, "_folded", False)) or type(m).__name__ == "Identity"
+
+
+def _effective_pairs(model: Module):
+    """(producer, consumer) pairs with single-use edges, looking through modules that became identities."""
+    for m in model.all_modules():
+        if isinstance(m, Sequential):
+            mods = [c for c in m.modules if not _is_identity(c)]
+            for a, b in zip(mods, mods[1:]):
+                yield a, b
+        elif isinstance(m, Graph):
+            for n in m.exec_order:
+                if _is_identity(n.element) or n in m.output_nodes or len(n.next) != 1:
+                    continue
+                nxt = n.next[0]
+                while _is_identity(nxt.element) and len(nxt.next) == 1 and len(nxt.prev) == 1 and \
+                        nxt not in m.output_nodes:
+                    nxt = nxt.next[0]
+                if len(nxt.prev) == 1 and not _is_identity(nxt.element):
+                    yield n.element, nxt.element
+
+
+def _fuse_through_identities(model: Module):
+    """After conv+BN folding the BN is an identity, so a ReLU behind it can still go into the conv epilogue."""
+    for a, b in _effective_pairs(model):
+        if type(b) is LC.ReLU and not getattr(b, "_fused", False) and \
+                isinstance(a, (LC.SpatialConvolution, LC.Linear)) and not a._fuse_relu:
+            a._fuse_relu, b._fused = True, True
+
+
+Quantizer.register(LC.Linear, QL.Linear)
+Quantizer.register(LC.SpatialConvolution, QL.SpatialConvolution)
+Quantizer.register(LC.SpatialDilatedConvolution, QL.SpatialDilatedConvolution)

@@ -14,6 +14,8 @@
 // MN-major means the non-contraction index is contiguous ([K, rows] row-major). wgrad needs MN-major for both
 // operands, dgrad needs an MN-major B; the tensor core consumes both directly (idesc a_major/b_major bits), so no
 // transposes are ever materialised.
+#include <cuda_fp8.h>
+
 #include "bigdl_b200.h"
 #include "host_common.h"
 #include "ptx.cuh"
@@ -22,6 +24,8 @@ namespace bdl {
 
 constexpr int BM = 128;
 constexpr int BK = 64;  // 64 bf16 = 128 bytes = one swizzle row
+// dynamic shared memory available to the operand ring: 227 KB minus alignment slack, barriers and the epilogue columns
+constexpr size_t kSmemBudget = 227 * 1024 - 1024 - 512 - 4096;
 constexpr int kMaxStages = 8;
 constexpr int kGemmThreads = 192;
 constexpr int kTmemCols = 512;
@@ -58,6 +62,8 @@ struct GemmParams {
   int flags;
   void* D;
   const float* bias;
+  const float* col_scale;    // fp8 only: per-output-column dequantisation scale
+  const float* out_qscale;   // fp8 only, out_fp32 == 2: device scalar 448 / absmax of the next layer's input
   // implicit-GEMM convolution (kConv != 0): the A (fprop/dgrad) or B (wgrad) operand is gathered from an NHWC
   // activation tensor by TMA im2col loads instead of being read from a materialised column matrix.
   int cv_Ho, cv_Wo;          // output spatial size of the traversal
@@ -74,7 +80,101 @@ struct GemmParams {
 };
 
 // kConv: 0 plain GEMM; 1 A operand via im2col TMA (conv fprop, and dgrad when kBMN); 2 B operand via im2col TMA (wgrad)
-template <bool kAMN, bool kBMN, int kConv>
+// One 16-column chunk of one accumulator row: dequantise / bias / ReLU, then store as fp32 (plain or red.add), bf16 or
+// requantised e4m3. ``sb``/``ss`` point at this chunk's bias / scale columns in shared memory (16-byte aligned).
+template <bool kFp8>
+__device__ __forceinline__ void epilogue_store16(const GemmParams& p, const uint32_t* r, int row, int n0,
+                                                 const float* sb, const float* ss, bool has_bias, bool use_scale,
+                                                 bool atomic) {
+  if (n0 >= p.N) return;
+  float v[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
+  const bool full = (n0 + 16 <= p.N);
+  if (kFp8 && use_scale) {
+#pragma unroll
+    for (int j = 0; j < 16; j += 4) {
+      const float4 s4 = *reinterpret_cast<const float4*>(ss + j);
+      v[j] *= s4.x; v[j + 1] *= s4.y; v[j + 2] *= s4.z; v[j + 3] *= s4.w;
+    }
+  }
+  if (has_bias) {
+#pragma unroll
+    for (int j = 0; j < 16; j += 4) {
+      const float4 b4 = *reinterpret_cast<const float4*>(sb + j);
+      v[j] += b4.x; v[j + 1] += b4.y; v[j + 2] += b4.z; v[j + 3] += b4.w;
+    }
+  }
+  if (p.flags & BDL_GEMM_RELU) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
+  }
+  if (kFp8 && p.out_fp32 == 2) {
+    // requantise for the next fp8 layer: q = sat_e4m3(v * out_qscale), 16 bytes per lane-row
+    const float qs = __ldg(p.out_qscale);
+    uint8_t* dst = reinterpret_cast<uint8_t*>(p.D) + static_cast<long long>(row) * p.ldd + n0;
+    uint32_t w[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const uint32_t lo = __nv_cvt_float2_to_fp8x2(make_float2(v[4 * j] * qs, v[4 * j + 1] * qs), __NV_SATFINITE,
+                                                   __NV_E4M3);
+      const uint32_t hi = __nv_cvt_float2_to_fp8x2(make_float2(v[4 * j + 2] * qs, v[4 * j + 3] * qs), __NV_SATFINITE,
+                                                   __NV_E4M3);
+      w[j] = lo | (hi << 16);
+    }
+    if (full && ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0)) {
+      *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
+    } else {
+      for (int j = 0; j < 16; ++j)
+        if (n0 + j < p.N) dst[j] = static_cast<uint8_t>((w[j >> 2] >> ((j & 3) * 8)) & 0xffu);
+    }
+  } else if (p.out_fp32) {
+    float* dst = reinterpret_cast<float*>(p.D) + static_cast<long long>(row) * p.ldd + n0;
+    const bool al = full && ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0);
+    if (atomic) {
+      if (al) {
+#pragma unroll
+        for (int j = 0; j < 16; j += 4)
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + j), "f"(v[j]), "f"(v[j + 1]),
+                       "f"(v[j + 2]), "f"(v[j + 3])
+                       : "memory");
+      } else {
+        for (int j = 0; j < 16; ++j)
+          if (n0 + j < p.N) atomicAdd(dst + j, v[j]);
+      }
+    } else if (al) {
+#pragma unroll
+      for (int j = 0; j < 16; j += 4)
+        *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+    } else {
+      for (int j = 0; j < 16; ++j)
+        if (n0 + j < p.N) dst[j] = v[j];
+    }
+  } else {
+    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.D) + static_cast<long long>(row) * p.ldd + n0;
+    const bool al = full && ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0);
+    if (al) {
+      uint4 q0, q1;
+      q0.x = pack_bf16x2(v[0], v[1]);
+      q0.y = pack_bf16x2(v[2], v[3]);
+      q0.z = pack_bf16x2(v[4], v[5]);
+      q0.w = pack_bf16x2(v[6], v[7]);
+      q1.x = pack_bf16x2(v[8], v[9]);
+      q1.y = pack_bf16x2(v[10], v[11]);
+      q1.z = pack_bf16x2(v[12], v[13]);
+      q1.w = pack_bf16x2(v[14], v[15]);
+      *reinterpret_cast<uint4*>(dst) = q0;
+      *reinterpret_cast<uint4*>(dst + 8) = q1;
+    } else {
+      for (int j = 0; j < 16; ++j)
+        if (n0 + j < p.N) dst[j] = __float2bfloat16_rn(v[j]);
+    }
+  }
+}
+
+// kFp8: operands are e4m3 bytes (128 per swizzle row, UMMA K = 32) multiplied with kind::f8f6f4; the epilogue applies a
+//       per-output-column fp32 scale (activation scale x per-channel weight scale) before bias/ReLU. K-major only.
+template <bool kAMN, bool kBMN, int kConv, bool kFp8 = false>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                          const GemmParams p) {
@@ -84,6 +184,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   __shared__ __align__(8) uint64_t tfull_bar[2];
   __shared__ __align__(8) uint64_t tempty_bar[2];
   __shared__ uint32_t tmem_base_slot;
+  __shared__ __align__(16) float epi_cols[2][2][256];   // [accumulator stage][bias | scale][column of the tile]
 
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = threadIdx.x & 31u;
@@ -111,7 +212,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
 
-  const int num_kb = kConv ? p.cv_num_kb : (p.K + BK - 1) / BK;
+  constexpr int KE = kFp8 ? 128 : 64;   // elements per 128-byte k block
+  const int num_kb = kConv ? p.cv_num_kb : (p.K + KE - 1) / KE;
   const int tiles_mn = p.tiles_m * p.tiles_n;
   const int total_work = tiles_mn * p.splits;
 
@@ -164,10 +266,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           const uint32_t sa = tiles + stage * stage_bytes;
           const uint32_t sb = sa + a_bytes;
           mbar_expect_tx(fb, stage_bytes);
-          const int k0 = kb * BK;
+          const int k0 = kb * KE;
           if (kConv == 1) {
             // k block = (filter tap, 64-channel block); A tile = 128 consecutive output pixels of that tap
-            tma_load_im2col_4d(sa, &tmA, fb, cv_cb * 64, cv_w, cv_h, cv_img, static_cast<uint16_t>(cv_s * p.cv_dw),
+            tma_load_im2col_4d(sa, &tmA, fb, cv_cb * KE, cv_w, cv_h, cv_img, static_cast<uint16_t>(cv_s * p.cv_dw),
                                static_cast<uint16_t>(cv_r * p.cv_dh));
             const int tap = cv_r * p.cv_kw + cv_s;
             if (kBMN) {
@@ -176,7 +278,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
               for (int j = 0; j < p.b_rows / 64; ++j)
                 tma_load_2d(sb + j * 8192u, &tmB, fb, btap * p.N + n0 + 64 * j, cv_cb * 64);
             } else {
-              tma_load_2d(sb, &tmB, fb, tap * p.cv_C + cv_cb * 64, n0);
+              tma_load_2d(sb, &tmB, fb, tap * p.cv_C + cv_cb * KE, n0);
             }
             if (++cv_cb == p.cv_cblocks) {   // advance (tap, channel block) without dividing
               cv_cb = 0;
@@ -228,7 +330,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     // ------------------------------------------------------------ MMA issuer
     if (lane == 0) {
       // instruction descriptor: c=f32 [4,6), a=bf16 [7,10), b=bf16 [10,13), a_major 15, b_major 16, N>>3 [17,23), M>>4 [24,29)
-      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(kAMN) << 15) |
+      // fp8: a/b format 0 = E4M3; bf16: format 1
+      const uint32_t idesc = (1u << 4) | (kFp8 ? 0u : ((1u << 7) | (1u << 10))) | (static_cast<uint32_t>(kAMN) << 15) |
                              (static_cast<uint32_t>(kBMN) << 16) | (static_cast<uint32_t>(p.block_n >> 3) << 17) |
                              (static_cast<uint32_t>(BM >> 4) << 24);
       int stage = 0;
@@ -252,7 +355,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                                         : make_smem_desc_sw128(sa + k * 32u, 16u, 1024u);
             const uint64_t bdesc = kBMN ? make_smem_desc_sw128(sb + k * 2048u, 8192u, 1024u)
                                         : make_smem_desc_sw128(sb + k * 32u, 16u, 1024u);
-            umma_f16(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            if (kFp8)
+              umma_f8(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            else
+              umma_f16(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           }
           umma_commit(smem_u32(&empty_bar[stage]));
           if (++stage == p.num_stages) {
@@ -269,10 +375,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   } else {
     // ------------------------------------------------------------ epilogue (warps 2..5)
     const uint32_t quad = warp & 3u;  // TMEM lane quadrant this warp may read
+    const uint32_t et = threadIdx.x - 64u;   // 0..127 within the epilogue warps
     uint32_t acc = 0, acc_phase = 0;
     const bool has_bias = (p.flags & BDL_GEMM_BIAS) != 0;
-    const bool relu = (p.flags & BDL_GEMM_RELU) != 0;
     const bool atomic = (p.flags & BDL_GEMM_ATOMIC_ADD) != 0;
+    const bool use_scale = kFp8 && p.col_scale != nullptr;
     for (int work = blockIdx.x; work < total_work; work += gridDim.x) {
       const int split = work / tiles_mn;
       const int rem = work - split * tiles_mn;
@@ -280,71 +387,33 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       const int n_blk = rem - m_blk * p.tiles_n;
       const int row = m_blk * BM + static_cast<int>(quad * 32u + lane);
       const int nbase = n_blk * p.block_n;
+      // Stage this tile's bias / dequantisation columns in shared memory while the MMAs are still running: reading
+      // them with __ldg inside the column loop put a long-scoreboard stall on every 16-column chunk.
+      float* sb = &epi_cols[acc][0][0];
+      float* ss = &epi_cols[acc][1][0];
+      const bool tile_bias = has_bias && (!atomic || split == 0);
+      if (has_bias || use_scale) {
+        for (int c = static_cast<int>(et); c < p.block_n; c += 128) {
+          const int n = nbase + c;
+          sb[c] = (tile_bias && n < p.N) ? __ldg(p.bias + n) : 0.f;
+          if (kFp8) ss[c] = (use_scale && n < p.N) ? __ldg(p.col_scale + n) : 1.f;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+      }
       mbar_wait(smem_u32(&tfull_bar[acc]), acc_phase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((quad * 32u) << 16) + acc * kAccStride;
       const bool row_ok = row < p.M;
-      for (int c = 0; c < p.block_n; c += 16) {
-        uint32_t r[16];
-        tmem_ld_16(t_row + static_cast<uint32_t>(c), r);
+      for (int c = 0; c < p.block_n; c += 32) {
+        uint32_t r0[16], r1[16];
+        const bool two = c + 16 < p.block_n;
+        tmem_ld_16(t_row + static_cast<uint32_t>(c), r0);
+        if (two) tmem_ld_16(t_row + static_cast<uint32_t>(c + 16), r1);
         tmem_ld_wait();
-        const int n0 = nbase + c;
-        if (!row_ok || n0 >= p.N) continue;
-        float v[16];
-#pragma unroll
-        for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
-        const bool full = (n0 + 16 <= p.N);
-        if (has_bias && (!atomic || split == 0)) {
-#pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (full || n0 + j < p.N) v[j] += __ldg(p.bias + n0 + j);
-        }
-        if (relu) {
-#pragma unroll
-          for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
-        }
-        if (p.out_fp32) {
-          float* dst = reinterpret_cast<float*>(p.D) + static_cast<long long>(row) * p.ldd + n0;
-          const bool al = full && ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0);
-          if (atomic) {
-            if (al) {
-#pragma unroll
-              for (int j = 0; j < 16; j += 4)
-                asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + j), "f"(v[j]), "f"(v[j + 1]),
-                             "f"(v[j + 2]), "f"(v[j + 3])
-                             : "memory");
-            } else {
-              for (int j = 0; j < 16; ++j)
-                if (n0 + j < p.N) atomicAdd(dst + j, v[j]);
-            }
-          } else if (al) {
-#pragma unroll
-            for (int j = 0; j < 16; j += 4)
-              *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-          } else {
-            for (int j = 0; j < 16; ++j)
-              if (n0 + j < p.N) dst[j] = v[j];
-          }
-        } else {
-          __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.D) + static_cast<long long>(row) * p.ldd + n0;
-          const bool al = full && ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0);
-          if (al) {
-            uint4 q0, q1;
-            q0.x = pack_bf16x2(v[0], v[1]);
-            q0.y = pack_bf16x2(v[2], v[3]);
-            q0.z = pack_bf16x2(v[4], v[5]);
-            q0.w = pack_bf16x2(v[6], v[7]);
-            q1.x = pack_bf16x2(v[8], v[9]);
-            q1.y = pack_bf16x2(v[10], v[11]);
-            q1.z = pack_bf16x2(v[12], v[13]);
-            q1.w = pack_bf16x2(v[14], v[15]);
-            *reinterpret_cast<uint4*>(dst) = q0;
-            *reinterpret_cast<uint4*>(dst + 8) = q1;
-          } else {
-            for (int j = 0; j < 16; ++j)
-              if (n0 + j < p.N) dst[j] = __float2bfloat16_rn(v[j]);
-          }
-        }
+        if (!row_ok) continue;
+        epilogue_store16<kFp8>(p, r0, row, nbase + c, sb + c, ss + c, has_bias, use_scale, atomic);
+        if (two) epilogue_store16<kFp8>(p, r1, row, nbase + c + 16, sb + c + 16, ss + c + 16, has_bias, use_scale,
+                                        atomic);
       }
       tc_fence_before();
       __syncwarp();
@@ -422,7 +491,7 @@ extern "C" int bdl_gemm_bf16(const void* A, const void* B, void* D, const float*
   p.D = D;
   p.bias = bias;
   const size_t stage_bytes = static_cast<size_t>(BM) * BK * 2 + static_cast<size_t>(p.b_rows) * BK * 2;
-  const size_t budget = 227 * 1024 - 1024 - 256;
+  const size_t budget = kSmemBudget;
   int stages = static_cast<int>(budget / stage_bytes);
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) return bdl_fail("bdl_gemm_bf16: tile does not fit in shared memory");
@@ -447,7 +516,7 @@ extern "C" int bdl_gemm_bf16(const void* A, const void* B, void* D, const float*
 #define BDL_LAUNCH_GEMM(AMN, BMN)                                                                                 \
   do {                                                                                                            \
     auto kfn = gemm_bf16_tcgen05_kernel<AMN, BMN, 0>;                                                                \
-    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 256);     \
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemBudget + 1024));     \
     if (e != cudaSuccess) return bdl_fail_cuda("cudaFuncSetAttribute(gemm)", e);                                  \
     kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, p);                                                       \
   } while (0)
@@ -531,7 +600,7 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
   p.D = D;
   p.bias = bias;
   const size_t stage_bytes = static_cast<size_t>(BM) * BK * 2 + static_cast<size_t>(p.b_rows) * BK * 2;
-  const size_t budget = 227 * 1024 - 1024 - 256;
+  const size_t budget = kSmemBudget;
   int stages = static_cast<int>(budget / stage_bytes);
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) return bdl_fail("bdl_conv_igemm_bf16: tile does not fit in shared memory");
@@ -563,7 +632,7 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
 #define BDL_LAUNCH_CONV(AMN, BMN, CV)                                                                             \
   do {                                                                                                            \
     auto kfn = gemm_bf16_tcgen05_kernel<AMN, BMN, CV>;                                                            \
-    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 256);     \
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemBudget + 1024));     \
     if (e != cudaSuccess) return bdl_fail_cuda("cudaFuncSetAttribute(conv gemm)", e);                             \
     kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, p);                                                       \
   } while (0)
@@ -575,4 +644,81 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
     BDL_LAUNCH_CONV(true, true, 2);
 #undef BDL_LAUNCH_CONV
   return bdl_check_launch("gemm_bf16_tcgen05_kernel<conv>");
+}
+
+
+// ------------------------------------------------------------------------------------------------ fp8 (e4m3) inference
+// D[M,N] = (A_q[M,K] * B_q[N,K]^T) * col_scale[n] (+bias)(ReLU); A_q/B_q are e4m3 bytes, K-major, pitches in bytes
+// (multiples of 16). With conv != 0 the A operand is gathered from an NHWC e4m3 tensor by TMA im2col (fprop only).
+// This is the B200 form of the reference's int8 paths: BigQuant MixPrecisionGEMM (core/bigquant, S/nn/quantized/*) and
+// MKL-DNN x8s8s32x convolution with output scales (S/nn/mkldnn/SpatialConvolution.scala:237-247,325-372).
+extern "C" int bdl_gemm_fp8(const void* A, const void* B, void* D, const float* bias, const float* col_scale,
+                            const float* out_qscale, const void* conv_geom, int M, int N, int K, long long lda, long long ldb, long long ldd,
+                            int out_fp32, int flags, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if ((reinterpret_cast<uintptr_t>(A) & 15u) || (reinterpret_cast<uintptr_t>(B) & 15u) || (lda % 16) || (ldb % 16))
+    return bdl_fail("bdl_gemm_fp8: operands must be 16-byte aligned with pitches that are multiples of 16 bytes");
+  if (flags & BDL_GEMM_ATOMIC_ADD) return bdl_fail("bdl_gemm_fp8: inference kernel, no accumulate mode");
+  const int num_sms = bdl_num_sms();
+  GemmParams p{};
+  const int* cg = static_cast<const int*>(conv_geom);   // {N,H,W,C,Ho,Wo,kh,kw,sh,sw,ph,pw,dh,dw} or NULL
+  int gm = M;
+  if (cg) {
+    p.cv_Ho = cg[4]; p.cv_Wo = cg[5]; p.cv_kh = cg[6]; p.cv_kw = cg[7]; p.cv_sh = cg[8]; p.cv_sw = cg[9];
+    p.cv_ph = cg[10]; p.cv_pw = cg[11]; p.cv_dh = cg[12]; p.cv_dw = cg[13]; p.cv_C = cg[3]; p.cv_nimg = cg[0];
+    p.cv_cblocks = (cg[3] + 127) / 128;
+    p.cv_num_kb = cg[6] * cg[7] * p.cv_cblocks;
+    p.fd_hw.init(static_cast<uint32_t>(cg[4]) * cg[5]);
+    p.fd_wo.init(static_cast<uint32_t>(cg[5]));
+    p.fd_cblocks.init(static_cast<uint32_t>(p.cv_cblocks));
+    p.fd_kw.init(static_cast<uint32_t>(cg[7]));
+    p.fd_c.init(static_cast<uint32_t>(cg[3]));
+    gm = cg[0] * cg[4] * cg[5];
+    K = cg[6] * cg[7] * cg[3];
+  }
+  p.M = gm;
+  p.N = N;
+  p.K = K;
+  p.block_n = pick_block_n(gm, N, num_sms);
+  p.b_rows = p.block_n;
+  p.tiles_m = (gm + BM - 1) / BM;
+  p.tiles_n = (N + p.block_n - 1) / p.block_n;
+  p.splits = 1;
+  p.ldd = ldd;
+  p.out_fp32 = out_fp32;
+  p.flags = flags;
+  p.D = D;
+  p.bias = bias;
+  p.col_scale = col_scale;
+  p.out_qscale = out_qscale;
+  if (out_fp32 == 2 && !out_qscale) return bdl_fail("bdl_gemm_fp8: e4m3 output needs out_qscale");
+  const size_t stage_bytes = static_cast<size_t>(BM) * 128 + static_cast<size_t>(p.b_rows) * 128;
+  int stages = static_cast<int>(kSmemBudget / stage_bytes);
+  if (stages > kMaxStages) stages = kMaxStages;
+  p.num_stages = stages;
+  const size_t smem = stages * stage_bytes + 1024;
+  CUtensorMap tmA, tmB;
+  int rc;
+  if (cg)
+    rc = bdl_make_tmap_im2col_u8(&tmA, A, cg[3], cg[2], cg[1], cg[0], lda, -cg[11], -cg[10],
+                                 cg[11] - cg[13] * (cg[7] - 1), cg[10] - cg[12] * (cg[6] - 1), 128, BM, cg[9], cg[8]);
+  else
+    rc = bdl_make_tmap_2d_u8(&tmA, A, static_cast<uint64_t>(K), static_cast<uint64_t>(M), lda, 128, BM);
+  if (rc) return rc;
+  rc = bdl_make_tmap_2d_u8(&tmB, B, static_cast<uint64_t>(K), static_cast<uint64_t>(N), ldb, 128, p.block_n);
+  if (rc) return rc;
+  const long long total = static_cast<long long>(p.tiles_m) * p.tiles_n;
+  const int grid = static_cast<int>(total < num_sms ? total : num_sms);
+  if (cg) {
+    auto kfn = gemm_bf16_tcgen05_kernel<false, false, 1, true>;
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemBudget + 1024));
+    if (e != cudaSuccess) return bdl_fail_cuda("cudaFuncSetAttribute(fp8 conv)", e);
+    kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, p);
+  } else {
+    auto kfn = gemm_bf16_tcgen05_kernel<false, false, 0, true>;
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemBudget + 1024));
+    if (e != cudaSuccess) return bdl_fail_cuda("cudaFuncSetAttribute(fp8 gemm)", e);
+    kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, p);
+  }
+  return bdl_check_launch("gemm_tcgen05_kernel<fp8>");
 }

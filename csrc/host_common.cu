@@ -102,19 +102,36 @@ static EncodeIm2colFn get_encode_im2col() {
   return fn;
 }
 
+static int make_tmap_im2col(CUtensorMap* out, CUtensorMapDataType dt, int esize, const void* base, int C, int W, int H,
+                           int N, long long ld_pixel, int lower_w, int lower_h, int upper_w, int upper_h,
+                           int channels_per_pixel, int pixels_per_column, int stride_w, int stride_h);
+
 int bdl_make_tmap_im2col_bf16(CUtensorMap* out, const void* base, int C, int W, int H, int N, long long ld_pixel,
                               int lower_w, int lower_h, int upper_w, int upper_h, int channels_per_pixel,
                               int pixels_per_column, int stride_w, int stride_h) {
+  return make_tmap_im2col(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, C, W, H, N, ld_pixel, lower_w, lower_h,
+                          upper_w, upper_h, channels_per_pixel, pixels_per_column, stride_w, stride_h);
+}
+int bdl_make_tmap_im2col_u8(CUtensorMap* out, const void* base, int C, int W, int H, int N, long long ld_pixel,
+                            int lower_w, int lower_h, int upper_w, int upper_h, int channels_per_pixel,
+                            int pixels_per_column, int stride_w, int stride_h) {
+  return make_tmap_im2col(out, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, base, C, W, H, N, ld_pixel, lower_w, lower_h, upper_w,
+                          upper_h, channels_per_pixel, pixels_per_column, stride_w, stride_h);
+}
+
+static int make_tmap_im2col(CUtensorMap* out, CUtensorMapDataType dt, int esize, const void* base, int C, int W, int H,
+                           int N, long long ld_pixel, int lower_w, int lower_h, int upper_w, int upper_h,
+                           int channels_per_pixel, int pixels_per_column, int stride_w, int stride_h) {
   EncodeIm2colFn fn = get_encode_im2col();
   if (!fn) return bdl_fail("cuTensorMapEncodeIm2col entry point not available (no CUDA driver?)");
   cuuint64_t dims[4] = {static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H),
                         static_cast<cuuint64_t>(N)};
-  cuuint64_t strides[3] = {static_cast<cuuint64_t>(ld_pixel) * 2, static_cast<cuuint64_t>(ld_pixel) * 2 * W,
-                           static_cast<cuuint64_t>(ld_pixel) * 2 * W * H};
+  cuuint64_t strides[3] = {static_cast<cuuint64_t>(ld_pixel) * esize, static_cast<cuuint64_t>(ld_pixel) * esize * W,
+                           static_cast<cuuint64_t>(ld_pixel) * esize * W * H};
   int lower[2] = {lower_w, lower_h};
   int upper[2] = {upper_w, upper_h};
   cuuint32_t estr[4] = {1, static_cast<cuuint32_t>(stride_w), static_cast<cuuint32_t>(stride_h), 1};
-  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, lower, upper,
+  CUresult r = fn(out, dt, 4, const_cast<void*>(base), dims, strides, lower, upper,
                   static_cast<cuuint32_t>(channels_per_pixel), static_cast<cuuint32_t>(pixels_per_column), estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);

@@ -164,6 +164,20 @@ int bdl_lstm_gates_fwd(const void* g, const float* c_prev, void* h, float* c, vo
 int bdl_lstm_gates_bwd(const void* dh, const float* dc_in, const void* gates, const float* c, const float* c_prev,
                        void* dg, float* dc_prev, long long B, int H, void* stream);
 
+/* ---- fp8 (e4m3) quantised inference (csrc/gemm_tcgen05.cu kFp8, csrc/quantize.cu). Reference: core/bigquant/native
+ *      (MixPrecisionGEMM, quantize), S/nn/quantized/*, S/nn/MklInt8Convertible.scala, S/nn/mkldnn/SpatialConvolution.scala
+ *      :237-247,325-372. D = (A_q * B_q^T) * col_scale[n] (+bias)(ReLU); conv_geom = NULL for a plain GEMM or 14 ints
+ *      {N,H,W,C,Ho,Wo,kh,kw,sh,sw,ph,pw,dh,dw} to gather A from an NHWC e4m3 tensor with TMA im2col. out_fp32: 0 bf16, 1 fp32,
+ *      2 e4m3 requantised with the device scalar *out_qscale (= 448 / absmax of the consumer's input). */
+int bdl_gemm_fp8(const void* A, const void* B, void* D, const float* bias, const float* col_scale,
+                 const float* out_qscale, const void* conv_geom, int M, int N, int K, long long lda, long long ldb, long long ldd, int out_fp32, int flags,
+                 void* stream);
+int bdl_row_absmax(const void* x, float* out, long long rows, long long cols, long long ld, int is_bf16, void* stream);
+int bdl_quantize_e4m3(const void* x, void* q, const float* absmax, int per_row, long long rows, long long cols,
+                      long long ldx, long long ldq, int is_bf16, void* stream);
+int bdl_fp8_colscale(const float* act_absmax, const float* w_absmax, float* out, int n, void* stream);
+int bdl_quantize_int8_rows(const float* w, void* q, const float* absmax, long long rows, long long cols, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

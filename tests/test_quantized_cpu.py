@@ -1,0 +1,108 @@
+"""Quantiser on CPU: module swapping, emulated fp8 arithmetic accuracy, calibration bookkeeping, backward is an error.
+Mirrors S/test/.../nn/quantized/{QuantizableSpec,LinearSpec,SpatialConvolutionSpec}.scala."""
+import numpy as np
+import pytest
+import torch
+
+from bigdl_b200.nn import layer as L
+from bigdl_b200 import quantized as QZ
+from bigdl_b200.quantized import Quantizer
+
+
+def _lenet_like():
+    return (L.Sequential()
+            .add(L.SpatialConvolution(3, 16, 3, 3, 1, 1, 1, 1))
+            .add(L.SpatialBatchNormalization(16))
+            .add(L.ReLU())
+            .add(L.SpatialConvolution(16, 32, 3, 3, 2, 2, 1, 1))
+            .add(L.ReLU())
+            .add(L.SpatialMaxPooling(2, 2, 2, 2))
+            .add(L.Reshape([32 * 4 * 4]))
+            .add(L.Linear(32 * 4 * 4, 64))
+            .add(L.ReLU())
+            .add(L.Linear(64, 10)))
+
+
+def test_quantize_swaps_layers_and_keeps_original():
+    torch.manual_seed(0)
+    m = _lenet_like()
+    x = torch.randn(4, 3, 16, 16)
+    m.evaluate()
+    ref = m.forward(x).clone()
+    q = m.quantize()
+    kinds = [type(c).__name__ for c in q.modules]
+    assert isinstance(q.modules[0], QZ.SpatialConvolution) and isinstance(q.modules[7], QZ.Linear), kinds
+    assert isinstance(m.modules[0], L.SpatialConvolution) and not isinstance(m.modules[0], QZ.QuantizedModule)
+    out = q.forward(x)
+    rel = float((out - ref).norm() / ref.norm())
+    assert rel < 0.08, rel
+    # the float model is untouched
+    assert torch.allclose(m.forward(x), ref)
+
+
+def test_backward_raises():
+    q = L.Sequential().add(L.Linear(8, 4)).quantize()
+    x = torch.randn(2, 8)
+    q.forward(x)
+    with pytest.raises(ValueError, match="quantized model"):
+        q.modules[0].backward(x, torch.randn(2, 4))
+
+
+def test_graph_quantize():
+    torch.manual_seed(1)
+    inp = L.Input()
+    c1 = L.SpatialConvolution(16, 16, 1, 1)(inp)
+    r1 = L.ReLU()(c1)
+    c2 = L.SpatialConvolution(16, 16, 3, 3, 1, 1, 1, 1)(r1)
+    add = L.CAddTable()([c2, inp])
+    g = L.Model([inp], [add]).evaluate()
+    x = torch.randn(2, 16, 8, 8)
+    ref = g.forward(x).clone()
+    q = g.quantize()
+    names = [type(n.element).__module__ for n in q.exec_order]
+    assert sum(n.endswith("quantized.layers") for n in names) == 2
+    out = q.forward(x)
+    assert float((out - ref).norm() / ref.norm()) < 0.08
+
+
+def test_calibrate_sets_static_scales_and_links():
+    torch.manual_seed(2)
+    m = _lenet_like().evaluate()
+    q = m.quantize()
+    xs = [torch.randn(4, 3, 16, 16) for _ in range(3)]
+    Quantizer.calibrate(q, xs)
+    qs = Quantizer.quantized_layers(q)
+    assert all(l.static_scale for l in qs)
+    want = max(float(x.abs().max()) for x in xs)
+    assert abs(qs[0].getInputScales()[0][0] - want) < 1e-5
+    # conv0 (+folded BN + fused ReLU) feeds conv1 directly: linked; linear0 → linear1 linked
+    assert qs[0]._emit_q is qs[1] and qs[2]._emit_q is qs[3]
+    assert qs[1]._emit_q is None            # max-pool in between
+    ref = m.forward(xs[0]).clone()
+    out = q.forward(xs[0])
+    assert float((out - ref).norm() / ref.norm()) < 0.1
+
+
+def test_weight_quantisation_error_bound():
+    torch.manual_seed(3)
+    lin = L.Linear(64, 32)
+    q = QZ.Linear.from_float(lin)
+    w, wd = lin.weight.detach(), q.dequantized_weight()
+    # e4m3 has 3 mantissa bits: relative error <= 2^-4 per element for normal values, absolute error bounded by the
+    # sub-normal step (2^-9 * absmax/448 * 448) for tiny ones
+    err = (w - wd).abs()
+    bound = w.abs() * 2 ** -4 + q._buffers["weight_absmax"].reshape(-1, 1) * 2 ** -9
+    assert bool((err <= bound + 1e-9).all())
+
+
+def test_quantized_save_load_roundtrip(tmp_path):
+    torch.manual_seed(4)
+    m = L.Sequential().add(L.Linear(16, 8)).add(L.ReLU()).add(L.Linear(8, 4)).evaluate()
+    q = m.quantize()
+    x = torch.randn(3, 16)
+    ref = q.forward(x).clone()
+    p = str(tmp_path / "q.bigdl")
+    q.saveModule(p, overWrite=True)
+    q2 = L.Module.loadModule(p).evaluate()
+    assert isinstance(q2.modules[0], QZ.Linear)
+    assert torch.allclose(q2.forward(x), ref, atol=1e-6)

@@ -184,6 +184,10 @@ class SpatialConvolution(QuantizedModule):
         q._buffers["weight_absmax"] = am
         q._buffers["bias"] = m.bias.detach().float().clone() if m.with_bias else torch.zeros(O, device=w.device)
         q._fuse_relu = getattr(m, "_fuse_relu", False)
+        if cg < 16 and m.n_group == 1:
+            # An RGB stem would waste 7/8 of every 128-byte fp8 k-block on channel padding, and first layers are the
+            # usual high-precision exception in int8/fp8 deployments: keep a bf16 copy and run the bf16 kernel on GPU.
+            q.register_buffer("weight_hp", w.to(torch.bfloat16).contiguous(memory_format=torch.channels_last))
         if m.hasName():
             q.setName(m.getName())
         return q
@@ -219,7 +223,16 @@ class SpatialConvolution(QuantizedModule):
         Ho, Wo = self._out_hw(H, W, pads)
         sym = pads[0] == pads[2] and pads[1] == pads[3]
         with torch.no_grad():
-            if native(x) and self.n_group == 1 and sym:
+            if native(x) and "weight_hp" in self._buffers and x.dtype != torch.uint8:
+                from ..ops.functions import ConvFn
+
+                if self.calibrating:
+                    self._act_absmax(x.detach())
+                geom = (self.kernel_h, self.kernel_w, self.stride_h, self.stride_w, *pads, self.dilation_h,
+                        self.dilation_w, 1)
+                w16 = self._buffers["weight_hp"]
+                y = ConvFn.apply(x.detach(), w16, self._buffers["bias"], w16, geom, self._fuse_relu, 1.0, 1.0)
+            elif native(x) and self.n_group == 1 and sym:
                 y = self._forward_fp8(x, N, H, W, Ho, Wo, pads)
             else:
                 y = self._forward_emulated(x, pads)

@@ -1,9 +1,12 @@
 // bf16 GEMM on 5th-gen tensor cores: D[M,N] = opA(A) * opB(B)^T (+bias)(ReLU), fp32 accumulation in TMEM.
 //
-// One persistent CTA per SM, 6 warps:
+// One persistent CTA per SM, 10 warps:
 //   warp 0      TMA producer   (cp.async.bulk.tensor.2d -> 128B-swizzled smem ring, mbarrier complete_tx)
 //   warp 1      MMA issuer     (one lane issues tcgen05.mma.cta_group::1.kind::f16, tcgen05.commit frees slots)
-//   warps 2..5  epilogue       (tcgen05.ld TMEM -> registers -> bias/ReLU -> bf16|fp32 global, or fp32 red.add)
+//   warps 2..9  epilogue       (tcgen05.ld TMEM -> registers -> scale/bias/ReLU -> bf16|fp32|e4m3 global, or fp32
+//               red.add). Two warps per TMEM lane quadrant split a tile's columns; each keeps the next 32 columns'
+//               tcgen05.ld in flight while it converts and stores the current ones, and the tile's bias/scale columns
+//               are staged in shared memory before the accumulator is ready (small-K GEMMs are epilogue-bound).
 // Two TMEM accumulator stages (2 x 256 columns) let the epilogue of tile i overlap the MMAs of tile i+1.
 //
 // This single kernel is the engine behind Linear fwd/bwd, 1x1 conv, im2col conv fprop/dgrad/wgrad and the
@@ -27,7 +30,8 @@ constexpr int BK = 64;  // 64 bf16 = 128 bytes = one swizzle row
 // dynamic shared memory available to the operand ring: 227 KB minus alignment slack, barriers and the epilogue columns
 constexpr size_t kSmemBudget = 227 * 1024 - 1024 - 512 - 4096;
 constexpr int kMaxStages = 8;
-constexpr int kGemmThreads = 192;
+constexpr int kGemmThreads = 320;   // TMA warp, MMA warp, 8 epilogue warps (two per TMEM lane quadrant)
+constexpr int kEpiThreads = 256;
 constexpr int kTmemCols = 512;
 constexpr int kAccStride = 256;  // TMEM columns between the two accumulator stages
 
@@ -200,7 +204,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(smem_u32(&tfull_bar[s]), 1);
-      mbar_init(smem_u32(&tempty_bar[s]), 4);
+      mbar_init(smem_u32(&tempty_bar[s]), 8);
     }
     fence_mbar_init();
     tma_prefetch_desc(&tmA);
@@ -373,9 +377,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     }
     __syncwarp();
   } else {
-    // ------------------------------------------------------------ epilogue (warps 2..5)
+    // ------------------------------------------------------------ epilogue (warps 2..9)
     const uint32_t quad = warp & 3u;  // TMEM lane quadrant this warp may read
-    const uint32_t et = threadIdx.x - 64u;   // 0..127 within the epilogue warps
+    const uint32_t et = threadIdx.x - 64u;   // 0..255 within the epilogue warps
+    const uint32_t half = (warp - 2u) >> 2;  // warps 2..5 take the low columns of a tile, 6..9 the high ones
     uint32_t acc = 0, acc_phase = 0;
     const bool has_bias = (p.flags & BDL_GEMM_BIAS) != 0;
     const bool atomic = (p.flags & BDL_GEMM_ATOMIC_ADD) != 0;
@@ -393,27 +398,52 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       float* ss = &epi_cols[acc][1][0];
       const bool tile_bias = has_bias && (!atomic || split == 0);
       if (has_bias || use_scale) {
-        for (int c = static_cast<int>(et); c < p.block_n; c += 128) {
+        for (int c = static_cast<int>(et); c < p.block_n; c += kEpiThreads) {
           const int n = nbase + c;
           sb[c] = (tile_bias && n < p.N) ? __ldg(p.bias + n) : 0.f;
           if (kFp8) ss[c] = (use_scale && n < p.N) ? __ldg(p.col_scale + n) : 1.f;
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
       }
       mbar_wait(smem_u32(&tfull_bar[acc]), acc_phase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((quad * 32u) << 16) + acc * kAccStride;
       const bool row_ok = row < p.M;
-      for (int c = 0; c < p.block_n; c += 32) {
-        uint32_t r0[16], r1[16];
-        const bool two = c + 16 < p.block_n;
-        tmem_ld_16(t_row + static_cast<uint32_t>(c), r0);
-        if (two) tmem_ld_16(t_row + static_cast<uint32_t>(c + 16), r1);
+      // the two warps of a TMEM lane quadrant split the tile's columns
+      const int c_split = ((p.block_n / 16 + 1) / 2) * 16;
+      const int c_begin = half ? c_split : 0;
+      const int c_end = half ? p.block_n : c_split;
+      // Two register sets: the TMEM loads of the next 32 columns are in flight while this set is converted and stored.
+      uint32_t a0[16], a1[16], b0[16], b1[16];
+      int c = c_begin;
+      if (c < c_end) {
+        tmem_ld_16(t_row + static_cast<uint32_t>(c), a0);
+        if (c + 16 < c_end) tmem_ld_16(t_row + static_cast<uint32_t>(c + 16), a1);
+      }
+      while (c < c_end) {
         tmem_ld_wait();
-        if (!row_ok) continue;
-        epilogue_store16<kFp8>(p, r0, row, nbase + c, sb + c, ss + c, has_bias, use_scale, atomic);
-        if (two) epilogue_store16<kFp8>(p, r1, row, nbase + c + 16, sb + c + 16, ss + c + 16, has_bias, use_scale,
-                                        atomic);
+        if (c + 32 < c_end) {
+          tmem_ld_16(t_row + static_cast<uint32_t>(c + 32), b0);
+          if (c + 48 < c_end) tmem_ld_16(t_row + static_cast<uint32_t>(c + 48), b1);
+        }
+        if (row_ok) {
+          epilogue_store16<kFp8>(p, a0, row, nbase + c, sb + c, ss + c, has_bias, use_scale, atomic);
+          if (c + 16 < c_end)
+            epilogue_store16<kFp8>(p, a1, row, nbase + c + 16, sb + c + 16, ss + c + 16, has_bias, use_scale, atomic);
+        }
+        c += 32;
+        if (c >= c_end) break;
+        tmem_ld_wait();
+        if (c + 32 < c_end) {
+          tmem_ld_16(t_row + static_cast<uint32_t>(c + 32), a0);
+          if (c + 48 < c_end) tmem_ld_16(t_row + static_cast<uint32_t>(c + 48), a1);
+        }
+        if (row_ok) {
+          epilogue_store16<kFp8>(p, b0, row, nbase + c, sb + c, ss + c, has_bias, use_scale, atomic);
+          if (c + 16 < c_end)
+            epilogue_store16<kFp8>(p, b1, row, nbase + c + 16, sb + c + 16, ss + c + 16, has_bias, use_scale, atomic);
+        }
+        c += 32;
       }
       tc_fence_before();
       __syncwarp();

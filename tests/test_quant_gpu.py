@@ -76,8 +76,11 @@ def test_quantized_conv_matches_emulation(C, O, k, s, p, d, HW):
     qg = q.cloneModule().to("cuda")
     out = qg.forward(x.cuda().to(torch.bfloat16).contiguous(memory_format=torch.channels_last)).float().cpu()
     assert out.shape == ref.shape
-    # activations reach the GPU layer as bf16, the CPU path quantises fp32: allow the bf16 input rounding
-    assert float((out - ref).norm() / ref.norm()) < 0.02
+    if C >= 16:
+        # activations reach the GPU layer as bf16, the CPU path quantises fp32: allow the bf16 input rounding
+        assert float((out - ref).norm() / ref.norm()) < 0.02
+    else:
+        assert "weight_hp" in qg._buffers          # RGB stem stays in bf16 on the GPU
     full = F.relu(F.conv2d(x, conv.weight.detach(), conv.bias.detach(), s, p, d))
     assert float((out - full).norm() / full.norm()) < 0.08
 

@@ -41,6 +41,21 @@ class FlatParams:
         return start, end - start
 
 
+    def module_ranges(self):
+        """[(leaf module, offset, padded length)] in flat (= forward registration) order, one entry per module."""
+        out: list = []
+        for m, _, o, n in self.entries:
+            end = o + _align(n)
+            if out and out[-1][0] is m:
+                out[-1] = (m, out[-1][1], end - out[-1][1])
+            else:
+                out.append((m, o, end - o))
+        if out:                          # the last range stops at the end of the buffer
+            m, o, _ = out[-1]
+            out[-1] = (m, o, self.weights.numel() - o)
+        return out
+
+
 def partition_range(total: int, parts: int, rank: int) -> tuple[int, int]:
     base, extra = divmod(total, parts)
     start = rank * base + min(rank, extra)

@@ -408,6 +408,9 @@ class Module:
 
     def _call(self, input):
         """Graph-building call used by containers and training loops (no detach, no host sync)."""
+        pre = self.__dict__.get("_pre_call_hook")      # ParallelOptimizer bucket boundary / lazy parameter update
+        if pre is not None:
+            input = pre(self, input)
         out = self.updateOutput(input)
         self.output = out
         return out

@@ -311,6 +311,9 @@ class Optimizer:
             om.save(os.path.join(path, fname), self.overwrite_checkpoint)
 
     def _gather_for_checkpoint(self):
+        st = getattr(self, "_strategy", None)
+        if st is not None:
+            st.drain()
         if self._param_sync is not None:
             self._param_sync.gather_master_weights()
 
@@ -388,7 +391,7 @@ class DistriOptimizer(Optimizer):
             self._param_sync = None
 
 
-def _train_loop(opt: Optimizer, distributed: bool):
+def _train_loop(opt: Optimizer, distributed: bool, strategy_factory=None):
     from ..parallel.all_reduce_parameter import AllReduceParameter
 
     model, criterion, dataset = opt.model, opt.criterion, opt.dataset
@@ -403,7 +406,8 @@ def _train_loop(opt: Optimizer, distributed: bool):
     world = dist.get_world_size() if (distributed and dist.is_initialized()) else 1
     ranges = opt._check_submodules(flat) if len(opt.optim_methods) > 1 else None
 
-    sync = AllReduceParameter(flat, backend=None if world > 1 else "local")
+    # ParallelOptimizer keeps full (non-sharded) weights and optimizer state on every rank: no sharded master copy
+    sync = AllReduceParameter(flat, backend=None if (world > 1 and strategy_factory is None) else "local")
     sync.init()
     opt._param_sync = sync
     single = opt._single_method()
@@ -435,6 +439,10 @@ def _train_loop(opt: Optimizer, distributed: bool):
     graphs: dict = {}
     graph_ok = (device.type == "cuda" and bool(config.get("bigdl.cudaGraph")) and single is not None
                 and clip.l2norm is None and sync.backend in ("local", "p2p") and config.get("bigdl.engineType") == "b200")
+    strategy = strategy_factory(model, world) if strategy_factory is not None else None
+    if strategy is not None:
+        graph_ok = False
+        opt._strategy = strategy
 
     while not opt.end_when(state):
         t0 = time.time()
@@ -459,7 +467,11 @@ def _train_loop(opt: Optimizer, distributed: bool):
             seed._bdl_is_one = True
             torch.autograd.backward(loss, seed)
             model._apply_regularizers()
-            if single is not None:
+            if strategy is not None:
+                for om_ in strategy.methods:
+                    om_.clip_range = clip.constant
+                strategy.after_backward()
+            elif single is not None:
                 sync.step(single, avg_numbers=world, l2_clip=clip.l2norm)
             else:
                 _multi_method_step(opt, sync, flat, ranges, world, clip)
@@ -510,6 +522,8 @@ def _train_loop(opt: Optimizer, distributed: bool):
         for om in opt.optim_methods.values():
             if om is not lead:
                 om.state["epoch"], om.state["neval"] = state["epoch"], state["neval"]
+        if strategy is not None:
+            strategy.sync_states(state)
         cb = getattr(opt, "_iteration_callback", None)
         if cb is not None:
             cb(state, loss)
@@ -521,6 +535,9 @@ def _train_loop(opt: Optimizer, distributed: bool):
     if pending_loss is not None:
         opt._loss_events[pending_loss[0]].synchronize()
         state["Loss"] = float(opt._loss_ring[pending_loss[0]][0])
+    if strategy is not None:
+        strategy.drain()           # apply the last iteration's averaged gradients
+        strategy.detach()
     sync.gather_master_weights()
     if flat.compute is not None and sync.backend == "local":
         flat.dirty = True

@@ -27,6 +27,7 @@ _DEFAULTS: dict[str, Any] = {
     "bigdl.parameter.backend": "auto",       # auto | p2p (fused NVLink kernels) | nccl | gloo
     "bigdl.parallelOptimizer.iterationPerTime": 1,
     "bigdl.parallelOptimizer.parameterBlocks": 10,
+    "bigdl.parallel.bucketMB": 16.0,         # ParallelOptimizer bucket size (fp32 gradient bytes)
     # fusion flags (S/nn/mkldnn/DnnGraph.scala:412-463)
     "bigdl.mkldnn.fusion": True,
     "bigdl.mkldnn.fusion.convbn": True,

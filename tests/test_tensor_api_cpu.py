@@ -1,0 +1,110 @@
+"""Torch7-style Tensor API (mirrors T/tensor/DenseTensorSpec.scala, DenseTensorMathSpec.scala, SparseTensorSpec.scala,
+QuantizedTensorSpec.scala)."""
+import numpy as np
+import torch
+
+from bigdl_b200.tensor import QuantizedTensor, SparseTensor, Storage, Tensor, cat
+
+
+def test_one_based_views_share_storage():
+    t = Tensor(3, 4).fill(0)
+    assert t.nDimension() == 2 and t.size() == [3, 4] and t.size(2) == 4 and t.stride() == [4, 1]
+    row = t.select(1, 2)
+    row.fill(7)
+    assert t.valueAt(2, 1) == 7 and t.valueAt(1, 1) == 0
+    sub = t.narrow(2, 2, 2)
+    assert sub.size() == [3, 2] and sub.storageOffset() == 2
+    sub.setValue(1, 1, 5.0)
+    assert t.valueAt(1, 2) == 5.0
+    assert t(2).size() == [4] and t(2, 3) == 7
+    s = Storage(torch.arange(12.0))
+    v = Tensor(s, 3, [2, 3])
+    assert v.valueAt(1, 1) == 2.0 and v.valueAt(2, 3) == 7.0
+
+
+def test_math_overloads_are_in_place_and_return_self():
+    a = Tensor([[1.0, 2.0], [3.0, 4.0]])
+    b = Tensor([[1.0, 1.0], [1.0, 1.0]])
+    assert a.add(2.0, b) is a and a.t.tolist() == [[3.0, 4.0], [5.0, 6.0]]
+    a.add(b, -1.0, b)
+    assert a.t.tolist() == [[0.0, 0.0], [0.0, 0.0]]
+    c = Tensor(2, 2).fill(1)
+    c.addmm(0.5, Tensor([[1.0, 2.0], [3.0, 4.0]]), Tensor([[1.0, 0.0], [0.0, 1.0]]))
+    assert c.t.tolist() == [[1.5, 2.0], [2.5, 3.0]]
+    d = Tensor(2).fill(0)
+    d.addmv(1.0, Tensor([[1.0, 2.0], [3.0, 4.0]]), Tensor([1.0, 1.0]))
+    assert d.t.tolist() == [3.0, 7.0]
+    e = Tensor(2, 2).fill(0).addr(1.0, Tensor([1.0, 2.0]), Tensor([3.0, 4.0]))
+    assert e.t.tolist() == [[3.0, 4.0], [6.0, 8.0]]
+    f = Tensor([1.0, 4.0, 9.0]).sqrt()
+    assert f.t.tolist() == [1.0, 2.0, 3.0]
+    g = Tensor(3).fill(1).addcmul(2.0, Tensor([1.0, 2.0, 3.0]), Tensor([1.0, 1.0, 2.0]))
+    assert g.t.tolist() == [3.0, 5.0, 13.0]
+    assert (Tensor([[1.0, 2.0]]) * Tensor([[1.0], [1.0]])).t.tolist() == [[3.0]]      # matrix product like Scala `*`
+    assert Tensor([3.0, 4.0]).norm(2) == 5.0 and Tensor([3.0, 4.0]).sumSquare() == 25.0
+    assert Tensor([1.0, 2.0]).dot(Tensor([3.0, 4.0])) == 11.0
+
+
+def test_reductions_use_one_based_indices():
+    t = Tensor([[1.0, 9.0, 3.0], [7.0, 2.0, 8.0]])
+    v, i = t.max(2)
+    assert v.t.tolist() == [[9.0], [8.0]] and i.t.tolist() == [[2.0], [3.0]]
+    v, i = t.min(1)
+    assert i.t.tolist() == [[1.0, 2.0, 1.0]]
+    v, i = t.topk(2, 2, increase=False)
+    assert v.t.tolist() == [[9.0, 3.0], [8.0, 7.0]] and i.t.tolist() == [[2.0, 3.0], [3.0, 1.0]]
+    assert t.sum() == 30.0 and t.sum(1).t.tolist() == [[8.0, 11.0, 11.0]] and abs(t.mean() - 5.0) < 1e-6
+    idx = Tensor([[1.0, 1.0, 1.0]])
+    assert Tensor(1, 3).gather(1, idx, t).t.tolist() == [[1.0, 9.0, 3.0]]
+    assert t.index(2, Tensor([3.0, 1.0])).t.tolist() == [[3.0, 1.0], [8.0, 7.0]]
+
+
+def test_resize_copy_closures_and_masks():
+    t = Tensor(2, 3).fill(1)
+    t.resize(3, 2)
+    assert t.size() == [3, 2] and t.sum() == 6.0
+    t.resize(2, 2)
+    assert t.size() == [2, 2]
+    t.copy(Tensor([1.0, 2.0, 3.0, 4.0]))
+    assert t.t.tolist() == [[1.0, 2.0], [3.0, 4.0]]
+    t.apply1(lambda v: v * 2)
+    assert t.t.tolist() == [[2.0, 4.0], [6.0, 8.0]]
+    t.map(Tensor(2, 2).fill(1), lambda a, b: a - b)
+    assert t.t.tolist() == [[1.0, 3.0], [5.0, 7.0]]
+    m = t.gt(4.0)
+    assert m.t.tolist() == [[0.0, 0.0], [1.0, 1.0]]
+    assert t.maskedSelect(m).t.tolist() == [5.0, 7.0]
+    t.maskedFill(m, 0.0)
+    assert t.sum() == 4.0
+    assert Tensor.range(1, 5, 2).t.tolist() == [1.0, 3.0, 5.0]
+    assert cat([Tensor(1, 2).fill(1), Tensor(1, 2).fill(2)], 1).size() == [2, 2]
+    assert Tensor([1.0]).almostEqual(Tensor([1.0005]), 1e-3) and Tensor([1.0]) == Tensor([1.0])
+    k = Tensor([[1.0, 0.0], [0.0, -1.0]])
+    x = Tensor(torch.arange(9.0).reshape(3, 3))
+    assert x.xcorr2(k).t.tolist() == [[-4.0, -4.0], [-4.0, -4.0]]
+    assert x.conv2(k).t.tolist() == [[4.0, 4.0], [4.0, 4.0]]
+
+
+def test_sparse_tensor():
+    sp = Tensor.sparse([[1, 1, 3], [1, 3, 2]], [1.0, 2.0, 3.0], (3, 3))          # 0-based like torch? no: explicit below
+    sp = SparseTensor([[1, 1, 3], [1, 3, 2]], [1.0, 2.0, 3.0], (3, 3), one_based=True)
+    d = sp.to_dense()
+    assert d.t.tolist() == [[1.0, 0.0, 2.0], [0.0, 0.0, 0.0], [0.0, 3.0, 0.0]]
+    assert sp.numNonZeroByRow() == [2, 0, 1] and sp.nElement() == 3
+    w = torch.arange(6.0).reshape(3, 2)
+    assert torch.equal(sp.mm(w), d.t @ w)
+    assert sp.narrow(1, 3, 1).to_dense().t.tolist() == [[0.0, 3.0, 0.0]]
+    j = SparseTensor.concat(2, [sp, sp])
+    assert j.size() == [3, 6] and j.nElement() == 6
+    assert SparseTensor.from_dense(d).to_dense() == d
+
+
+def test_quantized_tensor_matches_reference_rule():
+    w = torch.tensor([[0.5, -1.0, 0.25], [2.0, 1.0, -0.5]])
+    q = Tensor(w).toQuantizedTensor()
+    assert isinstance(q, QuantizedTensor)
+    assert q.q.tolist() == [[64, -127, 32], [127, 64, -32]]       # round(x/absmax*127)
+    assert q.maxOfRow.tolist() == [0.5, 2.0] and q.minOfRow.tolist() == [-1.0, -0.5]
+    assert (q.dequantize() - w).abs().max() < 0.01
+    b, am = q.to_e4m3()
+    assert b.dtype == torch.uint8 and b.shape == (2, 16) and torch.allclose(am, torch.tensor([1.0, 2.0]), atol=0.01)

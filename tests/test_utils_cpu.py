@@ -1,0 +1,69 @@
+import time
+
+import pytest
+import torch
+
+from bigdl_b200.utils.directed_graph import Node
+from bigdl_b200.utils.file import File
+from bigdl_b200.utils.shape import MultiShape, Shape, SingleShape
+from bigdl_b200.utils.thread_pool import ThreadPool
+from bigdl_b200.utils.util import Crc32, HashFunc, LayerException, kthLargest, shift
+
+
+def test_shape():
+    s = Shape([2, 3])
+    assert isinstance(s, SingleShape) and s.toSingle() == [2, 3]
+    assert s.copyAndUpdate(-1, 5).toSingle() == [2, 5]
+    m = Shape([Shape([1, 2]), [3]])
+    assert isinstance(m, MultiShape) and m.toMulti()[1] == SingleShape([3])
+    with pytest.raises(ValueError):
+        s.toMulti()
+
+
+def test_file_roundtrip(tmp_path):
+    p = str(tmp_path / "a" / "obj.bin")
+    File.save({"w": torch.ones(3)}, p)
+    assert torch.equal(File.load(p)["w"], torch.ones(3))
+    with pytest.raises(FileExistsError):
+        File.save(1, p)
+    File.save(2, p, isOverwrite=True)
+    assert File.load("file://" + p) == 2
+    File.saveBytes(b"xyz", str(tmp_path / "b.bin"))
+    assert File.readBytes(str(tmp_path / "b.bin")) == b"xyz"
+    with pytest.raises(IOError):
+        File.load("hdfs://nn/path")
+
+
+def test_misc_utils():
+    assert kthLargest([3, 1, 2], 1) == 3
+    assert shift([1, 2, 3, 4], 0, 2) == [2, 3, 1, 4]
+    assert HashFunc.murmurhash3_32(b"", 0) == 0
+    assert HashFunc.murmurhash3_32(b"hello", 0) == 0x248BFA47          # public MurmurHash3 test vector
+    assert HashFunc.murmurhash3_32("The quick brown fox jumps over the lazy dog", 0x9747B28C) == 0x2FA826CD
+    assert Crc32.crc32c(b"123456789") == 0xE3069283
+    e = LayerException("Sequential/Linear[fc1]", ValueError("bad"))
+    assert "fc1" in str(e) and isinstance(e.error, ValueError)
+
+
+def test_thread_pool_timeout_marks_stragglers():
+    tp = ThreadPool(4)
+    assert tp.invokeAndWait([lambda i=i: i * i for i in range(5)]) == [0, 1, 4, 9, 16]
+    futs = tp.invokeAndWait2([lambda: 1, lambda: time.sleep(0.5) or 2], timeout=0.1)
+    assert [f.abandoned for f in futs] == [False, True]
+    tp.sync(tp.invoke([lambda: None]))
+    tp.shutdown()
+
+
+def test_directed_graph():
+    a, b, c, d = Node("a"), Node("b"), Node("c"), Node("d")
+    a >> b >> d
+    a >> c >> d
+    g = a.graph()
+    order = [n.element for n in g.topologySort()]
+    assert order[0] == "a" and order[-1] == "d" and g.size() == 4 and g.edges() == 4
+    assert [n.element for n in d.graph(reverse=True).topologySort()][0] == "d"
+    d >> a
+    with pytest.raises(ValueError):
+        g.topologySort()
+    d.delete(a)
+    assert g.cloneGraph().size() == 4

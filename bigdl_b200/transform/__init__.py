@@ -1,0 +1,1 @@
+from . import vision  # noqa: F401

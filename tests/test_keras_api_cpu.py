@@ -1,0 +1,112 @@
+"""Keras-style API: shape inference against known Keras-1.2.2 shapes, functional Model, compile/fit/evaluate/predict
+(mirrors T/keras/nn/*Spec.scala and pyspark/test/bigdl/keras/test_newapi.py)."""
+import numpy as np
+import pytest
+import torch
+
+import bigdl_b200.nn.keras as K
+
+
+def _out(layer, shape):
+    return tuple(layer.build(list(shape)))
+
+
+def test_shape_inference_core_layers():
+    assert _out(K.Dense(5, activation="relu"), (7,)) == (5,)
+    assert _out(K.Dense(5), (3, 7)) == (3, 5)
+    assert _out(K.Flatten(), (2, 3, 4)) == (24,)
+    assert _out(K.Reshape((4, -1)), (2, 3, 4)) == (4, 6)
+    assert _out(K.Permute((2, 1, 3)), (2, 3, 4)) == (3, 2, 4)
+    assert _out(K.RepeatVector(4), (6,)) == (4, 6)
+    assert _out(K.Embedding(100, 8), (12,)) == (12, 8)
+    assert _out(K.BatchNormalization(), (3, 8, 8)) == (3, 8, 8)
+    assert _out(K.Highway(), (6,)) == (6,)
+    assert _out(K.MaxoutDense(3), (6,)) == (3,)
+
+
+def test_shape_inference_conv_pool():
+    assert _out(K.Convolution2D(8, 3, 3), (3, 16, 16)) == (8, 14, 14)
+    assert _out(K.Convolution2D(8, 3, 3, border_mode="same", subsample=(2, 2)), (3, 16, 16)) == (8, 8, 8)
+    assert _out(K.Convolution2D(8, 3, 3, dim_ordering="tf"), (16, 16, 3)) == (14, 14, 8)
+    assert _out(K.Convolution1D(6, 3), (10, 4)) == (8, 6)
+    assert _out(K.Convolution1D(6, 3, border_mode="same"), (10, 4)) == (10, 6)
+    assert _out(K.Convolution3D(4, 2, 2, 2), (3, 6, 6, 6)) == (4, 5, 5, 5)
+    assert _out(K.AtrousConvolution2D(4, 3, 3, atrous_rate=(2, 2)), (3, 12, 12)) == (4, 8, 8)
+    assert _out(K.AtrousConvolution1D(4, 3, atrous_rate=2), (12, 5)) == (8, 4)
+    assert _out(K.Deconvolution2D(3, 3, 3, subsample=(2, 2)), (4, 5, 5)) == (3, 11, 11)
+    assert _out(K.SeparableConvolution2D(6, 3, 3), (3, 10, 10)) == (6, 8, 8)
+    assert _out(K.MaxPooling2D(), (3, 8, 8)) == (3, 4, 4)
+    assert _out(K.AveragePooling2D((3, 3), strides=(2, 2), border_mode="same"), (3, 9, 9)) == (3, 5, 5)
+    assert _out(K.MaxPooling1D(2), (10, 4)) == (5, 4)
+    assert _out(K.AveragePooling3D(), (2, 4, 4, 4)) == (2, 2, 2, 2)
+    assert _out(K.GlobalAveragePooling2D(), (5, 7, 7)) == (5,)
+    assert _out(K.GlobalMaxPooling1D(), (9, 4)) == (4,)
+    assert _out(K.GlobalMaxPooling3D(), (3, 4, 4, 4)) == (3,)
+    assert _out(K.ZeroPadding2D((1, 2)), (3, 8, 8)) == (3, 10, 12)
+    assert _out(K.ZeroPadding1D(2), (5, 3)) == (9, 3)
+    assert _out(K.Cropping2D(((1, 1), (2, 2))), (3, 8, 8)) == (3, 6, 4)
+    assert _out(K.Cropping1D((1, 2)), (8, 3)) == (5, 3)
+    assert _out(K.UpSampling2D((2, 3)), (3, 4, 4)) == (3, 8, 12)
+    assert _out(K.UpSampling1D(3), (4, 5)) == (12, 5)
+    assert _out(K.LocallyConnected2D(4, 3, 3), (2, 6, 6)) == (4, 4, 4)
+
+
+def test_shape_inference_recurrent():
+    assert _out(K.LSTM(6), (5, 4)) == (6,)
+    assert _out(K.GRU(6, return_sequences=True), (5, 4)) == (5, 6)
+    assert _out(K.SimpleRNN(3, go_backwards=True), (5, 4)) == (3,)
+    assert _out(K.Bidirectional(K.LSTM(6, return_sequences=True)), (5, 4)) == (5, 12)
+    assert _out(K.Bidirectional(K.GRU(6), merge_mode="sum"), (5, 4)) == (6,)
+    assert _out(K.TimeDistributed(K.Dense(7)), (5, 4)) == (5, 7)
+    assert _out(K.ConvLSTM2D(4, 3, return_sequences=True), (3, 2, 8, 8)) == (3, 4, 8, 8)
+
+
+def test_sequential_requires_input_shape_and_tracks_shapes():
+    m = K.Sequential()
+    with pytest.raises(ValueError):
+        m.add(K.Dense(3))
+    m.add(K.Convolution2D(4, 3, 3, activation="relu", input_shape=(1, 12, 12)))
+    m.add(K.MaxPooling2D())
+    m.add(K.Flatten())
+    m.add(K.Dense(10, activation="softmax"))
+    assert m.getOutputShape() == (None, 10) and m.getInputShape() == (None, 1, 12, 12)
+    y = m.forward(torch.randn(3, 1, 12, 12))
+    assert tuple(y.shape) == (3, 10) and torch.allclose(y.sum(1), torch.ones(3), atol=1e-5)
+    with pytest.raises(TypeError):
+        m.add(__import__("bigdl_b200.nn.layer", fromlist=["Linear"]).Linear(10, 2))
+
+
+def test_functional_model_and_merge():
+    a = K.Input(shape=(8,))
+    b = K.Input(shape=(8,))
+    da = K.Dense(6, activation="tanh")(a)
+    db = K.Dense(6, activation="tanh")(b)
+    merged = K.merge([da, db], mode="concat")
+    out = K.Dense(2)(merged)
+    model = K.Model([a, b], out)
+    assert model.getOutputShape() == (None, 2)
+    y = model.forward([torch.randn(4, 8), torch.randn(4, 8)])
+    assert tuple(y.shape) == (4, 2)
+
+
+def test_compile_fit_evaluate_predict():
+    from bigdl_b200.utils.random_generator import RNG
+
+    RNG.setSeed(5)
+    torch.manual_seed(5)
+    rs = np.random.RandomState(0)
+    x = rs.randn(128, 4).astype(np.float32)
+    y = (x.sum(1) > 0).astype(np.float32) + 1          # 1-based classes
+    model = K.Sequential()
+    model.add(K.Dense(16, activation="relu", input_shape=(4,)))
+    model.add(K.Dense(2, activation="softmax"))
+    with pytest.raises(RuntimeError):
+        model.fit(x, y)
+    model.compile(optimizer="adam", loss="sparse_categorical_crossentropy", metrics=["accuracy"])
+    model.fit(x, y, batch_size=16, nb_epoch=40, validation_data=(x, y))
+    loss, acc = model.evaluate(x, y, batch_size=32)
+    assert acc > 0.9 and loss < 0.6
+    pred = model.predict(x, batch_size=32)
+    assert len(pred) == 128 and tuple(np.asarray(pred[0]).shape) == (2,)
+    with pytest.raises(TypeError):
+        model.compile(optimizer="nope", loss="mse")

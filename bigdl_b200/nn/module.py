@@ -652,6 +652,43 @@ class Module:
 
     load_model = loadModule
 
+    @staticmethod
+    def loadTorch(path: str):
+        from ..interop.torchfile import load_torch_module
+
+        return load_torch_module(path)
+
+    load_torch = loadTorch
+
+    @staticmethod
+    def loadCaffe(model, defPath: str, modelPath: str, matchAll: bool = True):
+        """Copy weights from a caffemodel into an existing model by layer name (CaffeLoader.load)."""
+        from ..interop.caffe import CaffeLoader
+
+        return CaffeLoader.load(model, defPath, modelPath, matchAll)
+
+    @staticmethod
+    def loadCaffeModel(defPath: str, modelPath: str):
+        from ..interop.caffe import CaffeLoader
+
+        return CaffeLoader.loadCaffe(defPath, modelPath)[0]
+
+    load_caffe, load_caffe_model = loadCaffe, loadCaffeModel
+
+    @staticmethod
+    def loadTF(path: str, inputs, outputs, byteOrder: str = "little_endian", binFile: str | None = None):
+        from ..interop.tensorflow import load_tf
+
+        return load_tf(path, inputs, outputs, byteOrder, binFile)
+
+    load_tensorflow = loadTF
+
+    @staticmethod
+    def load_keras(json_path=None, hdf5_path=None, by_name=False):
+        from ..interop.keras_converter import load_keras
+
+        return load_keras(json_path, hdf5_path, by_name)
+
     def saveTorch(self, path: str, overWrite: bool = False):
         from ..interop.torchfile import save_torch_module
 

@@ -79,3 +79,93 @@ def test_t7_reads_torch_written_layout(tmp_path):
     p.write_bytes(bytes(out))
     m = T7.load(str(p))
     assert isinstance(m, L.Linear) and m.weight.tolist() == [[0, 1, 2], [3, 4, 5]] and m.bias.tolist() == [6, 7]
+
+
+def _branchy_model():
+    torch.manual_seed(1)
+    inp = L.Input("data")
+    c1 = L.SpatialConvolution(3, 8, 3, 3, 1, 1, 1, 1).setName("conv1")(inp)
+    bn = L.SpatialBatchNormalization(8).setName("bn1")(c1)
+    r1 = L.ReLU().setName("relu1")(bn)
+    p1 = L.SpatialMaxPooling(2, 2, 2, 2).setName("pool1")(r1)
+    a = L.SpatialConvolution(8, 4, 1, 1).setName("branch_a")(p1)
+    b = L.SpatialConvolution(8, 4, 3, 3, 1, 1, 1, 1).setName("branch_b")(p1)
+    cat = L.JoinTable(2).setName("concat")([a, b])
+    lrn = L.SpatialCrossMapLRN(3, 1e-3, 0.75, 1.0).setName("lrn")(cat)
+    add = L.CAddTable().setName("sum")([lrn, p1])
+    fl = L.View(8 * 4 * 4).setName("flat")(add)
+    fc = L.Linear(128, 5).setName("fc")(fl)
+    sm = L.SoftMax().setName("prob")(fc)
+    g = L.Model([inp], [sm])
+    g.node("bn1").element._buffers["runningMean"].uniform_(-0.5, 0.5)
+    g.node("bn1").element._buffers["runningVar"].uniform_(0.5, 1.5)
+    return g.evaluate()
+
+
+def test_caffe_export_import_roundtrip(tmp_path):
+    from bigdl_b200.interop.caffe import CaffeLoader
+
+    g = _branchy_model()
+    x = torch.randn(2, 3, 8, 8)
+    ref = g.forward(x).clone()
+    proto, model = str(tmp_path / "net.prototxt"), str(tmp_path / "net.caffemodel")
+    g.saveCaffe(proto, model)
+    txt = open(proto).read()
+    assert 'type: "Convolution"' in txt and 'type: "BatchNorm"' in txt and 'type: "Scale"' in txt and "blobs" not in txt
+    g2, crit = CaffeLoader.loadCaffe(proto, model)
+    assert crit is None
+    out = g2.evaluate().forward(x)
+    assert torch.allclose(out, ref, atol=1e-5)
+    # copy-by-name into a fresh model of the same structure
+    fresh = _branchy_model()
+    for m in fresh.all_modules():
+        for p in m._parameters.values():
+            p.data.zero_()
+    L.Module.loadCaffe(fresh, proto, model, matchAll=False)
+    assert torch.equal(fresh.node("fc").element.weight, g.node("fc").element.weight)
+    extra = L.Sequential().add(L.Linear(3, 3).setName("not_in_caffe"))
+    with pytest.raises(ValueError, match="cannot map"):
+        L.Module.loadCaffe(extra, proto, model, matchAll=True)
+
+
+def test_caffe_prototxt_semantics(tmp_path):
+    """Hand-written prototxt: V2 syntax, in-place ReLU, ceil-mode pooling, loss layer → criterion."""
+    from bigdl_b200.interop import caffe_pb as P
+    from bigdl_b200.interop.caffe import CaffeLoader
+
+    proto = tmp_path / "n.prototxt"
+    proto.write_text('''
+name: "tiny"
+input: "data"
+input_dim: 1 input_dim: 2 input_dim: 7 input_dim: 7
+layer { name: "conv" type: "Convolution" bottom: "data" top: "conv"
+        convolution_param { num_output: 3 kernel_size: 3 stride: 2 } }
+layer { name: "relu" type: "ReLU" bottom: "conv" top: "conv" }
+layer { name: "pool" type: "Pooling" bottom: "conv" top: "pool" pooling_param { pool: MAX kernel_size: 2 stride: 2 } }
+layer { name: "ip" type: "InnerProduct" bottom: "pool" top: "ip" inner_product_param { num_output: 4 } }
+layer { name: "acc" type: "Accuracy" bottom: "ip" bottom: "label" top: "acc" include { phase: TEST } }
+layer { name: "loss" type: "SoftmaxWithLoss" bottom: "ip" bottom: "label" top: "loss" }
+''')
+    net = P.NetParameter()
+    rs = np.random.RandomState(0)
+    for name, shapes in (("conv", [(3, 2, 3, 3), (3,)]), ("ip", [(4, 12), (4,)])):
+        l = net.layer.add()
+        l.name = name
+        for s in shapes:
+            b = l.blobs.add()
+            b.shape.dim.extend(s)
+            b.data.extend(rs.randn(*s).astype(np.float32).reshape(-1).tolist())
+    model = tmp_path / "n.caffemodel"
+    model.write_bytes(net.SerializeToString())
+    g, crit = CaffeLoader.loadCaffe(str(proto), str(model))
+    assert type(crit).__name__ == "ClassNLLCriterion"
+    x = torch.randn(2, 2, 7, 7)
+    y = g.evaluate().forward(x)
+    # conv 7->3 (stride 2), pool ceil((3-2)/2)+1 = 2 → 3*2*2 = 12 features
+    assert tuple(y.shape) == (2, 4) and torch.allclose(y.sum(1), torch.ones(2), atol=1e-5)
+    w = torch.tensor(np.asarray(net.layer[0].blobs[0].data, dtype=np.float32).reshape(3, 2, 3, 3))
+    b = torch.tensor(np.asarray(net.layer[0].blobs[1].data, dtype=np.float32))
+    h = torch.nn.functional.max_pool2d(torch.relu(torch.nn.functional.conv2d(x, w, b, 2)), 2, 2, ceil_mode=True)
+    w2 = torch.tensor(np.asarray(net.layer[1].blobs[0].data, dtype=np.float32).reshape(4, 12))
+    b2 = torch.tensor(np.asarray(net.layer[1].blobs[1].data, dtype=np.float32))
+    assert torch.allclose(y, torch.softmax(h.reshape(2, -1) @ w2.t() + b2, 1), atol=1e-5)

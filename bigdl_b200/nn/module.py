@@ -33,6 +33,8 @@ def _as_activity(x, device=None):
     if isinstance(x, torch.Tensor):
         return x if device is None or x.device == device else x.to(device)
     if isinstance(x, np.ndarray):
+        if x.dtype == object or x.dtype.kind in "US":
+            return x                       # string / object columns (feature-column ops) stay numpy
         t = torch.from_numpy(np.ascontiguousarray(x))
         if t.dtype == torch.float64:
             t = t.float()
@@ -44,9 +46,7 @@ def _as_activity(x, device=None):
     if isinstance(x, (int, float)):
         t = torch.tensor(float(x))
         return t if device is None else t.to(device)
-    if x is None:
-        return None
-    raise TypeError(f"unsupported activity type {type(x)}")
+    return x        # None, strings, sparse tensors and other opaque activities pass through
 
 
 def _detach(x):
@@ -428,8 +428,11 @@ class Module:
     def forward(self, input):
         """Run the layer; returns the output detached from the autograd graph (numpy in → numpy out)."""
         t0 = time.perf_counter_ns()
-        want_numpy = isinstance(input, np.ndarray) or (
-            isinstance(input, (list, tuple)) and len(input) > 0 and all(isinstance(v, np.ndarray) for v in input))
+        def _num(v):
+            return isinstance(v, np.ndarray) and v.dtype != object and v.dtype.kind not in "US"
+
+        want_numpy = _num(input) or (
+            isinstance(input, (list, tuple)) and len(input) > 0 and all(_num(v) for v in input))
         x = _as_activity(input, self.device() if self.torch_parameters() else None)
 
         def leaf(t):

@@ -17,7 +17,11 @@ class SparseTensor:
         val = torch.as_tensor(np.asarray(values) if not isinstance(values, torch.Tensor) else values)
         if val.dtype == torch.float64:
             val = val.float()             # the reference's default numeric type is Float
-        self.sp = torch.sparse_coo_tensor(idx, val, tuple(shape), check_invariants=False).coalesce()
+        import warnings
+
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            self.sp = torch.sparse_coo_tensor(idx, val, tuple(shape), check_invariants=False).coalesce()
 
     @staticmethod
     def from_dense(t) -> "SparseTensor":

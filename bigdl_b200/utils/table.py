@@ -168,7 +168,11 @@ def map_activity(fn, x):
         return fn(x)
     if x is None:
         return None
-    return Table(*[map_activity(fn, v) for v in (x.to_list() if isinstance(x, Table) else x)])
+    if isinstance(x, Table):
+        return Table(*[map_activity(fn, v) for v in x.to_list()])
+    if isinstance(x, (list, tuple)):
+        return Table(*[map_activity(fn, v) for v in x])
+    return x            # opaque leaf (string column, sparse tensor, …) travels unchanged
 
 
 def unflatten_like(template, flat: Iterable[Any]):

@@ -169,3 +169,87 @@ layer { name: "loss" type: "SoftmaxWithLoss" bottom: "ip" bottom: "label" top: "
     w2 = torch.tensor(np.asarray(net.layer[1].blobs[0].data, dtype=np.float32).reshape(4, 12))
     b2 = torch.tensor(np.asarray(net.layer[1].blobs[1].data, dtype=np.float32))
     assert torch.allclose(y, torch.softmax(h.reshape(2, -1) @ w2.t() + b2, 1), atol=1e-5)
+
+
+def test_tensorflow_export_import_roundtrip(tmp_path):
+    from bigdl_b200.interop.tensorflow import load_tf, save_tf, SUPPORTED_OPS
+
+    assert len(SUPPORTED_OPS) > 120
+    torch.manual_seed(2)
+    m = (L.Sequential()
+         .add(L.SpatialConvolution(3, 6, 3, 3, 1, 1, 1, 1).setName("conv1"))
+         .add(L.SpatialBatchNormalization(6).setName("bn"))
+         .add(L.ReLU().setName("relu"))
+         .add(L.SpatialMaxPooling(2, 2, 2, 2).setName("pool"))
+         .add(L.SpatialConvolution(6, 4, 3, 3, 2, 2, -1, -1).setName("conv_same"))
+         .add(L.Tanh().setName("tanh"))
+         .add(L.Reshape([4 * 2 * 2]).setName("flat"))
+         .add(L.Linear(16, 5).setName("fc"))
+         .add(L.SoftMax().setName("prob")))
+    m.modules[1]._buffers["runningMean"].uniform_(-0.3, 0.3)
+    m.modules[1]._buffers["runningVar"].uniform_(0.5, 1.5)
+    m.evaluate()
+    x = torch.randn(2, 3, 8, 8)
+    ref = m.forward(x).clone()
+    p = str(tmp_path / "model.pb")
+    outs = m.saveTF([("input", [None, 3, 8, 8])], p)
+    g = load_tf(p, ["input"], ["prob"])
+    y = g.evaluate().forward(x.permute(0, 2, 3, 1).contiguous())         # the exported graph is NHWC
+    assert torch.allclose(y, ref, atol=1e-5)
+    # weight-slot constants came back as trainable variables → the imported graph can be fine-tuned
+    w, gflat = g.getParameters()
+    n_params = sum(p_.numel() for _, _, p_ in g.leaf_parameters())
+    assert n_params == sum(p_.numel() for p_ in [m.modules[0].weight, m.modules[0].bias, m.modules[4].weight,
+                                                 m.modules[4].bias, m.modules[7].weight, m.modules[7].bias]) + 12
+    g.training()
+    out = g.forward(x.permute(0, 2, 3, 1).contiguous())
+    g.backward(x.permute(0, 2, 3, 1).contiguous(), torch.randn_like(out))
+    assert float(gflat.abs().sum()) > 0
+
+
+def test_tensorflow_graphdef_with_control_flow_and_ops():
+    """Hand-built GraphDef: out = cond(pred, x*2, x+1) then reduce/concat/strided-slice ops."""
+    from bigdl_b200.interop import tf_pb as P
+    from bigdl_b200.interop.tensorflow import load_tf
+
+    gd = P.GraphDef()
+
+    def node(op, name, inputs=(), **attrs):
+        n = gd.node.add()
+        n.op, n.name = op, name
+        n.input.extend(inputs)
+        for k, v in attrs.items():
+            if isinstance(v, np.ndarray):
+                n.attr[k].tensor.CopyFrom(P.numpy_to_tensor(v))
+            elif isinstance(v, bool):
+                n.attr[k].b = v
+            elif isinstance(v, int):
+                n.attr[k].i = v
+        return n
+
+    node("Placeholder", "x")
+    node("Placeholder", "pred")
+    node("Switch", "sw", ["x", "pred"])
+    node("Const", "two", value=np.array(2.0, np.float32))
+    node("Const", "one", value=np.array(1.0, np.float32))
+    node("Mul", "t", ["sw:1", "two"])
+    node("Add", "f", ["sw", "one"])
+    node("Merge", "m", ["f", "t"])
+    node("Const", "axis", value=np.array([1], np.int32))
+    node("Sum", "s", ["m", "axis"], keep_dims=True)
+    node("Const", "cat_axis", value=np.array(1, np.int32))
+    node("ConcatV2", "cat", ["m", "s", "cat_axis"])
+    node("Const", "b", value=np.array([0, 1], np.int32))
+    node("Const", "e", value=np.array([0, 3], np.int32))
+    node("Const", "st", value=np.array([1, 1], np.int32))
+    node("StridedSlice", "out", ["cat", "b", "e", "st"], begin_mask=1, end_mask=1)
+    g = load_tf(gd.SerializeToString(), ["x", "pred"], ["out"])
+    assert type(g).__name__ == "DynamicGraph"
+    x = torch.tensor([[1.0, 2.0], [3.0, 4.0]])
+    assert g.forward([x, torch.tensor(True)]).tolist() == [[4.0, 6.0], [8.0, 14.0]]
+    assert g.forward([x, torch.tensor(False)]).tolist() == [[3.0, 5.0], [5.0, 9.0]]
+    with pytest.raises(ValueError, match="unsupported TensorFlow op"):
+        bad = P.GraphDef()
+        bad.node.add(op="Placeholder", name="x")
+        bad.node.add(op="SomeExoticOp", name="y", input=["x"])
+        load_tf(bad.SerializeToString(), ["x"], ["y"])

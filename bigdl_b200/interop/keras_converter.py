@@ -1,0 +1,255 @@
+"""Keras-1.2.2 model import (P/keras/converter.py:1-1759: ``DefinitionLoader`` builds a model from the JSON definition,
+``WeightLoader`` copies HDF5 weights, layer by layer, converting Keras' weight layouts).
+
+``load_keras(json_path, hdf5_path)`` mirrors ``Model.load_keras``. The definition side has no dependencies. HDF5 needs
+``h5py``, which this image does not ship, so ``WeightLoader.load_weights_from_hdf5`` raises a clear error without it;
+``load_weights_from_arrays`` takes {layer name: [arrays]} (e.g. from ``np.load`` of an exported ``.npz``) and applies
+the same layout conversions."""
+from __future__ import annotations
+
+import json
+
+import numpy as np
+import torch
+
+from ..nn import keras as K
+
+
+def _shape(cfg):
+    bis = cfg.get("batch_input_shape")
+    return tuple(bis[1:]) if bis else None
+
+
+def _common(cfg):
+    kw = {}
+    s = _shape(cfg)
+    if s is not None:
+        kw["input_shape"] = s
+    if cfg.get("name"):
+        kw["name"] = cfg["name"]
+    return kw
+
+
+def _conv_common(cfg):
+    return dict(init=cfg.get("init", "glorot_uniform"), activation=_act(cfg), border_mode=cfg.get("border_mode", "valid"),
+                bias=cfg.get("bias", True))
+
+
+def _act(cfg):
+    a = cfg.get("activation")
+    return None if a in (None, "linear") else a
+
+
+_BUILDERS = {
+    "Dense": lambda c: K.Dense(c["output_dim"], init=c.get("init", "glorot_uniform"), activation=_act(c),
+                               bias=c.get("bias", True), **_common(c)),
+    "Activation": lambda c: K.Activation(c["activation"], **_common(c)),
+    "Dropout": lambda c: K.Dropout(c["p"], **_common(c)),
+    "Flatten": lambda c: K.Flatten(**_common(c)),
+    "Reshape": lambda c: K.Reshape(c["target_shape"], **_common(c)),
+    "Permute": lambda c: K.Permute(c["dims"], **_common(c)),
+    "RepeatVector": lambda c: K.RepeatVector(c["n"], **_common(c)),
+    "Masking": lambda c: K.Masking(c.get("mask_value", 0.0), **_common(c)),
+    "Highway": lambda c: K.Highway(activation=_act(c), bias=c.get("bias", True), **_common(c)),
+    "MaxoutDense": lambda c: K.MaxoutDense(c["output_dim"], c.get("nb_feature", 4), bias=c.get("bias", True), **_common(c)),
+    "Embedding": lambda c: K.Embedding(c["input_dim"], c["output_dim"], init=c.get("init", "uniform"),
+                                       **({"input_shape": (c["input_length"],)} if c.get("input_length") else {}),
+                                       **({"name": c["name"]} if c.get("name") else {})),
+    "BatchNormalization": lambda c: K.BatchNormalization(c.get("epsilon", 1e-3), c.get("mode", 0), c.get("axis", 1),
+                                                         c.get("momentum", 0.99), **_common(c)),
+    "Convolution1D": lambda c: K.Convolution1D(c["nb_filter"], c["filter_length"], subsample_length=c.get("subsample_length", 1),
+                                               **_conv_common(c), **_common(c)),
+    "Convolution2D": lambda c: K.Convolution2D(c["nb_filter"], c["nb_row"], c["nb_col"], subsample=tuple(c.get("subsample", (1, 1))),
+                                               dim_ordering=c.get("dim_ordering", "th"), **_conv_common(c), **_common(c)),
+    "Convolution3D": lambda c: K.Convolution3D(c["nb_filter"], c["kernel_dim1"], c["kernel_dim2"], c["kernel_dim3"],
+                                               subsample=tuple(c.get("subsample", (1, 1, 1))), **_conv_common(c), **_common(c)),
+    "AtrousConvolution2D": lambda c: K.AtrousConvolution2D(c["nb_filter"], c["nb_row"], c["nb_col"], activation=_act(c),
+                                                           subsample=tuple(c.get("subsample", (1, 1))),
+                                                           atrous_rate=tuple(c.get("atrous_rate", (1, 1))), **_common(c)),
+    "Deconvolution2D": lambda c: K.Deconvolution2D(c["nb_filter"], c["nb_row"], c["nb_col"], c.get("output_shape"),
+                                                   activation=_act(c), subsample=tuple(c.get("subsample", (1, 1))),
+                                                   bias=c.get("bias", True), **_common(c)),
+    "SeparableConvolution2D": lambda c: K.SeparableConvolution2D(c["nb_filter"], c["nb_row"], c["nb_col"], activation=_act(c),
+                                                                 border_mode=c.get("border_mode", "valid"),
+                                                                 subsample=tuple(c.get("subsample", (1, 1))),
+                                                                 depth_multiplier=c.get("depth_multiplier", 1),
+                                                                 dim_ordering=c.get("dim_ordering", "th"), **_common(c)),
+    "MaxPooling1D": lambda c: K.MaxPooling1D(c.get("pool_length", 2), c.get("stride"), c.get("border_mode", "valid"), **_common(c)),
+    "AveragePooling1D": lambda c: K.AveragePooling1D(c.get("pool_length", 2), c.get("stride"), c.get("border_mode", "valid"), **_common(c)),
+    "MaxPooling2D": lambda c: K.MaxPooling2D(tuple(c.get("pool_size", (2, 2))), c.get("strides"), c.get("border_mode", "valid"),
+                                             c.get("dim_ordering", "th"), **_common(c)),
+    "AveragePooling2D": lambda c: K.AveragePooling2D(tuple(c.get("pool_size", (2, 2))), c.get("strides"),
+                                                     c.get("border_mode", "valid"), c.get("dim_ordering", "th"), **_common(c)),
+    "MaxPooling3D": lambda c: K.MaxPooling3D(tuple(c.get("pool_size", (2, 2, 2))), c.get("strides"), **_common(c)),
+    "AveragePooling3D": lambda c: K.AveragePooling3D(tuple(c.get("pool_size", (2, 2, 2))), c.get("strides"), **_common(c)),
+    "GlobalMaxPooling1D": lambda c: K.GlobalMaxPooling1D(**_common(c)),
+    "GlobalAveragePooling1D": lambda c: K.GlobalAveragePooling1D(**_common(c)),
+    "GlobalMaxPooling2D": lambda c: K.GlobalMaxPooling2D(c.get("dim_ordering", "th"), **_common(c)),
+    "GlobalAveragePooling2D": lambda c: K.GlobalAveragePooling2D(c.get("dim_ordering", "th"), **_common(c)),
+    "ZeroPadding1D": lambda c: K.ZeroPadding1D(c.get("padding", 1), **_common(c)),
+    "ZeroPadding2D": lambda c: K.ZeroPadding2D(tuple(c.get("padding", (1, 1))), c.get("dim_ordering", "th"), **_common(c)),
+    "Cropping1D": lambda c: K.Cropping1D(tuple(c.get("cropping", (1, 1))), **_common(c)),
+    "Cropping2D": lambda c: K.Cropping2D(c.get("cropping", ((0, 0), (0, 0))), c.get("dim_ordering", "th"), **_common(c)),
+    "UpSampling1D": lambda c: K.UpSampling1D(c.get("length", 2), **_common(c)),
+    "UpSampling2D": lambda c: K.UpSampling2D(tuple(c.get("size", (2, 2))), c.get("dim_ordering", "th"), **_common(c)),
+    "UpSampling3D": lambda c: K.UpSampling3D(tuple(c.get("size", (2, 2, 2))), **_common(c)),
+    "LeakyReLU": lambda c: K.LeakyReLU(c.get("alpha", 0.3), **_common(c)),
+    "ELU": lambda c: K.ELU(c.get("alpha", 1.0), **_common(c)),
+    "ThresholdedReLU": lambda c: K.ThresholdedReLU(c.get("theta", 1.0), **_common(c)),
+    "GaussianNoise": lambda c: K.GaussianNoise(c["sigma"], **_common(c)),
+    "GaussianDropout": lambda c: K.GaussianDropout(c["p"], **_common(c)),
+    "SpatialDropout1D": lambda c: K.SpatialDropout1D(c.get("p", 0.5), **_common(c)),
+    "SpatialDropout2D": lambda c: K.SpatialDropout2D(c.get("p", 0.5), c.get("dim_ordering", "th"), **_common(c)),
+    "SimpleRNN": lambda c: K.SimpleRNN(c["output_dim"], c.get("activation", "tanh"), c.get("return_sequences", False),
+                                       c.get("go_backwards", False), **_common(c)),
+    "LSTM": lambda c: K.LSTM(c["output_dim"], c.get("activation", "tanh"), c.get("inner_activation", "hard_sigmoid"),
+                             c.get("return_sequences", False), c.get("go_backwards", False), **_common(c)),
+    "GRU": lambda c: K.GRU(c["output_dim"], c.get("activation", "tanh"), c.get("inner_activation", "hard_sigmoid"),
+                           c.get("return_sequences", False), c.get("go_backwards", False), **_common(c)),
+}
+
+
+class DefinitionLoader:
+    @staticmethod
+    def _layer(spec):
+        cls, cfg = spec["class_name"], spec["config"]
+        if cls == "TimeDistributed":
+            return K.TimeDistributed(DefinitionLoader._layer(cfg["layer"]), **_common(cfg))
+        if cls == "Bidirectional":
+            return K.Bidirectional(DefinitionLoader._layer(cfg["layer"]), cfg.get("merge_mode", "concat"), **_common(cfg))
+        if cls == "InputLayer":
+            return K.InputLayer(**_common(cfg))
+        if cls in ("Sequential", "Model"):
+            return DefinitionLoader.from_config(spec)
+        if cls not in _BUILDERS:
+            raise ValueError(f"Unsupported keras layer: {cls}")
+        return _BUILDERS[cls](cfg)
+
+    @staticmethod
+    def from_config(model_spec):
+        cls = model_spec["class_name"]
+        if cls == "Sequential":
+            m = K.Sequential()
+            for spec in model_spec["config"]:
+                m.add(DefinitionLoader._layer(spec))
+            return m
+        if cls == "Model":
+            cfg = model_spec["config"]
+            nodes = {}
+            for spec in cfg["layers"]:
+                name = spec["name"]
+                if spec["class_name"] == "InputLayer":
+                    nodes[name] = K.Input(shape=_shape(spec["config"]), name=name)
+                    continue
+                inbound = [nodes[i[0]] for i in spec["inbound_nodes"][0]]
+                if spec["class_name"] == "Merge":
+                    c = spec["config"]
+                    layer = K.Merge(mode=c.get("mode", "sum"), concat_axis=c.get("concat_axis", -1), name=name)
+                    nodes[name] = layer(inbound)
+                else:
+                    layer = DefinitionLoader._layer(spec)
+                    nodes[name] = layer(inbound if len(inbound) > 1 else inbound[0])
+            ins = [nodes[i[0]] for i in cfg["input_layers"]]
+            outs = [nodes[o[0]] for o in cfg["output_layers"]]
+            return K.Model(ins if len(ins) > 1 else ins[0], outs if len(outs) > 1 else outs[0])
+        raise ValueError(f"Unsupported keras model type: {cls}")
+
+    @staticmethod
+    def from_json_str(s: str):
+        return DefinitionLoader.from_config(json.loads(s))
+
+    @staticmethod
+    def from_json_path(path: str):
+        with open(path) as f:
+            return DefinitionLoader.from_json_str(f.read())
+
+
+def _find_layer(model, name):
+    for m in model.all_modules():
+        if m.hasName() and m.getName() == name:
+            return m
+    return None
+
+
+class WeightLoader:
+    """Keras layouts → framework layouts: Dense W [in,out] → [out,in]; Convolution2D th W [out,in,kh,kw] as is, tf W
+    [kh,kw,in,out] → permuted; BatchNormalization [gamma, beta, mean, std-or-var]; Embedding [vocab, dim]."""
+
+    @staticmethod
+    def _apply(layer, arrays):
+        params = [p for _, _, p in layer.leaf_parameters()]
+        arrays = [np.asarray(a, dtype=np.float32) for a in arrays]
+        cls = type(layer).__name__
+        with torch.no_grad():
+            if cls == "Dense":
+                params[0].copy_(torch.from_numpy(arrays[0].T.copy()))
+                if len(params) > 1 and len(arrays) > 1:
+                    params[1].copy_(torch.from_numpy(arrays[1]))
+            elif cls == "Convolution2D":
+                w = arrays[0]
+                if w.shape != tuple(params[0].shape):
+                    w = w.transpose(3, 2, 0, 1)
+                params[0].copy_(torch.from_numpy(np.ascontiguousarray(w)))
+                if len(params) > 1 and len(arrays) > 1:
+                    params[1].copy_(torch.from_numpy(arrays[1]))
+            elif cls == "BatchNormalization":
+                params[0].copy_(torch.from_numpy(arrays[0]))
+                params[1].copy_(torch.from_numpy(arrays[1]))
+                bn = [m for m in layer.all_modules() if "runningMean" in m._buffers][0]
+                bn._buffers["runningMean"].copy_(torch.from_numpy(arrays[2]))
+                bn._buffers["runningVar"].copy_(torch.from_numpy(arrays[3]))
+            elif cls == "Embedding":
+                params[0].copy_(torch.from_numpy(arrays[0]))
+            else:
+                if len(arrays) != len(params):
+                    raise ValueError(f"{cls} {layer.getName()}: expected {len(params)} weight arrays, got {len(arrays)}")
+                for p, a in zip(params, arrays):
+                    if a.size != p.numel():
+                        raise ValueError(f"{cls} {layer.getName()}: weight size mismatch {a.shape} vs {tuple(p.shape)}")
+                    p.copy_(torch.from_numpy(a.reshape(p.shape) if a.shape == tuple(p.shape) else a.T.reshape(p.shape)))
+        for m in layer.all_modules():
+            m._mark_weights_dirty()
+
+    @staticmethod
+    def load_weights_from_arrays(model, weights: dict, by_name: bool = False):
+        for name, arrays in weights.items():
+            layer = _find_layer(model, name)
+            if layer is None:
+                if by_name:
+                    continue
+                raise ValueError(f"layer {name} not found in the model")
+            WeightLoader._apply(layer, arrays)
+        return model
+
+    @staticmethod
+    def load_weights_from_hdf5(model, hdf5_path: str, by_name: bool = False):
+        try:
+            import h5py
+        except ImportError as e:
+            raise ImportError("reading Keras HDF5 weights needs h5py, which is not installed in this environment; "
+                              "export the weights to .npz and use load_weights_from_arrays") from e
+        weights = {}
+        with h5py.File(hdf5_path, "r") as f:
+            g = f["model_weights"] if "model_weights" in f else f
+            for lname in [n.decode() if isinstance(n, bytes) else n for n in g.attrs["layer_names"]]:
+                names = [n.decode() if isinstance(n, bytes) else n for n in g[lname].attrs["weight_names"]]
+                if names:
+                    weights[lname] = [np.asarray(g[lname][n]) for n in names]
+        return WeightLoader.load_weights_from_arrays(model, weights, by_name)
+
+
+def load_keras(json_path=None, hdf5_path=None, by_name=False):
+    if json_path is None:
+        raise ValueError("a model definition (json) is required: HDF5-only loading needs h5py")
+    model = DefinitionLoader.from_json_path(json_path)
+    if hdf5_path:
+        if hdf5_path.endswith(".npz"):
+            data = np.load(hdf5_path)
+            grouped: dict = {}
+            for k in data.files:
+                lname, _, idx = k.rpartition("/")
+                grouped.setdefault(lname, []).append((int(idx), data[k]))
+            WeightLoader.load_weights_from_arrays(model, {k: [a for _, a in sorted(v)] for k, v in grouped.items()}, by_name)
+        else:
+            WeightLoader.load_weights_from_hdf5(model, hdf5_path, by_name)
+    return model

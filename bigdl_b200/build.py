@@ -89,7 +89,7 @@ def build_host(force: bool = False) -> Path:
     if not force and out.exists() and stamp.exists() and stamp.read_text() == digest:
         return out
     LIBDIR.mkdir(parents=True, exist_ok=True)
-    _run([CXX, *CXX_FLAGS, "-shared", "-o", str(out), *map(str, srcs)])
+    _run([CXX, *CXX_FLAGS, "-shared", "-Wl,-Bsymbolic", "-o", str(out), *map(str, srcs)])
     stamp.write_text(digest)
     return out
 

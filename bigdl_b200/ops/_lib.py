@@ -33,7 +33,9 @@ def _load(name: str):
                 _build.build_host()
         except Exception as e:  # pragma: no cover - build environment problems
             raise NativeError(f"{name} is missing and could not be built: {e}") from e
-    return ctypes.CDLL(str(path), mode=ctypes.RTLD_GLOBAL)
+    # The CUDA library is loaded globally (its symbols are looked up by name from other extensions); the host runtime
+    # stays local so its C++ runtime symbols cannot interpose on those of OpenCV / torch loaded later.
+    return ctypes.CDLL(str(path), mode=ctypes.RTLD_GLOBAL if name == "libbigdl_b200.so" else ctypes.RTLD_LOCAL)
 
 
 def cuda_lib():

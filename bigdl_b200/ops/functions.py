@@ -190,6 +190,7 @@ class ConvFn(Function):
         lib = _lib.cuda_lib()
         b32 = bias.detach() if bias is not None else None
         implicit = (not direct) and groups == 1 and C % 8 == 0 and C >= 16 and O % 8 == 0 and _IGEMM[0]
+        kept_cols = None
         if implicit:
             conv_igemm(0, xn, ldx, w2, y2, O, Ho, Wo, kh, kw, sh, sw, pt, pl, dh, dw, bias=b32, relu=relu)
         for g in range(groups if not implicit else 0):
@@ -202,12 +203,20 @@ class ConvFn(Function):
             if direct:
                 a = x2[:, g * Cg:(g + 1) * Cg]
             else:
-                a = workspace(M * Kp, x.device).view(M, Kp)
+                # The only convolutions left on this path are the RGB stems (C < 16) and grouped ones. The stem's patch
+                # matrix is identical in fprop and wgrad, so when a backward will follow it is kept (a dedicated
+                # buffer instead of the shared workspace) and the second 0.6 ms im2col pass is skipped.
+                keep = groups == 1 and ctx.needs_input_grad[1] and M * Kp * 2 <= (4 << 30)
+                a = (torch.empty(M * Kp, dtype=torch.bfloat16, device=x.device) if keep
+                     else workspace(M * Kp, x.device)).view(M, Kp)
                 xg = xn[..., g * Cg:(g + 1) * Cg]
                 _lib.check(lib.bdl_im2col_nhwc_bf16(xg.data_ptr(), a.data_ptr(), N, H, W, Cg, Ho, Wo, kh, kw, sh, sw,
                                                     pt, pl, dh, dw, ldx, Kp, _lib.stream_ptr()), "bdl_im2col_nhwc_bf16")
                 _lib.count_launch()
+                if keep:
+                    kept_cols = a
             gemm_bf16(a, wg, bias=bg, relu=relu, out=y2[:, g * Og:(g + 1) * Og])
+        ctx.kept_cols = kept_cols
         ctx.save_for_backward(xn, w4, y if relu else None)
         ctx.params = (weight, bias, geom, relu, scale_w, scale_b,
                       (N, H, W, C, Ho, Wo, O, K, Kp, direct, ldx, ldy, c_real, implicit), x.shape)
@@ -250,7 +259,7 @@ class ConvFn(Function):
         done_w = done_x = False
         if implicit:
             ldz = dz.stride(0)
-            if gw is not None and not padded_c and C % 64 == 0 and scale_w == 1.0 and gw2.stride(1) == 1:
+            if gw is not None and not padded_c and C % 8 == 0 and C >= 16 and scale_w == 1.0 and gw2.stride(1) == 1:
                 conv_igemm(2, xn, ldx, dz, gw2, O, Ho, Wo, kh, kw, sh, sw, pt, pl, dh, dw, accumulate=True)
                 done_w = True
             if need_dx and sh == 1 and sw == 1 and dh * (kh - 1) - pt >= 0 and dw * (kw - 1) - pl >= 0:
@@ -264,6 +273,8 @@ class ConvFn(Function):
             dzg = dz[:, g * Og:(g + 1) * Og]
             if direct:
                 a = x2[:, g * Cg:(g + 1) * Cg]
+            elif gw is not None and not done_w and ctx.kept_cols is not None:
+                a = ctx.kept_cols                      # patch matrix kept by forward
             elif gw is not None and not done_w:
                 a = workspace(M * Kp, dy.device).view(M, Kp)
                 xg = xn[..., g * Cg:(g + 1) * Cg]

@@ -87,14 +87,15 @@ struct GemmParams {
 // One 16-column chunk of one accumulator row: dequantise / bias / ReLU, then store as fp32 (plain or red.add), bf16 or
 // requantised e4m3. ``sb``/``ss`` point at this chunk's bias / scale columns in shared memory (16-byte aligned).
 template <bool kFp8>
-__device__ __forceinline__ void epilogue_store16(const GemmParams& p, const uint32_t* r, int row, int n0,
+__device__ __forceinline__ void epilogue_store16(const GemmParams& p, const uint32_t* r, int row, int n0, int nvalid,
                                                  const float* sb, const float* ss, bool has_bias, bool use_scale,
                                                  bool atomic) {
-  if (n0 >= p.N) return;
+  // n0 = first OUTPUT column of this chunk, nvalid = how many of its 16 columns exist (<= 0: nothing to store)
+  if (nvalid <= 0) return;
   float v[16];
 #pragma unroll
   for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
-  const bool full = (n0 + 16 <= p.N);
+  const bool full = nvalid >= 16;
   if (kFp8 && use_scale) {
 #pragma unroll
     for (int j = 0; j < 16; j += 4) {
@@ -130,7 +131,7 @@ __device__ __forceinline__ void epilogue_store16(const GemmParams& p, const uint
       *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
     } else {
       for (int j = 0; j < 16; ++j)
-        if (n0 + j < p.N) dst[j] = static_cast<uint8_t>((w[j >> 2] >> ((j & 3) * 8)) & 0xffu);
+        if (j < nvalid) dst[j] = static_cast<uint8_t>((w[j >> 2] >> ((j & 3) * 8)) & 0xffu);
     }
   } else if (p.out_fp32) {
     float* dst = reinterpret_cast<float*>(p.D) + static_cast<long long>(row) * p.ldd + n0;
@@ -144,7 +145,7 @@ __device__ __forceinline__ void epilogue_store16(const GemmParams& p, const uint
                        : "memory");
       } else {
         for (int j = 0; j < 16; ++j)
-          if (n0 + j < p.N) atomicAdd(dst + j, v[j]);
+          if (j < nvalid) atomicAdd(dst + j, v[j]);
       }
     } else if (al) {
 #pragma unroll
@@ -152,7 +153,7 @@ __device__ __forceinline__ void epilogue_store16(const GemmParams& p, const uint
         *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
     } else {
       for (int j = 0; j < 16; ++j)
-        if (n0 + j < p.N) dst[j] = v[j];
+        if (j < nvalid) dst[j] = v[j];
     }
   } else {
     __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.D) + static_cast<long long>(row) * p.ldd + n0;
@@ -171,7 +172,7 @@ __device__ __forceinline__ void epilogue_store16(const GemmParams& p, const uint
       *reinterpret_cast<uint4*>(dst + 8) = q1;
     } else {
       for (int j = 0; j < 16; ++j)
-        if (n0 + j < p.N) dst[j] = __float2bfloat16_rn(v[j]);
+        if (j < nvalid) dst[j] = __float2bfloat16_rn(v[j]);
     }
   }
 }
@@ -413,6 +414,23 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       const int c_split = ((p.block_n / 16 + 1) / 2) * 16;
       const int c_begin = half ? c_split : 0;
       const int c_end = half ? p.block_n : c_split;
+      // Column mapping of a 16-column chunk starting at tile column cc. Plain GEMM / fprop / dgrad: output column =
+      // nbase + cc. wgrad (kConv == 2): the GEMM N axis is padded per filter tap to a multiple of 64 channels
+      // (tap * Cpad + ch) so that the im2col atoms tile it; the real dW column is tap * C + ch and channels >= C
+      // (zero-filled by TMA) are dropped here.
+#define EPI_STORE(REGS, CC)                                                                                       \
+  do {                                                                                                            \
+    int n_out = nbase + (CC), n_valid;                                                                            \
+    if (kConv == 2) {                                                                                             \
+      const uint32_t tap_ = p.fd_c.quot(static_cast<uint32_t>(n_out));                                            \
+      const int rem_ = n_out - static_cast<int>(tap_ * p.fd_c.div);                                               \
+      n_valid = (n_out < p.N) ? (p.cv_C - rem_) : 0;                                                              \
+      n_out = static_cast<int>(tap_) * p.cv_C + rem_;                                                             \
+    } else {                                                                                                      \
+      n_valid = p.N - n_out;                                                                                      \
+    }                                                                                                             \
+    epilogue_store16<kFp8>(p, REGS, row, n_out, n_valid, sb + (CC), ss + (CC), has_bias, use_scale, atomic);       \
+  } while (0)
       // Two register sets: the TMEM loads of the next 32 columns are in flight while this set is converted and stored.
       uint32_t a0[16], a1[16], b0[16], b1[16];
       int c = c_begin;
@@ -427,9 +445,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           if (c + 48 < c_end) tmem_ld_16(t_row + static_cast<uint32_t>(c + 48), b1);
         }
         if (row_ok) {
-          epilogue_store16<kFp8>(p, a0, row, nbase + c, sb + c, ss + c, has_bias, use_scale, atomic);
-          if (c + 16 < c_end)
-            epilogue_store16<kFp8>(p, a1, row, nbase + c + 16, sb + c + 16, ss + c + 16, has_bias, use_scale, atomic);
+          EPI_STORE(a0, c);
+          if (c + 16 < c_end) EPI_STORE(a1, c + 16);
         }
         c += 32;
         if (c >= c_end) break;
@@ -439,12 +456,12 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           if (c + 48 < c_end) tmem_ld_16(t_row + static_cast<uint32_t>(c + 48), a1);
         }
         if (row_ok) {
-          epilogue_store16<kFp8>(p, b0, row, nbase + c, sb + c, ss + c, has_bias, use_scale, atomic);
-          if (c + 16 < c_end)
-            epilogue_store16<kFp8>(p, b1, row, nbase + c + 16, sb + c + 16, ss + c + 16, has_bias, use_scale, atomic);
+          EPI_STORE(b0, c);
+          if (c + 16 < c_end) EPI_STORE(b1, c + 16);
         }
         c += 32;
       }
+#undef EPI_STORE
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
@@ -579,7 +596,7 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
   if ((reinterpret_cast<uintptr_t>(act) & 15u) || (reinterpret_cast<uintptr_t>(other) & 15u) || (ld_act % 8) ||
       (ld_other % 8))
     return bdl_fail("bdl_conv_igemm_bf16: operands must be 16-byte aligned with pitches that are multiples of 8");
-  if (mode == 2 && (C % 64)) return bdl_fail("bdl_conv_igemm_bf16: wgrad needs C % 64 == 0");
+  if (mode == 2 && (C % 8)) return bdl_fail("bdl_conv_igemm_bf16: wgrad needs C % 8 == 0");
   if (mode == 2 && !(flags & BDL_GEMM_ATOMIC_ADD)) return bdl_fail("bdl_conv_igemm_bf16: wgrad accumulates (ATOMIC_ADD)");
   const int num_sms = bdl_num_sms();
   const long long Mpix = static_cast<long long>(N) * Ho * Wo;
@@ -592,11 +609,13 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
   p.fd_wo.init(static_cast<uint32_t>(Wo));
   p.fd_cblocks.init(static_cast<uint32_t>(p.cv_cblocks));
   p.fd_kw.init(static_cast<uint32_t>(kw));
-  p.fd_c.init(static_cast<uint32_t>(C));
+  // wgrad pads every tap's channel range to whole 64-channel atoms on the GEMM N axis (see EPI_STORE in the kernel)
+  const int c_pad = p.cv_cblocks * 64;
+  p.fd_c.init(static_cast<uint32_t>(mode == 2 ? c_pad : C));
   int gm, gn;
   if (mode == 2) {
     gm = O;
-    gn = taps * C;
+    gn = taps * c_pad;
     p.K = static_cast<int>(Mpix);
     p.cv_num_kb = static_cast<int>((Mpix + 63) / 64);
   } else {

@@ -58,7 +58,14 @@ def test_igemm_dgrad(case):
     _close(dx.reshape(N, H, W, C).permute(0, 3, 1, 2), xr.grad, 3e-2, 5e-2)
 
 
-@pytest.mark.parametrize("case", [c for c in CASES if c[1] % 64 == 0])
+WGRAD_EXTRA = [
+    (2, 24, 9, 9, 48, 5, 5, 1, 1, 2, 2, 1, 1),        # C < 64: one partly-filled channel atom per tap
+    (2, 160, 7, 7, 224, 3, 3, 1, 1, 1, 1, 1, 1),      # C = 2.5 atoms, O not a multiple of 128
+    (2, 72, 8, 8, 40, 3, 3, 2, 2, 1, 1, 1, 1),        # C % 16 == 8: a 16-column chunk is only half valid
+]
+
+
+@pytest.mark.parametrize("case", CASES + WGRAD_EXTRA)
 def test_igemm_wgrad(case):
     from bigdl_b200.ops.gemm import conv_igemm
     N, C, H, W, O, kh, kw, sh, sw, ph, pw, dh, dw = case

@@ -165,10 +165,12 @@ class ConvFn(Function):
         c_real = C
         w4 = w16.permute(0, 2, 3, 1)                        # OHWI physical order
         if groups == 1 and C % 8 != 0 and C < 8:
-            # tiny channel counts (the RGB stem): pad to 8 channels so the 16-byte vector im2col path applies
-            xn = torch.nn.functional.pad(xn, (0, 8 - C))
-            w4 = torch.nn.functional.pad(w4, (0, 8 - C))
-            C, ldx = 8, 8
+            # tiny channel counts (the RGB stem): pad to 4 (or 8) channels so a vector im2col path applies; 4 keeps the
+            # patch matrix half the size of the 8-channel padding
+            cp = 4 if C <= 4 else 8
+            xn = torch.nn.functional.pad(xn, (0, cp - C))
+            w4 = torch.nn.functional.pad(w4, (0, cp - C))
+            C, ldx = cp, cp
         asym = (pt != pb) or (pl != pr)
         if asym:
             # TF-style SAME padding can be asymmetric: materialise the extra bottom/right rows once
@@ -250,7 +252,7 @@ class ConvFn(Function):
         x2 = rows2d(xn, ldx)
         w2 = w4.reshape(O, kh * kw * Cg)
         gw = _acc_grad(weight, scale_w)
-        padded_c = c_real != C and groups == 1 and C == 8 and c_real < 8
+        padded_c = c_real != C and groups == 1 and C in (4, 8) and c_real < C
         gw2 = None
         if gw is not None and not padded_c:
             gw2 = gw.permute(0, 2, 3, 1).reshape(O, kh * kw * Cg)
@@ -285,7 +287,7 @@ class ConvFn(Function):
                 if padded_c:
                     tmp = torch.zeros((O, Kp), device=dy.device)
                     gemm_bf16(dzg, a, a_mn=True, b_mn=True, out=tmp, accumulate=True)
-                    gw.permute(0, 2, 3, 1).add_(tmp.view(O, kh, kw, C)[..., :c_real], alpha=scale_w)
+                    gw.permute(0, 2, 3, 1).add_(tmp[:, :K].reshape(O, kh, kw, C)[..., :c_real], alpha=scale_w)
                 else:
                     tgt = gw2[g * Og:(g + 1) * Og]
                     if scale_w == 1.0 and Kp == K and tgt.stride(1) == 1:

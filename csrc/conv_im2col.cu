@@ -46,6 +46,37 @@ __global__ void im2col_nhwc_vec_kernel(const __nv_bfloat16* __restrict__ x, __nv
   }
 }
 
+// 4-channel pixels (the RGB stem padded to 4): 8-byte gathers; the thread with tap == taps zero-fills the K padding.
+__global__ void im2col_nhwc_vec4_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ col,
+                                        const ConvGeom g) {
+  const long long M = static_cast<long long>(g.N) * g.Ho * g.Wo;
+  const int taps = g.kh * g.kw;
+  const int K = taps * 4;
+  const int per_row = taps + (g.Kp > K ? 1 : 0);
+  const long long total = M * per_row;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const long long m = i / per_row;
+    const int tap = static_cast<int>(i - m * per_row);
+    if (tap == taps) {
+      for (int k = K; k < g.Kp; k += 4) *reinterpret_cast<uint2*>(col + m * g.Kp + k) = make_uint2(0, 0);
+      continue;
+    }
+    const int kx = tap % g.kw;
+    const int ky = tap / g.kw;
+    const int wo = static_cast<int>(m % g.Wo);
+    const long long t = m / g.Wo;
+    const int ho = static_cast<int>(t % g.Ho);
+    const int n = static_cast<int>(t / g.Ho);
+    const int hi = ho * g.sh - g.ph + ky * g.dh;
+    const int wi = wo * g.sw - g.pw + kx * g.dw;
+    uint2 v = make_uint2(0, 0);
+    if (hi >= 0 && hi < g.H && wi >= 0 && wi < g.W)
+      v = *reinterpret_cast<const uint2*>(x + ((static_cast<long long>(n) * g.H + hi) * g.W + wi) * g.ldx);
+    *reinterpret_cast<uint2*>(col + m * g.Kp + tap * 4) = v;
+  }
+}
+
 // scalar path (e.g. the 3-channel stem): one thread per column-matrix element, padding columns written as zero.
 __global__ void im2col_nhwc_scalar_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ col,
                                           const ConvGeom g) {
@@ -160,10 +191,15 @@ extern "C" int bdl_im2col_nhwc_bf16(const void* x, void* col, int N, int H, int 
   const long long M = static_cast<long long>(N) * Ho * Wo;
   const bool vec = (C % 8 == 0) && (ldx % 8 == 0) && (Kp == kh * kw * C) && !(reinterpret_cast<uintptr_t>(x) & 15u) &&
                    !(reinterpret_cast<uintptr_t>(col) & 15u);
+  const bool vec4 = (C == 4) && (ldx % 4 == 0) && (Kp % 4 == 0) && !(reinterpret_cast<uintptr_t>(x) & 7u) &&
+                    !(reinterpret_cast<uintptr_t>(col) & 7u);
   if (vec) {
     const long long total = M * kh * kw * (C / 8);
     im2col_nhwc_vec_kernel<<<grid_for(total), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x),
                                                             static_cast<__nv_bfloat16*>(col), g);
+  } else if (vec4) {
+    im2col_nhwc_vec4_kernel<<<grid_for(M * (kh * kw + 1)), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x),
+                                                                         static_cast<__nv_bfloat16*>(col), g);
   } else {
     im2col_nhwc_scalar_kernel<<<grid_for(M * Kp), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x),
                                                                 static_cast<__nv_bfloat16*>(col), g);

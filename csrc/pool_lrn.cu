@@ -101,16 +101,21 @@ __global__ void maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const u
     const int h = static_cast<int>(t % g.H);
     const int n = static_cast<int>(t / g.H);
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    for (int ky = 0; ky < g.kh; ++ky) {
-      const int hh = h + g.ph - ky;
-      if (hh < 0 || hh % g.sh) continue;
-      const int ho = hh / g.sh;
-      if (ho >= g.Ho) continue;
-      for (int kx = 0; kx < g.kw; ++kx) {
-        const int ww = w + g.pw - kx;
-        if (ww < 0 || ww % g.sw) continue;
-        const int wo = ww / g.sw;
-        if (wo >= g.Wo) continue;
+    // output windows covering (h, w): ho in [ceil((h+ph-kh+1)/sh), floor((h+ph)/sh)] — at most ceil(k/s)^2 of them,
+    // found with two divisions per axis instead of testing every tap
+    const int hp = h + g.ph, wp = w + g.pw;
+    int ho0 = hp - g.kh + 1;
+    ho0 = ho0 <= 0 ? 0 : (ho0 + g.sh - 1) / g.sh;
+    int ho1 = hp / g.sh;
+    if (ho1 >= g.Ho) ho1 = g.Ho - 1;
+    int wo0 = wp - g.kw + 1;
+    wo0 = wo0 <= 0 ? 0 : (wo0 + g.sw - 1) / g.sw;
+    int wo1 = wp / g.sw;
+    if (wo1 >= g.Wo) wo1 = g.Wo - 1;
+    for (int ho = ho0; ho <= ho1; ++ho) {
+      const int ky = hp - ho * g.sh;
+      for (int wo = wo0; wo <= wo1; ++wo) {
+        const int kx = wp - wo * g.sw;
         const long long opix = (static_cast<long long>(n) * g.Ho + ho) * g.Wo + wo;
         const uint2 pk = *reinterpret_cast<const uint2*>(idx + opix * g.C + cv * 8);
         float f[8];
@@ -230,13 +235,15 @@ __device__ __forceinline__ void lrn_load24(const __nv_bfloat16* row, int c0, int
   }
 }
 
-template <typename I>
+template <typename I, int kHalf>
 __global__ void lrn_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long pixels,
                                int C, long long ldx, long long ldy, int size, float alpha, float beta, float k) {
   const int cvec = C / 8;
   const I total = static_cast<I>(pixels) * cvec;
   const I stride = static_cast<I>(gridDim.x) * blockDim.x;
-  const int pre = (size - 1) / 2, post = size - 1 - pre;
+  // kHalf > 0: symmetric window of 2*kHalf+1 known at compile time (size 5 in Inception/AlexNet) — the predicated
+  // 17-tap loops below collapse to exactly the taps used
+  const int pre = kHalf ? kHalf : (size - 1) / 2, post = kHalf ? kHalf : size - 1 - pre;
   const float as = alpha / size;
   for (I i = static_cast<I>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
     const int cv = static_cast<int>(i % cvec);
@@ -260,17 +267,18 @@ __global__ void lrn_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat1
   }
 }
 
+// (kernel templates take <index type, kHalf>)
 // dx_c = dy_c * s_c^-beta - 2*alpha*beta/size * x_c * sum_{c' : c in window(c')} dy_c' * x_c' * s_c'^(-beta-1)
 // c is inside window(c') iff c - post <= c' <= c + pre; s_c' needs x over [c'-pre, c'+post], so the 24-wide
 // neighbourhood covers everything for windows up to 9 (pre, post <= 4).
-template <typename I>
+template <typename I, int kHalf>
 __global__ void lrn_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                                __nv_bfloat16* __restrict__ dx, long long pixels, int C, long long ldx, long long ldy,
                                long long lddx, int size, float alpha, float beta, float k) {
   const int cvec = C / 8;
   const I total = static_cast<I>(pixels) * cvec;
   const I stride = static_cast<I>(gridDim.x) * blockDim.x;
-  const int pre = (size - 1) / 2, post = size - 1 - pre;
+  const int pre = kHalf ? kHalf : (size - 1) / 2, post = kHalf ? kHalf : size - 1 - pre;
   const float as = alpha / size;
   for (I i = static_cast<I>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
     const int cv = static_cast<int>(i % cvec);
@@ -286,6 +294,11 @@ __global__ void lrn_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_b
     float ratio[16], pw[16];
 #pragma unroll
     for (int t = 0; t < 16; ++t) {
+      if (kHalf && (t < 4 - kHalf || t >= 12 + kHalf)) {   // never read by the cross sum below
+        ratio[t] = 0.f;
+        pw[t] = 0.f;
+        continue;
+      }
       const int cp = c0 - 4 + t;
       if (cp < 0 || cp >= C) {   // outside the tensor: contributes nothing (and k may be 0)
         ratio[t] = 0.f;
@@ -370,6 +383,21 @@ __global__ void lrn_bwd_wide_kernel(const __nv_bfloat16* __restrict__ x, const _
       KERNEL<unsigned int><<<grid_for(TOTAL), 256, 0, st_>>>(__VA_ARGS__);       \
     else                                                                         \
       KERNEL<long long><<<grid_for(TOTAL), 256, 0, st_>>>(__VA_ARGS__);          \
+  } while (0)
+
+#define BDL_LRN_DISPATCH(KERNEL, SIZE, TOTAL, ...)                                          \
+  do {                                                                                    \
+    const bool small_ = (TOTAL) < (1ll << 31) - (1ll << 24);                              \
+    if ((SIZE) == 5) {                                                                    \
+      if (small_) KERNEL<unsigned int, 2><<<grid_for(TOTAL), 256, 0, st_>>>(__VA_ARGS__); \
+      else KERNEL<long long, 2><<<grid_for(TOTAL), 256, 0, st_>>>(__VA_ARGS__);           \
+    } else if ((SIZE) == 3) {                                                             \
+      if (small_) KERNEL<unsigned int, 1><<<grid_for(TOTAL), 256, 0, st_>>>(__VA_ARGS__); \
+      else KERNEL<long long, 1><<<grid_for(TOTAL), 256, 0, st_>>>(__VA_ARGS__);           \
+    } else {                                                                              \
+      if (small_) KERNEL<unsigned int, 0><<<grid_for(TOTAL), 256, 0, st_>>>(__VA_ARGS__); \
+      else KERNEL<long long, 0><<<grid_for(TOTAL), 256, 0, st_>>>(__VA_ARGS__);           \
+    }                                                                                     \
   } while (0)
 
 static int grid_for(long long total) {
@@ -472,7 +500,7 @@ extern "C" int bdl_lrn_fwd_nhwc_bf16(const void* x, void* y, long long pixels, i
   if (size <= 9)
     {
     cudaStream_t st_ = static_cast<cudaStream_t>(stream);
-    BDL_IDX_DISPATCH(lrn_fwd_kernel, static_cast<long long>(pixels * (C / 8)), 
+    BDL_LRN_DISPATCH(lrn_fwd_kernel, size, static_cast<long long>(pixels * (C / 8)), 
         static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), pixels, C, ldx, ldy, size, alpha, beta,
         k);
   }
@@ -492,7 +520,7 @@ extern "C" int bdl_lrn_bwd_nhwc_bf16(const void* x, const void* dy, void* dx, lo
   if (size <= 9)
     {
     cudaStream_t st_ = static_cast<cudaStream_t>(stream);
-    BDL_IDX_DISPATCH(lrn_bwd_kernel, static_cast<long long>(pixels * (C / 8)), 
+    BDL_LRN_DISPATCH(lrn_bwd_kernel, size, static_cast<long long>(pixels * (C / 8)), 
         static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx),
         pixels, C, ldx, ldy, lddx, size, alpha, beta, k);
   }

@@ -51,5 +51,39 @@ def main():
               flush=True)
 
 
+def bn_main():
+    from bigdl_b200.ops import _lib
+
+    lib = _lib.cuda_lib()
+    dev = torch.device("cuda")
+    for M, C in [(200704, 64), (200704, 256), (50176, 128), (50176, 512), (12544, 256), (12544, 1024), (3136, 512),
+                 (3136, 2048)]:
+        n_copy = max(1, (200 << 20) // (M * C * 2) + 1)
+        xs = [torch.randn(M, C, device=dev).to(torch.bfloat16) for _ in range(n_copy)]
+        dys = [torch.randn(M, C, device=dev).to(torch.bfloat16) for _ in range(min(n_copy, 4))]
+        sums = torch.zeros(2 * C, device=dev)
+        mean, inv = torch.zeros(C, device=dev), torch.ones(C, device=dev)
+        k = [0]
+
+        def fwd():
+            i = k[0] % n_copy
+            k[0] += 1
+            _lib.check(lib.bdl_bn_stats(xs[i].data_ptr(), sums.data_ptr(), M, C, C, _lib.stream_ptr()), "bn_stats")
+
+        def bwd():
+            i = k[0] % n_copy
+            k[0] += 1
+            _lib.check(lib.bdl_bn_bwd_reduce(dys[i % len(dys)].data_ptr(), xs[i].data_ptr(), None, mean.data_ptr(),
+                                             inv.data_ptr(), sums.data_ptr(), M, C, C, C, 0, _lib.stream_ptr()), "bn_bwd")
+        for name, fn, passes in (("bn_stats", fwd, 1), ("bn_bwd_reduce", bwd, 2)):
+            us = timeit(fn)
+            print(json.dumps({"kernel": name, "M": M, "C": C, "us": round(us, 1),
+                              "GBps": round(M * C * 2 * passes / us / 1e3, 1), "bps": os.environ.get("BDL_BN_BPS", "default")}),
+                  flush=True)
+
+
 if __name__ == "__main__":
-    main()
+    if "--bn" in sys.argv:
+        bn_main()
+    else:
+        main()

@@ -9,6 +9,8 @@
 //   y = gamma * (x - mean) / sqrt(var_biased + eps) + beta
 //   running = (1 - momentum) * running + momentum * batch, with the UNBIASED batch variance for runningVar.
 // mkldnn twin: S/nn/mkldnn/SpatialBatchNormalization.scala (fused ReLU :44-83).
+#include <cstdlib>
+
 #include "bigdl_b200.h"
 #include "host_common.h"
 #include "ptx.cuh"
@@ -63,13 +65,13 @@ __global__ void bn_reduce_kernel(const __nv_bfloat16* __restrict__ a, const __nv
     if (tr < rif) {
       long long r = r0 + tr;
       if (kMode == 0) {
-        // forward statistics: 4 independent 16-byte loads in flight per thread
-        for (; r + 3ll * rif < r1; r += 4ll * rif) {
-          uint4 v[4];
+        // forward statistics: 8 independent 16-byte loads in flight per thread
+        for (; r + 7ll * rif < r1; r += 8ll * rif) {
+          uint4 v[8];
 #pragma unroll
-          for (int u = 0; u < 4; ++u) v[u] = *reinterpret_cast<const uint4*>(a + (r + u * rif) * lda + cv * 8);
+          for (int u = 0; u < 8; ++u) v[u] = *reinterpret_cast<const uint4*>(a + (r + u * rif) * lda + cv * 8);
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
+          for (int u = 0; u < 8; ++u) {
             const __nv_bfloat162* q = reinterpret_cast<const __nv_bfloat162*>(&v[u]);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
@@ -83,17 +85,17 @@ __global__ void bn_reduce_kernel(const __nv_bfloat16* __restrict__ a, const __nv
         }
       }
       if (kMode == 1) {
-        // backward sums: two rows (six 16-byte loads) in flight per thread
-        for (; r + 1ll * rif < r1; r += 2ll * rif) {
-          uint4 va[2], vx[2], vy[2];
+        // backward sums: four rows (up to twelve 16-byte loads) in flight per thread
+        for (; r + 3ll * rif < r1; r += 4ll * rif) {
+          uint4 va[4], vx[4], vy[4];
 #pragma unroll
-          for (int u = 0; u < 2; ++u) {
+          for (int u = 0; u < 4; ++u) {
             va[u] = *reinterpret_cast<const uint4*>(a + (r + u * rif) * lda + cv * 8);
             vx[u] = *reinterpret_cast<const uint4*>(x + (r + u * rif) * ldx + cv * 8);
             if (y) vy[u] = *reinterpret_cast<const uint4*>(y + (r + u * rif) * ldy + cv * 8);
           }
 #pragma unroll
-          for (int u = 0; u < 2; ++u) {
+          for (int u = 0; u < 4; ++u) {
             const __nv_bfloat162* qa = reinterpret_cast<const __nv_bfloat162*>(&va[u]);
             const __nv_bfloat162* qx = reinterpret_cast<const __nv_bfloat162*>(&vx[u]);
             const __nv_bfloat162* qy = reinterpret_cast<const __nv_bfloat162*>(&vy[u]);
@@ -150,15 +152,35 @@ __global__ void bn_reduce_kernel(const __nv_bfloat16* __restrict__ a, const __nv
     }
     __syncthreads();
     if (tr == 0) {
+      float t0[8], t1[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        float t0 = 0.f, t1 = 0.f;
+        float a0 = 0.f, a1 = 0.f;
         for (int t = 0; t < rif; ++t) {
-          t0 += red[(t * vcols + tc) * 16 + j];
-          t1 += red[(t * vcols + tc) * 16 + 8 + j];
+          a0 += red[(t * vcols + tc) * 16 + j];
+          a1 += red[(t * vcols + tc) * 16 + 8 + j];
         }
-        atomicAdd(out + cv * 8 + j, t0);
-        atomicAdd(out + C + cv * 8 + j, t1);
+        t0[j] = a0;
+        t1[j] = a1;
+      }
+      // four 16-byte reductions instead of sixteen scalar atomics: every block ends here on the same 2C addresses, and
+      // the L2 atomic transaction count (not the bytes streamed) was what bounded this kernel
+      float* d0 = out + cv * 8;
+      float* d1 = out + C + cv * 8;
+      if (((reinterpret_cast<uintptr_t>(d0) | reinterpret_cast<uintptr_t>(d1)) & 15u) == 0) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(d0 + 4 * h), "f"(t0[4 * h]),
+                       "f"(t0[4 * h + 1]), "f"(t0[4 * h + 2]), "f"(t0[4 * h + 3]) : "memory");
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(d1 + 4 * h), "f"(t1[4 * h]),
+                       "f"(t1[4 * h + 1]), "f"(t1[4 * h + 2]), "f"(t1[4 * h + 3]) : "memory");
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          atomicAdd(d0 + j, t0[j]);
+          atomicAdd(d1 + j, t1[j]);
+        }
       }
     }
   }
@@ -364,18 +386,31 @@ static void stream_geometry(long long M, int C, int* grid, int* rpb, size_t* sme
   *smem = 0;
 }
 
-static void reduce_geometry(long long M, int C, int* grid, int* rpb, size_t* smem) {
+// Reduction kernels end with 2*C red.add on the same addresses in every block, so the block count is kept at one or a
+// few per SM and memory-level parallelism comes from 8-12 independent loads in flight per thread.
+// (Sweep on B200, benchmarks/eltwise_bench.py --bn: backward is fastest with one block per SM everywhere; the forward
+// statistics want more blocks only for the largest activations.) BDL_BN_BPS / BDL_BN_THREADS override for tuning.
+static int bn_env(const char* name) {
+  const char* e = getenv(name);
+  return e ? atoi(e) : 0;
+}
+static void reduce_geometry(long long M, int C, int mode, int* grid, int* rpb, int* threads, size_t* smem) {
+  static const int bps_override = bn_env("BDL_BN_BPS");
+  static const int thr_override = bn_env("BDL_BN_THREADS");
   const int sms = bdl_num_sms();
   const int cvec = C / 8;
-  const int vcols = cvec < 256 ? cvec : 256;
-  const int rif = 256 / vcols;
-  // every block ends with 2*C atomics on the same addresses: keep the block count low for wide layers and let the
-  // unrolled loads (4 rows in flight per thread) provide the memory-level parallelism instead
-  long long blocks_target = static_cast<long long>(sms) * (C >= 1024 ? 1 : (C >= 256 ? 2 : 4));
+  const int nthr = thr_override > 0 ? thr_override : 256;   // the backward variant needs >128 registers: 256 threads max
+  const int vcols = cvec < nthr ? cvec : nthr;
+  const int rif = nthr / vcols;
+  const long long elems = M * C;
+  int bps = mode == 1 ? 1 : (elems >= (40ll << 20) ? 4 : (elems >= (8ll << 20) ? 2 : 1));
+  if (bps_override > 0) bps = bps_override;
+  const long long blocks_target = static_cast<long long>(sms) * bps;
   long long r = (M + blocks_target - 1) / blocks_target;
   if (r < 4ll * rif) r = 4ll * rif;
   *rpb = static_cast<int>(r);
   *grid = static_cast<int>((M + r - 1) / r);
+  *threads = nthr;
   *smem = static_cast<size_t>(rif) * vcols * 16 * sizeof(float);
 }
 
@@ -383,10 +418,10 @@ static void reduce_geometry(long long M, int C, int* grid, int* rpb, size_t* sme
 extern "C" int bdl_bn_stats(const void* x, float* sums, long long M, int C, long long ldx, void* stream) {
   if (bn_check("bdl_bn_stats: C and pitch must be multiples of 8, pointer 16-byte aligned", C, ldx, ldx, x, x))
     return BDL_ERR_INVALID;
-  int grid, rpb;
+  int grid, rpb, threads;
   size_t smem;
-  reduce_geometry(M, C, &grid, &rpb, &smem);
-  bn_reduce_kernel<0><<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
+  reduce_geometry(M, C, 0, &grid, &rpb, &threads, &smem);
+  bn_reduce_kernel<0><<<grid, threads, smem, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(x), nullptr, nullptr, nullptr, nullptr, sums, M, C, ldx, 0, 0, rpb);
   return bdl_check_launch("bn_reduce_kernel<0>");
 }
@@ -419,10 +454,10 @@ extern "C" int bdl_bn_bwd_reduce(const void* dy, const void* x, const void* y, c
   if (bn_check("bdl_bn_bwd_reduce: C and pitches must be multiples of 8, pointers 16-byte aligned", C, lddy, ldx, dy,
                x))
     return BDL_ERR_INVALID;
-  int grid, rpb;
+  int grid, rpb, threads;
   size_t smem;
-  reduce_geometry(M, C, &grid, &rpb, &smem);
-  bn_reduce_kernel<1><<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
+  reduce_geometry(M, C, 1, &grid, &rpb, &threads, &smem);
+  bn_reduce_kernel<1><<<grid, threads, smem, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
       static_cast<const __nv_bfloat16*>(y), mean, invstd, sums, M, C, lddy, ldx, ldy, rpb);
   return bdl_check_launch("bn_reduce_kernel<1>");

@@ -372,8 +372,12 @@ class View(Module):
     set_num_input_dims = setNumInputDims
 
     def updateOutput(self, input):
-        if -1 in self.sizes:
-            batch = (self.num_input_dims > 0 and input.dim() == self.num_input_dims + 1)
+        # View.scala batchSize(): with numInputDims set, one extra leading dim is the batch (even a batch of 1);
+        # otherwise the batch is inferred from the element count
+        if self.num_input_dims > 0 and input.dim() == self.num_input_dims + 1:
+            batch = True
+        elif -1 in self.sizes:
+            batch = False
         else:
             batch = input.numel() != self.num_elements
         if batch:

@@ -169,9 +169,14 @@ def map_activity(fn, x):
     if x is None:
         return None
     if isinstance(x, Table):
-        return Table(*[map_activity(fn, v) for v in x.to_list()])
+        out = Table()
+        for k, v in x.items():          # keeps non-positional keys ("bboxes", "masks", …)
+            out[k] = map_activity(fn, v)
+        return out
     if isinstance(x, (list, tuple)):
-        return Table(*[map_activity(fn, v) for v in x])
+        if all(isinstance(v, (torch.Tensor, Table)) for v in x):
+            return Table(*[map_activity(fn, v) for v in x])
+        return x
     return x            # opaque leaf (string column, sparse tensor, …) travels unchanged
 
 

@@ -272,3 +272,25 @@ def test_misc_layers_smoke():
     emb = torch.randn(1, 3, 5)
     trees = torch.tensor([[[2, 3, -1], [0, 0, 1], [4, 5, 0], [0, 0, 2], [0, 0, 3]]]).float()
     assert tree.forward(T(emb, trees)).shape == (1, 5, 4)
+
+
+def test_inception_v2_and_maskrcnn_models():
+    """Model-zoo additions: BN-Inception (S/models/inception/Inception_v2.scala) and Mask R-CNN inference
+    (S/models/maskrcnn/MaskRCNN.scala)."""
+    import torch
+
+    from bigdl_b200.models.inception_v2 import Inception_v2, Inception_v2_NoAuxClassifier
+    from bigdl_b200.models.maskrcnn import MaskRCNN, MaskRCNNParams
+    from bigdl_b200.utils.table import Table
+
+    m = Inception_v2_NoAuxClassifier(20).evaluate()
+    assert tuple(m.forward(torch.randn(1, 3, 224, 224)).shape) == (1, 20)
+    assert tuple(Inception_v2(7).evaluate().forward(torch.randn(1, 3, 224, 224)).shape) == (1, 21)
+    torch.manual_seed(0)
+    p = MaskRCNNParams(preNmsTopNTest=50, postNmsTopNTest=20, maxPerImage=5, boxScoreThresh=0.0)
+    det = MaskRCNN(64, 32, 5, p).evaluate()
+    out = det.forward(Table(torch.randn(1, 3, 128, 160), torch.tensor([[128.0, 160.0, 256.0, 320.0]])))
+    r = out[1]
+    n = r["bboxes"].shape[0]
+    assert 0 < n <= 5 and r["classes"].shape[0] == n and len(r["masks"]) == n
+    assert r["masks"][0].height == 256 and r["masks"][0].width == 320      # decoded at the ORIGINAL image size

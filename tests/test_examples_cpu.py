@@ -1,0 +1,59 @@
+"""The bundled examples and CLI tools run end to end on CPU with synthetic data (the reference keeps its examples under
+integration tests: spark/dl/src/test/integration-test.robot)."""
+import importlib.util
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _load(name):
+    spec = importlib.util.spec_from_file_location(name, os.path.join(ROOT, "examples", name + ".py"))
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[name] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def test_lenet_local_example_learns():
+    assert _load("lenet_local").main(["-e", "3", "-f", "/nonexistent"]) > 0.9
+
+
+def test_load_model_example_round_trips_every_format():
+    assert _load("load_model").main([]) < 1e-5
+
+
+def test_int8_inference_example():
+    rel, agree = _load("int8_inference").main(["--iters", "2", "-o", "/tmp/_q_example.bigdl"])
+    assert rel < 0.05 and agree > 0.8
+
+
+def test_ml_pipeline_example():
+    m = _load("ml_pipeline")
+    assert m.logistic_regression() > 0.9 and m.multi_label_regression() < 0.05
+
+
+def test_cli_tools(tmp_path, capsys):
+    import json
+
+    from bigdl_b200.cli import convert_model, imagenet_seqfile_generator, local_optimizer_perf
+
+    local_optimizer_perf.main(["-m", "lenet5", "-b", "16", "-i", "12", "--device", "cpu"])
+    line = [l for l in capsys.readouterr().out.splitlines() if l.startswith("{")][-1]
+    assert json.loads(line)["records_per_second"] > 0
+    # ImageNet folder → sequence files → dataset
+    import cv2
+    import numpy as np
+
+    for split in ("train", "val"):
+        for cls in ("n01", "n02"):
+            os.makedirs(tmp_path / "imgs" / split / cls)
+            for i in range(3):
+                cv2.imwrite(str(tmp_path / "imgs" / split / cls / f"{i}.jpg"),
+                            np.random.randint(0, 255, (40, 60, 3), dtype=np.uint8))
+    imagenet_seqfile_generator.main(["-f", str(tmp_path / "imgs"), "-o", str(tmp_path / "seq"), "-p", "2", "-b", "4",
+                                     "--scaleSize", "32", "-n"])
+    from bigdl_b200.dataset.seqfile import seq_file_dataset
+
+    ds = seq_file_dataset(str(tmp_path / "seq" / "train"), 1000, distributed=False)
+    assert ds.size() == 6

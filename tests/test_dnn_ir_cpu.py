@@ -1,0 +1,64 @@
+"""mkldnn-named API and the IR conversion utilities (T/nn/mkldnn/*Spec.scala, T/utils/intermediate/*Spec.scala)."""
+import torch
+
+from bigdl_b200.nn import layer as L
+from bigdl_b200.nn import mkldnn as D
+from bigdl_b200.utils.intermediate import BlasToIR, ConversionUtils, IRToBlas, IRToDnn
+
+
+def test_dnn_sequential_compile_inference_folds_bn():
+    torch.manual_seed(0)
+    m = (D.Sequential().add(D.Input([2, 3, 8, 8])).add(D.SpatialConvolution(3, 8, 3, 3, 1, 1, 1, 1))
+         .add(D.SpatialBatchNormalization(8)).add(D.ReLU()).add(D.MaxPooling(2, 2, 2, 2)).add(D.Output()))
+    m.modules[2]._buffers["runningMean"].uniform_(-0.2, 0.2)
+    m.modules[2]._buffers["runningVar"].uniform_(0.5, 1.5)
+    x = torch.randn(2, 3, 8, 8)
+    ref = m.evaluate().forward(x).clone()
+    m.compile(D.Phase.InferencePhase, device="cpu")
+    assert getattr(m.modules[2], "_folded", False)
+    assert torch.allclose(m.forward(x), ref, atol=1e-5)
+
+
+def test_reorder_memory_layout_and_dtype():
+    r = D.ReorderMemory(D.HeapData([2, 4, 3, 3], D.Memory.Format.nchw), D.NativeData([2, 4, 3, 3], D.Memory.Format.nhwc,
+                                                                                     D.Memory.DataType.BF16))
+    y = r.forward(torch.randn(2, 4, 3, 3))
+    assert y.dtype == torch.bfloat16 and y.is_contiguous(memory_format=torch.channels_last)
+
+
+def test_dnn_rnn_shapes():
+    assert tuple(D.RNN("vanilla_lstm", 6, 5, layers=2).forward(torch.randn(3, 4, 6)).shape) == (3, 4, 5)
+    assert tuple(D.RNN("vanilla_gru", 6, 5, direction="bidirectional_concat").forward(torch.randn(3, 4, 6)).shape) == (3, 4, 10)
+
+
+def test_ir_roundtrip_sequential_and_graph():
+    torch.manual_seed(1)
+    seq = (L.Sequential().add(L.Linear(6, 8)).add(L.ReLU())
+           .add(L.Sequential().add(L.Linear(8, 8)).add(L.Tanh())).add(L.Linear(8, 3)))
+    ir = BlasToIR.convert(seq)
+    assert [n.element.op for n in ir.nodes] == ["Linear", "ReLU", "Linear", "Tanh", "Linear"]      # nested chain flattened
+    assert "Linear" in ir.summary()
+    x = torch.randn(4, 6)
+    ref = seq.forward(x).clone()
+    g = IRToBlas.convert(ir)
+    assert torch.allclose(g.forward(x), ref)
+    dnn = IRToDnn.convert(ir)
+    assert isinstance(dnn, D.DnnGraph) and torch.allclose(dnn.compile(D.Phase.InferencePhase, device="cpu").forward(x), ref)
+    # weights are shared with the source model, not copied
+    assert g.exec_order[1].element is seq.modules[0]
+    # graph with a branch
+    inp = L.Input()
+    a = L.Linear(4, 4)(inp)
+    b = L.Linear(4, 4)(inp)
+    out = L.CAddTable()([a, b])
+    model = L.Model([inp], [out])
+    ir2 = BlasToIR.convert(model)
+    assert len(ir2) == 4 and ir2.nodes[3].prev == [1, 2]
+    xx = torch.randn(2, 4)
+    assert torch.allclose(IRToBlas.convert(ir2).forward(xx), model.forward(xx))
+
+
+def test_conversion_utils_cpu_is_identity():
+    m = L.Sequential().add(L.Linear(3, 2))
+    assert ConversionUtils.convert(m, device="cpu") is m
+    assert ConversionUtils.convertBack(m) is m

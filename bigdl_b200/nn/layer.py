@@ -11,3 +11,5 @@ from .layers_attention import *  # noqa: F401,F403
 from .layers_detection import *  # noqa: F401,F403
 from .initialization_method import *  # noqa: F401,F403
 from .layers_recurrent import RnnCell as RNN  # noqa: F401  (Python API name, P/nn/layer.py)
+from .dynamic_graph import DynamicGraph  # noqa: F401,E402
+from .layers_attention import TransformerOperation  # noqa: F401,E402

@@ -320,3 +320,46 @@ class SequenceBeamSearch(Module):
             raise ValueError("SequenceBeamSearch needs setLogitFn(fn) or to be driven by a Transformer")
         enc, bias = to_table(input).to_list()[:2]
         return self.search(self._logit_fn, {"enc": enc, "enc_bias": bias}, enc.shape[0], enc.device)
+
+
+class TransformerOperation:
+    """Helper functions of the Transformer (S/nn/TransformerOperation.scala:30-174) under their reference names."""
+
+    @staticmethod
+    def getPositionEncode(length: int, hidden_size: int, min_timescale: float = 1.0, max_timescale: float = 1.0e4,
+                          device="cpu"):
+        return position_signal(length, hidden_size, device, min_timescale=min_timescale, max_timescale=max_timescale)
+
+    @staticmethod
+    def attentionBiasLowerTriangle(length: int, device="cpu"):
+        return causal_bias(length, device)
+
+    @staticmethod
+    def getPaddingBias(ids: torch.Tensor, padding_value: float = 0.0):
+        return padding_bias(ids, padding_value)
+
+    @staticmethod
+    def shiftRight3D(x: torch.Tensor) -> torch.Tensor:
+        """Shift the time axis right by one, zero-filling the first step (decoder input preparation)."""
+        out = torch.zeros_like(x)
+        out[:, 1:] = x[:, :-1]
+        return out
+
+    @staticmethod
+    def initRangeTensor(length: int, device="cpu") -> torch.Tensor:
+        return torch.arange(length, dtype=torch.float32, device=device)
+
+    @staticmethod
+    def dense(input_size: int, output_size: int, bias: bool = True, activation=None, name: str | None = None):
+        """Dense layer applied to the last axis of a 3-D tensor (TimeDistributed Linear + optional activation)."""
+        from .layers_core import Linear
+        from .layers_recurrent import TimeDistributed
+        from .module import Sequential
+
+        lin = Linear(input_size, output_size, with_bias=bias)
+        if name:
+            lin.setName(name)
+        seq = Sequential().add(TimeDistributed(lin))
+        if activation is not None:
+            seq.add(activation)
+        return seq

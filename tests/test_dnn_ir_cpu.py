@@ -62,3 +62,16 @@ def test_conversion_utils_cpu_is_identity():
     m = L.Sequential().add(L.Linear(3, 2))
     assert ConversionUtils.convert(m, device="cpu") is m
     assert ConversionUtils.convertBack(m) is m
+
+
+def test_to_graph_shares_layers_and_matches():
+    torch.manual_seed(2)
+    m = (L.Sequential().add(L.Linear(4, 6)).add(L.ReLU())
+         .add(L.ConcatTable(L.Linear(6, 3), L.Sequential().add(L.Linear(6, 3)).add(L.Tanh()))).add(L.CAddTable())
+         .add(L.Concat(2).add(L.Linear(3, 2)).add(L.Linear(3, 5))))
+    x = torch.randn(3, 4)
+    ref = m.forward(x).clone()
+    g = m.toGraph()
+    assert type(g).__name__ == "Graph" and torch.allclose(g.forward(x), ref)
+    assert any(n.element is m.modules[0] for n in g.exec_order)
+    assert g.toGraph() is g

@@ -20,7 +20,7 @@ def train(backend, iters, rank, world, dev):
     from bigdl_b200.utils import config
     from bigdl_b200.utils.random_generator import RNG
 
-    config.set("bigdl.parameter.backend", backend)
+    config.set("bigdl.parameter.backend", "nccl" if backend == "parallel" else backend)
     RNG.setSeed(7)
     m = Sequential()
     m.add(SpatialConvolution(8, 32, 3, 3, 1, 1, 1, 1)).add(ReLU()).add(SpatialMaxPooling(2, 2, 2, 2))
@@ -31,7 +31,13 @@ def train(backend, iters, rank, world, dev):
     x = torch.randn(32, 8, 32, 32, generator=g).pin_memory()
     y = torch.randint(1, 17, (32,), generator=g).float().pin_memory()
     ds = FixedMiniBatchDataSet(MiniBatch(x, y), epoch_size=10 ** 9, distributed=True)
-    opt = Optimizer(m, ds, ClassNLLCriterion(), MaxIteration(iters), 32 * world, SGD(0.05, momentum=0.9, dampening=0.0))
+    om = SGD(0.05, momentum=0.9, dampening=0.0)
+    if backend == "parallel":
+        from bigdl_b200.optim.parallel_optimizer import ParallelOptimizer
+
+        opt = ParallelOptimizer(m, ds, ClassNLLCriterion(), MaxIteration(iters), 32 * world, om, bucket_mb=0.05)
+    else:
+        opt = Optimizer(m, ds, ClassNLLCriterion(), MaxIteration(iters), 32 * world, om)
     opt.optimize()
     torch.cuda.synchronize()
     w = m._flat.compute.float().clone()
@@ -49,6 +55,8 @@ def main():
     Engine.init()
     w_p2p, l_p2p = train("p2p", 8, rank, world, dev)
     w_nccl, l_nccl = train("nccl", 8, rank, world, dev)
+    w_par, l_par = train("parallel", 8, rank, world, dev)       # ParallelOptimizer: bucketed async all-reduce
+    diff_par = float((w_par - w_nccl).abs().max())
     # all ranks must hold identical compute weights
     ref = w_p2p.clone()
     dist.broadcast(ref, 0)
@@ -59,8 +67,9 @@ def main():
     scale = float(w_nccl.abs().max())
     if rank == 0:
         print(json.dumps({"world": world, "ranks_identical": bool(flags.item()), "p2p_vs_nccl_max_abs_diff": diff,
-                          "weight_scale": scale, "loss_p2p": l_p2p, "loss_nccl": l_nccl}))
-    ok = bool(flags.item()) and diff <= 2e-2 * scale + 1e-3
+                          "parallel_vs_nccl_max_abs_diff": diff_par, "weight_scale": scale, "loss_p2p": l_p2p,
+                          "loss_nccl": l_nccl, "loss_parallel": l_par}))
+    ok = bool(flags.item()) and diff <= 2e-2 * scale + 1e-3 and diff_par <= 2e-2 * scale + 1e-3
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)
 

@@ -13,3 +13,4 @@ from .initialization_method import *  # noqa: F401,F403
 from .layers_recurrent import RnnCell as RNN  # noqa: F401  (Python API name, P/nn/layer.py)
 from .dynamic_graph import DynamicGraph  # noqa: F401,E402
 from .layers_attention import TransformerOperation  # noqa: F401,E402
+from . import int8_convertible as _int8_convertible  # noqa: F401,E402  (attaches calcScales & friends to Module)

@@ -38,6 +38,8 @@ class Quantizer:
         _fuse_through_identities(m)
         out = cls._convert(m)
         out.evaluate()
+        if any(l.static_scale for l in cls.quantized_layers(out)):
+            cls.link_chains(out)
         if dev.type == "cuda" and out.torch_parameters():
             out.getParameters()
         return out
@@ -46,7 +48,11 @@ class Quantizer:
     def _convert(cls, m: Module) -> Module:
         q = cls._registry.get(type(m))
         if q is not None:
-            return q.from_float(m)
+            qm = q.from_float(m)
+            st = m.__dict__.get("_mkl_int8")          # scales recorded by calcScales (MklInt8Convertible)
+            if st and st.get("inputScales") and st["inputScales"][0]:
+                qm.setInputScales([[max(st["inputScales"][0])]])
+            return qm
         if isinstance(m, Graph):
             for n in m.exec_order:
                 new = cls._convert(n.element)

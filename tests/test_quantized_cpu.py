@@ -106,3 +106,28 @@ def test_quantized_save_load_roundtrip(tmp_path):
     q2 = L.Module.loadModule(p).evaluate()
     assert isinstance(q2.modules[0], QZ.Linear)
     assert torch.allclose(q2.forward(x), ref, atol=1e-6)
+
+
+def test_calc_scales_feed_static_quantisation(tmp_path):
+    """MklInt8Convertible flow: calcScales on the float model → scales saved in the .bigdl file → quantize() picks them
+    up as static activation scales (S/example/mkldnn/int8/GenerateInt8Scales.scala)."""
+    torch.manual_seed(5)
+    m = _lenet_like().evaluate()
+    m.setWeightDimMask(1, overrideSubmodules=True)
+    x = torch.randn(4, 3, 16, 16)
+    m.calcScales(x)
+    conv0, fc = m.modules[0], m.modules[9]
+    assert abs(conv0.getInputScales()[0][0] - float(x.abs().max())) < 1e-6
+    assert len(conv0.getWeightScales()[0]) == 16                      # mask 1 → one scale per output channel
+    assert abs(fc.getOutputScales()[0][0] - float(m.forward(x).abs().max())) < 1e-5
+    assert m.getInputScales()[0][0] == conv0.getInputScales()[0][0]   # containers record their own activity too
+    p = str(tmp_path / "scaled.bigdl")
+    m.saveModule(p, overWrite=True)
+    back = L.Module.loadModule(p)
+    assert back.modules[0].getInputScales() == conv0.getInputScales()
+    q = back.evaluate().quantize()
+    qs = Quantizer.quantized_layers(q)
+    assert all(l.static_scale for l in qs) and qs[0]._emit_q is qs[1]
+    ref = m.forward(x)
+    out = q.forward(x)
+    assert float((out - ref).norm() / ref.norm()) < 0.1

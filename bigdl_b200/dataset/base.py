@@ -362,3 +362,41 @@ class FixedMiniBatchDataSet(AbstractDataSet):
             return gen()
         n = max(1, math.ceil(self._size / max(self.batch.size(), 1)))
         return iter([self.batch] * n)
+
+
+# ---- reference class names kept as aliases (S/dataset/Sample.scala ArraySample:138 / TensorSample:446)
+ArraySample = Sample
+TensorSample = Sample
+
+
+class SparseMiniBatch(MiniBatch):
+    """MiniBatch whose features may be ``bigdl_b200.tensor.SparseTensor``s (S/dataset/MiniBatch.scala SparseMiniBatch):
+    sparse features of the samples are concatenated along the batch dimension, dense ones stacked as usual."""
+
+    @staticmethod
+    def from_samples(samples, feature_padding=None, label_padding=None):
+        from ..tensor.sparse import SparseTensor
+
+        first = samples[0]
+        feats = first.features if hasattr(first, "features") else [first.feature()]
+        out = []
+        for i in range(len(feats)):
+            col = [(s.features[i] if hasattr(s, "features") else s.feature()) for s in samples]
+            if isinstance(col[0], SparseTensor):
+                rows = [c if c.nDimension() == 2 else SparseTensor(torch.cat([torch.zeros(1, c.sp._nnz(), dtype=torch.long),
+                                                                                 c.sp.indices()]), c.sp.values(),
+                                                                      (1,) + tuple(c.sp.shape)) for c in col]
+                out.append(SparseTensor.concat(1, rows))
+            else:
+                out.append(torch.stack([torch.as_tensor(c) for c in col]))
+        labels = [s.label() for s in samples]
+        tgt = torch.stack([torch.as_tensor(l) for l in labels]) if labels and labels[0] is not None else None
+        return SparseMiniBatch(out if len(out) > 1 else out[0], tgt)
+
+
+def _sort_by_length(samples):
+    return sorted(samples, key=lambda s: int(torch.as_tensor(s.feature()).shape[0]))
+
+
+DataSet.sortRDD = staticmethod(lambda data, is_in_order=True, group_size=1: DistributedDataSet(_sort_by_length(list(data))))
+DataSet.sort_rdd = DataSet.sortRDD

@@ -347,3 +347,52 @@ def test_keras_json_definition_and_weights(tmp_path):
         "input_layers": [["in", 0, 0]], "output_layers": [["m", 0, 0]]}}
     fm = DefinitionLoader.from_config(func)
     assert tuple(fm.forward(torch.randn(5, 6)).shape) == (5, 4)
+
+
+def test_tfrecord_and_session(tmp_path):
+    from bigdl_b200.dataset.base import DataSet, Sample
+    from bigdl_b200.interop import tf_pb as P
+    from bigdl_b200.interop.tf_session import Session
+    from bigdl_b200.interop.tfrecord import FixedLengthRecordReader, TFRecordIterator, TFRecordWriter, encode_example
+    from bigdl_b200.nn.criterion import MSECriterion
+    from bigdl_b200.nn.tf import parse_example
+    from bigdl_b200.optim.optim_method import SGD
+    from bigdl_b200.optim.trigger import Trigger
+
+    path = str(tmp_path / "data.tfrecord")
+    with TFRecordWriter(path) as w:
+        for i in range(3):
+            w.write(encode_example({"x": [float(i), 2.0], "id": [i], "name": f"rec{i}"}))
+    recs = [parse_example(r) for r in TFRecordIterator(path)]
+    assert recs[2]["x"] == ("float", [2.0, 2.0]) and recs[1]["id"] == ("int64", [1]) and recs[0]["name"] == ("bytes", [b"rec0"])
+    raw = tmp_path / "fixed.bin"
+    raw.write_bytes(b"HH" + b"".join(bytes([i]) * 3 + b"-" for i in range(4)) + b"F")
+    assert [r for r in FixedLengthRecordReader(str(raw), 1, 2, 1, 3)] == [bytes([i]) * 3 for i in range(4)]
+
+    # y = x @ W + b as a TF graph with trainable constants; fit it to a known linear map through Session.train
+    gd = P.GraphDef()
+    def node(op, name, inputs=(), **attrs):
+        n = gd.node.add()
+        n.op, n.name = op, name
+        n.input.extend(inputs)
+        for k, v in attrs.items():
+            n.attr[k].tensor.CopyFrom(P.numpy_to_tensor(v))
+    node("Placeholder", "x")
+    node("Const", "W", value=np.zeros((3, 2), np.float32))
+    node("Const", "b", value=np.zeros(2, np.float32))
+    node("MatMul", "mm", ["x", "W"])
+    node("BiasAdd", "y", ["mm", "b"])
+    rs = np.random.RandomState(0)
+    X = rs.randn(64, 3).astype(np.float32)
+    Wt = np.array([[1.0, -1.0], [0.5, 2.0], [-2.0, 0.0]], np.float32)
+    Y = X @ Wt + np.array([0.5, -0.5], np.float32)
+    ds = DataSet.array([Sample(X[i], Y[i]) for i in range(64)])
+    sess = Session(gd)
+    assert sess.placeholders() == ["x"]
+    model = sess.train(["y"], ds, SGD(0.1), MSECriterion(), Trigger.maxEpoch(40), batch_size=16)
+    pred = np.stack([np.asarray(p) for p in sess.predict(["y"], ds, batch_size=16)])
+    assert np.abs(pred - Y).max() < 0.05
+    out = sess.run(["y"], {"x": X[:2]})
+    assert np.allclose(out.detach().numpy(), pred[:2], atol=1e-5)
+    saved = sess.saveParameters(str(tmp_path / "vars.npz"))
+    assert np.abs(np.load(saved)["W"] - Wt).max() < 0.05

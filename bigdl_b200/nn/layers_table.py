@@ -10,6 +10,8 @@ TableOperation. Dimensions and indices in constructors are 1-based like the refe
 from __future__ import annotations
 
 import torch
+
+from ..utils import config
 import torch.nn.functional as F
 
 from ..utils.table import Table, flatten_activity, to_table
@@ -25,6 +27,16 @@ def _dim(d: int, ndim: int, n_input_dims: int = -1) -> int:
     if n_input_dims > 0 and ndim == n_input_dims + 1:
         z += 1
     return z
+
+
+_SIDE: dict = {}
+
+
+def _side_streams(device, n: int):
+    pool = _SIDE.setdefault(device.index, [])
+    while len(pool) < n:
+        pool.append(torch.cuda.Stream(device=device))
+    return pool[:n]
 
 
 def _tl(x) -> list:
@@ -85,10 +97,26 @@ class Concat(Container):
         ctot = sum(t.n_output_plane for t in tails)
         big = torch.empty((input.shape[0], Ho, Wo, ctot), dtype=torch.bfloat16, device=input.device)
         outs, c = [], 0
-        for branch, tail in zip(self.modules, tails):
+        multi = bool(config.get("bigdl.concat.streams")) and len(self.modules) > 1
+        if multi:
+            # The branches are independent and, in Inception, individually too small to fill 148 SMs: run them on side
+            # streams (forked from / joined to the current stream, which also works under CUDA-graph capture). Autograd
+            # replays each branch's backward on the stream its forward ran on.
+            main = torch.cuda.current_stream(input.device)
+            side = _side_streams(input.device, len(self.modules) - 1)
+        for i, (branch, tail) in enumerate(zip(self.modules, tails)):
             tail._next_out_hint = big[..., c:c + tail.n_output_plane]
-            outs.append(branch._call(input))
+            if multi and i > 0:
+                st = side[i - 1]
+                st.wait_stream(main)
+                with torch.cuda.stream(st):
+                    outs.append(branch._call(input))
+            else:
+                outs.append(branch._call(input))
             c += tail.n_output_plane
+        if multi:
+            for st in side:
+                main.wait_stream(st)
         return Fn.ConcatViewFn.apply(big, *outs)
 
 

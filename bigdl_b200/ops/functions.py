@@ -137,16 +137,23 @@ class LinearFn(Function):
                 else:
                     gb.add_(ew.colsum(dy2, torch.zeros(N, device=dy.device)), alpha=scale_b)
         gw = _acc_grad(weight, scale_w)
+        wk = w16
+        if N % 8:
+            # dY is an MN-major operand of both backward GEMMs, so its row pitch must be a multiple of 8 elements:
+            # zero-pad the output dimension (small classifiers such as 10-way heads)
+            n8 = (N + 7) // 8 * 8
+            dz = torch.nn.functional.pad(dz, (0, n8 - N))
+            wk = torch.nn.functional.pad(w16, (0, 0, 0, n8 - N))
         if gw is not None:
-            if scale_w == 1.0 and gw.is_contiguous():
+            if scale_w == 1.0 and gw.is_contiguous() and N % 8 == 0:
                 gemm_bf16(dz, x2, a_mn=True, b_mn=True, out=gw, accumulate=True)
             else:
-                tmp = torch.zeros(gw.shape, device=gw.device)
+                tmp = torch.zeros((dz.shape[1], x2.shape[1]), device=gw.device)
                 gemm_bf16(dz, x2, a_mn=True, b_mn=True, out=tmp, accumulate=True)
-                gw.add_(tmp, alpha=scale_w)
+                gw.add_(tmp[:N], alpha=scale_w)
         dx = None
         if ctx.needs_input_grad[0]:
-            dx = gemm_bf16(dz, w16, b_mn=True).reshape(xshape)
+            dx = gemm_bf16(dz, wk, b_mn=True).reshape(xshape)
         return dx, None, None, None, None, None, None
 
 

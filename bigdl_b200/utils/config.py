@@ -36,6 +36,7 @@ _DEFAULTS: dict[str, Any] = {
     "bigdl.mkldnn.fusion.convsum": True,
     # misc
     "bigdl.cudaGraph": True,
+    "bigdl.concat.streams": True,            # run the branches of a channel Concat on side streams
     "bigdl.utils.LoggerFilter.disable": False,
     "bigdl.utils.LoggerFilter.logFile": "bigdl.log",
     "bigdl.utils.LoggerFilter.enableSparkLog": True,

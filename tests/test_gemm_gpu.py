@@ -59,3 +59,26 @@ def test_gemm_splitk_accumulate():
     ref = 1.0 + dy.float().t() @ x.float()
     err = (acc - ref).abs().max().item()
     assert err <= 2e-3 * ref.abs().max().item() + 1e-2, err
+
+
+def test_linear_fn_output_size_not_multiple_of_8():
+    """10-way classifier head: backward pads dY for the MN-major GEMM operands."""
+    import torch
+    from bigdl_b200.nn.layer import Linear
+
+    torch.manual_seed(0)
+    lin = Linear(64, 10)
+    ref = lin.cloneModule()
+    lin.cuda()
+    x = torch.randn(32, 64)
+    go = torch.randn(32, 10)
+    y = lin.forward(x.cuda().to(torch.bfloat16))
+    gi = lin.backward(x.cuda().to(torch.bfloat16), go.cuda().to(torch.bfloat16))
+    yr = ref.forward(x)
+    gir = ref.backward(x, go)
+    assert torch.allclose(y.float().cpu(), yr, atol=5e-2, rtol=5e-2)
+    assert torch.allclose(gi.float().cpu(), gir, atol=5e-2, rtol=5e-2)
+    gw = [p.grad for p in lin.torch_parameters()]
+    gwr = [p.grad for p in ref.torch_parameters()]
+    for a, b in zip(gw, gwr):
+        assert torch.allclose(a.float().cpu(), b, atol=0.15, rtol=5e-2)

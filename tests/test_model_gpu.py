@@ -131,3 +131,49 @@ def test_graphed_step_matches_eager():
     assert _rel(w_g, w_e) < 2e-3, _rel(w_g, w_e)
     assert _rel(rm_g, rm_e) < 2e-3
     assert abs(l_g - l_e) < 2e-2 * max(1.0, abs(l_e))
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_concat_side_streams_match_single_stream(graph):
+    """Running Concat branches on side streams must not change the training trajectory (eager and CUDA-graph step)."""
+    from bigdl_b200.dataset.base import FixedMiniBatchDataSet, MiniBatch
+    from bigdl_b200.models.inception import Inception_Layer_v1
+    from bigdl_b200.nn.criterion import ClassNLLCriterion
+    from bigdl_b200.nn.layer import (Linear, LogSoftMax, ReLU, Sequential, SpatialAveragePooling, SpatialConvolution,
+                                     SpatialMaxPooling, View)
+    from bigdl_b200.optim.optim_method import SGD
+    from bigdl_b200.optim.optimizer import LocalOptimizer
+    from bigdl_b200.optim.trigger import MaxIteration
+    from bigdl_b200.utils import config
+    from bigdl_b200.utils.random_generator import RNG
+
+    def run(streams):
+        config.set("bigdl.concat.streams", streams)
+        config.set("bigdl.cudaGraph", graph)
+        RNG.setSeed(11)
+        torch.manual_seed(11)
+        net = Sequential()
+        net.add(SpatialConvolution(3, 64, 7, 7, 2, 2, 3, 3)).add(ReLU(True)).add(SpatialMaxPooling(3, 3, 2, 2).ceil())
+        net.add(Inception_Layer_v1(64, ((32,), (48, 64), (8, 16), (16,)), "a/"))
+        net.add(Inception_Layer_v1(128, ((64,), (64, 96), (16, 32), (32,)), "b/"))
+        net.add(SpatialAveragePooling(16, 16, 1, 1)).add(View(224).setNumInputDims(3)).add(Linear(224, 10)).add(LogSoftMax())
+        net.cuda()
+        g = torch.Generator().manual_seed(3)
+        x = torch.randn(16, 3, 64, 64, generator=g)
+        y = torch.randint(1, 11, (16,), generator=g).float()
+        ds = FixedMiniBatchDataSet(MiniBatch(x, y), epoch_size=10 ** 9, distributed=False)
+        opt = LocalOptimizer(net, ds, ClassNLLCriterion(), MaxIteration(12), 16, SGD(0.05, momentum=0.9, dampening=0.0))
+        opt.optimize()
+        torch.cuda.synchronize()
+        w, _ = net.getParameters()
+        return w.clone(), float(opt.state["Loss"])
+
+    try:
+        w0, l0 = run(False)
+        w1, l1 = run(True)
+    finally:
+        config.unset("bigdl.concat.streams")
+        config.unset("bigdl.cudaGraph")
+    # identical kernels and inputs; only fp32 atomic accumulation order may differ
+    assert _rel(w1, w0) < 2e-3, _rel(w1, w0)
+    assert abs(l1 - l0) < 2e-2 * max(abs(l0), 1.0)

@@ -25,13 +25,16 @@ class Quantizer:
     def quantize(cls, model: Module, fold_bn: bool = True) -> Module:
         """Returns a quantised deep copy in evaluate mode (AbstractModule.quantize clones first, S/nn/abstractnn/
         AbstractModule.scala:920-928)."""
-        from ..nn.fusion import fold_bn as do_fold, fuse
+        from ..nn.fusion import fold_bn as do_fold, fuse, unfuse
 
         from ..nn.flat import unflatten_parameters
 
         m = model.cloneModule().evaluate()
         dev = m.device()
         unflatten_parameters(m)
+        # a model that already lived on the GPU carries fusion flags (e.g. BN+ReLU); they must be recomputed AFTER the BN
+        # folding, otherwise a folded BN would still apply "its" ReLU — a no-op on e4m3 bytes handed over by a conv
+        unfuse(m)
         if fold_bn:
             do_fold(m)
         fuse(m)

@@ -131,3 +131,20 @@ def test_calc_scales_feed_static_quantisation(tmp_path):
     ref = m.forward(x)
     out = q.forward(x)
     assert float((out - ref).norm() / ref.norm()) < 0.1
+
+
+def test_quantize_model_that_was_already_fused():
+    """Fusion flags set before quantize() (a model that lived on the GPU) must not leave a ReLU on a folded BN."""
+    from bigdl_b200.nn.fusion import fuse
+
+    torch.manual_seed(6)
+    m = _lenet_like().evaluate()
+    x = torch.randn(4, 3, 16, 16)
+    ref = m.forward(x).clone()
+    fuse(m)
+    assert m.modules[1]._fuse_relu                      # BN + ReLU fused
+    q = m.quantize()
+    Quantizer.calibrate(q, [x])
+    assert not q.modules[1]._fuse_relu and q.modules[0]._fuse_relu      # the ReLU moved into the conv epilogue
+    out = q.forward(x)
+    assert float((out - ref).norm() / ref.norm()) < 0.1

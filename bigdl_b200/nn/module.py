@@ -464,6 +464,10 @@ class Module:
         pairs = [(o, g.to(o.dtype)) for o, g in zip(outs, gos) if o.requires_grad]
         if pairs:
             self._backward_scaled(pairs, ins)
+        if torch.cuda.is_available():
+            from ..ops.functions import join_side_streams
+
+            join_side_streams()
         self.gradInput = map_activity(
             lambda t: (t.grad if t.grad is not None else torch.zeros_like(t)) if t.is_floating_point()
             else torch.zeros_like(t, dtype=torch.float32), self._graph_in)

@@ -19,6 +19,36 @@ from .gemm import conv_igemm, gemm_bf16
 
 _WS: dict = {}
 
+# ---- weight-gradient side stream ----------------------------------------------------------------------------------
+# dgrad is on the critical path of backward (the next layer needs it), wgrad is not: it only has to finish before the
+# optimizer step. wgrad GEMMs are therefore issued on a per-device side stream, where they fill the SMs that the small
+# dgrad kernels of the following layers leave idle. ``join_side_streams`` must run before anything reads the gradient
+# buffer (training loops call it right after ``autograd.backward``; it is part of the captured CUDA graph).
+_WGRAD_STREAM: dict = {}
+_WGRAD_KEEP: list = []          # operands of in-flight wgrad GEMMs, kept alive until the join
+
+
+def _wgrad_side(device):
+    from ..utils import config
+
+    if not config.get("bigdl.wgrad.stream"):
+        return None
+    st = _WGRAD_STREAM.get(device.index)
+    if st is None:
+        st = _WGRAD_STREAM[device.index] = torch.cuda.Stream(device=device)
+    return st
+
+
+def join_side_streams(device=None):
+    """Make the current stream wait for every outstanding side-stream weight-gradient GEMM."""
+    if not _WGRAD_KEEP:
+        return
+    cur = torch.cuda.current_stream(device)
+    for idx, st in _WGRAD_STREAM.items():
+        if device is None or device.index in (None, idx):
+            cur.wait_stream(st)
+    _WGRAD_KEEP.clear()
+
 
 def workspace(numel: int, device, slot: int = 0) -> torch.Tensor:
     """Grow-only bf16 scratch buffer shared by all conv layers of a device (im2col / dgrad columns)."""
@@ -146,7 +176,14 @@ class LinearFn(Function):
             wk = torch.nn.functional.pad(w16, (0, 0, 0, n8 - N))
         if gw is not None:
             if scale_w == 1.0 and gw.is_contiguous() and N % 8 == 0:
-                gemm_bf16(dz, x2, a_mn=True, b_mn=True, out=gw, accumulate=True)
+                side = _wgrad_side(dz.device)
+                if side is not None:
+                    side.wait_stream(torch.cuda.current_stream(dz.device))
+                    with torch.cuda.stream(side):
+                        gemm_bf16(dz, x2, a_mn=True, b_mn=True, out=gw, accumulate=True)
+                    _WGRAD_KEEP.append((dz, x2))
+                else:
+                    gemm_bf16(dz, x2, a_mn=True, b_mn=True, out=gw, accumulate=True)
             else:
                 tmp = torch.zeros((dz.shape[1], x2.shape[1]), device=gw.device)
                 gemm_bf16(dz, x2, a_mn=True, b_mn=True, out=tmp, accumulate=True)
@@ -269,7 +306,14 @@ class ConvFn(Function):
         if implicit:
             ldz = dz.stride(0)
             if gw is not None and not padded_c and C % 8 == 0 and C >= 16 and scale_w == 1.0 and gw2.stride(1) == 1:
-                conv_igemm(2, xn, ldx, dz, gw2, O, Ho, Wo, kh, kw, sh, sw, pt, pl, dh, dw, accumulate=True)
+                side = _wgrad_side(dz.device)
+                if side is not None:
+                    side.wait_stream(torch.cuda.current_stream(dz.device))
+                    with torch.cuda.stream(side):
+                        conv_igemm(2, xn, ldx, dz, gw2, O, Ho, Wo, kh, kw, sh, sw, pt, pl, dh, dw, accumulate=True)
+                    _WGRAD_KEEP.append((dz, xn))
+                else:
+                    conv_igemm(2, xn, ldx, dz, gw2, O, Ho, Wo, kh, kw, sh, sw, pt, pl, dh, dw, accumulate=True)
                 done_w = True
             if need_dx and sh == 1 and sw == 1 and dh * (kh - 1) - pt >= 0 and dw * (kw - 1) - pl >= 0:
                 dz_nhwc = torch.as_strided(dz, (N, Ho, Wo, O), (Ho * Wo * ldz, Wo * ldz, ldz, 1), dz.storage_offset())
@@ -298,7 +342,14 @@ class ConvFn(Function):
                 else:
                     tgt = gw2[g * Og:(g + 1) * Og]
                     if scale_w == 1.0 and Kp == K and tgt.stride(1) == 1:
-                        gemm_bf16(dzg, a, a_mn=True, b_mn=True, out=tgt, accumulate=True)
+                        side = _wgrad_side(dz.device) if (direct or ctx.kept_cols is not None) else None
+                        if side is not None:          # operands are not in the shared workspace: safe to defer
+                            side.wait_stream(torch.cuda.current_stream(dz.device))
+                            with torch.cuda.stream(side):
+                                gemm_bf16(dzg, a, a_mn=True, b_mn=True, out=tgt, accumulate=True)
+                            _WGRAD_KEEP.append((dz, a, xn))
+                        else:
+                            gemm_bf16(dzg, a, a_mn=True, b_mn=True, out=tgt, accumulate=True)
                     else:
                         tmp = torch.zeros((Og, Kp), device=dy.device)
                         gemm_bf16(dzg, a, a_mn=True, b_mn=True, out=tmp, accumulate=True)

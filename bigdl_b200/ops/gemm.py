@@ -8,6 +8,14 @@ import torch
 from . import _lib
 
 BIAS, RELU, ATOMIC_ADD = 1, 2, 4
+_LOG = [] if __import__("os").environ.get("BDL_LOG_GEMM") else None      # shape log for per-layer roofline analysis
+
+
+def _log(kind, **kw):
+    if _LOG is not None:
+        _LOG.append(dict(kind=kind, **kw))
+        with open(__import__("os").environ["BDL_LOG_GEMM"], "a") as f:
+            f.write(__import__("json").dumps(_LOG[-1]) + "\n")
 
 
 def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False, bias=None, relu=False,
@@ -31,6 +39,7 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: boo
     flags = (BIAS if bias is not None else 0) | (RELU if relu else 0) | (ATOMIC_ADD if accumulate else 0)
     if bias is not None:
         assert bias.dtype == torch.float32 and bias.is_contiguous()
+    _log("gemm", M=M, N=N, K=K, a_mn=int(a_mn), b_mn=int(b_mn), acc=int(accumulate))
     rc = lib.bdl_gemm_bf16(_lib.ptr(a), _lib.ptr(b), _lib.ptr(out), _lib.ptr(bias), M, N, K,
                            a.stride(0), b.stride(0), out.stride(0), int(a_mn), int(b_mn),
                            int(out.dtype == torch.float32), flags, splits, _lib.stream_ptr())
@@ -47,6 +56,7 @@ def conv_igemm(mode: int, act: torch.Tensor, ld_act: int, other: torch.Tensor, o
     lib = _lib.cuda_lib()
     N, H, W, C = act.shape
     flags = (BIAS if bias is not None else 0) | (RELU if relu else 0) | (ATOMIC_ADD if accumulate else 0)
+    _log("conv", mode=mode, N=N, H=H, W=W, C=C, O=O, Ho=Ho, Wo=Wo, kh=kh, kw=kw, sh=sh)
     rc = lib.bdl_conv_igemm_bf16(mode, act.data_ptr(), N, H, W, C, ld_act, other.data_ptr(), other.stride(0),
                                  out.data_ptr(), out.stride(0), _lib.ptr(bias), O, Ho, Wo, kh, kw, sh, sw, ph, pw, dh,
                                  dw, int(out.dtype == torch.float32), flags, splits, _lib.stream_ptr())

@@ -141,6 +141,9 @@ class GraphedTrainStep:
         seed = torch.ones((), dtype=loss.dtype, device=loss.device)
         seed._bdl_is_one = True
         torch.autograd.backward(loss, seed)
+        from ..ops.functions import join_side_streams
+
+        join_side_streams()
         self.model._apply_regularizers()
         self.sync.step_device_hp(self._plan, self.hp_dev.data_ptr(), self.epoch_dev.data_ptr())
         self._count_body_launches = _lib.LAUNCHES - before

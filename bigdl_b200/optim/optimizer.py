@@ -466,6 +466,10 @@ def _train_loop(opt: Optimizer, distributed: bool, strategy_factory=None):
             seed = torch.ones((), dtype=loss.dtype, device=loss.device)
             seed._bdl_is_one = True
             torch.autograd.backward(loss, seed)
+            if device.type == "cuda":
+                from ..ops.functions import join_side_streams
+
+                join_side_streams()
             model._apply_regularizers()
             if strategy is not None:
                 for om_ in strategy.methods:

@@ -149,6 +149,7 @@ def test_concat_side_streams_match_single_stream(graph):
 
     def run(streams):
         config.set("bigdl.concat.streams", streams)
+        config.set("bigdl.wgrad.stream", streams)
         config.set("bigdl.cudaGraph", graph)
         RNG.setSeed(11)
         torch.manual_seed(11)
@@ -173,6 +174,7 @@ def test_concat_side_streams_match_single_stream(graph):
         w1, l1 = run(True)
     finally:
         config.unset("bigdl.concat.streams")
+        config.unset("bigdl.wgrad.stream")
         config.unset("bigdl.cudaGraph")
     # identical kernels and inputs; only fp32 atomic accumulation order may differ
     assert _rel(w1, w0) < 2e-3, _rel(w1, w0)

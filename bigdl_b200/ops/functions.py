@@ -194,12 +194,103 @@ class LinearFn(Function):
         return dx, None, None, None, None, None, None
 
 
+_STEM_S2D: list = [True]
+
+
+def _stem_s2d_plan(x, w16, geom, needs_dx):
+    """Decide whether a stride-2 few-channel convolution (the 7x7/2 RGB stems of Inception and ResNet) runs as a
+    space-to-depth + stride-1 implicit GEMM. The explicit path writes and re-reads a [N*Ho*Wo, 7*7*4] patch matrix
+    (0.4 GB at batch 128); the folded input is 16 channels wide, which the TMA-im2col kernel accepts directly."""
+    kh, kw, sh, sw, pt, pl, pb, pr, dh, dw, groups = geom
+    N, C, H, W = x.shape
+    O = w16.shape[0]
+    if not (_STEM_S2D[0] and _IGEMM[0] and groups == 1 and C <= 4 and sh == 2 and sw == 2 and dh == 1 and dw == 1
+            and pt == pb and pl == pr and O % 8 == 0 and not needs_dx and kh >= 3 and kw >= 3
+            and x.dtype in (torch.float32, torch.bfloat16)):
+        return None
+    th, tw = (kh + 1) // 2, (kw + 1) // 2
+    R, S = (H + 2 * pt + 1) // 2, (W + 2 * pl + 1) // 2
+    Ho, Wo = (H + 2 * pt - kh) // 2 + 1, (W + 2 * pl - kw) // 2 + 1
+    if R - th + 1 != Ho or S - tw + 1 != Wo:
+        return None
+    return th, tw, R, S, Ho, Wo
+
+
+def _stem_s2d_weight(w4, th, tw):
+    """[O,kh,kw,C] → [O, th*tw*16] with tap (i,j), channel (a*2+b)*C+c holding w[o, 2i+a, 2j+b, c]."""
+    O, kh, kw, C = w4.shape
+    wp = torch.nn.functional.pad(w4, (0, 0, 0, 2 * tw - kw, 0, 2 * th - kh))
+    wp = wp.reshape(O, th, 2, tw, 2, C).permute(0, 1, 3, 2, 4, 5).reshape(O, th, tw, 4 * C)
+    return torch.nn.functional.pad(wp, (0, 16 - 4 * C)).reshape(O, th * tw * 16)
+
+
+def _stem_s2d_forward(ctx, x, weight, bias, w16, geom, relu, scale_w, scale_b, plan):
+    kh, kw = geom[0], geom[1]
+    pt, pl = geom[4], geom[5]
+    th, tw, R, S, Ho, Wo = plan
+    N, C, H, W = x.shape
+    O = w16.shape[0]
+    lib = _lib.cuda_lib()
+    x2 = torch.empty((N, R, S, 16), dtype=torch.bfloat16, device=x.device)
+    st = x.stride()
+    _lib.check(lib.bdl_s2d_stem_bf16(x.data_ptr(), int(x.dtype == torch.float32), x2.data_ptr(), N, C, H, W, st[0],
+                                     st[1], st[2], st[3], pt, pl, R, S, _lib.stream_ptr()), "bdl_s2d_stem_bf16")
+    _lib.count_launch()
+    wk = _stem_s2d_weight(w16.permute(0, 2, 3, 1), th, tw)
+    hint = _take_out_hint()
+    if hint is not None and tuple(hint.shape) == (N, Ho, Wo, O):
+        y, ldy = hint, hint.stride(2)
+    else:
+        y, ldy = torch.empty((N, Ho, Wo, O), dtype=torch.bfloat16, device=x.device), O
+    b32 = bias.detach() if bias is not None else None
+    conv_igemm(0, x2, 16, wk, rows2d(y, ldy), O, Ho, Wo, th, tw, 1, 1, 0, 0, 1, 1, bias=b32, relu=relu)
+    ctx.s2d = (plan, (N, C, H, W, O, kh, kw), ldy)
+    ctx.save_for_backward(x2, y if relu else None)
+    ctx.params = (weight, bias, geom, relu, scale_w, scale_b, None, x.shape)
+    return y.permute(0, 3, 1, 2)
+
+
+def _stem_s2d_backward(ctx, dy):
+    x2, y = ctx.saved_tensors
+    weight, bias, geom, relu, scale_w, scale_b, _, _ = ctx.params
+    (th, tw, R, S, Ho, Wo), (N, C, H, W, O, kh, kw), ldy = ctx.s2d
+    M = N * Ho * Wo
+    dy4, ldd = nhwc_pitched(dy)
+    dyn = rows2d(dy4, ldd)
+    gb = _acc_grad(bias, scale_b)
+    if relu:
+        dz = torch.empty((M, O), dtype=torch.bfloat16, device=dy.device)
+        gtmp = gb if (gb is not None and scale_b == 1.0) else torch.zeros(O, device=dy.device)
+        ew.colsum(dyn, gtmp, rows2d(y, ldy), dz)
+        if gb is not None and scale_b != 1.0:
+            gb.add_(gtmp, alpha=scale_b)
+    else:
+        dz = dyn
+        if gb is not None:
+            if scale_b == 1.0:
+                ew.colsum(dyn, gb)
+            else:
+                gb.add_(ew.colsum(dyn, torch.zeros(O, device=dy.device)), alpha=scale_b)
+    gw = _acc_grad(weight, scale_w)
+    if gw is not None:
+        tmp = torch.zeros((O, th * tw * 16), device=dy.device)
+        conv_igemm(2, x2, 16, dz, tmp, O, Ho, Wo, th, tw, 1, 1, 0, 0, 1, 1, accumulate=True)
+        g = tmp.view(O, th, tw, 16)[..., :4 * C].reshape(O, th, tw, 2, 2, C).permute(0, 1, 3, 2, 4, 5)
+        g = g.reshape(O, 2 * th, 2 * tw, C)[:, :kh, :kw]
+        gw.permute(0, 2, 3, 1).add_(g, alpha=scale_w)
+    return None, None, None, None, None, None, None, None
+
+
 class ConvFn(Function):
     """2-D convolution, NHWC bf16, explicit-GEMM on the tcgen05 kernel (1x1/s1/p0 convs skip im2col entirely)."""
 
     @staticmethod
     def forward(ctx, x, weight, bias, w16, geom, relu, scale_w, scale_b):
         kh, kw, sh, sw, pt, pl, pb, pr, dh, dw, groups = geom
+        ctx.s2d = None
+        plan = _stem_s2d_plan(x, w16, geom, ctx.needs_input_grad[0])
+        if plan is not None:
+            return _stem_s2d_forward(ctx, x, weight, bias, w16, geom, relu, scale_w, scale_b, plan)
         xn, ldx = nhwc_pitched(x)
         N, H, W, C = xn.shape
         O = w16.shape[0]
@@ -270,6 +361,8 @@ class ConvFn(Function):
 
     @staticmethod
     def backward(ctx, dy):
+        if ctx.s2d is not None:
+            return _stem_s2d_backward(ctx, dy)
         xn, w4, y = ctx.saved_tensors
         weight, bias, geom, relu, scale_w, scale_b, dims, xshape = ctx.params
         kh, kw, sh, sw, pt, pl, pb, pr, dh, dw, groups = geom

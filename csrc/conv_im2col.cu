@@ -207,6 +207,60 @@ extern "C" int bdl_im2col_nhwc_bf16(const void* x, void* col, int N, int H, int 
   return bdl_check_launch("im2col_nhwc_kernel");
 }
 
+// Space-to-depth for stride-2 RGB stems: y[n, I, J, (a*2+b)*C + c] = xpad[n, c, 2I+a, 2J+b] where xpad is x with
+// (pt, pl) zero rows/columns in front; channels 4C..15 are zero. A k x k stride-2 convolution over x then equals a
+// ceil(k/2) x ceil(k/2) stride-1 VALID convolution over y with 16 channels, which the TMA-im2col implicit GEMM runs
+// without any patch matrix. One thread writes one 32-byte output pixel; x is read through element strides so NCHW fp32
+// (what the data pipeline delivers) and channels-last bf16 both work without a conversion pass.
+template <typename T>
+__global__ void s2d_stem_kernel(const T* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int C, int H, int W,
+                                long long sn, long long sc, long long sh, long long sw, int pt, int pl, int R,
+                                int S) {
+  const long long total = static_cast<long long>(N) * R * S;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int J = static_cast<int>(i % S);
+    const long long t = i / S;
+    const int I = static_cast<int>(t % R);
+    const int n = static_cast<int>(t / R);
+    alignas(16) __nv_bfloat16 v[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) v[k] = __float2bfloat16_rn(0.f);
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+      const int h = 2 * I + a - pt;
+      if (h < 0 || h >= H) continue;
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        const int w = 2 * J + b - pl;
+        if (w < 0 || w >= W) continue;
+        const T* px = x + n * sn + h * sh + w * sw;
+        for (int c = 0; c < C; ++c) v[(a * 2 + b) * C + c] = __float2bfloat16_rn(static_cast<float>(px[c * sc]));
+      }
+    }
+    uint4* dst = reinterpret_cast<uint4*>(y + i * 16);
+    dst[0] = *reinterpret_cast<const uint4*>(v);
+    dst[1] = *reinterpret_cast<const uint4*>(v + 8);
+  }
+}
+
+extern "C" int bdl_s2d_stem_bf16(const void* x, int x_is_fp32, void* y, int N, int C, int H, int W, long long sn,
+                                 long long sc, long long sh, long long sw, int pt, int pl, int R, int S,
+                                 void* stream) {
+  if (C < 1 || C > 4) return bdl_fail("bdl_s2d_stem_bf16: C must be 1..4");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const long long total = static_cast<long long>(N) * R * S;
+  if (x_is_fp32)
+    s2d_stem_kernel<float><<<grid_for(total), 256, 0, st>>>(static_cast<const float*>(x),
+                                                            static_cast<__nv_bfloat16*>(y), N, C, H, W, sn, sc, sh,
+                                                            sw, pt, pl, R, S);
+  else
+    s2d_stem_kernel<__nv_bfloat16><<<grid_for(total), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x),
+                                                                    static_cast<__nv_bfloat16*>(y), N, C, H, W, sn,
+                                                                    sc, sh, sw, pt, pl, R, S);
+  return bdl_check_launch("s2d_stem_kernel");
+}
+
 extern "C" int bdl_col2im_nhwc_bf16(const void* col, void* dx, int N, int H, int W, int C, int Ho, int Wo, int kh,
                                     int kw, int sh, int sw, int ph, int pw, int dh, int dw, long long ldx, int Kp,
                                     void* stream) {

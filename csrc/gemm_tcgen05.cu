@@ -19,6 +19,8 @@
 // transposes are ever materialised.
 #include <cuda_fp8.h>
 
+#include <cstdlib>
+
 #include "bigdl_b200.h"
 #include "host_common.h"
 #include "ptx.cuh"
@@ -80,6 +82,7 @@ struct GemmParams {
   int cv_flip;               // dgrad: B uses the spatially flipped tap
   int cv_num_kb;             // number of 64-wide k blocks (taps * cblocks for fprop/dgrad, ceil(M/64) for wgrad)
   int cv_nimg;               // batch size of the gathered tensor (first out-of-bounds image index)
+  int cv_aw;                 // channels per gathered atom: 64 (128B swizzle) or, for C <= 32, 32 / 16 (64B / 32B swizzle)
   FastDiv fd_hw, fd_wo, fd_cblocks, fd_kw, fd_c;
 };
 
@@ -218,6 +221,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   const uint32_t tmem_base = tmem_base_slot;
 
   constexpr int KE = kFp8 ? 128 : 64;   // elements per 128-byte k block
+  const bool small_c = kConv != 0 && !kFp8 && p.cv_aw < 64;
   const int num_kb = kConv ? p.cv_num_kb : (p.K + KE - 1) / KE;
   const int tiles_mn = p.tiles_m * p.tiles_n;
   const int total_work = tiles_mn * p.splits;
@@ -241,6 +245,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         int at_c0[4] = {0, 0, 0, 0};
         uint16_t at_ow[4] = {0, 0, 0, 0}, at_oh[4] = {0, 0, 0, 0};
         bool at_ok[4] = {false, false, false, false};
+        uint32_t sm_off[16];
         if (kConv == 1) {
           const uint32_t img = p.fd_hw.quot(static_cast<uint32_t>(m0));
           const uint32_t rem = static_cast<uint32_t>(m0) - img * p.fd_hw.div;
@@ -249,10 +254,21 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           cv_img = static_cast<int>(img);
           cv_h = static_cast<int>(ho) * p.cv_sh - p.cv_ph;
           cv_w = static_cast<int>(wo) * p.cv_sw - p.cv_pw;
-          const uint32_t tap = p.fd_cblocks.quot(static_cast<uint32_t>(kb0));
-          cv_cb = kb0 - static_cast<int>(tap) * p.cv_cblocks;
+          const uint32_t tap = small_c ? static_cast<uint32_t>(kb0 * (64 / p.cv_aw))
+                                       : p.fd_cblocks.quot(static_cast<uint32_t>(kb0));
+          cv_cb = small_c ? 0 : kb0 - static_cast<int>(tap) * p.cv_cblocks;
           cv_r = static_cast<int>(p.fd_kw.quot(tap));
           cv_s = static_cast<int>(tap) - cv_r * p.cv_kw;
+        } else if (kConv == 2 && small_c) {
+          // one atom per filter tap (C <= atom width): atom j of this tile is tap n0 / aw + j
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const uint32_t tap = static_cast<uint32_t>(n0 / p.cv_aw + j);
+            const uint32_t r = p.fd_kw.quot(tap);
+            sm_off[j] = tap < static_cast<uint32_t>(p.cv_kh * p.cv_kw)
+                            ? (((tap - r * p.fd_kw.div) * p.cv_dw) | ((r * p.cv_dh) << 16))
+                            : 0xFFFFFFFFu;
+          }
         } else if (kConv == 2) {
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
@@ -270,9 +286,47 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           const uint32_t fb = smem_u32(&full_bar[stage]);
           const uint32_t sa = tiles + stage * stage_bytes;
           const uint32_t sb = sa + a_bytes;
-          mbar_expect_tx(fb, stage_bytes);
           const int k0 = kb * KE;
-          if (kConv == 1) {
+          if (kConv == 1 && !kBMN && small_c) {
+            // k block = 64 / aw filter taps, each gathered as its own [128 pixels x aw channels] narrow-swizzle region
+            const int tpb = 64 / p.cv_aw;
+            const int taps = p.cv_kh * p.cv_kw;
+            int tap = kb * tpb;
+            const int nv = taps - tap < tpb ? taps - tap : tpb;
+            const uint32_t a_tap = BM * p.cv_aw * 2, b_tap = static_cast<uint32_t>(p.block_n) * p.cv_aw * 2;
+            mbar_expect_tx(fb, nv * (a_tap + b_tap));
+            for (int j = 0; j < nv; ++j, ++tap) {
+              tma_load_im2col_4d(sa + j * a_tap, &tmA, fb, 0, cv_w, cv_h, cv_img,
+                                 static_cast<uint16_t>(cv_s * p.cv_dw), static_cast<uint16_t>(cv_r * p.cv_dh));
+              tma_load_2d(sb + j * b_tap, &tmB, fb, tap * p.cv_C, n0);
+              if (++cv_s == p.cv_kw) {
+                cv_s = 0;
+                ++cv_r;
+              }
+            }
+          } else if (kConv == 2 && small_c) {
+            mbar_expect_tx(fb, stage_bytes);
+            tma_load_2d(sa, &tmA, fb, m0, k0);
+            tma_load_2d(sa + 8192u, &tmA, fb, m0 + 64, k0);
+            const uint32_t img = p.fd_hw.quot(static_cast<uint32_t>(k0));
+            const uint32_t rem = static_cast<uint32_t>(k0) - img * p.fd_hw.div;
+            const uint32_t ho = p.fd_wo.quot(rem);
+            const uint32_t wo = rem - ho * p.fd_wo.div;
+            const int w = static_cast<int>(wo) * p.cv_sw - p.cv_pw, h = static_cast<int>(ho) * p.cv_sh - p.cv_ph;
+            const uint32_t b_atom = 64u * p.cv_aw * 2;
+            const int natoms = p.b_rows / p.cv_aw;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              if (j < natoms) {
+                if (sm_off[j] != 0xFFFFFFFFu)
+                  tma_load_im2col_4d(sb + j * b_atom, &tmB, fb, 0, w, h, static_cast<int>(img),
+                                     static_cast<uint16_t>(sm_off[j] & 0xFFFFu), static_cast<uint16_t>(sm_off[j] >> 16));
+                else
+                  tma_load_im2col_4d(sb + j * b_atom, &tmB, fb, 0, -p.cv_pw, -p.cv_ph, p.cv_nimg, 0, 0);
+              }
+            }
+          } else if (kConv == 1) {
+            mbar_expect_tx(fb, stage_bytes);
             // k block = (filter tap, 64-channel block); A tile = 128 consecutive output pixels of that tap
             tma_load_im2col_4d(sa, &tmA, fb, cv_cb * KE, cv_w, cv_h, cv_img, static_cast<uint16_t>(cv_s * p.cv_dw),
                                static_cast<uint16_t>(cv_r * p.cv_dh));
@@ -294,6 +348,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             }
           } else if (kConv == 2) {
             // wgrad: k block = 64 consecutive output pixels; A = dY^T (MN-major), B atoms = im2col gathers
+            mbar_expect_tx(fb, stage_bytes);
             tma_load_2d(sa, &tmA, fb, m0, k0);
             tma_load_2d(sa + 8192u, &tmA, fb, m0 + 64, k0);
             const uint32_t img = p.fd_hw.quot(static_cast<uint32_t>(k0));
@@ -311,6 +366,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
               }
             }
           } else {
+          mbar_expect_tx(fb, stage_bytes);
           if (kAMN) {
             // A stored [K, M]: two boxes of {64 m, 64 k}
             tma_load_2d(sa, &tmA, fb, m0, k0);
@@ -354,6 +410,25 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           tc_fence_after();
           const uint32_t sa = tiles + stage * stage_bytes;
           const uint32_t sb = sa + a_bytes;
+          if (kConv == 1 && !kBMN && small_c) {
+            const int tpb = 64 / p.cv_aw;
+            const int left = p.cv_kh * p.cv_kw - kb * tpb;
+            const int nv = left < tpb ? left : tpb;
+            const uint32_t a_tap = BM * p.cv_aw * 2, b_tap = static_cast<uint32_t>(p.block_n) * p.cv_aw * 2;
+            const uint32_t sbo = 8u * p.cv_aw * 2, layout = p.cv_aw == 32 ? 4u : 6u;
+            for (int j = 0; j < nv; ++j)
+              for (int k = 0; k < p.cv_aw / 16; ++k)
+                umma_f16(d_tmem, make_smem_desc(sa + j * a_tap + k * 32u, 16u, sbo, layout),
+                         make_smem_desc(sb + j * b_tap + k * 32u, 16u, sbo, layout), idesc,
+                         (kb > kb0 || j > 0 || k > 0) ? 1u : 0u);
+          } else if (kConv == 2 && small_c) {
+            const uint32_t row = p.cv_aw * 2u, layout = p.cv_aw == 32 ? 4u : 6u;
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k)
+              umma_f16(d_tmem, make_smem_desc_sw128(sa + k * 2048u, 8192u, 1024u),
+                       make_smem_desc(sb + k * 16u * row, 64u * row, 8u * row, layout), idesc,
+                       (kb > kb0 || k > 0) ? 1u : 0u);
+          } else {
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
             const uint64_t adesc = kAMN ? make_smem_desc_sw128(sa + k * 2048u, 8192u, 1024u)
@@ -364,6 +439,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
               umma_f8(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
             else
               umma_f16(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
           }
           umma_commit(smem_u32(&empty_bar[stage]));
           if (++stage == p.num_stages) {
@@ -609,8 +685,14 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
   p.fd_wo.init(static_cast<uint32_t>(Wo));
   p.fd_cblocks.init(static_cast<uint32_t>(p.cv_cblocks));
   p.fd_kw.init(static_cast<uint32_t>(kw));
-  // wgrad pads every tap's channel range to whole 64-channel atoms on the GEMM N axis (see EPI_STORE in the kernel)
-  const int c_pad = p.cv_cblocks * 64;
+  // Few-channel inputs (C <= 32: Inception's 5x5 reductions, the space-to-depth RGB stems) are gathered with 32- or
+  // 16-channel boxes into 64B / 32B-swizzled atoms, so a 64-wide k block (fprop) or N atom (wgrad) holds 2 or 4 filter
+  // taps instead of one tap plus zero padding.
+  static const bool small_ok = [] { const char* e = getenv("BDL_IGEMM_SMALLC"); return !(e && e[0] == '0'); }();
+  const int aw = (small_ok && mode != 1 && C <= 32) ? (C <= 16 ? 16 : 32) : 64;
+  p.cv_aw = aw;
+  // wgrad pads every tap's channel range to whole atoms on the GEMM N axis (see EPI_STORE in the kernel)
+  const int c_pad = aw < 64 ? aw : p.cv_cblocks * 64;
   p.fd_c.init(static_cast<uint32_t>(mode == 2 ? c_pad : C));
   int gm, gn;
   if (mode == 2) {
@@ -622,13 +704,14 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
     gm = static_cast<int>(Mpix);
     gn = O;
     p.K = taps * p.cv_cblocks * 64;
-    p.cv_num_kb = taps * p.cv_cblocks;
+    p.cv_num_kb = aw < 64 ? (taps * aw + 63) / 64 : taps * p.cv_cblocks;
   }
   p.M = gm;
   p.N = gn;
   p.block_n = pick_block_n(gm, gn, num_sms);
   const bool b_mn = (mode != 0);
   p.b_rows = b_mn ? ((p.block_n + 63) / 64) * 64 : p.block_n;
+  if (mode == 2 && aw < 64) p.b_rows = ((p.block_n + aw - 1) / aw) * aw;
   p.tiles_m = (gm + BM - 1) / BM;
   p.tiles_n = (gn + p.block_n - 1) / p.block_n;
   const long long tiles_mn = static_cast<long long>(p.tiles_m) * p.tiles_n;
@@ -663,14 +746,14 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
   if (mode == 2) {
     rc = bdl_make_tmap_2d_bf16(&tmA, other, static_cast<uint64_t>(O), static_cast<uint64_t>(Mpix), ld_other, 64, 64);
     if (rc) return rc;
-    rc = bdl_make_tmap_im2col_bf16(&tmB, act, C, W, H, N, ld_act, -pw, -ph, up_w, up_h, 64, 64, sw, sh);
+    rc = bdl_make_tmap_im2col_bf16_sw(&tmB, act, C, W, H, N, ld_act, -pw, -ph, up_w, up_h, aw, 64, sw, sh, aw * 2);
     if (rc) return rc;
   } else {
-    rc = bdl_make_tmap_im2col_bf16(&tmA, act, C, W, H, N, ld_act, -pw, -ph, up_w, up_h, 64, BM, sw, sh);
+    rc = bdl_make_tmap_im2col_bf16_sw(&tmA, act, C, W, H, N, ld_act, -pw, -ph, up_w, up_h, aw, BM, sw, sh, aw * 2);
     if (rc) return rc;
     if (mode == 0)
-      rc = bdl_make_tmap_2d_bf16(&tmB, other, static_cast<uint64_t>(taps) * C, static_cast<uint64_t>(O), ld_other, 64,
-                                 p.block_n);
+      rc = bdl_make_tmap_2d_bf16_sw(&tmB, other, static_cast<uint64_t>(taps) * C, static_cast<uint64_t>(O), ld_other,
+                                    aw, p.block_n, aw * 2);
     else  // weights [Cact rows, taps*O cols]
       rc = bdl_make_tmap_2d_bf16(&tmB, other, static_cast<uint64_t>(taps) * O, static_cast<uint64_t>(C), ld_other, 64,
                                  64);
@@ -715,6 +798,7 @@ extern "C" int bdl_gemm_fp8(const void* A, const void* B, void* D, const float* 
   if (cg) {
     p.cv_Ho = cg[4]; p.cv_Wo = cg[5]; p.cv_kh = cg[6]; p.cv_kw = cg[7]; p.cv_sh = cg[8]; p.cv_sw = cg[9];
     p.cv_ph = cg[10]; p.cv_pw = cg[11]; p.cv_dh = cg[12]; p.cv_dw = cg[13]; p.cv_C = cg[3]; p.cv_nimg = cg[0];
+    p.cv_aw = 64;
     p.cv_cblocks = (cg[3] + 127) / 128;
     p.cv_num_kb = cg[6] * cg[7] * p.cv_cblocks;
     p.fd_hw.init(static_cast<uint32_t>(cg[4]) * cg[5]);

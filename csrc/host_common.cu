@@ -55,8 +55,12 @@ static EncodeTiledFn get_encode_tiled() {
   return fn;
 }
 
+static CUtensorMapSwizzle swizzle_enum(int bytes) {
+  return bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B : bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B;
+}
+
 static int make_tmap_2d(CUtensorMap* out, CUtensorMapDataType dt, int esize, const void* base, uint64_t dim0,
-                        uint64_t dim1, long long ld, uint32_t box0, uint32_t box1) {
+                        uint64_t dim1, long long ld, uint32_t box0, uint32_t box1, int swizzle_bytes = 128) {
   EncodeTiledFn fn = get_encode_tiled();
   if (!fn) return bdl_fail("cuTensorMapEncodeTiled entry point not available (no CUDA driver?)");
   cuuint64_t dims[2] = {dim0, dim1};
@@ -64,7 +68,7 @@ static int make_tmap_2d(CUtensorMap* out, CUtensorMapDataType dt, int esize, con
   cuuint32_t box[2] = {box0, box1};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(out, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                  swizzle_enum(swizzle_bytes), CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     char buf[256];
     snprintf(buf, sizeof(buf),
@@ -78,6 +82,10 @@ static int make_tmap_2d(CUtensorMap* out, CUtensorMapDataType dt, int esize, con
 int bdl_make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t dim0, uint64_t dim1, long long ld, uint32_t box0,
                           uint32_t box1) {
   return make_tmap_2d(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dim0, dim1, ld, box0, box1);
+}
+int bdl_make_tmap_2d_bf16_sw(CUtensorMap* out, const void* base, uint64_t dim0, uint64_t dim1, long long ld,
+                             uint32_t box0, uint32_t box1, int swizzle_bytes) {
+  return make_tmap_2d(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dim0, dim1, ld, box0, box1, swizzle_bytes);
 }
 int bdl_make_tmap_2d_u8(CUtensorMap* out, const void* base, uint64_t dim0, uint64_t dim1, long long ld, uint32_t box0,
                         uint32_t box1) {
@@ -104,13 +112,20 @@ static EncodeIm2colFn get_encode_im2col() {
 
 static int make_tmap_im2col(CUtensorMap* out, CUtensorMapDataType dt, int esize, const void* base, int C, int W, int H,
                            int N, long long ld_pixel, int lower_w, int lower_h, int upper_w, int upper_h,
-                           int channels_per_pixel, int pixels_per_column, int stride_w, int stride_h);
+                           int channels_per_pixel, int pixels_per_column, int stride_w, int stride_h,
+                           int swizzle_bytes = 128);
 
 int bdl_make_tmap_im2col_bf16(CUtensorMap* out, const void* base, int C, int W, int H, int N, long long ld_pixel,
                               int lower_w, int lower_h, int upper_w, int upper_h, int channels_per_pixel,
                               int pixels_per_column, int stride_w, int stride_h) {
   return make_tmap_im2col(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, C, W, H, N, ld_pixel, lower_w, lower_h,
                           upper_w, upper_h, channels_per_pixel, pixels_per_column, stride_w, stride_h);
+}
+int bdl_make_tmap_im2col_bf16_sw(CUtensorMap* out, const void* base, int C, int W, int H, int N, long long ld_pixel,
+                                 int lower_w, int lower_h, int upper_w, int upper_h, int channels_per_pixel,
+                                 int pixels_per_column, int stride_w, int stride_h, int swizzle_bytes) {
+  return make_tmap_im2col(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, C, W, H, N, ld_pixel, lower_w, lower_h,
+                          upper_w, upper_h, channels_per_pixel, pixels_per_column, stride_w, stride_h, swizzle_bytes);
 }
 int bdl_make_tmap_im2col_u8(CUtensorMap* out, const void* base, int C, int W, int H, int N, long long ld_pixel,
                             int lower_w, int lower_h, int upper_w, int upper_h, int channels_per_pixel,
@@ -121,7 +136,8 @@ int bdl_make_tmap_im2col_u8(CUtensorMap* out, const void* base, int C, int W, in
 
 static int make_tmap_im2col(CUtensorMap* out, CUtensorMapDataType dt, int esize, const void* base, int C, int W, int H,
                            int N, long long ld_pixel, int lower_w, int lower_h, int upper_w, int upper_h,
-                           int channels_per_pixel, int pixels_per_column, int stride_w, int stride_h) {
+                           int channels_per_pixel, int pixels_per_column, int stride_w, int stride_h,
+                           int swizzle_bytes) {
   EncodeIm2colFn fn = get_encode_im2col();
   if (!fn) return bdl_fail("cuTensorMapEncodeIm2col entry point not available (no CUDA driver?)");
   cuuint64_t dims[4] = {static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H),
@@ -133,7 +149,7 @@ static int make_tmap_im2col(CUtensorMap* out, CUtensorMapDataType dt, int esize,
   cuuint32_t estr[4] = {1, static_cast<cuuint32_t>(stride_w), static_cast<cuuint32_t>(stride_h), 1};
   CUresult r = fn(out, dt, 4, const_cast<void*>(base), dims, strides, lower, upper,
                   static_cast<cuuint32_t>(channels_per_pixel), static_cast<cuuint32_t>(pixels_per_column), estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_enum(swizzle_bytes), CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     char buf[320];

@@ -20,6 +20,11 @@ CASES = [
     (2, 16, 10, 10, 32, 5, 5, 1, 1, 2, 2, 1, 1),
     (2, 64, 15, 15, 64, 3, 3, 2, 2, 1, 1, 1, 1),      # strided traversal
     (2, 64, 12, 12, 64, 3, 3, 1, 1, 2, 2, 2, 2),      # dilation
+    (2, 32, 14, 14, 64, 5, 5, 1, 1, 2, 2, 1, 1),      # C <= 32: 32-channel atoms, 64B swizzle, 2 taps per k block
+    (2, 24, 14, 14, 64, 5, 5, 1, 1, 2, 2, 1, 1),      # C = 24 inside a 32-channel atom (zero-filled tail)
+    (3, 16, 19, 19, 48, 4, 4, 1, 1, 0, 0, 1, 1),      # 16-channel atoms, 32B swizzle, 4 taps per k block (s2d stem)
+    (2, 8, 12, 12, 32, 3, 3, 1, 1, 1, 1, 1, 1),       # C = 8 inside a 16-channel atom; 9 taps = 2 k blocks + 1 tap
+    (2, 32, 15, 15, 40, 3, 3, 2, 2, 1, 1, 1, 1),      # strided, 64B swizzle
 ]
 
 
@@ -82,3 +87,50 @@ def test_igemm_wgrad(case):
         dy.float().reshape(N, Ho, Wo, O).permute(0, 3, 1, 2))
     ref = 1.0 + wr.grad.permute(0, 2, 3, 1).reshape(O, -1)
     _close(gw, ref, 2e-2, 0.3)
+
+
+@pytest.mark.parametrize("shape", [(4, 3, 64, 64, 64, 7, 3), (2, 3, 56, 40, 32, 5, 2), (2, 1, 28, 28, 16, 3, 1),
+                                   (3, 3, 33, 35, 24, 7, 3)])
+@pytest.mark.parametrize("fp32_in", [True, False])
+def test_stem_space_to_depth_conv(shape, fp32_in):
+    """Stride-2 RGB stem through the space-to-depth + stride-1 implicit GEMM: output, weight and bias gradients vs
+    fp32 conv2d, and vs the explicit im2col path it replaces."""
+    from bigdl_b200.ops import functions as fn
+    N, C, H, W, O, k, p = shape
+    torch.manual_seed(1)
+    x = torch.randn(N, C, H, W, device="cuda")
+    if not fp32_in:
+        x = x.bfloat16().contiguous(memory_format=torch.channels_last)
+    geom = (k, k, 2, 2, p, p, p, p, 1, 1, 1)
+    plan = fn._stem_s2d_plan(x, torch.empty(O, C, k, k), geom, False)
+    outs = []
+    for use in (True, False):
+        fn._STEM_S2D[0] = use
+        try:
+            w = (torch.randn(O, C, k, k, device="cuda", generator=torch.Generator("cuda").manual_seed(2)) * 0.1
+                 ).requires_grad_()
+            b = torch.zeros(O, device="cuda").requires_grad_()
+            w.grad, b.grad = torch.zeros_like(w), torch.zeros_like(b)
+            w16 = w.detach().bfloat16().contiguous(memory_format=torch.channels_last)
+            y = fn.ConvFn.apply(x, w, b, w16, geom, True, 1.0, 1.0)
+            gy = torch.randn(y.shape, device="cuda", generator=torch.Generator("cuda").manual_seed(3)).bfloat16()
+            y.backward(gy)
+            torch.cuda.synchronize()
+            outs.append((y.detach().float(), w.grad.clone(), b.grad.clone()))
+        finally:
+            fn._STEM_S2D[0] = True
+    wr = w16.float().detach().requires_grad_()
+    br = torch.zeros(O, device="cuda", requires_grad=True)
+    # the kernel rounds x to bf16: give the oracle the same values so the ReLU masks agree
+    yr = F.relu(F.conv2d(x.bfloat16().float(), wr, br, 2, p))
+    yr.backward(gy.float())
+    for name, (y, gw, gb) in zip(("s2d", "im2col"), outs):
+        if name == "s2d" and plan is None:
+            continue
+        for what, a, b, atol in (("y", y, yr, 3e-2), ("gw", gw, wr.grad, 0.02 * wr.grad.abs().max().item()),
+                                 ("gb", gb, br.grad, 0.02 * br.grad.abs().max().item())):
+            err = (a.float() - b.float()).abs()
+            assert bool((err <= atol + 3e-2 * b.abs()).all()), \
+                f"{name}/{what}: max err {err.max().item():.4g}, ref max {b.abs().max().item():.4g}"
+    if shape[0] == 4:
+        assert plan is not None

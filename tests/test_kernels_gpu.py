@@ -91,6 +91,25 @@ def test_maxpool(k, s, p, ceil):
     _close(gx.cpu(), xr.grad, 1e-2, 1e-2)
 
 
+@pytest.mark.parametrize("H", [7, 14, 28, 8])
+@pytest.mark.parametrize("s,p,ceil", [(1, 1, False), (2, 0, True), (2, 1, False), (1, 0, False)])
+def test_maxpool3_sliding_window(H, s, p, ceil):
+    """The strip-walking 3x3 kernels at map sizes that are / are not multiples of the 7-row strip."""
+    from bigdl_b200.nn.layers_core import SpatialMaxPooling
+    torch.manual_seed(20)
+    pool = SpatialMaxPooling(3, 3, s, s, p, p, to_ceil=ceil)
+    x = torch.randn(2, 24, H, H + 3, device=DEV).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    y = pool.forward(x)
+    xr = x.float().cpu().requires_grad_(True)
+    yr = pool._call(xr)
+    assert y.shape == yr.shape
+    _close(y.cpu(), yr, 0, 0)
+    go = torch.randn_like(yr).to(torch.bfloat16)
+    gx = pool.backward(x, go.to(DEV))
+    yr.backward(go.float())
+    _close(gx.cpu(), xr.grad, 1e-2, 1e-2)
+
+
 @pytest.mark.parametrize("k,s,p,ceil,cip", [(7, 1, 0, False, True), (5, 3, 0, True, True), (3, 2, 1, False, False)])
 def test_avgpool(k, s, p, ceil, cip):
     from bigdl_b200.nn.layers_core import SpatialAveragePooling
@@ -216,7 +235,7 @@ def test_optim_kernels_match_cpu(name):
         g = torch.randn(n)
         a.update(xc, g.clone())
         b.update(xg, g.to(DEV), w16=w16)
-    _close(xg.cpu(), xc, 1e-5, 1e-6)
+    _close(xg.cpu(), xc, 1e-5, 1e-5)   # host libm vs device rsqrt differ in the last ulps
     assert torch.equal(w16, xg.to(torch.bfloat16))
 
 

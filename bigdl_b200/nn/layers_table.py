@@ -104,15 +104,18 @@ class Concat(Container):
             # replays each branch's backward on the stream its forward ran on.
             main = torch.cuda.current_stream(input.device)
             side = _side_streams(input.device, len(self.modules) - 1)
+        # one fused gradient sum for the fan-out instead of autograd's chain of binary adds
+        xs = Fn.FanOutFn.apply(input, len(self.modules)) if (input.requires_grad and len(self.modules) > 1) \
+            else (input,) * len(self.modules)
         for i, (branch, tail) in enumerate(zip(self.modules, tails)):
             tail._next_out_hint = big[..., c:c + tail.n_output_plane]
             if multi and i > 0:
                 st = side[i - 1]
                 st.wait_stream(main)
                 with torch.cuda.stream(st):
-                    outs.append(branch._call(input))
+                    outs.append(branch._call(xs[i]))
             else:
-                outs.append(branch._call(input))
+                outs.append(branch._call(xs[i]))
             c += tail.n_output_plane
         if multi:
             for st in side:

@@ -66,6 +66,7 @@ _SIGNATURES = {
     "bdl_cast_bf16_to_f32": [_P, _P, _Z, _P],
     "bdl_bf16_trunc_add": [_P, _P, _P, _Z, _P],
     "bdl_eltwise_bf16": [_I, _P, _P, _P, _Z, _F, _P],
+    "bdl_addn_bf16": [_P, _I, _P, _Z, _P],
     "bdl_colsum_bf16": [_P, _P, _P, _P, _L, _I, _L, _L, _L, _P],
     "bdl_dropout_fwd_bf16": [_P, _P, _P, _Z, _F, _U64, _U64, _P],
     "bdl_dropout_bwd_bf16": [_P, _P, _P, _Z, _F, _P],

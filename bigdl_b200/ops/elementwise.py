@@ -71,6 +71,20 @@ def eltwise(op: int, a: torch.Tensor, b: torch.Tensor | None = None, out: torch.
     return out
 
 
+def addn(tensors, out: torch.Tensor | None = None) -> torch.Tensor:
+    """Sum of 2..8 bf16 tensors sharing one dense memory layout, in a single pass (fp32 accumulate)."""
+    import ctypes
+
+    a = tensors[0]
+    if out is None:
+        out = torch.empty_like(a)
+    arr = (ctypes.c_void_p * len(tensors))(*[t.data_ptr() for t in tensors])
+    lib = _lib.cuda_lib()
+    _lib.check(lib.bdl_addn_bf16(arr, len(tensors), out.data_ptr(), a.numel(), _lib.stream_ptr()), "bdl_addn_bf16")
+    _lib.count_launch()
+    return out
+
+
 def colsum(x2d: torch.Tensor, out: torch.Tensor, y2d: torch.Tensor | None = None, dz2d: torch.Tensor | None = None):
     """out[c] += sum_m x[m, c]; with y given, dz = x * (y > 0) is produced and summed (ReLU-bwd + bias-grad fusion)."""
     lib = _lib.cuda_lib()

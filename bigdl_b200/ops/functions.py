@@ -473,6 +473,35 @@ class ConvFn(Function):
         return dx, None, None, None, None, None, None, None
 
 
+class FanOutFn(Function):
+    """Identity that hands the same activation to ``n`` consumers; its backward sums their gradients in ONE kernel
+    instead of autograd's chain of n-1 binary adds (an Inception module input feeds four branches: 5 tensor passes
+    instead of 9). Gradients that are not dense bf16 in a common layout fall back to torch adds."""
+
+    @staticmethod
+    def forward(ctx, x, n):
+        ctx.n = n
+        return tuple(x.view_as(x) for _ in range(n))
+
+    @staticmethod
+    def backward(ctx, *grads):
+        gs = [g for g in grads if g is not None]
+        if not gs:
+            return None, None
+        if len(gs) == 1:
+            return gs[0], None
+        g0 = gs[0]
+        same = all(g.dtype == torch.bfloat16 and g.is_cuda and g.shape == g0.shape and g.stride() == g0.stride()
+                   and g.data_ptr() % 16 == 0 for g in gs)
+        dense = g0.is_contiguous() or (g0.dim() == 4 and g0.is_contiguous(memory_format=torch.channels_last))
+        if same and dense and g0.numel() % 8 == 0 and len(gs) <= 8:
+            return ew.addn(gs), None
+        total = gs[0]
+        for g in gs[1:]:
+            total = total + g
+        return total, None
+
+
 class MaxPoolFn(Function):
     @staticmethod
     def forward(ctx, x, kh, kw, sh, sw, ph, pw, Ho, Wo):

@@ -40,6 +40,17 @@ __device__ __forceinline__ bf16x8 pack8(const float (&f)[8]) {
   return p;
 }
 
+// x[lane] = y[lane] > 0 ? x[lane] : +0 on packed bf16x2 (HSET2 mask + AND)
+__device__ __forceinline__ void relu_mask8(bf16x8& x, const bf16x8& y) {
+  const __nv_bfloat162 z = __floats2bfloat162_rn(0.f, 0.f);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const uint32_t m = __hgt2_mask(y.v[i], z);
+    uint32_t b = *reinterpret_cast<uint32_t*>(&x.v[i]) & m;
+    x.v[i] = *reinterpret_cast<__nv_bfloat162*>(&b);
+  }
+}
+
 // ------------------------------------------------------------------ casts
 template <bool kTruncate>
 __global__ void cast_f32_bf16_kernel(const float* __restrict__ src, uint16_t* __restrict__ dst, size_t n) {
@@ -196,28 +207,23 @@ __global__ void colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, const __
 #pragma unroll
         for (int u = 0; u < kU; ++u) {
           float fx[8];
-          unpack8(vx[u], fx);
           if (kReluBwd) {
-            float fy[8];
-            unpack8(vy[u], fy);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) fx[j] = fy[j] > 0.f ? fx[j] : 0.f;
-            *reinterpret_cast<bf16x8*>(dz + (r + static_cast<long long>(u) * rif) * ldz + cv * 8) = pack8(fx);
+            relu_mask8(vx[u], vy[u]);     // packed: x &= (y > 0) lane mask, no unpack / repack of dz
+            *reinterpret_cast<bf16x8*>(dz + (r + static_cast<long long>(u) * rif) * ldz + cv * 8) = vx[u];
           }
+          unpack8(vx[u], fx);
 #pragma unroll
           for (int j = 0; j < 8; ++j) acc[j] += fx[j];
         }
       }
       for (; r < r1; r += rif) {
         float fx[8];
-        unpack8(*reinterpret_cast<const bf16x8*>(x + r * ldx + cv * 8), fx);
+        bf16x8 vx1 = *reinterpret_cast<const bf16x8*>(x + r * ldx + cv * 8);
         if (kReluBwd) {
-          float fy[8];
-          unpack8(*reinterpret_cast<const bf16x8*>(y + r * ldy + cv * 8), fy);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) fx[j] = fy[j] > 0.f ? fx[j] : 0.f;
-          *reinterpret_cast<bf16x8*>(dz + r * ldz + cv * 8) = pack8(fx);
+          relu_mask8(vx1, *reinterpret_cast<const bf16x8*>(y + r * ldy + cv * 8));
+          *reinterpret_cast<bf16x8*>(dz + r * ldz + cv * 8) = vx1;
         }
+        unpack8(vx1, fx);
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[j] += fx[j];
       }
@@ -436,6 +442,56 @@ extern "C" int bdl_eltwise_bf16(int op, const void* a, const void* b, void* out,
       return bdl_fail("bdl_eltwise_bf16: unknown op");
   }
   return bdl_check_launch("ew_bf16_kernel");
+}
+
+// out = sum of up to 8 dense bf16 tensors (fp32 accumulate): the gradient of an activation that fans out to several
+// branches (an Inception module input feeds four) in one pass instead of a chain of binary adds.
+struct AddNPtrs {
+  const __nv_bfloat16* p[8];
+};
+template <int kN>
+__global__ void addn_bf16_kernel(const AddNPtrs in, __nv_bfloat16* __restrict__ out, size_t n8) {
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n8; i += stride) {
+    bf16x8 v[kN];
+#pragma unroll
+    for (int t = 0; t < kN; ++t) v[t] = reinterpret_cast<const bf16x8*>(in.p[t])[i];
+    float acc[8];
+    unpack8(v[0], acc);
+#pragma unroll
+    for (int t = 1; t < kN; ++t) {
+      float f[8];
+      unpack8(v[t], f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += f[j];
+    }
+    reinterpret_cast<bf16x8*>(out)[i] = pack8(acc);
+  }
+}
+
+extern "C" int bdl_addn_bf16(const void* const* ptrs, int count, void* out, size_t n, void* stream) {
+  if (count < 2 || count > 8) return bdl_fail("bdl_addn_bf16: 2..8 inputs");
+  if (n % 8) return bdl_fail("bdl_addn_bf16: element count must be a multiple of 8");
+  AddNPtrs a{};
+  for (int t = 0; t < count; ++t) {
+    if (reinterpret_cast<uintptr_t>(ptrs[t]) & 15u) return bdl_fail("bdl_addn_bf16: pointers must be 16-byte aligned");
+    a.p[t] = static_cast<const __nv_bfloat16*>(ptrs[t]);
+  }
+  if (reinterpret_cast<uintptr_t>(out) & 15u) return bdl_fail("bdl_addn_bf16: pointers must be 16-byte aligned");
+  if (n == 0) return BDL_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int g = ew_grid(n / 8 + 1);
+  __nv_bfloat16* o = static_cast<__nv_bfloat16*>(out);
+  switch (count) {
+    case 2: addn_bf16_kernel<2><<<g, 256, 0, st>>>(a, o, n / 8); break;
+    case 3: addn_bf16_kernel<3><<<g, 256, 0, st>>>(a, o, n / 8); break;
+    case 4: addn_bf16_kernel<4><<<g, 256, 0, st>>>(a, o, n / 8); break;
+    case 5: addn_bf16_kernel<5><<<g, 256, 0, st>>>(a, o, n / 8); break;
+    case 6: addn_bf16_kernel<6><<<g, 256, 0, st>>>(a, o, n / 8); break;
+    case 7: addn_bf16_kernel<7><<<g, 256, 0, st>>>(a, o, n / 8); break;
+    default: addn_bf16_kernel<8><<<g, 256, 0, st>>>(a, o, n / 8); break;
+  }
+  return bdl_check_launch("addn_bf16_kernel");
 }
 
 extern "C" int bdl_colsum_bf16(const void* x, const void* y, void* dz, float* out, long long M, int C, long long ldx,

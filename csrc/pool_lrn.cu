@@ -259,63 +259,72 @@ __global__ void maxpool3_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const 
     int wo0 = wp - 2;
     wo0 = wo0 <= 0 ? 0 : (wo0 + S - 1) / S;
     const int wo1 = min(wp / S, g.Wo - 1);
-    float a0[8], a1[8], a2[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) a0[j] = a1[j] = a2[j] = 0.f;
+    // accumulators are packed bf16x2: an input element receives one contribution in the common case (exact), and a
+    // few adds otherwise round like the final bf16 store does
+    uint4 a0 = make_uint4(0, 0, 0, 0), a1 = a0, a2 = a0;
     __nv_bfloat16* dcol = dx + (static_cast<long long>(n) * g.H * g.W + w) * g.ldx + cv * 8;
+    const uint4 zero4 = make_uint4(0, 0, 0, 0);
     int next_emit = h0;                             // rows [h0, next_emit) are already written
     for (int ho = ho_first; ho <= ho_last; ++ho) {
       const int hbase = ho * S - g.ph;              // input row of ky = 0
       // rows before hbase that were never reached by any window (only possible at the strip start) are zero
-      for (; next_emit < min(hbase, h1); ++next_emit) {
-        const float z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        store8(dcol + static_cast<long long>(next_emit) * g.W * g.ldx, z);
-      }
+      for (; next_emit < min(hbase, h1); ++next_emit)
+        *reinterpret_cast<uint4*>(dcol + static_cast<long long>(next_emit) * g.W * g.ldx) = zero4;
       for (int wo = wo0; wo <= wo1; ++wo) {
         const uint32_t kx = static_cast<uint32_t>(wp - wo * S);
         const long long opix = (static_cast<long long>(n) * g.Ho + ho) * g.Wo + wo;
-        const uint2 pk = *reinterpret_cast<const uint2*>(idx + opix * g.C + cv * 8);
-        float f[8];
-        load8(dy + opix * g.ldy + cv * 8, f);
+        uint2 pk = *reinterpret_cast<const uint2*>(idx + opix * g.C + cv * 8);
+        const uint4 d = *reinterpret_cast<const uint4*>(dy + opix * g.ldy + cv * 8);
+        // tap byte b -> bf16 lane 0x3F80 | b (1 + b/128, a normal number), compared against the three taps of this
+        // column that land on rows hbase, hbase+1, hbase+2
+        pk.x |= 0x80808080u;
+        pk.y |= 0x80808080u;
+        const uint32_t lanes[4] = {__byte_perm(pk.x, 0x3F3F3F3Fu, 0x4140), __byte_perm(pk.x, 0x3F3F3F3Fu, 0x4342),
+                                   __byte_perm(pk.y, 0x3F3F3F3Fu, 0x4140), __byte_perm(pk.y, 0x3F3F3F3Fu, 0x4342)};
+        const uint32_t t0 = (0x3F80u | kx) * 0x00010001u, t1 = t0 + 0x00030003u, t2 = t0 + 0x00060006u;
+        const uint32_t dq[4] = {d.x, d.y, d.z, d.w};
+        uint32_t* p0 = reinterpret_cast<uint32_t*>(&a0);
+        uint32_t* p1 = reinterpret_cast<uint32_t*>(&a1);
+        uint32_t* p2 = reinterpret_cast<uint32_t*>(&a2);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const uint32_t tap = ((j < 4 ? pk.x : pk.y) >> (8 * (j & 3))) & 0xFFu;
-          a0[j] += tap == kx ? f[j] : 0.f;
-          a1[j] += tap == kx + 3u ? f[j] : 0.f;
-          a2[j] += tap == kx + 6u ? f[j] : 0.f;
+        for (int q = 0; q < 4; ++q) {
+          const __nv_bfloat162 lq = *reinterpret_cast<const __nv_bfloat162*>(&lanes[q]);
+          const uint32_t m0 = __heq2_mask(lq, *reinterpret_cast<const __nv_bfloat162*>(&t0)) & dq[q];
+          const uint32_t m1 = __heq2_mask(lq, *reinterpret_cast<const __nv_bfloat162*>(&t1)) & dq[q];
+          const uint32_t m2 = __heq2_mask(lq, *reinterpret_cast<const __nv_bfloat162*>(&t2)) & dq[q];
+          __nv_bfloat162 s0 = __hadd2(*reinterpret_cast<__nv_bfloat162*>(&p0[q]), *reinterpret_cast<const __nv_bfloat162*>(&m0));
+          __nv_bfloat162 s1 = __hadd2(*reinterpret_cast<__nv_bfloat162*>(&p1[q]), *reinterpret_cast<const __nv_bfloat162*>(&m1));
+          __nv_bfloat162 s2 = __hadd2(*reinterpret_cast<__nv_bfloat162*>(&p2[q]), *reinterpret_cast<const __nv_bfloat162*>(&m2));
+          p0[q] = *reinterpret_cast<uint32_t*>(&s0);
+          p1[q] = *reinterpret_cast<uint32_t*>(&s1);
+          p2[q] = *reinterpret_cast<uint32_t*>(&s2);
         }
       }
       // rows no later output row can reach are complete: hbase .. hbase+S-1
       if (hbase >= h0 && hbase < h1 && hbase >= next_emit) {
-        store8(dcol + static_cast<long long>(hbase) * g.W * g.ldx, a0);
+        *reinterpret_cast<uint4*>(dcol + static_cast<long long>(hbase) * g.W * g.ldx) = a0;
         next_emit = hbase + 1;
       }
       if (S == 2 && hbase + 1 >= h0 && hbase + 1 < h1 && hbase + 1 >= next_emit) {
-        store8(dcol + static_cast<long long>(hbase + 1) * g.W * g.ldx, a1);
+        *reinterpret_cast<uint4*>(dcol + static_cast<long long>(hbase + 1) * g.W * g.ldx) = a1;
         next_emit = hbase + 2;
       }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        if (S == 1) {
-          a0[j] = a1[j];
-          a1[j] = a2[j];
-        } else {
-          a0[j] = a2[j];
-          a1[j] = 0.f;
-        }
-        a2[j] = 0.f;
+      if (S == 1) {
+        a0 = a1;
+        a1 = a2;
+      } else {
+        a0 = a2;
+        a1 = zero4;
       }
+      a2 = zero4;
     }
     // tail: rows still held in the accumulators, then rows below every window
     const int hb = (ho_last + 1) * S - g.ph;        // row that a0 now stands for
     for (; next_emit < h1; ++next_emit) {
-      const float z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-      if (ho_last >= ho_first && next_emit == hb)
-        store8(dcol + static_cast<long long>(next_emit) * g.W * g.ldx, a0);
-      else if (ho_last >= ho_first && S == 1 && next_emit == hb + 1)
-        store8(dcol + static_cast<long long>(next_emit) * g.W * g.ldx, a1);
-      else
-        store8(dcol + static_cast<long long>(next_emit) * g.W * g.ldx, z);
+      uint4 v = zero4;
+      if (ho_last >= ho_first && next_emit == hb) v = a0;
+      else if (ho_last >= ho_first && S == 1 && next_emit == hb + 1) v = a1;
+      *reinterpret_cast<uint4*>(dcol + static_cast<long long>(next_emit) * g.W * g.ldx) = v;
     }
   }
 }

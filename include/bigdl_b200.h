@@ -54,6 +54,8 @@ int bdl_bf16_trunc_add(const void* a, const void* b, void* out, size_t n, void* 
  *           9 scale(alpha), 10 axpy(alpha*a+b), 11 sub, 12 max, 13 relu6 */
 int bdl_eltwise_bf16(int op, const void* a, const void* b, void* out, size_t n, float alpha, void* stream);
 /* out[c] += sum_m x[m,c]; with y != NULL: dz = (y>0 ? x : 0) is written and summed (fused ReLU-bwd + bias grad). */
+/* out = sum of `count` (2..8) dense bf16 tensors of n elements (n % 8 == 0), fp32 accumulate */
+int bdl_addn_bf16(const void* const* ptrs, int count, void* out, size_t n, void* stream);
 int bdl_colsum_bf16(const void* x, const void* y, void* dz, float* out, long long M, int C, long long ldx,
                     long long ldy, long long ldz, void* stream);
 int bdl_dropout_fwd_bf16(const void* x, void* y, void* mask, size_t n, float p, unsigned long long seed,

@@ -264,7 +264,7 @@ class SpatialMaxPooling(Module):
             x = x.permute(0, 3, 1, 2)
         H, W = x.shape[2], x.shape[3]
         ph, pw, Ho, Wo = _pool_geometry(self, H, W)
-        if native(x) and x.shape[1] % 8 == 0:
+        if native(x) and x.shape[1] % 8 == 0 and self.kh * self.kw <= 127:
             from ..ops.functions import MaxPoolFn
 
             y = MaxPoolFn.apply(x, self.kh, self.kw, self.dh, self.dw, ph, pw, Ho, Wo)

@@ -231,10 +231,11 @@ def _stem_s2d_forward(ctx, x, weight, bias, w16, geom, relu, scale_w, scale_b, p
     N, C, H, W = x.shape
     O = w16.shape[0]
     lib = _lib.cuda_lib()
-    x2 = torch.empty((N, R, S, 16), dtype=torch.bfloat16, device=x.device)
+    # horizontal taps folded into channels as well: [N, R, Wo, tw*16] and a th x 1 convolution (full 128-byte gathers)
+    x2 = torch.empty((N, R, Wo, tw * 16), dtype=torch.bfloat16, device=x.device)
     st = x.stride()
     _lib.check(lib.bdl_s2d_stem_bf16(x.data_ptr(), int(x.dtype == torch.float32), x2.data_ptr(), N, C, H, W, st[0],
-                                     st[1], st[2], st[3], pt, pl, R, S, _lib.stream_ptr()), "bdl_s2d_stem_bf16")
+                                     st[1], st[2], st[3], pt, pl, R, Wo, tw, _lib.stream_ptr()), "bdl_s2d_stem_bf16")
     _lib.count_launch()
     wk = _stem_s2d_weight(w16.permute(0, 2, 3, 1), th, tw)
     hint = _take_out_hint()
@@ -243,7 +244,7 @@ def _stem_s2d_forward(ctx, x, weight, bias, w16, geom, relu, scale_w, scale_b, p
     else:
         y, ldy = torch.empty((N, Ho, Wo, O), dtype=torch.bfloat16, device=x.device), O
     b32 = bias.detach() if bias is not None else None
-    conv_igemm(0, x2, 16, wk, rows2d(y, ldy), O, Ho, Wo, th, tw, 1, 1, 0, 0, 1, 1, bias=b32, relu=relu)
+    conv_igemm(0, x2, tw * 16, wk, rows2d(y, ldy), O, Ho, Wo, th, 1, 1, 1, 0, 0, 1, 1, bias=b32, relu=relu)
     ctx.s2d = (plan, (N, C, H, W, O, kh, kw), ldy)
     ctx.save_for_backward(x2, y if relu else None)
     ctx.params = (weight, bias, geom, relu, scale_w, scale_b, None, x.shape)
@@ -274,7 +275,7 @@ def _stem_s2d_backward(ctx, dy):
     gw = _acc_grad(weight, scale_w)
     if gw is not None:
         tmp = torch.zeros((O, th * tw * 16), device=dy.device)
-        conv_igemm(2, x2, 16, dz, tmp, O, Ho, Wo, th, tw, 1, 1, 0, 0, 1, 1, accumulate=True)
+        conv_igemm(2, x2, tw * 16, dz, tmp, O, Ho, Wo, th, 1, 1, 1, 0, 0, 1, 1, accumulate=True)
         g = tmp.view(O, th, tw, 16)[..., :4 * C].reshape(O, th, tw, 2, 2, C).permute(0, 1, 3, 2, 4, 5)
         g = g.reshape(O, 2 * th, 2 * tw, C)[:, :kh, :kw]
         gw.permute(0, 2, 3, 1).add_(g, alpha=scale_w)

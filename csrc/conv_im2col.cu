@@ -207,20 +207,24 @@ extern "C" int bdl_im2col_nhwc_bf16(const void* x, void* col, int N, int H, int 
   return bdl_check_launch("im2col_nhwc_kernel");
 }
 
-// Space-to-depth for stride-2 RGB stems: y[n, I, J, (a*2+b)*C + c] = xpad[n, c, 2I+a, 2J+b] where xpad is x with
-// (pt, pl) zero rows/columns in front; channels 4C..15 are zero. A k x k stride-2 convolution over x then equals a
-// ceil(k/2) x ceil(k/2) stride-1 VALID convolution over y with 16 channels, which the TMA-im2col implicit GEMM runs
-// without any patch matrix. One thread writes one 32-byte output pixel; x is read through element strides so NCHW fp32
-// (what the data pipeline delivers) and channels-last bf16 both work without a conversion pass.
+// Space-to-depth for stride-2 RGB stems, with the horizontal filter taps folded into channels as well:
+//   y[n, I, J, j*16 + (a*2+b)*C + c] = xpad[n, c, 2I+a, 2(J+j)+b]      j < tw, J < Wo, channels 4C..15 of each tap zero
+// where xpad is x with (pt, pl) zero rows/columns in front. A k x k stride-2 convolution over x then equals a
+// ceil(k/2) x 1 stride-1 VALID convolution over y with tw*16 channels (64 for the 7x7 stems), which the TMA-im2col
+// implicit GEMM runs with full 128-byte rows: the gather is bound by rows fetched, not bytes, so 4 taps of 128 B beat
+// 16 taps of 32 B by ~4x. One thread writes one 32-byte tap; x is read through element strides so NCHW fp32 (what the
+// data pipeline delivers) and channels-last bf16 both work without a conversion pass.
 template <typename T>
 __global__ void s2d_stem_kernel(const T* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int C, int H, int W,
                                 long long sn, long long sc, long long sh, long long sw, int pt, int pl, int R,
-                                int S) {
-  const long long total = static_cast<long long>(N) * R * S;
+                                int Wo, int tw) {
+  const long long total = static_cast<long long>(N) * R * Wo * tw;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int J = static_cast<int>(i % S);
-    const long long t = i / S;
+    const int j = static_cast<int>(i % tw);
+    long long t = i / tw;
+    const int J = static_cast<int>(t % Wo);
+    t /= Wo;
     const int I = static_cast<int>(t % R);
     const int n = static_cast<int>(t / R);
     alignas(16) __nv_bfloat16 v[16];
@@ -232,7 +236,7 @@ __global__ void s2d_stem_kernel(const T* __restrict__ x, __nv_bfloat16* __restri
       if (h < 0 || h >= H) continue;
 #pragma unroll
       for (int b = 0; b < 2; ++b) {
-        const int w = 2 * J + b - pl;
+        const int w = 2 * (J + j) + b - pl;
         if (w < 0 || w >= W) continue;
         const T* px = x + n * sn + h * sh + w * sw;
         for (int c = 0; c < C; ++c) v[(a * 2 + b) * C + c] = __float2bfloat16_rn(static_cast<float>(px[c * sc]));
@@ -245,19 +249,19 @@ __global__ void s2d_stem_kernel(const T* __restrict__ x, __nv_bfloat16* __restri
 }
 
 extern "C" int bdl_s2d_stem_bf16(const void* x, int x_is_fp32, void* y, int N, int C, int H, int W, long long sn,
-                                 long long sc, long long sh, long long sw, int pt, int pl, int R, int S,
+                                 long long sc, long long sh, long long sw, int pt, int pl, int R, int Wo, int tw,
                                  void* stream) {
   if (C < 1 || C > 4) return bdl_fail("bdl_s2d_stem_bf16: C must be 1..4");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const long long total = static_cast<long long>(N) * R * S;
+  const long long total = static_cast<long long>(N) * R * Wo * tw;
   if (x_is_fp32)
     s2d_stem_kernel<float><<<grid_for(total), 256, 0, st>>>(static_cast<const float*>(x),
                                                             static_cast<__nv_bfloat16*>(y), N, C, H, W, sn, sc, sh,
-                                                            sw, pt, pl, R, S);
+                                                            sw, pt, pl, R, Wo, tw);
   else
     s2d_stem_kernel<__nv_bfloat16><<<grid_for(total), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x),
                                                                     static_cast<__nv_bfloat16*>(y), N, C, H, W, sn,
-                                                                    sc, sh, sw, pt, pl, R, S);
+                                                                    sc, sh, sw, pt, pl, R, Wo, tw);
   return bdl_check_launch("s2d_stem_kernel");
 }
 

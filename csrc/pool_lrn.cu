@@ -53,38 +53,34 @@ __global__ void maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfl
     t /= g.Wo;
     const int ho = static_cast<int>(t % g.Ho);
     const int n = static_cast<int>(t / g.Ho);
-    float best[8];
-    uint8_t bi[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      best[j] = -INFINITY;
-      bi[j] = 0;
-    }
+    // packed bf16x2 compare/max (bf16 order == fp32 order): 3 instructions per channel pair and tap
+    uint32_t best[4] = {0xFF80FF80u, 0xFF80FF80u, 0xFF80FF80u, 0xFF80FF80u};   // -inf
+    uint32_t bi[4] = {0, 0, 0, 0};                                              // tap index per 16-bit lane
     for (int ky = 0; ky < g.kh; ++ky) {
       const int hi = ho * g.sh - g.ph + ky;
       if (hi < 0 || hi >= g.H) continue;
       for (int kx = 0; kx < g.kw; ++kx) {
         const int wi = wo * g.sw - g.pw + kx;
         if (wi < 0 || wi >= g.W) continue;
-        float f[8];
-        load8(x + ((static_cast<long long>(n) * g.H + hi) * g.W + wi) * g.ldx + cv * 8, f);
-        const uint8_t tap = static_cast<uint8_t>(ky * g.kw + kx);
+        const uint4 v = *reinterpret_cast<const uint4*>(x + ((static_cast<long long>(n) * g.H + hi) * g.W + wi) * g.ldx + cv * 8);
+        const uint32_t f[4] = {v.x, v.y, v.z, v.w};
+        const uint32_t tap = static_cast<uint32_t>(ky * g.kw + kx) * 0x00010001u;
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if (f[j] > best[j]) {
-            best[j] = f[j];
-            bi[j] = tap;
-          }
+        for (int q = 0; q < 4; ++q) {
+          const __nv_bfloat162 fq = *reinterpret_cast<const __nv_bfloat162*>(&f[q]);
+          const __nv_bfloat162 bq = *reinterpret_cast<const __nv_bfloat162*>(&best[q]);
+          const uint32_t gt = __hgt2_mask(fq, bq);
+          const __nv_bfloat162 m = __hmax2(bq, fq);
+          best[q] = *reinterpret_cast<const uint32_t*>(&m);
+          bi[q] = (bi[q] & ~gt) | (tap & gt);
+        }
       }
     }
     const long long opix = (static_cast<long long>(n) * g.Ho + ho) * g.Wo + wo;
-    store8(y + opix * g.ldy + cv * 8, best);
-    if (idx) {
-      uint2 pk;
-      pk.x = bi[0] | (bi[1] << 8) | (bi[2] << 16) | (static_cast<uint32_t>(bi[3]) << 24);
-      pk.y = bi[4] | (bi[5] << 8) | (bi[6] << 16) | (static_cast<uint32_t>(bi[7]) << 24);
-      *reinterpret_cast<uint2*>(idx + opix * g.C + cv * 8) = pk;
-    }
+    *reinterpret_cast<uint4*>(y + opix * g.ldy + cv * 8) = make_uint4(best[0], best[1], best[2], best[3]);
+    if (idx)
+      *reinterpret_cast<uint2*>(idx + opix * g.C + cv * 8) =
+          make_uint2(__byte_perm(bi[0], bi[1], 0x6420), __byte_perm(bi[2], bi[3], 0x6420));
   }
 }
 
@@ -102,7 +98,8 @@ __global__ void maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const u
     t /= g.W;
     const int h = static_cast<int>(t % g.H);
     const int n = static_cast<int>(t / g.H);
-    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    // packed bf16x2 accumulation: exact when windows do not overlap (k == stride), a few roundings otherwise
+    uint32_t acc[4] = {0, 0, 0, 0};
     // output windows covering (h, w): ho in [ceil((h+ph-kh+1)/sh), floor((h+ph)/sh)] — at most ceil(k/s)^2 of them,
     // found with two divisions per axis instead of testing every tap
     const int hp = h + g.ph, wp = w + g.pw;
@@ -119,18 +116,27 @@ __global__ void maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const u
       for (int wo = wo0; wo <= wo1; ++wo) {
         const int kx = wp - wo * g.sw;
         const long long opix = (static_cast<long long>(n) * g.Ho + ho) * g.Wo + wo;
-        const uint2 pk = *reinterpret_cast<const uint2*>(idx + opix * g.C + cv * 8);
-        float f[8];
-        load8(dy + opix * g.ldy + cv * 8, f);
-        const uint32_t tap = static_cast<uint32_t>(ky * g.kw + kx);
+        uint2 pk = *reinterpret_cast<const uint2*>(idx + opix * g.C + cv * 8);
+        const uint4 d = *reinterpret_cast<const uint4*>(dy + opix * g.ldy + cv * 8);
+        // tap byte b -> bf16 lane 0x3F80 | b (a normal number) so HSET2.EQ can compare two channels at once
+        pk.x |= 0x80808080u;
+        pk.y |= 0x80808080u;
+        const uint32_t lanes[4] = {__byte_perm(pk.x, 0x3F3F3F3Fu, 0x4140), __byte_perm(pk.x, 0x3F3F3F3Fu, 0x4342),
+                                   __byte_perm(pk.y, 0x3F3F3F3Fu, 0x4140), __byte_perm(pk.y, 0x3F3F3F3Fu, 0x4342)};
+        const uint32_t want = (0x3F80u | static_cast<uint32_t>(ky * g.kw + kx)) * 0x00010001u;
+        const uint32_t dq[4] = {d.x, d.y, d.z, d.w};
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const uint32_t b = ((j < 4 ? pk.x : pk.y) >> (8 * (j & 3))) & 0xFFu;
-          if (b == tap) acc[j] += f[j];
+        for (int q = 0; q < 4; ++q) {
+          const uint32_t m = __heq2_mask(*reinterpret_cast<const __nv_bfloat162*>(&lanes[q]),
+                                         *reinterpret_cast<const __nv_bfloat162*>(&want)) & dq[q];
+          const __nv_bfloat162 sum = __hadd2(*reinterpret_cast<const __nv_bfloat162*>(&acc[q]),
+                                             *reinterpret_cast<const __nv_bfloat162*>(&m));
+          acc[q] = *reinterpret_cast<const uint32_t*>(&sum);
         }
       }
     }
-    store8(dx + ((static_cast<long long>(n) * g.H + h) * g.W + w) * g.ldx + cv * 8, acc);
+    *reinterpret_cast<uint4*>(dx + ((static_cast<long long>(n) * g.H + h) * g.W + w) * g.ldx + cv * 8) =
+        make_uint4(acc[0], acc[1], acc[2], acc[3]);
   }
 }
 
@@ -635,7 +641,7 @@ extern "C" int bdl_maxpool_fwd_nhwc_bf16(const void* x, void* y, void* idx, int 
   if (check_pool("bdl_maxpool_fwd_nhwc_bf16: C and pitches must be multiples of 8, pointers 16-byte aligned", C, ldx,
                  ldy, x, y))
     return BDL_ERR_INVALID;
-  if (kh * kw > 255) return bdl_fail("bdl_maxpool_fwd_nhwc_bf16: window larger than 255 taps");
+  if (kh * kw > 127) return bdl_fail("bdl_maxpool_fwd_nhwc_bf16: window larger than 127 taps");
   const PoolGeom g = make_pool(N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph, pw, ldx, ldy, 0, 0);
   const long long total = static_cast<long long>(N) * Ho * Wo * (C / 8);
   if (pool3_sliding(kh, kw, sh, sw)) {

@@ -71,9 +71,10 @@ int bdl_copy2d_bf16(const void* src, void* dst, long long rows, int C, long long
 /* ---- NHWC im2col / col2im (csrc/conv_im2col.cu). Reference: S/nn/NNPrimitive.scala:24-1719. */
 int bdl_im2col_nhwc_bf16(const void* x, void* col, int N, int H, int W, int C, int Ho, int Wo, int kh, int kw, int sh,
                          int sw, int ph, int pw, int dh, int dw, long long ldx, int Kp, void* stream);
-/* space-to-depth of a stride-2 RGB stem input into a 16-channel NHWC bf16 tensor [N,R,S,16] (see conv_im2col.cu) */
+/* space-to-depth of a stride-2 RGB stem input, horizontal taps folded into channels: [N,R,Wo,tw*16] bf16 (see
+   conv_im2col.cu) */
 int bdl_s2d_stem_bf16(const void* x, int x_is_fp32, void* y, int N, int C, int H, int W, long long sn, long long sc,
-                      long long sh, long long sw, int pt, int pl, int R, int S, void* stream);
+                      long long sh, long long sw, int pt, int pl, int R, int Wo, int tw, void* stream);
 int bdl_col2im_nhwc_bf16(const void* col, void* dx, int N, int H, int W, int C, int Ho, int Wo, int kh, int kw, int sh,
                          int sw, int ph, int pw, int dh, int dw, long long ldx, int Kp, void* stream);
 

@@ -20,7 +20,7 @@ def train(backend, iters, rank, world, dev):
     from bigdl_b200.utils import config
     from bigdl_b200.utils.random_generator import RNG
 
-    config.set("bigdl.parameter.backend", "nccl" if backend == "parallel" else backend)
+    config.set("bigdl.parameter.backend", {"parallel": "nccl", "parallel_p2p": "p2p"}.get(backend, backend))
     RNG.setSeed(7)
     m = Sequential()
     m.add(SpatialConvolution(8, 32, 3, 3, 1, 1, 1, 1)).add(ReLU()).add(SpatialMaxPooling(2, 2, 2, 2))
@@ -32,7 +32,7 @@ def train(backend, iters, rank, world, dev):
     y = torch.randint(1, 17, (32,), generator=g).float().pin_memory()
     ds = FixedMiniBatchDataSet(MiniBatch(x, y), epoch_size=10 ** 9, distributed=True)
     om = SGD(0.05, momentum=0.9, dampening=0.0)
-    if backend == "parallel":
+    if backend.startswith("parallel"):
         from bigdl_b200.optim.parallel_optimizer import ParallelOptimizer
 
         opt = ParallelOptimizer(m, ds, ClassNLLCriterion(), MaxIteration(iters), 32 * world, om, bucket_mb=0.05)
@@ -56,7 +56,12 @@ def main():
     w_p2p, l_p2p = train("p2p", 8, rank, world, dev)
     w_nccl, l_nccl = train("nccl", 8, rank, world, dev)
     w_par, l_par = train("parallel", 8, rank, world, dev)       # ParallelOptimizer: bucketed async all-reduce
-    diff_par = float((w_par - w_nccl).abs().max())
+    from bigdl_b200.parallel import distri_parameter_synchronizer as dps
+
+    before = dps.P2P_ALLREDUCE_CALLS
+    w_pp, l_pp = train("parallel_p2p", 8, rank, world, dev)     # same, buckets reduced by the one-shot NVLink kernel
+    p2p_calls = dps.P2P_ALLREDUCE_CALLS - before
+    diff_par = max(float((w_par - w_nccl).abs().max()), float((w_pp - w_nccl).abs().max()))
     # all ranks must hold identical compute weights
     ref = w_p2p.clone()
     dist.broadcast(ref, 0)
@@ -68,8 +73,9 @@ def main():
     if rank == 0:
         print(json.dumps({"world": world, "ranks_identical": bool(flags.item()), "p2p_vs_nccl_max_abs_diff": diff,
                           "parallel_vs_nccl_max_abs_diff": diff_par, "weight_scale": scale, "loss_p2p": l_p2p,
-                          "loss_nccl": l_nccl, "loss_parallel": l_par}))
-    ok = bool(flags.item()) and diff <= 2e-2 * scale + 1e-3 and diff_par <= 2e-2 * scale + 1e-3
+                          "loss_nccl": l_nccl, "loss_parallel": l_par, "loss_parallel_p2p": l_pp,
+                          "p2p_bucket_allreduces": p2p_calls}))
+    ok = bool(flags.item()) and diff <= 2e-2 * scale + 1e-3 and diff_par <= 2e-2 * scale + 1e-3 and p2p_calls > 0
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)
 

@@ -20,6 +20,9 @@ import torch
 import torch.distributed as dist
 
 
+P2P_ALLREDUCE_CALLS = 0          # buckets reduced by the peer-memory kernel in this process (diagnostics)
+
+
 @dataclass
 class _Bucket:
     name: str
@@ -37,10 +40,16 @@ class _Bucket:
 
 
 class DistriParameterSynchronizer:
-    def __init__(self, world: int | None = None, compress: str = "auto", group=None):
+    def __init__(self, world: int | None = None, compress: str = "auto", group=None, backend: str | None = None):
         self.world = world if world is not None else (dist.get_world_size() if dist.is_initialized() else 1)
         self.group = group
         self.compress = compress
+        # "p2p": one-shot all-reduce over NVLink peer memory (csrc/comm_fused.cu, reduce + write-back mode of the fused
+        # kernel, flag barriers in peer memory); "nccl": dist.all_reduce on the communication stream (the baseline)
+        from ..utils import config
+
+        self.backend = backend or config.get("bigdl.parameter.backend")
+        self._p2p = None
         self.buckets: dict[str, _Bucket] = {}
         self._order: list[str] = []
         self._comm_stream = None
@@ -76,7 +85,9 @@ class DistriParameterSynchronizer:
             cs = self._comm_stream
             cs.wait_stream(torch.cuda.current_stream(b.grads.device))     # grads were written on the compute stream
             with torch.cuda.stream(cs):
-                if self._use_bf16(b):
+                if self._p2p_ready(b):
+                    self._p2p_allreduce(b)
+                elif self._use_bf16(b):
                     b.payload = b.grads.to(torch.bfloat16)
                     dist.all_reduce(b.payload, group=self.group)
                     b.grads.copy_(b.payload)
@@ -88,6 +99,62 @@ class DistriParameterSynchronizer:
                 b.event.record(cs)
         else:
             b.work = dist.all_reduce(b.grads, group=self.group, async_op=True)
+
+    # ------------------------------------------------------------------ NVLink peer-memory data path
+    def _p2p_ready(self, b: _Bucket) -> bool:
+        if self.backend not in ("auto", "p2p") or self.compress == "none" or not dist.is_initialized():
+            return False
+        if self._p2p is None:
+            try:
+                self._p2p = self._p2p_init(b.grads.device)
+            except Exception as e:            # no peer access between the GPUs of this job: fall back to NCCL
+                if self.backend == "p2p":
+                    raise
+                import logging
+
+                logging.getLogger("bigdl_b200").warning("peer-memory all-reduce unavailable (%s); using NCCL", e)
+                self._p2p = False
+        return bool(self._p2p) and b.offset % 8 == 0 and b.length % 8 == 0
+
+    def _p2p_init(self, device):
+        from .symmetric import SymmetricBuffer
+
+        P = max(b.offset + b.length for b in self.buckets.values())
+        off_flags = (P * 2 + 255) // 256 * 256
+        sym = SymmetricBuffer(off_flags + 256, self.group, device)
+        return {"sym": sym, "g16": sym.view(torch.int16, 0, P), "g16_ptrs": sym.peer_ptr_array(0),
+                "flag_ptrs": sym.peer_ptr_array(off_flags),
+                "local_sync": torch.zeros(2, dtype=torch.int32, device=device),
+                "epoch_dev": torch.zeros(1, dtype=torch.int64, device=device),
+                "rank": dist.get_rank(self.group)}
+
+    def _p2p_allreduce(self, b: _Bucket):
+        """grads[bucket] = mean over ranks, one kernel: every rank loads the bucket's bf16 slice of every peer over
+        NVLink, sums in fp32 in rank order and writes the average back (the one-shot form of S/utils/
+        DistriParameterSynchronizer.scala:234-356's fetch → aggregate → put)."""
+        import ctypes
+
+        from ..ops import _lib
+        from ..optim.optim_method import pack_hp
+        from .all_reduce_parameter import CM_BARRIER_BEGIN, CM_BARRIER_END, CM_REDUCE, CM_WRITE_GRAD
+
+        p = self._p2p
+        lib = _lib.cuda_lib()
+        st = _lib.stream_ptr()
+        g16 = p["g16"][b.offset:b.offset + b.length]
+        _lib.check(lib.bdl_compress_grads(b.grads.data_ptr(), g16.data_ptr(), b.length, 0, 0, st), "bdl_compress_grads")
+        hp = pack_hp(gscale=1.0 / self.world)
+        buf = ctypes.create_string_buffer(hp, len(hp))
+        mode = CM_REDUCE | CM_WRITE_GRAD | CM_BARRIER_BEGIN | CM_BARRIER_END
+        _lib.check(lib.bdl_fused_rs_update(p["g16_ptrs"], None, p["flag_ptrs"], self.world, p["rank"], b.offset,
+                                           b.length, None, b.grads.data_ptr(), None, None, 0,
+                                           ctypes.cast(buf, ctypes.c_void_p), None, mode, 1, p["local_sync"].data_ptr(),
+                                           None, 32, p["epoch_dev"].data_ptr(), st), "bdl_fused_rs_update")
+        _lib.check(lib.bdl_counter_add(p["epoch_dev"].data_ptr(), 1, st), "bdl_counter_add")
+        _lib.count_launch(3)
+        b.stats["p2p"] = b.stats.get("p2p", 0) + 1
+        global P2P_ALLREDUCE_CALLS
+        P2P_ALLREDUCE_CALLS += 1
 
     def get(self, name: str):
         """Wait until ``name``'s averaged gradients are available; returns ``(weights, grads)`` views, or ``None``

@@ -68,7 +68,12 @@ class _Engine:
             return int(conf)
         if self.device.type == "cuda":
             return torch.cuda.get_device_properties(self.device).multi_processor_count
-        return os.cpu_count() or 1
+        try:      # physical cores, like the reference's Engine (hyper-threads do not help the BLAS-bound CPU path)
+            from . import native
+
+            return native.physical_cores()
+        except Exception:
+            return os.cpu_count() or 1
 
     core_number = coreNumber
 

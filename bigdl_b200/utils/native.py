@@ -31,6 +31,8 @@ def lib():
             "bdlh_quantize_rows_int8": ([P, P, P, I, I], None),
             "bdlh_int8_gemm": ([P, P, P, P, P, P, I, I, I], None),
             "bdlh_version": ([], C.c_char_p),
+            "bdlh_set_affinity": ([P, I], I), "bdlh_get_affinity": ([P, I], I),
+            "bdlh_logical_cores": ([], I), "bdlh_physical_cores": ([], I),
         }
         for name, (args, res) in sigs.items():
             fn = getattr(h, name)
@@ -193,3 +195,27 @@ def pool_size() -> int:
 
 def pool_resize(n: int):
     lib().bdlh_pool_resize(int(n))
+
+
+def set_affinity(cpus) -> None:
+    """Pin the calling thread to the given logical CPUs (reference: MklDnn.setAffinity, affinity.c)."""
+    arr = (C.c_int * len(cpus))(*[int(c) for c in cpus])
+    if lib().bdlh_set_affinity(arr, len(cpus)) != 0:
+        raise OSError("sched_setaffinity failed")
+
+
+def get_affinity() -> list[int]:
+    arr = (C.c_int * 4096)()
+    n = lib().bdlh_get_affinity(arr, 4096)
+    if n < 0:
+        raise OSError("sched_getaffinity failed")
+    return [arr[i] for i in range(min(n, 4096))]
+
+
+def logical_cores() -> int:
+    return int(lib().bdlh_logical_cores())
+
+
+def physical_cores() -> int:
+    """Distinct (package, core) pairs — what the reference's Engine uses for its default core number."""
+    return int(lib().bdlh_physical_cores())

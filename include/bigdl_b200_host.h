@@ -12,6 +12,11 @@ extern "C" {
 #endif
 
 /* ---- thread pool (S/utils/ThreadPool.scala, Engine.default/Engine.model) */
+/* CPU affinity / topology (csrc/host/affinity.cpp). Reference: C/native-dnn/src/main/c/affinity.c, native_utils.c */
+int bdlh_set_affinity(const int* cpus, int n);
+int bdlh_get_affinity(int* cpus, int cap);
+int bdlh_logical_cores(void);
+int bdlh_physical_cores(void);
 int bdlh_pool_size(void);
 void bdlh_pool_resize(int threads);
 

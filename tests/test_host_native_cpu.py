@@ -138,3 +138,16 @@ def test_optimizer_writes_summaries(tmp_path):
     opt.optimize()
     assert len(ts.readScalar("Loss")) == 6 and len(ts.readScalar("LearningRate")) == 6
     ts.close()
+
+
+def test_affinity_and_core_counts():
+    from bigdl_b200.utils import native
+    cur = native.get_affinity()
+    assert cur and all(isinstance(c, int) for c in cur)
+    assert 1 <= native.physical_cores() <= native.logical_cores()
+    native.set_affinity(cur[:1])
+    try:
+        assert native.get_affinity() == cur[:1]
+    finally:
+        native.set_affinity(cur)
+    assert native.get_affinity() == cur

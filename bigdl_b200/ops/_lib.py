@@ -71,6 +71,7 @@ _SIGNATURES = {
     "bdl_dropout_fwd_bf16": [_P, _P, _P, _Z, _F, _U64, _U64, _P],
     "bdl_dropout_bwd_bf16": [_P, _P, _P, _Z, _F, _P],
     "bdl_copy2d_bf16": [_P, _P, _L, _I, _L, _L, _I, _P],
+    "bdl_image_batch_u8": [_P, _P, _P, _P] + [_I] * 6 + [_P, _P, _I, _I, _P],
     "bdl_s2d_stem_bf16": [_P, _I, _P] + [_I] * 4 + [_L] * 4 + [_I] * 5 + [_P],
     "bdl_im2col_nhwc_bf16": [_P, _P] + [_I] * 14 + [_L, _I, _P],
     "bdl_col2im_nhwc_bf16": [_P, _P] + [_I] * 14 + [_L, _I, _P],

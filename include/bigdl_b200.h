@@ -68,6 +68,11 @@ int bdl_dropout_bwd_bf16(const void* dy, const void* mask, void* dx, size_t n, f
 int bdl_copy2d_bf16(const void* src, void* dst, long long rows, int C, long long lds, long long ldd, int accumulate,
                     void* stream);
 
+/* ---- input pipeline on the GPU (csrc/data_ops.cu): uint8 HWC frames -> crop + flip + normalise -> bf16/fp32 batch.
+ *      crop_xy: [N,2] int32 device (x0,y0) or NULL = centre crop; flip: [N] uint8 device or NULL. */
+int bdl_image_batch_u8(const void* src_u8, void* dst, const int* crop_xy, const void* flip, int N, int H, int W, int C,
+                       int Hc, int Wc, const float* mean, const float* std_, int out_fp32, int out_nchw, void* stream);
+
 /* ---- NHWC im2col / col2im (csrc/conv_im2col.cu). Reference: S/nn/NNPrimitive.scala:24-1719. */
 int bdl_im2col_nhwc_bf16(const void* x, void* col, int N, int H, int W, int C, int Ho, int Wo, int kh, int kw, int sh,
                          int sw, int ph, int pw, int dh, int dw, long long ldx, int Kp, void* stream);

@@ -178,3 +178,19 @@ def test_vision_frame_transformers(tmp_path):
     batches = list(V.MTImageFeatureToBatch(32, 32, 3, to_rgb=False)(
         V.LocalImageFrame([V.ImageFeature(im[:32, :32].copy(), [float(i + 1)]) for i, im in enumerate(imgs)])))
     assert [bt.size() for bt in batches] == [3, 1] and batches[0].getTarget().tolist() == [1.0, 2.0, 3.0]
+
+
+def test_gpu_image_batcher_cpu_path_is_deterministic_and_normalised():
+    import torch
+    from bigdl_b200.ops.data import GPUImageBatcher, image_batch
+    from bigdl_b200.utils.random_generator import RNG
+
+    frames = torch.randint(0, 256, (6, 36, 40, 3), dtype=torch.uint8)
+    RNG.setSeed(3)
+    a = GPUImageBatcher(32, 32, (100, 110, 120), (50, 55, 60), train=True, dtype=torch.float32)(frames)
+    RNG.setSeed(3)
+    b = GPUImageBatcher(32, 32, (100, 110, 120), (50, 55, 60), train=True, dtype=torch.float32)(frames)
+    assert a.shape == (6, 3, 32, 32) and torch.equal(a, b)
+    c = image_batch(frames, 32, 32, (100, 110, 120), (50, 55, 60), dtype=torch.float32)
+    ref = (frames[:, 2:34, 4:36].float() - torch.tensor([100., 110., 120.])) / torch.tensor([50., 55., 60.])
+    assert torch.allclose(c, ref.permute(0, 3, 1, 2))

@@ -312,3 +312,22 @@ def test_recurrent_lstm_on_gpu_matches_cpu():
     gx = r.backward(x.cuda().to(torch.bfloat16), go.cuda().to(torch.bfloat16))
     gr = ref.backward(x, go)
     _close(gx.cpu(), gr, 8e-2, 8e-2)
+
+
+@pytest.mark.parametrize("layout", ["nhwc", "nchw"])
+def test_gpu_image_batch_matches_torch(layout):
+    """uint8 frames -> crop + flip + normalise on the device vs the torch restatement of the same pipeline."""
+    from bigdl_b200.ops.data import _image_batch_torch, image_batch
+    torch.manual_seed(30)
+    frames = torch.randint(0, 256, (5, 40, 48, 3), dtype=torch.uint8)
+    crop = torch.tensor([[0, 0], [16, 8], [3, 5], [16, 0], [7, 8]], dtype=torch.int32)
+    flip = torch.tensor([0, 1, 1, 0, 1], dtype=torch.uint8)
+    mean, std = (104.0, 117.0, 123.0), (58.0, 57.0, 57.5)
+    cl = layout == "nhwc"
+    for dt in (torch.float32, torch.bfloat16):
+        got = image_batch(frames.to(DEV), 32, 32, mean, std, crop, flip, dt, cl)
+        ref = _image_batch_torch(frames, 32, 32, mean, std, crop, flip, torch.float32, cl)
+        assert got.shape == ref.shape == (5, 3, 32, 32)
+        _close(got.float().cpu(), ref, 1e-2 if dt == torch.bfloat16 else 1e-6, 1e-5)
+    centre = image_batch(frames.to(DEV), 32, 32, mean, std, None, None, torch.float32, cl)
+    _close(centre.cpu(), _image_batch_torch(frames, 32, 32, mean, std, None, None, torch.float32, cl), 1e-6, 1e-5)

@@ -174,6 +174,14 @@ class GRU(Cell):
     def step(self, xt, hidden):
         h = hidden[0]
         H = self.hidden_size
+        if xt.is_cuda and self.activation is None and self.inner_activation is None and xt.dtype == torch.bfloat16:
+            # two fused pointwise kernels around the two recurrent GEMMs (csrc/recurrent.cu)
+            from ..ops.recurrent import gru_out, gru_rz
+
+            hb = h if h.dtype == torch.bfloat16 else h.to(torch.bfloat16)
+            z, hr = gru_rz(xt[:, :2 * H], self.h2g._call(hb), hb)
+            h2 = gru_out(xt[:, 2 * H:], self.h2c._call(hr), z, hb)
+            return h2, [h2]
         inner = torch.sigmoid if self.inner_activation is None else self.inner_activation._call
         act = torch.tanh if self.activation is None else self.activation._call
         rz = inner(xt[:, :2 * H] + self.h2g._call(h))

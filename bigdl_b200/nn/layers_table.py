@@ -105,8 +105,12 @@ class Concat(Container):
             main = torch.cuda.current_stream(input.device)
             side = _side_streams(input.device, len(self.modules) - 1)
         # one fused gradient sum for the fan-out instead of autograd's chain of binary adds
-        xs = Fn.FanOutFn.apply(input, len(self.modules)) if (input.requires_grad and len(self.modules) > 1) \
-            else (input,) * len(self.modules)
+        if input.requires_grad and len(self.modules) > 1:
+            gf = input.grad_fn      # the previous zero-copy Concat, if this input is its fused-ReLU output
+            prod = gf if (type(gf).__name__ == "ConcatViewFnBackward" and getattr(gf, "relu_all", False)) else None
+            xs = Fn.FanOutFn.apply(input, len(self.modules), prod)
+        else:
+            xs = (input,) * len(self.modules)
         for i, (branch, tail) in enumerate(zip(self.modules, tails)):
             tail._next_out_hint = big[..., c:c + tail.n_output_plane]
             if multi and i > 0:
@@ -120,7 +124,8 @@ class Concat(Container):
         if multi:
             for st in side:
                 main.wait_stream(st)
-        return Fn.ConcatViewFn.apply(big, *outs)
+        relu_all = all(bool(getattr(t, "_fuse_relu", False)) for t in tails)
+        return Fn.ConcatViewFn.apply(big, relu_all, *outs)
 
 
 class ConcatTable(Container):

@@ -67,11 +67,16 @@ _SIGNATURES = {
     "bdl_bf16_trunc_add": [_P, _P, _P, _Z, _P],
     "bdl_eltwise_bf16": [_I, _P, _P, _P, _Z, _F, _P],
     "bdl_addn_bf16": [_P, _I, _P, _Z, _P],
+    "bdl_colsum_sumn_relu_bf16": [_P, _I, _P, _P, _P, _L, _I, _P],
     "bdl_colsum_bf16": [_P, _P, _P, _P, _L, _I, _L, _L, _L, _P],
     "bdl_dropout_fwd_bf16": [_P, _P, _P, _Z, _F, _U64, _U64, _P],
     "bdl_dropout_bwd_bf16": [_P, _P, _P, _Z, _F, _P],
     "bdl_copy2d_bf16": [_P, _P, _L, _I, _L, _L, _I, _P],
     "bdl_image_batch_u8": [_P, _P, _P, _P] + [_I] * 6 + [_P, _P, _I, _I, _P],
+    "bdl_gru_rz_fwd": [_P] * 5 + [_L, _I, _L, _L, _P],
+    "bdl_gru_rz_bwd": [_P] * 6 + [_L, _I, _L, _P],
+    "bdl_gru_out_fwd": [_P] * 6 + [_L, _I, _L, _L, _L, _P],
+    "bdl_gru_out_bwd": [_P] * 7 + [_L, _I, _L, _L, _P],
     "bdl_s2d_stem_bf16": [_P, _I, _P] + [_I] * 4 + [_L] * 4 + [_I] * 5 + [_P],
     "bdl_im2col_nhwc_bf16": [_P, _P] + [_I] * 14 + [_L, _I, _P],
     "bdl_col2im_nhwc_bf16": [_P, _P] + [_I] * 14 + [_L, _I, _P],

@@ -85,6 +85,20 @@ def addn(tensors, out: torch.Tensor | None = None) -> torch.Tensor:
     return out
 
 
+def colsum_sum_relu(tensors, y: torch.Tensor, dz: torch.Tensor, out: torch.Tensor):
+    """dz = (y > 0) * sum(tensors); out[c] += column sums of dz. All dense, same layout, [.., C] innermost."""
+    import ctypes
+
+    C = out.numel()
+    M = y.numel() // C
+    arr = (ctypes.c_void_p * len(tensors))(*[t.data_ptr() for t in tensors])
+    lib = _lib.cuda_lib()
+    _lib.check(lib.bdl_colsum_sumn_relu_bf16(arr, len(tensors), y.data_ptr(), dz.data_ptr(), out.data_ptr(), M, C,
+                                             _lib.stream_ptr()), "bdl_colsum_sumn_relu_bf16")
+    _lib.count_launch()
+    return dz
+
+
 def colsum(x2d: torch.Tensor, out: torch.Tensor, y2d: torch.Tensor | None = None, dz2d: torch.Tensor | None = None):
     """out[c] += sum_m x[m, c]; with y given, dz = x * (y > 0) is produced and summed (ReLU-bwd + bias-grad fusion)."""
     lib = _lib.cuda_lib()

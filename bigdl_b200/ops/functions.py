@@ -40,7 +40,9 @@ def _wgrad_side(device):
 
 
 def join_side_streams(device=None):
-    """Make the current stream wait for every outstanding side-stream weight-gradient GEMM."""
+    """Make the current stream wait for every outstanding side-stream weight-gradient GEMM (and drop per-backward
+    side-channel state)."""
+    _PREMASKED.clear()
     if not _WGRAD_KEEP:
         return
     cur = torch.cuda.current_stream(device)
@@ -105,22 +107,51 @@ def _take_out_hint():
     return h
 
 
+# Gradients that already had a consumer's ReLU mask applied and its bias gradient summed, keyed by (data_ptr, shape):
+# ConcatViewFn.backward does that once for all branch tails of a Concat; the tails' ConvFn.backward picks its slice up
+# here instead of running its own column-sum pass. Cleared after every backward (join_side_streams).
+_PREMASKED: dict = {}
+
+
 class ConcatViewFn(Function):
     """The branches already wrote into channel slices of ``big`` ([N,H,W,Ctot]); expose it as one NCHW tensor whose
-    gradient is handed back to the branches as (pitched) channel slices — no copies in either direction."""
+    gradient is handed back to the branches as (pitched) channel slices — no copies in either direction.
+
+    When every branch ends in a conv with fused bias + ReLU (``relu_all``: ``big`` then IS the ReLU output of all of
+    them), the backward runs ONE fused ReLU-mask + bias-gradient column sum over the full width instead of one narrow,
+    pitched pass per branch (four per Inception module), and hands out slices of the masked gradient."""
 
     @staticmethod
-    def forward(ctx, big, *outs):
+    def forward(ctx, big, relu_all, *outs):
         ctx.sizes = [o.shape[1] for o in outs]
+        ctx.relu_all = bool(relu_all)
+        if ctx.relu_all:
+            ctx.save_for_backward(big)
         return big.permute(0, 3, 1, 2)
 
     @staticmethod
     def backward(ctx, g):
+        ready = ctx.__dict__.pop("_ready", None)
+        if ready is not None and ready[0].data_ptr() == g.data_ptr() and tuple(g.shape[2:]) == tuple(ready[0].shape[1:3]):
+            sums = ready[1]              # the consumer's fan-out node already summed, masked and column-summed
+        elif ctx.relu_all and g.is_cuda and g.dtype == torch.bfloat16:
+            (big,) = ctx.saved_tensors
+            gn, ld = nhwc_pitched(g)
+            N, H, W, Ct = gn.shape
+            dz = torch.empty((N, H, W, Ct), dtype=torch.bfloat16, device=g.device)
+            sums = torch.zeros(Ct, dtype=torch.float32, device=g.device)
+            ew.colsum(rows2d(gn, ld), sums, rows2d(big, Ct), rows2d(dz, Ct))
+            g = dz.permute(0, 3, 1, 2)
+        else:
+            sums = None
         grads, c = [], 0
         for n in ctx.sizes:
-            grads.append(g[:, c:c + n])
+            sl = g[:, c:c + n]
+            if sums is not None:
+                _PREMASKED[(sl.data_ptr(), tuple(sl.shape))] = sums[c:c + n]
+            grads.append(sl)
             c += n
-        return (None, *grads)
+        return (None, None, *grads)
 
 
 def _acc_grad(param: torch.Tensor, scale: float):
@@ -374,7 +405,14 @@ class ConvFn(Function):
         dy4, ldd = nhwc_pitched(dy)
         dyn = rows2d(dy4, ldd)
         gb = _acc_grad(bias, scale_b)
-        if relu:
+        pre = _PREMASKED.pop((dy.data_ptr(), tuple(dy.shape)), None) if (relu and _PREMASKED) else None
+        if pre is not None:
+            # the Concat above already masked this slice with our ReLU output and summed its columns
+            dz = dyn
+            if gb is not None:
+                pre.record_stream(torch.cuda.current_stream(dy.device))
+                gb.add_(pre, alpha=scale_b)
+        elif relu:
             dz = torch.empty((M, O), dtype=torch.bfloat16, device=dy.device)
             gtmp = gb if (gb is not None and scale_b == 1.0) else torch.zeros(O, device=dy.device)
             ew.colsum(dyn, gtmp, rows2d(y, ldy), dz)
@@ -477,30 +515,48 @@ class ConvFn(Function):
 class FanOutFn(Function):
     """Identity that hands the same activation to ``n`` consumers; its backward sums their gradients in ONE kernel
     instead of autograd's chain of n-1 binary adds (an Inception module input feeds four branches: 5 tensor passes
-    instead of 9). Gradients that are not dense bf16 in a common layout fall back to torch adds."""
+    instead of 9). Gradients that are not dense bf16 in a common layout fall back to torch adds.
+
+    ``producer``: the ConcatViewFn node that produced ``x`` when ``x`` is the fused-ReLU output of a zero-copy Concat.
+    Then the sum, that Concat's ReLU mask and its bias-gradient column sums are one kernel; the masked gradient is
+    parked on the producer node, which recognises it (by address) and skips its own pass."""
 
     @staticmethod
-    def forward(ctx, x, n):
+    def forward(ctx, x, n, producer=None):
         ctx.n = n
+        ctx.producer = producer
+        if producer is not None:
+            ctx.save_for_backward(x)
         return tuple(x.view_as(x) for _ in range(n))
 
     @staticmethod
     def backward(ctx, *grads):
         gs = [g for g in grads if g is not None]
         if not gs:
-            return None, None
-        if len(gs) == 1:
-            return gs[0], None
+            return None, None, None
         g0 = gs[0]
         same = all(g.dtype == torch.bfloat16 and g.is_cuda and g.shape == g0.shape and g.stride() == g0.stride()
                    and g.data_ptr() % 16 == 0 for g in gs)
         dense = g0.is_contiguous() or (g0.dim() == 4 and g0.is_contiguous(memory_format=torch.channels_last))
+        prod = ctx.producer
+        if (prod is not None and same and 2 <= len(gs) <= 4 and g0.dim() == 4
+                and g0.is_contiguous(memory_format=torch.channels_last) and g0.shape[1] % 8 == 0):
+            (x,) = ctx.saved_tensors
+            if x.is_contiguous(memory_format=torch.channels_last) and x.dtype == torch.bfloat16:
+                N, Ct, H, W = g0.shape
+                dz = torch.empty((N, H, W, Ct), dtype=torch.bfloat16, device=g0.device)
+                sums = torch.zeros(Ct, dtype=torch.float32, device=g0.device)
+                ew.colsum_sum_relu(gs, x, dz, sums)
+                prod._ready = (dz, sums)
+                return dz.permute(0, 3, 1, 2), None, None
+        if len(gs) == 1:
+            return gs[0], None, None
         if same and dense and g0.numel() % 8 == 0 and len(gs) <= 8:
-            return ew.addn(gs), None
+            return ew.addn(gs), None, None
         total = gs[0]
         for g in gs[1:]:
             total = total + g
-        return total, None
+        return total, None, None
 
 
 class MaxPoolFn(Function):

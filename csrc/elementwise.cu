@@ -469,6 +469,131 @@ __global__ void addn_bf16_kernel(const AddNPtrs in, __nv_bfloat16* __restrict__ 
   }
 }
 
+// Fan-out gradient sum + ReLU backward + bias gradient in one pass: z = (y > 0) ? sum_t in_t : 0 is written to dz and
+// column-summed into out. All tensors are dense [M, C] (C % 8 == 0). Same thread layout as colsum_bf16_kernel.
+template <int kN>
+__global__ void colsum_sumn_relu_kernel(const AddNPtrs in, const __nv_bfloat16* __restrict__ y,
+                                        __nv_bfloat16* __restrict__ dz, float* __restrict__ out, long long M, int C,
+                                        int rows_per_block) {
+  extern __shared__ float red[];
+  const int cvec = C / 8;
+  const int vcols = cvec < static_cast<int>(blockDim.x) ? cvec : blockDim.x;
+  const int rif = blockDim.x / vcols;
+  const int tc = threadIdx.x % vcols;
+  const int tr = threadIdx.x / vcols;
+  const long long r0 = static_cast<long long>(blockIdx.x) * rows_per_block;
+  long long r1 = r0 + rows_per_block;
+  if (r1 > M) r1 = M;
+  for (int cv = tc; cv < cvec; cv += vcols) {
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (tr < rif) {
+      constexpr int kU = 2;
+      long long r = r0 + tr;
+      for (; r + (kU - 1ll) * rif < r1; r += static_cast<long long>(kU) * rif) {
+        bf16x8 v[kU][kN], vy[kU];
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+          const long long off = (r + static_cast<long long>(u) * rif) * C + cv * 8;
+#pragma unroll
+          for (int t = 0; t < kN; ++t) v[u][t] = *reinterpret_cast<const bf16x8*>(in.p[t] + off);
+          vy[u] = *reinterpret_cast<const bf16x8*>(y + off);
+        }
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+          float s[8];
+          unpack8(v[u][0], s);
+#pragma unroll
+          for (int t = 1; t < kN; ++t) {
+            float f[8];
+            unpack8(v[u][t], f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) s[j] += f[j];
+          }
+          bf16x8 z = pack8(s);
+          relu_mask8(z, vy[u]);
+          *reinterpret_cast<bf16x8*>(dz + (r + static_cast<long long>(u) * rif) * C + cv * 8) = z;
+          unpack8(z, s);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] += s[j];
+        }
+      }
+      for (; r < r1; r += rif) {
+        const long long off = r * C + cv * 8;
+        float s[8];
+        unpack8(*reinterpret_cast<const bf16x8*>(in.p[0] + off), s);
+#pragma unroll
+        for (int t = 1; t < kN; ++t) {
+          float f[8];
+          unpack8(*reinterpret_cast<const bf16x8*>(in.p[t] + off), f);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) s[j] += f[j];
+        }
+        bf16x8 z = pack8(s);
+        relu_mask8(z, *reinterpret_cast<const bf16x8*>(y + off));
+        *reinterpret_cast<bf16x8*>(dz + off) = z;
+        unpack8(z, s);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += s[j];
+      }
+    }
+    __syncthreads();
+    if (tr < rif) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) red[(tr * vcols + tc) * 8 + j] = acc[j];
+    }
+    __syncthreads();
+    if (tr == 0) {
+      float s8[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float sum = 0.f;
+        for (int t = 0; t < rif; ++t) sum += red[(t * vcols + tc) * 8 + j];
+        s8[j] = sum;
+      }
+      float* dst = out + cv * 8;
+      if ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0) {
+        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(s8[0]), "f"(s8[1]), "f"(s8[2]),
+                     "f"(s8[3]) : "memory");
+        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + 4), "f"(s8[4]), "f"(s8[5]), "f"(s8[6]),
+                     "f"(s8[7]) : "memory");
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) atomicAdd(dst + j, s8[j]);
+      }
+    }
+  }
+}
+
+extern "C" int bdl_colsum_sumn_relu_bf16(const void* const* ptrs, int count, const void* y, void* dz, float* out,
+                                         long long M, int C, void* stream) {
+  if (count < 2 || count > 4) return bdl_fail("bdl_colsum_sumn_relu_bf16: 2..4 addends");
+  if (C % 8) return bdl_fail("bdl_colsum_sumn_relu_bf16: C must be a multiple of 8");
+  if (M <= 0) return BDL_OK;
+  AddNPtrs a{};
+  for (int t = 0; t < count; ++t) {
+    if (reinterpret_cast<uintptr_t>(ptrs[t]) & 15u) return bdl_fail("bdl_colsum_sumn_relu_bf16: unaligned addend");
+    a.p[t] = static_cast<const __nv_bfloat16*>(ptrs[t]);
+  }
+  if ((reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(dz)) & 15u)
+    return bdl_fail("bdl_colsum_sumn_relu_bf16: unaligned y / dz");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int sms = bdl_num_sms();
+  long long rpb = (M + static_cast<long long>(sms) * 4 - 1) / (static_cast<long long>(sms) * 4);
+  if (rpb < 16) rpb = 16;
+  const int grid = static_cast<int>((M + rpb - 1) / rpb);
+  const int cvec = C / 8;
+  const int vcols = cvec < 256 ? cvec : 256;
+  const int rif = 256 / vcols;
+  const size_t smem = static_cast<size_t>(rif) * vcols * 8 * sizeof(float);
+  const __nv_bfloat16* yp = static_cast<const __nv_bfloat16*>(y);
+  __nv_bfloat16* zp = static_cast<__nv_bfloat16*>(dz);
+  const int rp = static_cast<int>(rpb);
+  if (count == 2) colsum_sumn_relu_kernel<2><<<grid, 256, smem, st>>>(a, yp, zp, out, M, C, rp);
+  else if (count == 3) colsum_sumn_relu_kernel<3><<<grid, 256, smem, st>>>(a, yp, zp, out, M, C, rp);
+  else colsum_sumn_relu_kernel<4><<<grid, 256, smem, st>>>(a, yp, zp, out, M, C, rp);
+  return bdl_check_launch("colsum_sumn_relu_kernel");
+}
+
 extern "C" int bdl_addn_bf16(const void* const* ptrs, int count, void* out, size_t n, void* stream) {
   if (count < 2 || count > 8) return bdl_fail("bdl_addn_bf16: 2..8 inputs");
   if (n % 8) return bdl_fail("bdl_addn_bf16: element count must be a multiple of 8");

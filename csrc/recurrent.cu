@@ -64,6 +64,80 @@ __global__ void lstm_bwd_kernel(const __nv_bfloat16* __restrict__ dh, const floa
   }
 }
 
+// ---- GRU (S/nn/GRU.scala:72-160): two pointwise stages around the two recurrent GEMMs of a step.
+// stage 1: r, z = sigmoid(x_rz + h.U_rz); hr = h * r          (hr feeds the candidate GEMM)
+// stage 2: hh = tanh(x_c + hr.U_c);  h' = (1 - z) * hh + z * h
+__global__ void gru_rz_fwd_kernel(const __nv_bfloat16* __restrict__ xrz, const __nv_bfloat16* __restrict__ hg,
+                                  const __nv_bfloat16* __restrict__ h, __nv_bfloat16* __restrict__ rz,
+                                  __nv_bfloat16* __restrict__ hr, long long B, int H, long long ldx, long long ldh) {
+  const long long total = B * H;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const long long b = i / H;
+    const int j = static_cast<int>(i - b * H);
+    const float r = sigm(__bfloat162float(xrz[b * ldx + j]) + __bfloat162float(hg[b * 2 * H + j]));
+    const float z = sigm(__bfloat162float(xrz[b * ldx + H + j]) + __bfloat162float(hg[b * 2 * H + H + j]));
+    rz[b * 2 * H + j] = __float2bfloat16_rn(r);
+    rz[b * 2 * H + H + j] = __float2bfloat16_rn(z);
+    hr[i] = __float2bfloat16_rn(__bfloat162float(h[b * ldh + j]) * r);
+  }
+}
+
+// d_hr: grad of hr; d_z: grad of z (from stage 2). Outputs d_pre [B,2H] (grad of both x_rz and h.U_rz), d_h [B,H].
+__global__ void gru_rz_bwd_kernel(const __nv_bfloat16* __restrict__ d_hr, const __nv_bfloat16* __restrict__ d_z,
+                                  const __nv_bfloat16* __restrict__ rz, const __nv_bfloat16* __restrict__ h,
+                                  __nv_bfloat16* __restrict__ d_pre, __nv_bfloat16* __restrict__ d_h, long long B,
+                                  int H, long long ldh) {
+  const long long total = B * H;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const long long b = i / H;
+    const int j = static_cast<int>(i - b * H);
+    const float r = __bfloat162float(rz[b * 2 * H + j]), z = __bfloat162float(rz[b * 2 * H + H + j]);
+    const float ghr = d_hr ? __bfloat162float(d_hr[i]) : 0.f;
+    const float gz = d_z ? __bfloat162float(d_z[i]) : 0.f;
+    const float hv = __bfloat162float(h[b * ldh + j]);
+    d_pre[b * 2 * H + j] = __float2bfloat16_rn(ghr * hv * r * (1.f - r));
+    d_pre[b * 2 * H + H + j] = __float2bfloat16_rn(gz * z * (1.f - z));
+    d_h[i] = __float2bfloat16_rn(ghr * r);
+  }
+}
+
+__global__ void gru_out_fwd_kernel(const __nv_bfloat16* __restrict__ xc, const __nv_bfloat16* __restrict__ hc,
+                                   const __nv_bfloat16* __restrict__ z, const __nv_bfloat16* __restrict__ h,
+                                   __nv_bfloat16* __restrict__ hh, __nv_bfloat16* __restrict__ out, long long B, int H,
+                                   long long ldx, long long ldz, long long ldh) {
+  const long long total = B * H;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const long long b = i / H;
+    const int j = static_cast<int>(i - b * H);
+    const float c = tanhf(__bfloat162float(xc[b * ldx + j]) + __bfloat162float(hc[i]));
+    const float zv = __bfloat162float(z[b * ldz + j]);
+    hh[i] = __float2bfloat16_rn(c);
+    out[i] = __float2bfloat16_rn((1.f - zv) * c + zv * __bfloat162float(h[b * ldh + j]));
+  }
+}
+
+// outputs: d_pre_c [B,H] (grad of x_c and of hr.U_c), d_z [B,H], d_h [B,H] (direct path through z * h)
+__global__ void gru_out_bwd_kernel(const __nv_bfloat16* __restrict__ d_out, const __nv_bfloat16* __restrict__ hh,
+                                   const __nv_bfloat16* __restrict__ z, const __nv_bfloat16* __restrict__ h,
+                                   __nv_bfloat16* __restrict__ d_pre_c, __nv_bfloat16* __restrict__ d_z,
+                                   __nv_bfloat16* __restrict__ d_h, long long B, int H, long long ldz, long long ldh) {
+  const long long total = B * H;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const long long b = i / H;
+    const int j = static_cast<int>(i - b * H);
+    const float g = __bfloat162float(d_out[i]);
+    const float c = __bfloat162float(hh[i]), zv = __bfloat162float(z[b * ldz + j]);
+    const float hv = __bfloat162float(h[b * ldh + j]);
+    d_pre_c[i] = __float2bfloat16_rn(g * (1.f - zv) * (1.f - c * c));
+    d_z[i] = __float2bfloat16_rn(g * (hv - c));
+    d_h[i] = __float2bfloat16_rn(g * zv);
+  }
+}
+
 static int rgrid(long long total) {
   const long long cap = static_cast<long long>(bdl_num_sms()) * 8;
   long long b = (total + 255) / 256;
@@ -92,4 +166,44 @@ extern "C" int bdl_lstm_gates_bwd(const void* dh, const float* dc_in, const void
       static_cast<const __nv_bfloat16*>(dh), dc_in, static_cast<const __nv_bfloat16*>(gates), c, c_prev,
       static_cast<__nv_bfloat16*>(dg), dc_prev, B, H);
   return bdl_check_launch("lstm_bwd_kernel");
+}
+
+extern "C" int bdl_gru_rz_fwd(const void* xrz, const void* hg, const void* h, void* rz, void* hr, long long B, int H,
+                              long long ldx, long long ldh, void* stream) {
+  if (B <= 0 || H <= 0) return BDL_OK;
+  gru_rz_fwd_kernel<<<rgrid(B * H), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(xrz), static_cast<const __nv_bfloat16*>(hg),
+      static_cast<const __nv_bfloat16*>(h), static_cast<__nv_bfloat16*>(rz), static_cast<__nv_bfloat16*>(hr), B, H, ldx,
+      ldh);
+  return bdl_check_launch("gru_rz_fwd_kernel");
+}
+
+extern "C" int bdl_gru_rz_bwd(const void* d_hr, const void* d_z, const void* rz, const void* h, void* d_pre, void* d_h,
+                              long long B, int H, long long ldh, void* stream) {
+  if (B <= 0 || H <= 0) return BDL_OK;
+  gru_rz_bwd_kernel<<<rgrid(B * H), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(d_hr), static_cast<const __nv_bfloat16*>(d_z),
+      static_cast<const __nv_bfloat16*>(rz), static_cast<const __nv_bfloat16*>(h), static_cast<__nv_bfloat16*>(d_pre),
+      static_cast<__nv_bfloat16*>(d_h), B, H, ldh);
+  return bdl_check_launch("gru_rz_bwd_kernel");
+}
+
+extern "C" int bdl_gru_out_fwd(const void* xc, const void* hc, const void* z, const void* h, void* hh, void* out,
+                               long long B, int H, long long ldx, long long ldz, long long ldh, void* stream) {
+  if (B <= 0 || H <= 0) return BDL_OK;
+  gru_out_fwd_kernel<<<rgrid(B * H), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(xc), static_cast<const __nv_bfloat16*>(hc),
+      static_cast<const __nv_bfloat16*>(z), static_cast<const __nv_bfloat16*>(h), static_cast<__nv_bfloat16*>(hh),
+      static_cast<__nv_bfloat16*>(out), B, H, ldx, ldz, ldh);
+  return bdl_check_launch("gru_out_fwd_kernel");
+}
+
+extern "C" int bdl_gru_out_bwd(const void* d_out, const void* hh, const void* z, const void* h, void* d_pre_c,
+                               void* d_z, void* d_h, long long B, int H, long long ldz, long long ldh, void* stream) {
+  if (B <= 0 || H <= 0) return BDL_OK;
+  gru_out_bwd_kernel<<<rgrid(B * H), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(d_out), static_cast<const __nv_bfloat16*>(hh),
+      static_cast<const __nv_bfloat16*>(z), static_cast<const __nv_bfloat16*>(h), static_cast<__nv_bfloat16*>(d_pre_c),
+      static_cast<__nv_bfloat16*>(d_z), static_cast<__nv_bfloat16*>(d_h), B, H, ldz, ldh);
+  return bdl_check_launch("gru_out_bwd_kernel");
 }

@@ -56,6 +56,9 @@ int bdl_eltwise_bf16(int op, const void* a, const void* b, void* out, size_t n, 
 /* out[c] += sum_m x[m,c]; with y != NULL: dz = (y>0 ? x : 0) is written and summed (fused ReLU-bwd + bias grad). */
 /* out = sum of `count` (2..8) dense bf16 tensors of n elements (n % 8 == 0), fp32 accumulate */
 int bdl_addn_bf16(const void* const* ptrs, int count, void* out, size_t n, void* stream);
+/* dz = (y > 0) ? sum of `count` (2..4) dense [M,C] bf16 tensors : 0, and out[c] += column sums of dz */
+int bdl_colsum_sumn_relu_bf16(const void* const* ptrs, int count, const void* y, void* dz, float* out, long long M,
+                              int C, void* stream);
 int bdl_colsum_bf16(const void* x, const void* y, void* dz, float* out, long long M, int C, long long ldx,
                     long long ldy, long long ldz, void* stream);
 int bdl_dropout_fwd_bf16(const void* x, void* y, void* mask, size_t n, float p, unsigned long long seed,
@@ -174,6 +177,15 @@ int bdl_lstm_gates_fwd(const void* g, const float* c_prev, void* h, float* c, vo
                        long long ldg, void* stream);
 int bdl_lstm_gates_bwd(const void* dh, const float* dc_in, const void* gates, const float* c, const float* c_prev,
                        void* dg, float* dc_prev, long long B, int H, void* stream);
+/* GRU step, two pointwise stages around the recurrent GEMMs (S/nn/GRU.scala): all tensors bf16; ld* = row pitches */
+int bdl_gru_rz_fwd(const void* xrz, const void* hg, const void* h, void* rz, void* hr, long long B, int H,
+                   long long ldx, long long ldh, void* stream);
+int bdl_gru_rz_bwd(const void* d_hr, const void* d_z, const void* rz, const void* h, void* d_pre, void* d_h,
+                   long long B, int H, long long ldh, void* stream);
+int bdl_gru_out_fwd(const void* xc, const void* hc, const void* z, const void* h, void* hh, void* out, long long B,
+                    int H, long long ldx, long long ldz, long long ldh, void* stream);
+int bdl_gru_out_bwd(const void* d_out, const void* hh, const void* z, const void* h, void* d_pre_c, void* d_z,
+                    void* d_h, long long B, int H, long long ldz, long long ldh, void* stream);
 
 /* ---- fp8 (e4m3) quantised inference (csrc/gemm_tcgen05.cu kFp8, csrc/quantize.cu). Reference: core/bigquant/native
  *      (MixPrecisionGEMM, quantize), S/nn/quantized/*, S/nn/MklInt8Convertible.scala, S/nn/mkldnn/SpatialConvolution.scala

@@ -331,3 +331,28 @@ def test_gpu_image_batch_matches_torch(layout):
         _close(got.float().cpu(), ref, 1e-2 if dt == torch.bfloat16 else 1e-6, 1e-5)
     centre = image_batch(frames.to(DEV), 32, 32, mean, std, None, None, torch.float32, cl)
     _close(centre.cpu(), _image_batch_torch(frames, 32, 32, mean, std, None, None, torch.float32, cl), 1e-6, 1e-5)
+
+
+def test_gru_fused_step_matches_reference():
+    from bigdl_b200.ops.recurrent import gru_out, gru_rz
+    torch.manual_seed(13)
+    B, H = 48, 64
+    xt = torch.randn(B, 3 * H, device=DEV).bfloat16().requires_grad_()
+    hg = torch.randn(B, 2 * H, device=DEV).bfloat16().requires_grad_()
+    hc = torch.randn(B, H, device=DEV).bfloat16().requires_grad_()
+    h = torch.randn(B, H, device=DEV).bfloat16().requires_grad_()
+    z, hr = gru_rz(xt[:, :2 * H], hg, h)
+    out = gru_out(xt[:, 2 * H:], hc, z, h)
+    f = [t.detach().float().requires_grad_() for t in (xt, hg, hc, h)]
+    rz = torch.sigmoid(f[0][:, :2 * H] + f[1])
+    r_ref, z_ref = rz[:, :H], rz[:, H:]
+    hr_ref = f[3] * r_ref
+    hh = torch.tanh(f[0][:, 2 * H:] + f[2])
+    out_ref = (1 - z_ref) * hh + z_ref * f[3]
+    _close(hr, hr_ref, 2e-2, 2e-2)
+    _close(out, out_ref, 2e-2, 2e-2)
+    g1, g2 = torch.randn_like(out_ref), torch.randn_like(hr_ref)
+    torch.autograd.backward([out, hr], [g1.bfloat16(), g2.bfloat16()])
+    torch.autograd.backward([out_ref, hr_ref], [g1.bfloat16().float(), g2.bfloat16().float()])
+    for a, b in zip((xt, hg, hc, h), f):
+        _close(a.grad, b.grad, 4e-2, 4e-2)

@@ -170,3 +170,19 @@ def test_tf_helper_ops():
     assert img.shape == (4, 4, 3) and img[0, 0].tolist() == [2, 1, 0]          # RGB order
     raw = TF.DecodeRaw(torch.int16).forward(np.array([struct.pack("<3h", 1, -2, 3)], dtype=object))
     assert raw.tolist() == [1, -2, 3]
+
+
+def test_fanout_fn_sums_branch_gradients():
+    """FanOutFn is an identity whose backward is the sum of its consumers' gradients (torch path on CPU)."""
+    import torch
+    from bigdl_b200.ops.functions import FanOutFn
+
+    x = torch.randn(2, 8, 4, 4, requires_grad=True)
+    a, b, c = FanOutFn.apply(x, 3)
+    (a * 2 + b.pow(2) + c.sin()).sum().backward()
+    ref = 2 + 2 * x.detach() + x.detach().cos()
+    assert torch.allclose(x.grad, ref, atol=1e-6)
+    y = torch.randn(3, 5, requires_grad=True)
+    (only,) = FanOutFn.apply(y, 1)
+    only.sum().backward()
+    assert torch.equal(y.grad, torch.ones_like(y))

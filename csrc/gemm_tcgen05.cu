@@ -552,11 +552,27 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
 }
 
 // ------------------------------------------------------------------------------------------- host
-static int pick_block_n(int M, int N, int num_sms) {
+static int pick_block_n(int M, int N, int num_sms, bool split_k = false) {
   if (N <= 256) return ((N + 15) / 16) * 16;
   // Prefer the widest tile that still gives every SM work; otherwise fall back to narrower tiles.
   const int tiles_m = (M + BM - 1) / BM;
   const int cands[3] = {256, 192, 128};
+  if (split_k && static_cast<long long>(tiles_m) * ((N + 127) / 128) < num_sms) {
+    // Split-K problems (weight gradients: small M x N, huge K) fill the SMs through the K split, and every n tile
+    // re-reads the whole A operand from L2, which is what bounds them: take the fewest n tiles, narrowest on a tie.
+    static const bool on = [] { const char* e = getenv("BDL_WGRAD_WIDE"); return !(e && e[0] == '0'); }();
+    if (on) {
+      int best = 128, best_tn = (N + 127) / 128;
+      for (int i = 1; i >= 0; --i) {
+        const int tn = (N + cands[i] - 1) / cands[i];
+        if (tn < best_tn) {
+          best_tn = tn;
+          best = cands[i];
+        }
+      }
+      return best;
+    }
+  }
   int best = 128;
   double best_cost = 1e30;
   for (int i = 0; i < 3; ++i) {
@@ -591,7 +607,7 @@ extern "C" int bdl_gemm_bf16(const void* A, const void* B, void* D, const float*
   p.M = M;
   p.N = N;
   p.K = K;
-  p.block_n = pick_block_n(M, N, num_sms);
+  p.block_n = pick_block_n(M, N, num_sms, (flags & BDL_GEMM_ATOMIC_ADD) != 0 && splits <= 0);
   p.b_rows = b_mn ? ((p.block_n + 63) / 64) * 64 : p.block_n;
   p.tiles_m = (M + BM - 1) / BM;
   p.tiles_n = (N + p.block_n - 1) / p.block_n;
@@ -708,7 +724,7 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
   }
   p.M = gm;
   p.N = gn;
-  p.block_n = pick_block_n(gm, gn, num_sms);
+  p.block_n = pick_block_n(gm, gn, num_sms, mode == 2 && splits <= 0);
   const bool b_mn = (mode != 0);
   p.b_rows = b_mn ? ((p.block_n + 63) / 64) * 64 : p.block_n;
   if (mode == 2 && aw < 64) p.b_rows = ((p.block_n + aw - 1) / aw) * aw;

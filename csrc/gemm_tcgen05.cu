@@ -82,6 +82,8 @@ struct GemmParams {
   int cv_flip;               // dgrad: B uses the spatially flipped tap
   int cv_num_kb;             // number of 64-wide k blocks (taps * cblocks for fprop/dgrad, ceil(M/64) for wgrad)
   int cv_nimg;               // batch size of the gathered tensor (first out-of-bounds image index)
+  int dual_m;                // MN-major A only: one CTA owns two stacked 128-row tiles (both TMEM accumulator stages),
+                             // so the B operand of a weight gradient is fetched once per 256 output rows
   int cv_aw;                 // channels per gathered atom: 64 (128B swizzle) or, for C <= 32, 32 / 16 (64B / 32B swizzle)
   FastDiv fd_hw, fd_wo, fd_cblocks, fd_kw, fd_c;
 };
@@ -197,7 +199,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = threadIdx.x & 31u;
   const uint32_t tiles = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t a_bytes = BM * BK * 2;
+  const uint32_t a_bytes = BM * BK * 2 * (kAMN && p.dual_m ? 2 : 1);
   const uint32_t b_bytes = static_cast<uint32_t>(p.b_rows) * BK * 2;
   const uint32_t stage_bytes = a_bytes + b_bytes;
 
@@ -238,7 +240,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         const int n_blk = rem - m_blk * p.tiles_n;
         const int kb0 = static_cast<int>((static_cast<long long>(split) * num_kb) / p.splits);
         const int kb1 = static_cast<int>((static_cast<long long>(split + 1) * num_kb) / p.splits);
-        const int m0 = m_blk * BM;
+        const int m0 = m_blk * BM * (kAMN && p.dual_m ? 2 : 1);
         const int n0 = n_blk * p.block_n;
         // implicit-GEMM bookkeeping hoisted out of the k loop
         int cv_img = 0, cv_h = 0, cv_w = 0, cv_r = 0, cv_s = 0, cv_cb = 0;
@@ -308,6 +310,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             mbar_expect_tx(fb, stage_bytes);
             tma_load_2d(sa, &tmA, fb, m0, k0);
             tma_load_2d(sa + 8192u, &tmA, fb, m0 + 64, k0);
+            if (p.dual_m) {
+              tma_load_2d(sa + 16384u, &tmA, fb, m0 + 128, k0);
+              tma_load_2d(sa + 24576u, &tmA, fb, m0 + 192, k0);
+            }
             const uint32_t img = p.fd_hw.quot(static_cast<uint32_t>(k0));
             const uint32_t rem = static_cast<uint32_t>(k0) - img * p.fd_hw.div;
             const uint32_t ho = p.fd_wo.quot(rem);
@@ -351,6 +357,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             mbar_expect_tx(fb, stage_bytes);
             tma_load_2d(sa, &tmA, fb, m0, k0);
             tma_load_2d(sa + 8192u, &tmA, fb, m0 + 64, k0);
+            if (p.dual_m) {
+              tma_load_2d(sa + 16384u, &tmA, fb, m0 + 128, k0);
+              tma_load_2d(sa + 24576u, &tmA, fb, m0 + 192, k0);
+            }
             const uint32_t img = p.fd_hw.quot(static_cast<uint32_t>(k0));
             const uint32_t rem = static_cast<uint32_t>(k0) - img * p.fd_hw.div;
             const uint32_t ho = p.fd_wo.quot(rem);
@@ -371,6 +381,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             // A stored [K, M]: two boxes of {64 m, 64 k}
             tma_load_2d(sa, &tmA, fb, m0, k0);
             tma_load_2d(sa + 8192u, &tmA, fb, m0 + 64, k0);
+            if (p.dual_m) {
+              tma_load_2d(sa + 16384u, &tmA, fb, m0 + 128, k0);
+              tma_load_2d(sa + 24576u, &tmA, fb, m0 + 192, k0);
+            }
           } else {
             tma_load_2d(sa, &tmA, fb, k0, m0);  // box {64 k, 128 m}
           }
@@ -402,7 +416,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         const int split = work / tiles_mn;
         const int kb0 = static_cast<int>((static_cast<long long>(split) * num_kb) / p.splits);
         const int kb1 = static_cast<int>((static_cast<long long>(split + 1) * num_kb) / p.splits);
+        const bool dual = kAMN && p.dual_m;
         mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1u);
+        if (dual) mbar_wait(smem_u32(&tempty_bar[1]), acc_phase ^ 1u);   // dual: acc is always 0, both stages are ours
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * kAccStride;
         for (int kb = kb0; kb < kb1; ++kb) {
@@ -424,10 +440,14 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           } else if (kConv == 2 && small_c) {
             const uint32_t row = p.cv_aw * 2u, layout = p.cv_aw == 32 ? 4u : 6u;
 #pragma unroll
-            for (int k = 0; k < BK / 16; ++k)
-              umma_f16(d_tmem, make_smem_desc_sw128(sa + k * 2048u, 8192u, 1024u),
-                       make_smem_desc(sb + k * 16u * row, 64u * row, 8u * row, layout), idesc,
+            for (int k = 0; k < BK / 16; ++k) {
+              const uint64_t bdesc = make_smem_desc(sb + k * 16u * row, 64u * row, 8u * row, layout);
+              umma_f16(d_tmem, make_smem_desc_sw128(sa + k * 2048u, 8192u, 1024u), bdesc, idesc,
                        (kb > kb0 || k > 0) ? 1u : 0u);
+              if (dual)
+                umma_f16(d_tmem + kAccStride, make_smem_desc_sw128(sa + 16384u + k * 2048u, 8192u, 1024u), bdesc,
+                         idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            }
           } else {
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
@@ -439,6 +459,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
               umma_f8(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
             else
               umma_f16(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            if (kAMN && !kFp8 && dual)
+              umma_f16(d_tmem + kAccStride, make_smem_desc_sw128(sa + 16384u + k * 2048u, 8192u, 1024u), bdesc, idesc,
+                       (kb > kb0 || k > 0) ? 1u : 0u);
           }
           }
           umma_commit(smem_u32(&empty_bar[stage]));
@@ -448,8 +471,13 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           }
         }
         umma_commit(smem_u32(&tfull_bar[acc]));
-        acc ^= 1u;
-        if (acc == 0) acc_phase ^= 1u;
+        if (dual) {
+          umma_commit(smem_u32(&tfull_bar[1]));
+          acc_phase ^= 1u;
+        } else {
+          acc ^= 1u;
+          if (acc == 0) acc_phase ^= 1u;
+        }
       }
     }
     __syncwarp();
@@ -467,7 +495,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       const int rem = work - split * tiles_mn;
       const int m_blk = rem / p.tiles_n;
       const int n_blk = rem - m_blk * p.tiles_n;
-      const int row = m_blk * BM + static_cast<int>(quad * 32u + lane);
+      const int nhalves = (kAMN && p.dual_m) ? 2 : 1;   // dual: accumulator stage h holds rows [256 m_blk + 128 h, +128)
+      for (int hm = 0; hm < nhalves; ++hm) {
+      const int row = (m_blk * nhalves + hm) * BM + static_cast<int>(quad * 32u + lane);
       const int nbase = n_blk * p.block_n;
       // Stage this tile's bias / dequantisation columns in shared memory while the MMAs are still running: reading
       // them with __ldg inside the column loop put a long-scoreboard stall on every 16-column chunk.
@@ -543,6 +573,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
       acc ^= 1u;
       if (acc == 0) acc_phase ^= 1u;
+      }
     }
   }
 
@@ -552,6 +583,16 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
 }
 
 // ------------------------------------------------------------------------------------------- host
+// Two stacked 128-row tiles per CTA (see GemmParams::dual_m): only when the halved tile count still fills the SMs,
+// directly or through the K split.
+static bool want_dual_m(int M, long long tiles_n, int num_kb, int num_sms, bool atomic) {
+  static const bool on = [] { const char* e = getenv("BDL_GEMM_DUALM"); return !(e && e[0] == '0'); }();
+  if (!on || !atomic || M <= BM) return false;
+  const long long tiles = static_cast<long long>((M + 2 * BM - 1) / (2 * BM)) * tiles_n;
+  const long long max_splits = num_kb / 4 > 0 ? num_kb / 4 : 1;
+  return tiles * max_splits >= num_sms;
+}
+
 static int pick_block_n(int M, int N, int num_sms, bool split_k = false) {
   if (N <= 256) return ((N + 15) / 16) * 16;
   // Prefer the widest tile that still gives every SM work; otherwise fall back to narrower tiles.
@@ -612,6 +653,10 @@ extern "C" int bdl_gemm_bf16(const void* A, const void* B, void* D, const float*
   p.tiles_m = (M + BM - 1) / BM;
   p.tiles_n = (N + p.block_n - 1) / p.block_n;
   const int num_kb = (K + BK - 1) / BK;
+  if (a_mn && want_dual_m(M, p.tiles_n, num_kb, num_sms, (flags & BDL_GEMM_ATOMIC_ADD) != 0)) {
+    p.dual_m = 1;
+    p.tiles_m = (M + 2 * BM - 1) / (2 * BM);
+  }
   const long long tiles_mn = static_cast<long long>(p.tiles_m) * p.tiles_n;
   if (splits <= 0) {
     splits = 1;
@@ -629,7 +674,7 @@ extern "C" int bdl_gemm_bf16(const void* A, const void* B, void* D, const float*
   p.flags = flags;
   p.D = D;
   p.bias = bias;
-  const size_t stage_bytes = static_cast<size_t>(BM) * BK * 2 + static_cast<size_t>(p.b_rows) * BK * 2;
+  const size_t stage_bytes = static_cast<size_t>(BM) * BK * 2 * (p.dual_m ? 2 : 1) + static_cast<size_t>(p.b_rows) * BK * 2;
   const size_t budget = kSmemBudget;
   int stages = static_cast<int>(budget / stage_bytes);
   if (stages > kMaxStages) stages = kMaxStages;
@@ -730,6 +775,10 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
   if (mode == 2 && aw < 64) p.b_rows = ((p.block_n + aw - 1) / aw) * aw;
   p.tiles_m = (gm + BM - 1) / BM;
   p.tiles_n = (gn + p.block_n - 1) / p.block_n;
+  if (mode == 2 && want_dual_m(gm, p.tiles_n, p.cv_num_kb, num_sms, true)) {
+    p.dual_m = 1;
+    p.tiles_m = (gm + 2 * BM - 1) / (2 * BM);
+  }
   const long long tiles_mn = static_cast<long long>(p.tiles_m) * p.tiles_n;
   if (splits <= 0) {
     splits = 1;
@@ -747,7 +796,7 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
   p.flags = flags;
   p.D = D;
   p.bias = bias;
-  const size_t stage_bytes = static_cast<size_t>(BM) * BK * 2 + static_cast<size_t>(p.b_rows) * BK * 2;
+  const size_t stage_bytes = static_cast<size_t>(BM) * BK * 2 * (p.dual_m ? 2 : 1) + static_cast<size_t>(p.b_rows) * BK * 2;
   const size_t budget = kSmemBudget;
   int stages = static_cast<int>(budget / stage_bytes);
   if (stages > kMaxStages) stages = kMaxStages;

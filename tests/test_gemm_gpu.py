@@ -61,6 +61,23 @@ def test_gemm_splitk_accumulate():
     assert err <= 2e-3 * ref.abs().max().item() + 1e-2, err
 
 
+@pytest.mark.parametrize("Cout,Kd", [(192, 576), (320, 264), (256, 1152), (136, 96)])
+def test_gemm_splitk_two_stacked_m_tiles(Cout, Kd):
+    """Weight-gradient shapes with more than 128 output rows: one CTA owns two stacked 128-row accumulators (dual_m),
+    including a last pair whose second half is partly or wholly out of range, and wide n tiles."""
+    from bigdl_b200.ops.gemm import gemm_bf16
+    torch.manual_seed(4)
+    M = 128 * 160
+    dy = torch.randn(M, Cout, device="cuda").bfloat16()
+    x = torch.randn(M, Kd, device="cuda").bfloat16()
+    acc = torch.ones(Cout, Kd, device="cuda")
+    gemm_bf16(dy, x, a_mn=True, b_mn=True, out=acc, accumulate=True)
+    torch.cuda.synchronize()
+    ref = 1.0 + dy.float().t() @ x.float()
+    err = (acc - ref).abs().max().item()
+    assert err <= 2e-3 * ref.abs().max().item() + 1e-2, err
+
+
 def test_linear_fn_output_size_not_multiple_of_8():
     """10-way classifier head: backward pads dY for the MN-major GEMM operands."""
     import torch

@@ -67,6 +67,8 @@ WGRAD_EXTRA = [
     (2, 24, 9, 9, 48, 5, 5, 1, 1, 2, 2, 1, 1),        # C < 64: one partly-filled channel atom per tap
     (2, 160, 7, 7, 224, 3, 3, 1, 1, 1, 1, 1, 1),      # C = 2.5 atoms, O not a multiple of 128
     (2, 72, 8, 8, 40, 3, 3, 2, 2, 1, 1, 1, 1),        # C % 16 == 8: a 16-column chunk is only half valid
+    (8, 64, 56, 56, 192, 3, 3, 1, 1, 1, 1, 1, 1),     # O > 128 with a long pixel axis: two stacked m tiles per CTA
+    (8, 32, 40, 40, 320, 3, 3, 1, 1, 1, 1, 1, 1),     # same with 32-channel atoms and a half-empty last tile pair
 ]
 
 

@@ -82,8 +82,8 @@ struct GemmParams {
   int cv_flip;               // dgrad: B uses the spatially flipped tap
   int cv_num_kb;             // number of 64-wide k blocks (taps * cblocks for fprop/dgrad, ceil(M/64) for wgrad)
   int cv_nimg;               // batch size of the gathered tensor (first out-of-bounds image index)
-  int dual_m;                // MN-major A only: one CTA owns two stacked 128-row tiles (both TMEM accumulator stages),
-                             // so the B operand of a weight gradient is fetched once per 256 output rows
+  int dual_m;                // one CTA owns two stacked 128-row tiles (both TMEM accumulator stages), so the B operand
+                             // is fetched from L2 once per 256 output rows (bf16 kernels only)
   int cv_aw;                 // channels per gathered atom: 64 (128B swizzle) or, for C <= 32, 32 / 16 (64B / 32B swizzle)
   FastDiv fd_hw, fd_wo, fd_cblocks, fd_kw, fd_c;
 };
@@ -184,7 +184,7 @@ __device__ __forceinline__ void epilogue_store16(const GemmParams& p, const uint
 
 // kFp8: operands are e4m3 bytes (128 per swizzle row, UMMA K = 32) multiplied with kind::f8f6f4; the epilogue applies a
 //       per-output-column fp32 scale (activation scale x per-channel weight scale) before bias/ReLU. K-major only.
-template <bool kAMN, bool kBMN, int kConv, bool kFp8 = false>
+template <bool kAMN, bool kBMN, int kConv, bool kFp8 = false, bool kDual = false>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                          const GemmParams p) {
@@ -199,7 +199,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = threadIdx.x & 31u;
   const uint32_t tiles = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t a_bytes = BM * BK * 2 * (kAMN && p.dual_m ? 2 : 1);
+  const uint32_t a_bytes = BM * BK * 2 * (kDual ? 2 : 1);
   const uint32_t b_bytes = static_cast<uint32_t>(p.b_rows) * BK * 2;
   const uint32_t stage_bytes = a_bytes + b_bytes;
 
@@ -240,10 +240,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         const int n_blk = rem - m_blk * p.tiles_n;
         const int kb0 = static_cast<int>((static_cast<long long>(split) * num_kb) / p.splits);
         const int kb1 = static_cast<int>((static_cast<long long>(split + 1) * num_kb) / p.splits);
-        const int m0 = m_blk * BM * (kAMN && p.dual_m ? 2 : 1);
+        const int m0 = m_blk * BM * (kDual ? 2 : 1);
         const int n0 = n_blk * p.block_n;
         // implicit-GEMM bookkeeping hoisted out of the k loop
         int cv_img = 0, cv_h = 0, cv_w = 0, cv_r = 0, cv_s = 0, cv_cb = 0;
+        int cv_img2 = 0, cv_h2 = 0, cv_w2 = 0;
         int at_c0[4] = {0, 0, 0, 0};
         uint16_t at_ow[4] = {0, 0, 0, 0}, at_oh[4] = {0, 0, 0, 0};
         bool at_ok[4] = {false, false, false, false};
@@ -256,6 +257,14 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           cv_img = static_cast<int>(img);
           cv_h = static_cast<int>(ho) * p.cv_sh - p.cv_ph;
           cv_w = static_cast<int>(wo) * p.cv_sw - p.cv_pw;
+          if (kDual) {   // base pixel of the second 128-row half
+            const uint32_t img2 = p.fd_hw.quot(static_cast<uint32_t>(m0 + BM));
+            const uint32_t rem2 = static_cast<uint32_t>(m0 + BM) - img2 * p.fd_hw.div;
+            const uint32_t ho2 = p.fd_wo.quot(rem2);
+            cv_img2 = static_cast<int>(img2);
+            cv_h2 = static_cast<int>(ho2) * p.cv_sh - p.cv_ph;
+            cv_w2 = static_cast<int>(rem2 - ho2 * p.fd_wo.div) * p.cv_sw - p.cv_pw;
+          }
           const uint32_t tap = small_c ? static_cast<uint32_t>(kb0 * (64 / p.cv_aw))
                                        : p.fd_cblocks.quot(static_cast<uint32_t>(kb0));
           cv_cb = small_c ? 0 : kb0 - static_cast<int>(tap) * p.cv_cblocks;
@@ -310,7 +319,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             mbar_expect_tx(fb, stage_bytes);
             tma_load_2d(sa, &tmA, fb, m0, k0);
             tma_load_2d(sa + 8192u, &tmA, fb, m0 + 64, k0);
-            if (p.dual_m) {
+            if (kDual) {
               tma_load_2d(sa + 16384u, &tmA, fb, m0 + 128, k0);
               tma_load_2d(sa + 24576u, &tmA, fb, m0 + 192, k0);
             }
@@ -336,6 +345,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             // k block = (filter tap, 64-channel block); A tile = 128 consecutive output pixels of that tap
             tma_load_im2col_4d(sa, &tmA, fb, cv_cb * KE, cv_w, cv_h, cv_img, static_cast<uint16_t>(cv_s * p.cv_dw),
                                static_cast<uint16_t>(cv_r * p.cv_dh));
+            if (kDual)
+              tma_load_im2col_4d(sa + 16384u, &tmA, fb, cv_cb * KE, cv_w2, cv_h2, cv_img2,
+                                 static_cast<uint16_t>(cv_s * p.cv_dw), static_cast<uint16_t>(cv_r * p.cv_dh));
             const int tap = cv_r * p.cv_kw + cv_s;
             if (kBMN) {
               // dgrad: B[k = cout block][n = cin] is the (flipped) tap's [Cout, Cin] slice of the OHWI weights
@@ -357,7 +369,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             mbar_expect_tx(fb, stage_bytes);
             tma_load_2d(sa, &tmA, fb, m0, k0);
             tma_load_2d(sa + 8192u, &tmA, fb, m0 + 64, k0);
-            if (p.dual_m) {
+            if (kDual) {
               tma_load_2d(sa + 16384u, &tmA, fb, m0 + 128, k0);
               tma_load_2d(sa + 24576u, &tmA, fb, m0 + 192, k0);
             }
@@ -381,12 +393,13 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             // A stored [K, M]: two boxes of {64 m, 64 k}
             tma_load_2d(sa, &tmA, fb, m0, k0);
             tma_load_2d(sa + 8192u, &tmA, fb, m0 + 64, k0);
-            if (p.dual_m) {
+            if (kDual) {
               tma_load_2d(sa + 16384u, &tmA, fb, m0 + 128, k0);
               tma_load_2d(sa + 24576u, &tmA, fb, m0 + 192, k0);
             }
           } else {
             tma_load_2d(sa, &tmA, fb, k0, m0);  // box {64 k, 128 m}
+            if (kDual) tma_load_2d(sa + 16384u, &tmA, fb, k0, m0 + BM);
           }
           if (kBMN) {
             for (int j = 0; j < p.b_rows / 64; ++j) tma_load_2d(sb + j * 8192u, &tmB, fb, n0 + 64 * j, k0);
@@ -416,7 +429,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         const int split = work / tiles_mn;
         const int kb0 = static_cast<int>((static_cast<long long>(split) * num_kb) / p.splits);
         const int kb1 = static_cast<int>((static_cast<long long>(split + 1) * num_kb) / p.splits);
-        const bool dual = kAMN && p.dual_m;
+        constexpr bool dual = kDual;
         mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1u);
         if (dual) mbar_wait(smem_u32(&tempty_bar[1]), acc_phase ^ 1u);   // dual: acc is always 0, both stages are ours
         tc_fence_after();
@@ -459,9 +472,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
               umma_f8(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
             else
               umma_f16(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-            if (kAMN && !kFp8 && dual)
-              umma_f16(d_tmem + kAccStride, make_smem_desc_sw128(sa + 16384u + k * 2048u, 8192u, 1024u), bdesc, idesc,
-                       (kb > kb0 || k > 0) ? 1u : 0u);
+            if (dual)
+              umma_f16(d_tmem + kAccStride,
+                       kAMN ? make_smem_desc_sw128(sa + 16384u + k * 2048u, 8192u, 1024u)
+                            : make_smem_desc_sw128(sa + 16384u + k * 32u, 16u, 1024u),
+                       bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           }
           }
           umma_commit(smem_u32(&empty_bar[stage]));
@@ -495,7 +510,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       const int rem = work - split * tiles_mn;
       const int m_blk = rem / p.tiles_n;
       const int n_blk = rem - m_blk * p.tiles_n;
-      const int nhalves = (kAMN && p.dual_m) ? 2 : 1;   // dual: accumulator stage h holds rows [256 m_blk + 128 h, +128)
+      const int nhalves = kDual ? 2 : 1;   // dual: accumulator stage h holds rows [256 m_blk + 128 h, +128)
       for (int hm = 0; hm < nhalves; ++hm) {
       const int row = (m_blk * nhalves + hm) * BM + static_cast<int>(quad * 32u + lane);
       const int nbase = n_blk * p.block_n;
@@ -699,7 +714,8 @@ extern "C" int bdl_gemm_bf16(const void* A, const void* B, void* D, const float*
   const int grid = static_cast<int>(total < num_sms ? total : num_sms);
 #define BDL_LAUNCH_GEMM(AMN, BMN)                                                                                 \
   do {                                                                                                            \
-    auto kfn = gemm_bf16_tcgen05_kernel<AMN, BMN, 0>;                                                                \
+    auto kfn = p.dual_m ? gemm_bf16_tcgen05_kernel<AMN, BMN, 0, false, true>                                         \
+                        : gemm_bf16_tcgen05_kernel<AMN, BMN, 0, false, false>;                                       \
     cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemBudget + 1024));     \
     if (e != cudaSuccess) return bdl_fail_cuda("cudaFuncSetAttribute(gemm)", e);                                  \
     kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, p);                                                       \
@@ -779,6 +795,17 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
     p.dual_m = 1;
     p.tiles_m = (gm + 2 * BM - 1) / (2 * BM);
   }
+  if (mode != 2 && aw == 64) {
+    // fprop / dgrad with a long reduction (K >= 1024) and several waves of tiles: 256 pixels per CTA halve the L2
+    // reads of the weight operand per MAC (these GEMMs are bound by L2 -> SM bandwidth, not by the tensor pipe); the
+    // price is an epilogue that no longer overlaps the next tile's main loop, hence the K threshold.
+    static const int min_kb = [] { const char* e = getenv("BDL_GEMM_DUALM_FPROP_KB"); return e ? atoi(e) : 8; }();
+    const long long pairs = static_cast<long long>((gm + 2 * BM - 1) / (2 * BM)) * p.tiles_n;
+    if (min_kb > 0 && p.cv_num_kb >= min_kb && pairs >= 2ll * num_sms) {
+      p.dual_m = 1;
+      p.tiles_m = (gm + 2 * BM - 1) / (2 * BM);
+    }
+  }
   const long long tiles_mn = static_cast<long long>(p.tiles_m) * p.tiles_n;
   if (splits <= 0) {
     splits = 1;
@@ -828,7 +855,8 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
   const int grid = static_cast<int>(total < num_sms ? total : num_sms);
 #define BDL_LAUNCH_CONV(AMN, BMN, CV)                                                                             \
   do {                                                                                                            \
-    auto kfn = gemm_bf16_tcgen05_kernel<AMN, BMN, CV>;                                                            \
+    auto kfn = p.dual_m ? gemm_bf16_tcgen05_kernel<AMN, BMN, CV, false, true>                                     \
+                        : gemm_bf16_tcgen05_kernel<AMN, BMN, CV, false, false>;                                   \
     cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemBudget + 1024));     \
     if (e != cudaSuccess) return bdl_fail_cuda("cudaFuncSetAttribute(conv gemm)", e);                             \
     kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, p);                                                       \

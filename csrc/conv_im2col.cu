@@ -212,19 +212,21 @@ extern "C" int bdl_im2col_nhwc_bf16(const void* x, void* col, int N, int H, int 
 // where xpad is x with (pt, pl) zero rows/columns in front. A k x k stride-2 convolution over x then equals a
 // ceil(k/2) x 1 stride-1 VALID convolution over y with tw*16 channels (64 for the 7x7 stems), which the TMA-im2col
 // implicit GEMM runs with full 128-byte rows: the gather is bound by rows fetched, not bytes, so 4 taps of 128 B beat
-// 16 taps of 32 B by ~4x. One thread writes one 32-byte tap; x is read through element strides so NCHW fp32 (what the
-// data pipeline delivers) and channels-last bf16 both work without a conversion pass.
+// 16 taps of 32 B by ~4x. One thread gathers one 2x2 block and stores it to its tw pixels; x is read through element
+// strides so NCHW fp32 (what the data pipeline delivers) and channels-last bf16 both work without a conversion pass.
 template <typename T>
 __global__ void s2d_stem_kernel(const T* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int C, int H, int W,
                                 long long sn, long long sc, long long sh, long long sw, int pt, int pl, int R,
                                 int Wo, int tw) {
-  const long long total = static_cast<long long>(N) * R * Wo * tw;
+  // One thread gathers one 2x2 pixel block (16 channels) ONCE and stores it to the tw output pixels it belongs to:
+  // block column Jb is tap j of output pixel Jb - j. (Gathering per (pixel, tap) read every input element tw times.)
+  const int S = Wo + tw - 1;                                   // block columns that feed some output pixel
+  const long long total = static_cast<long long>(N) * R * S;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const int cout = tw * 16;
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int j = static_cast<int>(i % tw);
-    long long t = i / tw;
-    const int J = static_cast<int>(t % Wo);
-    t /= Wo;
+    const int Jb = static_cast<int>(i % S);
+    long long t = i / S;
     const int I = static_cast<int>(t % R);
     const int n = static_cast<int>(t / R);
     alignas(16) __nv_bfloat16 v[16];
@@ -236,15 +238,21 @@ __global__ void s2d_stem_kernel(const T* __restrict__ x, __nv_bfloat16* __restri
       if (h < 0 || h >= H) continue;
 #pragma unroll
       for (int b = 0; b < 2; ++b) {
-        const int w = 2 * (J + j) + b - pl;
+        const int w = 2 * Jb + b - pl;
         if (w < 0 || w >= W) continue;
         const T* px = x + n * sn + h * sh + w * sw;
         for (int c = 0; c < C; ++c) v[(a * 2 + b) * C + c] = __float2bfloat16_rn(static_cast<float>(px[c * sc]));
       }
     }
-    uint4* dst = reinterpret_cast<uint4*>(y + i * 16);
-    dst[0] = *reinterpret_cast<const uint4*>(v);
-    dst[1] = *reinterpret_cast<const uint4*>(v + 8);
+    const uint4 lo = *reinterpret_cast<const uint4*>(v), hi = *reinterpret_cast<const uint4*>(v + 8);
+    __nv_bfloat16* row = y + (static_cast<long long>(n) * R + I) * Wo * cout;
+    for (int j = 0; j < tw; ++j) {
+      const int J = Jb - j;
+      if (J < 0 || J >= Wo) continue;
+      uint4* dst = reinterpret_cast<uint4*>(row + static_cast<long long>(J) * cout + j * 16);
+      dst[0] = lo;
+      dst[1] = hi;
+    }
   }
 }
 
@@ -253,7 +261,7 @@ extern "C" int bdl_s2d_stem_bf16(const void* x, int x_is_fp32, void* y, int N, i
                                  void* stream) {
   if (C < 1 || C > 4) return bdl_fail("bdl_s2d_stem_bf16: C must be 1..4");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const long long total = static_cast<long long>(N) * R * Wo * tw;
+  const long long total = static_cast<long long>(N) * R * (Wo + tw - 1);
   if (x_is_fp32)
     s2d_stem_kernel<float><<<grid_for(total), 256, 0, st>>>(static_cast<const float*>(x),
                                                             static_cast<__nv_bfloat16*>(y), N, C, H, W, sn, sc, sh,

@@ -67,3 +67,24 @@ def test_directed_graph():
         g.topologySort()
     d.delete(a)
     assert g.cloneGraph().size() == 4
+
+
+def test_nn_shape_helpers_follow_the_reference_rules():
+    from bigdl_b200.nn import utils as U
+    from bigdl_b200.nn.layer import Linear, Sequential
+
+    # Inception pool1: 112 -> 56 with 3x3/2 ceil mode, no padding
+    assert U.getOutSizeAndPadding(112, 112, 2, 2, 3, 3, 0, 0, True) == [0, 0, 0, 0, 56, 56]
+    assert U.getOutSizeAndPadding(112, 112, 2, 2, 3, 3, 0, 0, False)[-2:] == [55, 55]
+    # padded ceil mode drops a window that would start in the padding
+    assert U.getOutSizeAndPadding(4, 4, 2, 2, 2, 2, 1, 1, True)[-2:] == [3, 3]
+    assert U.getSAMEOutSizeAndPadding(224, 224, 2, 2, 7, 7) == [2, 3, 2, 3, 112, 112]
+    assert U.getSAMEOutSizeAndPadding(5, 5, 1, 1, 3, 3, 4, 1, 3)[-3:] == [4, 5, 5]
+    assert U.getPaddingAndOutputSize(112, 112, 2, 2, 3, 3, 0, 0, True) == (0, 1, 0, 1, 56, 56)
+    assert U.getOutputShape(7, 9, 16) == [16, 7, 9]
+    assert U.getOutputShape(7, 9, 16, 4, "NHWC") == [4, 7, 9, 16]
+    m = Sequential().add(Linear(4, 4)).add(Linear(4, 2))
+    assert not U.isLayerwiseScaled(m)
+    m.modules[1].setScaleW(0.5)
+    assert U.isLayerwiseScaled(m)
+    assert "Reshape" in U.ErrorInfo.constrainInputAsVectorOrBatch

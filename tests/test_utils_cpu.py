@@ -88,3 +88,31 @@ def test_nn_shape_helpers_follow_the_reference_rules():
     m.modules[1].setScaleW(0.5)
     assert U.isLayerwiseScaled(m)
     assert "Reshape" in U.ErrorInfo.constrainInputAsVectorOrBatch
+
+
+def test_reflection_utils_roundtrip_and_dnn_tensor():
+    import torch
+    from bigdl_b200.nn.layer import SpatialConvolution
+    from bigdl_b200.tensor import DnnTensor, Tensor
+    from bigdl_b200.utils.reflection import ReflectionUtils as R
+
+    conv = SpatialConvolution(3, 8, 5, 5, 2, 2, 1, 1)
+    op, args = R.reflectToIR(conv)
+    assert op == "SpatialConvolution" and args["n_output_plane"] == 8
+    assert R.getPrimCtorParams(SpatialConvolution)[:2] == ["n_input_plane", "n_output_plane"]
+    twin = R.reflectFromIR(op, args)
+    assert twin.weight.shape == conv.weight.shape and (twin.stride_h, twin.pad_w) == (2, 1)
+
+    before = DnnTensor.liveCount()
+    a, b = DnnTensor(2, 3, device="cpu"), DnnTensor([2, 3], device="cpu")
+    a.copy(Tensor(torch.arange(6.).reshape(2, 3)))
+    b.copy(a).axpby(2.0, 0.5, a)          # b = 2a + 0.5b = 2.5a
+    assert torch.allclose(b.dense().t, 2.5 * torch.arange(6.).reshape(2, 3))
+    assert a.size() == [2, 3] and a.size(2) == 3 and a.nElement() == 6 and DnnTensor.liveCount() == before + 2
+    a.release(); a.release()
+    assert a.isReleased() and DnnTensor.liveCount() == before + 1
+    try:
+        a.zero()
+        raise AssertionError("released tensor must refuse work")
+    except RuntimeError:
+        pass

@@ -118,6 +118,60 @@ class _DnnContainerMixin:
         return self
 
 
+class ReorderManager:
+    """Decides where layout conversions are needed and caches them (ReorderManager.scala): ``register(from, to)``
+    creates the ReorderMemory for a (producer format, consumer format) pair once; ``infer`` applies it."""
+
+    def __init__(self):
+        self._reorders: dict = {}
+
+    @staticmethod
+    def _key(a: MemoryData, b: MemoryData):
+        return (type(a).__name__, tuple(a.shape), a.layout, a.dtype, type(b).__name__, tuple(b.shape), b.layout, b.dtype)
+
+    def register(self, from_: MemoryData, to: MemoryData):
+        if self.needReorder(from_, to) and self._key(from_, to) not in self._reorders:
+            self._reorders[self._key(from_, to)] = ReorderMemory(from_, to)
+
+    @staticmethod
+    def needReorder(from_: MemoryData, to: MemoryData) -> bool:
+        return from_.layout != to.layout or from_.dtype != to.dtype
+
+    def infer(self, from_: MemoryData, to: MemoryData, output):
+        r = self._reorders.get(self._key(from_, to))
+        return output if r is None else r.forward(output)
+
+    def release(self):
+        self._reorders.clear()
+
+
+class TensorMMap:
+    """A parameter with a plain fp32 master ("dense") and the engine's compute copy ("native": bf16 on the GPU), kept
+    in step by ``sync()`` — the heap/native weight mirror of TensorMMap.scala:34-131. The flat parameter buffer of a
+    model does this for all layers at once; this class is the single-tensor form of the same contract."""
+
+    def __init__(self, size, device=None):
+        self.dense = torch.zeros(tuple(size))
+        dev = torch.device(device) if device is not None else torch.device(
+            "cuda" if torch.cuda.is_available() else "cpu")
+        self._native = torch.zeros(tuple(size), dtype=torch.bfloat16 if dev.type == "cuda" else torch.float32, device=dev)
+
+    def native(self) -> torch.Tensor:
+        return self._native
+
+    def sync(self):
+        """dense → native (called every training forward in the reference)."""
+        self._native.copy_(self.dense)
+        return self
+
+    def syncToHeap(self):
+        self.dense.copy_(self._native)
+        return self
+
+    def release(self):
+        self._native = None
+
+
 class Sequential(_Sequential, _DnnContainerMixin):
     """mkldnn.Sequential (S/nn/mkldnn/Sequential.scala:29-445)."""
 
@@ -217,3 +271,18 @@ class Fusion:
     fuse = staticmethod(fuse)
     unfuse = staticmethod(unfuse)
     fusionConvBn = staticmethod(fold_bn)
+
+
+# the reference's base classes of dnn layers / containers: every layer here already satisfies their contract
+MklDnnLayer = Module
+MklDnnContainer = _DnnContainerMixin
+
+
+class Perf:
+    """Local perf harness entry point (S/nn/mkldnn/Perf.scala:40-140): ``Perf.main(["-m", "resnet50", ...])``."""
+
+    @staticmethod
+    def main(argv=None):
+        from ..cli import perf
+
+        return perf.main(argv)

@@ -354,3 +354,230 @@ def all_reduce_result(res: ValidationResult) -> ValidationResult:
     if isinstance(res, ContiguousResult):
         return ContiguousResult(v[0], int(round(v[1])), res.name)
     return type(res).from_vector(v)
+
+
+# ---------------------------------------------------------------------------------------------- detection mAP
+class MAPType:
+    """Which interpolation the average precision uses (ValidationMethod.scala:410-413)."""
+    VOC2007, VOC2010, COCO = "voc2007", "voc2010", "coco"
+
+
+MAPPascalVoc2007, MAPPascalVoc2010, MAPCOCO = MAPType.VOC2007, MAPType.VOC2010, MAPType.COCO
+
+
+class MAPValidationResult(ValidationResult):
+    """Per-class (confidence, hit) lists + ground-truth counts; the AP is only computed in ``result()``
+    (ValidationMethod.scala:418-545). ``-1`` marks a COCO class without ground truth; such classes are left out of
+    the mean."""
+
+    def __init__(self, n_class, k, predict_for_class, gt_cnt, the_type=MAPPascalVoc2010, skip_class=-1):
+        assert skip_class == -1 or 0 <= skip_class < n_class, f"Invalid skipClass {skip_class}"
+        self.n_class, self.k, self.type, self.skip = n_class, k, the_type, skip_class
+        self.predict, self.gt_cnt = predict_for_class, list(gt_cnt)
+
+    def class_ap(self, c: int) -> float:
+        recs = sorted(self.predict[c], key=lambda r: -r[0])
+        if self.k > 0:
+            recs = recs[:self.k]
+        pos, tp, pnr = self.gt_cnt[c], 0, []
+        for j, (_, hit) in enumerate(recs):
+            if hit:
+                tp += 1
+                pnr.append((tp / pos, tp / (j + 1)))          # (recall, precision)
+
+        def max_p(recall):
+            return max((p for r, p in pnr if r >= recall), default=0.0)
+
+        if self.type == MAPPascalVoc2007:
+            return sum(max_p(0.1 * r) for r in range(11)) / 11
+        if self.type == MAPPascalVoc2010:
+            return sum(max_p(r / pos) for r in range(1, pos + 1)) / pos if pos else 0.0
+        if pos == 0:
+            return -1.0
+        return sum(max_p(0.01 * r) for r in range(101)) / 101
+
+    def result(self):
+        aps = [self.class_ap(c) for c in range(self.n_class) if c != self.skip]
+        if self.type == MAPCOCO:
+            valid = [a for a in aps if a != -1.0]
+            return (sum(valid) / len(valid) if valid else 0.0), 1
+        return sum(aps) / (self.n_class - (0 if self.skip == -1 else 1)), 1
+
+    def __add__(self, other):
+        return MAPValidationResult(self.n_class, self.k, [a + b for a, b in zip(self.predict, other.predict)],
+                                   [a + b for a, b in zip(self.gt_cnt, other.gt_cnt)], self.type, self.skip)
+
+    def as_vector(self):
+        raise NotImplementedError("detection results are gathered with all_gather_object")
+
+    def __repr__(self):
+        return f"MAPObjectDetection: {self.result()[0]}"
+
+
+class MAPMultiIOUValidationResult(ValidationResult):
+    """One MAPValidationResult per IoU threshold, averaged (COCO's mAP@[.5:.95]; ValidationMethod.scala:602-660)."""
+
+    def __init__(self, impl):
+        self.impl = list(impl)
+
+    def result(self):
+        return sum(r.result()[0] for r in self.impl) / len(self.impl), 1
+
+    def __add__(self, other):
+        assert len(self.impl) == len(other.impl)
+        return MAPMultiIOUValidationResult([a + b for a, b in zip(self.impl, other.impl)])
+
+    def as_vector(self):
+        raise NotImplementedError("detection results are gathered with all_gather_object")
+
+    def __repr__(self):
+        return f"MAPObjectDetection(multi-IoU): {self.result()[0]}"
+
+
+class _GroundTruth:
+    __slots__ = ("label", "diff", "box", "rle", "occupied", "coco")
+
+    def __init__(self, coco, n_iou, label, diff, box=None, rle=None):
+        self.coco, self.label, self.diff, self.box, self.rle = coco, label, diff, box, rle
+        self.occupied = [False] * n_iou
+
+    def can_occupy(self, i):        # a COCO crowd region may absorb any number of detections
+        return (self.coco and self.diff == 1) or not self.occupied[i]
+
+    def iou(self, x1, y1, x2, y2, det_rle=None):
+        if self.rle is not None:
+            from ..dataset.segmentation import MaskUtils
+
+            return MaskUtils.rleIOU(det_rle, self.rle, self.diff != 0)
+        gx1, gy1, gx2, gy2 = self.box
+        inter = max(min(gx2, x2) - max(gx1, x1) + 1, 0) * max(min(gy2, y2) - max(gy1, y1) + 1, 0)
+        det_area = (x2 - x1 + 1) * (y2 - y1 + 1)
+        union = det_area if (self.coco and self.diff != 0) else det_area + (gx2 - gx1 + 1) * (gy2 - gy1 + 1) - inter
+        return inter / union
+
+
+def _field(tab, key):
+    if isinstance(tab, dict):
+        return tab.get(key)
+    try:
+        return tab[key]
+    except (KeyError, IndexError):
+        return None
+
+
+def _table_items(t):
+    if isinstance(t, (list, tuple)):
+        return list(t)
+    if hasattr(t, "to_list"):
+        return t.to_list()
+    return [t[i] for i in range(1, len(t) + 1)]
+
+
+class MeanAveragePrecisionObjectDetection(ValidationMethod):
+    """Detection mAP, Pascal VOC 2007 / 2010 or COCO rules (ValidationMethod.scala:674-760, MAPUtil :286-408).
+
+    ``output``: per image a table ``{bboxes [n,4], classes [n], scores [n] (, masks)}`` — or one 2-D tensor whose
+    rows are ``[n, (label, score, x1, y1, x2, y2) * n]``; ``target``: per image ``{bboxes, classes ([n] or [2,n] with a
+    "difficult" row), is_crowd (, masks)}``. Class ids start at 0. Detections are matched greedily in descending score
+    order to the best still-free ground truth of their class with IoU >= threshold; a match to a difficult / crowd
+    region counts neither as hit nor as miss."""
+
+    def __init__(self, classes: int, topK: int = -1, iouThres=(0.5,), theType=MAPPascalVoc2010, skipClass: int = -1,
+                 isSegmentation: bool = False):
+        self.classes, self.k, self.iou = classes, topK, [float(v) for v in iouThres]
+        self.type, self.skip, self.seg = theType, skipClass, isSegmentation
+        self.name = "MAPObjectDetection"
+
+    def _ground_truth(self, target):
+        coco = self.type == MAPCOCO
+        gt_cnt = [0] * self.classes
+        images = []
+        for roi in _table_items(target):
+            regs = []
+            bbox = _field(roi, "bboxes") if roi is not None and len(roi) > 0 else None
+            if bbox is not None and len(bbox):
+                bbox = torch.as_tensor(bbox).float().reshape(-1, 4)
+                cls = torch.as_tensor(_field(roi, "classes")).float()
+                crowd = _field(roi, "is_crowd")
+                crowd = torch.zeros(bbox.shape[0]) if crowd is None else torch.as_tensor(crowd).float().reshape(-1)
+                masks = _field(roi, "masks") if self.seg else None
+                assert (cls.shape[-1] if cls.dim() == 2 else cls.numel()) == bbox.shape[0] == crowd.numel()
+                for j in range(bbox.shape[0]):
+                    label, d = (int(cls[0, j]), float(cls[1, j])) if cls.dim() == 2 else (int(cls.reshape(-1)[j]), 0.0)
+                    assert 0 <= label < self.classes, f"Bad label id {label}"
+                    diff = 1.0 if (float(crowd[j]) != 0 or d != 0) else 0.0
+                    regs.append(_GroundTruth(coco, len(self.iou), label, diff, tuple(float(v) for v in bbox[j]),
+                                             masks[j] if masks is not None else None))
+                    if diff == 0:
+                        gt_cnt[label] += 1
+            images.append(regs)
+        return images, gt_cnt
+
+    def _match(self, regs, label, score, x1, y1, x2, y2, mask, predict):
+        assert 0 <= label < self.classes, f"Bad label id {label}"
+        for i, thr in enumerate(self.iou):
+            best = None
+            for gt in regs:
+                if gt.label != label or not gt.can_occupy(i):
+                    continue
+                r = gt.iou(x1, y1, x2, y2, mask)
+                if r < thr:
+                    continue
+                if best is None or (gt.diff < best[0].diff if gt.diff != best[0].diff else r >= best[1]):
+                    best = (gt, r)
+            if best is not None:
+                best[0].occupied[i] = True
+            if best is None or best[0].diff == 0:
+                predict[i][label].append((score, best is not None))
+
+    def __call__(self, output, target):
+        images, gt_cnt = self._ground_truth(target)
+        predict = [[[] for _ in range(self.classes)] for _ in self.iou]
+        if isinstance(output, torch.Tensor):
+            assert not self.seg, "Cannot get segmentation data from tensor output for MAP"
+            out = output.float().cpu()
+            assert out.dim() == 2
+            for img in range(out.shape[0]):
+                n = int(out[img, 0])
+                for b in range(n):
+                    lab, sc, x1, y1, x2, y2 = (float(v) for v in out[img, 1 + 6 * b:7 + 6 * b])
+                    self._match(images[img], int(lab), sc, x1, y1, x2, y2, None, predict)
+        else:
+            outs = _table_items(output)
+            assert len(outs) == len(images), "The number of images in the output and in the target should be the same"
+            for regs, det in zip(images, outs):
+                if det is None or len(det) == 0:
+                    continue
+                bbox = torch.as_tensor(_field(det, "bboxes")).float().reshape(-1, 4)
+                scores = torch.as_tensor(_field(det, "scores")).float().reshape(-1)
+                labels = torch.as_tensor(_field(det, "classes")).float().reshape(-1)
+                masks = _field(det, "masks") if self.seg else None
+                assert bbox.shape[0] == labels.numel() == scores.numel()
+                for j in sorted(range(bbox.shape[0]), key=lambda q: -float(scores[q])):
+                    x1, y1, x2, y2 = (float(v) for v in bbox[j])
+                    self._match(regs, int(labels[j]), float(scores[j]), x1, y1, x2, y2,
+                                masks[j] if masks is not None else None, predict)
+        res = [MAPValidationResult(self.classes, self.k, p, gt_cnt, self.type, self.skip) for p in predict]
+        return res[0] if len(res) == 1 else MAPMultiIOUValidationResult(res)
+
+    # ---- factories of the reference's companion object (ValidationMethod.scala:762-840)
+    @staticmethod
+    def coco(nClasses: int, topK: int = -1, skipClass: int = 0, iouThres=(0.5, 0.05, 10), isSegmentation=False):
+        start, step, n = iouThres
+        return MeanAveragePrecisionObjectDetection(nClasses, topK, [start + i * step for i in range(n)], MAPCOCO,
+                                                   skipClass, isSegmentation)
+
+    @staticmethod
+    def pascalVOC(nClasses: int, useVoc2007: bool = False, topK: int = -1, skipClass: int = 0):
+        return MeanAveragePrecisionObjectDetection(nClasses, topK, (0.5,),
+                                                   MAPPascalVoc2007 if useVoc2007 else MAPPascalVoc2010, skipClass)
+
+
+MeanAveragePrecision.cocoBBox = staticmethod(
+    lambda nClasses, topK=-1, skipClass=0, iouThres=(0.5, 0.05, 10):
+    MeanAveragePrecisionObjectDetection.coco(nClasses, topK, skipClass, iouThres, False))
+MeanAveragePrecision.cocoSegmentation = staticmethod(
+    lambda nClasses, topK=-1, skipClass=0, iouThres=(0.5, 0.05, 10):
+    MeanAveragePrecisionObjectDetection.coco(nClasses, topK, skipClass, iouThres, True))
+MeanAveragePrecision.pascalVOC = staticmethod(MeanAveragePrecisionObjectDetection.pascalVOC)
+MeanAveragePrecision.classification = staticmethod(lambda nClasses, topK=-1: MeanAveragePrecision(topK, nClasses))

@@ -1,5 +1,7 @@
 """fp8 quantised inference (reference: S/nn/quantized/*, core/bigquant, S/nn/MklInt8Convertible.scala)."""
 from .layers import Linear, QuantizedModule, SpatialConvolution, SpatialDilatedConvolution
+from .quantization import Desc, QuantSerializer, Quantization
 from .quantizer import Quantizer
 
-__all__ = ["Linear", "QuantizedModule", "SpatialConvolution", "SpatialDilatedConvolution", "Quantizer"]
+__all__ = ["Linear", "QuantizedModule", "SpatialConvolution", "SpatialDilatedConvolution", "Quantizer", "Quantization", "Desc",
+           "QuantSerializer"]

@@ -75,3 +75,35 @@ def test_to_graph_shares_layers_and_matches():
     assert type(g).__name__ == "Graph" and torch.allclose(g.forward(x), ref)
     assert any(n.element is m.modules[0] for n in g.exec_order)
     assert g.toGraph() is g
+
+
+def test_reorder_manager_tensor_mmap_and_quantization_rule():
+    import torch
+    from bigdl_b200.nn import mkldnn as D
+    from bigdl_b200.quantized import Desc, QuantSerializer, Quantization
+    from bigdl_b200.nn.layer import SpatialConvolution
+
+    rm = D.ReorderManager()
+    a = D.HeapData([2, 4, 3, 3], D.Memory.Format.nchw)
+    b = D.NativeData([2, 4, 3, 3], D.Memory.Format.nhwc)
+    assert rm.needReorder(a, b) and not rm.needReorder(a, a.cloneFormat())
+    rm.register(a, b)
+    x = torch.randn(2, 4, 3, 3)
+    y = rm.infer(a, b, x)
+    assert torch.equal(x, y) and y.is_contiguous(memory_format=torch.channels_last)
+    assert rm.infer(b, a, x) is x           # not registered: passes through
+
+    mm = D.TensorMMap([3, 2], device="cpu")
+    mm.dense.copy_(torch.arange(6.).reshape(3, 2))
+    assert torch.equal(mm.sync().native(), mm.dense)
+    mm.native().mul_(2)
+    assert torch.equal(mm.syncToHeap().dense, 2 * torch.arange(6.).reshape(3, 2))
+
+    assert Quantization.quantize(0.5, 1.0, -2.0) == 32 and abs(Quantization.dequantize(32, 1.0, -2.0) - 0.5039) < 1e-3
+    w = torch.randn(6, 4, 3, 3)
+    q, mx, mn = Quantization.quantize_tensor(w)
+    assert q.dtype == torch.int8 and int(q.abs().max()) == 127
+    assert (Quantization.dequantize_tensor(q, mx, mn) - w).abs().max() <= float(w.abs().max()) / 127 * 0.51
+    assert Quantization.loss(w) < 0.02
+    d = Desc.of(SpatialConvolution(4, 6, 3, 3))
+    assert (d.nOutputPlane, d.nInputPlane, d.kernelH) == (6, 4, 3)

@@ -148,3 +148,19 @@ def test_quantize_model_that_was_already_fused():
     assert not q.modules[1]._fuse_relu and q.modules[0]._fuse_relu      # the ReLU moved into the conv epilogue
     out = q.forward(x)
     assert float((out - ref).norm() / ref.norm()) < 0.1
+
+
+def test_quant_serializer_roundtrip():
+    import torch
+    from bigdl_b200.nn.layer import Linear
+    from bigdl_b200.quantized import QuantSerializer
+    from bigdl_b200.quantized.layers import Linear as QLinear
+
+    torch.manual_seed(0)
+    a, b = QLinear.from_float(Linear(16, 8)), QLinear.from_float(Linear(16, 8))
+    x = torch.randn(4, 16)
+    assert not torch.allclose(a.forward(x), b.forward(x))
+    payload = QuantSerializer.serialize(a)
+    assert payload["weight_q"].dtype.name == "uint8" and payload["desc"] == {"outputSize": 8, "inputSize": 16}
+    QuantSerializer.deserialize(b, payload)
+    assert torch.equal(a.forward(x), b.forward(x))

@@ -116,3 +116,46 @@ def test_reflection_utils_roundtrip_and_dnn_tensor():
         raise AssertionError("released tensor must refuse work")
     except RuntimeError:
         pass
+
+
+def test_detection_map_voc_and_coco():
+    import torch
+    from bigdl_b200.optim.validation import (MAPCOCO, MAPPascalVoc2007, MeanAveragePrecision,
+                                              MeanAveragePrecisionObjectDetection)
+
+    # image 0: two class-1 objects (second one "difficult"), one class-2 object; image 1: one class-1 object
+    target = [
+        {"bboxes": torch.tensor([[10., 10, 50, 50], [100, 100, 150, 150], [200, 200, 260, 260]]),
+         "classes": torch.tensor([[1., 1, 2], [0, 1, 0]]), "is_crowd": torch.zeros(3)},
+        {"bboxes": torch.tensor([[20., 20, 80, 80]]), "classes": torch.tensor([1.]), "is_crowd": torch.zeros(1)},
+    ]
+    output = [
+        {"bboxes": torch.tensor([[12., 11, 50, 52], [11, 10, 49, 50], [100, 100, 150, 150], [205, 200, 260, 255],
+                                 [300, 300, 340, 340]]),
+         "classes": torch.tensor([1., 1, 1, 2, 2]), "scores": torch.tensor([0.9, 0.8, 0.7, 0.95, 0.3])},
+        {"bboxes": torch.tensor([[300., 300, 350, 350]]), "classes": torch.tensor([1.]), "scores": torch.tensor([0.85])},
+    ]
+    m = MeanAveragePrecisionObjectDetection(3, skipClass=0)
+    r = m(output, target)
+    # class 1: 2 countable GTs; ranked hits: 0.9 TP, 0.85 FP, 0.8 FP (duplicate), 0.7 ignored (difficult)
+    assert r.gt_cnt == [0, 2, 1]
+    assert sorted(r.predict[1], reverse=True) == [(0.9, True), (0.85, False), (0.8, False)] or \
+        [round(s, 2) for s, _ in sorted(r.predict[1], reverse=True)] == [0.9, 0.85, 0.8]
+    ap1 = r.class_ap(1)           # recall 0.5 at precision 1.0, recall 1.0 never reached -> (1.0 + 0) / 2
+    assert abs(ap1 - 0.5) < 1e-6
+    assert abs(r.class_ap(2) - 1.0) < 1e-6      # 0.95 TP first, then one FP
+    assert abs(r.result()[0] - 0.75) < 1e-6
+    # merging two halves equals one pass
+    a = m(output[:1], target[:1]) + m(output[1:], target[1:])
+    assert abs(a.result()[0] - 0.75) < 1e-6
+    v07 = MeanAveragePrecisionObjectDetection(3, theType=MAPPascalVoc2007, skipClass=0)(output, target)
+    assert abs(v07.class_ap(1) - 6 / 11) < 1e-6  # precision 1 for the recall points 0 .. 0.5
+    coco = MeanAveragePrecision.cocoBBox(3)(output, target)
+    assert 0.0 < coco.result()[0] <= 1.0 and len(coco.impl) == 10
+    # tensor form of the detections: [n, (label, score, x1, y1, x2, y2) * n]
+    row0 = [5.] + sum(([float(c), float(s)] + [float(v) for v in b] for b, c, s in
+                       zip(output[0]["bboxes"], output[0]["classes"], output[0]["scores"])), [])
+    row1 = [1., 1., 0.85, 300, 300, 350, 350] + [0.] * 24
+    t = MeanAveragePrecisionObjectDetection(3, skipClass=0)(torch.tensor([row0, row1]), target)
+    assert abs(t.result()[0] - 0.75) < 1e-6
+    assert MeanAveragePrecisionObjectDetection(3, theType=MAPCOCO, skipClass=0)(output, target).class_ap(0) == -1.0

@@ -119,6 +119,13 @@ def get_spark_sql_context(sc=None):
     return None
 
 
+def get_dtype(bigdl_type):
+    """numpy dtype of a bigdl_type string ("float" / "double")."""
+    import numpy as np
+
+    return np.float64 if bigdl_type == "double" else np.float32
+
+
 def to_list(a):
     return a if isinstance(a, list) else [a]
 

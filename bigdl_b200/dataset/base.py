@@ -400,3 +400,7 @@ def _sort_by_length(samples):
 
 DataSet.sortRDD = staticmethod(lambda data, is_in_order=True, group_size=1: DistributedDataSet(_sort_by_length(list(data))))
 DataSet.sort_rdd = DataSet.sortRDD
+
+
+# The reference's concrete distributed data set (one cached array per partition + a shuffled index, DataSet.scala:247-322)
+CachedDistriDataSet = DistributedDataSet

@@ -183,3 +183,6 @@ class LabeledSentenceToSample(Transformer):
 def read_sentences(path: str) -> list[str]:
     with open(path, encoding="utf-8") as f:
         return [l.strip() for l in f if l.strip()]
+
+
+from .base import PaddingParam  # noqa: E402,F401  (text pipelines pad variable-length sentences with it)

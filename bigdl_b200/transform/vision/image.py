@@ -680,6 +680,36 @@ class RoiResize(FeatureTransformer):
         f["label"].bboxes = f["label"].bboxes * np.array([w / ow, h / oh, w / ow, h / oh], dtype=np.float32)
 
 
+class ScaleResize(FeatureTransformer):
+    """Resize so that the shorter side becomes ``min_size`` unless that would push the longer side past ``max_size``
+    (then the longer side becomes ``max_size``); with ``resize_roi`` the RoiLabel boxes follow
+    (augmentation/ScaleResize.scala:41-90 — the Mask R-CNN evaluation resize)."""
+
+    def __init__(self, min_size: int, max_size: int = -1, resize_roi: bool = False):
+        self.min_size, self.max_size, self.resize_roi = min_size, max_size, resize_roi
+
+    def _size(self, h: int, w: int):
+        size = self.min_size
+        if self.max_size > 0:
+            lo, hi = (h, w) if w > h else (w, h)
+            if hi / lo * size > self.max_size:
+                size = int(round(self.max_size * lo / hi))
+        if (w <= h and w == size) or (h <= w and h == size):
+            return h, w
+        return (size * h // w, size) if w < h else (size, size * w // h)
+
+    def transformMat(self, f):
+        import cv2
+
+        h, w = f["mat"].shape[:2]
+        nh, nw = self._size(h, w)
+        f["mat"] = cv2.resize(f["mat"], (nw, nh), interpolation=cv2.INTER_LINEAR)
+        lab = f.get("label") if hasattr(f, "get") else None
+        if self.resize_roi and isinstance(lab, RoiLabel):
+            oh, ow = (f.get("originalSize") or (h, w))[:2]
+            lab.bboxes = lab.bboxes * np.array([nw / ow, nh / oh, nw / ow, nh / oh], dtype=np.float32)
+
+
 class RoiProject(FeatureTransformer):
     """Project normalised boxes into the crop/expand window stored by the preceding transformer and drop boxes that
     fall outside (RoiProject.scala; ``need_meet_center_constraint`` keeps only boxes whose centre is inside)."""

@@ -194,3 +194,18 @@ def test_gpu_image_batcher_cpu_path_is_deterministic_and_normalised():
     c = image_batch(frames, 32, 32, (100, 110, 120), (50, 55, 60), dtype=torch.float32)
     ref = (frames[:, 2:34, 4:36].float() - torch.tensor([100., 110., 120.])) / torch.tensor([50., 55., 60.])
     assert torch.allclose(c, ref.permute(0, 3, 1, 2))
+
+
+def test_scale_resize_rule_and_aliases():
+    import numpy as np
+    from bigdl_b200.dataset.base import CachedDistriDataSet, DistributedDataSet
+    from bigdl_b200.transform.vision.image import ScaleResize
+
+    t = ScaleResize(800, 1333)
+    assert t._size(480, 640) == (800, 1066)        # shorter side to 800
+    assert t._size(300, 1200) == (333, 1332)       # capped by the longer side
+    assert t._size(800, 1000) == (800, 1000)       # already there
+    f = {"mat": np.zeros((48, 64, 3), np.uint8)}
+    ScaleResize(24).transformMat(f)
+    assert f["mat"].shape[:2] == (24, 32)
+    assert CachedDistriDataSet is DistributedDataSet

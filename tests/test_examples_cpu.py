@@ -57,3 +57,7 @@ def test_cli_tools(tmp_path, capsys):
 
     ds = seq_file_dataset(str(tmp_path / "seq" / "train"), 1000, distributed=False)
     assert ds.size() == 6
+
+
+def test_tree_lstm_sentiment_example_learns():
+    assert _load("tree_lstm_sentiment").main(["-e", "3"]) > 0.7

@@ -88,6 +88,8 @@ def _capture_ctor(cls):
     cls.__init__ = wrapped
 
 
+_NVTX = [False]       # set by utils.profiling.enable_nvtx
+
 class Module:
     """Base class of every layer (reference: AbstractModule[A, B, T])."""
 
@@ -411,7 +413,14 @@ class Module:
         pre = self.__dict__.get("_pre_call_hook")      # ParallelOptimizer bucket boundary / lazy parameter update
         if pre is not None:
             input = pre(self, input)
-        out = self.updateOutput(input)
+        if _NVTX[0]:                                   # utils/profiling.enable_nvtx: one range per layer call
+            torch.cuda.nvtx.range_push(f"{type(self).__name__}:{self.getName()}")
+            try:
+                out = self.updateOutput(input)
+            finally:
+                torch.cuda.nvtx.range_pop()
+        else:
+            out = self.updateOutput(input)
         self.output = out
         return out
 

@@ -36,6 +36,7 @@ _DEFAULTS: dict[str, Any] = {
     "bigdl.mkldnn.fusion.convsum": True,
     # misc
     "bigdl.cudaGraph": True,
+    "bigdl.nvtx": False,                     # NVTX range per layer call (utils/profiling.py)
     "bigdl.wgrad.stream": False,             # issue weight-gradient GEMMs on a side stream (joined after backward)
     "bigdl.concat.streams": True,            # run the branches of a channel Concat on side streams
     "bigdl.utils.LoggerFilter.disable": False,

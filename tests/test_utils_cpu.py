@@ -159,3 +159,18 @@ def test_detection_map_voc_and_coco():
     t = MeanAveragePrecisionObjectDetection(3, skipClass=0)(torch.tensor([row0, row1]), target)
     assert abs(t.result()[0] - 0.75) < 1e-6
     assert MeanAveragePrecisionObjectDetection(3, theType=MAPCOCO, skipClass=0)(output, target).class_ap(0) == -1.0
+
+
+def test_profile_layers_reports_every_leaf_once():
+    import torch
+    from bigdl_b200.nn.layer import Linear, ReLU, Sequential
+    from bigdl_b200.utils.profiling import enable_nvtx, format_profile, profile_layers
+
+    m = Sequential().add(Linear(8, 16).setName("fc1")).add(ReLU().setName("act")).add(Linear(16, 4).setName("fc2"))
+    rows = profile_layers(m, torch.randn(5, 8), warmup=1, iters=2)
+    assert [r[0] for r in rows] == ["fc1", "act", "fc2"] and all(r[2] >= 0 for r in rows)
+    assert "fc2" in format_profile(rows)
+    assert "updateOutput" not in m.modules[0].__dict__          # wrappers removed
+    enable_nvtx(True)                                           # no GPU here: stays off, forward still works
+    assert m.forward(torch.randn(2, 8)).shape == (2, 4)
+    enable_nvtx(False)

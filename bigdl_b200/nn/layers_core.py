@@ -185,6 +185,11 @@ class SpatialConvolution(Module):
             geom = (self.kernel_h, self.kernel_w, self.stride_h, self.stride_w, pt, pl, pb, pr, self.dilation_h,
                     self.dilation_w, self.n_group)
             xin = x if self.propagate_back else x.detach()
+            res = self.__dict__.pop("_next_residual", None)     # conv + sum fusion (set by a fused ConcatTable)
+            if res is not None:
+                from ..ops.functions import set_residual_hint
+
+                set_residual_hint(res)
             hint = self.__dict__.pop("_next_out_hint", None)
             if hint is not None:
                 from ..ops.functions import set_out_hint

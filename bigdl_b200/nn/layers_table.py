@@ -130,7 +130,32 @@ class Concat(Container):
 
 class ConcatTable(Container):
     def updateOutput(self, input):
+        tail = self.__dict__.get("_res_tail")
+        if (tail is not None and not self.isTraining() and isinstance(input, torch.Tensor) and input.is_cuda
+                and not torch.is_grad_enabled()):       # the fused conv has no backward for the shortcut operand
+            fused = self._residual_forward(input, tail)
+            if fused is not None:
+                return fused
         return Table(*[m._call(input) for m in self.modules])
+
+    def _residual_forward(self, input, tail):
+        """Inference residual block with the sum folded into the main branch's last convolution (fusion.py marks
+        ``_res_tail`` / ``_res_main`` / ``_res_relu``): the shortcut runs first, the tail conv adds it (and applies the
+        ReLU that follows the CAddTable) in its GEMM epilogue. Returns a one-element table whose tensor is tagged as
+        already summed, or None when the convolution could not take the residual (then the plain path runs)."""
+        from ..ops.functions import take_residual_hint
+
+        main = self.__dict__["_res_main"]
+        shortcut = self.modules[1 - main]._call(input)
+        if not (isinstance(shortcut, torch.Tensor) and shortcut.dtype == torch.bfloat16):
+            return None
+        tail.__dict__["_next_residual"] = (shortcut, bool(self.__dict__.get("_res_relu", False)))
+        y = self.modules[main]._call(input)
+        tail.__dict__.pop("_next_residual", None)
+        if take_residual_hint() is not None:          # the conv did not consume it: finish with an ordinary add
+            return Table(y, shortcut) if main == 0 else Table(shortcut, y)
+        y._bdl_sum_done = True
+        return Table(y)
 
 
 class ParallelTable(Container):
@@ -262,6 +287,8 @@ class CAddTable(_CReduce):
 
     def updateOutput(self, input):
         xs = _tl(input)
+        if len(xs) == 1 and getattr(xs[0], "_bdl_sum_done", False):
+            return xs[0]          # a fused ConcatTable already added the shortcut (and applied the ReLU) in the conv
         if (len(xs) == 2 and xs[0].is_cuda and xs[0].dtype == torch.bfloat16 and xs[1].dtype == torch.bfloat16
                 and xs[0].shape == xs[1].shape):
             from .layers_core import native

@@ -107,6 +107,21 @@ def _take_out_hint():
     return h
 
 
+_RES_HINT: list = [None]
+
+
+def set_residual_hint(res):
+    """``(shortcut [N,O,Ho,Wo] bf16, relu)``: the next ConvFn.forward that can (1x1 direct or implicit-GEMM path, no
+    autograd) adds the shortcut and applies the ReLU in its GEMM epilogue — the conv + sum fusion of a residual block
+    (S/nn/mkldnn/Fusion.scala fusionCAddTable). ``take_residual_hint`` returns it if nobody consumed it."""
+    _RES_HINT[0] = res
+
+
+def take_residual_hint():
+    h, _RES_HINT[0] = _RES_HINT[0], None
+    return h
+
+
 # Gradients that already had a consumer's ReLU mask applied and its bias gradient summed, keyed by (data_ptr, shape):
 # ConcatViewFn.backward does that once for all branch tails of a Concat; the tails' ConvFn.backward picks its slice up
 # here instead of running its own column-sum pass. Cleared after every backward (join_side_streams).
@@ -360,8 +375,18 @@ class ConvFn(Function):
         b32 = bias.detach() if bias is not None else None
         implicit = (not direct) and groups == 1 and C % 8 == 0 and C >= 16 and O % 8 == 0 and _IGEMM[0]
         kept_cols = None
+        res2d = None
+        if _RES_HINT[0] is not None and groups == 1 and (implicit or direct):     # only set under no_grad (ConcatTable)
+            rs, rrelu = take_residual_hint()
+            if tuple(rs.shape) == (N, O, Ho, Wo) and rs.dtype == torch.bfloat16:
+                rn, ldr = nhwc_pitched(rs)
+                res2d, relu = rows2d(rn, ldr), bool(relu or rrelu)
+                ctx.fused_residual = True
+            else:
+                set_residual_hint((rs, rrelu))          # shapes disagree: leave it to the caller's add
         if implicit:
-            conv_igemm(0, xn, ldx, w2, y2, O, Ho, Wo, kh, kw, sh, sw, pt, pl, dh, dw, bias=b32, relu=relu)
+            conv_igemm(0, xn, ldx, w2, y2, O, Ho, Wo, kh, kw, sh, sw, pt, pl, dh, dw, bias=b32, relu=relu,
+                       residual=res2d)
         for g in range(groups if not implicit else 0):
             wg = w2[g * Og:(g + 1) * Og]
             if Kp != K:
@@ -384,7 +409,7 @@ class ConvFn(Function):
                 _lib.count_launch()
                 if keep:
                     kept_cols = a
-            gemm_bf16(a, wg, bias=bg, relu=relu, out=y2[:, g * Og:(g + 1) * Og])
+            gemm_bf16(a, wg, bias=bg, relu=relu, out=y2[:, g * Og:(g + 1) * Og], residual=res2d if direct else None)
         ctx.kept_cols = kept_cols
         ctx.save_for_backward(xn, w4, y if relu else None)
         ctx.params = (weight, bias, geom, relu, scale_w, scale_b,

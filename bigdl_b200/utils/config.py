@@ -34,6 +34,7 @@ _DEFAULTS: dict[str, Any] = {
     "bigdl.mkldnn.fusion.bnrelu": True,
     "bigdl.mkldnn.fusion.convrelu": True,
     "bigdl.mkldnn.fusion.convsum": True,
+    "bigdl.fusion.residual": True,           # inference: shortcut add + ReLU inside the last conv's GEMM epilogue
     # misc
     "bigdl.cudaGraph": True,
     "bigdl.nvtx": False,                     # NVTX range per layer call (utils/profiling.py)

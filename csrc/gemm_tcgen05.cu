@@ -70,6 +70,8 @@ struct GemmParams {
   const float* bias;
   const float* col_scale;    // fp8 only: per-output-column dequantisation scale
   const float* out_qscale;   // fp8 only, out_fp32 == 2: device scalar 448 / absmax of the next layer's input
+  const __nv_bfloat16* residual;   // optional [M, N] bf16 tensor (row pitch ldr) added before the ReLU: the shortcut of a
+  long long ldr;                   // residual block, so conv + add + ReLU is one pass (reference: Fusion.fusionCAddTable)
   // implicit-GEMM convolution (kConv != 0): the A (fprop/dgrad) or B (wgrad) operand is gathered from an NHWC
   // activation tensor by TMA im2col loads instead of being read from a materialised column matrix.
   int cv_Ho, cv_Wo;          // output spatial size of the traversal
@@ -113,6 +115,21 @@ __device__ __forceinline__ void epilogue_store16(const GemmParams& p, const uint
     for (int j = 0; j < 16; j += 4) {
       const float4 b4 = *reinterpret_cast<const float4*>(sb + j);
       v[j] += b4.x; v[j + 1] += b4.y; v[j + 2] += b4.z; v[j + 3] += b4.w;
+    }
+  }
+  if (p.residual) {
+    const __nv_bfloat16* rp = p.residual + static_cast<long long>(row) * p.ldr + n0;
+    if (full && ((reinterpret_cast<uintptr_t>(rp) & 15u) == 0)) {
+      const uint4 r0 = __ldg(reinterpret_cast<const uint4*>(rp)), r1 = __ldg(reinterpret_cast<const uint4*>(rp) + 1);
+      const uint32_t w[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        v[2 * j] += __uint_as_float(w[j] << 16);
+        v[2 * j + 1] += __uint_as_float(w[j] & 0xFFFF0000u);
+      }
+    } else {
+      for (int j = 0; j < 16; ++j)
+        if (j < nvalid) v[j] += __bfloat162float(rp[j]);
     }
   }
   if (p.flags & BDL_GEMM_RELU) {
@@ -598,6 +615,17 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
 }
 
 // ------------------------------------------------------------------------------------------- host
+// The residual operand of the NEXT launch from this host thread (bdl_gemm_set_residual): consumed and cleared by
+// bdl_gemm_bf16 / bdl_conv_igemm_bf16 / bdl_gemm_fp8, so the launch signatures stay as they are.
+static thread_local const void* g_next_residual = nullptr;
+static thread_local long long g_next_ldr = 0;
+static void take_residual(GemmParams& p) {
+  p.residual = static_cast<const __nv_bfloat16*>(g_next_residual);
+  p.ldr = g_next_ldr;
+  g_next_residual = nullptr;
+  g_next_ldr = 0;
+}
+
 // Two stacked 128-row tiles per CTA (see GemmParams::dual_m): only when the halved tile count still fills the SMs,
 // directly or through the K split.
 static bool want_dual_m(int M, long long tiles_n, int num_kb, int num_sms, bool atomic) {
@@ -660,6 +688,8 @@ extern "C" int bdl_gemm_bf16(const void* A, const void* B, void* D, const float*
     return bdl_fail("bdl_gemm_bf16: A/B must be 16-byte aligned with leading dimensions that are multiples of 8");
   const int num_sms = bdl_num_sms();
   GemmParams p{};
+  take_residual(p);
+  if (p.residual && ((flags & BDL_GEMM_ATOMIC_ADD) || out_fp32)) return bdl_fail("bdl_gemm_bf16: residual needs a bf16 output");
   p.M = M;
   p.N = N;
   p.K = K;
@@ -756,6 +786,8 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
   if (Mpix >= (1ll << 31)) return bdl_fail("bdl_conv_igemm_bf16: too many output pixels");
   const int taps = kh * kw;
   GemmParams p{};
+  take_residual(p);
+  if (p.residual && (mode != 0 || out_fp32)) return bdl_fail("bdl_conv_igemm_bf16: residual is a forward, bf16-output option");
   p.cv_Ho = Ho; p.cv_Wo = Wo; p.cv_sh = sh; p.cv_sw = sw; p.cv_ph = ph; p.cv_pw = pw; p.cv_dh = dh; p.cv_dw = dw;
   p.cv_kh = kh; p.cv_kw = kw; p.cv_C = C; p.cv_cblocks = (C + 63) / 64; p.cv_flip = (mode == 1); p.cv_nimg = N;
   p.fd_hw.init(static_cast<uint32_t>(Ho) * Wo);
@@ -886,6 +918,7 @@ extern "C" int bdl_gemm_fp8(const void* A, const void* B, void* D, const float* 
   if (flags & BDL_GEMM_ATOMIC_ADD) return bdl_fail("bdl_gemm_fp8: inference kernel, no accumulate mode");
   const int num_sms = bdl_num_sms();
   GemmParams p{};
+  take_residual(p);
   const int* cg = static_cast<const int*>(conv_geom);   // {N,H,W,C,Ho,Wo,kh,kw,sh,sw,ph,pw,dh,dw} or NULL
   int gm = M;
   if (cg) {
@@ -947,4 +980,11 @@ extern "C" int bdl_gemm_fp8(const void* A, const void* B, void* D, const float* 
     kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, p);
   }
   return bdl_check_launch("gemm_tcgen05_kernel<fp8>");
+}
+
+extern "C" int bdl_gemm_set_residual(const void* residual_bf16, long long ld) {
+  if (residual_bf16 && ld <= 0) return bdl_fail("bdl_gemm_set_residual: row pitch must be positive");
+  g_next_residual = residual_bf16;
+  g_next_ldr = ld;
+  return BDL_OK;
 }

@@ -32,6 +32,10 @@ int bdl_stream_capture_status(void* stream);
 #define BDL_GEMM_BIAS 1
 #define BDL_GEMM_RELU 2
 #define BDL_GEMM_ATOMIC_ADD 4
+/* Residual operand of the NEXT bdl_gemm_bf16 / bdl_conv_igemm_bf16 (fprop) / bdl_gemm_fp8 launch issued by this host
+ * thread: D = act(A*B + bias + residual), residual bf16 [M,N] with row pitch ld (elements). Cleared by that launch.
+ * Reference: the conv + sum post-op of S/nn/mkldnn/Fusion.scala (fusionCAddTable). */
+int bdl_gemm_set_residual(const void* residual_bf16, long long ld);
 int bdl_gemm_bf16(const void* A, const void* B, void* D, const float* bias, int M, int N, int K, long long lda,
                   long long ldb, long long ldd, int a_mn, int b_mn, int out_fp32, int flags, int splits, void* stream);
 /* Implicit-GEMM convolution on the same kernel: the gathered operand is fetched from the NHWC activation tensor by

@@ -180,3 +180,70 @@ def test_concat_side_streams_match_single_stream(graph):
     # identical kernels and inputs; only fp32 atomic accumulation order may differ
     assert _rel(w1, w0) < 2e-3, _rel(w1, w0)
     assert abs(l1 - l0) < 2e-2 * max(abs(l0), 1.0)
+
+
+@pytest.mark.parametrize("kind", ["bottleneck_identity", "bottleneck_projection", "basic"])
+def test_residual_block_conv_sum_fusion_matches_unfused(kind):
+    """Inference residual block: shortcut add + ReLU folded into the last convolution's GEMM epilogue must equal the
+    separate add kernel, and must actually be taken (one launch fewer, tagged output)."""
+    from bigdl_b200.nn.fusion import fold_bn, fuse
+    from bigdl_b200.nn.layer import (CAddTable, ConcatTable, Identity, ReLU, Sequential, SpatialBatchNormalization,
+                                     SpatialConvolution)
+    from bigdl_b200.ops import _lib
+    from bigdl_b200.utils import config
+    from bigdl_b200.utils.random_generator import RNG
+
+    RNG.setSeed(9)
+    torch.manual_seed(9)
+    n_in, n = (64, 16) if kind != "basic" else (32, 32)
+
+    def bn(c):
+        b = SpatialBatchNormalization(c)
+        b._buffers["runningMean"].normal_(0, 0.2)
+        b._buffers["runningVar"].uniform_(0.5, 1.5)
+        return b
+
+    s = Sequential()
+    if kind == "basic":
+        s.add(SpatialConvolution(n_in, n, 3, 3, 1, 1, 1, 1)).add(bn(n)).add(ReLU(True))
+        s.add(SpatialConvolution(n, n, 3, 3, 1, 1, 1, 1)).add(bn(n))
+        n_out = n
+    else:
+        s.add(SpatialConvolution(n_in, n, 1, 1)).add(bn(n)).add(ReLU(True))
+        s.add(SpatialConvolution(n, n, 3, 3, 1, 1, 1, 1)).add(bn(n)).add(ReLU(True))
+        s.add(SpatialConvolution(n, n * 4, 1, 1)).add(bn(n * 4))
+        n_out = n * 4
+    if kind == "bottleneck_projection":
+        short = Sequential().add(SpatialConvolution(n_in, n_out, 1, 1)).add(bn(n_out))
+    else:
+        short = Identity()
+    block = Sequential().add(ConcatTable().add(s).add(short)).add(CAddTable(True)).add(ReLU(True))
+    block.evaluate()
+    fold_bn(block)
+    block.cuda()
+    x = torch.randn(4, n_in, 14, 14, device="cuda").bfloat16().contiguous(memory_format=torch.channels_last)
+    outs, launches = {}, {}
+    for fused in (False, True):
+        config.set("bigdl.fusion.residual", fused)
+        try:
+            from bigdl_b200.nn.fusion import unfuse
+            unfuse(block)
+            fuse(block)
+            with torch.no_grad():
+                block._call(x)                      # warm-up (tensor maps, lazy state)
+                n0 = _lib.LAUNCHES
+                outs[fused] = block._call(x).float()
+                launches[fused] = _lib.LAUNCHES - n0
+        finally:
+            config.unset("bigdl.fusion.residual")
+    torch.cuda.synchronize()
+    with torch.no_grad():
+        config.set("bigdl.fusion.residual", True)
+        fuse(block)
+        t = block.modules[0]._call(x)
+        config.unset("bigdl.fusion.residual")
+    assert len(t) == 1 and getattr(t[1], "_bdl_sum_done", False), "the convolution did not take the shortcut"
+    assert launches[True] < launches[False], launches
+    err = (outs[True] - outs[False]).abs().max().item()
+    assert err <= 2e-2 * outs[False].abs().max().item() + 1e-2, err
+    assert float(outs[True].min()) >= 0.0

@@ -199,12 +199,53 @@ __device__ __forceinline__ void epilogue_store16(const GemmParams& p, const uint
   }
 }
 
+// Math of one 16-column chunk only (bias, residual, ReLU) -> 16 bf16 packed into two 16-byte vectors, for the
+// shared-memory staged TMA-store epilogue. nvalid <= 0 or row >= M: the values are never written (the TMA store clips).
+__device__ __forceinline__ void epilogue_pack16(const GemmParams& p, const uint32_t* r, int row, int n0, int nvalid,
+                                                const float* sb, bool has_bias, uint4& q0, uint4& q1) {
+  float v[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
+  if (has_bias) {
+#pragma unroll
+    for (int j = 0; j < 16; j += 4) {
+      const float4 b4 = *reinterpret_cast<const float4*>(sb + j);
+      v[j] += b4.x; v[j + 1] += b4.y; v[j + 2] += b4.z; v[j + 3] += b4.w;
+    }
+  }
+  if (p.residual && row < p.M && nvalid > 0) {
+    const __nv_bfloat16* rp = p.residual + static_cast<long long>(row) * p.ldr + n0;
+    if (nvalid >= 16 && ((reinterpret_cast<uintptr_t>(rp) & 15u) == 0)) {
+      const uint4 r0 = __ldg(reinterpret_cast<const uint4*>(rp)), r1 = __ldg(reinterpret_cast<const uint4*>(rp) + 1);
+      const uint32_t w[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        v[2 * j] += __uint_as_float(w[j] << 16);
+        v[2 * j + 1] += __uint_as_float(w[j] & 0xFFFF0000u);
+      }
+    } else {
+      for (int j = 0; j < 16; ++j)
+        if (j < nvalid) v[j] += __bfloat162float(rp[j]);
+    }
+  }
+  if (p.flags & BDL_GEMM_RELU) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
+  }
+  q0.x = pack_bf16x2(v[0], v[1]);   q0.y = pack_bf16x2(v[2], v[3]);
+  q0.z = pack_bf16x2(v[4], v[5]);   q0.w = pack_bf16x2(v[6], v[7]);
+  q1.x = pack_bf16x2(v[8], v[9]);   q1.y = pack_bf16x2(v[10], v[11]);
+  q1.z = pack_bf16x2(v[12], v[13]); q1.w = pack_bf16x2(v[14], v[15]);
+}
+
 // kFp8: operands are e4m3 bytes (128 per swizzle row, UMMA K = 32) multiplied with kind::f8f6f4; the epilogue applies a
 //       per-output-column fp32 scale (activation scale x per-channel weight scale) before bias/ReLU. K-major only.
-template <bool kAMN, bool kBMN, int kConv, bool kFp8 = false, bool kDual = false>
+// kTmaStore: bf16 outputs leave through shared memory and TMA stores (one 32-row x 128-byte box per warp and 64-column
+//       group) instead of 32-byte per-row stores; the staging area follows the pipeline stages in dynamic smem.
+template <bool kAMN, bool kBMN, int kConv, bool kFp8 = false, bool kDual = false, bool kTmaStore = false>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                         const GemmParams p) {
+                         const __grid_constant__ CUtensorMap tmD, const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[kMaxStages];
   __shared__ __align__(8) uint64_t empty_bar[kMaxStages];
@@ -547,6 +588,47 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       mbar_wait(smem_u32(&tfull_bar[acc]), acc_phase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((quad * 32u) << 16) + acc * kAccStride;
+      if (kTmaStore) {
+        // this warp's staging box: 32 rows x 128 bytes, 16-byte chunks XOR-swizzled by (row & 7) like the tensor map
+        const uint32_t stg = tiles + static_cast<uint32_t>(p.num_stages) * stage_bytes + (warp - 2u) * 4096u;
+        const int row0 = (m_blk * nhalves + hm) * BM + static_cast<int>(quad * 32u);
+        const int g_split = ((p.block_n + 127) / 128) * 64;
+        const int g_begin = half ? g_split : 0;
+        const int g_end = half ? ((p.block_n + 63) / 64) * 64 : g_split;
+        for (int c = g_begin; c < g_end; c += 64) {
+          uint32_t r0[16], r1[16], r2[16], r3[16];
+          tmem_ld_16(t_row + static_cast<uint32_t>(c), r0);
+          tmem_ld_16(t_row + static_cast<uint32_t>(c + 16), r1);
+          tmem_ld_16(t_row + static_cast<uint32_t>(c + 32), r2);
+          tmem_ld_16(t_row + static_cast<uint32_t>(c + 48), r3);
+          if (lane == 0) tma_store_wait_read0();      // the previous box has left the staging buffer
+          __syncwarp();
+          tmem_ld_wait();
+          uint4 q[8];
+          epilogue_pack16(p, r0, row, nbase + c, p.N - (nbase + c), sb + c, has_bias, q[0], q[1]);
+          epilogue_pack16(p, r1, row, nbase + c + 16, p.N - (nbase + c + 16), sb + c + 16, has_bias, q[2], q[3]);
+          epilogue_pack16(p, r2, row, nbase + c + 32, p.N - (nbase + c + 32), sb + c + 32, has_bias, q[4], q[5]);
+          epilogue_pack16(p, r3, row, nbase + c + 48, p.N - (nbase + c + 48), sb + c + 48, has_bias, q[6], q[7]);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t a = stg + lane * 128u + ((static_cast<uint32_t>(j) ^ (lane & 7u)) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(q[j].x), "r"(q[j].y), "r"(q[j].z),
+                         "r"(q[j].w) : "memory");
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmD, stg, nbase + c, row0);
+            tma_store_commit();
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
+        acc ^= 1u;
+        if (acc == 0) acc_phase ^= 1u;
+        continue;
+      }
       const bool row_ok = row < p.M;
       // the two warps of a TMEM lane quadrant split the tile's columns
       const int c_split = ((p.block_n / 16 + 1) / 2) * 16;
@@ -609,6 +691,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     }
   }
 
+  if (kTmaStore && warp >= 2 && lane == 0) tma_store_wait0();   // shared memory must outlive the bulk stores
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc<kTmemCols>(tmem_base);
@@ -624,6 +707,15 @@ static void take_residual(GemmParams& p) {
   p.ldr = g_next_ldr;
   g_next_residual = nullptr;
   g_next_ldr = 0;
+}
+
+// bf16, non-accumulating outputs can leave through shared memory + TMA stores (kTmaStore): needs a 16-byte aligned D
+// whose row pitch is a multiple of 8 elements. max_kb: only epilogue-heavy problems (short reductions) take it.
+constexpr size_t kStageOutBytes = 8 * 4096;
+static bool want_tma_store(const void* D, long long ldd, int out_fp32, int flags, bool a_mn, int num_kb) {
+  static const int max_kb = [] { const char* e = getenv("BDL_GEMM_TMA_STORE_KB"); return e ? atoi(e) : 1 << 30; }();
+  return max_kb > 0 && num_kb <= max_kb && !a_mn && !out_fp32 && !(flags & BDL_GEMM_ATOMIC_ADD) && (ldd % 8) == 0 &&
+         (reinterpret_cast<uintptr_t>(D) & 15u) == 0;
 }
 
 // Two stacked 128-row tiles per CTA (see GemmParams::dual_m): only when the halved tile count still fills the SMs,
@@ -720,12 +812,18 @@ extern "C" int bdl_gemm_bf16(const void* A, const void* B, void* D, const float*
   p.D = D;
   p.bias = bias;
   const size_t stage_bytes = static_cast<size_t>(BM) * BK * 2 * (p.dual_m ? 2 : 1) + static_cast<size_t>(p.b_rows) * BK * 2;
-  const size_t budget = kSmemBudget;
+  const bool tma_out = want_tma_store(D, ldd, out_fp32, flags, a_mn != 0, num_kb);
+  const size_t budget = kSmemBudget - (tma_out ? kStageOutBytes : 0);
   int stages = static_cast<int>(budget / stage_bytes);
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) return bdl_fail("bdl_gemm_bf16: tile does not fit in shared memory");
   p.num_stages = stages;
-  const size_t smem = stages * stage_bytes + 1024;
+  const size_t smem = stages * stage_bytes + 1024 + (tma_out ? kStageOutBytes : 0);
+  CUtensorMap tmD{};
+  if (tma_out) {
+    const int rcd = bdl_make_tmap_2d_bf16(&tmD, D, static_cast<uint64_t>(N), static_cast<uint64_t>(M), ldd, 64, 32);
+    if (rcd) return rcd;
+  }
 
   CUtensorMap tmA, tmB;
   int rc;
@@ -744,11 +842,12 @@ extern "C" int bdl_gemm_bf16(const void* A, const void* B, void* D, const float*
   const int grid = static_cast<int>(total < num_sms ? total : num_sms);
 #define BDL_LAUNCH_GEMM(AMN, BMN)                                                                                 \
   do {                                                                                                            \
-    auto kfn = p.dual_m ? gemm_bf16_tcgen05_kernel<AMN, BMN, 0, false, true>                                         \
-                        : gemm_bf16_tcgen05_kernel<AMN, BMN, 0, false, false>;                                       \
+    auto kfn = p.dual_m ? gemm_bf16_tcgen05_kernel<AMN, BMN, 0, false, true, false>                                  \
+               : (tma_out && !(AMN)) ? gemm_bf16_tcgen05_kernel<AMN, BMN, 0, false, false, !(AMN)>                   \
+                                     : gemm_bf16_tcgen05_kernel<AMN, BMN, 0, false, false, false>;                   \
     cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemBudget + 1024));     \
     if (e != cudaSuccess) return bdl_fail_cuda("cudaFuncSetAttribute(gemm)", e);                                  \
-    kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, p);                                                       \
+    kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, tmD, p);                                                  \
   } while (0)
   if (a_mn && b_mn)
     BDL_LAUNCH_GEMM(true, true);
@@ -856,12 +955,18 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
   p.D = D;
   p.bias = bias;
   const size_t stage_bytes = static_cast<size_t>(BM) * BK * 2 * (p.dual_m ? 2 : 1) + static_cast<size_t>(p.b_rows) * BK * 2;
-  const size_t budget = kSmemBudget;
+  const bool tma_out = want_tma_store(D, ldd, out_fp32, flags, mode == 2, p.cv_num_kb);
+  const size_t budget = kSmemBudget - (tma_out ? kStageOutBytes : 0);
   int stages = static_cast<int>(budget / stage_bytes);
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) return bdl_fail("bdl_conv_igemm_bf16: tile does not fit in shared memory");
   p.num_stages = stages;
-  const size_t smem = stages * stage_bytes + 1024;
+  const size_t smem = stages * stage_bytes + 1024 + (tma_out ? kStageOutBytes : 0);
+  CUtensorMap tmD{};
+  if (tma_out) {
+    const int rcd = bdl_make_tmap_2d_bf16(&tmD, D, static_cast<uint64_t>(gn), static_cast<uint64_t>(gm), ldd, 64, 32);
+    if (rcd) return rcd;
+  }
 
   // bounding box of base pixel positions: [-pad, dim - 1 + pad - dil*(k-1)] (inclusive), traversal stride = conv stride
   const int up_w = pw - dw * (kw - 1), up_h = ph - dh * (kh - 1);
@@ -887,11 +992,13 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
   const int grid = static_cast<int>(total < num_sms ? total : num_sms);
 #define BDL_LAUNCH_CONV(AMN, BMN, CV)                                                                             \
   do {                                                                                                            \
-    auto kfn = p.dual_m ? gemm_bf16_tcgen05_kernel<AMN, BMN, CV, false, true>                                     \
-                        : gemm_bf16_tcgen05_kernel<AMN, BMN, CV, false, false>;                                   \
+    auto kfn = p.dual_m ? (tma_out && !(AMN) ? gemm_bf16_tcgen05_kernel<AMN, BMN, CV, false, true, !(AMN)>        \
+                                             : gemm_bf16_tcgen05_kernel<AMN, BMN, CV, false, true, false>)        \
+                        : (tma_out && !(AMN) ? gemm_bf16_tcgen05_kernel<AMN, BMN, CV, false, false, !(AMN)>       \
+                                             : gemm_bf16_tcgen05_kernel<AMN, BMN, CV, false, false, false>);      \
     cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemBudget + 1024));     \
     if (e != cudaSuccess) return bdl_fail_cuda("cudaFuncSetAttribute(conv gemm)", e);                             \
-    kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, p);                                                       \
+    kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, tmD, p);                                                  \
   } while (0)
   if (mode == 0)
     BDL_LAUNCH_CONV(false, false, 1);
@@ -972,12 +1079,12 @@ extern "C" int bdl_gemm_fp8(const void* A, const void* B, void* D, const float* 
     auto kfn = gemm_bf16_tcgen05_kernel<false, false, 1, true>;
     cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemBudget + 1024));
     if (e != cudaSuccess) return bdl_fail_cuda("cudaFuncSetAttribute(fp8 conv)", e);
-    kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, p);
+    kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, tmA, p);
   } else {
     auto kfn = gemm_bf16_tcgen05_kernel<false, false, 0, true>;
     cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemBudget + 1024));
     if (e != cudaSuccess) return bdl_fail_cuda("cudaFuncSetAttribute(fp8 gemm)", e);
-    kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, p);
+    kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, tmA, p);
   }
   return bdl_check_launch("gemm_tcgen05_kernel<fp8>");
 }

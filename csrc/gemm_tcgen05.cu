@@ -201,11 +201,22 @@ __device__ __forceinline__ void epilogue_store16(const GemmParams& p, const uint
 
 // Math of one 16-column chunk only (bias, residual, ReLU) -> 16 bf16 packed into two 16-byte vectors, for the
 // shared-memory staged TMA-store epilogue. nvalid <= 0 or row >= M: the values are never written (the TMA store clips).
+// kFp8: the per-column dequantisation scales ``ss`` are applied first; with ``to_e4m3`` the 16 values are requantised
+// (v * out_qscale, saturating) into q0 alone.
+template <bool kFp8>
 __device__ __forceinline__ void epilogue_pack16(const GemmParams& p, const uint32_t* r, int row, int n0, int nvalid,
-                                                const float* sb, bool has_bias, uint4& q0, uint4& q1) {
+                                                const float* sb, const float* ss, bool has_bias, bool use_scale,
+                                                bool to_e4m3, float qs, uint4& q0, uint4& q1) {
   float v[16];
 #pragma unroll
   for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
+  if (kFp8 && use_scale) {
+#pragma unroll
+    for (int j = 0; j < 16; j += 4) {
+      const float4 s4 = *reinterpret_cast<const float4*>(ss + j);
+      v[j] *= s4.x; v[j + 1] *= s4.y; v[j + 2] *= s4.z; v[j + 3] *= s4.w;
+    }
+  }
   if (has_bias) {
 #pragma unroll
     for (int j = 0; j < 16; j += 4) {
@@ -231,6 +242,19 @@ __device__ __forceinline__ void epilogue_pack16(const GemmParams& p, const uint3
   if (p.flags & BDL_GEMM_RELU) {
 #pragma unroll
     for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
+  }
+  if (kFp8 && to_e4m3) {
+    uint32_t w[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const uint32_t lo = __nv_cvt_float2_to_fp8x2(make_float2(v[4 * j] * qs, v[4 * j + 1] * qs), __NV_SATFINITE,
+                                                   __NV_E4M3);
+      const uint32_t hi = __nv_cvt_float2_to_fp8x2(make_float2(v[4 * j + 2] * qs, v[4 * j + 3] * qs), __NV_SATFINITE,
+                                                   __NV_E4M3);
+      w[j] = lo | (hi << 16);
+    }
+    q0 = make_uint4(w[0], w[1], w[2], w[3]);
+    return;
   }
   q0.x = pack_bf16x2(v[0], v[1]);   q0.y = pack_bf16x2(v[2], v[3]);
   q0.z = pack_bf16x2(v[4], v[5]);   q0.w = pack_bf16x2(v[6], v[7]);
@@ -605,15 +629,31 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           __syncwarp();
           tmem_ld_wait();
           uint4 q[8];
-          epilogue_pack16(p, r0, row, nbase + c, p.N - (nbase + c), sb + c, has_bias, q[0], q[1]);
-          epilogue_pack16(p, r1, row, nbase + c + 16, p.N - (nbase + c + 16), sb + c + 16, has_bias, q[2], q[3]);
-          epilogue_pack16(p, r2, row, nbase + c + 32, p.N - (nbase + c + 32), sb + c + 32, has_bias, q[4], q[5]);
-          epilogue_pack16(p, r3, row, nbase + c + 48, p.N - (nbase + c + 48), sb + c + 48, has_bias, q[6], q[7]);
+          const bool e4 = kFp8 && p.out_fp32 == 2;
+          const float qs = e4 ? __ldg(p.out_qscale) : 1.f;
+          epilogue_pack16<kFp8>(p, r0, row, nbase + c, p.N - (nbase + c), sb + c, ss + c, has_bias, use_scale, e4, qs,
+                                q[0], q[1]);
+          epilogue_pack16<kFp8>(p, r1, row, nbase + c + 16, p.N - (nbase + c + 16), sb + c + 16, ss + c + 16, has_bias,
+                                use_scale, e4, qs, q[2], q[3]);
+          epilogue_pack16<kFp8>(p, r2, row, nbase + c + 32, p.N - (nbase + c + 32), sb + c + 32, ss + c + 32, has_bias,
+                                use_scale, e4, qs, q[4], q[5]);
+          epilogue_pack16<kFp8>(p, r3, row, nbase + c + 48, p.N - (nbase + c + 48), sb + c + 48, ss + c + 48, has_bias,
+                                use_scale, e4, qs, q[6], q[7]);
+          if (e4) {
+            // e4m3 output: 64 columns = 64-byte rows, 64B-swizzled (chunk ^ ((row >> 1) & 3)) like its tensor map
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const uint32_t a = stg + lane * 128u + ((static_cast<uint32_t>(j) ^ (lane & 7u)) << 4);
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(q[j].x), "r"(q[j].y), "r"(q[j].z),
-                         "r"(q[j].w) : "memory");
+            for (int j = 0; j < 4; ++j) {
+              const uint32_t a = stg + lane * 64u + ((static_cast<uint32_t>(j) ^ ((lane >> 1) & 3u)) << 4);
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(q[2 * j].x), "r"(q[2 * j].y),
+                           "r"(q[2 * j].z), "r"(q[2 * j].w) : "memory");
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const uint32_t a = stg + lane * 128u + ((static_cast<uint32_t>(j) ^ (lane & 7u)) << 4);
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(q[j].x), "r"(q[j].y), "r"(q[j].z),
+                           "r"(q[j].w) : "memory");
+            }
           }
           fence_proxy_async_smem();
           __syncwarp();
@@ -1059,10 +1099,21 @@ extern "C" int bdl_gemm_fp8(const void* A, const void* B, void* D, const float* 
   p.out_qscale = out_qscale;
   if (out_fp32 == 2 && !out_qscale) return bdl_fail("bdl_gemm_fp8: e4m3 output needs out_qscale");
   const size_t stage_bytes = static_cast<size_t>(BM) * 128 + static_cast<size_t>(p.b_rows) * 128;
-  int stages = static_cast<int>(kSmemBudget / stage_bytes);
+  // bf16 (kind 0) and e4m3 (kind 2) outputs can go through the staged TMA-store epilogue
+  const long long d_esize = out_fp32 == 2 ? 1 : 2;
+  const bool tma_out = (out_fp32 == 0 || out_fp32 == 2) && (reinterpret_cast<uintptr_t>(D) & 15u) == 0 &&
+                       (ldd * d_esize) % 16 == 0 && want_tma_store(D, 8, 0, flags, false, 0);
+  int stages = static_cast<int>((kSmemBudget - (tma_out ? kStageOutBytes : 0)) / stage_bytes);
   if (stages > kMaxStages) stages = kMaxStages;
   p.num_stages = stages;
-  const size_t smem = stages * stage_bytes + 1024;
+  const size_t smem = stages * stage_bytes + 1024 + (tma_out ? kStageOutBytes : 0);
+  CUtensorMap tmD{};
+  if (tma_out) {
+    const int rcd = out_fp32 == 2
+                        ? bdl_make_tmap_2d_u8_sw(&tmD, D, static_cast<uint64_t>(N), static_cast<uint64_t>(gm), ldd, 64, 32, 64)
+                        : bdl_make_tmap_2d_bf16(&tmD, D, static_cast<uint64_t>(N), static_cast<uint64_t>(gm), ldd, 64, 32);
+    if (rcd) return rcd;
+  }
   CUtensorMap tmA, tmB;
   int rc;
   if (cg)
@@ -1076,15 +1127,17 @@ extern "C" int bdl_gemm_fp8(const void* A, const void* B, void* D, const float* 
   const long long total = static_cast<long long>(p.tiles_m) * p.tiles_n;
   const int grid = static_cast<int>(total < num_sms ? total : num_sms);
   if (cg) {
-    auto kfn = gemm_bf16_tcgen05_kernel<false, false, 1, true>;
+    auto kfn = tma_out ? gemm_bf16_tcgen05_kernel<false, false, 1, true, false, true>
+                       : gemm_bf16_tcgen05_kernel<false, false, 1, true, false, false>;
     cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemBudget + 1024));
     if (e != cudaSuccess) return bdl_fail_cuda("cudaFuncSetAttribute(fp8 conv)", e);
-    kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, tmA, p);
+    kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, tma_out ? tmD : tmA, p);
   } else {
-    auto kfn = gemm_bf16_tcgen05_kernel<false, false, 0, true>;
+    auto kfn = tma_out ? gemm_bf16_tcgen05_kernel<false, false, 0, true, false, true>
+                       : gemm_bf16_tcgen05_kernel<false, false, 0, true, false, false>;
     cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemBudget + 1024));
     if (e != cudaSuccess) return bdl_fail_cuda("cudaFuncSetAttribute(fp8 gemm)", e);
-    kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, tmA, p);
+    kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, tma_out ? tmD : tmA, p);
   }
   return bdl_check_launch("gemm_tcgen05_kernel<fp8>");
 }

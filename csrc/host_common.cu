@@ -87,6 +87,10 @@ int bdl_make_tmap_2d_bf16_sw(CUtensorMap* out, const void* base, uint64_t dim0, 
                              uint32_t box0, uint32_t box1, int swizzle_bytes) {
   return make_tmap_2d(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dim0, dim1, ld, box0, box1, swizzle_bytes);
 }
+int bdl_make_tmap_2d_u8_sw(CUtensorMap* out, const void* base, uint64_t dim0, uint64_t dim1, long long ld, uint32_t box0,
+                           uint32_t box1, int swizzle_bytes) {
+  return make_tmap_2d(out, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, base, dim0, dim1, ld, box0, box1, swizzle_bytes);
+}
 int bdl_make_tmap_2d_u8(CUtensorMap* out, const void* base, uint64_t dim0, uint64_t dim1, long long ld, uint32_t box0,
                         uint32_t box1) {
   return make_tmap_2d(out, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, base, dim0, dim1, ld, box0, box1);

@@ -19,6 +19,8 @@ int bdl_make_tmap_2d_bf16_sw(CUtensorMap* out, const void* base, uint64_t dim0, 
 int bdl_make_tmap_im2col_bf16_sw(CUtensorMap* out, const void* base, int C, int W, int H, int N, long long ld_pixel,
                                  int lower_w, int lower_h, int upper_w, int upper_h, int channels_per_pixel,
                                  int pixels_per_column, int stride_w, int stride_h, int swizzle_bytes);
+int bdl_make_tmap_2d_u8_sw(CUtensorMap* out, const void* base, uint64_t dim0, uint64_t dim1, long long ld, uint32_t box0,
+                           uint32_t box1, int swizzle_bytes);
 int bdl_make_tmap_2d_u8(CUtensorMap* out, const void* base, uint64_t dim0, uint64_t dim1, long long ld, uint32_t box0,
                         uint32_t box1);
 

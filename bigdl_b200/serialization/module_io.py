@@ -413,6 +413,8 @@ def _proto_to_module(p: pb.BigDLModule, storages):
             m = cls(*kwargs.pop(var_pos[0]), **kwargs)
         else:
             m = cls(**kwargs)
+        if type(m).__name__ == "Node":          # ``Input()`` builds a graph node around the placeholder module
+            m = m.element
         if p.subModules and hasattr(m, "_deser_children"):
             m._deser_children([_proto_to_module(s, storages) for s in p.subModules])
         elif p.subModules and not _rebuilds_children(m):

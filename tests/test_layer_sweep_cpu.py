@@ -141,3 +141,90 @@ def test_layer_gradients_match_finite_differences(name):
     assert checker.checkLayer(m, x), f"{name}: input gradient"
     if m.parameters()[0]:
         assert checker.checkWeight(m, x), f"{name}: parameter gradient"
+
+
+# ------------------------------------------------------------------------------------------------- criterions
+from bigdl_b200.nn import criterion as C  # noqa: E402
+
+
+def _probs(shape):
+    return torch.softmax(torch.randn(*shape), dim=-1)
+
+
+def _labels(n, k):
+    return torch.randint(1, k + 1, (n,)).float()
+
+
+def _pm1(shape):
+    return (torch.randint(0, 2, shape).float() * 2 - 1)
+
+
+CRITERIONS = {
+    "ClassNLL": (lambda: C.ClassNLLCriterion(), lambda: torch.log_softmax(torch.randn(4, 5), 1), lambda: _labels(4, 5)),
+    "ClassNLL_weights": (lambda: C.ClassNLLCriterion(torch.tensor([0.5, 1.0, 2.0, 1.5, 0.1])),
+                         lambda: torch.log_softmax(torch.randn(4, 5), 1), lambda: _labels(4, 5)),
+    "CrossEntropy": (lambda: C.CrossEntropyCriterion(), lambda: torch.randn(4, 5), lambda: _labels(4, 5)),
+    "MSE": (lambda: C.MSECriterion(), lambda: torch.randn(4, 5), lambda: torch.randn(4, 5)),
+    "Abs": (lambda: C.AbsCriterion(), lambda: torch.randn(4, 5), lambda: torch.randn(4, 5) + 3),
+    "BCE": (lambda: C.BCECriterion(), lambda: torch.rand(4, 5) * 0.8 + 0.1, lambda: torch.randint(0, 2, (4, 5)).float()),
+    "SmoothL1": (lambda: C.SmoothL1Criterion(), lambda: torch.randn(4, 5), lambda: torch.randn(4, 5) + 3),
+    "Margin": (lambda: C.MarginCriterion(), lambda: torch.randn(4, 5) * 3, lambda: _pm1((4, 5))),
+    "MarginRanking": (lambda: C.MarginRankingCriterion(), lambda: T(torch.randn(6) * 3, torch.randn(6) * 3),
+                      lambda: _pm1((6,))),
+    "MultiMargin": (lambda: C.MultiMarginCriterion(), lambda: torch.randn(4, 5) * 3, lambda: _labels(4, 5)),
+    "MultiLabelSoftMargin": (lambda: C.MultiLabelSoftMarginCriterion(), lambda: torch.randn(4, 5),
+                             lambda: torch.randint(0, 2, (4, 5)).float()),
+    "SoftMargin": (lambda: C.SoftMarginCriterion(), lambda: torch.randn(4, 5), lambda: _pm1((4, 5))),
+    "HingeEmbedding": (lambda: C.HingeEmbeddingCriterion(2.0), lambda: torch.rand(4, 5) * 4, lambda: _pm1((4, 5))),
+    "CosineEmbedding": (lambda: C.CosineEmbeddingCriterion(0.1), lambda: T(torch.randn(4, 5), torch.randn(4, 5)),
+                        lambda: _pm1((4,))),
+    "CosineDistance": (lambda: C.CosineDistanceCriterion(), lambda: torch.randn(4, 5), lambda: torch.randn(4, 5)),
+    "CosineProximity": (lambda: C.CosineProximityCriterion(), lambda: torch.randn(4, 5), lambda: torch.randn(4, 5)),
+    "DistKLDiv": (lambda: C.DistKLDivCriterion(), lambda: torch.log(_probs((4, 5))), lambda: _probs((4, 5))),
+    "KullbackLeiblerDivergence": (lambda: C.KullbackLeiblerDivergenceCriterion(), lambda: _probs((4, 5)),
+                                  lambda: _probs((4, 5))),
+    "Poisson": (lambda: C.PoissonCriterion(), lambda: torch.rand(4, 5) + 0.5, lambda: torch.rand(4, 5) * 3),
+    "DiceCoefficient": (lambda: C.DiceCoefficientCriterion(), lambda: torch.rand(4, 5), lambda: torch.randint(0, 2, (4, 5)).float()),
+    "L1Cost": (lambda: C.L1Cost(), lambda: torch.randn(4, 5) + 2.5, lambda: torch.zeros(4, 5)),
+    "MeanAbsolutePercentage": (lambda: C.MeanAbsolutePercentageCriterion(), lambda: torch.rand(4, 5) + 2,
+                               lambda: torch.rand(4, 5) + 0.5),
+    "MeanSquaredLogarithmic": (lambda: C.MeanSquaredLogarithmicCriterion(), lambda: torch.rand(4, 5) + 0.5,
+                               lambda: torch.rand(4, 5) + 0.5),
+    "CategoricalCrossEntropy": (lambda: C.CategoricalCrossEntropy(), lambda: _probs((4, 5)),
+                                lambda: torch.nn.functional.one_hot(torch.randint(0, 5, (4,)), 5).float()),
+    "DotProduct": (lambda: C.DotProductCriterion(), lambda: torch.randn(4, 5), lambda: torch.randn(4, 5)),
+    "ClassSimplex": (lambda: C.ClassSimplexCriterion(5), lambda: torch.randn(4, 5), lambda: _labels(4, 5)),
+    "SoftmaxWith": (lambda: C.SoftmaxWithCriterion(), lambda: torch.randn(2, 5, 3, 3), lambda: torch.randint(1, 6, (2, 1, 3, 3)).float()),
+    "TimeDistributed": (lambda: C.TimeDistributedCriterion(C.MSECriterion(), True), lambda: torch.randn(3, 4, 5),
+                        lambda: torch.randn(3, 4, 5)),
+    "Parallel": (lambda: C.ParallelCriterion().add(C.MSECriterion(), 0.5).add(C.AbsCriterion(), 2.0),
+                 lambda: T(torch.randn(4, 5), torch.randn(4, 3)), lambda: T(torch.randn(4, 5), torch.randn(4, 3) + 3)),
+    "Multi": (lambda: C.MultiCriterion().add(C.MSECriterion(), 0.5).add(C.SmoothL1Criterion(), 2.0),
+              lambda: torch.randn(4, 5), lambda: torch.randn(4, 5) + 3),
+}
+
+
+@pytest.mark.parametrize("name", sorted(CRITERIONS))
+def test_criterion_gradient_matches_finite_differences(name):
+    RNG.setSeed(7)
+    torch.manual_seed(7)
+    make, make_in, make_tgt = CRITERIONS[name]
+    crit, x, t = make(), make_in(), make_tgt()
+    loss = float(crit.forward(x, t))
+    assert loss == loss          # not NaN
+    g = crit.backward(x, t)
+    xs = x.to_list() if hasattr(x, "to_list") else [x]
+    gs = g.to_list() if hasattr(g, "to_list") else [g]
+    eps = 1e-3
+    for xi, gi in zip(xs, gs):
+        flat = xi.reshape(-1)
+        assert flat.data_ptr() == xi.data_ptr()
+        for i in torch.randperm(flat.numel())[:24]:
+            old = float(flat[i])
+            flat[i] = old + eps
+            up = float(crit.forward(x, t))
+            flat[i] = old - eps
+            dn = float(crit.forward(x, t))
+            flat[i] = old
+            num, ana = (up - dn) / (2 * eps), float(gi.reshape(-1)[i])
+            assert abs(num - ana) <= 2e-2 * max(1.0, abs(ana), abs(num)), (name, int(i), num, ana)

@@ -61,3 +61,7 @@ def test_cli_tools(tmp_path, capsys):
 
 def test_tree_lstm_sentiment_example_learns():
     assert _load("tree_lstm_sentiment").main(["-e", "3"]) > 0.7
+
+
+def test_keras_imdb_lstm_example_learns():
+    assert _load("keras_imdb_lstm").main(["-e", "3"]) > 0.85

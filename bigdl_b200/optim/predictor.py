@@ -71,8 +71,18 @@ class Predictor:
         return res
 
     def predictImage(self, image_frame, output_layer=None, predict_key="predict"):
-        feats = image_frame.features() if hasattr(image_frame, "features") else list(image_frame)
-        samples = [f.get_sample() if hasattr(f, "get_sample") else f for f in feats]
+        feats = getattr(image_frame, "features", None)
+        feats = feats() if callable(feats) else (list(image_frame) if feats is None else list(feats))
+
+        def sample_of(f):
+            if hasattr(f, "get_sample"):
+                return f.get_sample()
+            try:
+                return f["sample"]          # written by ImageFrameToSample
+            except (KeyError, TypeError, IndexError):
+                return f
+
+        samples = [sample_of(f) for f in feats]
         outs = self._outputs(samples)
         for f, o in zip(feats, outs):
             if hasattr(f, "__setitem__"):

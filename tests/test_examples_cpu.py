@@ -65,3 +65,7 @@ def test_tree_lstm_sentiment_example_learns():
 
 def test_keras_imdb_lstm_example_learns():
     assert _load("keras_imdb_lstm").main(["-e", "3"]) > 0.85
+
+
+def test_image_validation_example_runs_the_imageframe_path():
+    assert _load("image_validation").main(["-n", "90", "-e", "25"]) > 0.9

@@ -677,9 +677,13 @@ class Module:
     load_torch = loadTorch
 
     @staticmethod
-    def loadCaffe(model, defPath: str, modelPath: str, matchAll: bool = True):
-        """Copy weights from a caffemodel into an existing model by layer name (CaffeLoader.load)."""
+    def loadCaffe(model, defPath: str, modelPath: str, matchAll: bool = True, match_all: bool | None = None):
+        """Copy weights from a caffemodel into an existing model by layer name (CaffeLoader.load); ``match_all`` is the
+        Python API's spelling of ``matchAll``."""
         from ..interop.caffe import CaffeLoader
+
+        if match_all is not None:
+            matchAll = match_all
 
         return CaffeLoader.load(model, defPath, modelPath, matchAll)
 

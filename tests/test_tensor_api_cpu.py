@@ -108,3 +108,52 @@ def test_quantized_tensor_matches_reference_rule():
     assert (q.dequantize() - w).abs().max() < 0.01
     b, am = q.to_e4m3()
     assert b.dtype == torch.uint8 and b.shape == (2, 16) and torch.allclose(am, torch.tensor([1.0, 2.0]), atol=0.01)
+
+
+def test_remaining_tensor_math_and_shape_methods():
+    """The TensorMath / Tensor methods no other test calls (S/tensor/TensorMath.scala, Tensor.scala), 1-based dims."""
+    import torch
+    from bigdl_b200.tensor import Tensor
+
+    a = Tensor(torch.tensor([[1., 2., 3.], [4., 5., 6.]]))
+    b = Tensor(torch.tensor([[2., 2., 2.], [0.5, 0.5, 0.5]]))
+    assert torch.equal(Tensor(2, 3).cmul(a, b).t, a.t * b.t) and torch.equal(Tensor(2, 3).cdiv(a, b).t, a.t / b.t)
+    assert torch.equal(Tensor(2, 3).mul(a, 3.0).t, a.t * 3) and torch.equal(Tensor(2, 3).div(a, b).t, a.t / b.t)
+    assert torch.equal(a.clone().cmul(b).t, a.t * b.t) and torch.equal(a.clone().mul(2.0).t, a.t * 2)
+    assert torch.equal(Tensor(2, 3).cmax(a, b).t, torch.maximum(a.t, b.t))
+    assert torch.equal(Tensor(2, 3).cmin(a, b).t, torch.minimum(a.t, b.t))
+    assert torch.equal(a.clone().cmax(3.5).t, a.t.clamp(min=3.5))
+    assert torch.allclose(a.clone().addcdiv(2.0, a, b).t, a.t + 2.0 * a.t / b.t)
+    m, v = Tensor(torch.randn(3, 4)), Tensor(torch.randn(4))
+    assert torch.allclose(Tensor(3).mv(m, v).t, m.t @ v.t)
+    b1, b2 = Tensor(torch.randn(2, 3, 4)), Tensor(torch.randn(2, 4, 5))
+    assert torch.allclose(Tensor(2, 3, 5).bmm(b1, b2).t, torch.bmm(b1.t, b2.t))
+    M = Tensor(torch.randn(2, 3, 5))
+    assert torch.allclose(Tensor(2, 3, 5).baddbmm(0.5, M, 2.0, b1, b2).t, 0.5 * M.t + 2.0 * torch.bmm(b1.t, b2.t))
+    assert torch.equal(a.eq(a).t, torch.ones(2, 3)) and float(a.ge(4.0).t.sum()) == 3 and float(a.le(2.0).t.sum()) == 2
+    assert abs(a.prod() - 720.0) < 1e-6 if not isinstance(a.prod(), Tensor) else abs(float(a.prod().t) - 720.0) < 1e-6
+    assert torch.allclose(Tensor(2, 3).log1p(a).t, torch.log1p(a.t)) and torch.allclose(Tensor(2, 3).inv(a).t, 1 / a.t)
+    vals, idx = a.sort(2, True)
+    assert torch.equal(vals.t[0], torch.tensor([3., 2., 1.])) and int(idx.t[0, 0]) == 3          # 1-based indices
+    assert a.clone().addSingletonDimension(1).size() == [1, 2, 3]      # in place on the receiver, like the reference
+    assert Tensor(1, 3, 1).squeeze().size() == [3] and Tensor(1, 3, 1).squeeze(1).size() == [3, 1]
+    assert Tensor(1, 3).squeezeNewTensor().size() == [3]
+    c = Tensor(torch.arange(6.).reshape(2, 3))
+    assert c.t_().size() == [3, 2]
+    assert Tensor(torch.ones(1, 3)).expandAs(Tensor(4, 3)).size() == [4, 3]
+    assert Tensor(torch.ones(2)).repeatTensor(3, 2).size() == [3, 4]
+    assert Tensor(5).resizeAs(Tensor(2, 3)).size() == [2, 3]
+    assert Tensor(torch.arange(6.)).unfold(1, 2, 2).size() == [3, 2]
+    assert Tensor.scalar(3.5).isScalar() and abs(float(Tensor.scalar(3.5).t) - 3.5) < 1e-6
+    assert Tensor().isEmpty() and not a.isEmpty() and a.isContiguous() and a.isSameSizeAs(b)
+    assert a.getType() == torch.float32 and a.toTensor() is a
+    z = Tensor(2, 3).zipWith(a, b, lambda p, q: p + 2 * q)
+    assert torch.allclose(z.t, a.t + 2 * b.t)
+    acc = Tensor(torch.zeros(3, 2))
+    acc.indexAdd(1, torch.tensor([1., 3., 1.]), torch.ones(3, 2))
+    assert torch.equal(acc.t, torch.tensor([[2., 2.], [0., 0.], [1., 1.]]))
+    dst = Tensor(torch.zeros(2, 3))
+    dst.maskedCopy(torch.tensor([[1, 0, 1], [0, 1, 0]]), torch.tensor([7., 8., 9.]))
+    assert torch.equal(dst.t, torch.tensor([[7., 0., 8.], [0., 9., 0.]]))
+    bern = Tensor(1000).bernoulli(0.3)
+    assert 0.2 < float(bern.t.mean()) < 0.4 and set(bern.t.unique().tolist()) <= {0.0, 1.0}

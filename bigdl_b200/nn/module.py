@@ -576,19 +576,17 @@ class Module:
     clear_state = clearState
 
     def cloneModule(self):
+        """Deep copy with its own parameter storage. The source keeps its flat parameter buffer: optimizers, captured
+        CUDA graphs and the parameter synchroniser hold pointers into it, so it must never be rebuilt behind their
+        back (``__deepcopy__`` clones every parameter out of the buffer individually)."""
         self.clearState()
-        from .flat import unflatten_parameters
-
         was_flat = getattr(self, "_flat", None) is not None
         dev = self.device()
-        unflatten_parameters(self)
         c = copy.deepcopy(self)
         for m in c.all_modules():
             m._uid = next(_uid)
-        if was_flat:
-            self.getParameters()
-            if dev.type == "cuda":
-                c.getParameters()
+        if was_flat and dev.type == "cuda":
+            c.getParameters()
         return c
 
     clone = cloneModule
@@ -613,6 +611,8 @@ class Module:
                     memo[id(p)] = q
                     od[n] = q
                 new.__dict__[k] = od
+            elif k in ("_train_summary", "_val_summary", "_pre_call_hook"):
+                continue              # run-time attachments (event writers own threads and locks): not part of a copy
             else:
                 new.__dict__[k] = copy.deepcopy(v, memo)
         return new

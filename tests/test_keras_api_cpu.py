@@ -110,3 +110,28 @@ def test_compile_fit_evaluate_predict():
     assert len(pred) == 128 and tuple(np.asarray(pred[0]).shape) == (2,)
     with pytest.raises(TypeError):
         model.compile(optimizer="nope", loss="mse")
+
+
+def test_keras_predict_classes_tensorboard_and_checkpoint(tmp_path):
+    import os
+    import numpy as np
+    import bigdl_b200.nn.keras as K
+    from bigdl_b200.utils.random_generator import RNG
+
+    RNG.setSeed(8)
+    rs = np.random.RandomState(0)
+    x = rs.randn(96, 4).astype(np.float32)
+    y = (x[:, 0] > 0).astype(np.float32) + (x[:, 1] > 0).astype(np.float32)          # 3 classes: 0, 1, 2
+    m = K.Sequential()
+    m.add(K.Dense(16, activation="relu", input_shape=(4,)))
+    m.add(K.Dense(3, activation="softmax"))
+    m.compile(optimizer="adam", loss="sparse_categorical_crossentropy", metrics=["accuracy"])
+    m.set_tensorboard(str(tmp_path / "tb"), "kapp").set_checkpoint(str(tmp_path / "ck"))
+    os.makedirs(str(tmp_path / "ck"), exist_ok=True)
+    m.fit(x, y + 1, batch_size=16, nb_epoch=100)             # class ids are 1-based for the loss, as in the reference
+    zero = m.predict_classes(x, batch_size=32)
+    one = m.predict_classes(x, batch_size=32, zero_based_label=False)
+    assert len(zero) == 96 and [c + 1 for c in zero] == one and set(zero) <= {0, 1, 2}
+    assert float(np.mean(np.asarray(zero) == y)) > 0.8
+    assert len(m._train_summary.read_scalar("Loss")) > 0                              # fit() wrote TensorBoard scalars
+    assert any(f.startswith("model") for _, _, fs in os.walk(str(tmp_path / "ck")) for f in fs)

@@ -247,3 +247,40 @@ def test_residual_block_conv_sum_fusion_matches_unfused(kind):
     err = (outs[True] - outs[False]).abs().max().item()
     assert err <= 2e-2 * outs[False].abs().max().item() + 1e-2, err
     assert float(outs[True].min()) >= 0.0
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_checkpointing_does_not_disturb_gpu_training(tmp_path, graph):
+    """Same as the CPU test, on the GPU path where a captured CUDA graph holds pointers into the flat buffers."""
+    from bigdl_b200.dataset.base import FixedMiniBatchDataSet, MiniBatch
+    from bigdl_b200.nn.criterion import ClassNLLCriterion
+    from bigdl_b200.nn.layer import Linear, LogSoftMax, ReLU, Sequential, SpatialConvolution, View
+    from bigdl_b200.optim.optim_method import SGD
+    from bigdl_b200.optim.optimizer import Optimizer
+    from bigdl_b200.optim.trigger import MaxIteration, SeveralIteration
+    from bigdl_b200.utils import config
+    from bigdl_b200.utils.random_generator import RNG
+
+    def run(ck):
+        config.set("bigdl.cudaGraph", graph)
+        try:
+            RNG.setSeed(17)
+            m = Sequential()
+            m.add(SpatialConvolution(8, 16, 3, 3, 1, 1, 1, 1)).add(ReLU())
+            m.add(View(16 * 8 * 8).setNumInputDims(3)).add(Linear(16 * 8 * 8, 8)).add(LogSoftMax())
+            m.cuda()
+            g = torch.Generator().manual_seed(1)
+            x = torch.randn(16, 8, 8, 8, generator=g)
+            y = torch.randint(1, 9, (16,), generator=g).float()
+            opt = Optimizer(m, FixedMiniBatchDataSet(MiniBatch(x, y), 16, distributed=False), ClassNLLCriterion(),
+                            MaxIteration(10), 16, SGD(0.05, momentum=0.9))
+            if ck:
+                opt.setCheckpoint(str(tmp_path / f"c{int(graph)}"), SeveralIteration(3))
+            opt.optimize()
+            torch.cuda.synchronize()
+            return m._flat.weights.clone(), float(opt.state["Loss"])
+        finally:
+            config.unset("bigdl.cudaGraph")
+
+    (wa, la), (wb, lb) = run(False), run(True)
+    assert _rel(wb, wa) < 1e-6 and abs(la - lb) < 1e-6

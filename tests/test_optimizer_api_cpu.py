@@ -115,3 +115,27 @@ def test_checkpoint_helpers_and_summaries(tmp_path):
     ts.add_histogram("hist", torch.randn(100), 7)
     ts.close() if hasattr(ts, "close") else None
     vs.close() if hasattr(vs, "close") else None
+
+
+def test_checkpointing_does_not_disturb_training(tmp_path):
+    """Saving a snapshot clones the model; the live model's flat parameter buffer (which the optimizer updates) must
+    stay in place — trajectories with and without checkpoints are identical."""
+    def run(ck):
+        model, ds = _problem()
+        opt = LocalOptimizer(model, ds, MSECriterion(), MaxIteration(12), 16, SGD(0.1, momentum=0.9))
+        if ck:
+            opt.setCheckpoint(str(tmp_path / "c"), SeveralIteration(2))
+        w_before = model.getParameters()[0]
+        opt.optimize()
+        assert model.getParameters()[0].data_ptr() == w_before.data_ptr()
+        return model.getParameters()[0].clone(), float(opt.state["Loss"])
+
+    (wa, la), (wb, lb) = run(False), run(True)
+    assert torch.equal(wa, wb) and la == lb
+    # and a clone never aliases or re-homes its source
+    m, _ = _problem()
+    w, _ = m.getParameters()
+    c = m.cloneModule()
+    c.modules[0].weight.data.add_(1.0)
+    assert m.getParameters()[0].data_ptr() == w.data_ptr()
+    assert not torch.equal(c.modules[0].weight, m.modules[0].weight)

@@ -326,7 +326,11 @@ class DataSet:
 
     @staticmethod
     def imageFrame(frame):
-        return frame.toDataSet() if hasattr(frame, "toDataSet") else DataSet.array(list(frame))
+        """DataSet of the frame's ImageFeatures (DataSet.scala ``imageFrame``: a DataSet[ImageFeature], to be piped
+        through image transformers); use ``frame.toDataSet()`` for the Samples written by ImageFrameToSample."""
+        feats = getattr(frame, "features", None)
+        feats = list(feats() if callable(feats) else feats) if feats is not None else list(frame)
+        return DataSet.array(feats, bool(getattr(frame, "is_distributed", lambda: False)()))
 
     @staticmethod
     def ImageFolder(path: str, scale_to: int = 256, distributed: bool = False):

@@ -247,9 +247,16 @@ class BatchMatMul(Operation):
 
 
 class Cast(Operation):
+    """Convert to ``dtype`` — a torch dtype or the reference's type names ("float", "double", "int", "long", ...)."""
+
+    _NAMES = {"float": torch.float32, "float32": torch.float32, "double": torch.float64, "float64": torch.float64,
+              "int": torch.int32, "int32": torch.int32, "long": torch.int64, "int64": torch.int64,
+              "short": torch.int16, "char": torch.int8, "byte": torch.uint8, "bool": torch.bool, "boolean": torch.bool,
+              "half": torch.float16, "bfloat16": torch.bfloat16}
+
     def __init__(self, dtype=torch.float32):
         super().__init__()
-        self.dtype = dtype
+        self.dtype = self._NAMES[dtype.lower()] if isinstance(dtype, str) else dtype
 
     def updateOutput(self, input):
         return input.to(self.dtype)

@@ -186,3 +186,36 @@ def test_fanout_fn_sums_branch_gradients():
     (only,) = FanOutFn.apply(y, 1)
     only.sum().backward()
     assert torch.equal(y.grad, torch.ones_like(y))
+
+
+def test_elementwise_and_logical_ops_against_torch():
+    """The TF-style forward-only ops no other test constructs (S/nn/ops/*.scala), each against its torch equivalent."""
+    import torch
+    import bigdl_b200.nn.ops as O
+    from bigdl_b200.utils.table import T
+
+    x = torch.tensor([[-1.5, 0.4, 2.5], [3.0, -0.2, 0.5]])
+    y = torch.tensor([[1.0, 0.4, -2.5], [2.0, 5.0, 0.5]])
+    p = x.abs() + 0.5
+    special = torch.tensor([1.0, float("inf"), float("nan")])
+    cases = [
+        (O.Floor(), x, torch.floor(x)), (O.Rint(), x, torch.round(x)), (O.Sign(), x, torch.sign(x)),
+        (O.Expm1(), x, torch.expm1(x)), (O.Inv(), x, 1 / x), (O.Erfc(), x, torch.erfc(x)),
+        (O.Lgamma(), p, torch.lgamma(p)), (O.Digamma(), p, torch.digamma(p)),
+        (O.IsFinite(), special, torch.tensor([True, False, False])),
+        (O.IsInf(), special, torch.tensor([False, True, False])),
+        (O.LogicalNot(), torch.tensor([True, False]), torch.tensor([False, True])),
+        (O.Equal(), T(x, y), x == y), (O.NotEqual(), T(x, y), x != y), (O.GreaterEqual(), T(x, y), x >= y),
+        (O.LogicalAnd(), T(x > 0, y > 0), (x > 0) & (y > 0)), (O.LogicalOr(), T(x > 0, y > 0), (x > 0) | (y > 0)),
+        (O.Minimum(), T(x, y), torch.minimum(x, y)), (O.Pow(), T(x.abs(), y), x.abs() ** y),
+    ]
+    for op, inp, ref in cases:
+        out = op.forward(inp)
+        assert out.shape == ref.shape and torch.allclose(out.float(), ref.float(), atol=1e-5), type(op).__name__
+    assert int(O.Rank().forward(x)) == 2
+    assert O.Round().forward(x).shape == x.shape and O.Mod().forward(T(x, y)).shape == x.shape
+    assert O.Cast("int").forward(x).dtype == torch.int32 and O.Cast(torch.float64).forward(x).dtype == torch.float64
+    u = O.RandomUniform(0.0, 1.0).forward(torch.tensor([200, 3]))
+    assert tuple(u.shape) == (200, 3) and 0.0 <= float(u.min()) and float(u.max()) <= 1.0
+    tn = O.TruncatedNormal(0.0, 1.0).forward(torch.tensor([500, 2]))
+    assert tuple(tn.shape) == (500, 2) and float(tn.abs().max()) <= 2.0 + 1e-5

@@ -228,3 +228,75 @@ def test_criterion_gradient_matches_finite_differences(name):
             flat[i] = old
             num, ana = (up - dn) / (2 * eps), float(gi.reshape(-1)[i])
             assert abs(num - ana) <= 2e-2 * max(1.0, abs(ana), abs(num)), (name, int(i), num, ana)
+
+
+# ------------------------------------------------------------------------------------------------- rarely used layers
+def _vol():
+    return torch.randn(2, 3, 4, 6, 6)
+
+
+SMOKE = {
+    "BinaryThreshold": (lambda: L.BinaryThreshold(0.1), _vec, (3, 8)),
+    "RReLU": (lambda: L.RReLU(), _vec, (3, 8)),
+    "Clamp": (lambda: L.Clamp(-1, 1), _vec, (3, 8)),
+    "SpatialDropout1D": (lambda: L.SpatialDropout1D(0.3), lambda: torch.randn(2, 5, 4), (2, 5, 4)),
+    "SpatialDropout2D": (lambda: L.SpatialDropout2D(0.3), _img, IMG),
+    "SpatialDropout3D": (lambda: L.SpatialDropout3D(0.3), _vol, (2, 3, 4, 6, 6)),
+    "GaussianDropout": (lambda: L.GaussianDropout(0.3), _vec, (3, 8)),
+    "GaussianNoise": (lambda: L.GaussianNoise(0.3), _vec, (3, 8)),
+    "GaussianSampler": (lambda: L.GaussianSampler(), lambda: T(_vec(), _vec()), (3, 8)),
+    "NegativeEntropyPenalty": (lambda: L.NegativeEntropyPenalty(0.1), lambda: torch.softmax(_vec(), 1), (3, 8)),
+    "ActivityRegularization": (lambda: L.ActivityRegularization(0.1, 0.1), _vec, (3, 8)),
+    "MapTable": (lambda: L.MapTable(L.Linear(8, 3)), lambda: T(_vec(), _vec()), [(3, 3), (3, 3)]),
+    "Bottle": (lambda: L.Bottle(L.Linear(8, 3), 2, 2), lambda: torch.randn(2, 3, 8), (2, 3, 3)),
+    "BifurcateSplitTable": (lambda: L.BifurcateSplitTable(2), _vec, [(3, 4), (3, 4)]),
+    "FlattenTable": (lambda: L.FlattenTable(), lambda: T(_vec(), T(_vec(), _vec())), [(3, 8)] * 3),
+    "NarrowTable": (lambda: L.NarrowTable(2, 2), lambda: T(_vec(), _vec(), _vec()), [(3, 8)] * 2),
+    "Pack": (lambda: L.Pack(1), lambda: T(_vec(), _vec()), (2, 3, 8)),
+    "CMinTable": (lambda: L.CMinTable(), lambda: T(_vec(), _vec()), (3, 8)),
+    "CAveTable": (lambda: L.CAveTable(), lambda: T(_vec(), _vec()), (3, 8)),
+    "MixtureTable": (lambda: L.MixtureTable(), lambda: T(torch.softmax(torch.randn(3, 2), 1), T(_vec(), _vec())), (3, 8)),
+    "InferReshape": (lambda: L.InferReshape([-1, 4]), _vec, (6, 4)),
+    "Contiguous": (lambda: L.Contiguous(), lambda: _vec().t(), (8, 3)),
+    "Index": (lambda: L.Index(1), lambda: T(_vec(), torch.tensor([1., 3.])), (2, 8)),
+    "Masking": (lambda: L.Masking(0.0), lambda: torch.randn(2, 5, 4), (2, 5, 4)),
+    "ExpandSize": (lambda: L.ExpandSize([3, 8]), lambda: torch.randn(1, 8), (3, 8)),
+    "Reverse": (lambda: L.Reverse(2), _vec, (3, 8)),
+    "Cropping3D": (lambda: L.Cropping3D([1, 1], [1, 1], [1, 1]), _vol, (2, 3, 2, 4, 4)),
+    "Min": (lambda: L.Min(2), _vec, (3,)),
+    "CrossProduct": (lambda: L.CrossProduct(), lambda: T(_vec(), _vec(), _vec()), (3, 3)),
+    "NormalizeScale": (lambda: L.NormalizeScale(2.0, scale=20.0, size=[1, 4, 1, 1]), _img, IMG),
+    "SpatialContrastiveNormalization": (lambda: L.SpatialContrastiveNormalization(4), _img, IMG),
+    "SpatialShareConvolution": (lambda: L.SpatialShareConvolution(4, 5, 3, 3), _img, (2, 5, 4, 4)),
+    "SpatialConvolutionMap": (lambda: L.SpatialConvolutionMap(L.SpatialConvolutionMap.full(4, 3), 3, 3), _img, (2, 3, 4, 4)),
+    "VolumetricFullConvolution": (lambda: L.VolumetricFullConvolution(3, 2, 2, 2, 2), _vol, (2, 2, 5, 7, 7)),
+    "VolumetricAveragePooling": (lambda: L.VolumetricAveragePooling(2, 2, 2), _vol, (2, 3, 2, 3, 3)),
+    "UpSampling3D": (lambda: L.UpSampling3D([2, 2, 2]), _vol, (2, 3, 8, 12, 12)),
+    "FeedForwardNetwork": (lambda: L.FeedForwardNetwork(8, 16, 0.0), lambda: torch.randn(2, 3, 8), (2, 3, 8)),
+}
+
+
+@pytest.mark.parametrize("name", sorted(SMOKE))
+def test_rarely_used_layers_forward_backward(name):
+    RNG.setSeed(9)
+    torch.manual_seed(9)
+    ctor, make_input, shape = SMOKE[name]
+    m = ctor()
+    x = make_input()
+    y = m.forward(x)
+    ys = y.to_list() if hasattr(y, "to_list") else [y]
+    assert [tuple(t.shape) for t in ys] == (shape if isinstance(shape, list) else [tuple(shape)]), name
+    assert all(torch.isfinite(t.float()).all() for t in ys)
+    go = T(*[torch.ones_like(t) for t in ys]) if hasattr(y, "to_list") else torch.ones_like(y)
+    gi = m.backward(x, go)
+    gis = gi.to_list() if hasattr(gi, "to_list") else [gi]
+    xs = [t for t in (x.to_list() if hasattr(x, "to_list") else [x])]
+    flat_x = []
+    for t in xs:
+        flat_x.extend(t.to_list() if hasattr(t, "to_list") else [t])
+    flat_g = []
+    for t in gis:
+        flat_g.extend(t.to_list() if hasattr(t, "to_list") else [t])
+    for a, b in zip(flat_x, flat_g):
+        if b is not None and a.is_floating_point():
+            assert tuple(a.shape) == tuple(b.shape), name

@@ -135,3 +135,37 @@ def test_keras_predict_classes_tensorboard_and_checkpoint(tmp_path):
     assert float(np.mean(np.asarray(zero) == y)) > 0.8
     assert len(m._train_summary.read_scalar("Loss")) > 0                              # fit() wrote TensorBoard scalars
     assert any(f.startswith("model") for _, _, fs in os.walk(str(tmp_path / "ck")) for f in fs)
+
+
+def test_remaining_keras_layers_infer_and_produce_the_same_shape():
+    """Keras-style layers not covered above: the inferred output shape must equal the shape actually produced."""
+    import torch
+    import bigdl_b200.nn.keras as K
+
+    cases = [
+        (lambda: K.Activation("tanh", input_shape=(5,)), (5,), (5,)),
+        (lambda: K.Masking(0.0, input_shape=(4, 3)), (4, 3), (4, 3)),
+        (lambda: K.AveragePooling1D(2, input_shape=(6, 3)), (6, 3), (3, 3)),
+        (lambda: K.MaxPooling3D(input_shape=(2, 4, 4, 4)), (2, 4, 4, 4), (2, 2, 2, 2)),
+        (lambda: K.GlobalAveragePooling1D(input_shape=(6, 3)), (6, 3), (3,)),
+        (lambda: K.GlobalMaxPooling2D(input_shape=(3, 4, 4)), (3, 4, 4), (3,)),
+        (lambda: K.GlobalAveragePooling3D(input_shape=(2, 4, 4, 4)), (2, 4, 4, 4), (2,)),
+        (lambda: K.ZeroPadding3D((1, 1, 1), input_shape=(2, 3, 3, 3)), (2, 3, 3, 3), (2, 5, 5, 5)),
+        (lambda: K.Cropping3D(((1, 1), (1, 1), (1, 1)), input_shape=(2, 4, 4, 4)), (2, 4, 4, 4), (2, 2, 2, 2)),
+        (lambda: K.UpSampling3D((2, 2, 2), input_shape=(2, 3, 3, 3)), (2, 3, 3, 3), (2, 6, 6, 6)),
+        (lambda: K.ThresholdedReLU(0.5, input_shape=(5,)), (5,), (5,)),
+        (lambda: K.GaussianNoise(0.1, input_shape=(5,)), (5,), (5,)),
+        (lambda: K.GaussianDropout(0.1, input_shape=(5,)), (5,), (5,)),
+        (lambda: K.SpatialDropout1D(0.3, input_shape=(6, 3)), (6, 3), (6, 3)),
+        (lambda: K.SpatialDropout2D(0.3, input_shape=(3, 4, 4)), (3, 4, 4), (3, 4, 4)),
+        (lambda: K.SpatialDropout3D(0.3, input_shape=(2, 4, 4, 4)), (2, 4, 4, 4), (2, 4, 4, 4)),
+    ]
+    for make, in_shape, out_shape in cases:
+        m = K.Sequential()
+        m.add(make())
+        y = m.forward(torch.randn(2, *in_shape))
+        assert tuple(y.shape) == (2,) + out_shape, type(m.modules[0]).__name__
+        assert tuple(m.getOutputShape())[1:] == out_shape
+    thr = K.Sequential()
+    thr.add(K.ThresholdedReLU(0.5, input_shape=(3,)))
+    assert torch.equal(thr.forward(torch.tensor([[0.4, 0.6, -1.0]])), torch.tensor([[0.0, 0.6, 0.0]]))

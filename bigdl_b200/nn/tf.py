@@ -336,21 +336,29 @@ class TensorArraySize(Operation):
         return torch.tensor(len(h.items), dtype=torch.int32)
 
 
+class _StackStore:
+    """Handle of a TF stack resource (a plain list would be flattened into a Table when passed between nodes)."""
+
+    def __init__(self):
+        self.items: list = []
+
+
 class StackCreator(Operation):
     def updateOutput(self, input):
-        return []
+        return _StackStore()
 
 
 class StackPush(Operation):
     def updateOutput(self, input):
         h, v = _ins(input, 2)
-        h.append(v)
+        h.items.append(v)
         return v
 
 
 class StackPop(Operation):
     def updateOutput(self, input):
-        return (input[0] if isinstance(input, (Table, tuple)) else input).pop()
+        h = input if isinstance(input, _StackStore) else _ins(input)[0]
+        return h.items.pop()
 
 
 # ------------------------------------------------------------------------------------------------ parsing / images

@@ -60,3 +60,31 @@ def test_tf_helper_ops():
     assert [o.tolist() for o in offs.to_list()] == [[0, 0], [0, 3]]
     ok, buf = cv2.imencode(".png", np.random.RandomState(0).randint(0, 255, (6, 7, 3)).astype(np.uint8))
     assert ok and tuple(TF.DecodeImage(3).forward(buf.tobytes()).shape) == (6, 7, 3)
+
+
+def test_tensor_array_stack_and_assign_ops():
+    """TF data-flow helpers (S/nn/tf/{DataFlowOps,StateOps}.scala): a TensorArray written, scattered, read, concatenated
+    and split; a stack pushed and popped; Assign copying into a Variable's storage."""
+    handle, flow = TF.TensorArrayCreator().forward(torch.tensor(3)).to_list()
+    TF.TensorArrayWrite().forward(T(handle, torch.tensor(0), torch.tensor([1., 2.]), flow))
+    TF.TensorArrayScatter().forward(T(handle, torch.tensor([1, 2]), torch.tensor([[3., 4.], [5., 6.]]), flow))
+    assert torch.equal(TF.TensorArrayRead().forward(T(handle, torch.tensor(2), flow)), torch.tensor([5., 6.]))
+    assert int(TF.TensorArraySize().forward(T(handle, flow))) == 3
+    assert torch.equal(TF.TensorArrayGather().forward(T(handle, torch.tensor([2, 0]), flow)),
+                       torch.tensor([[5., 6.], [1., 2.]]))
+    cat, lens = TF.TensorArrayConcat().forward(T(handle, flow)).to_list()
+    assert torch.equal(cat, torch.tensor([1., 2., 3., 4., 5., 6.])) and lens.tolist() == [2, 2, 2]
+    h2, f2 = TF.TensorArrayCreator().forward(torch.tensor(2)).to_list()
+    TF.TensorArraySplit().forward(T(h2, torch.arange(5.), torch.tensor([2, 3]), f2))
+    assert torch.equal(TF.TensorArrayRead().forward(T(h2, torch.tensor(1), f2)), torch.tensor([2., 3., 4.]))
+
+    stack = TF.StackCreator().forward(None)
+    TF.StackPush().forward(T(stack, torch.tensor([1.])))
+    TF.StackPush().forward(T(stack, torch.tensor([2.])))
+    assert float(TF.StackPop().forward(T(stack))) == 2.0 and float(TF.StackPop().forward(T(stack))) == 1.0
+
+    var = TF.Variable(torch.zeros(2, 2))
+    ref = var.forward(torch.zeros(1))
+    out = TF.Assign().forward(T(ref, torch.ones(2, 2)))
+    assert torch.equal(out, torch.ones(2, 2)) and torch.equal(var.forward(torch.zeros(1)), torch.ones(2, 2))
+    assert TF.ControlDependency().forward(T(torch.tensor([1.]))) is None

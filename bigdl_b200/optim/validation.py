@@ -319,7 +319,8 @@ class PrecisionRecallAUC(ValidationMethod):
             npos = max(l.sum(), 1)
             prec = np.concatenate([[1.0], tp / np.maximum(tp + fp, 1)])
             rec = np.concatenate([[0.0], tp / npos])
-            return float(np.trapz(prec, rec)), len(s)
+            trapezoid = getattr(np, "trapezoid", None) or np.trapz
+            return float(trapezoid(prec, rec)), len(s)
 
         def __add__(self, o):
             return PrecisionRecallAUC._Res(self.scores + o.scores, self.labels + o.labels)

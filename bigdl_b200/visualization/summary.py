@@ -162,6 +162,20 @@ class Summary:
         self.writer = FileWriter(self.folder)
         self._triggers: dict = {}
 
+    # builders of the serialized ``Summary`` messages (the companion object's Summary.scalar / Summary.histogram,
+    # Summary.scala:95,108) for callers that drive a FileWriter themselves
+    @staticmethod
+    def scalar(tag: str, value: float) -> bytes:
+        return proto.summary_scalar(tag, float(value))
+
+    @staticmethod
+    def histogram(tag: str, values) -> bytes:
+        import torch
+
+        if isinstance(values, torch.Tensor):
+            values = values.detach().float().cpu().numpy()
+        return proto.summary_histogram(tag, histogram_proto(values))
+
     def addScalar(self, tag: str, value: float, step: int):
         v = float(value)
         self.writer.addSummary(proto.summary_scalar(tag, v), step)

@@ -174,3 +174,28 @@ def test_profile_layers_reports_every_leaf_once():
     enable_nvtx(True)                                           # no GPU here: stays off, forward still works
     assert m.forward(torch.randn(2, 8)).shape == (2, 4)
     enable_nvtx(False)
+
+
+def test_thread_pool_file_bytes_and_dlmodel_feature_size(tmp_path):
+    from bigdl_b200.utils.file import File
+    from bigdl_b200.utils.thread_pool import ThreadPool
+
+    pool = ThreadPool(2)
+    assert pool.getPoolSize() == 2
+    pool.setPoolSize(3)
+    assert pool.getPoolSize() == 3
+    pool.setMKLThread(1)
+    assert sorted(pool.invokeAndWait([lambda i=i: i * i for i in range(5)])) == [0, 1, 4, 9, 16]
+    p = str(tmp_path / "blob.bin")
+    File.save_bytes(b"\x00\x01payload", p, True)
+    assert File.read_bytes(p) == b"\x00\x01payload"
+
+    import pandas as pd
+    from bigdl_b200.dlframes import DLModel
+    from bigdl_b200.nn.layer import Linear
+
+    m = DLModel(Linear(3, 2), [3])
+    assert m.getFeatureSize() == [3]
+    m.setFeatureSize([3]).setBatchSize(2)
+    out = m.transform(pd.DataFrame({"features": [[1.0, 2.0, 3.0], [0.0, 0.0, 0.0]]}))
+    assert len(out["prediction"]) == 2 and len(out["prediction"][0]) == 2

@@ -72,3 +72,34 @@ def test_keras_and_misc_import_paths():
         .setBatchSize(16).setMaxEpoch(30).setLearningRate(0.5)
     out = clf.fit(df).transform(df)
     assert (out["prediction"] == df["label"]).mean() > 0.9
+
+
+def test_util_common_and_engine_helpers(tmp_path):
+    """The py4j-era helper functions of P/util/{common,engine}.py keep their names and return sensible values without
+    a JVM or Spark."""
+    import os
+    import numpy as np
+    import bigdl.util.common as C
+    import bigdl.util.engine as E
+
+    assert C.init_executor_gateway() is None and C.get_spark_context() is None and C.get_spark_sql_context() is None
+    nodes, cores = C.get_node_and_core_number()
+    assert nodes >= 1 and cores >= 1
+    C.redire_spark_logs(log_path=str(tmp_path / "bigdl.log"))
+    C.show_bigdl_info_logs()
+    conf = C.get_bigdl_conf()
+    assert isinstance(conf, dict) and "bigdl.engineType" in C.create_spark_conf()
+    assert C.get_dtype("double") is np.float64 and C.get_dtype("float") is np.float32
+    samples = C.to_sample_rdd(np.zeros((4, 3), np.float32), np.ones(4, np.float32))
+    assert len(samples) == 4
+    assert os.path.isdir(os.path.dirname(C.create_tmp_path()) or "/")
+    p = str(tmp_path / "t.txt")
+    with open(p, "w") as f:
+        f.write("hello")
+    assert C.text_from_path(p) == "hello" and C.get_local_file(p) == p
+    assert type(C.get_activation_by_name("relu")).__name__ == "ReLU"
+    assert type(C.get_activation_by_name("tanh")).__name__ == "Tanh"
+    assert E.exist_pyspark() in (True, False) and E.compare_version("2.2.0", "2.1.9") == 1
+    assert E.compare_version("1.6.0", "2.0.0") == -1 and E.compare_version("2.0", "2.0") == 0
+    assert E.is_spark_below_2_2() is False and E.prepare_env() is None and isinstance(E.get_bigdl_classpath(), str)
+    E.check_spark_source_conflict("a", "b")

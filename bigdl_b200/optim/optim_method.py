@@ -70,6 +70,18 @@ class MultiStep(LearningRateSchedule):
         o.state["evalCounter"] = n + 1
 
 
+class EpochBoundaries:
+    """Picklable ``epoch -> exponent`` function for EpochDecay / EpochDecayWithWarmUp: the number of boundaries that
+    ``epoch`` has reached (``EpochBoundaries(30, 60, 80)`` is TrainImageNet.scala:117-120's imageNetDecay). A local
+    function works too, but an OptimMethod holding one cannot be written by setCheckpoint."""
+
+    def __init__(self, *boundaries: int):
+        self.boundaries = tuple(sorted(int(b) for b in boundaries))
+
+    def __call__(self, epoch: int) -> int:
+        return sum(1 for b in self.boundaries if epoch >= b)
+
+
 class EpochDecay(LearningRateSchedule):
     def __init__(self, decay_type):
         super().__init__()

@@ -71,7 +71,14 @@ def save_optim_method(om, path: str, overwrite: bool = False):
     for k in ("old_dirs", "old_stps", "g_old", "dir"):
         c.state.delete(k)
     tmp = path + ".tmp"
-    torch.save({"format": "bigdl_b200.optim.v1", "optim": c}, tmp)
+    try:
+        torch.save({"format": "bigdl_b200.optim.v1", "optim": c}, tmp)
+    except (AttributeError, TypeError) as e:   # pickle's complaint about a lambda / local function
+        if os.path.exists(tmp):
+            os.remove(tmp)
+        raise TypeError(f"optim method {type(om).__name__} cannot be saved: {e}. Learning-rate schedules must hold "
+                        "module-level functions or callable objects (e.g. optim_method.EpochBoundaries), not "
+                        "lambdas or local functions") from e
     os.replace(tmp, path)
 
 

@@ -26,17 +26,14 @@ def build(name, classes):
 
 
 def optim_method(a, iters_per_epoch, world):
-    from bigdl_b200.optim.optim_method import SGD, EpochDecayWithWarmUp, Poly, SequentialSchedule, Warmup
+    from bigdl_b200.optim.optim_method import SGD, EpochBoundaries, EpochDecayWithWarmUp, Poly, SequentialSchedule, Warmup
 
     base = a.learningRate
     if a.model == "resnet":
         # linear warm-up to maxLr over warmupEpoch epochs, then x0.1 at epochs 30/60/80 (TrainImageNet.scala:117-135)
         warm_iters = a.warmupEpoch * iters_per_epoch
         delta = (a.maxLr - base) / max(warm_iters, 1)
-
-        def decay(epoch):
-            return 3 if epoch >= 80 else 2 if epoch >= 60 else 1 if epoch >= 30 else 0
-        sched = EpochDecayWithWarmUp(warm_iters, delta, decay)
+        sched = EpochDecayWithWarmUp(warm_iters, delta, EpochBoundaries(30, 60, 80))
         return SGD(base, 0.0, a.weightDecay, 0.9, 0.0, False, learningrate_schedule=sched)
     max_iter = a.maxIteration or a.maxEpoch * iters_per_epoch
     warm_iters = a.warmupEpoch * iters_per_epoch
@@ -61,6 +58,8 @@ def main(argv=None):
     ap.add_argument("--warmupEpoch", type=int, default=0)
     ap.add_argument("--weightDecay", type=float, default=1e-4)
     ap.add_argument("--checkpoint", default=None)
+    ap.add_argument("--checkpointIteration", type=int, default=0,
+                    help="snapshot every N iterations instead of every epoch (models/inception/Options.scala)")
     ap.add_argument("--summary", default=None, help="TensorBoard log dir")
     ap.add_argument("--syncBN", action="store_true")
     a = ap.parse_args(argv)
@@ -102,7 +101,8 @@ def main(argv=None):
     if val is not None:
         opt.setValidation(Trigger.everyEpoch(), val, [Top1Accuracy(), Top5Accuracy()], a.batchSize)
     if a.checkpoint:
-        opt.setCheckpoint(a.checkpoint, Trigger.everyEpoch())
+        opt.setCheckpoint(a.checkpoint, Trigger.severalIteration(a.checkpointIteration) if a.checkpointIteration
+                          else Trigger.everyEpoch())
     if a.summary and rank == 0:
         from bigdl_b200.visualization import TrainSummary, ValidationSummary
 

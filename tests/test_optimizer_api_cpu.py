@@ -139,3 +139,24 @@ def test_checkpointing_does_not_disturb_training(tmp_path):
     c.modules[0].weight.data.add_(1.0)
     assert m.getParameters()[0].data_ptr() == w.data_ptr()
     assert not torch.equal(c.modules[0].weight, m.modules[0].weight)
+
+
+def test_epoch_boundaries_schedule_survives_a_checkpoint(tmp_path):
+    """EpochDecayWithWarmUp with the picklable EpochBoundaries decay: values, save/load, and the error for a local
+    function (which pickle cannot write) names the fix and leaves no partial file behind."""
+    import pytest
+    from bigdl_b200.optim.optim_method import SGD, EpochBoundaries, EpochDecayWithWarmUp, OptimMethod
+
+    d = EpochBoundaries(60, 30, 80)
+    assert [d(e) for e in (1, 29, 30, 59, 60, 80, 200)] == [0, 0, 1, 1, 2, 3, 3]
+    om = SGD(0.1, learningrate_schedule=EpochDecayWithWarmUp(0, 0.0, d))
+    p = str(tmp_path / "om")
+    om.save(p)
+    back = OptimMethod.load(p)
+    assert back.learningRateSchedule.decay_type.boundaries == (30, 60, 80)
+
+    bad = SGD(0.1, learningrate_schedule=EpochDecayWithWarmUp(0, 0.0, lambda e: 0))
+    q = str(tmp_path / "bad")
+    with pytest.raises(TypeError, match="EpochBoundaries"):
+        bad.save(q)
+    assert not (tmp_path / "bad").exists() and not (tmp_path / "bad.tmp").exists()

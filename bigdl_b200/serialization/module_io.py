@@ -22,6 +22,7 @@ import inspect
 import os
 import re
 import struct
+import sys
 
 import numpy as np
 import torch
@@ -55,6 +56,70 @@ class _Ctx:
         return self.next_id
 
 
+# Fixed-width packed fields of TensorStorage go in and out as raw little-endian bytes (one wire-format record: tag,
+# byte length, payload) instead of one Python object per element — a VGG-16 snapshot is 134 M floats.
+_RAW_FIELDS = {"float_data": (2, np.float32), "double_data": (3, np.float64), "bool_data": (4, np.uint8)}
+_RAW_MIN = 256
+
+
+def _varint(n: int) -> bytes:
+    out = bytearray()
+    while True:
+        b = n & 0x7F
+        n >>= 7
+        out.append(b | (0x80 if n else 0))
+        if not n:
+            return bytes(out)
+
+
+def _fill_storage(st, field: str, flat: torch.Tensor):
+    if field in _RAW_FIELDS and flat.numel() >= _RAW_MIN and sys.byteorder == "little":
+        num, npdt = _RAW_FIELDS[field]
+        raw = flat.numpy().astype(npdt, copy=False).tobytes()
+        st.MergeFromString(bytes([num << 3 | 2]) + _varint(len(raw)) + raw)
+    else:
+        getattr(st, field).extend(flat.tolist())
+
+
+def _read_varint(buf, pos):
+    v = shift = 0
+    while True:
+        b = buf[pos]
+        pos += 1
+        v |= (b & 0x7F) << shift
+        if not b & 0x80:
+            return v, pos
+        shift += 7
+
+
+def _storage_flat(st, field: str, dtype) -> torch.Tensor:
+    """The ``field`` values of a TensorStorage as a flat tensor."""
+    vals = getattr(st, field)
+    if field not in _RAW_FIELDS or len(vals) < _RAW_MIN or sys.byteorder != "little":
+        return torch.tensor(list(vals), dtype=dtype)
+    want, npdt = _RAW_FIELDS[field]
+    buf = memoryview(st.SerializeToString())
+    pos, parts = 0, []
+    while pos < len(buf):
+        tag, pos = _read_varint(buf, pos)
+        num, wt = tag >> 3, tag & 7
+        if wt == 0:
+            _, pos = _read_varint(buf, pos)
+        elif wt == 1:
+            pos += 8
+        elif wt == 5:
+            pos += 4
+        elif wt == 2:
+            n, pos = _read_varint(buf, pos)
+            if num == want:
+                parts.append(np.frombuffer(buf[pos:pos + n], dtype=npdt))
+            pos += n
+        else:
+            raise ValueError(f"unexpected wire type {wt} in TensorStorage")
+    arr = parts[0].copy() if len(parts) == 1 else np.concatenate(parts)
+    return torch.from_numpy(arr).to(dtype)
+
+
 def tensor_to_proto(t: torch.Tensor, ctx: _Ctx | None, inline: bool = False) -> pb.BigDLTensor:
     t = t.detach().cpu()
     out = pb.BigDLTensor()
@@ -82,11 +147,12 @@ def tensor_to_proto(t: torch.Tensor, ctx: _Ctx | None, inline: bool = False) -> 
     tid = ctx.new_id() if ctx else 0
     sid = ctx.new_id() if ctx else 0
     out.id = tid
-    st = pb.TensorStorage(datatype=dt, id=sid)
-    getattr(st, field).extend(data.reshape(-1).tolist())
     if ctx is None or inline:
-        out.storage.CopyFrom(st)
+        out.storage.datatype, out.storage.id = dt, sid
+        _fill_storage(out.storage, field, data.reshape(-1))
     else:
+        st = pb.TensorStorage(datatype=dt, id=sid)
+        _fill_storage(st, field, data.reshape(-1))
         out.storage.datatype, out.storage.id = dt, sid
         ctx.storages[sid] = st
         ctx.tensors[tid] = out
@@ -101,7 +167,7 @@ def proto_to_tensor(p: pb.BigDLTensor, storages: dict[int, torch.Tensor]) -> tor
                          ("long_data", torch.int64), ("bool_data", torch.bool)):
         vals = getattr(st, field)
         if len(vals):
-            flat = torch.tensor(list(vals), dtype=dtype)
+            flat = _storage_flat(st, field, dtype)
             break
     if flat is None:
         flat = storages.get(sid)
@@ -455,6 +521,8 @@ def _proto_to_module(p: pb.BigDLModule, storages):
 
 # ---------------------------------------------------------------- file level
 _DT_CODE = {"float_data": 2, "double_data": 3, "int_data": 0, "long_data": 1, "bool_data": 5}
+_DT_TORCH = {"float_data": torch.float32, "double_data": torch.float64, "int_data": torch.int32,
+             "long_data": torch.int64, "bool_data": torch.bool}
 
 
 def save_module(module, path: str, weight_path: str | None = None, overwrite: bool = False):
@@ -466,23 +534,21 @@ def save_module(module, path: str, weight_path: str | None = None, overwrite: bo
     m = _portable_copy(module)
     ctx = _Ctx()
     root = _module_to_proto(m, ctx)
-    gs = pb.NameAttrList(name="global_storage")
+    root.attr["global_storage"].dataType = pb.DataType.NAME_ATTR_LIST
+    gs = root.attr["global_storage"].nameAttrListValue
+    gs.name = "global_storage"
     if weight_path is None:
         for tid, t in ctx.tensors.items():
-            full = pb.BigDLTensor()
-            full.CopyFrom(t)
-            full.storage.CopyFrom(ctx.storages[t.storage.id])
             av = gs.attr[str(tid)]
             av.dataType = pb.DataType.TENSOR
-            av.tensorValue.CopyFrom(full)
+            av.tensorValue.CopyFrom(t)
+            av.tensorValue.storage.CopyFrom(ctx.storages[t.storage.id])
     else:
         for tid, t in ctx.tensors.items():
             av = gs.attr[str(tid)]
             av.dataType = pb.DataType.TENSOR
             av.tensorValue.CopyFrom(t)
         _write_weight_file(weight_path, ctx)
-    root.attr["global_storage"].dataType = pb.DataType.NAME_ATTR_LIST
-    root.attr["global_storage"].nameAttrListValue.CopyFrom(gs)
     os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
     with open(path + ".tmp", "wb") as f:
         f.write(root.SerializeToString())
@@ -505,7 +571,7 @@ def _write_weight_file(path: str, ctx: _Ctx):
         for field, code in _DT_CODE.items():
             vals = getattr(st, field)
             if len(vals):
-                arr = np.asarray(list(vals))
+                arr = _storage_flat(st, field, _DT_TORCH[field]).numpy()
                 fmt = {"float_data": ">f4", "double_data": ">f8", "int_data": ">i4", "long_data": ">i8",
                        "bool_data": ">i1"}[field]
                 put(struct.pack(">iii", sid, code, arr.size))

@@ -113,3 +113,23 @@ def test_save_load_convenience_wrappers(tmp_path):
     assert torch.allclose(back.evaluate().forward(x), y, atol=1e-5)
     again = Module.load_caffe(_net(), proto, weights, match_all=False)
     assert torch.allclose(again.evaluate().forward(x), y, atol=1e-5)
+
+
+def test_bulk_tensor_storage_bytes_match_the_elementwise_encoding(monkeypatch):
+    """Large float/double/bool storages are written as one raw packed record; the bytes on the wire and the values
+    read back must be the same as with the element-by-element encoder."""
+    import torch
+    from bigdl_b200.serialization import module_io as mio
+
+    torch.manual_seed(0)
+    for t in (torch.randn(40, 20), torch.randn(300, dtype=torch.float64), torch.rand(17, 31) > 0.5,
+              torch.randint(-5, 5, (400,)), torch.randn(50, 30).t()):
+        fast = mio.tensor_to_proto(t, None)
+        monkeypatch.setattr(mio, "_RAW_MIN", 1 << 60)
+        slow = mio.tensor_to_proto(t, None)
+        back_slow = mio.proto_to_tensor(fast, {})
+        monkeypatch.setattr(mio, "_RAW_MIN", 256)
+        assert fast.SerializeToString() == slow.SerializeToString()
+        back = mio.proto_to_tensor(fast, {})
+        assert back.dtype == back_slow.dtype and torch.equal(back, back_slow)
+        assert torch.equal(back.to(t.dtype), t)

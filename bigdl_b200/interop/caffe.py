@@ -10,11 +10,13 @@ text_format. Caffe semantics kept: pooling output sizes round UP, InnerProduct f
 from __future__ import annotations
 
 import os
+import sys
 
 import numpy as np
 import torch
 from google.protobuf import text_format
 
+from ..serialization.module_io import packed_merge, packed_read
 from . import caffe_pb as P
 
 
@@ -30,7 +32,10 @@ def _read_net(def_path: str | None, model_path: str | None):
 
 
 def _blob(b) -> torch.Tensor:
-    data = np.asarray(b.data if len(b.data) else b.double_data, dtype=np.float32)
+    if len(b.data) >= 256 and sys.byteorder == "little":     # one raw record instead of a Python float per element
+        data = packed_read(b, 5, np.float32)
+    else:
+        data = np.asarray(b.data if len(b.data) else b.double_data, dtype=np.float32)
     if b.HasField("shape") and len(b.shape.dim):
         shape = [int(d) for d in b.shape.dim]
     else:
@@ -403,7 +408,11 @@ class CaffePersister:
         def blob(layer, t):
             b = layer.blobs.add()
             b.shape.dim.extend(list(t.shape))
-            b.data.extend(t.detach().float().reshape(-1).tolist())
+            flat = t.detach().float().reshape(-1)
+            if flat.numel() >= 256 and sys.byteorder == "little":
+                packed_merge(b, 5, flat.cpu().numpy())
+            else:
+                b.data.extend(flat.tolist())
 
         def emit(m, bottoms):
             """Returns the top name produced by ``m``."""
@@ -494,6 +503,56 @@ class CaffePersister:
                 layer.concat_param.axis = m.dimension - 1
             elif isinstance(m, (L.View, L.Reshape, L.InferReshape)):
                 layer.type = "Flatten"
+            # the rest of Converter.scala:297-329's toCaffe table
+            elif isinstance(m, L.SpatialFullConvolution):
+                layer.type = "Deconvolution"
+                cp = layer.convolution_param
+                has_bias = getattr(m, "bias", None) is not None
+                cp.num_output, cp.group, cp.bias_term = m.nout, m.n_group, has_bias
+                cp.kernel_h, cp.kernel_w, cp.stride_h, cp.stride_w = m.kh, m.kw, m.dh, m.dw
+                cp.pad_h, cp.pad_w = m.pad_h, m.pad_w
+                blob(layer, m.weight.reshape(m.nin, m.nout // m.n_group, m.kh, m.kw))
+                if has_bias:
+                    blob(layer, m.bias)
+            elif isinstance(m, L.SpatialWithinChannelLRN):
+                layer.type = "LRN"
+                lp = layer.lrn_param
+                lp.local_size, lp.alpha, lp.beta, lp.norm_region = m.size, m.alpha, m.beta, 1
+            elif isinstance(m, L.Threshold):
+                layer.type = "Threshold"
+                layer.threshold_param.threshold = m.th
+            elif isinstance(m, L.ELU):
+                layer.type = "ELU"
+                layer.elu_param.alpha = m.alpha
+            elif isinstance(m, L.PReLU):
+                layer.type = "PReLU"
+                layer.prelu_param.channel_shared = m.n_output_plane == 0
+                blob(layer, m.weight)
+            elif isinstance(m, L.Power):
+                layer.type = "Power"
+                layer.power_param.power, layer.power_param.scale, layer.power_param.shift = m.power, m.scale, m.shift
+            elif isinstance(m, L.Abs):
+                layer.type = "AbsVal"
+            elif isinstance(m, L.Exp):
+                layer.type = "Exp"
+            elif isinstance(m, L.Log):
+                layer.type = "Log"
+            elif isinstance(m, L.Scale):
+                layer.type = "Scale"
+                layer.scale_param.bias_term = True
+                ps = [p for _, _, p in m.leaf_parameters()]
+                blob(layer, ps[0].reshape(-1))
+                blob(layer, ps[1].reshape(-1))
+            elif isinstance(m, (L.Add, L.CAdd)):
+                layer.type = "Bias"
+                blob(layer, m.bias.reshape(-1))
+            elif isinstance(m, L.Replicate):
+                layer.type = "Tile"
+                layer.tile_param.axis, layer.tile_param.tiles = m.dim - 1, m.n_features
+            elif isinstance(m, L.CSubTable):
+                layer.type = "Eltwise"
+                layer.eltwise_param.operation = 1
+                layer.eltwise_param.coeff.extend([1.0, -1.0])
             else:
                 raise ValueError(f"saveCaffe: unsupported module {type(m).__name__}")
             return layer.name

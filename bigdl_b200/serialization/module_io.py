@@ -72,11 +72,16 @@ def _varint(n: int) -> bytes:
             return bytes(out)
 
 
+def packed_merge(msg, field_number: int, arr: np.ndarray):
+    """Append ``arr`` to the packed fixed-width repeated field ``field_number`` of ``msg`` as one wire record."""
+    raw = np.ascontiguousarray(arr).tobytes()
+    msg.MergeFromString(_varint(field_number << 3 | 2) + _varint(len(raw)) + raw)
+
+
 def _fill_storage(st, field: str, flat: torch.Tensor):
     if field in _RAW_FIELDS and flat.numel() >= _RAW_MIN and sys.byteorder == "little":
         num, npdt = _RAW_FIELDS[field]
-        raw = flat.numpy().astype(npdt, copy=False).tobytes()
-        st.MergeFromString(bytes([num << 3 | 2]) + _varint(len(raw)) + raw)
+        packed_merge(st, num, flat.numpy().astype(npdt, copy=False))
     else:
         getattr(st, field).extend(flat.tolist())
 
@@ -92,13 +97,9 @@ def _read_varint(buf, pos):
         shift += 7
 
 
-def _storage_flat(st, field: str, dtype) -> torch.Tensor:
-    """The ``field`` values of a TensorStorage as a flat tensor."""
-    vals = getattr(st, field)
-    if field not in _RAW_FIELDS or len(vals) < _RAW_MIN or sys.byteorder != "little":
-        return torch.tensor(list(vals), dtype=dtype)
-    want, npdt = _RAW_FIELDS[field]
-    buf = memoryview(st.SerializeToString())
+def packed_read(msg, field_number: int, npdt) -> np.ndarray:
+    """All values of the packed fixed-width repeated field ``field_number`` of ``msg``, read from its wire bytes."""
+    buf = memoryview(msg.SerializeToString())
     pos, parts = 0, []
     while pos < len(buf):
         tag, pos = _read_varint(buf, pos)
@@ -111,13 +112,23 @@ def _storage_flat(st, field: str, dtype) -> torch.Tensor:
             pos += 4
         elif wt == 2:
             n, pos = _read_varint(buf, pos)
-            if num == want:
+            if num == field_number:
                 parts.append(np.frombuffer(buf[pos:pos + n], dtype=npdt))
             pos += n
         else:
-            raise ValueError(f"unexpected wire type {wt} in TensorStorage")
-    arr = parts[0].copy() if len(parts) == 1 else np.concatenate(parts)
-    return torch.from_numpy(arr).to(dtype)
+            raise ValueError(f"unexpected wire type {wt} in {type(msg).__name__}")
+    if not parts:
+        return np.zeros(0, dtype=npdt)
+    return parts[0].copy() if len(parts) == 1 else np.concatenate(parts)
+
+
+def _storage_flat(st, field: str, dtype) -> torch.Tensor:
+    """The ``field`` values of a TensorStorage as a flat tensor."""
+    vals = getattr(st, field)
+    if field not in _RAW_FIELDS or len(vals) < _RAW_MIN or sys.byteorder != "little":
+        return torch.tensor(list(vals), dtype=dtype)
+    want, npdt = _RAW_FIELDS[field]
+    return torch.from_numpy(packed_read(st, want, npdt)).to(dtype)
 
 
 def tensor_to_proto(t: torch.Tensor, ctx: _Ctx | None, inline: bool = False) -> pb.BigDLTensor:

@@ -396,3 +396,27 @@ def test_tfrecord_and_session(tmp_path):
     assert np.allclose(out.detach().numpy(), pred[:2], atol=1e-5)
     saved = sess.saveParameters(str(tmp_path / "vars.npz"))
     assert np.abs(np.load(saved)["W"] - Wt).max() < 0.05
+
+
+def test_caffe_export_covers_the_activation_and_affine_layers(tmp_path):
+    """saveCaffe → loadCaffeModel for the rest of the reference's toCaffe table (Converter.scala:297-329): ELU, PReLU,
+    Deconvolution, Scale, Bias, AbsVal, Power, within-channel LRN, Threshold, Exp; weights above 256 elements take the
+    raw packed-record path."""
+    import torch
+    from bigdl_b200.nn import layer as L
+    from bigdl_b200.nn.module import Module
+
+    torch.manual_seed(0)
+    m = (L.Sequential().add(L.SpatialConvolution(3, 4, 3, 3, 1, 1, 1, 1)).add(L.ELU(0.7))
+         .add(L.SpatialFullConvolution(4, 6, 3, 3, 2, 2, 1, 1)).add(L.PReLU(6)).add(L.Scale([1, 6, 1, 1])).add(L.Abs())
+         .add(L.Power(2.0, 0.5, 0.1)).add(L.SpatialWithinChannelLRN(3, 0.5, 0.75)).add(L.CAdd([1, 6, 1, 1]))
+         .add(L.Threshold(0.2, 0.0)).add(L.Exp()))
+    for p in m.parameters()[0]:
+        if p.abs().sum() == 0:
+            p.data.normal_()
+    m.evaluate()
+    proto, weights = str(tmp_path / "n.prototxt"), str(tmp_path / "n.caffemodel")
+    m.saveCaffe(proto, weights)
+    back = Module.loadCaffeModel(proto, weights).evaluate()
+    x = torch.randn(2, 3, 6, 6)
+    assert torch.allclose(m.forward(x), back.forward(x), atol=1e-6)

@@ -663,9 +663,13 @@ def save_tf(model, inputs, path: str, byteOrder: str = "little_endian", dataForm
     b = _GraphBuilder()
     nhwc = dataFormat.lower() == "nhwc"
     f32 = np.dtype(np.float32)
+    used: set = set()
 
     def emit(m, ins):
-        name = m.getName() if m.hasName() else b.fresh(type(m).__name__)
+        name = m.getName()                # the generated default name too, so callers can ask loadTF for it
+        if name in used:
+            name = b.fresh(name)
+        used.add(name)
         x = ins[0] if ins else None
         if isinstance(m, Sequential):
             cur = ins

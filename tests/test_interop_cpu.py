@@ -420,3 +420,19 @@ def test_caffe_export_covers_the_activation_and_affine_layers(tmp_path):
     back = Module.loadCaffeModel(proto, weights).evaluate()
     x = torch.randn(2, 3, 6, 6)
     assert torch.allclose(m.forward(x), back.forward(x), atol=1e-6)
+
+
+def test_tf_export_keeps_default_module_names(tmp_path):
+    """A model whose layers were never named exports under getName(), so the caller can ask loadTF for
+    ``model.modules[-1].getName()`` as the reference's users do."""
+    import torch
+    from bigdl_b200.nn import layer as L
+    from bigdl_b200.nn.module import Module
+
+    torch.manual_seed(0)
+    m = L.Sequential().add(L.Linear(8, 6)).add(L.Tanh()).add(L.Linear(6, 3))
+    p = str(tmp_path / "m.pb")
+    m.saveTF([("input", [2, 8])], p)
+    back = Module.loadTF(p, ["input"], [m.modules[-1].getName()])
+    x = torch.randn(2, 8)
+    assert torch.allclose(m.forward(x), back.forward(x), atol=1e-5)

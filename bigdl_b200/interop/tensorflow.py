@@ -746,6 +746,38 @@ def save_tf(model, inputs, path: str, byteOrder: str = "little_endian", dataForm
                 raise ValueError("LRN export needs NHWC")
             return b.node("LRN", name, [x], T=f32, depth_radius=(m.size - 1) // 2, bias=float(m.k),
                           alpha=float(m.alpha) / m.size, beta=float(m.beta))
+        # the remaining entries of TensorflowSaver.scala:171-194 — these act on non-image tensors, axes are taken as given
+        if isinstance(m, L.Squeeze):
+            dims = [int(d) - 1 + (1 if m.batch_mode else 0) for d in (m.dims or [])]
+            return b.node("Squeeze", name, [x], T=f32, squeeze_dims=dims)
+        if isinstance(m, L.Mean):
+            axis = b.const(name + "/axis", np.array([m.dimension - 1], np.int32))
+            return b.node("Mean", name, [x, axis], T=f32, keep_dims=not m.squeeze)
+        if isinstance(m, L.Padding):
+            rank = m.n_input_dim + 1                       # exported graphs are batched
+            d = abs(m.dim) if m.n_input_dim else m.dim - 1
+            p = np.zeros((rank, 2), np.int32)
+            p[d, 0 if m.pad < 0 else 1] = abs(m.pad)
+            if m.value != 0.0:
+                return b.node("PadV2", name, [x, b.const(name + "/paddings", p),
+                                              b.const(name + "/value", np.array(m.value, np.float32))], T=f32)
+            return b.node("Pad", name, [x, b.const(name + "/paddings", p)], T=f32)
+        if isinstance(m, L.Scale):
+            ps = [q.detach().numpy() for _, _, q in m.leaf_parameters()]
+            w, bias = ps[0], ps[1]
+            if nhwc and w.ndim == 4:
+                w, bias = w.transpose(0, 2, 3, 1), bias.transpose(0, 2, 3, 1)
+            y = b.node("Mul", name + "/mul", [x, b.const(name + "/weight", w.copy())], T=f32)
+            return b.node("Add", name, [y, b.const(name + "/bias", bias.copy())], T=f32)
+        if isinstance(m, L.TemporalConvolution):
+            # (B, T, Cin) → (B, 1, T, Cin) NHWC → Conv2D with a [1, kw, Cin, Cout] filter → back to (B, T', Cout)
+            w = m.weight.detach().numpy().reshape(m.out, m.kw, m.inp).transpose(1, 2, 0)[None].copy()
+            e = b.node("ExpandDims", name + "/expand", [x, b.const(name + "/expand_axis", np.array(1, np.int32))], T=f32)
+            y = b.node("Conv2D", name + "/conv", [e, b.const(name + "/weight", w)], T=f32, strides=[1, 1, m.dw, 1],
+                       padding="VALID", data_format="NHWC")
+            y = b.node("BiasAdd", name + "/bias_add", [y, b.const(name + "/bias", m.bias.detach().numpy().copy())],
+                       T=f32, data_format="NHWC")
+            return b.node("Squeeze", name, [y], T=f32, squeeze_dims=[1])
         raise ValueError(f"saveTF: unsupported module {type(m).__name__}")
 
     placeholders = []

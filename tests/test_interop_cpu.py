@@ -436,3 +436,30 @@ def test_tf_export_keeps_default_module_names(tmp_path):
     back = Module.loadTF(p, ["input"], [m.modules[-1].getName()])
     x = torch.randn(2, 8)
     assert torch.allclose(m.forward(x), back.forward(x), atol=1e-5)
+
+
+def test_tf_export_sequence_and_affine_layers(tmp_path):
+    """TemporalConvolution / Padding / Mean / Squeeze / Scale of the reference's saver table (TensorflowSaver.scala:
+    171-194) survive saveTF → loadTF."""
+    import torch
+    from bigdl_b200.nn import layer as L
+    from bigdl_b200.nn.module import Module
+
+    torch.manual_seed(0)
+    m = (L.Sequential().add(L.TemporalConvolution(4, 5, 3, 1)).add(L.Tanh()).add(L.Padding(1, 2, 2, 0.5))
+         .add(L.Padding(2, -1, 2)).add(L.Mean(2, squeeze=False)).add(L.Squeeze(2)))
+    x = torch.randn(3, 9, 4)
+    p = str(tmp_path / "seq.pb")
+    m.saveTF([("input", [3, 9, 4])], p)
+    back = Module.loadTF(p, ["input"], [m.modules[-1].getName()])
+    assert torch.allclose(m.forward(x), back.forward(x), atol=1e-5)
+
+    m2 = L.Sequential().add(L.SpatialConvolution(3, 4, 3, 3)).add(L.Scale([1, 4, 1, 1])).add(L.ReLU())
+    for q in m2.modules[1].parameters()[0]:
+        q.data.normal_()
+    x = torch.randn(2, 3, 6, 6)
+    p = str(tmp_path / "img.pb")
+    m2.saveTF([("input", [2, 3, 6, 6])], p)
+    back = Module.loadTF(p, ["input"], [m2.modules[-1].getName()])
+    out = back.forward(x.permute(0, 2, 3, 1).contiguous()).permute(0, 3, 1, 2)
+    assert torch.allclose(m2.forward(x), out, atol=1e-5)

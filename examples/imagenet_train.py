@@ -60,6 +60,8 @@ def main(argv=None):
     ap.add_argument("--checkpoint", default=None)
     ap.add_argument("--checkpointIteration", type=int, default=0,
                     help="snapshot every N iterations instead of every epoch (models/inception/Options.scala)")
+    ap.add_argument("--resume", default=None, help="checkpoint folder: continue from its newest model.N / state.N "
+                    "(the reference's --model / --state snapshot pair)")
     ap.add_argument("--summary", default=None, help="TensorBoard log dir")
     ap.add_argument("--syncBN", action="store_true")
     a = ap.parse_args(argv)
@@ -73,7 +75,19 @@ def main(argv=None):
 
     rank, world, dev = init_distributed()
     Engine.init()
-    model = build(a.model, a.classNum).to(dev)
+    model, resumed_om = build(a.model, a.classNum), None
+    if a.resume:
+        from bigdl_b200.nn.module import Module
+        from bigdl_b200.optim.optim_method import OptimMethod
+        from bigdl_b200.serialization.snapshot import latest_file
+
+        mf, sf = latest_file(a.resume, "model."), latest_file(a.resume, "state.")
+        if mf is None or sf is None:
+            raise SystemExit(f"--resume {a.resume}: no model.N / state.N pair found")
+        model, resumed_om = Module.load(mf), OptimMethod.load(sf)
+        if rank == 0:
+            print(f"resuming from {mf} (iteration {resumed_om.state['neval'] - 1}, epoch {resumed_om.state['epoch']})")
+    model = model.to(dev)
     if a.syncBN:
         from bigdl_b200.parallel import enable_sync_batchnorm
 
@@ -97,7 +111,7 @@ def main(argv=None):
         iters_per_epoch = 100
     end = Trigger.maxIteration(a.maxIteration) if a.maxIteration else Trigger.maxEpoch(a.maxEpoch)
     opt = Optimizer(model=model, training_set=train, criterion=ClassNLLCriterion(),
-                    optim_method=optim_method(a, iters_per_epoch, world), end_trigger=end, batch_size=a.batchSize * world)
+                    optim_method=resumed_om or optim_method(a, iters_per_epoch, world), end_trigger=end, batch_size=a.batchSize * world)
     if val is not None:
         opt.setValidation(Trigger.everyEpoch(), val, [Top1Accuracy(), Top5Accuracy()], a.batchSize)
     if a.checkpoint:

@@ -123,7 +123,13 @@ class GraphedTrainStep:
                 else:
                     v.zero_()               # created during warm-up: logically "not there yet"
         fresh = not snap["hist_keys"]
-        self.om.state = snap["om_state"]
+        # restore IN PLACE: the training loop holds an alias of this Table (epoch / neval bookkeeping), so the object
+        # must stay the same or epoch-based schedules would read a frozen copy under graph replay
+        live = self.om.state
+        for k in list(live.keys()):
+            del live[k]
+        for k, v in snap["om_state"].items():
+            live[k] = v
         for k, v in snap["om_attrs"].items():
             self.om.__dict__[k] = v
         if fresh and self.om._hist:

@@ -353,6 +353,10 @@ class DistriOptimizer(Optimizer):
         retry_times = int(config.get("bigdl.failure.retryTimes"))
         retry_interval = float(config.get("bigdl.failure.retryTimeInterval"))
         retry_num, last_failure = 0, time.time()
+        if self.checkpoint_path is not None:
+            # one timestamped folder per optimize() call, fixed BEFORE the retry loop (DistriOptimizer.scala:874-880):
+            # a retry must find the snapshots the failed attempt wrote
+            self._checkpoint_dir = os.path.join(self.checkpoint_path, datetime.now().strftime("%Y%m%d_%H%M%S"))
         while True:
             try:
                 return _train_loop(self, distributed=True)
@@ -376,9 +380,16 @@ class DistriOptimizer(Optimizer):
         from ..serialization.snapshot import latest_file, load_optim_method, load_snapshot_into
 
         root = getattr(self, "_checkpoint_dir", None) or self.checkpoint_path
-        model_file = latest_file(root, "model")
+        # release the failed attempt's parameter plane first: on the p2p backend the model's bf16 compute weights
+        # alias the symmetric buffer, so they are moved to private memory before that buffer is freed
+        if self._param_sync is not None:
+            self._param_sync.close()
+            self._param_sync = None
+        model_file = latest_file(root, "model") if os.path.isdir(root) else None
         if model_file is None:
-            raise RuntimeError("no model snapshot found to recover from")
+            # no snapshot yet: retry from the model and optim methods as they are (DistriOptimizer.scala:925-938)
+            log.warning("no model snapshot under %s; retrying from the current model", root)
+            return
         load_snapshot_into(self.model, model_file)
         for name in list(self.optim_methods):
             f = latest_file(root, f"optimMethod-{name}")
@@ -386,9 +397,6 @@ class DistriOptimizer(Optimizer):
                 om = load_optim_method(f)
                 om.clearHistory()
                 self.optim_methods[name] = om
-        if self._param_sync is not None:
-            self._param_sync.close()
-            self._param_sync = None
 
 
 def _train_loop(opt: Optimizer, distributed: bool, strategy_factory=None):
@@ -406,6 +414,9 @@ def _train_loop(opt: Optimizer, distributed: bool, strategy_factory=None):
     world = dist.get_world_size() if (distributed and dist.is_initialized()) else 1
     ranges = opt._check_submodules(flat) if len(opt.optim_methods) > 1 else None
 
+    prev_sync = model.__dict__.pop("_param_sync_keepalive", None)
+    if prev_sync is not None:
+        prev_sync.close()       # an earlier optimize() parked its symmetric buffer on the model; release it (collective)
     # ParallelOptimizer keeps full (non-sharded) weights and optimizer state on every rank: no sharded master copy
     sync = AllReduceParameter(flat, backend=None if (world > 1 and strategy_factory is None) else "local")
     sync.init()
@@ -426,8 +437,10 @@ def _train_loop(opt: Optimizer, distributed: bool, strategy_factory=None):
     records_this_epoch = state.getOrElse("recordsProcessedThisEpoch", 0)
     epoch_size = dataset.size()
     if opt.checkpoint_path is not None:
-        opt._checkpoint_dir = os.path.join(opt.checkpoint_path, datetime.now().strftime("%Y%m%d_%H%M%S")) \
-            if distributed else opt.checkpoint_path
+        if not distributed:
+            opt._checkpoint_dir = opt.checkpoint_path
+        elif getattr(opt, "_checkpoint_dir", None) is None:
+            opt._checkpoint_dir = os.path.join(opt.checkpoint_path, datetime.now().strftime("%Y%m%d_%H%M%S"))
     dataset.shuffle()
     data_iter = dataset.data(train=True)
     prefetch = _Prefetcher(data_iter, device) if device.type == "cuda" else None

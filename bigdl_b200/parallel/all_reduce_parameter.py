@@ -360,6 +360,22 @@ class AllReduceParameter:
         return fl.weights
 
     def close(self):
+        """Free the symmetric buffer. The model's bf16 compute weights live inside it on the p2p backend, so they are
+        first re-homed in private memory (every layer's view is re-pointed) — nothing may alias freed device memory."""
         if self._sym is not None:
+            fl = self.flat
+            if fl.compute is not None and getattr(self, "g16", None) is not None:
+                self._rebind_compute(torch.empty(self.P, dtype=torch.bfloat16, device=self.device))
+            self.g16 = None
             self._sym.close()
             self._sym = None
+            self._inited = False
+
+    def __del__(self):
+        try:
+            # only un-shared buffers are freed by the finaliser: a peer may still have a shared one mapped, and those
+            # are released collectively by close() (the optimizer does that before it builds the next one)
+            if self._sym is not None and self._sym.local_ptr is not None and self.world == 1:
+                self._sym.close(collective=False)
+        except Exception:  # noqa: BLE001 - interpreter shutdown
+            pass

@@ -75,7 +75,9 @@ class SymmetricBuffer:
             arr[r] = self.ptrs[r] + offset_bytes
         return arr
 
-    def close(self):
+    def close(self, collective: bool = True):
+        """Unmap the peers' copies and free the local one. ``collective=False`` (finalisers) skips the barrier that
+        normally keeps a rank from freeing memory a slower peer still has mapped."""
         lib = _lib.cuda_lib()
         if lib is None or self.local_ptr is None:
             return
@@ -83,7 +85,7 @@ class SymmetricBuffer:
         for p in self._opened:
             lib.bdl_ipc_close(ctypes.c_void_p(p))
         self._opened = []
-        if self.world > 1 and dist.is_initialized():
+        if collective and self.world > 1 and dist.is_initialized():
             try:
                 dist.barrier(group=self.group)
             except Exception:

@@ -342,6 +342,8 @@ def _module_to_proto(m, ctx: _Ctx) -> pb.BigDLModule:
     cls = type(m)
     out.moduleType = _JVM_PREFIX + cls.__name__ if cls.__module__.startswith("bigdl_b200.nn") else \
         f"{cls.__module__}.{cls.__name__}"
+    if not cls.__module__.startswith(("bigdl_b200.", "bigdl.")):
+        _USER_CLASSES.setdefault(out.moduleType, cls)     # a class this process saved is one it may load back
     out.version = "0.10.0"
     out.train = m.isTraining()
     out.id = id(m) & 0x7FFFFFFF
@@ -450,8 +452,38 @@ def _resolve_class(module_type: str):
             except ImportError:
                 pass
         raise KeyError(f"no layer registered for module type {module_type}")
-    modname, _, cname = module_type.rpartition(".")
-    return getattr(importlib.import_module(modname), cname)
+    # Anything outside the BigDL namespace must have been registered explicitly (register_module_class): a model file
+    # is data, and resolving arbitrary dotted names from it would let a crafted file instantiate any importable class.
+    cls = _USER_CLASSES.get(module_type)
+    if cls is None:
+        modname, _, cname = module_type.rpartition(".")
+        if modname.split(".")[0] in ("bigdl_b200", "bigdl"):
+            cls = getattr(importlib.import_module(modname), cname, None)
+    from ..nn.module import Module as _Module
+
+    if cls is None or not (inspect.isclass(cls) and issubclass(cls, _Module)) and not _is_node_factory(cls):
+        raise KeyError(f"module type {module_type!r} is not a registered layer class "
+                       "(use serialization.module_io.register_module_class for custom layers)")
+    return cls
+
+
+_USER_CLASSES: dict = {}
+
+
+def register_module_class(cls, name: str | None = None):
+    """Allow ``loadModule`` to rebuild a user-defined layer (the reference's ModuleSerializer.registerModule,
+    S/utils/serializer/ModuleSerializer.scala:163-170). ``name`` defaults to the class's dotted path."""
+    from ..nn.module import Module as _Module
+
+    if not (inspect.isclass(cls) and issubclass(cls, _Module)):
+        raise TypeError("only Module subclasses can be registered for deserialisation")
+    _USER_CLASSES[name or f"{cls.__module__}.{cls.__qualname__}"] = cls
+    return cls
+
+
+def _is_node_factory(obj) -> bool:
+    """``Input`` is a function that wraps a placeholder module in a graph Node; it lives in bigdl_b200.nn."""
+    return callable(obj) and getattr(obj, "__module__", "").startswith("bigdl_b200.nn") and getattr(obj, "__name__", "") == "Input"
 
 
 def _proto_to_module(p: pb.BigDLModule, storages):
@@ -504,11 +536,17 @@ def _proto_to_module(p: pb.BigDLModule, storages):
         if "ceilMode" in attrs and hasattr(m, "ceil_mode"):
             m.ceil_mode = bool(attrs["ceilMode"])
         targets = [q for _, _, q in m.leaf_parameters()] if _rebuilds_children(m) else list(m._parameters.values())
-        if len(p.parameters) and len(p.parameters) == len(targets):
+        if len(p.parameters) and len(p.parameters) != len(targets):
+            raise ValueError(f"module {p.name or p.moduleType}: the file holds {len(p.parameters)} parameter tensors "
+                             f"but the rebuilt {type(m).__name__} has {len(targets)}")
+        if len(p.parameters):
             with torch.no_grad():
                 for q, tp in zip(targets, p.parameters):
                     t = proto_to_tensor(tp, storages)
                     if t is not None:
+                        if t.numel() != q.numel():
+                            raise ValueError(f"module {p.name or p.moduleType}: parameter of {t.numel()} elements "
+                                             f"does not fit {tuple(q.shape)}")
                         q.copy_(t.reshape(q.shape).to(q.dtype))
         elif len(p.parameters) == 0 and (p.HasField("weight") or p.HasField("bias")):   # deprecated fields
             with torch.no_grad():

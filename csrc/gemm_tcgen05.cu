@@ -814,13 +814,13 @@ extern "C" int bdl_gemm_bf16(const void* A, const void* B, void* D, const float*
                              long long lda, long long ldb, long long ldd, int a_mn, int b_mn, int out_fp32, int flags,
                              int splits, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  GemmParams p{};
+  take_residual(p);   // first: a call that fails validation must not leave the residual armed for the next GEMM
   if (M <= 0 || N <= 0 || K <= 0) return bdl_fail("bdl_gemm_bf16: empty problem");
   if ((flags & BDL_GEMM_ATOMIC_ADD) && !out_fp32) return bdl_fail("bdl_gemm_bf16: ATOMIC_ADD needs fp32 output");
   if ((reinterpret_cast<uintptr_t>(A) & 15u) || (reinterpret_cast<uintptr_t>(B) & 15u) || (lda % 8) || (ldb % 8))
     return bdl_fail("bdl_gemm_bf16: A/B must be 16-byte aligned with leading dimensions that are multiples of 8");
   const int num_sms = bdl_num_sms();
-  GemmParams p{};
-  take_residual(p);
   if (p.residual && ((flags & BDL_GEMM_ATOMIC_ADD) || out_fp32)) return bdl_fail("bdl_gemm_bf16: residual needs a bf16 output");
   p.M = M;
   p.N = N;
@@ -914,6 +914,8 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
                                    int O, int Ho, int Wo, int kh, int kw, int sh, int sw, int ph, int pw, int dh,
                                    int dw, int out_fp32, int flags, int splits, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  GemmParams p{};
+  take_residual(p);
   if (mode < 0 || mode > 2) return bdl_fail("bdl_conv_igemm_bf16: mode must be 0 (fprop), 1 (dgrad) or 2 (wgrad)");
   if ((reinterpret_cast<uintptr_t>(act) & 15u) || (reinterpret_cast<uintptr_t>(other) & 15u) || (ld_act % 8) ||
       (ld_other % 8))
@@ -924,8 +926,6 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
   const long long Mpix = static_cast<long long>(N) * Ho * Wo;
   if (Mpix >= (1ll << 31)) return bdl_fail("bdl_conv_igemm_bf16: too many output pixels");
   const int taps = kh * kw;
-  GemmParams p{};
-  take_residual(p);
   if (p.residual && (mode != 0 || out_fp32)) return bdl_fail("bdl_conv_igemm_bf16: residual is a forward, bf16-output option");
   p.cv_Ho = Ho; p.cv_Wo = Wo; p.cv_sh = sh; p.cv_sw = sw; p.cv_ph = ph; p.cv_pw = pw; p.cv_dh = dh; p.cv_dw = dw;
   p.cv_kh = kh; p.cv_kw = kw; p.cv_C = C; p.cv_cblocks = (C + 63) / 64; p.cv_flip = (mode == 1); p.cv_nimg = N;
@@ -1060,12 +1060,12 @@ extern "C" int bdl_gemm_fp8(const void* A, const void* B, void* D, const float* 
                             const float* out_qscale, const void* conv_geom, int M, int N, int K, long long lda, long long ldb, long long ldd,
                             int out_fp32, int flags, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  GemmParams p{};
+  take_residual(p);
   if ((reinterpret_cast<uintptr_t>(A) & 15u) || (reinterpret_cast<uintptr_t>(B) & 15u) || (lda % 16) || (ldb % 16))
     return bdl_fail("bdl_gemm_fp8: operands must be 16-byte aligned with pitches that are multiples of 16 bytes");
   if (flags & BDL_GEMM_ATOMIC_ADD) return bdl_fail("bdl_gemm_fp8: inference kernel, no accumulate mode");
   const int num_sms = bdl_num_sms();
-  GemmParams p{};
-  take_residual(p);
   const int* cg = static_cast<const int*>(conv_geom);   // {N,H,W,C,Ho,Wo,kh,kw,sh,sw,ph,pw,dh,dw} or NULL
   int gm = M;
   if (cg) {

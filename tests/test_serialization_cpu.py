@@ -113,3 +113,22 @@ def test_snapshot_and_optim_method_files(tmp_path):
     om2 = OptimMethod.load(str(tmp_path / "optimMethod-LeNet.77"))
     assert om2.state["neval"] == 77 and om2.state["epoch"] == 3 and om2.momentum == 0.9
     assert om2._hist == {}            # history is dropped on save (S/optim/OptimMethod.scala:92-96)
+
+
+def test_load_rejects_unregistered_classes_and_parameter_mismatch(tmp_path):
+    """A model file is data: dotted names outside the registered layer classes must not be imported/instantiated, and a
+    parameter-count mismatch must fail loudly instead of leaving random weights (round-1 advisor findings)."""
+    m = L.Linear(4, 3)
+    path = str(tmp_path / "lin.bigdl")
+    m.saveModule(path, None, True)
+    root = pb.BigDLModule.FromString(open(path, "rb").read())
+    evil = pb.BigDLModule.FromString(root.SerializeToString())
+    evil.moduleType = "subprocess.Popen"
+    open(tmp_path / "evil.bigdl", "wb").write(evil.SerializeToString())
+    with pytest.raises(KeyError):
+        Module.loadModule(str(tmp_path / "evil.bigdl"))
+    short = pb.BigDLModule.FromString(root.SerializeToString())
+    del short.parameters[1:]
+    open(tmp_path / "short.bigdl", "wb").write(short.SerializeToString())
+    with pytest.raises(ValueError, match="parameter tensors"):
+        Module.loadModule(str(tmp_path / "short.bigdl"))

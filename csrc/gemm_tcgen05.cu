@@ -87,8 +87,26 @@ struct GemmParams {
   int dual_m;                // one CTA owns two stacked 128-row tiles (both TMEM accumulator stages), so the B operand
                              // is fetched from L2 once per 256 output rows (bf16 kernels only)
   int cv_aw;                 // channels per gathered atom: 64 (128B swizzle) or, for C <= 32, 32 / 16 (64B / 32B swizzle)
+  int group_m;               // tile rasterisation: > 0 walks the output in bands of group_m m-tiles, m fastest inside a
+                             // band, so the tiles in flight at one time share few A row-blocks AND few B column-blocks
+                             // (L2 working set ~ (group_m + W / group_m) operand panels instead of 1 + tiles_n)
   FastDiv fd_hw, fd_wo, fd_cblocks, fd_kw, fd_c;
 };
+
+__device__ __forceinline__ void decode_tile(const GemmParams& p, int rem, int& m_blk, int& n_blk) {
+  if (p.group_m <= 0) {
+    m_blk = rem / p.tiles_n;
+    n_blk = rem - m_blk * p.tiles_n;
+    return;
+  }
+  const int band = p.group_m * p.tiles_n;
+  const int g = rem / band;
+  const int first_m = g * p.group_m;
+  const int gsize = p.tiles_m - first_m < p.group_m ? p.tiles_m - first_m : p.group_m;
+  const int in = rem - g * band;
+  n_blk = in / gsize;
+  m_blk = first_m + (in - n_blk * gsize);
+}
 
 // kConv: 0 plain GEMM; 1 A operand via im2col TMA (conv fprop, and dgrad when kBMN); 2 B operand via im2col TMA (wgrad)
 // One 16-column chunk of one accumulator row: dequantise / bias / ReLU, then store as fp32 (plain or red.add), bf16 or
@@ -266,7 +284,12 @@ __device__ __forceinline__ void epilogue_pack16(const GemmParams& p, const uint3
 //       per-output-column fp32 scale (activation scale x per-channel weight scale) before bias/ReLU. K-major only.
 // kTmaStore: bf16 outputs leave through shared memory and TMA stores (one 32-row x 128-byte box per warp and 64-column
 //       group) instead of 32-byte per-row stores; the staging area follows the pipeline stages in dynamic smem.
-template <bool kAMN, bool kBMN, int kConv, bool kFp8 = false, bool kDual = false, bool kTmaStore = false>
+// kTwo: CTA-pair variant (launched as 2-CTA clusters): one tcgen05.mma.cta_group::2 covers 256 output rows; each CTA
+//       stages its own 128 rows of A and half of the B tile (no multicast — every CTA fetches its own slice), the leader
+//       (cluster rank 0) issues the MMAs and commits to the barriers of both CTAs, each CTA's epilogue drains its own
+//       128 TMEM rows. Per SM the B bytes from L2 and through shared memory are halved.
+template <bool kAMN, bool kBMN, int kConv, bool kFp8 = false, bool kDual = false, bool kTmaStore = false,
+          bool kTwo = false>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                          const __grid_constant__ CUtensorMap tmD, const GemmParams p) {
@@ -278,8 +301,12 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   __shared__ uint32_t tmem_base_slot;
   __shared__ __align__(16) float epi_cols[2][2][256];   // [accumulator stage][bias | scale][column of the tile]
 
+  static_assert(!kTwo || (!kAMN && kConv != 2), "CTA pairs: A must be K-major, no wgrad");
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = threadIdx.x & 31u;
+  const uint32_t crank = kTwo ? cluster_ctarank() : 0u;   // rank inside the CTA pair; rank 0 leads
+  const int work0 = kTwo ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
+  const int work_step = kTwo ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
   const uint32_t tiles = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t a_bytes = BM * BK * 2 * (kDual ? 2 : 1);
   const uint32_t b_bytes = static_cast<uint32_t>(p.b_rows) * BK * 2;
@@ -292,15 +319,19 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(smem_u32(&tfull_bar[s]), 1);
-      mbar_init(smem_u32(&tempty_bar[s]), 8);
+      mbar_init(smem_u32(&tempty_bar[s]), kTwo ? 16 : 8);   // pair: the leader also collects the peer's 8 warps
     }
     fence_mbar_init();
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
   }
-  if (warp == 1) tmem_alloc<kTmemCols>(smem_u32(&tmem_base_slot));
+  if (warp == 1) {
+    if (kTwo) tmem_alloc_pair<kTmemCols>(smem_u32(&tmem_base_slot));
+    else tmem_alloc<kTmemCols>(smem_u32(&tmem_base_slot));
+  }
   tc_fence_before();
-  __syncthreads();
+  if (kTwo) cluster_sync_all();   // the peer's barriers must be initialised before anything arrives on them remotely
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
 
@@ -315,15 +346,18 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int work = blockIdx.x; work < total_work; work += gridDim.x) {
+      for (int work = work0; work < total_work; work += work_step) {
         const int split = work / tiles_mn;
         const int rem = work - split * tiles_mn;
-        const int m_blk = rem / p.tiles_n;
-        const int n_blk = rem - m_blk * p.tiles_n;
+        int m_blk, n_blk;
+        decode_tile(p, rem, m_blk, n_blk);
         const int kb0 = static_cast<int>((static_cast<long long>(split) * num_kb) / p.splits);
         const int kb1 = static_cast<int>((static_cast<long long>(split + 1) * num_kb) / p.splits);
-        const int m0 = m_blk * BM * (kDual ? 2 : 1);
-        const int n0 = n_blk * p.block_n;
+        // pair: this CTA's 128 rows of the 256-row tile, and its half of the tile's B rows
+        // pair + dual: the pair owns 512 rows as two 256-row MMAs; this CTA stages rows [+128 crank, +128) of each
+        const int m0 = kTwo ? (m_blk * (kDual ? 4 : 2) + static_cast<int>(crank)) * BM : m_blk * BM * (kDual ? 2 : 1);
+        const int m0b = m0 + (kTwo ? 2 * BM : BM);   // first row of this CTA's second stacked half (kDual)
+        const int n0 = n_blk * p.block_n + (kTwo ? static_cast<int>(crank) * (p.block_n >> 1) : 0);
         // implicit-GEMM bookkeeping hoisted out of the k loop
         int cv_img = 0, cv_h = 0, cv_w = 0, cv_r = 0, cv_s = 0, cv_cb = 0;
         int cv_img2 = 0, cv_h2 = 0, cv_w2 = 0;
@@ -340,8 +374,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           cv_h = static_cast<int>(ho) * p.cv_sh - p.cv_ph;
           cv_w = static_cast<int>(wo) * p.cv_sw - p.cv_pw;
           if (kDual) {   // base pixel of the second 128-row half
-            const uint32_t img2 = p.fd_hw.quot(static_cast<uint32_t>(m0 + BM));
-            const uint32_t rem2 = static_cast<uint32_t>(m0 + BM) - img2 * p.fd_hw.div;
+            const uint32_t img2 = p.fd_hw.quot(static_cast<uint32_t>(m0b));
+            const uint32_t rem2 = static_cast<uint32_t>(m0b) - img2 * p.fd_hw.div;
             const uint32_t ho2 = p.fd_wo.quot(rem2);
             cv_img2 = static_cast<int>(img2);
             cv_h2 = static_cast<int>(ho2) * p.cv_sh - p.cv_ph;
@@ -376,7 +410,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         }
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
-          const uint32_t fb = smem_u32(&full_bar[stage]);
+          // pair: both CTAs' bytes are counted on the LEADER's full barrier (it alone waits on it, to issue the MMAs)
+          const uint32_t fb = kTwo ? mapa_shared(smem_u32(&full_bar[stage]), 0u) : smem_u32(&full_bar[stage]);
           const uint32_t sa = tiles + stage * stage_bytes;
           const uint32_t sb = sa + a_bytes;
           const int k0 = kb * KE;
@@ -420,6 +455,28 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                                      static_cast<uint16_t>(sm_off[j] & 0xFFFFu), static_cast<uint16_t>(sm_off[j] >> 16));
                 else
                   tma_load_im2col_4d(sb + j * b_atom, &tmB, fb, 0, -p.cv_pw, -p.cv_ph, p.cv_nimg, 0, 0);
+              }
+            }
+          } else if (kConv == 1 && kTwo) {
+            if (crank == 0) mbar_expect_tx(smem_u32(&full_bar[stage]), 2u * stage_bytes);
+            tma_load_im2col_4d_pair(sa, &tmA, fb, cv_cb * KE, cv_w, cv_h, cv_img, static_cast<uint16_t>(cv_s * p.cv_dw),
+                                    static_cast<uint16_t>(cv_r * p.cv_dh));
+            if (kDual)
+              tma_load_im2col_4d_pair(sa + 16384u, &tmA, fb, cv_cb * KE, cv_w2, cv_h2, cv_img2,
+                                      static_cast<uint16_t>(cv_s * p.cv_dw), static_cast<uint16_t>(cv_r * p.cv_dh));
+            const int tap = cv_r * p.cv_kw + cv_s;
+            if (kBMN) {
+              const int btap = p.cv_flip ? (p.cv_kh - 1 - cv_r) * p.cv_kw + (p.cv_kw - 1 - cv_s) : tap;
+              for (int j = 0; j < p.b_rows / 64; ++j)
+                tma_load_2d_pair(sb + j * 8192u, &tmB, fb, btap * p.N + n0 + 64 * j, cv_cb * 64);
+            } else {
+              tma_load_2d_pair(sb, &tmB, fb, tap * p.cv_C + cv_cb * KE, n0);
+            }
+            if (++cv_cb == p.cv_cblocks) {
+              cv_cb = 0;
+              if (++cv_s == p.cv_kw) {
+                cv_s = 0;
+                ++cv_r;
               }
             }
           } else if (kConv == 1) {
@@ -469,6 +526,15 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                   tma_load_im2col_4d(sb + j * 8192u, &tmB, fb, 0, -p.cv_pw, -p.cv_ph, p.cv_nimg, 0, 0);
               }
             }
+          } else if (kTwo) {
+            if (crank == 0) mbar_expect_tx(smem_u32(&full_bar[stage]), 2u * stage_bytes);
+            tma_load_2d_pair(sa, &tmA, fb, k0, m0);
+            if (kDual) tma_load_2d_pair(sa + 16384u, &tmA, fb, k0, m0b);
+            if (kBMN) {
+              for (int j = 0; j < p.b_rows / 64; ++j) tma_load_2d_pair(sb + j * 8192u, &tmB, fb, n0 + 64 * j, k0);
+            } else {
+              tma_load_2d_pair(sb, &tmB, fb, k0, n0);
+            }
           } else {
           mbar_expect_tx(fb, stage_bytes);
           if (kAMN) {
@@ -498,22 +564,26 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    if (lane == 0 && crank == 0) {
       // instruction descriptor: c=f32 [4,6), a=bf16 [7,10), b=bf16 [10,13), a_major 15, b_major 16, N>>3 [17,23), M>>4 [24,29)
       // fp8: a/b format 0 = E4M3; bf16: format 1
       const uint32_t idesc = (1u << 4) | (kFp8 ? 0u : ((1u << 7) | (1u << 10))) | (static_cast<uint32_t>(kAMN) << 15) |
                              (static_cast<uint32_t>(kBMN) << 16) | (static_cast<uint32_t>(p.block_n >> 3) << 17) |
-                             (static_cast<uint32_t>(BM >> 4) << 24);
+                             (static_cast<uint32_t>((kTwo ? 2 * BM : BM) >> 4) << 24);
       int stage = 0;
       uint32_t phase = 0;
       uint32_t acc = 0, acc_phase = 0;
-      for (int work = blockIdx.x; work < total_work; work += gridDim.x) {
+      for (int work = work0; work < total_work; work += work_step) {
         const int split = work / tiles_mn;
         const int kb0 = static_cast<int>((static_cast<long long>(split) * num_kb) / p.splits);
         const int kb1 = static_cast<int>((static_cast<long long>(split + 1) * num_kb) / p.splits);
         constexpr bool dual = kDual;
-        mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1u);
-        if (dual) mbar_wait(smem_u32(&tempty_bar[1]), acc_phase ^ 1u);   // dual: acc is always 0, both stages are ours
+        if (kTwo) mbar_wait_cluster(smem_u32(&tempty_bar[acc]), acc_phase ^ 1u);
+        else mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1u);
+        if (dual) {   // dual: acc is always 0, both stages are ours
+          if (kTwo) mbar_wait_cluster(smem_u32(&tempty_bar[1]), acc_phase ^ 1u);
+          else mbar_wait(smem_u32(&tempty_bar[1]), acc_phase ^ 1u);
+        }
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * kAccStride;
         for (int kb = kb0; kb < kb1; ++kb) {
@@ -550,26 +620,33 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                                         : make_smem_desc_sw128(sa + k * 32u, 16u, 1024u);
             const uint64_t bdesc = kBMN ? make_smem_desc_sw128(sb + k * 2048u, 8192u, 1024u)
                                         : make_smem_desc_sw128(sb + k * 32u, 16u, 1024u);
-            if (kFp8)
+            if (kTwo) {
+              if (kFp8) umma_f8_pair(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+              else umma_f16_pair(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            } else if (kFp8)
               umma_f8(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
             else
               umma_f16(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-            if (dual)
-              umma_f16(d_tmem + kAccStride,
-                       kAMN ? make_smem_desc_sw128(sa + 16384u + k * 2048u, 8192u, 1024u)
-                            : make_smem_desc_sw128(sa + 16384u + k * 32u, 16u, 1024u),
-                       bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            if (dual) {
+              const uint64_t adesc2 = kAMN ? make_smem_desc_sw128(sa + 16384u + k * 2048u, 8192u, 1024u)
+                                           : make_smem_desc_sw128(sa + 16384u + k * 32u, 16u, 1024u);
+              if (kTwo) umma_f16_pair(d_tmem + kAccStride, adesc2, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+              else umma_f16(d_tmem + kAccStride, adesc2, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            }
           }
           }
-          umma_commit(smem_u32(&empty_bar[stage]));
+          if (kTwo) umma_commit_pair(smem_u32(&empty_bar[stage]));
+          else umma_commit(smem_u32(&empty_bar[stage]));
           if (++stage == p.num_stages) {
             stage = 0;
             phase ^= 1u;
           }
         }
-        umma_commit(smem_u32(&tfull_bar[acc]));
+        if (kTwo) umma_commit_pair(smem_u32(&tfull_bar[acc]));
+        else umma_commit(smem_u32(&tfull_bar[acc]));
         if (dual) {
-          umma_commit(smem_u32(&tfull_bar[1]));
+          if (kTwo) umma_commit_pair(smem_u32(&tfull_bar[1]));
+          else umma_commit(smem_u32(&tfull_bar[1]));
           acc_phase ^= 1u;
         } else {
           acc ^= 1u;
@@ -587,14 +664,19 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     const bool has_bias = (p.flags & BDL_GEMM_BIAS) != 0;
     const bool atomic = (p.flags & BDL_GEMM_ATOMIC_ADD) != 0;
     const bool use_scale = kFp8 && p.col_scale != nullptr;
-    for (int work = blockIdx.x; work < total_work; work += gridDim.x) {
+    // pair: TMEM drained -> arrive on the LEADER's barrier (remote for the peer CTA)
+    const uint32_t tempty_addr[2] = {kTwo ? mapa_shared(smem_u32(&tempty_bar[0]), 0u) : smem_u32(&tempty_bar[0]),
+                                     kTwo ? mapa_shared(smem_u32(&tempty_bar[1]), 0u) : smem_u32(&tempty_bar[1])};
+    for (int work = work0; work < total_work; work += work_step) {
       const int split = work / tiles_mn;
       const int rem = work - split * tiles_mn;
-      const int m_blk = rem / p.tiles_n;
-      const int n_blk = rem - m_blk * p.tiles_n;
+      int m_blk, n_blk;
+      decode_tile(p, rem, m_blk, n_blk);
       const int nhalves = kDual ? 2 : 1;   // dual: accumulator stage h holds rows [256 m_blk + 128 h, +128)
       for (int hm = 0; hm < nhalves; ++hm) {
-      const int row = (m_blk * nhalves + hm) * BM + static_cast<int>(quad * 32u + lane);
+      const int tile_row0 = kTwo ? (m_blk * 2 * nhalves + hm * 2 + static_cast<int>(crank)) * BM
+                                 : (m_blk * nhalves + hm) * BM;
+      const int row = tile_row0 + static_cast<int>(quad * 32u + lane);
       const int nbase = n_blk * p.block_n;
       // Stage this tile's bias / dequantisation columns in shared memory while the MMAs are still running: reading
       // them with __ldg inside the column loop put a long-scoreboard stall on every 16-column chunk.
@@ -615,7 +697,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       if (kTmaStore) {
         // this warp's staging box: 32 rows x 128 bytes, 16-byte chunks XOR-swizzled by (row & 7) like the tensor map
         const uint32_t stg = tiles + static_cast<uint32_t>(p.num_stages) * stage_bytes + (warp - 2u) * 4096u;
-        const int row0 = (m_blk * nhalves + hm) * BM + static_cast<int>(quad * 32u);
+        const int row0 = tile_row0 + static_cast<int>(quad * 32u);
         const int g_split = ((p.block_n + 127) / 128) * 64;
         const int g_begin = half ? g_split : 0;
         const int g_end = half ? ((p.block_n + 63) / 64) * 64 : g_split;
@@ -664,7 +746,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
+        if (lane == 0) {
+          if (kTwo) mbar_arrive_cluster(tempty_addr[acc]);
+          else mbar_arrive(smem_u32(&tempty_bar[acc]));
+        }
         acc ^= 1u;
         if (acc == 0) acc_phase ^= 1u;
         continue;
@@ -724,7 +809,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
 #undef EPI_STORE
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
+      if (lane == 0) {
+        if (kTwo) mbar_arrive_cluster(tempty_addr[acc]);
+        else mbar_arrive(smem_u32(&tempty_bar[acc]));
+      }
       acc ^= 1u;
       if (acc == 0) acc_phase ^= 1u;
       }
@@ -733,8 +821,12 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
 
   if (kTmaStore && warp >= 2 && lane == 0) tma_store_wait0();   // shared memory must outlive the bulk stores
   tc_fence_before();
-  __syncthreads();
-  if (warp == 1) tmem_dealloc<kTmemCols>(tmem_base);
+  if (kTwo) cluster_sync_all();   // neither CTA may leave while the other can still signal it or read its operands
+  else __syncthreads();
+  if (warp == 1) {
+    if (kTwo) tmem_dealloc_pair<kTmemCols>(tmem_base);
+    else tmem_dealloc<kTmemCols>(tmem_base);
+  }
 }
 
 // ------------------------------------------------------------------------------------------- host
@@ -766,6 +858,76 @@ static bool want_dual_m(int M, long long tiles_n, int num_kb, int num_sms, bool 
   const long long tiles = static_cast<long long>((M + 2 * BM - 1) / (2 * BM)) * tiles_n;
   const long long max_splits = num_kb / 4 > 0 ? num_kb / 4 : 1;
   return tiles * max_splits >= num_sms;
+}
+
+// CTA-pair tiles (256 rows x block_n per 2-SM cluster) whenever they need no more waves than 128-row tiles do: the MMA
+// rate per SM is the same, the B operand bytes per SM are halved. BDL_GEMM_TWO=0 disables, =1 forces (when legal).
+static int g_pair_mode = [] { const char* e = getenv("BDL_GEMM_TWO"); return e ? atoi(e) : -1; }();
+// Measured (profiles/gemm_pair_r2.md): pairs pay off where the B panel is re-fetched by many m tiles and the reduction is
+// long — big Linear-style GEMMs (8192^3: 1.18 -> 1.53 PFLOP/s) and 512-channel 3x3 convolutions (+5..9 %); on short
+// reductions and narrow outputs (the early, bandwidth-bound conv layers) the 1-CTA kernel with stacked tiles and the
+// TMA-store epilogue is faster, so the default thresholds are conservative. `conv`: implicit-GEMM call.
+static bool want_two(int M, int block_n, int tiles_n, bool b_mn, int num_sms, int num_kb, bool conv = false) {
+  const int mode = g_pair_mode;
+  if (mode == 0 || M <= BM) return false;
+  if (b_mn ? (block_n % 128) != 0 : (block_n % 32) != 0) return false;
+  if (mode == 1) return true;
+  static const int min_kb = [] { const char* e = getenv("BDL_GEMM_TWO_MIN_KB"); return e ? atoi(e) : 16; }();
+  static const int min_kb_conv = [] { const char* e = getenv("BDL_CONV_TWO_MIN_KB"); return e ? atoi(e) : 64; }();
+  if (num_kb < (conv ? min_kb_conv : min_kb)) return false;
+  if (conv ? block_n < 256 : tiles_n < 2) return false;
+  const long long t1 = static_cast<long long>((M + BM - 1) / BM) * tiles_n;
+  const long long t2 = static_cast<long long>((M + 2 * BM - 1) / (2 * BM)) * tiles_n;
+  const long long w1 = (t1 + num_sms - 1) / num_sms, w2 = (t2 + num_sms / 2 - 1) / (num_sms / 2);
+  // wave efficiency of the pair tiling must not fall below the 1-CTA tiling's
+  return static_cast<double>(t2) / (w2 * (num_sms / 2)) + 1e-9 >= static_cast<double>(t1) / (w1 * num_sms) - 0.05;
+}
+
+// 512-row pair tiles (two stacked 256-row MMAs, all 512 TMEM columns): fewest operand bytes per MAC from L2 (the fabric,
+// not the tensor pipe, bounds large GEMMs), at the price of an epilogue that no longer overlaps the next main loop —
+// so only for long reductions with enough tiles to keep every pair busy.
+static bool want_pair_dual(int M, int tiles_n, int num_kb, int num_sms) {
+  static const int min_kb = [] { const char* e = getenv("BDL_GEMM_PAIR_DUAL_KB"); return e ? atoi(e) : 32; }();
+  if (min_kb <= 0 || num_kb < min_kb) return false;
+  const long long t4 = static_cast<long long>((M + 4 * BM - 1) / (4 * BM)) * tiles_n;
+  const long long slots = num_sms / 2, w4 = (t4 + slots - 1) / slots;
+  return t4 >= slots && static_cast<double>(t4) / (w4 * slots) >= 0.85;   // full waves only: the tile is 512 x block_n
+}
+
+template <bool AMN, bool BMN, int CV, bool FP8, bool TMAOUT, bool DUAL = false>
+static auto pair_kernel() {
+  if constexpr (!AMN && CV != 2)
+    return &gemm_bf16_tcgen05_kernel<AMN, BMN, CV, FP8, DUAL, TMAOUT, true>;
+  else
+    return &gemm_bf16_tcgen05_kernel<AMN, BMN, CV, FP8, false, TMAOUT, false>;
+}
+
+// One launch path for both forms: plain grid, or 2-CTA clusters for the pair kernels.
+using GemmKernel = void (*)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const GemmParams);
+static int launch_gemm_kernel(GemmKernel kfn, long long total_work, int num_sms, size_t smem, cudaStream_t stream,
+                              bool two, const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmD,
+                              const GemmParams& p, const char* what) {
+  cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemBudget + 1024));
+  if (e != cudaSuccess) return bdl_fail_cuda("cudaFuncSetAttribute(gemm)", e);
+  cudaLaunchConfig_t cfg{};
+  const long long slots = two ? num_sms / 2 : num_sms;
+  const int units = static_cast<int>(total_work < slots ? total_work : slots);
+  cfg.gridDim = dim3(two ? 2 * units : units);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  if (two) {
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+  }
+  e = cudaLaunchKernelEx(&cfg, kfn, tmA, tmB, tmD, p);
+  if (e != cudaSuccess) return bdl_fail_cuda(what, e);
+  return bdl_check_launch(what);
 }
 
 static int pick_block_n(int M, int N, int num_sms, bool split_k = false) {
@@ -834,6 +996,17 @@ extern "C" int bdl_gemm_bf16(const void* A, const void* B, void* D, const float*
     p.dual_m = 1;
     p.tiles_m = (M + 2 * BM - 1) / (2 * BM);
   }
+  const bool two = !a_mn && !p.dual_m && !(flags & BDL_GEMM_ATOMIC_ADD) && splits <= 1 &&
+                   want_two(M, p.block_n, p.tiles_n, b_mn != 0, num_sms, num_kb);
+  if (two) {
+    p.tiles_m = (M + 2 * BM - 1) / (2 * BM);
+    p.b_rows = p.block_n / 2;      // each CTA of the pair stages half of the tile's B rows
+    if (want_pair_dual(M, p.tiles_n, num_kb, num_sms)) {
+      p.dual_m = 1;                // 512 x block_n per pair: A 32 KB + B 16 KB per k block for twice the MACs
+      p.tiles_m = (M + 4 * BM - 1) / (4 * BM);
+    }
+  }
+  if (p.tiles_n > 1 && p.tiles_m > 1) p.group_m = 8;
   const long long tiles_mn = static_cast<long long>(p.tiles_m) * p.tiles_n;
   if (splits <= 0) {
     splits = 1;
@@ -852,7 +1025,8 @@ extern "C" int bdl_gemm_bf16(const void* A, const void* B, void* D, const float*
   p.D = D;
   p.bias = bias;
   const size_t stage_bytes = static_cast<size_t>(BM) * BK * 2 * (p.dual_m ? 2 : 1) + static_cast<size_t>(p.b_rows) * BK * 2;
-  const bool tma_out = want_tma_store(D, ldd, out_fp32, flags, a_mn != 0, num_kb);
+  // 512-row pair tiles spend the staging area on a fourth pipeline stage instead (their epilogue is a small share)
+  const bool tma_out = !(two && p.dual_m) && want_tma_store(D, ldd, out_fp32, flags, a_mn != 0, num_kb);
   const size_t budget = kSmemBudget - (tma_out ? kStageOutBytes : 0);
   int stages = static_cast<int>(budget / stage_bytes);
   if (stages > kMaxStages) stages = kMaxStages;
@@ -875,30 +1049,29 @@ extern "C" int bdl_gemm_bf16(const void* A, const void* B, void* D, const float*
   if (b_mn)
     rc = bdl_make_tmap_2d_bf16(&tmB, B, static_cast<uint64_t>(N), static_cast<uint64_t>(K), ldb, 64, 64);
   else
-    rc = bdl_make_tmap_2d_bf16(&tmB, B, static_cast<uint64_t>(K), static_cast<uint64_t>(N), ldb, 64, p.block_n);
+    rc = bdl_make_tmap_2d_bf16(&tmB, B, static_cast<uint64_t>(K), static_cast<uint64_t>(N), ldb, 64,
+                               two ? p.block_n / 2 : p.block_n);
   if (rc) return rc;
 
   const long long total = tiles_mn * splits;
-  const int grid = static_cast<int>(total < num_sms ? total : num_sms);
-#define BDL_LAUNCH_GEMM(AMN, BMN)                                                                                 \
-  do {                                                                                                            \
-    auto kfn = p.dual_m ? gemm_bf16_tcgen05_kernel<AMN, BMN, 0, false, true, false>                                  \
-               : (tma_out && !(AMN)) ? gemm_bf16_tcgen05_kernel<AMN, BMN, 0, false, false, !(AMN)>                   \
-                                     : gemm_bf16_tcgen05_kernel<AMN, BMN, 0, false, false, false>;                   \
-    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemBudget + 1024));     \
-    if (e != cudaSuccess) return bdl_fail_cuda("cudaFuncSetAttribute(gemm)", e);                                  \
-    kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, tmD, p);                                                  \
-  } while (0)
+  GemmKernel kfn;
+#define BDL_PICK_GEMM(AMN, BMN)                                                                                   \
+  kfn = two ? (p.dual_m ? (tma_out ? pair_kernel<AMN, BMN, 0, false, !(AMN), true>()                              \
+                                   : pair_kernel<AMN, BMN, 0, false, false, true>())                               \
+                        : (tma_out ? pair_kernel<AMN, BMN, 0, false, !(AMN)>() : pair_kernel<AMN, BMN, 0, false, false>())) \
+        : p.dual_m ? gemm_bf16_tcgen05_kernel<AMN, BMN, 0, false, true, false>                                    \
+        : (tma_out && !(AMN)) ? gemm_bf16_tcgen05_kernel<AMN, BMN, 0, false, false, !(AMN)>                       \
+                              : gemm_bf16_tcgen05_kernel<AMN, BMN, 0, false, false, false>
   if (a_mn && b_mn)
-    BDL_LAUNCH_GEMM(true, true);
+    BDL_PICK_GEMM(true, true);
   else if (a_mn)
-    BDL_LAUNCH_GEMM(true, false);
+    BDL_PICK_GEMM(true, false);
   else if (b_mn)
-    BDL_LAUNCH_GEMM(false, true);
+    BDL_PICK_GEMM(false, true);
   else
-    BDL_LAUNCH_GEMM(false, false);
-#undef BDL_LAUNCH_GEMM
-  return bdl_check_launch("gemm_bf16_tcgen05_kernel");
+    BDL_PICK_GEMM(false, false);
+#undef BDL_PICK_GEMM
+  return launch_gemm_kernel(kfn, total, num_sms, smem, stream, two, tmA, tmB, tmD, p, "gemm_bf16_tcgen05_kernel");
 }
 
 
@@ -977,6 +1150,20 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
       p.tiles_m = (gm + 2 * BM - 1) / (2 * BM);
     }
   }
+  // fprop / dgrad on CTA pairs (256 pixels x block_n per 2-SM cluster, half of the weight tile per CTA) replace the
+  // stacked-tile form wherever the pair tiling is legal
+  const bool two = mode != 2 && aw == 64 && !(flags & BDL_GEMM_ATOMIC_ADD) && splits <= 1 &&
+                   want_two(gm, p.block_n, p.tiles_n, b_mn, num_sms, p.cv_num_kb, true);
+  if (two) {
+    p.dual_m = 0;
+    p.tiles_m = (gm + 2 * BM - 1) / (2 * BM);
+    p.b_rows = p.block_n / 2;
+    if (want_pair_dual(gm, p.tiles_n, p.cv_num_kb, num_sms)) {
+      p.dual_m = 1;
+      p.tiles_m = (gm + 4 * BM - 1) / (4 * BM);
+    }
+  }
+  if (p.tiles_n > 1 && p.tiles_m > 1) p.group_m = 8;
   const long long tiles_mn = static_cast<long long>(p.tiles_m) * p.tiles_n;
   if (splits <= 0) {
     splits = 1;
@@ -995,7 +1182,7 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
   p.D = D;
   p.bias = bias;
   const size_t stage_bytes = static_cast<size_t>(BM) * BK * 2 * (p.dual_m ? 2 : 1) + static_cast<size_t>(p.b_rows) * BK * 2;
-  const bool tma_out = want_tma_store(D, ldd, out_fp32, flags, mode == 2, p.cv_num_kb);
+  const bool tma_out = !(two && p.dual_m) && want_tma_store(D, ldd, out_fp32, flags, mode == 2, p.cv_num_kb);
   const size_t budget = kSmemBudget - (tma_out ? kStageOutBytes : 0);
   int stages = static_cast<int>(budget / stage_bytes);
   if (stages > kMaxStages) stages = kMaxStages;
@@ -1022,32 +1209,30 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
     if (rc) return rc;
     if (mode == 0)
       rc = bdl_make_tmap_2d_bf16_sw(&tmB, other, static_cast<uint64_t>(taps) * C, static_cast<uint64_t>(O), ld_other,
-                                    aw, p.block_n, aw * 2);
+                                    aw, two ? p.block_n / 2 : p.block_n, aw * 2);
     else  // weights [Cact rows, taps*O cols]
       rc = bdl_make_tmap_2d_bf16(&tmB, other, static_cast<uint64_t>(taps) * O, static_cast<uint64_t>(C), ld_other, 64,
                                  64);
     if (rc) return rc;
   }
   const long long total = tiles_mn * splits;
-  const int grid = static_cast<int>(total < num_sms ? total : num_sms);
-#define BDL_LAUNCH_CONV(AMN, BMN, CV)                                                                             \
-  do {                                                                                                            \
-    auto kfn = p.dual_m ? (tma_out && !(AMN) ? gemm_bf16_tcgen05_kernel<AMN, BMN, CV, false, true, !(AMN)>        \
-                                             : gemm_bf16_tcgen05_kernel<AMN, BMN, CV, false, true, false>)        \
-                        : (tma_out && !(AMN) ? gemm_bf16_tcgen05_kernel<AMN, BMN, CV, false, false, !(AMN)>       \
-                                             : gemm_bf16_tcgen05_kernel<AMN, BMN, CV, false, false, false>);      \
-    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemBudget + 1024));     \
-    if (e != cudaSuccess) return bdl_fail_cuda("cudaFuncSetAttribute(conv gemm)", e);                             \
-    kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, tmD, p);                                                  \
-  } while (0)
+  GemmKernel kfn;
+#define BDL_PICK_CONV(AMN, BMN, CV)                                                                               \
+  kfn = two ? (p.dual_m ? (tma_out ? pair_kernel<AMN, BMN, CV, false, !(AMN), true>()                             \
+                                   : pair_kernel<AMN, BMN, CV, false, false, true>())                              \
+                        : (tma_out ? pair_kernel<AMN, BMN, CV, false, !(AMN)>() : pair_kernel<AMN, BMN, CV, false, false>())) \
+        : p.dual_m ? (tma_out && !(AMN) ? gemm_bf16_tcgen05_kernel<AMN, BMN, CV, false, true, !(AMN)>             \
+                                        : gemm_bf16_tcgen05_kernel<AMN, BMN, CV, false, true, false>)             \
+                   : (tma_out && !(AMN) ? gemm_bf16_tcgen05_kernel<AMN, BMN, CV, false, false, !(AMN)>            \
+                                        : gemm_bf16_tcgen05_kernel<AMN, BMN, CV, false, false, false>)
   if (mode == 0)
-    BDL_LAUNCH_CONV(false, false, 1);
+    BDL_PICK_CONV(false, false, 1);
   else if (mode == 1)
-    BDL_LAUNCH_CONV(false, true, 1);
+    BDL_PICK_CONV(false, true, 1);
   else
-    BDL_LAUNCH_CONV(true, true, 2);
-#undef BDL_LAUNCH_CONV
-  return bdl_check_launch("gemm_bf16_tcgen05_kernel<conv>");
+    BDL_PICK_CONV(true, true, 2);
+#undef BDL_PICK_CONV
+  return launch_gemm_kernel(kfn, total, num_sms, smem, stream, two, tmA, tmB, tmD, p, "gemm_bf16_tcgen05_kernel<conv>");
 }
 
 
@@ -1140,6 +1325,13 @@ extern "C" int bdl_gemm_fp8(const void* A, const void* B, void* D, const float* 
     kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, tma_out ? tmD : tmA, p);
   }
   return bdl_check_launch("gemm_tcgen05_kernel<fp8>");
+}
+
+// -1: CTA-pair tiles where the heuristic wants them (default), 0: never, 1: wherever they are legal. Returns the old mode.
+extern "C" int bdl_gemm_set_pair_mode(int mode) {
+  const int old = g_pair_mode;
+  g_pair_mode = mode < 0 ? -1 : (mode > 0 ? 1 : 0);
+  return old;
 }
 
 extern "C" int bdl_gemm_set_residual(const void* residual_bf16, long long ld) {

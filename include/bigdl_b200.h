@@ -36,6 +36,11 @@ int bdl_stream_capture_status(void* stream);
  * thread: D = act(A*B + bias + residual), residual bf16 [M,N] with row pitch ld (elements). Cleared by that launch.
  * Reference: the conv + sum post-op of S/nn/mkldnn/Fusion.scala (fusionCAddTable). */
 int bdl_gemm_set_residual(const void* residual_bf16, long long ld);
+/* CTA-pair tiles (tcgen05.mma.cta_group::2 on 2-CTA clusters: 256 rows per MMA, half of the B tile per SM) for GEMM,
+ * conv fprop and dgrad: -1 = where the wave heuristic wants them (default; env BDL_GEMM_TWO), 0 = never, 1 = wherever
+ * legal. Process-wide; returns the previous mode. Reference: the same S/nn/Linear.scala:78-167 /
+ * S/nn/SpatialConvolution.scala:253-521 GEMMs as bdl_gemm_bf16. */
+int bdl_gemm_set_pair_mode(int mode);
 int bdl_gemm_bf16(const void* A, const void* B, void* D, const float* bias, int M, int N, int K, long long lda,
                   long long ldb, long long ldd, int a_mn, int b_mn, int out_fp32, int flags, int splits, void* stream);
 /* Implicit-GEMM convolution on the same kernel: the gathered operand is fetched from the NHWC activation tensor by

@@ -99,3 +99,48 @@ def test_linear_fn_output_size_not_multiple_of_8():
     gwr = [p.grad for p in ref.torch_parameters()]
     for a, b in zip(gw, gwr):
         assert torch.allclose(a.float().cpu(), b, atol=0.15, rtol=5e-2)
+
+
+@pytest.fixture
+def pair_mode():
+    """Force (1) or forbid (0) the CTA-pair kernels for one test, restoring the heuristic afterwards."""
+    from bigdl_b200.ops import _lib
+    lib = _lib.cuda_lib()
+    old = []
+
+    def set_mode(m):
+        old.append(lib.bdl_gemm_set_pair_mode(m))
+
+    yield set_mode
+    if old:
+        lib.bdl_gemm_set_pair_mode(old[0])
+
+
+@pytest.mark.parametrize("b_mn", [False, True])
+@pytest.mark.parametrize("M,N,K", [(256, 256, 64), (300, 128, 200), (1024, 512, 1024), (2048, 96, 320), (8192, 384, 512),
+                                   (4096, 1000, 256),
+                                   (16384, 768, 1024), (19000, 520, 1032)])   # 512-row pair tiles + banded tile order
+def test_gemm_cta_pair_matches_single_cta_and_fp32(pair_mode, b_mn, M, N, K):
+    """cta_group::2 kernels (forced) vs the fp32 reference and vs the 1-CTA kernel: bf16 and fp32 outputs, bias + ReLU,
+    ragged M / N / K, both B majors."""
+    from bigdl_b200.ops.gemm import gemm_bf16
+    torch.manual_seed(3)
+    ldn = (N + 7) // 8 * 8
+    a = torch.randn(M, (K + 7) // 8 * 8, device="cuda").bfloat16()[:, :K]
+    b = torch.randn(K, ldn, device="cuda").bfloat16()[:, :N] if b_mn else torch.randn(N, (K + 7) // 8 * 8, device="cuda").bfloat16()[:, :K]
+    bias = torch.randn(N, device="cuda")
+    ref = a.float() @ (b.float() if b_mn else b.float().t())
+    outs = {}
+    for mode in (1, 0):
+        pair_mode(mode)
+        o32 = gemm_bf16(a, b, b_mn=b_mn, out_dtype=torch.float32)
+        o16 = torch.zeros(M, ldn, device="cuda", dtype=torch.bfloat16)
+        gemm_bf16(a, b, b_mn=b_mn, bias=bias, relu=True, out=o16[:, :N])
+        torch.cuda.synchronize()
+        outs[mode] = (o32, o16)
+        err = (o32 - ref).abs().max().item()
+        assert err <= 2e-3 * ref.abs().max().item() + 1e-3, (mode, err)
+        assert torch.allclose(o16[:, :N].float(), torch.relu(ref + bias), rtol=2e-2, atol=2e-1), mode
+        assert o16[:, N:].abs().max().item() == 0 if ldn > N else True
+    # same accumulation order per output element in both kernels -> identical results
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])

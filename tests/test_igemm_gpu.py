@@ -136,3 +136,54 @@ def test_stem_space_to_depth_conv(shape, fp32_in):
                 f"{name}/{what}: max err {err.max().item():.4g}, ref max {b.abs().max().item():.4g}"
     if shape[0] == 4:
         assert plan is not None
+
+
+PAIR_CASES = [
+    (8, 64, 16, 16, 128, 3, 3, 1, 1, 1, 1, 1, 1),
+    (4, 128, 14, 14, 256, 1, 1, 1, 1, 0, 0, 1, 1),
+    (5, 96, 12, 12, 64, 3, 3, 1, 1, 1, 1, 1, 1),      # C tail inside a 64-channel block, ragged last 256-pixel tile
+    (4, 64, 15, 15, 128, 3, 3, 2, 2, 1, 1, 1, 1),     # strided traversal
+    (3, 192, 17, 17, 320, 3, 3, 1, 1, 1, 1, 1, 1),    # two n tiles (block_n 192 + 128 or 256 + 64 depending on waves)
+    (64, 128, 28, 28, 256, 3, 3, 1, 1, 1, 1, 1, 1),   # long reduction, many tiles: 512-pixel pair tiles (two stacked MMAs)
+]
+
+
+@pytest.mark.parametrize("case", PAIR_CASES)
+def test_igemm_cta_pair_fprop_dgrad(case):
+    """Implicit-GEMM fprop and (stride-1) dgrad on the cta_group::2 kernels (forced) vs fp32 conv2d and vs the 1-CTA
+    kernels."""
+    from bigdl_b200.ops import _lib
+    from bigdl_b200.ops.gemm import conv_igemm
+    N, C, H, W, O, kh, kw, sh, sw, ph, pw, dh, dw = case
+    lib = _lib.cuda_lib()
+    torch.manual_seed(5)
+    x = torch.randn(N, H, W, C, device="cuda").bfloat16()
+    w = (torch.randn(O, kh, kw, C, device="cuda") * 0.1).bfloat16()
+    b = torch.randn(O, device="cuda")
+    Ho = (H + 2 * ph - dh * (kh - 1) - 1) // sh + 1
+    Wo = (W + 2 * pw - dw * (kw - 1) - 1) // sw + 1
+    ref = F.relu(F.conv2d(x.float().permute(0, 3, 1, 2), w.float().permute(0, 3, 1, 2), b, (sh, sw), (ph, pw), (dh, dw)))
+    old = lib.bdl_gemm_set_pair_mode(1)
+    try:
+        got = {}
+        for mode in (1, 0):
+            lib.bdl_gemm_set_pair_mode(mode)
+            y = torch.empty(N * Ho * Wo, O, device="cuda", dtype=torch.bfloat16)
+            conv_igemm(0, x, C, w.reshape(O, -1), y, O, Ho, Wo, kh, kw, sh, sw, ph, pw, dh, dw, bias=b, relu=True)
+            torch.cuda.synchronize()
+            _close(y.reshape(N, Ho, Wo, O).permute(0, 3, 1, 2), ref, 2e-2, 3e-2)
+            got[mode] = y
+        assert torch.equal(got[0], got[1])
+        if sh == 1 and sw == 1:
+            dy = torch.randn(N, Ho, Wo, O, device="cuda").bfloat16()
+            xr = x.float().permute(0, 3, 1, 2).requires_grad_(True)
+            F.conv2d(xr, w.float().permute(0, 3, 1, 2), None, 1, (ph, pw), (dh, dw)).backward(dy.float().permute(0, 3, 1, 2))
+            for mode in (1, 0):
+                lib.bdl_gemm_set_pair_mode(mode)
+                dx = torch.empty(N * H * W, C, device="cuda", dtype=torch.bfloat16)
+                conv_igemm(1, dy, O, w.reshape(O, -1), dx, C, H, W, kh, kw, 1, 1, dh * (kh - 1) - ph, dw * (kw - 1) - pw,
+                           dh, dw)
+                torch.cuda.synchronize()
+                _close(dx.reshape(N, H, W, C).permute(0, 3, 1, 2), xr.grad, 3e-2, 6e-2)
+    finally:
+        lib.bdl_gemm_set_pair_mode(old)

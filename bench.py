@@ -39,6 +39,7 @@ def parse():
     ap.add_argument("--batch", type=int, default=128, help="per-GPU batch (the reference perf harness default)")
     ap.add_argument("--backend", default=None, help="parameter backend override: p2p | nccl")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--set", action="append", help="config override key=value (repeatable)")
     ap.add_argument("--no-graph", action="store_true", help="issue every kernel eagerly instead of replaying a CUDA graph")
     return ap.parse_args()
 
@@ -144,6 +145,10 @@ def run_ours(args):
     Engine.init()
     if args.backend:
         config.set("bigdl.parameter.backend", args.backend)
+    for kv in args.set or []:                  # e.g. --set bigdl.parameter.p2p=monolithic (A/B runs)
+        k, v = kv.split("=", 1)
+        like = config._DEFAULTS.get(k)
+        config.set(k, config._coerce(v, like) if like is not None else v)
     RNG.setSeed(1234)          # same initial weights on every rank (the reference broadcasts the model)
     torch.manual_seed(1234 + rank)
     B, K, W = args.batch, args.steps, args.warmup
@@ -153,7 +158,7 @@ def run_ours(args):
     model.training()
     weights, grads = model.getParameters()
     flat = model._flat
-    sync = AllReduceParameter(flat, backend=None if world > 1 else "local").init()
+    sync = AllReduceParameter(flat, backend=None if world > 1 else "local", root=model).init()
     om = make_optim(K + W)
 
     x = torch.randn(B, 3, 224, 224, device=dev)

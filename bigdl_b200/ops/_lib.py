@@ -110,6 +110,10 @@ _SIGNATURES = {
                             _P],
     "bdl_dropout_fwd_bf16_ctr": [_P, _P, _P, _Z, _F, _U64, _P, _P],
     "bdl_counter_add": [_P, _U64, _P],
+    "bdl_bucket_rs_update": [_P, _P, _P, _I, _I, _L, _L, _L, _L, _P, _P, _P, _P, _P, _I, _P, _P, _I, ctypes.c_uint,
+                             ctypes.c_uint, _P, _L, _P, _P, _P, _L, _L, _I, _P],
+    "bdl_pull_gather": [_P, _P, _I, _I, _P, _I, ctypes.c_uint, ctypes.c_uint, _I, _P, _L, _I, _P],
+    "bdl_peer_clip_scale": [_P, _P, _I, _I, ctypes.c_uint, ctypes.c_uint, _P, _L, _P, _F, _P, _P, _P],
     "bdl_ipc_alloc": [_Z, _P, _P],
     "bdl_ipc_open": [_P, _P],
     "bdl_ipc_close": [_P],

@@ -26,8 +26,11 @@ _RING = 8
 
 class GraphedTrainStep:
     def __init__(self, model, criterion, sync, optim_method, example_input: torch.Tensor, example_target: torch.Tensor,
-                 world: int = 1, warmup_iters: int = 3):
-        self.model, self.criterion, self.sync, self.om, self.world = model, criterion, sync, optim_method, world
+                 world: int = 1, warmup_iters: int = 3, l2_clip: float | None = None):
+        # one OptimMethod, or the per-submodule list in the order of ``sync.method_ranges``
+        self.oms = list(optim_method) if isinstance(optim_method, (list, tuple)) else [optim_method]
+        self.model, self.criterion, self.sync, self.om, self.world = model, criterion, sync, self.oms[0], world
+        self.l2_clip = l2_clip
         dev = example_input.device
         self.device = dev
         self.x = torch.empty_like(example_input)
@@ -36,8 +39,9 @@ class GraphedTrainStep:
         self.y.copy_(example_target)
         lib = _lib.cuda_lib()
         self.hp_size = lib.bdl_optim_hp_size()
-        self.hp_dev = torch.zeros(self.hp_size, dtype=torch.uint8, device=dev)
-        self.hp_host = [torch.zeros(self.hp_size, dtype=torch.uint8).pin_memory() for _ in range(_RING)]
+        nm = len(self.oms)
+        self.hp_dev = torch.zeros(self.hp_size * nm, dtype=torch.uint8, device=dev)
+        self.hp_host = [torch.zeros(self.hp_size * nm, dtype=torch.uint8).pin_memory() for _ in range(_RING)]
         self._ring = 0
         self.epoch_dev = torch.zeros(1, dtype=torch.int64, device=dev)
         self.loss = None
@@ -95,9 +99,10 @@ class GraphedTrainStep:
             "weights": fl.weights.clone(), "compute": None if fl.compute is None else fl.compute.clone(),
             "part": None if self.sync.weight_partition is None else self.sync.weight_partition.clone(),
             "buffers": [{k: b.clone() for k, b in m._buffers.items() if isinstance(b, torch.Tensor)} for m in mods],
-            "om_state": self.om.state.clone(), "om_attrs": {k: copy.deepcopy(v) for k, v in self.om.__dict__.items()
-                                                           if k not in ("state", "_hist")},
-            "hist_keys": set(self.om._hist.keys()), "hist": {k: v.clone() for k, v in self.om._hist.items()},
+            "oms": [{"om_state": om.state.clone(),
+                     "om_attrs": {k: copy.deepcopy(v) for k, v in om.__dict__.items() if k not in ("state", "_hist")},
+                     "hist_keys": set(om._hist.keys()), "hist": {k: v.clone() for k, v in om._hist.items()}}
+                    for om in self.oms],
         }
 
     def _restore(self, snap):
@@ -117,23 +122,25 @@ class GraphedTrainStep:
             for m, saved in zip(self.model.all_modules(), snap["buffers"]):
                 for k, b in saved.items():
                     m._buffers[k].copy_(b)
-            for k, v in self.om._hist.items():
-                if k in snap["hist"]:
-                    v.copy_(snap["hist"][k])
-                else:
-                    v.zero_()               # created during warm-up: logically "not there yet"
-        fresh = not snap["hist_keys"]
-        # restore IN PLACE: the training loop holds an alias of this Table (epoch / neval bookkeeping), so the object
-        # must stay the same or epoch-based schedules would read a frozen copy under graph replay
-        live = self.om.state
-        for k in list(live.keys()):
-            del live[k]
-        for k, v in snap["om_state"].items():
-            live[k] = v
-        for k, v in snap["om_attrs"].items():
-            self.om.__dict__[k] = v
-        if fresh and self.om._hist:
-            self.om._hist_fresh = True      # first real step must behave like the very first update (SGD: v = g)
+            for om, sn in zip(self.oms, snap["oms"]):
+                for k, v in om._hist.items():
+                    if k in sn["hist"]:
+                        v.copy_(sn["hist"][k])
+                    else:
+                        v.zero_()               # created during warm-up: logically "not there yet"
+        for om, sn in zip(self.oms, snap["oms"]):
+            fresh = not sn["hist_keys"]
+            # restore IN PLACE: the training loop holds an alias of this Table (epoch / neval bookkeeping), so the
+            # object must stay the same or epoch-based schedules would read a frozen copy under graph replay
+            live = om.state
+            for k in list(live.keys()):
+                del live[k]
+            for k, v in sn["om_state"].items():
+                live[k] = v
+            for k, v in sn["om_attrs"].items():
+                om.__dict__[k] = v
+            if fresh and om._hist:
+                om._hist_fresh = True      # first real step must behave like the very first update (SGD: v = g)
         torch.cuda.synchronize(self.device)
         if self.world > 1 and dist.is_initialized():
             dist.barrier()
@@ -141,6 +148,9 @@ class GraphedTrainStep:
     # one iteration, identical in warm-up, capture and (implicitly) replay
     def _body(self):
         before = _lib.LAUNCHES
+        overlapped = self.sync.overlapped
+        if overlapped:      # arm the per-bucket exchange: pulls of remote weights now, reduce+update from inside backward
+            self.sync.begin_step(self.oms, self.world, self.l2_clip, hp_dev=self.hp_dev.data_ptr(), plans=self._plan)
         with torch.enable_grad():
             out = self.model._call(self.x)
             loss = self.criterion._call(out, self.y)
@@ -151,18 +161,23 @@ class GraphedTrainStep:
 
         join_side_streams()
         self.model._apply_regularizers()
-        self.sync.step_device_hp(self._plan, self.hp_dev.data_ptr(), self.epoch_dev.data_ptr())
+        if overlapped:
+            self.sync.end_step()
+        else:
+            self.sync.step_device_hp(self._plan[0], self.hp_dev.data_ptr(), self.epoch_dev.data_ptr())
         self._count_body_launches = _lib.LAUNCHES - before
         return loss.detach()
 
     def _push_hp(self):
         """Advance the OptimMethod's scalar state by one step on the host and ship the resulting OptimHP."""
-        self.om.gradient_scale = self.sync.grad_scale_for(self.world)
-        plan = self.om.native_plan(self.sync.update_target(), None)
-        self._plan = plan
+        plans = []
+        for i, om in enumerate(self.oms):
+            om.gradient_scale = self.sync.grad_scale_for(self.world)
+            plans.append(om.native_plan(self.sync.method_target(i), None))
+        self._plan = plans
         buf = self.hp_host[self._ring % _RING]
         self._ring += 1
-        buf.copy_(torch.frombuffer(bytearray(plan[1]), dtype=torch.uint8))
+        buf.copy_(torch.frombuffer(bytearray(b"".join(p[1] for p in plans)), dtype=torch.uint8))
         self.hp_dev.copy_(buf, non_blocking=True)
 
     def run(self, x_host: torch.Tensor | None = None, y_host: torch.Tensor | None = None) -> torch.Tensor:

@@ -418,12 +418,15 @@ def _train_loop(opt: Optimizer, distributed: bool, strategy_factory=None):
     if prev_sync is not None:
         prev_sync.close()       # an earlier optimize() parked its symmetric buffer on the model; release it (collective)
     # ParallelOptimizer keeps full (non-sharded) weights and optimizer state on every rank: no sharded master copy
-    sync = AllReduceParameter(flat, backend=None if (world > 1 and strategy_factory is None) else "local")
+    method_ranges = [(o, l) for o, l, _ in ranges] if ranges is not None else None
+    method_list = [opt.optim_methods[n] for _, _, n in ranges] if ranges is not None else None
+    sync = AllReduceParameter(flat, backend=None if (world > 1 and strategy_factory is None) else "local", root=model,
+                              method_ranges=method_ranges)
     sync.init()
     opt._param_sync = sync
     single = opt._single_method()
-    if single is None and sync.backend not in ("local", "gloo"):
-        raise NotImplementedError("per-submodule optim methods run on the local/gloo parameter backends")
+    if single is None and not sync.overlapped and sync.backend not in ("local", "gloo", "nccl"):
+        raise NotImplementedError("per-submodule optim methods run on the local / gloo / bucketed-p2p parameter backends")
 
     for om in opt.optim_methods.values():
         om.clearHistory()        # DistriOptimizer.scala:811 — history never survives into a new optimize() call
@@ -450,8 +453,12 @@ def _train_loop(opt: Optimizer, distributed: bool, strategy_factory=None):
     loss_value = float("nan")
     use_fused_loss = device.type == "cuda"
     graphs: dict = {}
-    graph_ok = (device.type == "cuda" and bool(config.get("bigdl.cudaGraph")) and single is not None
-                and clip.l2norm is None and sync.backend in ("local", "p2p") and config.get("bigdl.engineType") == "b200")
+    # per-submodule methods and global-norm clipping stay on the graph when the bucketed p2p plane carries them (device
+    # resident OptimHP table and clip scale); on one GPU they run eagerly
+    graph_ok = (device.type == "cuda" and bool(config.get("bigdl.cudaGraph")) and sync.backend in ("local", "p2p")
+                and config.get("bigdl.engineType") == "b200"
+                and ((single is not None and clip.l2norm is None) or sync.overlapped))
+    step_methods = method_list if method_list is not None else [single]
     strategy = strategy_factory(model, world) if strategy_factory is not None else None
     if strategy is not None:
         graph_ok = False
@@ -467,12 +474,17 @@ def _train_loop(opt: Optimizer, distributed: bool, strategy_factory=None):
             om.clip_range = clip.constant
         loss = None
         if graph_ok and len(batch.inputs) == 1 and len(batch.targets) == 1:
-            loss = _graph_step(opt, graphs, model, criterion, sync, single, batch, device, world)
+            loss = _graph_step(opt, graphs, model, criterion, sync, step_methods if sync.overlapped else single, batch,
+                               device, world, clip.l2norm)
             if loss is None:
                 graph_ok = False
         if loss is None:
             batch = opt._to_device(batch, device)
             x, y = batch.getInput(), batch.getTarget()
+            if sync.overlapped:
+                for om_ in step_methods:
+                    om_.clip_range = clip.constant
+                sync.begin_step(step_methods, world, clip.l2norm)
             with torch.enable_grad():
                 out = model._call(x)
                 loss = criterion._call(out, y)
@@ -488,6 +500,8 @@ def _train_loop(opt: Optimizer, distributed: bool, strategy_factory=None):
                 for om_ in strategy.methods:
                     om_.clip_range = clip.constant
                 strategy.after_backward()
+            elif sync.overlapped:
+                sync.end_step()
             elif single is not None:
                 sync.step(single, avg_numbers=world, l2_clip=clip.l2norm)
             else:
@@ -609,7 +623,7 @@ class _Prefetcher:
         return b
 
 
-def _graph_step(opt, graphs, model, criterion, sync, om, batch, device, world):
+def _graph_step(opt, graphs, model, criterion, sync, om, batch, device, world, l2_clip=None):
     """Run one iteration through a captured CUDA graph (one graph per batch shape). Returns the loss tensor, or None
     when this configuration cannot be captured (the caller then falls back to eager execution for good)."""
     from .graph_step import GraphedTrainStep
@@ -619,7 +633,7 @@ def _graph_step(opt, graphs, model, criterion, sync, om, batch, device, world):
     gs = graphs.get(key)
     if gs is None:
         try:
-            gs = GraphedTrainStep(model, criterion, sync, om, x.to(device), y.to(device), world)
+            gs = GraphedTrainStep(model, criterion, sync, om, x.to(device), y.to(device), world, l2_clip=l2_clip)
         except NotImplementedError as e:
             log.warning("CUDA-graph capture unavailable for this configuration (%s); running eagerly", e)
             return None

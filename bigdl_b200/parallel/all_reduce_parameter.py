@@ -49,8 +49,13 @@ def _bits_to_f32(b: torch.Tensor) -> torch.Tensor:
 
 class AllReduceParameter:
     def __init__(self, flat: FlatParams, group=None, backend: str | None = None, compress: str | None = None,
-                 align: int = 8):
+                 align: int = 8, root=None, method_ranges=None):
+        """``root``: the model whose parameters ``flat`` holds — lets the p2p backend cut gradient buckets at its
+        top-level layers and overlap their exchange with backward. ``method_ranges``: ``[(offset, length)]`` of the
+        per-submodule OptimMethods (sorted, tiling the vector); bucket borders then respect them."""
         self.flat = flat
+        self.root, self.method_ranges = root, method_ranges
+        self._plane = None
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -83,7 +88,9 @@ class AllReduceParameter:
         s, l = self.start, self.length
         self.weight_partition = self.flat.weights[s:s + l].clone()
         self.gradient_partition = torch.zeros(l, dtype=torch.float32, device=self.device)
-        if self.backend == "p2p":
+        if self.backend == "p2p" and config.get("bigdl.parameter.p2p") == "bucketed":
+            self._init_bucketed()
+        elif self.backend == "p2p":
             self._init_p2p()
         elif self.backend == "nccl":
             # equal-sized shards for the NCCL collectives
@@ -125,6 +132,56 @@ class AllReduceParameter:
         self._w16_ptrs = self._sym.peer_ptr_array(self._off_w16)
         self._flag_ptrs = self._sym.peer_ptr_array(self._off_flags)
 
+    def _init_bucketed(self):
+        """p2p backend, bucketed form (parallel/bucketed.py): the rank owns one sub-slice of every bucket; its master
+        weights / averaged gradients / optimizer state are the concatenation of those sub-slices."""
+        from .bucketed import BucketedP2P
+
+        pl = BucketedP2P(self, self.root, self.method_ranges)
+        self._plane = pl
+        self._sym = pl.sym
+        self.g16 = pl.g16
+        parts = [self.flat.weights[s:s + l] for s, l, _ in pl.my_slices()]
+        self.weight_partition = torch.cat(parts).clone() if parts else torch.zeros(0, device=self.device)
+        self.gradient_partition = torch.zeros(pl.part_len, dtype=torch.float32, device=self.device)
+        self.start, self.length = -1, pl.part_len          # not one contiguous range any more
+        self._rebind_compute(pl.w16)
+        self._epoch_dev = pl.epoch_dev
+
+    @property
+    def overlapped(self) -> bool:
+        """True when the gradient exchange is launched from inside backward (begin_step / end_step protocol)."""
+        return self._plane is not None
+
+    def method_target(self, i: int = 0) -> torch.Tensor:
+        """The fp32 vector OptimMethod ``i`` updates on this rank."""
+        if self._plane is None:
+            return self.update_target()
+        off, ln = self._plane.method_partition(i) if self.method_ranges else (0, self._plane.part_len)
+        return self.weight_partition[off:off + ln]
+
+    def begin_step(self, methods, avg_numbers: int | None = None, l2_clip: float | None = None, hp_dev: int | None = None,
+                   plans=None):
+        """Call BEFORE forward (bucketed p2p backend). ``methods``: the OptimMethod(s), in ``method_ranges`` order.
+        Resolves this step's hyper-parameters, issues the just-in-time weight pulls and arms the backward hooks."""
+        if not self._inited:
+            self.init()
+        avg = float(avg_numbers if avg_numbers is not None else self.world)
+        if plans is None:
+            plans = []
+            for i, om in enumerate(methods):
+                om.gradient_scale = avg if self.truncate else 1.0 / avg
+                plans.append(om.native_plan(self.method_target(i), None))
+        self._plane.begin_step(plans, hp_dev, avg, l2_clip)
+
+    def end_step(self):
+        self._plane.end_step()
+
+    def ensure_weights_current(self):
+        """Outside a training step (validation, checkpoint, end of training): pull every remote slice now."""
+        if self._plane is not None and self._inited:
+            self._plane.pull_all()
+
     def _rebind_compute(self, new_compute: torch.Tensor):
         """Make ``new_compute`` (bf16 [P]) the model's compute-weight buffer and re-point every layer's view."""
         from ..nn.flat import _physical_view
@@ -156,6 +213,10 @@ class AllReduceParameter:
         avg = float(avg_numbers if avg_numbers is not None else self.world)
         if self.backend == "local":
             return self._step_local(optim_method, avg, l2_clip)
+        if self._plane is not None:
+            # gradients are already complete (called after backward): same kernels, nothing left to overlap with
+            self.begin_step([optim_method], avg_numbers, l2_clip)
+            return self.end_step()
         if self.backend == "p2p":
             return self._step_p2p(optim_method, avg, l2_clip)
         if self.backend == "nccl":
@@ -164,7 +225,7 @@ class AllReduceParameter:
 
     # ---- graph-capturable form: every per-step scalar comes from device memory
     def update_target(self) -> torch.Tensor:
-        """The fp32 vector the OptimMethod updates on this rank (whole vector locally, my slice when sharded)."""
+        """The fp32 vector the OptimMethod updates on this rank (whole vector locally, my slice(s) when sharded)."""
         return self.flat.weights if self.backend == "local" else self.weight_partition
 
     def grad_scale_for(self, world: int) -> float:
@@ -187,8 +248,9 @@ class AllReduceParameter:
                           hp_dev=hp_dev)
             fl.dirty = False
             return
-        if self.backend != "p2p":
-            raise NotImplementedError("graph-captured steps run on the local and p2p parameter backends")
+        if self.backend != "p2p" or self._plane is not None:
+            raise NotImplementedError("graph-captured steps run on the local and p2p parameter backends "
+                                      "(bucketed p2p: begin_step / end_step)")
         lib = _lib.cuda_lib()
         st = _lib.stream_ptr()
         _lib.check(lib.bdl_compress_grads(fl.grads.data_ptr(), self.g16.data_ptr(), self.P, int(self.truncate), 1, st),
@@ -351,22 +413,57 @@ class AllReduceParameter:
         fl = self.flat
         if self.world == 1 or not self._inited or self.backend == "local":
             return fl.weights
+        if fl.weights.is_cuda and dist.get_backend(self.group) == "nccl":
+            # one device-side all-gather of the (padded) fp32 partitions; no pickling through the host
+            lens = [self._partition_len(r) for r in range(self.world)]
+            pad = max(lens)
+            mine = torch.zeros(pad, dtype=torch.float32, device=self.device)
+            mine[:self.weight_partition.numel()] = self.weight_partition
+            every = torch.empty(pad * self.world, dtype=torch.float32, device=self.device)
+            dist.all_gather_into_tensor(every, mine, group=self.group)
+            with torch.no_grad():
+                for r in range(self.world):
+                    blk = every[r * pad:r * pad + lens[r]]
+                    for s, l, po in self._partition_slices(r):
+                        if l:
+                            fl.weights[s:s + l] = blk[po:po + l]
+            self.ensure_weights_current()
+            return fl.weights
         parts = [None] * self.world
-        dist.all_gather_object(parts, (self.start, self.weight_partition.detach().cpu()), group=self.group)
+        dist.all_gather_object(parts, (self.rank, self.weight_partition.detach().cpu()), group=self.group)
         with torch.no_grad():
-            for s, blk in parts:
-                if blk.numel():
-                    fl.weights[s:s + blk.numel()] = blk.to(fl.weights.device)
+            for r, blk in parts:
+                for s, l, po in self._partition_slices(r):
+                    if l:
+                        fl.weights[s:s + l] = blk[po:po + l].to(fl.weights.device)
         return fl.weights
+
+    def _partition_slices(self, rank: int):
+        """[(global start, length, offset inside rank's partition)] for ``rank``."""
+        if self._plane is not None:
+            return self._plane.all_slices(rank)
+        if self.backend == "nccl":
+            s = min(rank * self._shard, self.P)
+            return [(s, max(0, min(self._shard, self.P - s)), 0)]
+        s, l = aligned_partition(self.P, self.world, rank, self.align)
+        return [(s, l, 0)]
+
+    def _partition_len(self, rank: int) -> int:
+        return sum(l for _, l, _ in self._partition_slices(rank))
 
     def close(self):
         """Free the symmetric buffer. The model's bf16 compute weights live inside it on the p2p backend, so they are
         first re-homed in private memory (every layer's view is re-pointed) — nothing may alias freed device memory."""
         if self._sym is not None:
             fl = self.flat
+            self.ensure_weights_current()
             if fl.compute is not None and getattr(self, "g16", None) is not None:
                 self._rebind_compute(torch.empty(self.P, dtype=torch.bfloat16, device=self.device))
             self.g16 = None
+            if self._plane is not None:
+                self._plane.remove_hooks()
+                self._plane.sym = None
+                self._plane = None
             self._sym.close()
             self._sym = None
             self._inited = False

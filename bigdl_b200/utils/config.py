@@ -25,6 +25,13 @@ _DEFAULTS: dict[str, Any] = {
     "bigdl.Parameter.syncPoolSize": 4,
     "bigdl.parameter.compress": "bf16_rn",   # bf16_rn | bf16_trunc (reference-exact) | fp32
     "bigdl.parameter.backend": "auto",       # auto | p2p (fused NVLink kernels) | nccl | gloo
+    "bigdl.parameter.p2p": "bucketed",       # bucketed (exchange overlapped with backward, pulled all-gather) | monolithic
+    "bigdl.parameter.overlap": True,         # False: one bucket = the whole vector (no overlap; for A/B measurements)
+    "bigdl.parameter.bucketMB": 8.0,         # fp32 gradient bytes per bucket of the bucketed p2p backend
+    "bigdl.parameter.firstBucketMB": 1.0,    # bucket 0 cannot overlap backward (its input has no gradient): keep it small
+    "bigdl.parameter.commBlocks": 48,        # CTAs per communication kernel launched INSIDE backward (they take SMs from it)
+    "bigdl.parameter.allgather": "push",     # push (owner stores to every peer after its update) | pull (consumers fetch)
+    "bigdl.parameter.gatherGemmMB": 4.0,     # Linear weights at least this big (bf16) are all-gathered by their GEMM
     "bigdl.parallelOptimizer.iterationPerTime": 1,
     "bigdl.parallelOptimizer.parameterBlocks": 10,
     "bigdl.parallel.bucketMB": 16.0,         # ParallelOptimizer bucket size (fp32 gradient bytes)

@@ -158,6 +158,33 @@ int bdl_fused_rs_update(const void* const* grad16_ptrs, void* const* w16_ptrs, v
                         float* s1, int kind, const void* hp_host, const void* hp_dev, int mode, unsigned int epoch,
                         void* local_sync, float* sumsq, int max_blocks, const void* epoch_dev, void* stream);
 /* cudaMalloc + cudaIpc handle exchange for the symmetric buffers (one process per GPU). handle64: 64 bytes. */
+/* Bucketed form of the above, one launch per gradient bucket from inside backward (communication stream):
+ * [compress my fp32 bucket -> bf16] -> begin barrier -> P2P reduce of my sub-slice -> average (-> device-side clip
+ * scale) -> OptimMethod -> bf16 weights stored into every peer's compute buffer (CM_PUBLISH; [hole_start, +hole_len) and
+ * CM_PUBLISH_LOCAL stay local for a consumer that gathers them itself) -> "ready" generation into every peer's flag
+ * area (no end barrier; consumers acquire it per bucket, bdl_pull_gather). mode = CM_* bits (csrc/comm_fused.cu); generation = *epoch_dev * gen_mul + gen_add; flag_off = element offset
+ * of this bucket's 3*nranks flag words; local_sync = 3 words shared by the stream-ordered launches of one plane.
+ * Reference: S/optim/ParallelOptimizer.scala:481-513 (per-bucket exchange inside backward) applied to the sharded
+ * update of S/optim/DistriOptimizer.scala:358-396 and S/parameters/AllReduceParameter.scala:236-328. */
+int bdl_bucket_rs_update(const void* const* grad16_ptrs, void* const* w16_ptrs, void* const* flag_ptrs, int nranks,
+                         int rank, long long b_start, long long b_len, long long start, long long length,
+                         float* grads32, float* master, float* grad_part, float* s0, float* s1, int kind,
+                         const void* hp_host, const void* hp_dev, int mode, unsigned int gen_mul, unsigned int gen_add,
+                         const void* epoch_dev, long long flag_off, void* local_sync, float* sumsq,
+                         const float* clip_scale, long long hole_start, long long hole_len, int max_blocks,
+                         void* stream);
+/* Pull side of the all-gather: copy remote sub-slices (segs = nsegs x {peer, start, len}) from their owners' compute
+ * buffers into mine, each after acquiring the owner's ready generation of (*epoch_dev - prev_steps).
+ * Reference: AllReduceParameter.getWeights, S/parameters/AllReduceParameter.scala:201-228. */
+int bdl_pull_gather(void* const* w16_ptrs, const void* my_flags, int nranks, int rank, const long long* segs, int nsegs,
+                    unsigned int gen_mul, unsigned int gen_add, int prev_steps, const void* epoch_dev,
+                    long long flag_off, int max_blocks, void* stream);
+/* Global-norm clipping on the device: exchange per-rank partial sums of squares through peer memory and write
+ * scale = min(1, max_norm / ||g||) where the update kernels read it (CM_CLIP_DEV). Resets *sumsq.
+ * Reference: L2NormClippingProcessor, S/parameters/ParameterOperations.scala:94-130. */
+int bdl_peer_clip_scale(void* const* slot_ptrs, void* const* flag_ptrs, int nranks, int rank, unsigned int gen_mul,
+                        unsigned int gen_add, const void* epoch_dev, long long flag_off, float* sumsq, float max_norm,
+                        float* scale_out, float* norm_out, void* stream);
 int bdl_ipc_alloc(size_t bytes, void** ptr, void* handle64);
 int bdl_ipc_open(const void* handle64, void** ptr);
 int bdl_ipc_close(void* ptr);

@@ -352,7 +352,10 @@ class BucketedP2P:
                 ctypes.cast(buf, ctypes.c_void_p) if buf is not None else None,
                 None if hp_dev is None else hp_dev + hsz * b.method, mode, self.nb, k + 1,
                 self.epoch_dev.data_ptr(), 3 * self.world * k, self.local_sync.data_ptr() + 16 * k, self.sumsq.data_ptr(),
-                self.clip_scale.data_ptr(), hole[0], hole[1], self.max_blocks if overlapped else 0,
+                self.clip_scale.data_ptr(), hole[0], hole[1],
+                # inside backward: enough CTAs for the bucket's bytes (one per 256 KB of fp32 gradients), capped so the
+                # compute stream keeps most SMs; after backward: every SM
+                min(self.max_blocks, max(16, b.length * 4 // (256 << 10))) if overlapped else 0,
                 _lib.stream_ptr()), "bdl_bucket_rs_update")
         _lib.count_launch()
         self._launched[k] = True

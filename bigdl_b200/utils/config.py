@@ -29,7 +29,7 @@ _DEFAULTS: dict[str, Any] = {
     "bigdl.parameter.overlap": True,         # False: one bucket = the whole vector (no overlap; for A/B measurements)
     "bigdl.parameter.bucketMB": 8.0,         # fp32 gradient bytes per bucket of the bucketed p2p backend
     "bigdl.parameter.firstBucketMB": 1.0,    # bucket 0 cannot overlap backward (its input has no gradient): keep it small
-    "bigdl.parameter.commBlocks": 48,        # CTAs per communication kernel launched INSIDE backward (they take SMs from it)
+    "bigdl.parameter.commBlocks": 96,        # CTAs per communication kernel launched INSIDE backward (they take SMs from it)
     "bigdl.parameter.allgather": "push",     # push (owner stores to every peer after its update) | pull (consumers fetch)
     "bigdl.parameter.gatherGemmMB": 4.0,     # Linear weights at least this big (bf16) are all-gathered by their GEMM
     "bigdl.parallelOptimizer.iterationPerTime": 1,

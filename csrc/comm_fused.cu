@@ -306,7 +306,11 @@ __device__ __forceinline__ void store8(float* p, const float* v) {
   *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
 }
 
-__global__ void __launch_bounds__(512)
+// kP: compile-time bound on the number of peers (8 on one NVSwitch box). With 8, the kernel fits 48 registers, so a
+// 512-thread CTA is co-resident with one of backward's GEMM CTAs (320 threads x 128 registers) on the same SM instead of
+// taking the SM away from the compute stream while it runs or waits for the slowest peer.
+template <int kP>
+__global__ void __launch_bounds__(512, kP <= 8 ? 2 : 1)
 bucket_rs_update_kernel(const BucketArgs a) {
   OptimHP hp = a.hp_dev ? *a.hp_dev : a.hp;
   const uint32_t gen = static_cast<uint32_t>(a.epoch_dev ? *a.epoch_dev : 0ull) * a.gen_mul + a.gen_add;
@@ -392,9 +396,9 @@ bucket_rs_update_kernel(const BucketArgs a) {
           }
         }
       } else {
-        uint4 raw[kMaxPeers];
+        uint4 raw[kP];
 #pragma unroll
-        for (int p = 0; p < kMaxPeers; ++p)
+        for (int p = 0; p < kP; ++p)
           if (p < nranks) {
             int src = rank + p;
             if (src >= nranks) src -= nranks;
@@ -403,7 +407,7 @@ bucket_rs_update_kernel(const BucketArgs a) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) g[j] = 0.f;
 #pragma unroll
-        for (int p = 0; p < kMaxPeers; ++p)
+        for (int p = 0; p < kP; ++p)
           if (p < nranks) {
             const uint32_t* r = reinterpret_cast<const uint32_t*>(&raw[p]);
 #pragma unroll
@@ -459,7 +463,7 @@ bucket_rs_update_kernel(const BucketArgs a) {
         *reinterpret_cast<uint4*>(a.peers.w16[rank] + goff) = o;
       } else if (mode & CM_PUBLISH) {
 #pragma unroll
-        for (int p = 0; p < kMaxPeers; ++p)
+        for (int p = 0; p < kP; ++p)
           if (p < nranks) {
             int dst = rank + p;
             if (dst >= nranks) dst -= nranks;
@@ -711,7 +715,10 @@ extern "C" int bdl_bucket_rs_update(const void* const* grad16_ptrs, void* const*
   if (max_blocks > 0) cap = max_blocks < bdl_num_sms() ? max_blocks : bdl_num_sms();
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
-  bucket_rs_update_kernel<<<static_cast<int>(blocks), threads, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  if (nranks <= 8)
+    bucket_rs_update_kernel<8><<<static_cast<int>(blocks), threads, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  else
+    bucket_rs_update_kernel<kMaxPeers><<<static_cast<int>(blocks), threads, 0, static_cast<cudaStream_t>(stream)>>>(a);
   return bdl_check_launch("bucket_rs_update_kernel");
 }
 

@@ -89,7 +89,11 @@ class Linear(Module):
             w16 = self.weight_for_compute("weight")
             if w16.dtype != torch.bfloat16:
                 w16 = w16.detach().to(torch.bfloat16)
-            return LinearFn.apply(input, self.weight, bias, w16, self._fuse_relu, self.scaleW, self.scaleB)
+            # sharded parameter plane: a callable that names the weight rows to gather from their owners during this
+            # training step (parallel/bucketed.py), absent otherwise
+            gp = self.__dict__.get("_gather_plan")
+            return LinearFn.apply(input, self.weight, bias, w16, self._fuse_relu, self.scaleW, self.scaleB,
+                                  gp() if gp is not None else None)
         w = self.weight
         if input.dtype != w.dtype:
             w = w.to(input.dtype)

@@ -611,7 +611,7 @@ class Module:
                     memo[id(p)] = q
                     od[n] = q
                 new.__dict__[k] = od
-            elif k in ("_train_summary", "_val_summary", "_pre_call_hook"):
+            elif k in ("_train_summary", "_val_summary", "_pre_call_hook", "_gather_plan"):
                 continue              # run-time attachments (event writers own threads and locks): not part of a copy
             else:
                 new.__dict__[k] = copy.deepcopy(v, memo)

@@ -175,7 +175,7 @@ def _acc_grad(param: torch.Tensor, scale: float):
 
 class LinearFn(Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, w16, relu, scale_w, scale_b):
+    def forward(ctx, x, weight, bias, w16, relu, scale_w, scale_b, gather=None):
         K = w16.shape[1]
         x2 = x.reshape(-1, K)
         if x2.dtype != torch.bfloat16:
@@ -184,7 +184,9 @@ class LinearFn(Function):
         if K % 8:
             raise _lib.NativeError("Linear on the tensor-core path needs inputSize % 8 == 0")
         b32 = bias.detach() if bias is not None else None
-        y = gemm_bf16(x2, w16, bias=b32, relu=relu)
+        from .gemm import linear_forward
+
+        y = linear_forward(x2, w16, b32, relu, gather=gather, key=id(weight))
         ctx.save_for_backward(x2, w16, y if relu else None)
         ctx.params = (weight, bias, relu, scale_w, scale_b, x.shape)
         return y.reshape(*x.shape[:-1], w16.shape[0])
@@ -237,7 +239,7 @@ class LinearFn(Function):
         dx = None
         if ctx.needs_input_grad[0]:
             dx = gemm_bf16(dz, wk, b_mn=True).reshape(xshape)
-        return dx, None, None, None, None, None, None
+        return dx, None, None, None, None, None, None, None
 
 
 _STEM_S2D: list = [True]

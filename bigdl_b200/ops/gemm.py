@@ -75,3 +75,61 @@ def conv_igemm(mode: int, act: torch.Tensor, ld_act: int, other: torch.Tensor, o
     _lib.check(rc, "bdl_conv_igemm_bf16")
     _lib.count_launch()
     return out
+
+
+_ACC_WS: dict = {}
+
+
+def _acc_workspace(M: int, N: int, device, key) -> torch.Tensor:
+    """Persistent zeroed fp32 [M, N] accumulator of one layer (``bdl_bias_act_finish`` re-zeroes it after every use)."""
+    k = (key, M, N, device.index)
+    t = _ACC_WS.get(k)
+    if t is None:
+        t = _ACC_WS[k] = torch.zeros(M, N, dtype=torch.float32, device=device)
+    return t
+
+
+def linear_forward(x2: torch.Tensor, w16: torch.Tensor, bias, relu: bool, gather=None, key=None) -> torch.Tensor:
+    """y = act(x2 @ w16^T + bias) for a Linear layer (bf16, x2 [M,K], w16 [N,K]).
+
+    Few rows and a long reduction (classifier heads: M = batch, K in the thousands) would leave most SMs idle — one n
+    tile each, all of them streaming weights — so those shapes run split-K into a per-layer fp32 accumulator followed
+    by one bias/activation pass. ``gather`` (parallel/bucketed.py) names the row blocks of the weight that other ranks
+    own: they are read from the owners' memory by the GEMM itself and written through to ``w16``."""
+    lib = _lib.cuda_lib()
+    M, K = x2.shape
+    N = w16.shape[0]
+    sms = torch.cuda.get_device_properties(x2.device).multi_processor_count
+    bn = 128
+    tiles = ((M + 127) // 128) * ((N + bn - 1) // bn)
+    split = tiles * 2 <= sms and K >= 2048 and N % 4 == 0
+    if gather is None and not split:
+        return gemm_bf16(x2, w16, bias=bias, relu=relu)
+    y = torch.empty((M, N), device=x2.device, dtype=torch.bfloat16)
+    if split:
+        acc = _acc_workspace(M, N, x2.device, key if key is not None else w16.data_ptr())
+        out, flags, b = acc, ATOMIC_ADD, None
+    else:
+        out, flags, b = y, (BIAS if bias is not None else 0) | (RELU if relu else 0), bias
+    _log("gemm", M=M, N=N, K=K, a_mn=0, b_mn=0, acc=int(split), gathered=int(gather is not None))
+    if gather is not None:
+        nr = gather["nranks"]
+        peers = (ctypes.c_void_p * nr)(*gather["ptrs"])
+        t0 = (ctypes.c_int * nr)(*gather["t0"])
+        t1 = (ctypes.c_int * nr)(*gather["t1"])
+        assert gather["block_n"] == bn
+        rc = lib.bdl_gemm_bf16_gathered(_lib.ptr(x2), _lib.ptr(w16), _lib.ptr(out), _lib.ptr(b), M, N, K, x2.stride(0),
+                                        w16.stride(0), out.stride(0), int(out.dtype == torch.float32), flags, 0, bn,
+                                        peers, t0, t1, nr, gather["rank"], _lib.stream_ptr())
+        _lib.check(rc, "bdl_gemm_bf16_gathered")
+    else:
+        rc = lib.bdl_gemm_bf16(_lib.ptr(x2), _lib.ptr(w16), _lib.ptr(out), _lib.ptr(b), M, N, K, x2.stride(0),
+                               w16.stride(0), out.stride(0), 0, 0, int(out.dtype == torch.float32), flags, 0,
+                               _lib.stream_ptr())
+        _lib.check(rc, "bdl_gemm_bf16")
+    _lib.count_launch()
+    if split:
+        _lib.check(lib.bdl_bias_act_finish(acc.data_ptr(), _lib.ptr(bias), y.data_ptr(), M, N, acc.stride(0), y.stride(0),
+                                           int(relu), _lib.stream_ptr()), "bdl_bias_act_finish")
+        _lib.count_launch()
+    return y

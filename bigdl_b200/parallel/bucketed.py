@@ -189,7 +189,9 @@ class BucketedP2P:
         self._pull_events = [None] * B
         self._step = None              # per-step launch context (set by begin_step)
         self._in_step = False
-        self.stats = {"bucket_launches": 0, "pull_launches": 0, "overlapped": 0}
+        self.stats = {"bucket_launches": 0, "pull_launches": 0, "overlapped": 0, "gathered_gemms": 0}
+        self._gather_mods = []
+        self._plan_gathered(float(config.get("bigdl.parameter.gatherGemmMB")))
         self._install_hooks()
 
     # ------------------------------------------------------------------ layout helpers
@@ -208,6 +210,60 @@ class BucketedP2P:
         off = mine[0].poff[self.rank]
         return off, sum(b.slices[self.rank][1] for b in mine)
 
+    # ------------------------------------------------------------------ all-gather fused into the consumer GEMM
+    GATHER_BLOCK_N = 128
+
+    def _plan_gathered(self, min_mb: float):
+        """Large ``Linear`` weights are not pushed to the peers after the update: the rows a rank owns (whole 128-row
+        tiles inside its sub-slice) stay in its buffer and every other rank's forward GEMM loads them from there
+        (csrc/gemm_tcgen05.cu kAG). One such range per (bucket, rank) — the kernel's publish "hole"."""
+        from ..nn.layers_core import Linear
+
+        if self.world == 1 or min_mb <= 0 or self.world > 8:
+            return
+        bn = self.GATHER_BLOCK_N
+        by_bucket: dict[int, list] = {}
+        for m, name, off, numel in self.flat.entries:
+            if not (isinstance(m, Linear) and name == "weight") or numel * 2 < min_mb * (1 << 20) or m.input_size % 8:
+                continue
+            b = next((bk for bk in self.buckets if bk.off <= off < bk.off + bk.length), None)
+            if b is None or off + numel > b.off + b.length or b.gathered:
+                continue                     # one gathered matrix per bucket (the kernel takes one hole per launch)
+            K, N = m.input_size, m.output_size
+            t0, t1, holes = [0] * self.world, [0] * self.world, []
+            for r in range(self.world):
+                s, l = b.slices[r]
+                lo, hi = max(s, off), min(s + l, off + numel)
+                if hi <= lo:
+                    continue
+                first = -(-(lo - off) // (K * bn))             # first whole tile inside the slice
+                last = (hi - off) // (K * bn)                    # one past the last whole tile
+                if hi == off + numel:
+                    last = -(-N // bn)                           # the ragged last tile belongs to whoever owns its rows
+                if last > first:
+                    t0[r], t1[r] = first, last
+                    hs = off + first * bn * K
+                    holes.append((r, hs, min(last * bn * K, numel) - first * bn * K))
+            if not holes:
+                continue
+            b.gathered = sorted((hs, hl) for _, hs, hl in holes)
+            self._hole_of = getattr(self, "_hole_of", {})
+            for r, hs, hl in holes:
+                self._hole_of[(b.index, r)] = (hs, hl)
+            plan = {"nranks": self.world, "rank": self.rank, "block_n": bn, "t0": t0, "t1": t1,
+                    "ptrs": [self.sym.ptrs[r] + self._off_w16 + 2 * off for r in range(self.world)]}
+            m.__dict__["_gather_plan"] = self._make_gather(plan)
+            self._gather_mods.append(m)
+
+    def _make_gather(self, plan):
+        def gather():
+            # only inside a training step is the local copy stale; outside, ensure_weights_current() has filled it
+            if not self._in_step or not torch.is_grad_enabled():
+                return None
+            self.stats["gathered_gemms"] += 1
+            return plan
+        return gather
+
     # ------------------------------------------------------------------ hooks
     def _install_hooks(self):
         for b in self.buckets:
@@ -225,6 +281,9 @@ class BucketedP2P:
             else:
                 m.__dict__["_pre_call_hook"] = prev
         self._hooked = []
+        for m in self._gather_mods:
+            m.__dict__.pop("_gather_plan", None)
+        self._gather_mods = []
 
     def _make_hook(self, i: int, prev):
         def hook(module, x):
@@ -341,7 +400,7 @@ class BucketedP2P:
         def at(t, o):
             return None if t is None else t.data_ptr() + 4 * o
 
-        hole = b.gathered[0] if b.gathered else (0, 0)
+        hole = getattr(self, "_hole_of", {}).get((k, self.rank), (0, 0))
         main = torch.cuda.current_stream(self.device)
         self.comm.wait_stream(main)
         with torch.cuda.stream(self.comm):

@@ -31,7 +31,11 @@ _DEFAULTS: dict[str, Any] = {
     "bigdl.parameter.firstBucketMB": 1.0,    # bucket 0 cannot overlap backward (its input has no gradient): keep it small
     "bigdl.parameter.commBlocks": 96,        # CTAs per communication kernel launched INSIDE backward (they take SMs from it)
     "bigdl.parameter.allgather": "push",     # push (owner stores to every peer after its update) | pull (consumers fetch)
-    "bigdl.parameter.gatherGemmMB": 4.0,     # Linear weights at least this big (bf16) are all-gathered by their GEMM
+    # Linear weights at least this big (bf16 MB) are NOT pushed by their owners; the forward GEMM gathers the remote row
+    # blocks itself (plain TMA loads from the owners' memory, written through to the local copy). 0 = off: measured on
+    # VGG-16 the pushed all-gather hides behind backward, the fused one sits on the forward's critical path
+    # (profiles/comm_r2.md), so it is opt-in.
+    "bigdl.parameter.gatherGemmMB": 0.0,
     "bigdl.parallelOptimizer.iterationPerTime": 1,
     "bigdl.parallelOptimizer.parameterBlocks": 10,
     "bigdl.parallel.bucketMB": 16.0,         # ParallelOptimizer bucket size (fp32 gradient bytes)

@@ -376,6 +376,48 @@ __global__ void counter_add_kernel(unsigned long long* c, unsigned long long v) 
 using namespace bdl;
 
 // *counter += v, stream ordered (device-side step counters for graph-captured training steps)
+// Finish of a split-K forward GEMM: y = act(acc + bias) as bf16, and the fp32 accumulator is re-zeroed in the same pass so
+// the next launch can red.add into it again without a memset (Linear forward with few rows: the K split is what fills
+// the SMs, S/nn/Linear.scala:78-104).
+__global__ void bias_act_finish_kernel(float* __restrict__ acc, const float* __restrict__ bias, __nv_bfloat16* __restrict__ y,
+                                       long long M, int N, long long ld_acc, long long ldy, int relu) {
+  const int nv = N / 4;
+  const long long total = M * nv;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long r = i / nv;
+    const int c = static_cast<int>(i - r * nv) * 4;
+    float4* ap = reinterpret_cast<float4*>(acc + r * ld_acc + c);
+    float4 v = *ap;
+    *ap = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (bias) {
+      const float4 b = *reinterpret_cast<const float4*>(bias + c);
+      v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
+    }
+    if (relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+    uint2 o;
+    o.x = *reinterpret_cast<uint32_t*>(&lo);
+    o.y = *reinterpret_cast<uint32_t*>(&hi);
+    *reinterpret_cast<uint2*>(y + r * ldy + c) = o;
+  }
+}
+
+extern "C" int bdl_bias_act_finish(float* acc, const float* bias, void* y, long long M, int N, long long ld_acc,
+                                   long long ldy, int relu, void* stream) {
+  if (M <= 0 || N <= 0) return BDL_OK;
+  if ((N % 4) || (ld_acc % 4) || (ldy % 4) || (reinterpret_cast<uintptr_t>(acc) & 15u) || (reinterpret_cast<uintptr_t>(y) & 7u) ||
+      (bias && (reinterpret_cast<uintptr_t>(bias) & 15u)))
+    return bdl_fail("bdl_bias_act_finish: N and the pitches must be multiples of 4, pointers vector-aligned");
+  const long long total = M * (N / 4);
+  long long blocks = (total + 255) / 256;
+  const long long cap = static_cast<long long>(bdl_num_sms()) * 8;
+  if (blocks > cap) blocks = cap;
+  bias_act_finish_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      acc, bias, static_cast<__nv_bfloat16*>(y), M, N, ld_acc, ldy, relu);
+  return bdl_check_launch("bias_act_finish_kernel");
+}
+
 extern "C" int bdl_counter_add(void* counter_dev, unsigned long long v, void* stream) {
   counter_add_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<unsigned long long*>(counter_dev), v);
   return bdl_check_launch("counter_add_kernel");

@@ -288,11 +288,25 @@ __device__ __forceinline__ void epilogue_pack16(const GemmParams& p, const uint3
 //       stages its own 128 rows of A and half of the B tile (no multicast — every CTA fetches its own slice), the leader
 //       (cluster rank 0) issues the MMAs and commits to the barriers of both CTAs, each CTA's epilogue drains its own
 //       128 TMEM rows. Per SM the B bytes from L2 and through shared memory are halved.
-template <bool kAMN, bool kBMN, int kConv, bool kFp8 = false, bool kDual = false, bool kTmaStore = false,
-          bool kTwo = false>
-__global__ void __launch_bounds__(kGemmThreads, 1)
-gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                         const __grid_constant__ CUtensorMap tmD, const GemmParams p) {
+// kAG: all-gather fused into the GEMM (Linear forward under the sharded parameter plane). The weight matrix B [N, K]
+//       is partitioned by rows among the ranks; an n tile whose rows another rank owns is loaded straight from THAT
+//       rank's memory — plain cp.async.bulk.tensor loads through a tensor map over the owner's buffer, one per CTA and k
+//       block, never multicast (TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load
+//       from another GPU's memory hung the GPU) — and, once landed, the tile is also TMA-stored into the local copy of
+//       the weights, so backward's dgrad and any later forward read local memory. The transfer of tile i+1..i+stages
+//       overlaps the MMAs of tile i through the ordinary operand ring.
+constexpr int kAgMaxRanks = 8;
+struct AgMaps {
+  CUtensorMap tm[kAgMaxRanks];   // B as seen in rank r's buffer (same shape / box / swizzle as the local map)
+  int t0[kAgMaxRanks];           // n tiles [t0[r], t1[r]) are fetched from rank r
+  int t1[kAgMaxRanks];
+  int nranks, rank;
+};
+
+template <bool kAMN, bool kBMN, int kConv, bool kFp8, bool kDual, bool kTmaStore, bool kTwo, bool kAG>
+__device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmD,
+                                                  const GemmParams& p, const AgMaps* ag) {
+  static_assert(!kAG || (!kAMN && !kBMN && kConv == 0 && !kFp8 && !kDual && !kTwo), "all-gather GEMM: plain K-major form");
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[kMaxStages];
   __shared__ __align__(8) uint64_t empty_bar[kMaxStages];
@@ -357,6 +371,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         // pair + dual: the pair owns 512 rows as two 256-row MMAs; this CTA stages rows [+128 crank, +128) of each
         const int m0 = kTwo ? (m_blk * (kDual ? 4 : 2) + static_cast<int>(crank)) * BM : m_blk * BM * (kDual ? 2 : 1);
         const int m0b = m0 + (kTwo ? 2 * BM : BM);   // first row of this CTA's second stacked half (kDual)
+        const CUtensorMap* ag_src = &tmB;
+        if (kAG) {
+          for (int r = 0; r < ag->nranks; ++r)
+            if (r != ag->rank && n_blk >= ag->t0[r] && n_blk < ag->t1[r]) ag_src = &ag->tm[r];
+        }
         const int n0 = n_blk * p.block_n + (kTwo ? static_cast<int>(crank) * (p.block_n >> 1) : 0);
         // implicit-GEMM bookkeeping hoisted out of the k loop
         int cv_img = 0, cv_h = 0, cv_w = 0, cv_r = 0, cv_s = 0, cv_cb = 0;
@@ -551,6 +570,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           }
           if (kBMN) {
             for (int j = 0; j < p.b_rows / 64; ++j) tma_load_2d(sb + j * 8192u, &tmB, fb, n0 + 64 * j, k0);
+          } else if (kAG) {
+            tma_load_2d(sb, ag_src, fb, k0, n0);   // the owner's copy of this weight tile (local map for my own rows)
           } else {
             tma_load_2d(sb, &tmB, fb, k0, n0);  // box {64 k, block_n}
           }
@@ -578,6 +599,15 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         const int kb0 = static_cast<int>((static_cast<long long>(split) * num_kb) / p.splits);
         const int kb1 = static_cast<int>((static_cast<long long>(split + 1) * num_kb) / p.splits);
         constexpr bool dual = kDual;
+        bool ag_remote = false;
+        int ag_n0 = 0;
+        if (kAG) {
+          int m_blk_, n_blk_;
+          decode_tile(p, work - split * tiles_mn, m_blk_, n_blk_);
+          ag_n0 = n_blk_ * p.block_n;
+          for (int r = 0; r < ag->nranks; ++r)
+            if (r != ag->rank && n_blk_ >= ag->t0[r] && n_blk_ < ag->t1[r]) ag_remote = true;
+        }
         if (kTwo) mbar_wait_cluster(smem_u32(&tempty_bar[acc]), acc_phase ^ 1u);
         else mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1u);
         if (dual) {   // dual: acc is always 0, both stages are ours
@@ -634,6 +664,13 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
               else umma_f16(d_tmem + kAccStride, adesc2, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
             }
           }
+          }
+          if (kAG && ag_remote) {
+            // write-through: the remote tile that just landed also goes into the local copy of the weights. The slot is
+            // released only after the bulk store has READ shared memory (the MMAs above read it concurrently).
+            tma_store_2d(&tmB, sb, kb * KE, ag_n0);
+            tma_store_commit();
+            tma_store_wait_read0();
           }
           if (kTwo) umma_commit_pair(smem_u32(&empty_bar[stage]));
           else umma_commit(smem_u32(&empty_bar[stage]));
@@ -823,10 +860,28 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   tc_fence_before();
   if (kTwo) cluster_sync_all();   // neither CTA may leave while the other can still signal it or read its operands
   else __syncthreads();
+  if (kAG && warp == 1 && lane == 0) tma_store_wait0();   // write-through stores complete before the CTA retires
   if (warp == 1) {
     if (kTwo) tmem_dealloc_pair<kTmemCols>(tmem_base);
     else tmem_dealloc<kTmemCols>(tmem_base);
   }
+}
+
+template <bool kAMN, bool kBMN, int kConv, bool kFp8 = false, bool kDual = false, bool kTmaStore = false,
+          bool kTwo = false>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                         const __grid_constant__ CUtensorMap tmD, const GemmParams p) {
+  gemm_tcgen05_body<kAMN, kBMN, kConv, kFp8, kDual, kTmaStore, kTwo, false>(tmA, tmB, tmD, p, nullptr);
+}
+
+// Linear forward with the all-gather of its weight rows fused in (see kAG above).
+template <bool kTmaStore>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_allgather_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                           const __grid_constant__ CUtensorMap tmD, const GemmParams p,
+                           const __grid_constant__ AgMaps ag) {
+  gemm_tcgen05_body<false, false, 0, false, false, kTmaStore, false, true>(tmA, tmB, tmD, p, &ag);
 }
 
 // ------------------------------------------------------------------------------------------- host
@@ -1074,6 +1129,88 @@ extern "C" int bdl_gemm_bf16(const void* A, const void* B, void* D, const float*
   return launch_gemm_kernel(kfn, total, num_sms, smem, stream, two, tmA, tmB, tmD, p, "gemm_bf16_tcgen05_kernel");
 }
 
+
+// ------------------------------------------------------------------------------------------------ all-gather + GEMM
+// D[M,N] = A[M,K] * B[N,K]^T (+bias)(ReLU) where the rows of B are sharded among `nranks` GPUs: n tiles
+// [t0[r], t1[r]) (tiles of `block_n` rows) are read from peer_B[r] — rank r's copy of the same matrix, a peer-mapped
+// pointer — and written through to the local B; every other tile is read from the local B. The caller guarantees (by
+// acquiring the owners' ready flags, bdl_pull_gather) that the owners' rows are final before this launch.
+// Reference: AllReduceParameter.getWeights (S/parameters/AllReduceParameter.scala:201-228) — the blocking all-gather at
+// the top of every iteration, S/optim/DistriOptimizer.scala:212 — fused into S/nn/Linear.scala:78-104 (updateOutput).
+extern "C" int bdl_gemm_bf16_gathered(const void* A, void* B_local, void* D, const float* bias, int M, int N, int K,
+                                      long long lda, long long ldb, long long ldd, int out_fp32, int flags, int splits,
+                                      int block_n, const void* const* peer_B, const int* t0, const int* t1, int nranks,
+                                      int rank, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (M <= 0 || N <= 0 || K <= 0) return bdl_fail("bdl_gemm_bf16_gathered: empty problem");
+  if (nranks < 1 || nranks > kAgMaxRanks || rank < 0 || rank >= nranks)
+    return bdl_fail("bdl_gemm_bf16_gathered: 1..8 ranks");
+  if (block_n < 16 || block_n > 256 || (block_n % 16)) return bdl_fail("bdl_gemm_bf16_gathered: block_n must be a multiple of 16 in [16,256]");
+  if ((flags & BDL_GEMM_ATOMIC_ADD) && !out_fp32) return bdl_fail("bdl_gemm_bf16_gathered: ATOMIC_ADD needs fp32 output");
+  if ((reinterpret_cast<uintptr_t>(A) & 15u) || (reinterpret_cast<uintptr_t>(B_local) & 15u) || (lda % 8) || (ldb % 8))
+    return bdl_fail("bdl_gemm_bf16_gathered: A/B must be 16-byte aligned with leading dimensions that are multiples of 8");
+  const int num_sms = bdl_num_sms();
+  GemmParams p{};
+  p.M = M; p.N = N; p.K = K;
+  p.block_n = block_n;
+  p.b_rows = block_n;
+  p.tiles_m = (M + BM - 1) / BM;
+  p.tiles_n = (N + block_n - 1) / block_n;
+  const int num_kb = (K + BK - 1) / BK;
+  const long long tiles_mn = static_cast<long long>(p.tiles_m) * p.tiles_n;
+  if (splits <= 0) {
+    splits = 1;
+    if ((flags & BDL_GEMM_ATOMIC_ADD) && tiles_mn < num_sms) {
+      splits = static_cast<int>(num_sms / tiles_mn);
+      const int max_by_k = num_kb / 4 > 0 ? num_kb / 4 : 1;
+      if (splits > max_by_k) splits = max_by_k;
+    }
+  }
+  if (splits > 1 && !(flags & BDL_GEMM_ATOMIC_ADD)) return bdl_fail("bdl_gemm_bf16_gathered: split-K needs ATOMIC_ADD");
+  if (splits > num_kb) splits = num_kb;
+  p.splits = splits;
+  p.ldd = ldd; p.out_fp32 = out_fp32; p.flags = flags; p.D = D; p.bias = bias;
+  const size_t stage_bytes = static_cast<size_t>(BM) * BK * 2 + static_cast<size_t>(p.b_rows) * BK * 2;
+  const bool tma_out = want_tma_store(D, ldd, out_fp32, flags, false, num_kb);
+  const size_t budget = kSmemBudget - (tma_out ? kStageOutBytes : 0);
+  int stages = static_cast<int>(budget / stage_bytes);
+  if (stages > kMaxStages) stages = kMaxStages;
+  p.num_stages = stages;
+  const size_t smem = stages * stage_bytes + 1024 + (tma_out ? kStageOutBytes : 0);
+  CUtensorMap tmA, tmB, tmD{};
+  int rc = bdl_make_tmap_2d_bf16(&tmA, A, static_cast<uint64_t>(K), static_cast<uint64_t>(M), lda, 64, BM);
+  if (rc) return rc;
+  rc = bdl_make_tmap_2d_bf16(&tmB, B_local, static_cast<uint64_t>(K), static_cast<uint64_t>(N), ldb, 64, block_n);
+  if (rc) return rc;
+  if (tma_out) {
+    rc = bdl_make_tmap_2d_bf16(&tmD, D, static_cast<uint64_t>(N), static_cast<uint64_t>(M), ldd, 64, 32);
+    if (rc) return rc;
+  }
+  AgMaps ag{};
+  ag.nranks = nranks;
+  ag.rank = rank;
+  for (int r = 0; r < nranks; ++r) {
+    ag.t0[r] = t0[r];
+    ag.t1[r] = t1[r];
+    if (r == rank || t0[r] >= t1[r]) {
+      ag.t0[r] = ag.t1[r] = 0;
+      ag.tm[r] = tmB;
+      continue;
+    }
+    if (t0[r] < 0 || t1[r] > p.tiles_n) return bdl_fail("bdl_gemm_bf16_gathered: tile range outside the matrix");
+    if (!peer_B[r] || (reinterpret_cast<uintptr_t>(peer_B[r]) & 15u)) return bdl_fail("bdl_gemm_bf16_gathered: bad peer pointer");
+    // an ordinary tiled map over the owner's buffer; the kernel only ever issues plain (non-multicast) loads through it
+    rc = bdl_make_tmap_2d_bf16(&ag.tm[r], peer_B[r], static_cast<uint64_t>(K), static_cast<uint64_t>(N), ldb, 64, block_n);
+    if (rc) return rc;
+  }
+  auto kfn = tma_out ? gemm_bf16_allgather_kernel<true> : gemm_bf16_allgather_kernel<false>;
+  cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemBudget + 1024));
+  if (e != cudaSuccess) return bdl_fail_cuda("cudaFuncSetAttribute(allgather gemm)", e);
+  const long long total = tiles_mn * splits;
+  const int grid = static_cast<int>(total < num_sms ? total : num_sms);
+  kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, tmD, p, ag);
+  return bdl_check_launch("gemm_bf16_allgather_kernel");
+}
 
 // ------------------------------------------------------------------------------------------------ implicit-GEMM conv
 // mode 0 (fprop):  D[N*Ho*Wo, O]      = im2col(act)[., (tap, c)] * Wt[O, (tap, c)]^T          (+bias)(ReLU)

@@ -47,6 +47,14 @@ int bdl_gemm_bf16(const void* A, const void* B, void* D, const float* bias, int 
  * TMA im2col loads (no column matrix). mode 0 fprop, 1 dgrad (caller passes the transposed-conv geometry, stride 1),
  * 2 wgrad (C % 64 == 0, accumulates with red.add). Reference: S/nn/SpatialConvolution.scala:253-521,
  * S/nn/NNPrimitive.scala im2col/col2im, S/nn/mkldnn/SpatialConvolution.scala:435-633. */
+/* Linear forward with the all-gather of its row-sharded weight fused in: n tiles [t0[r], t1[r]) (tiles of block_n rows)
+ * are loaded from peer_B[r] (rank r's copy, a peer-mapped pointer; plain non-multicast TMA loads) and written through to
+ * B_local, all other tiles come from B_local. splits / ATOMIC_ADD as bdl_gemm_bf16.
+ * Reference: AllReduceParameter.getWeights (S/parameters/AllReduceParameter.scala:201-228) fused into
+ * S/nn/Linear.scala:78-104. */
+int bdl_gemm_bf16_gathered(const void* A, void* B_local, void* D, const float* bias, int M, int N, int K, long long lda,
+                           long long ldb, long long ldd, int out_fp32, int flags, int splits, int block_n,
+                           const void* const* peer_B, const int* t0, const int* t1, int nranks, int rank, void* stream);
 int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int W, int C, long long ld_act, const void* other,
                         long long ld_other, void* D, long long ldd, const float* bias, int O, int Ho, int Wo, int kh,
                         int kw, int sh, int sw, int ph, int pw, int dh, int dw, int out_fp32, int flags, int splits,
@@ -76,6 +84,10 @@ int bdl_dropout_fwd_bf16(const void* x, void* y, void* mask, size_t n, float p, 
 int bdl_dropout_fwd_bf16_ctr(const void* x, void* y, void* mask, size_t n, float p, unsigned long long seed,
                              void* counter_dev, void* stream);
 int bdl_counter_add(void* counter_dev, unsigned long long v, void* stream);
+/* y = act(acc + bias) in bf16 from the fp32 accumulator of a split-K forward GEMM; re-zeroes acc for the next launch.
+ * Reference: the bias add of S/nn/Linear.scala:93-103 (+ the fused ReLU of S/nn/mkldnn/Fusion.scala). */
+int bdl_bias_act_finish(float* acc, const float* bias, void* y, long long M, int N, long long ld_acc, long long ldy,
+                        int relu, void* stream);
 int bdl_dropout_bwd_bf16(const void* dy, const void* mask, void* dx, size_t n, float p, void* stream);
 int bdl_copy2d_bf16(const void* src, void* dst, long long rows, int C, long long lds, long long ldd, int accumulate,
                     void* stream);

@@ -144,3 +144,46 @@ def test_gemm_cta_pair_matches_single_cta_and_fp32(pair_mode, b_mn, M, N, K):
         assert o16[:, N:].abs().max().item() == 0 if ldn > N else True
     # same accumulation order per output element in both kernels -> identical results
     assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+
+
+@pytest.mark.parametrize("M,N,K,ranks", [(128, 1024, 4096, 4), (96, 1000, 2048, 3), (384, 512, 512, 2), (128, 4096, 1024, 8)])
+def test_linear_forward_with_fused_allgather(M, N, K, ranks):
+    """The all-gather-fused GEMM on ONE GPU with N virtual owners (separate buffers stand in for the peers' memory —
+    the kernel only ever issues plain TMA loads through them): tiles read from the owner's buffer, written through to
+    the local copy, split-K + bias/ReLU finish and the single-pass form, vs the fp32 reference."""
+    from bigdl_b200.ops.gemm import linear_forward
+    torch.manual_seed(11)
+    dev = "cuda"
+    bn = 128
+    tiles = (N + bn - 1) // bn
+    x = torch.randn(M, K, device=dev).bfloat16()
+    w_true = (torch.randn(N, K, device=dev) * 0.05).bfloat16()
+    bias = torch.randn(N, device=dev)
+    # owner r holds tiles [t0[r], t1[r]); a tile in between two owners is "boundary" (already in the local copy)
+    cuts = [round(i * tiles / ranks) for i in range(ranks + 1)]
+    t0, t1 = [cuts[r] for r in range(ranks)], [cuts[r + 1] for r in range(ranks)]
+    if tiles >= 2 * ranks:
+        t1[0] -= 1                                   # leave one boundary tile that nobody serves remotely
+    me = 1 if ranks > 1 else 0
+    bufs = []
+    for r in range(ranks):
+        b = torch.full((N, K), float("nan"), device=dev, dtype=torch.bfloat16)
+        b[t0[r] * bn:t1[r] * bn] = w_true[t0[r] * bn:t1[r] * bn]
+        bufs.append(b)
+    local = bufs[me]
+    served = torch.zeros(N, dtype=torch.bool, device=dev)
+    for r in range(ranks):
+        served[t0[r] * bn:t1[r] * bn] = True
+    local[~served] = w_true[~served]                 # boundary rows were pushed by their owners
+    plan = {"nranks": ranks, "rank": me, "block_n": bn, "t0": t0, "t1": t1, "ptrs": [b.data_ptr() for b in bufs]}
+    ref = torch.relu(x.float() @ w_true.float().t() + bias)
+    y = linear_forward(x, local, bias, True, gather=plan, key=("t", M, N, K))
+    torch.cuda.synchronize()
+    assert torch.allclose(y.float(), ref, rtol=2e-2, atol=2e-1)
+    assert torch.equal(local, w_true)                # every remote tile was written through to the local copy
+    y2 = linear_forward(x, local, bias, True, gather=plan, key=("t", M, N, K))      # accumulator was re-zeroed
+    torch.cuda.synchronize()
+    assert torch.allclose(y2.float(), ref, rtol=2e-2, atol=2e-1)      # (split-K adds arrive in any order: not bit-equal)
+    y3 = linear_forward(x, w_true, bias, True, gather=None, key=("u", M, N, K))     # same shapes without the gather
+    torch.cuda.synchronize()
+    assert torch.allclose(y3.float(), ref, rtol=2e-2, atol=2e-1)

@@ -40,16 +40,20 @@ def parse():
     ap.add_argument("--backend", default=None, help="parameter backend override: p2p | nccl")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--set", action="append", help="config override key=value (repeatable)")
+    ap.add_argument("--no-gpu-baseline", action="store_true",
+                    help="skip the in-line PyTorch (cuDNN + NCCL DDP, CUDA graph) arm measured on the same config")
+    ap.add_argument("--no-comm-probe", action="store_true", help="skip the exposed-communication / NVLink probes (N > 1)")
     ap.add_argument("--no-graph", action="store_true", help="issue every kernel eagerly instead of replaying a CUDA graph")
     return ap.parse_args()
 
 
 class ClockSampler(threading.Thread):
-    """Samples SM clock / throttle reasons of this rank's GPU every 200 ms through NVML during the timed region."""
+    """Samples SM clock / power / throttle reasons of this rank's GPU every 20 ms through NVML during the timed region
+    (a 0.1 s region still gets several samples)."""
 
     def __init__(self, index: int):
         super().__init__(daemon=True)
-        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self.index, self.samples, self.reasons, self.max_mhz, self.power = index, [], set(), None, []
         self._stop_evt = threading.Event()
         self.ok = False
         try:
@@ -77,6 +81,10 @@ class ClockSampler(threading.Thread):
             try:
                 self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
                 try:
+                    self.power.append(nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
+                except Exception:
+                    pass
+                try:
                     r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
                 except Exception:
                     r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
@@ -85,15 +93,17 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(nm)
             except Exception:
                 pass
-            self._stop_evt.wait(0.2)
+            self._stop_evt.wait(0.02)
 
     def stop(self):
         self._stop_evt.set()
         if self.is_alive():
             self.join(timeout=2)
         s = sorted(self.samples)
+        pw = sorted(self.power)
         return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
-                "samples": len(s)}
+                "samples": len(s), "power_w_median": (round(pw[len(pw) // 2], 1) if pw else None),
+                "power_w_max": (round(pw[-1], 1) if pw else None)}
 
 
 def build_model(name):
@@ -143,6 +153,20 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     Engine.init()
+    gpu_baseline = None
+    if not args.no_gpu_baseline:
+        # the GPU bar BASELINE.json names: PyTorch (cuDNN/cuBLAS kernels, NCCL DDP) on the same model, per-GPU batch,
+        # optimizer, step count and box, captured in a CUDA graph like our own step; measured first, in this process
+        try:
+            from benchmarks.ddp_baseline import measure
+
+            smp = ClockSampler(local_rank)
+            smp.start()
+            gpu_baseline = measure(args.model, args.batch, args.steps, args.warmup)
+            gpu_baseline["clocks"] = smp.stop()
+        except Exception as e:  # noqa: BLE001 - the baseline must never take the product's measurement down
+            gpu_baseline = {"impl": "torch_ddp_cudnn", "unavailable": str(e).splitlines()[0][:200]}
+        torch.cuda.synchronize()
     if args.backend:
         config.set("bigdl.parameter.backend", args.backend)
     for kv in args.set or []:                  # e.g. --set bigdl.parameter.p2p=monolithic (A/B runs)
@@ -209,6 +233,22 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_max = float(t)
     sync_backend = sync.backend
+    # ---------------- multi-GPU correctness the driver can see: every rank must hold the same compute weights
+    crc_equal = None
+    if world > 1:
+        sync.ensure_weights_current()
+        torch.cuda.synchronize()
+        import zlib
+
+        crc = zlib.crc32(flat.compute.view(torch.int16).cpu().numpy().tobytes())
+        every = [None] * world
+        dist.all_gather_object(every, crc)
+        crc_equal = len(set(every)) == 1
+    plane = getattr(sync, "_plane", None)
+    comm_stats = None
+    if plane is not None:
+        comm_stats = {"buckets": plane.nb, "bucket_launches_inside_backward_per_step": sum(
+            1 for b in plane.buckets if b.index > 0 and b.first is not None), "allgather": "push" if plane.publish == 8 else "pull"}
     del sync
 
     # ---------------- end-to-end through the public API: pinned host batch -> H2D every step, loss D2H every step
@@ -245,6 +285,59 @@ def run_ours(args):
                "h2d_bytes_per_step": int(hx.numel() * 4 + hy.numel() * 4), "d2h_bytes_per_step": 4,
                "ms_per_step": round(ms2 / K, 3)}
 
+    # ---------------- exposed communication: the same captured step with the peers taken out (every kernel of the plane
+    # sees a world of one rank: no NVLink traffic, no waiting on other GPUs), device-timed the same way. Last, because it
+    # lets the ranks' weights drift apart.
+    exposed = None
+    if world > 1 and not args.no_comm_probe and use_graph:
+        sync2 = model.__dict__.get("_param_sync_keepalive") or getattr(opt, "_param_sync", None) if not args.no_e2e else None
+        try:
+            from bigdl_b200.optim.graph_step import GraphedTrainStep
+
+            sync3 = AllReduceParameter(flat, backend=None, root=model).init() if sync2 is None else sync2
+            pl = getattr(sync3, "_plane", None)
+            if pl is not None:
+                def timed(gs):
+                    for _ in range(W):
+                        gs.run()
+                    barrier()
+                    a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a.record()
+                    for _ in range(K):
+                        gs.run()
+                    b_.record()
+                    barrier()
+                    tt = torch.tensor([a.elapsed_time(b_)], dtype=torch.float64, device=dev)
+                    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                    return float(tt) / K
+
+                full_ms = timed(GraphedTrainStep(model, criterion, sync3, make_optim(K + W), x, y, world))
+                # communication kernels alone (all buckets, nothing to overlap with): achieved NVLink rate
+                om2 = make_optim(K + W)
+                barrier()
+                a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record()
+                for _ in range(K):
+                    sync3.begin_step([om2], world, None)
+                    sync3.end_step()
+                b_.record()
+                barrier()
+                tt = torch.tensor([a.elapsed_time(b_)], dtype=torch.float64, device=dev)
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                comm_ms = float(tt) / K
+                pl.dry = True
+                dry_ms = timed(GraphedTrainStep(model, criterion, sync3, make_optim(K + W), x, y, world))
+                pl.dry = False
+                nv_bytes = flat.numel * 2 * (world - 1) / world          # bf16 in (reduce) = bf16 out (weights), per GPU
+                exposed = {"step_ms": round(full_ms, 3), "step_ms_without_peers": round(dry_ms, 3),
+                           "exposed_comm_pct": round(max(0.0, (full_ms - dry_ms) / full_ms * 100), 2),
+                           "comm_kernels_alone_ms": round(comm_ms, 3),
+                           "nvlink_bytes_per_direction_per_gpu_per_step": int(nv_bytes),
+                           "nvlink_GBps_per_direction_when_alone": round(nv_bytes / (comm_ms / 1e3) / 1e9, 1),
+                           "nvlink_measured_peer_copy_GBps": 770}
+        except Exception as e:  # noqa: BLE001
+            exposed = {"unavailable": str(e).splitlines()[0][:200]}
+
     value = B * world * K / (ms_max / 1e3)
     if rank == 0:
         print(json.dumps({
@@ -257,7 +350,12 @@ def run_ours(args):
                        "parallelism": f"dp{world}", "optimizer": "SGD(momentum 0.9, wd 1e-4, Poly 0.5)",
                        "criterion": "ClassNLLCriterion", "parameter_backend": sync_backend, "cuda_graph": use_graph,
                        "l2_policy": "per-step activations+weights (>2 GB) exceed the 126 MB L2; no explicit flush"},
-            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "host_issue_ms_per_step": round(host_issue_ms, 3), "final_loss": round(final_loss, 4),
+            "clocks": clocks, "e2e": e2e, "gpu_baseline": gpu_baseline,
+            "vs_gpu_baseline": (round(value / gpu_baseline["value"], 3) if gpu_baseline and gpu_baseline.get("value") else None),
+            "e2e_vs_gpu_baseline": (round(e2e["value"] / gpu_baseline["value"], 3)
+                                    if e2e and gpu_baseline and gpu_baseline.get("value") else None),
+            "weights_crc_equal_across_ranks": crc_equal, "comm": comm_stats, "exposed_comm": exposed,
+            "gpu_launches": launches, "host_issue_ms_per_step": round(host_issue_ms, 3), "final_loss": round(final_loss, 4),
             "impl": "ours",
         }))
     if world > 1:

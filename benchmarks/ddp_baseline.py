@@ -64,6 +64,87 @@ def _model(name):
     return _LS(m)
 
 
+def measure(model_name: str, batch: int, steps: int, warmup: int, use_graph: bool = True):
+    """Device-timed images/s of PyTorch (cuDNN/cuBLAS, bf16 autocast, channels_last, fused SGD; DDP over NCCL when
+    WORLD_SIZE > 1) on the same model, per-GPU batch, optimizer and step count as bench.py's own arm. The whole step is
+    captured in a CUDA graph when that works (so the comparison is graph vs graph, not graph vs eager launch overhead);
+    the result says which form ran. Expects the process group to exist already when world > 1."""
+    import torch.distributed as dist
+
+    world = dist.get_world_size() if dist.is_initialized() else 1
+    dev = torch.device("cuda", torch.cuda.current_device())
+    torch.backends.cudnn.benchmark = True
+    m = _model(model_name).cuda().to(memory_format=torch.channels_last)
+    if world > 1:
+        m = nn.parallel.DistributedDataParallel(m, device_ids=[dev.index], gradient_as_bucket_view=True)
+    try:
+        opt = torch.optim.SGD(m.parameters(), lr=0.01, momentum=0.9, weight_decay=1e-4, fused=True)
+    except Exception:  # noqa: BLE001 - older builds
+        opt = torch.optim.SGD(m.parameters(), lr=0.01, momentum=0.9, weight_decay=1e-4)
+    x = torch.randn(batch, 3, 224, 224, device=dev).contiguous(memory_format=torch.channels_last)
+    y = torch.randint(0, 1000, (batch,), device=dev)
+
+    def body():
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            out = m(x)
+        loss = F.nll_loss(out.float(), y)
+        opt.zero_grad(set_to_none=False)
+        loss.backward()
+        opt.step()
+        return loss
+
+    graphed = False
+    step = body
+    graph_error = None
+    if use_graph and world > 1:
+        # capturing DDP's NCCL buckets failed on this stack and left the CUDA RNG in capture state; the baseline's steps
+        # are GPU-bound (>= 15 ms of kernels against ~10 ms of host issue), so eager issue does not handicap it
+        use_graph, graph_error = False, "DDP steps are issued eagerly (GPU-bound; graph capture of DDP is not reliable here)"
+    if use_graph:
+        try:
+            s = torch.cuda.Stream()
+            s.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s):
+                for _ in range(11 if world > 1 else 3):       # DDP needs its bucket rebuild done before capture
+                    body()
+            torch.cuda.current_stream().wait_stream(s)
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                static_loss = body()
+            step = lambda: (g.replay(), static_loss)[1]       # noqa: E731
+            graphed = True
+        except Exception as e:  # noqa: BLE001 - fall back to eager issue
+            torch.cuda.synchronize()
+            graph_error = str(e).splitlines()[0][:160]
+            step = body
+    for _ in range(warmup):
+        step()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    res = {"impl": "torch_ddp_cudnn", "value": round(batch * world * steps / (float(ms) / 1e3), 2), "unit": "images/s",
+           "ms_per_step": round(float(ms) / steps, 3), "n_gpus": world, "per_gpu_batch": batch, "steps": steps,
+           "warmup": warmup, "dtype": "bf16 autocast, channels_last", "cuda_graph": graphed,
+           "optimizer": "torch.optim.SGD(momentum 0.9, wd 1e-4, fused)"}
+    if graph_error is not None:
+        res["graph_note"] = graph_error
+    del m, opt
+    torch.cuda.empty_cache()
+    return res
+
+
 def run(args):
     import torch.distributed as dist
 
@@ -72,46 +153,11 @@ def run(args):
     lr = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(lr)
     if world > 1:
-        dist.init_process_group("nccl")
-    torch.backends.cudnn.benchmark = True
-    m = _model(args.model).cuda().to(memory_format=torch.channels_last)
-    if world > 1:
-        m = nn.parallel.DistributedDataParallel(m, device_ids=[lr], gradient_as_bucket_view=True)
-    opt = torch.optim.SGD(m.parameters(), lr=0.01, momentum=0.9, weight_decay=1e-4)
-    B = args.batch
-    x = torch.randn(B, 3, 224, 224, device="cuda").contiguous(memory_format=torch.channels_last)
-    y = torch.randint(0, 1000, (B,), device="cuda")
-
-    def step():
-        with torch.autocast("cuda", dtype=torch.bfloat16):
-            out = m(x)
-        loss = F.nll_loss(out.float(), y) if out.dtype != torch.float32 or True else None
-        opt.zero_grad(set_to_none=True)
-        loss.backward()
-        opt.step()
-        return loss
-
-    for _ in range(args.warmup):
-        step()
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(args.steps):
-        step()
-    e1.record()
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    ms = torch.tensor([e0.elapsed_time(e1)], device="cuda", dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
+    res = measure(args.model, args.batch, args.steps, args.warmup, use_graph=not getattr(args, "no_graph", False))
     if rank == 0:
-        v = B * world * args.steps / (float(ms) / 1e3)
-        print(json.dumps({"impl": "torch_ddp_cudnn", "metric": "train images/sec", "value": round(v, 2),
-                          "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                          "ms_per_step": round(float(ms) / args.steps, 3), "dtype": "bf16 autocast",
-                          "config": {"model": args.model, "per_gpu_batch": B}}))
+        res["metric"] = "train images/sec"
+        res["config"] = {"model": args.model, "per_gpu_batch": args.batch}
+        print(json.dumps(res))
     if world > 1:
         dist.destroy_process_group()

@@ -187,6 +187,11 @@ class BucketedP2P:
         self._hooked = []
         self._launched = [False] * B
         self._pull_events = [None] * B
+        # "dry" instrument (bench.py exposed_comm_pct): the same launches with the peers taken out — every kernel sees a
+        # world of one rank (its own buffers), so no NVLink traffic and no waiting, only the local work
+        self.dry = False
+        me = self.rank
+        self._self_tables = tuple((ctypes.c_void_p * 1)(t[me]) for t in (self._g16_ptrs, self._w16_ptrs, self._flag_ptrs))
         self._step = None              # per-step launch context (set by begin_step)
         self._in_step = False
         self.stats = {"bucket_launches": 0, "pull_launches": 0, "overlapped": 0, "gathered_gemms": 0}
@@ -321,7 +326,7 @@ class BucketedP2P:
         main = torch.cuda.current_stream(self.device)
         self.comm.wait_stream(main)
         lib, w = _lib.cuda_lib(), self.world
-        if w > 1:
+        if w > 1 and not self.dry:
             with torch.cuda.stream(self.comm):
                 st = _lib.stream_ptr()
                 for b in self.buckets:
@@ -404,8 +409,9 @@ class BucketedP2P:
         main = torch.cuda.current_stream(self.device)
         self.comm.wait_stream(main)
         with torch.cuda.stream(self.comm):
+            g16t, w16t, flt = self._self_tables if self.dry else (self._g16_ptrs, self._w16_ptrs, self._flag_ptrs)
             _lib.check(lib.bdl_bucket_rs_update(
-                self._g16_ptrs, self._w16_ptrs, self._flag_ptrs, self.world, self.rank, b.off, b.length, start, length,
+                g16t, w16t, flt, 1 if self.dry else self.world, 0 if self.dry else self.rank, b.off, b.length, start, length,
                 self.flat.grads.data_ptr(), at(sync.weight_partition, poff), at(sync.gradient_partition, poff),
                 at(s0, poff - moff), at(s1, poff - moff), kind,
                 ctypes.cast(buf, ctypes.c_void_p) if buf is not None else None,

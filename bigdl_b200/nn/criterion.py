@@ -81,6 +81,25 @@ def _class_index(target: torch.Tensor) -> torch.Tensor:
     return target.reshape(-1).long() - 1
 
 
+def fuse_final_logsoftmax(model, criterion, on: bool = True) -> bool:
+    """Mark (or unmark) the model's final LogSoftMax so that, while training, a plain ClassNLLCriterion consumes the
+    logits directly through the fused cross-entropy kernels. Returns whether the pattern matched. Only the LAST module
+    of a (nested) Sequential qualifies: its output goes to the criterion and nowhere else."""
+    from .layers_core import LogSoftMax
+    from .module import Sequential
+
+    m = model
+    while type(m) is Sequential and m.modules:
+        m = m.modules[-1]
+    ok = (isinstance(m, LogSoftMax) and type(criterion) is ClassNLLCriterion and criterion.logProbAsInput)
+    if isinstance(m, LogSoftMax):
+        if on and ok:
+            m.__dict__["_defer_to_criterion"] = True
+        else:
+            m.__dict__.pop("_defer_to_criterion", None)
+    return bool(ok and on)
+
+
 class ClassNLLCriterion(Criterion):
     """Negative log-likelihood over log-probabilities (or probabilities when ``logProbAsInput`` is false, clipped to
     [1e-8, 1-1e-8]); 1-based targets; rows whose target equals ``paddingValue`` are ignored; optional class weights;
@@ -92,6 +111,13 @@ class ClassNLLCriterion(Criterion):
         self.size_average, self.logProbAsInput, self.paddingValue = size_average, logProbAsInput, paddingValue
 
     def updateOutput(self, input, target):
+        if getattr(input, "_bdl_logits", False) and self.logProbAsInput:
+            # the model's final LogSoftMax deferred to us (see LogSoftMax): fused log-softmax + NLL on the logits
+            from ..ops.functions import XentFn
+
+            if self.weights is not None and (self.__dict__.get("_w_dev") is None or self._w_dev.device != input.device):
+                self._w_dev = self.weights.to(input.device).contiguous()
+            return XentFn.apply(input, target, self.__dict__.get("_w_dev"), self.size_average, self.paddingValue)
         x = input if input.dim() > 1 else input.unsqueeze(0)
         x = x.float()
         if not self.logProbAsInput:

@@ -509,6 +509,10 @@ class SoftMax(Module):
     def updateOutput(self, input):
         dim = input.dim() - self.pos if input.dim() > 1 else 0
         dim = 1 if input.dim() in (2, 4) else (0 if input.dim() in (1, 3) else dim)
+        if native(input) and dim == input.dim() - 1:
+            from ..ops.functions import SoftmaxFn
+
+            return SoftmaxFn.apply(input, False, input.dtype if input.dtype in (torch.bfloat16, torch.float32) else torch.float32)
         return F.softmax(input.float(), dim=dim).to(input.dtype)
 
 
@@ -519,6 +523,20 @@ class SoftMin(Module):
 
 
 class LogSoftMax(Module):
+    """log(softmax(x)) over the class dimension (S/nn/LogSoftMax.scala). During training with a ClassNLLCriterion the
+    optimizer marks the model's final LogSoftMax ``_defer_to_criterion``: it then hands the logits through, tagged, and
+    the criterion runs the fused log-softmax + NLL kernels on them (csrc/loss_softmax.cu) — one pass over the logits
+    instead of a materialised log-probability tensor plus gather/sum kernels."""
+
     def updateOutput(self, input):
         dim = 1 if input.dim() >= 2 else 0
+        if (self.__dict__.get("_defer_to_criterion") and self.isTraining() and torch.is_grad_enabled() and native(input)
+                and input.dim() == 2):
+            out = input.view_as(input)
+            out._bdl_logits = True
+            return out
+        if native(input) and dim == input.dim() - 1:
+            from ..ops.functions import SoftmaxFn
+
+            return SoftmaxFn.apply(input, True, torch.float32)
         return F.log_softmax(input.float(), dim=dim)

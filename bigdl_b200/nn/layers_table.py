@@ -125,7 +125,7 @@ class Concat(Container):
             for st in side:
                 main.wait_stream(st)
         relu_all = all(bool(getattr(t, "_fuse_relu", False)) for t in tails)
-        return Fn.ConcatViewFn.apply(big, relu_all, *outs)
+        return Fn.ConcatViewFn.apply(big, relu_all, tails, *outs)
 
 
 class ConcatTable(Container):

@@ -126,6 +126,46 @@ def take_residual_hint():
 # ConcatViewFn.backward does that once for all branch tails of a Concat; the tails' ConvFn.backward picks its slice up
 # here instead of running its own column-sum pass. Cleared after every backward (join_side_streams).
 _PREMASKED: dict = {}
+_BIAS_DONE = object()            # _PREMASKED value: masked AND the bias gradient is already in the flat buffer
+_SUMS: dict = {}                 # persistent, self-clearing fp32 column-sum vectors, one per Concat (see _concat_sums)
+
+
+def _concat_sums(key, Ct: int, device) -> torch.Tensor:
+    """Zeroed fp32 [Ct] scratch owned by one Concat: ``_scatter_bias_grads`` clears it again after use, so no fill kernel
+    runs per step (it is allocated during the eager warm-up iterations that precede a graph capture)."""
+    k = (key, Ct, device.index)
+    t = _SUMS.get(k)
+    if t is None:
+        t = _SUMS[k] = torch.zeros(Ct, dtype=torch.float32, device=device)
+    return t
+
+
+def _tail_bias_grads(tails):
+    """Bias-gradient views of a Concat's branch tails when ONE scatter kernel may feed them all, else None."""
+    if not tails or len(tails) > 8:
+        return None
+    out = []
+    for t in tails:
+        b = t._parameters.get("bias")
+        if b is None or not b.requires_grad or b.grad is None or t.scaleB != 1.0 or not getattr(t, "_fuse_relu", False):
+            return None
+        out.append(b.grad)
+    return out
+
+
+def _scatter_bias_grads(sums: torch.Tensor, grads, sizes):
+    import ctypes
+
+    lib = _lib.cuda_lib()
+    n = len(grads)
+    dst = (ctypes.c_void_p * n)(*[g.data_ptr() for g in grads])
+    offs, c = [], 0
+    for sz in sizes:
+        offs.append(c)
+        c += sz
+    _lib.check(lib.bdl_scatter_acc_clear_f32(sums.data_ptr(), dst, (ctypes.c_int * n)(*offs), (ctypes.c_int * n)(*sizes),
+                                             n, _lib.stream_ptr()), "bdl_scatter_acc_clear_f32")
+    _lib.count_launch()
 
 
 class ConcatViewFn(Function):
@@ -137,9 +177,10 @@ class ConcatViewFn(Function):
     pitched pass per branch (four per Inception module), and hands out slices of the masked gradient."""
 
     @staticmethod
-    def forward(ctx, big, relu_all, *outs):
+    def forward(ctx, big, relu_all, tails, *outs):
         ctx.sizes = [o.shape[1] for o in outs]
         ctx.relu_all = bool(relu_all)
+        ctx.tails = list(tails) if tails else None        # the branches' last convolutions (bias-gradient owners)
         if ctx.relu_all:
             ctx.save_for_backward(big)
         return big.permute(0, 3, 1, 2)
@@ -147,6 +188,7 @@ class ConcatViewFn(Function):
     @staticmethod
     def backward(ctx, g):
         ready = ctx.__dict__.pop("_ready", None)
+        tail_grads = _tail_bias_grads(ctx.tails) if ctx.relu_all else None
         if ready is not None and ready[0].data_ptr() == g.data_ptr() and tuple(g.shape[2:]) == tuple(ready[0].shape[1:3]):
             sums = ready[1]              # the consumer's fan-out node already summed, masked and column-summed
         elif ctx.relu_all and g.is_cuda and g.dtype == torch.bfloat16:
@@ -154,19 +196,27 @@ class ConcatViewFn(Function):
             gn, ld = nhwc_pitched(g)
             N, H, W, Ct = gn.shape
             dz = torch.empty((N, H, W, Ct), dtype=torch.bfloat16, device=g.device)
-            sums = torch.zeros(Ct, dtype=torch.float32, device=g.device)
+            sums = _concat_sums(id(ctx.tails[0]), Ct, g.device) if tail_grads is not None else \
+                torch.zeros(Ct, dtype=torch.float32, device=g.device)
+            if ready is not None and tail_grads is not None:
+                sums.zero_()             # a parked result that was not ours to use left its sums in the shared vector
             ew.colsum(rows2d(gn, ld), sums, rows2d(big, Ct), rows2d(dz, Ct))
             g = dz.permute(0, 3, 1, 2)
         else:
             sums = None
+        done = False
+        if sums is not None and tail_grads is not None:
+            # one kernel feeds every tail's bias gradient and clears the vector (the tails then add nothing themselves)
+            _scatter_bias_grads(sums, tail_grads, ctx.sizes)
+            done = True
         grads, c = [], 0
         for n in ctx.sizes:
             sl = g[:, c:c + n]
             if sums is not None:
-                _PREMASKED[(sl.data_ptr(), tuple(sl.shape))] = sums[c:c + n]
+                _PREMASKED[(sl.data_ptr(), tuple(sl.shape))] = _BIAS_DONE if done else sums[c:c + n]
             grads.append(sl)
             c += n
-        return (None, None, *grads)
+        return (None, None, None, *grads)
 
 
 def _acc_grad(param: torch.Tensor, scale: float):
@@ -436,7 +486,7 @@ class ConvFn(Function):
         if pre is not None:
             # the Concat above already masked this slice with our ReLU output and summed its columns
             dz = dyn
-            if gb is not None:
+            if gb is not None and pre is not _BIAS_DONE:
                 pre.record_stream(torch.cuda.current_stream(dy.device))
                 gb.add_(pre, alpha=scale_b)
         elif relu:
@@ -572,7 +622,10 @@ class FanOutFn(Function):
             if x.is_contiguous(memory_format=torch.channels_last) and x.dtype == torch.bfloat16:
                 N, Ct, H, W = g0.shape
                 dz = torch.empty((N, H, W, Ct), dtype=torch.bfloat16, device=g0.device)
-                sums = torch.zeros(Ct, dtype=torch.float32, device=g0.device)
+                # the producer Concat scatters (and clears) this vector when all its tails qualify — same test as there
+                tails = getattr(prod, "tails", None)
+                sums = _concat_sums(id(tails[0]), Ct, g0.device) if _tail_bias_grads(tails) is not None else \
+                    torch.zeros(Ct, dtype=torch.float32, device=g0.device)
                 ew.colsum_sum_relu(gs, x, dz, sums)
                 prod._ready = (dz, sums)
                 return dz.permute(0, 3, 1, 2), None, None
@@ -739,6 +792,46 @@ class DropoutFn(Function):
             dy = dy.contiguous(memory_format=torch.channels_last) if len(ctx.xstride) == 4 and ctx.xstride[1] == 1 \
                 else dy.contiguous()
         return ew.dropout_bwd(dy, mask, ctx.p), None, None
+
+
+class SoftmaxFn(Function):
+    """SoftMax / LogSoftMax over the last dimension on the native row kernel (csrc/loss_softmax.cu); any leading shape.
+    ``out_dtype``: dtype of the result (LogSoftMax returns fp32 like the reference's float tensors)."""
+
+    @staticmethod
+    def forward(ctx, x, log_form, out_dtype):
+        lib = _lib.cuda_lib()
+        C = x.shape[-1]
+        x2 = x.reshape(-1, C)
+        if x2.stride(-1) != 1:
+            x2 = x2.contiguous()
+        if x2.dtype not in (torch.bfloat16, torch.float32):
+            x2 = x2.float()
+        y = torch.empty(x2.shape, dtype=out_dtype, device=x.device)
+        _lib.check(lib.bdl_softmax_fwd(x2.data_ptr(), y.data_ptr(), x2.shape[0], C, x2.stride(0), y.stride(0),
+                                       int(x2.dtype == torch.bfloat16), int(out_dtype == torch.bfloat16), int(log_form),
+                                       _lib.stream_ptr()), "bdl_softmax_fwd")
+        _lib.count_launch()
+        ctx.save_for_backward(y)
+        ctx.cfg = (log_form, x.shape, x.dtype)
+        return y.reshape(x.shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        log_form, shape, in_dtype = ctx.cfg
+        lib = _lib.cuda_lib()
+        C = y.shape[-1]
+        d2 = dy.reshape(-1, C)
+        if d2.dtype not in (torch.bfloat16, torch.float32):
+            d2 = d2.float()
+        d2 = d2.contiguous()
+        dx = torch.empty_like(d2)
+        _lib.check(lib.bdl_softmax_bwd(y.data_ptr(), d2.data_ptr(), dx.data_ptr(), y.shape[0], C, y.stride(0),
+                                       d2.stride(0), dx.stride(0), int(y.dtype == torch.bfloat16),
+                                       int(d2.dtype == torch.bfloat16), int(log_form), _lib.stream_ptr()), "bdl_softmax_bwd")
+        _lib.count_launch()
+        return dx.reshape(shape).to(in_dtype), None, None
 
 
 class XentFn(Function):

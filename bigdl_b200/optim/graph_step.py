@@ -33,6 +33,9 @@ class GraphedTrainStep:
         self.l2_clip = l2_clip
         dev = example_input.device
         self.device = dev
+        from ..nn.criterion import fuse_final_logsoftmax
+
+        fuse_final_logsoftmax(model, criterion)          # LogSoftMax + ClassNLL -> fused cross-entropy kernels
         self.x = torch.empty_like(example_input)
         self.y = torch.empty_like(example_target)
         self.x.copy_(example_input)

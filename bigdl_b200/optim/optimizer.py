@@ -408,6 +408,10 @@ def _train_loop(opt: Optimizer, distributed: bool, strategy_factory=None):
         raise RuntimeError("Detect multi-task run on one Executor/Container (bigdl.check.singleton)")
     model.checkDuplicate()
     model.training()
+    if next(iter(model.torch_parameters()), torch.zeros(0)).is_cuda:
+        from ..nn.criterion import fuse_final_logsoftmax
+
+        fuse_final_logsoftmax(model, criterion)      # LogSoftMax + ClassNLL -> fused cross-entropy kernels (training only)
     device = model.device()
     weights, grads = model.getParameters()
     flat = model._flat

@@ -418,6 +418,40 @@ extern "C" int bdl_bias_act_finish(float* acc, const float* bias, void* y, long 
   return bdl_check_launch("bias_act_finish_kernel");
 }
 
+// Bias gradients of the branch tails of a channel Concat: the fused ReLU-mask + column-sum pass leaves ONE fp32 vector
+// [Ctot]; this adds each tail's segment into that tail's bias-gradient slot of the flat gradient buffer and clears the
+// vector again, so it can be a persistent buffer (no fill kernel per step) and the tails issue no add of their own.
+struct ScatterSegs {
+  float* dst[8];
+  int off[8];
+  int len[8];
+  int count;
+};
+__global__ void scatter_acc_clear_kernel(float* __restrict__ src, const ScatterSegs sg) {
+  for (int k = 0; k < sg.count; ++k)
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < sg.len[k]; i += gridDim.x * blockDim.x) {
+      const float v = src[sg.off[k] + i];
+      src[sg.off[k] + i] = 0.f;
+      sg.dst[k][i] += v;
+    }
+}
+extern "C" int bdl_scatter_acc_clear_f32(float* src, void* const* dst, const int* off, const int* len, int count,
+                                         void* stream) {
+  if (count < 1 || count > 8) return bdl_fail("bdl_scatter_acc_clear_f32: 1..8 segments");
+  ScatterSegs sg{};
+  sg.count = count;
+  int longest = 0;
+  for (int k = 0; k < count; ++k) {
+    sg.dst[k] = static_cast<float*>(dst[k]);
+    sg.off[k] = off[k];
+    sg.len[k] = len[k];
+    if (len[k] > longest) longest = len[k];
+  }
+  const int blocks = longest > 1024 ? 4 : 1;
+  scatter_acc_clear_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(src, sg);
+  return bdl_check_launch("scatter_acc_clear_kernel");
+}
+
 extern "C" int bdl_counter_add(void* counter_dev, unsigned long long v, void* stream) {
   counter_add_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<unsigned long long*>(counter_dev), v);
   return bdl_check_launch("counter_add_kernel");

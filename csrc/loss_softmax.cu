@@ -190,6 +190,99 @@ extern "C" int bdl_xent_bwd(const void* logits, const void* target, const float*
   return bdl_check_launch("xent_bwd_kernel");
 }
 
+// ------------------------------------------------------------------------------------------------ row softmax
+// SoftMax / LogSoftMax over the last dimension of a [rows, C] matrix, one warp per row, fp32 math, bf16 or fp32 I/O
+// (reference: S/nn/SoftMax.scala, S/nn/LogSoftMax.scala:37-120, S/nn/mkldnn/SoftMax.scala). Used by the layers, by
+// Attention's score normalisation and (log form) wherever the loss cannot take the logits directly.
+namespace bdl {
+template <typename T> __device__ __forceinline__ float ld_as_f32(const T* p, long long i);
+template <> __device__ __forceinline__ float ld_as_f32<float>(const float* p, long long i) { return p[i]; }
+template <> __device__ __forceinline__ float ld_as_f32<__nv_bfloat16>(const __nv_bfloat16* p, long long i) {
+  return __bfloat162float(p[i]);
+}
+template <typename T> __device__ __forceinline__ void st_from_f32(T* p, long long i, float v);
+template <> __device__ __forceinline__ void st_from_f32<float>(float* p, long long i, float v) { p[i] = v; }
+template <> __device__ __forceinline__ void st_from_f32<__nv_bfloat16>(__nv_bfloat16* p, long long i, float v) {
+  p[i] = __float2bfloat16_rn(v);
+}
+
+template <typename TI, typename TO>
+__global__ void __launch_bounds__(256) softmax_fwd_kernel(const TI* __restrict__ x, TO* __restrict__ y, long long rows,
+                                                          int C, long long ldx, long long ldy, int log_form) {
+  const long long row = static_cast<long long>(blockIdx.x) * 8 + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  const TI* xr = x + row * ldx;
+  float m = -INFINITY;
+  for (int c = lane; c < C; c += 32) m = fmaxf(m, ld_as_f32(xr, c));
+  m = warp_max(m);
+  float s = 0.f;
+  for (int c = lane; c < C; c += 32) s += __expf(ld_as_f32(xr, c) - m);
+  s = warp_sum(s);
+  TO* yr = y + row * ldy;
+  if (log_form) {
+    const float ls = m + __logf(s);
+    for (int c = lane; c < C; c += 32) st_from_f32(yr, c, ld_as_f32(xr, c) - ls);
+  } else {
+    const float inv = 1.f / s;
+    for (int c = lane; c < C; c += 32) st_from_f32(yr, c, __expf(ld_as_f32(xr, c) - m) * inv);
+  }
+}
+
+// softmax: dx = y * (dy - sum(dy * y));   log-softmax: dx = dy - exp(y) * sum(dy)
+template <typename TY, typename TD>
+__global__ void __launch_bounds__(256) softmax_bwd_kernel(const TY* __restrict__ y, const TD* __restrict__ dy,
+                                                          TD* __restrict__ dx, long long rows, int C, long long ldy,
+                                                          long long ldd, long long ldx, int log_form) {
+  const long long row = static_cast<long long>(blockIdx.x) * 8 + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  const TY* yr = y + row * ldy;
+  const TD* dr = dy + row * ldd;
+  float s = 0.f;
+  for (int c = lane; c < C; c += 32) s += log_form ? ld_as_f32(dr, c) : ld_as_f32(dr, c) * ld_as_f32(yr, c);
+  s = warp_sum(s);
+  TD* xr = dx + row * ldx;
+  for (int c = lane; c < C; c += 32) {
+    const float yv = ld_as_f32(yr, c), dv = ld_as_f32(dr, c);
+    st_from_f32(xr, c, log_form ? dv - __expf(yv) * s : yv * (dv - s));
+  }
+}
+}  // namespace bdl
+
+// dtype codes: 0 = fp32, 1 = bf16
+extern "C" int bdl_softmax_fwd(const void* x, void* y, long long rows, int C, long long ldx, long long ldy, int in_bf16,
+                               int out_bf16, int log_form, void* stream_) {
+  if (rows <= 0 || C <= 0) return BDL_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream_);
+  const int blocks = static_cast<int>((rows + 7) / 8);
+  if (in_bf16 && out_bf16)
+    bdl::softmax_fwd_kernel<<<blocks, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), rows, C, ldx, ldy, log_form);
+  else if (in_bf16)
+    bdl::softmax_fwd_kernel<<<blocks, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), static_cast<float*>(y), rows, C, ldx, ldy, log_form);
+  else if (out_bf16)
+    bdl::softmax_fwd_kernel<<<blocks, 256, 0, st>>>(static_cast<const float*>(x), static_cast<__nv_bfloat16*>(y), rows, C, ldx, ldy, log_form);
+  else
+    bdl::softmax_fwd_kernel<<<blocks, 256, 0, st>>>(static_cast<const float*>(x), static_cast<float*>(y), rows, C, ldx, ldy, log_form);
+  return bdl_check_launch("softmax_fwd_kernel");
+}
+
+extern "C" int bdl_softmax_bwd(const void* y, const void* dy, void* dx, long long rows, int C, long long ldy, long long ldd,
+                               long long ldx, int y_bf16, int d_bf16, int log_form, void* stream_) {
+  if (rows <= 0 || C <= 0) return BDL_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream_);
+  const int blocks = static_cast<int>((rows + 7) / 8);
+  if (y_bf16 && d_bf16)
+    bdl::softmax_bwd_kernel<<<blocks, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), rows, C, ldy, ldd, ldx, log_form);
+  else if (y_bf16)
+    bdl::softmax_bwd_kernel<<<blocks, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(y), static_cast<const float*>(dy), static_cast<float*>(dx), rows, C, ldy, ldd, ldx, log_form);
+  else if (d_bf16)
+    bdl::softmax_bwd_kernel<<<blocks, 256, 0, st>>>(static_cast<const float*>(y), static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), rows, C, ldy, ldd, ldx, log_form);
+  else
+    bdl::softmax_bwd_kernel<<<blocks, 256, 0, st>>>(static_cast<const float*>(y), static_cast<const float*>(dy), static_cast<float*>(dx), rows, C, ldy, ldd, ldx, log_form);
+  return bdl_check_launch("softmax_bwd_kernel");
+}
+
 extern "C" int bdl_topk_correct(const void* logits, const void* target, void* counts, long long B, int C, long long ld,
                                 int logits_bf16, int target_i64, void* stream) {
   if (B <= 0 || C <= 0) return BDL_OK;

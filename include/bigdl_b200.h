@@ -84,6 +84,10 @@ int bdl_dropout_fwd_bf16(const void* x, void* y, void* mask, size_t n, float p, 
 int bdl_dropout_fwd_bf16_ctr(const void* x, void* y, void* mask, size_t n, float p, unsigned long long seed,
                              void* counter_dev, void* stream);
 int bdl_counter_add(void* counter_dev, unsigned long long v, void* stream);
+/* dst[k][0:len[k]) += src[off[k] : off[k]+len[k]) for up to 8 segments, then src is cleared (persistent scratch): the
+ * bias gradients of the branch tails of a Concat out of one fused column-sum vector.
+ * Reference: accGradParameters of S/nn/SpatialConvolution.scala:429-521 (gradBias). */
+int bdl_scatter_acc_clear_f32(float* src, void* const* dst, const int* off, const int* len, int count, void* stream);
 /* y = act(acc + bias) in bf16 from the fp32 accumulator of a split-K forward GEMM; re-zeroes acc for the next launch.
  * Reference: the bias add of S/nn/Linear.scala:93-103 (+ the fused ReLU of S/nn/mkldnn/Fusion.scala). */
 int bdl_bias_act_finish(float* acc, const float* bias, void* y, long long M, int N, long long ld_acc, long long ldy,
@@ -125,6 +129,13 @@ int bdl_lrn_fwd_nhwc_bf16(const void* x, void* y, long long pixels, int C, long 
 int bdl_lrn_bwd_nhwc_bf16(const void* x, const void* dy, void* dx, long long pixels, int C, long long ldx,
                           long long ldy, long long lddx, int size, float alpha, float beta, float k, void* stream);
 
+/* SoftMax / LogSoftMax over the last dimension of a [rows, C] matrix (one warp per row, fp32 math; dtype codes 0 = fp32,
+ * 1 = bf16; log_form selects LogSoftMax) and their backward from the OUTPUT y.
+ * Reference: S/nn/SoftMax.scala, S/nn/LogSoftMax.scala:37-120, S/nn/mkldnn/SoftMax.scala. */
+int bdl_softmax_fwd(const void* x, void* y, long long rows, int C, long long ldx, long long ldy, int in_bf16, int out_bf16,
+                    int log_form, void* stream);
+int bdl_softmax_bwd(const void* y, const void* dy, void* dx, long long rows, int C, long long ldy, long long ldd,
+                    long long ldx, int y_bf16, int d_bf16, int log_form, void* stream);
 /* ---- fused LogSoftMax + ClassNLL (csrc/loss_softmax.cu). Reference: S/nn/ClassNLLCriterion.scala:70-242,
  *      S/nn/CrossEntropyCriterion.scala:35-53, S/optim/ValidationMethod.scala:173,827.
  *      scratch: 3*B floats kept between fwd and bwd; out: {loss, total weight}. Targets are 1-based. */

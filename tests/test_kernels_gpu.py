@@ -356,3 +356,33 @@ def test_gru_fused_step_matches_reference():
     torch.autograd.backward([out_ref, hr_ref], [g1.bfloat16().float(), g2.bfloat16().float()])
     for a, b in zip((xt, hg, hc, h), f):
         _close(a.grad, b.grad, 4e-2, 4e-2)
+
+
+@pytest.mark.parametrize("log_form", [False, True])
+@pytest.mark.parametrize("shape,dtype", [((128, 1000), torch.bfloat16), ((7, 33), torch.float32), ((4, 12, 35, 35), torch.bfloat16)])
+def test_softmax_rows_native(shape, dtype, log_form):
+    """SoftMax / LogSoftMax row kernel (fwd + bwd from the output) vs fp32 torch."""
+    from bigdl_b200.ops.functions import SoftmaxFn
+    torch.manual_seed(3)
+    x = (torch.randn(*shape, device="cuda") * 3).to(dtype).requires_grad_(True)
+    out_dtype = torch.float32 if log_form else dtype
+    y = SoftmaxFn.apply(x, log_form, out_dtype)
+    dy = torch.randn(*shape, device="cuda").to(out_dtype)
+    y.backward(dy)
+    xr = x.detach().float().requires_grad_(True)
+    yr = torch.log_softmax(xr, -1) if log_form else torch.softmax(xr, -1)
+    yr.backward(dy.float())
+    tol = 2e-2 if dtype == torch.bfloat16 else 1e-5
+    assert torch.allclose(y.float(), yr, rtol=tol, atol=tol)
+    assert torch.allclose(x.grad.float(), xr.grad, rtol=5 * tol, atol=5 * tol)
+
+
+def test_scatter_acc_clear():
+    from bigdl_b200.ops.functions import _scatter_bias_grads
+    src = torch.arange(40, device="cuda", dtype=torch.float32)
+    a, b, c = torch.ones(8, device="cuda"), torch.ones(24, device="cuda"), torch.ones(8, device="cuda")
+    ref = src.clone()
+    _scatter_bias_grads(src, [a, b, c], [8, 24, 8])
+    torch.cuda.synchronize()
+    assert torch.equal(a, 1 + ref[:8]) and torch.equal(b, 1 + ref[8:32]) and torch.equal(c, 1 + ref[32:])
+    assert float(src.abs().max()) == 0.0

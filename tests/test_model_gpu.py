@@ -284,3 +284,73 @@ def test_checkpointing_does_not_disturb_gpu_training(tmp_path, graph):
 
     (wa, la), (wb, lb) = run(False), run(True)
     assert _rel(wb, wa) < 1e-6 and abs(la - lb) < 1e-6
+
+
+def test_epoch_schedule_advances_under_graph_replay():
+    """Round-1 advisor finding: restoring the optimizer state after the capture warm-ups replaced the state Table the
+    training loop aliases, so ``epoch`` stayed 1 for every epoch-based schedule under CUDA-graph replay. EpochStep must
+    drop the learning rate when the second epoch starts, with the graph on."""
+    from bigdl_b200.dataset.base import FixedMiniBatchDataSet, MiniBatch
+    from bigdl_b200.nn.criterion import ClassNLLCriterion
+    from bigdl_b200.nn.layer import Linear, LogSoftMax, ReLU, Sequential
+    from bigdl_b200.optim.optim_method import SGD, EpochStep
+    from bigdl_b200.optim.optimizer import Optimizer
+    from bigdl_b200.optim.trigger import MaxIteration
+    from bigdl_b200.utils import config
+    from bigdl_b200.utils.random_generator import RNG
+
+    config.set("bigdl.cudaGraph", True)
+    try:
+        RNG.setSeed(5)
+        m = Sequential().add(Linear(64, 32)).add(ReLU()).add(Linear(32, 8)).add(LogSoftMax()).cuda()
+        g = torch.Generator().manual_seed(2)
+        x, y = torch.randn(16, 64, generator=g), torch.randint(1, 9, (16,), generator=g).float()
+        om = SGD(0.1, learningrate_schedule=EpochStep(1, 0.1))
+        # epoch = 3 iterations of 16 records
+        opt = Optimizer(m, FixedMiniBatchDataSet(MiniBatch(x, y), 48, distributed=False), ClassNLLCriterion(),
+                        MaxIteration(7), 16, om)
+        rates = []
+        opt.setIterationCallback(lambda state, loss: rates.append((state["epoch"], om.getLearningRate(),
+                                                                   -om.learningRateSchedule.currentRate)))
+        opt.optimize()
+        assert opt.state["epoch"] == 3 and om.state["epoch"] == 3, (opt.state["epoch"], om.state["epoch"])
+        used = [r[2] for r in rates]
+        assert len(used) == 7 and used[0] > 0 and used[0] == used[1] == used[2], used
+        assert abs(used[3] / used[0] - 0.1) < 1e-5 and used[3] == used[4] == used[5], used
+        assert abs(used[6] / used[0] - 0.01) < 1e-5, used
+    finally:
+        config.unset("bigdl.cudaGraph")
+
+
+def test_final_logsoftmax_defers_to_fused_cross_entropy():
+    """Training step with LogSoftMax + ClassNLLCriterion: the fused xent kernels (logits handed through) and the
+    materialised log-probabilities give the same loss and the same gradients."""
+    from bigdl_b200.nn.criterion import ClassNLLCriterion, fuse_final_logsoftmax
+    from bigdl_b200.nn.layer import Linear, LogSoftMax, ReLU, Sequential
+    from bigdl_b200.utils.random_generator import RNG
+
+    RNG.setSeed(9)
+    m = Sequential().add(Linear(64, 48)).add(ReLU()).add(Linear(48, 24)).add(LogSoftMax()).cuda()
+    m.training()
+    crit = ClassNLLCriterion()
+    x = torch.randn(32, 64, device="cuda")
+    y = torch.randint(1, 25, (32,), device="cuda").float()
+    res = {}
+    for fused in (False, True):
+        assert fuse_final_logsoftmax(m, crit, on=fused) == fused
+        m.zeroGradParameters()
+        with torch.enable_grad():
+            out = m._call(x)
+            loss = crit._call(out, y)
+        torch.autograd.backward(loss)
+        res[fused] = (float(loss), torch.cat([p.grad.flatten().clone() for p in m.torch_parameters()]))
+        assert getattr(out, "_bdl_logits", False) == fused
+    fuse_final_logsoftmax(m, crit, on=False)
+    assert abs(res[True][0] - res[False][0]) < 2e-3 * abs(res[False][0]) + 1e-4
+    assert _rel(res[True][1], res[False][1]) < 2e-2
+    # not while evaluating: the layer's output is log-probabilities again
+    fuse_final_logsoftmax(m, crit, on=True)
+    m.evaluate()
+    out = m.forward(x)
+    assert abs(float(out.float().exp().sum(1).mean()) - 1.0) < 1e-2
+    fuse_final_logsoftmax(m, crit, on=False)

@@ -102,3 +102,69 @@ def gemm_fp8(a_q: torch.Tensor, b_q: torch.Tensor, col_scale: torch.Tensor, *, k
     _lib.check(rc, "bdl_gemm_fp8")
     _lib.count_launch()
     return out
+
+
+# ---------------------------------------------------------------------------------------------- MX block scaling
+def mx_sf_bytes(rows: int, cols: int) -> int:
+    return ((rows + 127) // 128) * ((cols + 127) // 128) * 512
+
+
+def _mx_sf_index(rows: int, cols: int, device="cpu") -> torch.Tensor:
+    """[rows, ceil(cols/32)] -> byte offset of each scale inside the atom buffer (csrc/quantize.cu layout)."""
+    kb = (cols + 31) // 32
+    kg = (cols + 127) // 128
+    r = torch.arange(rows, device=device).unsqueeze(1)
+    k = torch.arange(kb, device=device).unsqueeze(0)
+    return ((r // 128) * kg + k // 4) * 512 + (r % 32) * 16 + ((r % 128) // 32) * 4 + (k % 4)
+
+
+def quantize_mxfp8(x2d: torch.Tensor):
+    """e4m3 bytes [rows, ceil16(cols)] + UE8M0 scale atoms, one scale per (row, 32 consecutive columns):
+    scale = smallest power of two with max|block| / scale <= 448. CPU tensors take the same rule in torch."""
+    rows, cols = x2d.shape
+    cp = (cols + 15) // 16 * 16
+    if not x2d.is_cuda:
+        kb = (cols + 31) // 32
+        xp = torch.zeros(rows, kb * 32)
+        xp[:, :cols] = x2d.detach().float()
+        am = xp.reshape(rows, kb, 32).abs().amax(-1)
+        e = torch.where(am > 0, torch.ceil(torch.log2(am / E4M3_MAX)), torch.zeros_like(am)).clamp(-127, 127) + 127
+        inv = torch.exp2(127 - e).unsqueeze(-1)
+        v = (xp.reshape(rows, kb, 32) * inv).clamp(-E4M3_MAX, E4M3_MAX).reshape(rows, kb * 32)[:, :cols]
+        q = torch.zeros(rows, cp, dtype=torch.uint8)
+        q[:, :cols] = v.to(torch.float8_e4m3fn).view(torch.uint8)
+        sf = torch.full((mx_sf_bytes(rows, cols),), 127, dtype=torch.uint8)
+        sf[_mx_sf_index(rows, cols).reshape(-1)] = e.to(torch.uint8).reshape(-1)
+        return q, sf
+    lib = _lib_or_die()
+    assert x2d.stride(1) == 1 and x2d.dtype in (torch.float32, torch.bfloat16)
+    q = (torch.empty if cp == cols else torch.zeros)((rows, cp), dtype=torch.uint8, device=x2d.device)
+    sf = torch.empty(mx_sf_bytes(rows, cols), dtype=torch.uint8, device=x2d.device)
+    _lib.check(lib.bdl_quantize_mxfp8(x2d.data_ptr(), q.data_ptr(), sf.data_ptr(), rows, cols, x2d.stride(0), cp,
+                                      int(x2d.dtype == torch.bfloat16), _lib.stream_ptr()), "bdl_quantize_mxfp8")
+    _lib.count_launch()
+    return q, sf
+
+
+def dequantize_mxfp8(q: torch.Tensor, sf: torch.Tensor, cols: int) -> torch.Tensor:
+    """fp32 [rows, cols] that the block-scaled operand (q, sf) represents exactly."""
+    rows = q.shape[0]
+    e = sf[_mx_sf_index(rows, cols, sf.device).reshape(-1)].reshape(rows, -1).float()
+    scale = torch.exp2(e - 127).repeat_interleave(32, dim=1)[:, :cols]
+    return q[:, :cols].view(torch.float8_e4m3fn).float() * scale
+
+
+def gemm_mxfp8(a_q: torch.Tensor, sfa: torch.Tensor, b_q: torch.Tensor, sfb: torch.Tensor, k: int, *, bias=None,
+               relu: bool = False, out: torch.Tensor | None = None, out_dtype=torch.bfloat16):
+    """D = A B^T for block-scaled e4m3 operands (``quantize_mxfp8``); the tensor core applies the per-block scales."""
+    lib = _lib_or_die()
+    m, n = a_q.shape[0], b_q.shape[0]
+    if out is None:
+        out = torch.empty((m, n), device=a_q.device, dtype=out_dtype)
+    flags = (BIAS if bias is not None else 0) | (RELU if relu else 0)
+    rc = lib.bdl_gemm_mxfp8(a_q.data_ptr(), b_q.data_ptr(), sfa.data_ptr(), sfb.data_ptr(), out.data_ptr(), _lib.ptr(bias),
+                            m, n, k, a_q.stride(0), b_q.stride(0), out.stride(0), int(out.dtype == torch.float32), flags,
+                            _lib.stream_ptr())
+    _lib.check(rc, "bdl_gemm_mxfp8")
+    _lib.count_launch()
+    return out

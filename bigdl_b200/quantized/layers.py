@@ -58,7 +58,7 @@ class QuantizedModule(Module):
 
     def _out_qscale(self):
         c = self._emit_q
-        if c is None or not c.static_scale or c.calibrating:
+        if c is None or not c.static_scale or c.calibrating or getattr(c, "block_scale", False):
             return None
         qs = c.__dict__.get("_in_qscale")
         if qs is None or qs.device != c._buffers["input_absmax"].device:
@@ -102,12 +102,47 @@ class Linear(QuantizedModule):
         self._fuse_relu = False
         self._init_quant_state()
 
+    def enable_block_scale(self, w: torch.Tensor | None = None):
+        """Switch to MX block scaling: e4m3 with one power-of-two scale per 32 consecutive inputs, for the weights (stored)
+        and the activations (quantised per call by ONE kernel: no abs-max pass, no calibration), multiplied by
+        ``tcgen05.mma.kind::mxf8f6f4.block_scale``. The scale follows the data block by block like BigQuant's per-window
+        ("local") thresholds do (core/bigquant/native/ops/shuffle/shuffle_im2col.h)."""
+        if w is None:
+            w = self.__dict__.pop("_w_float", None)      # the float weights, when the Quantizer is still converting
+        if w is None:
+            w = self.dequantized_weight()
+        wq, sf = Q.quantize_mxfp8(w.float().contiguous())
+        self.static_scale = False
+        self._buffers["weight_q"], self._buffers["weight_sf"] = wq, sf
+        self.block_scale = True
+        return self
+
+    def _block_scale_forward(self, x):
+        lead = x.shape[:-1]
+        K = self.input_size
+        x2 = x.detach().reshape(-1, K)
+        if native(x):
+            if x2.dtype != torch.bfloat16:
+                x2 = x2.to(torch.bfloat16)
+            xq, sfa = Q.quantize_mxfp8(x2.contiguous())
+            y = Q.gemm_mxfp8(xq, sfa, self._buffers["weight_q"], self._buffers["weight_sf"], K,
+                             bias=self._buffers["bias"], relu=self._fuse_relu)
+        else:
+            xq, sfa = Q.quantize_mxfp8(x2.float())
+            xd = Q.dequantize_mxfp8(xq, sfa, K)
+            wd = Q.dequantize_mxfp8(self._buffers["weight_q"].cpu(), self._buffers["weight_sf"].cpu(), K)
+            y = F.linear(xd, wd, self._buffers["bias"].cpu())
+            if self._fuse_relu:
+                y = F.relu(y)
+        return y.reshape(*lead, self.output_size)
+
     @classmethod
     def from_float(cls, m) -> "Linear":
         q = cls(m.input_size, m.output_size, m.with_bias)
         w = m.weight.detach().float()
         wq, am = _quantize_weight(w)
         q._buffers["weight_q"], q._buffers["weight_absmax"] = wq, am
+        q.__dict__["_w_float"] = w               # dropped by Quantizer.quantize once the scaling mode is settled
         if m.with_bias:
             q._buffers["bias"] = m.bias.detach().float().clone()
         else:
@@ -118,11 +153,16 @@ class Linear(QuantizedModule):
         return q
 
     def dequantized_weight(self) -> torch.Tensor:
+        if getattr(self, "block_scale", False):
+            return Q.dequantize_mxfp8(self._buffers["weight_q"], self._buffers["weight_sf"], self.input_size)
         return Q.dequantize_e4m3(self._buffers["weight_q"], self._buffers["weight_absmax"], per_row=True)[
             :, :self.input_size]
 
     def updateOutput(self, input):
         x = input
+        if getattr(self, "block_scale", False) and x.dtype != torch.uint8:
+            with torch.no_grad():
+                return self._block_scale_forward(x)
         lead = x.shape[:-1]
         K = self.input_size
         if native(x):

@@ -22,7 +22,7 @@ class Quantizer:
         cls._registry[float_cls] = quant_cls
 
     @classmethod
-    def quantize(cls, model: Module, fold_bn: bool = True) -> Module:
+    def quantize(cls, model: Module, fold_bn: bool = True, block_scale: bool | None = None) -> Module:
         """Returns a quantised deep copy in evaluate mode (AbstractModule.quantize clones first, S/nn/abstractnn/
         AbstractModule.scala:920-928)."""
         from ..nn.fusion import fold_bn as do_fold, fuse, unfuse
@@ -41,6 +41,20 @@ class Quantizer:
         _fuse_through_identities(m)
         out = cls._convert(m)
         out.evaluate()
+        if block_scale is None:
+            from ..utils import config
+
+            block_scale = bool(config.get("bigdl.quantized.blockScale"))
+        if block_scale:
+            # MX block scaling for the fully-connected layers (tcgen05 kind::mxf8f6f4.block_scale): per-32-element
+            # power-of-two scales computed on the fly, so these layers need neither abs-max passes nor calibration
+            from .layers import Linear as QLinear
+
+            for l in cls.quantized_layers(out):
+                if isinstance(l, QLinear):
+                    l.enable_block_scale()
+        for l in cls.quantized_layers(out):
+            l.__dict__.pop("_w_float", None)
         if any(l.static_scale for l in cls.quantized_layers(out)):
             cls.link_chains(out)
         if dev.type == "cuda" and out.torch_parameters():
@@ -101,7 +115,8 @@ class Quantizer:
         input channel count needs no padding (so the e4m3 tensor can be consumed in place). Returns the link count."""
         n = 0
         for a, b in _effective_pairs(model):
-            if isinstance(a, QL.QuantizedModule) and isinstance(b, QL.QuantizedModule) and b.static_scale:
+            if isinstance(a, QL.QuantizedModule) and isinstance(b, QL.QuantizedModule) and b.static_scale \
+                    and not getattr(b, "block_scale", False) and not getattr(a, "block_scale", False):
                 if isinstance(b, QL.SpatialConvolution):
                     ok = isinstance(a, QL.SpatialConvolution) and a.n_output_plane == b.n_input_plane and \
                         b.n_input_plane % 16 == 0 and b.n_group == 1 and b.data_format == a.data_format

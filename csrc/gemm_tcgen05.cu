@@ -87,6 +87,10 @@ struct GemmParams {
   int dual_m;                // one CTA owns two stacked 128-row tiles (both TMEM accumulator stages), so the B operand
                              // is fetched from L2 once per 256 output rows (bf16 kernels only)
   int cv_aw;                 // channels per gathered atom: 64 (128B swizzle) or, for C <= 32, 32 / 16 (64B / 32B swizzle)
+  // block-scaled fp8 (kFp8 plain GEMM only): UE8M0 scale bytes per (row, 32 k) in 512-byte atoms of 128 rows x 4 k
+  // blocks, [row block][k group] (csrc/quantize.cu). Non-null = tcgen05.mma.kind::mxf8f6f4.block_scale.
+  const uint8_t* mx_sfa;
+  const uint8_t* mx_sfb;
   int group_m;               // tile rasterisation: > 0 walks the output in bands of group_m m-tiles, m fastest inside a
                              // band, so the tiles in flight at one time share few A row-blocks AND few B column-blocks
                              // (L2 working set ~ (group_m + W / group_m) operand panels instead of 1 + tiles_n)
@@ -325,6 +329,9 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tmA, const 
   const uint32_t a_bytes = BM * BK * 2 * (kDual ? 2 : 1);
   const uint32_t b_bytes = static_cast<uint32_t>(p.b_rows) * BK * 2;
   const uint32_t stage_bytes = a_bytes + b_bytes;
+  // block-scaled fp8: 2 x 512-byte scale-factor atoms per stage, behind the operand ring (and the store staging)
+  const uint32_t sf_region = tiles + static_cast<uint32_t>(p.num_stages) * stage_bytes +
+                             (kTmaStore ? static_cast<uint32_t>(8 * 4096) : 0u);
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.num_stages; ++s) {
@@ -555,7 +562,7 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tmA, const 
               tma_load_2d_pair(sb, &tmB, fb, k0, n0);
             }
           } else {
-          mbar_expect_tx(fb, stage_bytes);
+          mbar_expect_tx(fb, stage_bytes + ((kFp8 && kConv == 0 && p.mx_sfa) ? 1024u : 0u));
           if (kAMN) {
             // A stored [K, M]: two boxes of {64 m, 64 k}
             tma_load_2d(sa, &tmA, fb, m0, k0);
@@ -574,6 +581,12 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tmA, const 
             tma_load_2d(sb, ag_src, fb, k0, n0);   // the owner's copy of this weight tile (local map for my own rows)
           } else {
             tma_load_2d(sb, &tmB, fb, k0, n0);  // box {64 k, block_n}
+          }
+          if (kFp8 && kConv == 0 && p.mx_sfa) {
+            // scale-factor atoms of this k group: A rows [m0, +128) and B rows [n0, +128) (block_n <= 128 here)
+            const uint32_t sfs = sf_region + static_cast<uint32_t>(stage) * 1024u;
+            bulk_load_1d(sfs, p.mx_sfa + (static_cast<long long>(m0 >> 7) * num_kb + kb) * 512, 512u, fb);
+            bulk_load_1d(sfs + 512u, p.mx_sfb + (static_cast<long long>(n0 >> 7) * num_kb + kb) * 512, 512u, fb);
           }
           }
           if (++stage == p.num_stages) {
@@ -650,7 +663,21 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tmA, const 
                                         : make_smem_desc_sw128(sa + k * 32u, 16u, 1024u);
             const uint64_t bdesc = kBMN ? make_smem_desc_sw128(sb + k * 2048u, 8192u, 1024u)
                                         : make_smem_desc_sw128(sb + k * 32u, 16u, 1024u);
-            if (kTwo) {
+            if (kFp8 && kConv == 0 && p.mx_sfa) {
+              // scale factors of this k group: shared -> TMEM once per stage (tcgen05.cp and tcgen05.mma execute in
+              // issue order, so the copy cannot overtake the previous stage's MMAs), then one MMA per 32-element block
+              // with the block's scale-byte index in the instruction descriptor
+              const uint32_t sfa_t = tmem_base + 128u, sfb_t = tmem_base + 132u;
+              if (k == 0) {
+                const uint32_t sfs = sf_region + static_cast<uint32_t>(stage) * 1024u;
+                utccp_sf(sfa_t, make_smem_desc(sfs, 0u, 128u, 0u));
+                utccp_sf(sfb_t, make_smem_desc(sfs + 512u, 0u, 128u, 0u));
+              }
+              const uint32_t idesc_mx = (static_cast<uint32_t>(k) << 4) | (static_cast<uint32_t>(p.block_n >> 3) << 17) |
+                                        (1u << 23) | (static_cast<uint32_t>(BM >> 4) << 24) |
+                                        (static_cast<uint32_t>(k) << 29);
+              umma_mxf8(d_tmem, adesc, bdesc, idesc_mx, sfa_t, sfb_t, (kb > kb0 || k > 0) ? 1u : 0u);
+            } else if (kTwo) {
               if (kFp8) umma_f8_pair(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
               else umma_f16_pair(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
             } else if (kFp8)
@@ -1462,6 +1489,58 @@ extern "C" int bdl_gemm_fp8(const void* A, const void* B, void* D, const float* 
     kfn<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, tma_out ? tmD : tmA, p);
   }
   return bdl_check_launch("gemm_tcgen05_kernel<fp8>");
+}
+
+// ------------------------------------------------------------------------------------------------ block-scaled fp8
+// D[M,N] = sum over 32-wide k blocks of (A_q 2^(sfa-127)) (B_q 2^(sfb-127))^T (+bias)(ReLU): e4m3 operands with one
+// UE8M0 scale per (row, 32 k), multiplied by tcgen05.mma.kind::mxf8f6f4.block_scale with the scale bytes staged in TMEM.
+// A_q [M, lda] / B_q [N, ldb]: e4m3 bytes, K-major, pitches multiples of 16 with zeroed padding; sfa / sfb: scale atoms
+// from bdl_quantize_mxfp8. Reference: BigQuant's per-window ("local") scales, core/bigquant/native/ops/shuffle/
+// shuffle_im2col.h and S/nn/quantized/Quantization.scala:35-62; S/nn/quantized/Linear.scala.
+extern "C" int bdl_gemm_mxfp8(const void* A, const void* B, const void* sfa, const void* sfb, void* D, const float* bias,
+                              int M, int N, int K, long long lda, long long ldb, long long ldd, int out_fp32, int flags,
+                              void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (M <= 0 || N <= 0 || K <= 0) return bdl_fail("bdl_gemm_mxfp8: empty problem");
+  if ((reinterpret_cast<uintptr_t>(A) & 15u) || (reinterpret_cast<uintptr_t>(B) & 15u) || (lda % 16) || (ldb % 16))
+    return bdl_fail("bdl_gemm_mxfp8: operands must be 16-byte aligned with pitches that are multiples of 16 bytes");
+  if (!sfa || !sfb || (reinterpret_cast<uintptr_t>(sfa) & 15u) || (reinterpret_cast<uintptr_t>(sfb) & 15u))
+    return bdl_fail("bdl_gemm_mxfp8: scale-factor atoms must be 16-byte aligned");
+  if (flags & BDL_GEMM_ATOMIC_ADD) return bdl_fail("bdl_gemm_mxfp8: inference kernel, no accumulate mode");
+  if (out_fp32 == 2) return bdl_fail("bdl_gemm_mxfp8: bf16 or fp32 output");
+  const int num_sms = bdl_num_sms();
+  GemmParams p{};
+  p.M = M; p.N = N; p.K = K;
+  // one scale atom covers 128 rows, and the TMEM columns beside the two 128-column accumulators hold the scale bytes
+  p.block_n = N <= 128 ? ((N + 15) / 16) * 16 : 128;
+  p.b_rows = p.block_n;
+  p.tiles_m = (M + BM - 1) / BM;
+  p.tiles_n = (N + p.block_n - 1) / p.block_n;
+  p.splits = 1;
+  p.ldd = ldd; p.out_fp32 = out_fp32; p.flags = flags; p.D = D; p.bias = bias;
+  p.mx_sfa = static_cast<const uint8_t*>(sfa);
+  p.mx_sfb = static_cast<const uint8_t*>(sfb);
+  if (p.tiles_n > 1 && p.tiles_m > 1) p.group_m = 8;
+  const size_t stage_bytes = static_cast<size_t>(BM) * 128 + static_cast<size_t>(p.b_rows) * 128;
+  const bool tma_out = out_fp32 == 0 && (reinterpret_cast<uintptr_t>(D) & 15u) == 0 && (ldd % 8) == 0;
+  int stages = static_cast<int>((kSmemBudget - (tma_out ? kStageOutBytes : 0)) / (stage_bytes + 1024));
+  if (stages > kMaxStages) stages = kMaxStages;
+  if (stages < 2) return bdl_fail("bdl_gemm_mxfp8: tile does not fit in shared memory");
+  p.num_stages = stages;
+  const size_t smem = stages * (stage_bytes + 1024) + 1024 + (tma_out ? kStageOutBytes : 0);
+  CUtensorMap tmA, tmB, tmD{};
+  int rc = bdl_make_tmap_2d_u8(&tmA, A, static_cast<uint64_t>(K), static_cast<uint64_t>(M), lda, 128, BM);
+  if (rc) return rc;
+  rc = bdl_make_tmap_2d_u8(&tmB, B, static_cast<uint64_t>(K), static_cast<uint64_t>(N), ldb, 128, p.block_n);
+  if (rc) return rc;
+  if (tma_out) {
+    rc = bdl_make_tmap_2d_bf16(&tmD, D, static_cast<uint64_t>(N), static_cast<uint64_t>(M), ldd, 64, 32);
+    if (rc) return rc;
+  }
+  GemmKernel kfn = tma_out ? gemm_bf16_tcgen05_kernel<false, false, 0, true, false, true>
+                           : gemm_bf16_tcgen05_kernel<false, false, 0, true, false, false>;
+  return launch_gemm_kernel(kfn, static_cast<long long>(p.tiles_m) * p.tiles_n, num_sms, smem, stream, false, tmA, tmB,
+                            tma_out ? tmD : tmA, p, "gemm_tcgen05_kernel<mxfp8>");
 }
 
 // -1: CTA-pair tiles where the heuristic wants them (default), 0: never, 1: wherever they are legal. Returns the old mode.

@@ -102,6 +102,52 @@ static int qgrid(long long total) {
   return static_cast<int>(b);
 }
 
+
+// ------------------------------------------------------------------------------------------------ MX block scaling
+// e4m3 values with one UE8M0 (power-of-two) scale per 32 consecutive K elements of every row — the operand format of
+// tcgen05.mma.kind::mxf8f6f4.block_scale. This is the B200 form of BigQuant's "local" quantisation, which keeps one
+// scale per im2col row window instead of one per tensor (core/bigquant/native/ops/shuffle/shuffle_im2col.h,
+// S/nn/quantized/Quantization.scala:35-62): the scale follows the data block by block.
+// Scale bytes are written in the layout the tensor core's scale-factor copy (tcgen05.cp 32x128b.warpx4) expects:
+// 512-byte atoms of 128 rows x 4 k blocks, byte offset (r % 32) * 16 + (r % 128) / 32 * 4 + (kb % 4), atoms ordered
+// [row block][k group]. One warp per (row, 32-element block).
+template <typename T>
+__global__ void quantize_mxfp8_kernel(const T* __restrict__ x, uint8_t* __restrict__ q, uint8_t* __restrict__ sf,
+                                      long long rows, long long cols, long long ldx, long long ldq, int kgroups) {
+  // the warp grid covers the PADDED extent (rows to 128, k blocks to 4): absent rows / blocks get scale 1 (byte 127), so
+  // no separate fill of the atom buffer is needed
+  const long long kblocks = static_cast<long long>(kgroups) * 4;
+  const long long rows_p = (rows + 127) / 128 * 128;
+  const long long total = rows_p * kblocks;
+  const long long w = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  if (w >= total) return;
+  const int lane = threadIdx.x & 31;
+  const long long r = w / kblocks;
+  const long long kb = w - r * kblocks;
+  const long long c = kb * 32 + lane;
+  const bool live = r < rows && c < cols;
+  const float v = live ? static_cast<float>(x[r * ldx + c]) : 0.f;
+  const float am = warp_max(fabsf(v));
+  // smallest power of two s with am / s <= 448 (e4m3 max); exponent biased by 127, 0 .. 254
+  int e = 127;
+  if (am > 0.f) {
+    int ex;
+    const float fr = frexpf(am / kE4M3Max, &ex);      // am / 448 = fr * 2^ex, fr in [0.5, 1)
+    e = (fr == 0.5f ? ex - 1 : ex) + 127;
+    e = e < 0 ? 0 : (e > 254 ? 254 : e);
+  }
+  const float inv = exp2f(static_cast<float>(127 - e));
+  if (live) q[r * ldq + c] = static_cast<uint8_t>(__nv_cvt_float_to_fp8(v * inv, __NV_SATFINITE, __NV_E4M3));
+  if (lane == 0) {
+    const long long atom = (r >> 7) * kgroups + (kb >> 2);
+    sf[atom * 512 + (r & 31) * 16 + ((r & 127) >> 5) * 4 + (kb & 3)] = static_cast<uint8_t>(e);
+  }
+}
+
+__global__ void fill_u8_kernel(uint8_t* p, size_t n, uint8_t v) {
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<size_t>(gridDim.x) * blockDim.x)
+    p[i] = v;
+}
 }  // namespace bdl
 
 using namespace bdl;
@@ -149,4 +195,23 @@ extern "C" int bdl_quantize_int8_rows(const float* w, void* q, const float* absm
   quantize_int8_rows_kernel<<<qgrid(rows * cols), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       w, static_cast<int8_t*>(q), absmax, rows, cols);
   return bdl_check_launch("quantize_int8_rows_kernel");
+}
+
+// q: [rows, ldq] e4m3 bytes (ldq >= cols, multiple of 16; the pad must already be zero); sf: ceil(rows/128) *
+// ceil(cols/128) atoms of 512 bytes (see quantize_mxfp8_kernel), bytes of absent rows / k blocks set to 127 (scale 1).
+extern "C" int bdl_quantize_mxfp8(const void* x, void* q, void* sf, long long rows, long long cols, long long ldx,
+                                  long long ldq, int is_bf16, void* stream_) {
+  if (rows <= 0 || cols <= 0) return BDL_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream_);
+  const int kgroups = static_cast<int>((cols + 127) / 128);
+  const long long warps = ((rows + 127) / 128 * 128) * (static_cast<long long>(kgroups) * 4);
+  const long long blocks = (warps * 32 + 255) / 256;
+  if (blocks >= (1ll << 31)) return bdl_fail("bdl_quantize_mxfp8: too large");
+  if (is_bf16)
+    bdl::quantize_mxfp8_kernel<<<static_cast<int>(blocks), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), static_cast<uint8_t*>(q),
+                                                                           static_cast<uint8_t*>(sf), rows, cols, ldx, ldq, kgroups);
+  else
+    bdl::quantize_mxfp8_kernel<<<static_cast<int>(blocks), 256, 0, st>>>(static_cast<const float*>(x), static_cast<uint8_t*>(q),
+                                                                           static_cast<uint8_t*>(sf), rows, cols, ldx, ldq, kgroups);
+  return bdl_check_launch("quantize_mxfp8_kernel");
 }

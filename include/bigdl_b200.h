@@ -41,6 +41,17 @@ int bdl_gemm_set_residual(const void* residual_bf16, long long ld);
  * legal. Process-wide; returns the previous mode. Reference: the same S/nn/Linear.scala:78-167 /
  * S/nn/SpatialConvolution.scala:253-521 GEMMs as bdl_gemm_bf16. */
 int bdl_gemm_set_pair_mode(int mode);
+/* Block-scaled fp8: e4m3 operands with one UE8M0 (power-of-two) scale per (row, 32 consecutive K elements).
+ * bdl_quantize_mxfp8 writes the e4m3 bytes (q, row pitch ldq, padding pre-zeroed) and the scale bytes (sf:
+ * ceil(rows/128) * ceil(cols/128) atoms of 512 bytes, offset (r%32)*16 + (r%128)/32*4 + kb%4 inside an atom — the layout
+ * tcgen05.cp 32x128b.warpx4 moves to TMEM). bdl_gemm_mxfp8 multiplies two such operands with
+ * tcgen05.mma.kind::mxf8f6f4.block_scale (scales applied by the tensor core, per block) and adds bias / ReLU.
+ * Reference: BigQuant's per-window scales (core/bigquant/native/ops/shuffle/shuffle_im2col.h),
+ * S/nn/quantized/Quantization.scala:35-62, S/nn/quantized/Linear.scala. */
+int bdl_quantize_mxfp8(const void* x, void* q, void* sf, long long rows, long long cols, long long ldx, long long ldq,
+                       int is_bf16, void* stream);
+int bdl_gemm_mxfp8(const void* A, const void* B, const void* sfa, const void* sfb, void* D, const float* bias, int M,
+                   int N, int K, long long lda, long long ldb, long long ldd, int out_fp32, int flags, void* stream);
 int bdl_gemm_bf16(const void* A, const void* B, void* D, const float* bias, int M, int N, int K, long long lda,
                   long long ldb, long long ldd, int a_mn, int b_mn, int out_fp32, int flags, int splits, void* stream);
 /* Implicit-GEMM convolution on the same kernel: the gathered operand is fetched from the NHWC activation tensor by

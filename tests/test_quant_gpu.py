@@ -130,3 +130,61 @@ def test_resnet_block_shared_quantisation():
     out = q.forward(xg).float().cpu()
     assert torch.isfinite(out).all()
     assert float((out - ref).norm() / ref.norm()) < 0.25
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 128), (256, 128, 512), (300, 200, 416), (1000, 64, 96), (512, 1000, 2048)])
+def test_mxfp8_block_scaled_gemm(M, N, K):
+    """tcgen05.mma.kind::mxf8f6f4.block_scale vs an fp32 GEMM of the SAME block-quantised operands (what the tensor core
+    must compute exactly, up to fp32 accumulation order), and the quantiser vs its torch restatement."""
+    from bigdl_b200.ops import quant as Q
+    torch.manual_seed(4)
+    # per-row / per-block magnitudes spread over several octaves: one scale per tensor would lose the small blocks
+    a = torch.randn(M, K, device="cuda") * torch.exp2(torch.randint(-6, 6, (M, 1), device="cuda").float())
+    b = torch.randn(N, K, device="cuda") * torch.exp2(torch.randint(-4, 4, (N, (K + 31) // 32), device="cuda").float()
+                                                      ).repeat_interleave(32, dim=1)[:, :K]
+    bias = torch.randn(N, device="cuda")
+    aq, sfa = Q.quantize_mxfp8(a.bfloat16())
+    bq, sfb = Q.quantize_mxfp8(b.bfloat16())
+    aq_c, sfa_c = Q.quantize_mxfp8(a.bfloat16().cpu())
+    assert torch.equal(aq.cpu(), aq_c) and torch.equal(sfa.cpu(), sfa_c)
+    ad, bd = Q.dequantize_mxfp8(aq, sfa, K), Q.dequantize_mxfp8(bq, sfb, K)
+    # block scaling keeps ~2 significant digits in EVERY block
+    assert float(((ad - a.bfloat16().float()).abs() / (a.abs() + 1e-3 * a.abs().amax(1, keepdim=True))).max()) < 0.13
+    ref = ad @ bd.t()
+    out = Q.gemm_mxfp8(aq, sfa, bq, sfb, K, out_dtype=torch.float32)
+    torch.cuda.synchronize()
+    err = (out - ref).abs().max().item()
+    assert err <= 1e-4 * ref.abs().max().item() + 1e-5, (err, ref.abs().max().item())
+    out16 = Q.gemm_mxfp8(aq, sfa, bq, sfb, K, bias=bias, relu=True)
+    torch.cuda.synchronize()
+    assert torch.allclose(out16.float(), torch.relu(ref + bias), rtol=1e-2, atol=1e-2 * ref.abs().max().item())
+    # against the unquantised product: block scales keep the relative error at the e4m3 level for every row
+    true = a.bfloat16().float() @ b.bfloat16().float().t()
+    rel = ((out - true).norm(dim=1) / (true.norm(dim=1) + 1e-6)).max().item()
+    assert rel < 0.09, rel
+
+
+def test_top1_agreement_on_gpu_kernels():
+    """The trained classifier of the CPU test, quantised and run on the tcgen05 fp8 kernels: per-tensor scales
+    (kind::f8f6f4) and MX block scales (kind::mxf8f6f4.block_scale) both keep >= 99.5 % top-1 agreement with the float
+    model (reference: T/integration/Quantization.scala:88-148, 'same top-1 accuracy')."""
+    import sys, os
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from test_quantized_cpu import _trained_mlp
+    from bigdl_b200.quantized.quantizer import Quantizer
+
+    m, batch = _trained_mlp()
+    x, y = batch(4096)
+    ref = m.forward(x).float()
+    m.cuda()
+    xg = x.cuda()
+    ref_gpu = m.forward(xg).float().cpu()
+    assert float((ref_gpu.argmax(1) == ref.argmax(1)).float().mean()) >= 0.995
+    errs = {}
+    for mode in (False, True):
+        q = Quantizer.quantize(m, block_scale=mode)
+        out = q.forward(xg).float().cpu()
+        agree = float((out.argmax(1) == ref.argmax(1)).float().mean())
+        assert agree >= 0.995, (mode, agree)
+        errs[mode] = float((out - ref).norm() / ref.norm())
+    assert errs[True] <= errs[False] * 1.05, errs

@@ -164,3 +164,65 @@ def test_quant_serializer_roundtrip():
     assert payload["weight_q"].dtype.name == "uint8" and payload["desc"] == {"outputSize": 8, "inputSize": 16}
     QuantSerializer.deserialize(b, payload)
     assert torch.equal(a.forward(x), b.forward(x))
+
+
+def _trained_mlp(seed=3, steps=150):
+    """A small classifier trained on synthetic clustered data, so that top-1 agreement is a meaningful statistic (the
+    reference's integration check trains/loads real models: T/integration/Quantization.scala:88-148)."""
+    import torch
+    from bigdl_b200.nn.criterion import ClassNLLCriterion
+    from bigdl_b200.nn.layer import Linear, LogSoftMax, ReLU, Sequential
+    from bigdl_b200.optim.optim_method import SGD
+    from bigdl_b200.utils.random_generator import RNG
+
+    RNG.setSeed(seed)
+    g = torch.Generator().manual_seed(seed)
+    centers = torch.randn(10, 96, generator=g) * 2.0
+    # feature scales spread over three orders of magnitude: the case per-tensor scales handle worst
+    fscale = torch.exp2(torch.linspace(-6, 4, 96))
+
+    def batch(n):
+        y = torch.randint(0, 10, (n,), generator=g)
+        x = (centers[y] + torch.randn(n, 96, generator=g)) * fscale
+        return x, (y + 1).float()
+
+    m = Sequential().add(Linear(96, 128)).add(ReLU()).add(Linear(128, 64)).add(ReLU()).add(Linear(64, 10)).add(LogSoftMax())
+    with torch.no_grad():
+        m.modules[0].weight.div_(fscale)           # first layer absorbs the feature scales (a trained net would learn this)
+    crit, om = ClassNLLCriterion(), SGD(0.05, momentum=0.9)
+    w, gr = m.getParameters()
+    m.training()
+    for _ in range(steps):
+        x, y = batch(64)
+        m.zeroGradParameters()
+        out = m.forward(x)
+        crit.forward(out, y)
+        m.backward(x, crit.backward(out, y))
+        om.update(w, gr)
+        m._mark_weights_dirty()
+    m.evaluate()
+    return m, batch
+
+
+def test_top1_agreement_of_quantised_models():
+    """Quantised vs float predictions on held-out data: >= 99.5 % top-1 agreement for both scaling modes (the reference
+    asks for 'same top-1 accuracy'), and the block-scaled (MX) Linear is at least as close to the float logits as the
+    per-tensor one on inputs whose features span many octaves."""
+    import torch
+    from bigdl_b200.quantized.quantizer import Quantizer
+
+    m, batch = _trained_mlp()
+    x, y = batch(2000)
+    ref = m.forward(x).float()
+    acc = float((ref.argmax(1) + 1 == y).float().mean())
+    assert acc > 0.9, acc                                  # the float model actually learned the task
+    errs = {}
+    for mode in (False, True):
+        q = Quantizer.quantize(m, block_scale=mode)
+        out = q.forward(x).float()
+        agree = float((out.argmax(1) == ref.argmax(1)).float().mean())
+        assert agree >= 0.995, (mode, agree)
+        errs[mode] = float((out - ref).norm() / ref.norm())
+    assert errs[True] <= errs[False] * 1.05, errs
+    from bigdl_b200.quantized.layers import Linear as QLinear
+    assert all(l.block_scale for l in Quantizer.quantized_layers(Quantizer.quantize(m, block_scale=True)) if isinstance(l, QLinear))

@@ -506,9 +506,16 @@ def _loopcond(n): return TFO.LoopCondition()
 def _variable(n): return None          # resolved from binFile by the loader
 
 
+from . import tensorflow_grad as _grad_ops  # noqa: E402,F401  (registers the *Grad / Conv3D / Dilation2D loaders)
+
 SUPPORTED_OPS = sorted(_LOADERS)
 _WEIGHT_SLOTS = {"Conv2D": [1], "DepthwiseConv2dNative": [1], "MatMul": [1], "BiasAdd": [1], "Conv2DBackpropInput": [1],
                  "FusedBatchNorm": [1, 2], "FusedBatchNormV2": [1, 2], "FusedBatchNormV3": [1, 2]}
+
+
+_MULTI_OUTPUT_OPS = ("Switch", "Split", "SplitV", "Unpack", "TopKV2", "TopK", "ParseExample", "ParseSingleExample",
+                     "BroadcastGradientArgs", "SoftmaxCrossEntropyWithLogits", "FusedBatchNormGrad",
+                     "FusedBatchNormGradV2", "FusedBatchNormGradV3")
 
 
 def _split_input(s: str):
@@ -596,14 +603,14 @@ def load_tf(path, inputs, outputs, byteOrder: str = "little_endian", binFile: st
             if ctrl:
                 continue                      # ordering-only edges: data dependencies already order a functional graph
             src_op = by_name[src].op
-            multi = src in multi_out or src_op in ("Switch", "Split", "SplitV", "Unpack", "TopKV2", "TopK")
+            multi = src in multi_out or src_op in _MULTI_OUTPUT_OPS
             nodes[src].add(nodes[name], (idx + 1) if multi else None)
     in_nodes = [nodes[i] for i in inputs]
     out_nodes = []
     for o in outputs:
         src, idx, _ = _split_input(o)
-        if idx:
-            sel = Node(_Fn(lambda t, i=idx: t[i + 1], 1), [nodes[src]])
+        if idx or (src not in inputs and (src in multi_out or by_name[src].op in _MULTI_OUTPUT_OPS)):
+            sel = Node(_Fn(lambda *ts, i=idx: ts[i]), [nodes[src]])         # a Table input arrives unpacked
             sel.element.setName(f"{src}_{idx}")
             out_nodes.append(sel)
         else:

@@ -214,10 +214,18 @@ class Optimizer:
 
     def setDropModuleProperty(self, dropPercentage: float, maxDropPercentage: float, batchsize: int = 100,
                               warmupIteration: int = 200):
-        """Straggler dropping (S/optim/Optimizer.scala:404-412). With one replica per GPU on one NVSwitch box there are
-        no per-core replicas to drop; the settings are stored and the threshold math lives in ``straggler.py``."""
+        """Straggler dropping (S/optim/Optimizer.scala:404-412, S/optim/DistriOptimizer.scala:241-244,342-344,423-449).
+        A replica here is a rank: after ``warmupIteration`` iterations every rank's forward+backward time is compared
+        with the k-th largest time of the last ``batchsize`` iterations; a rank above the threshold contributes no
+        gradient to that iteration (the average runs over the ranks that were kept), and an iteration that lost more
+        than ``maxDropPercentage`` of its ranks is discarded. The decision needs the ranks' times on the host every
+        iteration, so a drop policy runs the step eagerly on the nccl / gloo parameter backends."""
+        from ..parallel.straggler import DropPolicy
+
         self.drop_percentage, self.max_drop_percentage = dropPercentage, maxDropPercentage
         self.compute_threshold_batch_size, self.warmup_iteration_num = batchsize, warmupIteration
+        self._drop_policy = DropPolicy(dropPercentage, maxDropPercentage, batchsize, warmupIteration) \
+            if dropPercentage > 0 else None
         return self
 
     def prepareInput(self):
@@ -424,8 +432,11 @@ def _train_loop(opt: Optimizer, distributed: bool, strategy_factory=None):
     # ParallelOptimizer keeps full (non-sharded) weights and optimizer state on every rank: no sharded master copy
     method_ranges = [(o, l) for o, l, _ in ranges] if ranges is not None else None
     method_list = [opt.optim_methods[n] for _, _, n in ranges] if ranges is not None else None
-    sync = AllReduceParameter(flat, backend=None if (world > 1 and strategy_factory is None) else "local", root=model,
-                              method_ranges=method_ranges)
+    drop = getattr(opt, "_drop_policy", None) if (world > 1 and strategy_factory is None) else None
+    backend = None if (world > 1 and strategy_factory is None) else "local"
+    if drop is not None and device.type == "cuda" and config.get("bigdl.parameter.backend") in ("auto", "p2p"):
+        backend = "nccl"         # per-iteration host decisions (who is dropped) do not fit the captured p2p step
+    sync = AllReduceParameter(flat, backend=backend, root=model, method_ranges=method_ranges)
     sync.init()
     opt._param_sync = sync
     single = opt._single_method()
@@ -460,6 +471,7 @@ def _train_loop(opt: Optimizer, distributed: bool, strategy_factory=None):
     # per-submodule methods and global-norm clipping stay on the graph when the bucketed p2p plane carries them (device
     # resident OptimHP table and clip scale); on one GPU they run eagerly
     graph_ok = (device.type == "cuda" and bool(config.get("bigdl.cudaGraph")) and sync.backend in ("local", "p2p")
+                and drop is None
                 and config.get("bigdl.engineType") == "b200"
                 and ((single is not None and clip.l2norm is None) or sync.overlapped))
     step_methods = method_list if method_list is not None else [single]
@@ -468,9 +480,15 @@ def _train_loop(opt: Optimizer, distributed: bool, strategy_factory=None):
         graph_ok = False
         opt._strategy = strategy
 
+    # phase timers of the reference (S/optim/DistriOptimizer.scala:188-196): host clocks, so they are only taken when asked
+    # for (bigdl.metrics) — they need a stream synchronisation per phase — or when a drop policy needs compute times
+    metrics_on = bool(config.get("bigdl.metrics"))
+    for name in ("get weights average", "computing time average", "aggregate gradient time", "data fetch time"):
+        opt.metrics.set(name, 0.0, 1)
     while not opt.end_when(state):
         t0 = time.time()
         batch = next(prefetch) if prefetch is not None else next(data_iter)
+        opt.metrics.add("data fetch time", (time.time() - t0) * 1e9)
         if not isinstance(batch, MiniBatch):
             raise TypeError("the training dataset must yield MiniBatch (use SampleToMiniBatch or pass batch_size)")
         n_local = batch.size()
@@ -489,6 +507,7 @@ def _train_loop(opt: Optimizer, distributed: bool, strategy_factory=None):
                 for om_ in step_methods:
                     om_.clip_range = clip.constant
                 sync.begin_step(step_methods, world, clip.l2norm)
+            t_compute = time.perf_counter()
             with torch.enable_grad():
                 out = model._call(x)
                 loss = criterion._call(out, y)
@@ -500,16 +519,34 @@ def _train_loop(opt: Optimizer, distributed: bool, strategy_factory=None):
 
                 join_side_streams()
             model._apply_regularizers()
-            if strategy is not None:
+            if device.type == "cuda" and (drop is not None or metrics_on):
+                torch.cuda.current_stream(device).synchronize()       # the phase timers below are host clocks
+            compute_s = time.perf_counter() - t_compute
+            opt.metrics.add("computing time average", compute_s * 1e9)
+            t_agg = time.perf_counter()
+            kept = world
+            if drop is not None:
+                kept, discard = _apply_drop_policy(drop, state["neval"], compute_s, flat, world, device)
+                opt.metrics.set("dropped replicas", drop.dropped_total)
+                if discard:            # too many ranks were late: nobody updates (DistriOptimizer.scala:342-344)
+                    flat.grads.zero_()
+                    kept = 0
+            if kept == 0:
+                pass
+            elif strategy is not None:
                 for om_ in strategy.methods:
                     om_.clip_range = clip.constant
                 strategy.after_backward()
             elif sync.overlapped:
                 sync.end_step()
             elif single is not None:
-                sync.step(single, avg_numbers=world, l2_clip=clip.l2norm)
+                sync.step(single, avg_numbers=kept, l2_clip=clip.l2norm)
             else:
                 _multi_method_step(opt, sync, flat, ranges, world, clip)
+            if metrics_on:
+                if device.type == "cuda":
+                    torch.cuda.current_stream(device).synchronize()
+                opt.metrics.add("aggregate gradient time", (time.perf_counter() - t_agg) * 1e9)
 
         # ---- bookkeeping (DistriOptimizer.scala:399-474)
         if device.type == "cuda":
@@ -577,6 +614,8 @@ def _train_loop(opt: Optimizer, distributed: bool, strategy_factory=None):
     if flat.compute is not None and sync.backend == "local":
         flat.dirty = True
     opt.state = state
+    if metrics_on and opt._rank() == 0:
+        log.info(opt.metrics.summary())
     Engine.resetSingleton()
     if sync.backend == "p2p":
         # keep the symmetric buffers alive while the model still points its compute weights at them
@@ -625,6 +664,20 @@ class _Prefetcher:
                 t.record_stream(torch.cuda.current_stream(self.device))
         self._preload()
         return b
+
+
+def _apply_drop_policy(policy, iteration, compute_s, flat, world, device):
+    """Exchange the ranks' compute times, update the threshold, and zero THIS rank's gradients when it was too slow.
+    Returns (number of ranks kept, discard the iteration)."""
+    t = torch.tensor([compute_s], dtype=torch.float64, device=device if device.type == "cuda" else "cpu")
+    every = [torch.zeros_like(t) for _ in range(world)]
+    dist.all_gather(every, t)
+    times = [float(v) for v in every]
+    keep, discard = policy.apply(times)
+    policy.record(iteration, times)
+    if dist.get_rank() not in keep:
+        flat.grads.zero_()
+    return len(keep), discard
 
 
 def _graph_step(opt, graphs, model, criterion, sync, om, batch, device, world, l2_clip=None):

@@ -3,9 +3,9 @@ S/utils/Util.scala:32 ``kthLargest``): after ``warmupIteration`` iterations the 
 computations are abandoned by a timeout equal to the k-th largest observed time; an iteration in which more than
 ``maxDropPercentage`` were dropped is discarded entirely.
 
-On one NVSwitch box with one replica per GPU every rank runs the same kernels at the same clocks, so there is nothing to
-drop in steady state; the policy object is kept because multi-node jobs and heterogeneous boxes can still plug it into
-``Optimizer.setDropModuleProperty`` and because the threshold rule is part of the reference's observable behaviour."""
+``Optimizer.setDropModuleProperty`` builds the policy; the training loop (optim/optimizer.py ``_apply_drop_policy``)
+exchanges the ranks' forward+backward times every iteration, drops the gradients of ranks above the threshold and
+discards over-dropped iterations. A replica is a rank here (the reference drops per-core model replicas)."""
 from __future__ import annotations
 
 import random

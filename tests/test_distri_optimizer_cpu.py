@@ -100,3 +100,56 @@ def test_partition_rule():
     assert parts[0][0] == 0 and sum(l for _, l in parts) == 22280
     assert all(s % 8 == 0 and l % 8 == 0 for s, l in parts)
     assert all(parts[i][0] + parts[i][1] == parts[i + 1][0] for i in range(7))
+
+
+def _drop_worker(rank, world):
+    """Rank 1 is made slow after the warm-up; the drop policy must leave its gradient out (and keep the ranks' weights
+    identical), and a policy that tolerates no drops must discard those iterations altogether."""
+    import time as _time
+
+    import torch
+    from bigdl_b200.dataset.base import FixedMiniBatchDataSet, MiniBatch
+    from bigdl_b200.nn.criterion import MSECriterion
+    from bigdl_b200.nn.layer import Linear, Sequential
+    from bigdl_b200.nn.module import Module
+    from bigdl_b200.optim.optim_method import SGD
+    from bigdl_b200.optim.optimizer import Optimizer
+    from bigdl_b200.optim.trigger import MaxIteration
+    from bigdl_b200.utils import config
+    from bigdl_b200.utils.random_generator import RNG
+
+    class Slow(Module):
+        calls = 0
+
+        def updateOutput(self, input):
+            Slow.calls += 1
+            if rank == 1 and Slow.calls > 6:
+                _time.sleep(0.15)
+            return input
+
+    config.set("bigdl.parameter.compress", "fp32")
+    out = {}
+    for name, (drop, max_drop) in {"drop": (0.4, 0.5), "discard": (0.4, 0.4)}.items():
+        Slow.calls = 0
+        RNG.setSeed(3)
+        m = Sequential().add(Slow()).add(Linear(8, 4))
+        g = torch.Generator().manual_seed(10 + rank)
+        x, y = torch.randn(16, 8, generator=g), torch.randn(16, 4, generator=g)
+        opt = Optimizer(m, FixedMiniBatchDataSet(MiniBatch(x, y), 10 ** 6, distributed=True), MSECriterion(),
+                        MaxIteration(12), 16 * world, SGD(0.05))
+        opt.setDropModuleProperty(drop, max_drop, batchsize=3, warmupIteration=2)
+        w0 = m.getParameters()[0].clone()
+        opt.optimize()
+        out[name] = (m.getParameters()[0].clone(), opt._drop_policy.dropped_total, w0)
+    return out
+
+
+def test_straggler_drop_policy_is_applied():
+    res = run_ranks(_drop_worker, 2)
+    for name in ("drop", "discard"):
+        w0, w1 = res[0][name][0], res[1][name][0]
+        assert torch.equal(w0, w1), name                              # every rank applied the same decisions
+        assert res[0][name][1] == res[1][name][1] > 0, (name, res[0][name][1])
+    # a discarded iteration changes nothing, so "discard" moved the weights less than "drop" did
+    moved = {n: float((res[0][n][0] - res[0][n][2]).norm()) for n in ("drop", "discard")}
+    assert 0 < moved["discard"] < moved["drop"], moved

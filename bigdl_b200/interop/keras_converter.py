@@ -13,6 +13,7 @@ import numpy as np
 import torch
 
 from ..nn import keras as K
+from ..nn import layer as L
 
 
 def _shape(cfg):
@@ -106,7 +107,68 @@ _BUILDERS = {
                              c.get("return_sequences", False), c.get("go_backwards", False), **_common(c)),
     "GRU": lambda c: K.GRU(c["output_dim"], c.get("activation", "tanh"), c.get("inner_activation", "hard_sigmoid"),
                            c.get("return_sequences", False), c.get("go_backwards", False), **_common(c)),
+    # ---- the rest of pyspark/bigdl/keras/converter.py's create_* list
+    "TimeDistributedDense": lambda c: K.TimeDistributed(K.Dense(c["output_dim"], init=c.get("init", "glorot_uniform"),
+                                                                activation=_act(c), bias=c.get("bias", True)), **_common(c)),
+    "AtrousConvolution1D": lambda c: K.AtrousConvolution1D(c["nb_filter"], c["filter_length"], activation=_act(c),
+                                                           subsample_length=c.get("subsample_length", 1),
+                                                           atrous_rate=c.get("atrous_rate", 1), bias=c.get("bias", True),
+                                                           **_common(c)),
+    "ConvLSTM2D": lambda c: K.ConvLSTM2D(c["nb_filter"], c["nb_row"], c.get("nb_col"), c.get("activation", "tanh"),
+                                         c.get("inner_activation", "hard_sigmoid"), c.get("dim_ordering", "th"),
+                                         tuple(c.get("subsample", (1, 1))), c.get("border_mode", "same"),
+                                         return_sequences=c.get("return_sequences", False),
+                                         go_backwards=c.get("go_backwards", False), **_common(c)),
+    "GlobalMaxPooling3D": lambda c: K.GlobalMaxPooling3D(c.get("dim_ordering", "th"), **_common(c)),
+    "GlobalAveragePooling3D": lambda c: K.GlobalAveragePooling3D(c.get("dim_ordering", "th"), **_common(c)),
+    "ZeroPadding3D": lambda c: K.ZeroPadding3D(tuple(c.get("padding", (1, 1, 1))), c.get("dim_ordering", "th"), **_common(c)),
+    "Cropping3D": lambda c: K.Cropping3D(c.get("cropping", ((1, 1), (1, 1), (1, 1))), c.get("dim_ordering", "th"), **_common(c)),
+    "SpatialDropout3D": lambda c: K.SpatialDropout3D(c.get("p", 0.5), c.get("dim_ordering", "th"), **_common(c)),
+    "SReLU": lambda c: K.SReLU(c.get("t_left_init", "zero"), c.get("a_left_init", "glorot_uniform"),
+                               c.get("t_right_init", "glorot_uniform"), c.get("a_right_init", "one"),
+                               c.get("shared_axes"), **_common(c)),
+    "LocallyConnected1D": lambda c: K.LocallyConnected1D(c["nb_filter"], c["filter_length"], activation=_act(c),
+                                                         border_mode=c.get("border_mode", "valid"),
+                                                         subsample_length=c.get("subsample_length", 1),
+                                                         bias=c.get("bias", True), **_common(c)),
+    "LocallyConnected2D": lambda c: K.LocallyConnected2D(c["nb_filter"], c["nb_row"], c["nb_col"], activation=_act(c),
+                                                         border_mode=c.get("border_mode", "valid"),
+                                                         subsample=tuple(c.get("subsample", (1, 1))),
+                                                         dim_ordering=c.get("dim_ordering", "th"), bias=c.get("bias", True),
+                                                         **_common(c)),
+    "PReLU": lambda c: _wrap_module(L.PReLU(0), c),
+    "ParametricSoftplus": lambda c: _wrap_module(_ParametricSoftplus(c.get("alpha_init", 0.2), c.get("beta_init", 5.0)), c),
+    "ActivityRegularization": lambda c: _wrap_module(L.ActivityRegularization(c.get("l1", 0.0), c.get("l2", 0.0)), c),
 }
+
+
+class _ParametricSoftplus(L.Module):
+    """alpha * log(1 + exp(beta * x)) with learnable scalars (Keras 1.2.2 advanced activation; the reference only accepts
+    it with the shared default parameters, pyspark/bigdl/keras/converter.py create_parametricsoftplus)."""
+
+    def __init__(self, alpha=0.2, beta=5.0):
+        super().__init__()
+        self.register_parameter("alpha", torch.tensor([float(alpha)]))
+        self.register_parameter("beta", torch.tensor([float(beta)]))
+
+    def updateOutput(self, input):
+        return self.alpha.to(input.dtype) * torch.nn.functional.softplus(self.beta.to(input.dtype) * input)
+
+
+def _wrap_module(module, cfg):
+    """A shape-preserving framework module as a Keras layer."""
+    class _Wrapped(K.KerasLayer):
+        def __init__(self, m, **kw):
+            super().__init__(kw.pop("input_shape", None), **kw)
+            self._m = m
+
+        def doBuild(self, s):
+            return self._m
+
+        def computeOutputShape(self, s):
+            return s
+
+    return _Wrapped(module, **_common(cfg))
 
 
 class DefinitionLoader:
@@ -200,6 +262,70 @@ class WeightLoader:
                 bn._buffers["runningVar"].copy_(torch.from_numpy(arrays[3]))
             elif cls == "Embedding":
                 params[0].copy_(torch.from_numpy(arrays[0]))
+            elif cls in ("LSTM", "GRU", "SimpleRNN"):
+                WeightLoader._recurrent(layer, cls, arrays)
+            elif cls == "Bidirectional":
+                half = len(arrays) // 2
+                cells = [m for m in layer.all_modules() if "i2g" in m.__dict__ or "i2h" in m.__dict__]
+                inner = type(layer.layer).__name__
+                for cell, arrs in zip(cells, (arrays[:half], arrays[half:])):
+                    WeightLoader._cell(cell, inner, arrs)
+            elif cls == "TimeDistributed":
+                WeightLoader._apply(layer.layer, arrays)
+            elif cls in ("Convolution1D", "AtrousConvolution1D"):
+                # keras [filter_length, 1, in, out] -> conv weight [out, in, 1|k, k|1] (the layer runs it as a 2-D conv)
+                w = arrays[0]
+                w = w.reshape(w.shape[0], w.shape[-2], w.shape[-1]).transpose(2, 1, 0)          # [out, in, k]
+                params[0].copy_(torch.from_numpy(np.ascontiguousarray(w)).reshape(params[0].shape))
+                if len(params) > 1 and len(arrays) > 1:
+                    params[1].copy_(torch.from_numpy(arrays[1]))
+            elif cls in ("Convolution3D",):
+                w = arrays[0]
+                if w.shape != tuple(params[0].shape):
+                    w = w.transpose(4, 3, 0, 1, 2)                                               # tf: [d1,d2,d3,in,out]
+                params[0].copy_(torch.from_numpy(np.ascontiguousarray(w)).reshape(params[0].shape))
+                if len(params) > 1 and len(arrays) > 1:
+                    params[1].copy_(torch.from_numpy(arrays[1]))
+            elif cls in ("AtrousConvolution2D", "Deconvolution2D"):
+                w = arrays[0]
+                if w.size == params[0].numel() and w.shape != tuple(params[0].shape):
+                    w = w.transpose(3, 2, 0, 1) if cls == "AtrousConvolution2D" else w
+                    if cls == "Deconvolution2D" and w.shape != tuple(params[0].shape):
+                        w = w.transpose(1, 0, 2, 3) if w.transpose(1, 0, 2, 3).shape == tuple(params[0].shape) else \
+                            w.transpose(2, 3, 0, 1)
+                params[0].copy_(torch.from_numpy(np.ascontiguousarray(w)).reshape(params[0].shape))
+                if len(params) > 1 and len(arrays) > 1:
+                    params[1].copy_(torch.from_numpy(arrays[1]))
+            elif cls == "SeparableConvolution2D":
+                # keras: depthwise [kh, kw, in, mult] (tf) or [in*mult... ] (th), pointwise [1,1,in*mult,out], bias
+                dw, pw = arrays[0], arrays[1]
+                if dw.ndim == 4 and dw.shape[:2] != tuple(params[0].shape[-2:]):
+                    pass
+                if dw.shape != tuple(params[0].shape):
+                    dw = dw.transpose(2, 3, 0, 1).reshape(params[0].shape) if dw.size == params[0].numel() else dw
+                if pw.shape != tuple(params[1].shape):
+                    pw = pw.transpose(3, 2, 0, 1).reshape(params[1].shape) if pw.size == params[1].numel() else pw
+                params[0].copy_(torch.from_numpy(np.ascontiguousarray(dw)).reshape(params[0].shape))
+                params[1].copy_(torch.from_numpy(np.ascontiguousarray(pw)).reshape(params[1].shape))
+                if len(params) > 2 and len(arrays) > 2:
+                    params[2].copy_(torch.from_numpy(arrays[2]))
+            elif cls == "Highway":
+                # keras [W, W_carry, b, b_carry] (W [in, in]) -> Linear weights are [out, in]
+                lin = [m for m in layer.all_modules() if type(m).__name__ == "Linear"]
+                order = {0: (arrays[1], arrays[3] if len(arrays) > 3 else None),        # gate (carry) transform
+                         1: (arrays[0], arrays[2] if len(arrays) > 2 else None)}        # candidate transform
+                for i, m in enumerate(lin[:2]):
+                    w, b = order[i]
+                    m.weight.copy_(torch.from_numpy(w.T.copy()))
+                    if b is not None and "bias" in m._parameters:
+                        m.bias.copy_(torch.from_numpy(b))
+            elif cls == "MaxoutDense":
+                # keras W [nb_feature, in, out], b [nb_feature, out] -> one Linear(in, nb_feature * out)
+                w, b = arrays[0], (arrays[1] if len(arrays) > 1 else None)
+                k, i, o = w.shape
+                params[0].copy_(torch.from_numpy(np.ascontiguousarray(w.transpose(0, 2, 1).reshape(k * o, i))))
+                if b is not None and len(params) > 1:
+                    params[1].copy_(torch.from_numpy(b.reshape(-1)))
             else:
                 if len(arrays) != len(params):
                     raise ValueError(f"{cls} {layer.getName()}: expected {len(params)} weight arrays, got {len(arrays)}")
@@ -209,6 +335,35 @@ class WeightLoader:
                     p.copy_(torch.from_numpy(a.reshape(p.shape) if a.shape == tuple(p.shape) else a.T.reshape(p.shape)))
         for m in layer.all_modules():
             m._mark_weights_dirty()
+
+    @staticmethod
+    def _recurrent(layer, cls, arrays):
+        cell = [m for m in layer.all_modules() if "i2g" in m.__dict__ or "i2h" in m.__dict__][0]
+        WeightLoader._cell(cell, cls, arrays)
+
+    @staticmethod
+    def _cell(cell, cls, a):
+        """Keras 1.2.2 recurrent weight lists -> the cells' fused gate matrices (reference:
+        pyspark/bigdl/keras/converter.py convert_lstm / convert_gru / convert_simplernn).
+        LSTM  [W_i,U_i,b_i, W_c,U_c,b_c, W_f,U_f,b_f, W_o,U_o,b_o]  -> gate chunks [input, candidate, forget, output]
+        GRU   [W_z,U_z,b_z, W_r,U_r,b_r, W_h,U_h,b_h]               -> chunks [reset, update, candidate]
+        SimpleRNN [W, U, b]."""
+        t = lambda *xs: torch.from_numpy(np.ascontiguousarray(np.concatenate([x.T if x.ndim == 2 else x for x in xs])))  # noqa: E731
+        if cls == "LSTM":
+            cell.i2g.weight.copy_(t(a[0], a[3], a[6], a[9]))
+            cell.h2g.weight.copy_(t(a[1], a[4], a[7], a[10]))
+            cell.i2g.bias.copy_(t(a[2], a[5], a[8], a[11]))
+        elif cls == "GRU":
+            cell.i2g.weight.copy_(t(a[3], a[0], a[6]))
+            cell.i2g.bias.copy_(t(a[5], a[2], a[8]))
+            cell.h2g.weight.copy_(t(a[4], a[1]))
+            cell.h2c.weight.copy_(t(a[7]))
+        else:
+            cell.i2h.weight.copy_(t(a[0]))
+            cell.h2h.weight.copy_(t(a[1]))
+            cell.i2h.bias.copy_(t(a[2]))
+            if "bias" in cell.h2h._parameters:
+                cell.h2h.bias.zero_()
 
     @staticmethod
     def load_weights_from_arrays(model, weights: dict, by_name: bool = False):

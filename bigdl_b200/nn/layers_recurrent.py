@@ -18,6 +18,7 @@ import math
 import torch
 import torch.nn.functional as F
 
+from ..utils import config
 from ..utils.random_generator import RNG
 from ..utils.table import Table, to_table
 from .initialization_method import RandomUniform, VariableFormat
@@ -314,9 +315,35 @@ class Recurrent(Container):
 
     get_hidden_state = getHiddenState
 
+    def _fused_lstm(self, cell, x, reverse: bool = False):
+        """The whole sequence in one persistent kernel (csrc/lstm_seq.cu) when the cell is a plain LSTM on the GPU."""
+        from ..ops.recurrent import LstmSeqFn, lstm_seq_supported
+
+        if not (type(cell) is LSTM and cell.activation is None and cell.inner_activation is None and not self.mask_zero
+                and x.is_cuda and x.dim() == 3 and config.get("bigdl.engineType") == "b200"
+                and bool(config.get("bigdl.rnn.persistent"))
+                and lstm_seq_supported(cell.hidden_size, x.device)):
+            return None
+        proj = cell.pre(x)
+        if proj.dtype != torch.bfloat16:
+            return None
+        h0 = c0 = None
+        if self._init_hidden is not None:
+            h0, c0 = self._init_hidden[0], self._init_hidden[1]
+        w = cell.h2g.weight
+        w16 = cell.h2g.weight_for_compute("weight")
+        if w16.dtype != torch.bfloat16:
+            w16 = w16.detach().to(torch.bfloat16)
+        hs, h_last, c_last = LstmSeqFn.apply(proj, w, w16, h0, c0, reverse)
+        self._last_hidden = [h_last.detach(), c_last.detach()]
+        return hs
+
     def updateOutput(self, input):
         cell = self.cell
         x = input
+        fused = self._fused_lstm(cell, x)
+        if fused is not None:
+            return fused
         B, T = x.shape[0], x.shape[1]
         proj = cell.pre(x)
         spatial = tuple(proj.shape[3:]) if proj.dim() > 3 else None

@@ -79,6 +79,8 @@ _SIGNATURES = {
     "bdl_gru_out_bwd": [_P] * 7 + [_L, _I, _L, _L, _P],
     "bdl_gemm_set_residual": [_P, _L],
     "bdl_gemm_set_pair_mode": [_I],
+    "bdl_lstm_seq_fwd": [_P, _L, _L, _P, _P, _P, _P, _L, _L, _I, _P, _P, _P, _I, _I, _I, _I, _P, _P],
+    "bdl_lstm_seq_bwd": [_P, _L, _L, _P, _P, _P, _P, _P, _I, _P, _P, _I, _I, _I, _I, _P, _P],
     "bdl_quantize_mxfp8": [_P, _P, _P, _L, _L, _L, _L, _I, _P],
     "bdl_gemm_mxfp8": [_P, _P, _P, _P, _P, _P, _I, _I, _I, _L, _L, _L, _I, _I, _P],
     "bdl_scatter_acc_clear_f32": [_P, _P, _P, _P, _I, _P],

@@ -49,6 +49,7 @@ _DEFAULTS: dict[str, Any] = {
     # misc
     "bigdl.quantized.blockScale": False,     # Quantizer: MX block-scaled fp8 (one scale per 32 inputs) for Linear layers
     "bigdl.metrics": False,                  # per-phase host timers in the training loop (Metrics summary at the end)
+    "bigdl.rnn.persistent": True,            # LSTM layers: one persistent kernel per sequence (csrc/lstm_seq.cu)
     "bigdl.cudaGraph": True,
     "bigdl.nvtx": False,                     # NVTX range per layer call (utils/profiling.py)
     "bigdl.wgrad.stream": False,             # issue weight-gradient GEMMs on a side stream (joined after backward)

@@ -247,6 +247,21 @@ int bdl_lstm_gates_fwd(const void* g, const float* c_prev, void* h, float* c, vo
                        long long ldg, void* stream);
 int bdl_lstm_gates_bwd(const void* dh, const float* dc_in, const void* gates, const float* c, const float* c_prev,
                        void* dg, float* dc_prev, long long B, int H, void* stream);
+/* Persistent LSTM over a whole sequence (csrc/lstm_seq.cu): ONE cooperative launch per layer and direction runs all T
+ * steps with W_hh resident in shared memory, split across the SMs by hidden unit; the input projection xw = x W_ih^T + b
+ * [B,T,4H] is computed beforehand by one GEMM. Forward keeps hs [B,T,H] (hs_hread >= H: readable zero-padded row width,
+ * for 16-byte staging loads), cs [T,B,H] and the activated gates [T,B,4H];
+ * backward (BPTT, 2-D split of W_hh) produces dG [T,B,4,dg_hp] (dg_hp >= H: zero-padded, 16-byte aligned gate blocks),
+ * the gradient w.r.t. the gate pre-activations, from which
+ * dW_ih, dW_hh, db and dx are single GEMMs. counter: one zeroed uint32; dh_rec [2,B,H] / dc [B,H]: zeroed fp32 scratch
+ * (or the upstream dh_T in slot 0 / dc_T); at return dh_rec slot (T & 1) = dh0, dc = dc0. Gate order [i, g, f, o].
+ * Reference: S/nn/Recurrent.scala:243-527, S/nn/LSTM.scala:44-175, S/nn/mkldnn/RNN.scala:31-100. */
+int bdl_lstm_seq_fwd(const void* xw, long long xw_sb, long long xw_st, const void* whh, const void* h0, const float* c0,
+                     void* hs, long long hs_sb, long long hs_st, int hs_hread, float* cs, void* gates, float* c_last,
+                     int B, int T, int H, int reverse, void* counter, void* stream);
+int bdl_lstm_seq_bwd(const void* dhs, long long dhs_sb, long long dhs_st, const void* whh, const void* gates,
+                     const float* cs, const float* c0, void* dG, int dg_hp, float* dh_rec, float* dc, int B, int T,
+                     int H, int reverse, void* counter, void* stream);
 /* GRU step, two pointwise stages around the recurrent GEMMs (S/nn/GRU.scala): all tensors bf16; ld* = row pitches */
 int bdl_gru_rz_fwd(const void* xrz, const void* hg, const void* h, void* rz, void* hr, long long B, int H,
                    long long ldx, long long ldh, void* stream);

@@ -66,6 +66,16 @@ class Storage:
         return self
 
 
+def _native_math(*ts):
+    """The native fp32/fp64 BLAS + VML module when every operand qualifies (see tensor/mkl.py), else None."""
+    from . import mkl
+    t0 = ts[0]
+    for t in ts:
+        if not mkl.enabled_for(t) or t.dtype != t0.dtype or t.device != t0.device:
+            return None
+    return mkl
+
+
 class Tensor:
     __slots__ = ("t",)
 
@@ -415,10 +425,14 @@ class Tensor:
 
     def addmm(self, *a) -> "Tensor":
         """addmm(m1, m2) | addmm(v2, m1, m2) | addmm(v1, M, v2, m1, m2): self = v1*M + v2*m1@m2."""
-        if len(a) == 2:
-            self.t.addmm_(_raw(a[0]), _raw(a[1]))
-        elif len(a) == 3:
-            self.t.addmm_(_raw(a[1]), _raw(a[2]), alpha=a[0])
+        if len(a) in (2, 3):
+            alpha, m1, m2 = (1.0, *a) if len(a) == 2 else a
+            m1, m2 = _raw(m1), _raw(m2)
+            nm = _native_math(self.t, m1, m2)
+            if nm is not None and self.t.dim() == 2 and self.t.stride(1) == 1 and m1.dim() == 2 and m2.dim() == 2:
+                nm.mm(self.t, m1, m2, alpha=alpha, beta=1.0)
+            else:
+                self.t.addmm_(m1, m2, alpha=alpha)
         elif len(a) == 4:
             self._assign(torch.addmm(_raw(a[0]) * a[1] if False else _raw(a[0]), _raw(a[2]), _raw(a[3]), beta=1, alpha=a[1]))
         else:
@@ -427,32 +441,59 @@ class Tensor:
         return self
 
     def addmv(self, *a) -> "Tensor":
-        if len(a) == 2:
-            self.t.addmv_(_raw(a[0]), _raw(a[1]))
-        elif len(a) == 3:
-            self.t.addmv_(_raw(a[1]), _raw(a[2]), alpha=a[0])
+        if len(a) in (2, 3):
+            alpha, m, x = (1.0, *a) if len(a) == 2 else a
+            m, x = _raw(m), _raw(x)
+            nm = _native_math(self.t, m, x)
+            if nm is not None and self.t.dim() == 1 and m.dim() == 2 and x.dim() == 1:
+                nm.mv(self.t, m, x, alpha=alpha, beta=1.0)
+            else:
+                self.t.addmv_(m, x, alpha=alpha)
         else:
             beta, v, alpha, m, x = a
             self._assign(torch.addmv(_raw(v), _raw(m), _raw(x), beta=beta, alpha=alpha))
         return self
 
     def addr(self, *a) -> "Tensor":
-        if len(a) == 2:
-            self.t.addr_(_raw(a[0]), _raw(a[1]))
-        elif len(a) == 3:
-            self.t.addr_(_raw(a[1]), _raw(a[2]), alpha=a[0])
+        if len(a) in (2, 3):
+            alpha, x, y = (1.0, *a) if len(a) == 2 else a
+            x, y = _raw(x), _raw(y)
+            nm = _native_math(self.t, x, y)
+            if nm is not None and self.t.dim() == 2 and self.t.stride(1) == 1 and x.dim() == 1 and y.dim() == 1:
+                nm.ger(self.t, x, y, alpha=alpha)
+            else:
+                self.t.addr_(x, y, alpha=alpha)
         else:
             v1, M, v2, x, y = a
             self._assign(torch.addr(_raw(M), _raw(x), _raw(y), beta=v1, alpha=v2))
         return self
 
     def mm(self, m1, m2) -> "Tensor":
-        self._assign(_raw(m1) @ _raw(m2))
+        a, b = _raw(m1), _raw(m2)
+        nm = _native_math(a, b)
+        if nm is not None and a.dim() == 2 and b.dim() == 2:
+            out = self._result_buffer((a.shape[0], b.shape[1]), a)
+            nm.mm(out, a, b)                  # sgemm / dgemm of csrc/blas_vml.cu (N1)
+            return self
+        self._assign(a @ b)
         return self
 
     def mv(self, m, v) -> "Tensor":
-        self._assign(_raw(m) @ _raw(v))
+        a, x = _raw(m), _raw(v)
+        nm = _native_math(a, x)
+        if nm is not None and a.dim() == 2 and x.dim() == 1:
+            out = self._result_buffer((a.shape[0],), a)
+            nm.mv(out, a, x)
+            return self
+        self._assign(a @ x)
         return self
+
+    def _result_buffer(self, shape, like: torch.Tensor) -> torch.Tensor:
+        """self.t resized to ``shape`` (contiguous, dtype/device of ``like``) for a native kernel to write into."""
+        if (tuple(self.t.shape) != tuple(shape) or self.t.dtype != like.dtype or self.t.device != like.device
+                or not self.t.is_contiguous()):
+            self.t = torch.empty(shape, dtype=like.dtype, device=like.device)
+        return self.t
 
     def bmm(self, b1, b2) -> "Tensor":
         self._assign(torch.bmm(_raw(b1), _raw(b2)))
@@ -463,7 +504,11 @@ class Tensor:
         return self
 
     def dot(self, other) -> float:
-        return float((self.t.reshape(-1) * _raw(other).reshape(-1)).sum())
+        o = _raw(other)
+        nm = _native_math(self.t, o)
+        if nm is not None and self.t.numel() == o.numel():
+            return nm.dot(self.t, o)
+        return float((self.t.reshape(-1) * o.reshape(-1)).sum())
 
     def _assign(self, val: torch.Tensor):
         if tuple(val.shape) == tuple(self.t.shape) and val.dtype == self.t.dtype:
@@ -471,7 +516,19 @@ class Tensor:
         else:
             self.t = val.to(self.t.dtype) if self.t.numel() else val
 
+    _VML = {torch.sqrt: "Sqrt", torch.log: "Ln", torch.log1p: "Log1p", torch.exp: "Exp", torch.tanh: "Tanh",
+            torch.abs: "Abs"}
+
     def _unary(self, fn, src=None) -> "Tensor":
+        op = Tensor._VML.get(fn)
+        if op is not None:
+            s = self.t if src is None else _raw(src)
+            nm = _native_math(s)
+            if nm is not None and s.is_contiguous() and s.numel():
+                out = self.t if src is None else self._result_buffer(tuple(s.shape), s)
+                if out.is_contiguous():
+                    nm.unary(op, out, s)          # vsSqrt / vdLn ... of the native vector-math library (N1)
+                    return self
         if src is None:
             self.t.copy_(fn(self.t))
         else:

@@ -58,6 +58,7 @@ _DEFAULTS: dict[str, Any] = {
     "bigdl.utils.LoggerFilter.logFile": "bigdl.log",
     "bigdl.utils.LoggerFilter.enableSparkLog": True,
     "bigdl.tensor.fold": 1000,
+    "bigdl.tensor.nativeMath": "cuda",       # fp32/fp64 Tensor BLAS + VML on the native entry points: cuda | all | off
     "bigdl.ModelBroadcastFactory": "default",
 }
 

@@ -286,6 +286,25 @@ int bdl_quantize_e4m3(const void* x, void* q, const float* absmax, int per_row, 
 int bdl_fp8_colscale(const float* act_absmax, const float* w_absmax, float* out, int n, void* stream);
 int bdl_quantize_int8_rows(const float* w, void* q, const float* absmax, long long rows, long long cols, void* stream);
 
+/* ---- fp32 / fp64 BLAS + vector math for Tensor[Float] / Tensor[Double] (csrc/blas_vml.cu; host twins bdlh_* in
+ *      csrc/host/blas_vml.cpp). Reference: core/mkl2017-xeon-blas/src/main/c/mkl.c (vsAdd ... vsgemm, vd*), called from
+ *      S/tensor/TensorNumeric.scala:253-420. Column-major like BLAS; offsets are folded into the pointers.
+ *      vml op: 0 Add 1 Sub 2 Mul 3 Div 4 Powx(a, scalar) 5 Ln 6 Exp 7 Sqrt 8 Tanh 9 Abs 10 Log1p; b is NULL for unary ops.
+ *      dot writes its result to device memory (*result), deterministic summation order. */
+#define BDL_DECLARE_BLAS(SUF, T)                                                                                       \
+  int bdl_vml_##SUF(int op, long long n, const T* a, const T* b, T scalar, T* y, void* stream);                         \
+  int bdl_blas_axpy_##SUF(long long n, T alpha, const T* x, long long incx, T* y, long long incy, void* stream);        \
+  int bdl_blas_scal_##SUF(long long n, T alpha, T* x, long long incx, void* stream);                                    \
+  int bdl_blas_dot_##SUF(long long n, const T* x, long long incx, const T* y, long long incy, T* result, void* stream); \
+  int bdl_blas_ger_##SUF(int m, int n, T alpha, const T* x, long long incx, const T* y, long long incy, T* A,           \
+                         long long lda, void* stream);                                                                 \
+  int bdl_blas_gemv_##SUF(int trans, int m, int n, T alpha, const T* A, long long lda, const T* x, long long incx,      \
+                          T beta, T* y, long long incy, void* stream);                                                 \
+  int bdl_blas_gemm_##SUF(int transa, int transb, int m, int n, int k, T alpha, const T* A, long long lda, const T* B,  \
+                          long long ldb, T beta, T* C, long long ldc, void* stream);
+BDL_DECLARE_BLAS(f32, float)
+BDL_DECLARE_BLAS(f64, double)
+
 #ifdef __cplusplus
 }
 #endif

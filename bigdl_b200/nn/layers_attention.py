@@ -72,9 +72,13 @@ class Attention(Container):
         xs = to_table(input).to_list()
         x, y = xs[0], xs[1]
         bias = xs[2] if len(xs) > 2 else None
-        q = self._split(self.q._call(x))
-        k = self._split(self.k._call(y))
-        v = self._split(self.v._call(y))
+        qp, kp, vp = self.q._call(x), self.k._call(y), self.v._call(y)
+        if self._cache is None and not (self.train and self.attention_dropout > 0) and qp.dim() == 3:
+            from ..ops import attention as fused
+            if fused.supported(qp, kp, vp, self.num_heads) and (bias is None or not bias.requires_grad):
+                # one tcgen05 kernel: QK^T, bias, softmax and PV with the logits kept on chip (csrc/attention.cu)
+                return self.o._call(fused.attention(qp, kp, vp, bias, self.num_heads))
+        q, k, v = self._split(qp), self._split(kp), self._split(vp)
         if self._cache is not None:
             if "k" in self._cache:
                 k = torch.cat([self._cache["k"], k], dim=2)

@@ -79,6 +79,26 @@ static int make_tmap_2d(CUtensorMap* out, CUtensorMapDataType dt, int esize, con
   return BDL_OK;
 }
 
+int bdl_make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t dim0, uint64_t dim1, uint64_t dim2, long long ld1,
+                          long long ld2, uint32_t box0, uint32_t box1) {
+  EncodeTiledFn fn = get_encode_tiled();
+  if (!fn) return bdl_fail("cuTensorMapEncodeTiled entry point not available (no CUDA driver?)");
+  cuuint64_t dims[3] = {dim0, dim1, dim2};
+  cuuint64_t strides[2] = {static_cast<cuuint64_t>(ld1) * 2, static_cast<cuuint64_t>(ld2) * 2};
+  cuuint32_t box[3] = {box0, box1, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    char buf[256];
+    snprintf(buf, sizeof(buf), "cuTensorMapEncodeTiled(3d) failed (CUresult %d) dims=(%llu,%llu,%llu) ld=(%lld,%lld)",
+             (int)r, (unsigned long long)dim0, (unsigned long long)dim1, (unsigned long long)dim2, ld1, ld2);
+    return bdl_fail(buf);
+  }
+  return BDL_OK;
+}
+
 int bdl_make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t dim0, uint64_t dim1, long long ld, uint32_t box0,
                           uint32_t box1) {
   return make_tmap_2d(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dim0, dim1, ld, box0, box1);

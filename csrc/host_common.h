@@ -13,6 +13,10 @@ int bdl_num_sms();                                   // SM count of the current 
 // 2-D bf16 tensor map with 128-byte swizzle. dim0 is the contiguous dimension; ld is the row pitch in elements.
 int bdl_make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t dim0, uint64_t dim1, long long ld, uint32_t box0,
                           uint32_t box1);
+// 3-D bf16 tensor map (dims {dim0, dim1, dim2}, pitches ld1 / ld2 in elements), box {box0, box1, 1}, 128-byte swizzle,
+// zero fill outside the tensor: a [batch, length, width] activation read one (length x width) tile at a time.
+int bdl_make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t dim0, uint64_t dim1, uint64_t dim2, long long ld1,
+                          long long ld2, uint32_t box0, uint32_t box1);
 // Same for 1-byte elements (fp8): box0 is in elements (= bytes), at most 128.
 int bdl_make_tmap_2d_bf16_sw(CUtensorMap* out, const void* base, uint64_t dim0, uint64_t dim1, long long ld,
                              uint32_t box0, uint32_t box1, int swizzle_bytes);

@@ -286,6 +286,15 @@ int bdl_quantize_e4m3(const void* x, void* q, const float* absmax, int per_row, 
 int bdl_fp8_colscale(const float* act_absmax, const float* w_absmax, float* out, int n, void* stream);
 int bdl_quantize_int8_rows(const float* w, void* q, const float* absmax, long long rows, long long cols, void* stream);
 
+/* ---- fused multi-head attention forward (csrc/attention.cu): O = softmax(scale * Q K^T + bias) V per (batch, head), the
+ *      logits stay in TMEM / shared memory. Reference: S/nn/Attention.scala:95-114. Q [B,Lq,heads*D], K/V [B,Lk,heads*D]
+ *      bf16 (pitches in elements, multiples of 8), D = 64 or 128; bias fp32 with element strides over (batch, head,
+ *      query), key stride 1, 0 = broadcast, NULL = none; causal masks key > query + (Lk - Lq); lse [B,heads,Lq] fp32. */
+int bdl_attention_fwd(const void* Q, long long q_sb, long long q_sl, const void* K, long long k_sb, long long k_sl,
+                      const void* V, long long v_sb, long long v_sl, const float* bias, long long bias_sb,
+                      long long bias_sh, long long bias_sq, void* O, long long o_sb, long long o_sl, float* lse, int B,
+                      int heads, int Lq, int Lk, int D, float scale, int causal, void* stream);
+
 /* ---- fp32 / fp64 BLAS + vector math for Tensor[Float] / Tensor[Double] (csrc/blas_vml.cu; host twins bdlh_* in
  *      csrc/host/blas_vml.cpp). Reference: core/mkl2017-xeon-blas/src/main/c/mkl.c (vsAdd ... vsgemm, vd*), called from
  *      S/tensor/TensorNumeric.scala:253-420. Column-major like BLAS; offsets are folded into the pointers.

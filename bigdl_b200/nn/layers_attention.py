@@ -35,7 +35,9 @@ def position_signal(length: int, channels: int, device, dtype=torch.float32, min
 def causal_bias(length: int, device, dtype=torch.float32) -> torch.Tensor:
     """[1, 1, L, L] additive mask with -1e9 above the diagonal (TransformerOperation.attentionBiasLowerTriangle)."""
     m = torch.full((length, length), -1e9, device=device, dtype=torch.float32).triu(1)
-    return m.reshape(1, 1, length, length).to(dtype)
+    m = m.reshape(1, 1, length, length).to(dtype)
+    m._bdl_causal = True        # lets the fused kernel mask by index (and skip whole tiles) instead of reading L*L floats
+    return m
 
 
 def padding_bias(ids: torch.Tensor, padding_value: float, dtype=torch.float32) -> torch.Tensor:
@@ -77,7 +79,8 @@ class Attention(Container):
             from ..ops import attention as fused
             if fused.supported(qp, kp, vp, self.num_heads) and (bias is None or not bias.requires_grad):
                 # one tcgen05 kernel: QK^T, bias, softmax and PV with the logits kept on chip (csrc/attention.cu)
-                return self.o._call(fused.attention(qp, kp, vp, bias, self.num_heads))
+                causal = bool(getattr(bias, "_bdl_causal", False)) and qp.shape[1] == kp.shape[1]
+                return self.o._call(fused.attention(qp, kp, vp, None if causal else bias, self.num_heads, causal=causal))
         q, k, v = self._split(qp), self._split(kp), self._split(vp)
         if self._cache is not None:
             if "k" in self._cache:

@@ -17,6 +17,8 @@ from . import _lib
 _P, _I, _L, _F = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_float
 _lib.declare("bdl_attention_fwd", [_P, _L, _L, _P, _L, _L, _P, _L, _L, _P, _L, _L, _L, _P, _L, _L, _P, _I, _I, _I, _I,
                                    _I, _F, _I, _P])
+_lib.declare("bdl_attention_bwd", [_P, _L, _L, _P, _L, _L, _P, _L, _L, _P, _L, _L, _P, _L, _L, _P, _P, _P, _L, _L, _L, _P, _L,
+                                   _L, _P, _L, _L, _P, _L, _L, _I, _I, _I, _I, _I, _F, _I, _P])
 
 
 def supported(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int) -> bool:
@@ -57,6 +59,9 @@ def _bias_view(bias, B, heads, Lq, Lk):
     return b, tuple(st)
 
 
+_FORCE_TORCH_BACKWARD = False        # tests flip this to compare the native backward with the torch composition
+
+
 class AttentionFn(Function):
     @staticmethod
     def forward(ctx, q, k, v, bias, heads, scale, causal):
@@ -83,6 +88,25 @@ class AttentionFn(Function):
         heads, scale, causal, has_bias = ctx.cfg
         B, Lq, W = q.shape
         Lk, D = k.shape[1], W // heads
+        lib = _lib.cuda_lib()
+        if lib is not None and not _FORCE_TORCH_BACKWARD:
+            # two tcgen05 kernels (csrc/attention_bwd.cu): dQ (+ Delta), then dK / dV; P is recomputed from lse
+            go = _rows(d_out if d_out.dtype == torch.bfloat16 else d_out.to(torch.bfloat16))
+            qkv_grad = torch.empty((3, B, max(Lq, Lk), W), dtype=torch.bfloat16, device=q.device)
+            dq, dk, dv = qkv_grad[0, :, :Lq], qkv_grad[1, :, :Lk], qkv_grad[2, :, :Lk]
+            delta = torch.empty((B, heads, Lq), dtype=torch.float32, device=q.device)
+            bt = bias if has_bias else None
+            sb, sh, sq = (0, 0, 0)
+            if bt is not None:
+                sb, sh, sq = [0 if bt.shape[d] == 1 else bt.stride(d) for d in (0, 1, 2)]
+            _lib.check(lib.bdl_attention_bwd(
+                q.data_ptr(), q.stride(0), q.stride(1), k.data_ptr(), k.stride(0), k.stride(1), v.data_ptr(), v.stride(0),
+                v.stride(1), out.data_ptr(), out.stride(0), out.stride(1), go.data_ptr(), go.stride(0), go.stride(1),
+                lse.data_ptr(), delta.data_ptr(), _lib.ptr(bt), sb, sh, sq, dq.data_ptr(), dq.stride(0), dq.stride(1),
+                dk.data_ptr(), dk.stride(0), dk.stride(1), dv.data_ptr(), dv.stride(0), dv.stride(1), B, heads, Lq, Lk, D,
+                scale, int(causal), _lib.stream_ptr()), "bdl_attention_bwd")
+            _lib.count_launch(2)
+            return dq, dk, dv, None, None, None, None
 
         def split(t, L):
             return t.reshape(B, L, heads, D).transpose(1, 2)          # [B, heads, L, D]

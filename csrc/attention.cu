@@ -154,42 +154,56 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       const int k0 = j * kTileK;
       mbar_wait(smem_u32(&bars->s_full), ph);
       tc_fence_after();
-      // pass 1: row maximum of this tile
+      // Interior tiles without a bias tensor need no masks and no per-element scale in the max pass: the softmax warps
+      // are bound by instruction issue (one thread per row), so the common case is kept to ~4 instructions per logit.
+      const bool plain = (brow == nullptr) && (k0 + kTileK <= key_limit);
       float m_tile = -INFINITY;
 #pragma unroll 1
       for (int c0 = 0; c0 < kTileK; c0 += 32) {
-        uint32_t v0[16], v1[16];
-        tmem_ld_16(tS + lane_base + static_cast<uint32_t>(c0), v0);
-        tmem_ld_16(tS + lane_base + static_cast<uint32_t>(c0 + 16), v1);
+        uint32_t v[32];
+        tmem_ld_32(tS + lane_base + static_cast<uint32_t>(c0), v);    // warp-collective: never inside a divergent branch
         tmem_ld_wait();
+        if (plain) {
 #pragma unroll
-        for (int e = 0; e < 32; ++e) {
-          const int key = k0 + c0 + e;
-          float s = __uint_as_float(e < 16 ? v0[e] : v1[e - 16]) * sl2;
-          if (brow != nullptr && key < a.Lk) s += __ldg(brow + key) * kLog2e;
-          if (key < key_limit) m_tile = fmaxf(m_tile, s);
+          for (int e = 0; e < 32; e += 2)
+            m_tile = fmaxf(m_tile, fmaxf(__uint_as_float(v[e]), __uint_as_float(v[e + 1])));
+        } else {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) {
+            const int key = k0 + c0 + e;
+            float s = __uint_as_float(v[e]) * sl2;
+            if (brow != nullptr && key < a.Lk) s += __ldg(brow + key) * kLog2e;
+            if (key < key_limit) m_tile = fmaxf(m_tile, s);
+          }
         }
       }
+      if (plain) m_tile *= sl2;                              // scale > 0: max commutes with it
       const float m_new = fmaxf(m_run, m_tile);
       const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
-      const float alpha = exp2f(m_run - m_use);            // m_run = -inf -> 0
+      const float alpha = ex2_approx(m_run - m_use);        // m_run = -inf -> 0
       // pass 2: p = 2^(s - m), row sum, P tile to shared memory
       float l_tile = 0.f;
 #pragma unroll 1
       for (int c0 = 0; c0 < kTileK; c0 += 32) {
-        uint32_t v0[16], v1[16];
-        tmem_ld_16(tS + lane_base + static_cast<uint32_t>(c0), v0);
-        tmem_ld_16(tS + lane_base + static_cast<uint32_t>(c0 + 16), v1);
+        uint32_t v[32];
+        tmem_ld_32(tS + lane_base + static_cast<uint32_t>(c0), v);
         tmem_ld_wait();
         float pv[32];
+        if (plain) {
 #pragma unroll
-        for (int e = 0; e < 32; ++e) {
-          const int key = k0 + c0 + e;
-          float s = __uint_as_float(e < 16 ? v0[e] : v1[e - 16]) * sl2;
-          if (brow != nullptr && key < a.Lk) s += __ldg(brow + key) * kLog2e;
-          const float p = key < key_limit ? exp2f(s - m_use) : 0.f;
-          pv[e] = p;
-          l_tile += p;
+          for (int e = 0; e < 32; ++e) {
+            pv[e] = ex2_approx(fmaf(__uint_as_float(v[e]), sl2, -m_use));
+            l_tile += pv[e];
+          }
+        } else {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) {
+            const int key = k0 + c0 + e;
+            float s = __uint_as_float(v[e]) * sl2;
+            if (brow != nullptr && key < a.Lk) s += __ldg(brow + key) * kLog2e;
+            pv[e] = key < key_limit ? ex2_approx(s - m_use) : 0.f;
+            l_tile += pv[e];
+          }
         }
 #pragma unroll
         for (int g = 0; g < 4; ++g) {

@@ -55,6 +55,14 @@ static EncodeTiledFn get_encode_tiled() {
   return fn;
 }
 
+// cuTensorMapEncode* are driver calls: a thread that has not yet made a runtime call that binds the primary context
+// (autograd's backward worker threads, served from the caching allocator) gets CUDA_ERROR_INVALID_CONTEXT. Binding is
+// what cudaSetDevice does since CUDA 12.
+static bool bind_primary_context() {
+  int dev = 0;
+  return cudaGetDevice(&dev) == cudaSuccess && cudaSetDevice(dev) == cudaSuccess;
+}
+
 static CUtensorMapSwizzle swizzle_enum(int bytes) {
   return bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B : bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B;
 }
@@ -67,8 +75,12 @@ static int make_tmap_2d(CUtensorMap* out, CUtensorMapDataType dt, int esize, con
   cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * esize};
   cuuint32_t box[2] = {box0, box1};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(out, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  swizzle_enum(swizzle_bytes), CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = CUDA_SUCCESS;
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    r = fn(out, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+           swizzle_enum(swizzle_bytes), CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_ERROR_INVALID_CONTEXT || !bind_primary_context()) break;
+  }
   if (r != CUDA_SUCCESS) {
     char buf[256];
     snprintf(buf, sizeof(buf),
@@ -87,9 +99,13 @@ int bdl_make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t dim0, uin
   cuuint64_t strides[2] = {static_cast<cuuint64_t>(ld1) * 2, static_cast<cuuint64_t>(ld2) * 2};
   cuuint32_t box[3] = {box0, box1, 1};
   cuuint32_t estr[3] = {1, 1, 1};
-  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = CUDA_SUCCESS;
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_ERROR_INVALID_CONTEXT || !bind_primary_context()) break;
+  }
   if (r != CUDA_SUCCESS) {
     char buf[256];
     snprintf(buf, sizeof(buf), "cuTensorMapEncodeTiled(3d) failed (CUresult %d) dims=(%llu,%llu,%llu) ld=(%lld,%lld)",
@@ -171,10 +187,14 @@ static int make_tmap_im2col(CUtensorMap* out, CUtensorMapDataType dt, int esize,
   int lower[2] = {lower_w, lower_h};
   int upper[2] = {upper_w, upper_h};
   cuuint32_t estr[4] = {1, static_cast<cuuint32_t>(stride_w), static_cast<cuuint32_t>(stride_h), 1};
-  CUresult r = fn(out, dt, 4, const_cast<void*>(base), dims, strides, lower, upper,
-                  static_cast<cuuint32_t>(channels_per_pixel), static_cast<cuuint32_t>(pixels_per_column), estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_enum(swizzle_bytes), CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = CUDA_SUCCESS;
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    r = fn(out, dt, 4, const_cast<void*>(base), dims, strides, lower, upper,
+           static_cast<cuuint32_t>(channels_per_pixel), static_cast<cuuint32_t>(pixels_per_column), estr,
+           CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_enum(swizzle_bytes), CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_ERROR_INVALID_CONTEXT || !bind_primary_context()) break;
+  }
   if (r != CUDA_SUCCESS) {
     char buf[320];
     snprintf(buf, sizeof(buf),

@@ -294,6 +294,14 @@ int bdl_attention_fwd(const void* Q, long long q_sb, long long q_sl, const void*
                       const void* V, long long v_sb, long long v_sl, const float* bias, long long bias_sb,
                       long long bias_sh, long long bias_sq, void* O, long long o_sb, long long o_sl, float* lse, int B,
                       int heads, int Lq, int Lk, int D, float scale, int causal, void* stream);
+/* gradients w.r.t. Q, K, V (csrc/attention_bwd.cu): probabilities recomputed from lse; delta = [B,heads,Lq] fp32 scratch */
+int bdl_attention_bwd(const void* Q, long long q_sb, long long q_sl, const void* K, long long k_sb, long long k_sl,
+                      const void* V, long long v_sb, long long v_sl, const void* O, long long o_sb, long long o_sl,
+                      const void* dO, long long do_sb, long long do_sl, const float* lse, float* delta,
+                      const float* bias, long long bias_sb, long long bias_sh, long long bias_sq, void* dQ,
+                      long long dq_sb, long long dq_sl, void* dK, long long dk_sb, long long dk_sl, void* dV,
+                      long long dv_sb, long long dv_sl, int B, int heads, int Lq, int Lk, int D, float scale,
+                      int causal, void* stream);
 
 /* ---- fp32 / fp64 BLAS + vector math for Tensor[Float] / Tensor[Double] (csrc/blas_vml.cu; host twins bdlh_* in
  *      csrc/host/blas_vml.cpp). Reference: core/mkl2017-xeon-blas/src/main/c/mkl.c (vsAdd ... vsgemm, vd*), called from

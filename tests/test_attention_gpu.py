@@ -69,6 +69,32 @@ def test_strided_inputs_and_backward():
     assert _rel(got, x.grad) < 3e-2
 
 
+@pytest.mark.parametrize("B,Lq,Lk,heads,D,kind", [(2, 128, 128, 2, 64, "none"), (2, 200, 200, 3, 64, "causal_flag"),
+                                                  (1, 77, 300, 2, 64, "padding"), (2, 256, 130, 2, 128, "full"),
+                                                  (1, 300, 300, 2, 128, "causal_bias"), (2, 40, 40, 1, 64, "none")])
+def test_native_backward_matches_fp32(B, Lq, Lk, heads, D, kind):
+    q, k, v = _qkv(B, Lq, Lk, heads, D, seed=5)
+    bias, causal = None, False
+    if kind == "padding":
+        bias = torch.zeros(B, 1, 1, Lk, device=DEV)
+        bias[0, ..., Lk - 50:] = -1e9
+    elif kind == "full":
+        bias = torch.randn(B, heads, Lq, Lk, device=DEV)
+    elif kind == "causal_bias":
+        bias = torch.full((1, 1, Lq, Lk), -1e9, device=DEV).triu(1)
+    elif kind == "causal_flag":
+        causal = True
+    qs = [t.clone().requires_grad_(True) for t in (q, k, v)]
+    out = A.attention(*qs, bias, heads, causal=causal)
+    go = torch.randn_like(out)
+    out.backward(go)
+    fs = [t.detach().float().requires_grad_(True) for t in (q, k, v)]
+    ref = A.attention_reference(*fs, bias, heads, causal=causal)
+    ref.backward(go.float())
+    for name, got, want in zip("qkv", qs, fs):
+        assert _rel(got.grad, want.grad) < 3e-2, name
+
+
 def test_attention_layer_uses_the_kernel():
     from bigdl_b200.nn.layers_attention import Attention
     from bigdl_b200.ops import _lib

@@ -1,11 +1,12 @@
-"""COCO images + annotation json → SequenceFiles (S/models/utils/COCOSeqFileGenerator.scala): key = image file name,
-value = encoded image bytes followed by a compact annotation block (boxes, category indices, iscrowd flags, RLE masks)."""
+"""COCO images + annotation json -> SequenceFiles (S/models/utils/COCOSeqFileGenerator.scala:71-116).
+
+Record layout of the reference: key = ``COCOSerializeContext`` bytes (file name, height, width, annotations with
+category index / area / bbox / iscrowd / polygons or RLE counts, closed by ``COCODataset.MAGIC_NUM``), value = the raw
+image file bytes. ``read_coco_seqfile`` is the matching reader (DataSet.SeqFileFolder.filesToRoiImageFeatures)."""
 from __future__ import annotations
 
 import argparse
-import json
 import os
-import struct
 
 
 def main(argv=None):
@@ -13,33 +14,38 @@ def main(argv=None):
     ap.add_argument("-f", "--folder", required=True, help="image folder")
     ap.add_argument("-m", "--metaPath", required=True, help="instances_*.json")
     ap.add_argument("-o", "--output", required=True)
+    ap.add_argument("-p", "--parallel", type=int, default=1, help="accepted for compatibility; blocks are written in order")
     ap.add_argument("-b", "--blockSize", type=int, default=12800)
     a = ap.parse_args(argv)
-    from ..dataset.segmentation import COCODataset, MaskUtils
+    from ..dataset.segmentation import COCODataset
     from ..dataset.seqfile import SequenceFileWriter
 
     ds = COCODataset.load(a.metaPath, a.folder)
     os.makedirs(a.output, exist_ok=True)
-    writer, n, idx = None, 0, 0
+    images = []
     for im in ds.images:
-        if writer is None:
-            writer = SequenceFileWriter(os.path.join(a.output, f"coco-seq-{idx}.seq"))
-        with open(im.file_name, "rb") as f:
-            img = f.read()
-        anns = []
-        for an in im.annotations:
-            rle = an.segmentation.toRLE() if an.segmentation is not None else None
-            anns.append({"bbox": list(an.bbox), "category": ds.categoryId2Idx[an.category_id], "iscrowd": int(an.iscrowd),
-                         "rle": MaskUtils.RLE2String(rle) if rle is not None else None})
-        meta = json.dumps({"height": im.height, "width": im.width, "annotations": anns}).encode()
-        writer.append(os.path.basename(im.file_name).encode(), struct.pack(">i", len(img)) + img + meta)
-        n += 1
-        if n == a.blockSize:
-            writer.close()
-            writer, n, idx = None, 0, idx + 1
-    if writer is not None:
+        if os.path.isfile(im.path):
+            images.append(im)
+        else:
+            print(f"[Warning] The image file {os.path.basename(im.path)} does not exist.")
+    blocks = 0
+    for blk, start in enumerate(range(0, len(images), a.blockSize)):
+        writer = SequenceFileWriter(os.path.join(a.output, f"coco-seq-{blk}.seq"))
+        for im in images[start:start + a.blockSize]:
+            writer.append(ds.imageKey(im), im.data)
         writer.close()
-    print(f"{len(ds.images)} images → {idx + (1 if n else 0)} sequence files under {a.output}")
+        blocks += 1
+    print(f"{len(images)} images -> {blocks} sequence files under {a.output}")
+
+
+def read_coco_seqfile(path: str):
+    """Yield ``(file_name, height, width, [SimpleAnnotation], image_bytes)`` from one generated file."""
+    from ..dataset.segmentation import COCODataset
+    from ..dataset.seqfile import read_sequence_file
+
+    for key, value in read_sequence_file(path):
+        name, h, w, anns = COCODataset.parseKey(key)
+        yield name, h, w, anns, value
 
 
 if __name__ == "__main__":

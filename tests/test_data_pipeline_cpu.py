@@ -113,7 +113,7 @@ def test_rle_masks_and_coco(tmp_path):
     m2[2:5, 3:6] = 1
     assert abs(MaskUtils.rleIOU(rle, MaskUtils.binaryToRLE(m2)) - 4 / 14) < 1e-6
     poly = PolyMasks([[2, 1, 4, 1, 4, 3, 2, 3]], 5, 6).toRLE()
-    assert MaskUtils.rleArea(poly) == 9
+    assert MaskUtils.rleArea(poly) == 4                     # COCO rule: pixel centres inside [2,4) x [1,3)
     ann = {"images": [{"id": 7, "height": 5, "width": 6, "file_name": "a.jpg"}],
            "categories": [{"id": 18, "name": "dog"}, {"id": 3, "name": "car"}],
            "annotations": [{"id": 1, "image_id": 7, "category_id": 18, "bbox": [2, 1, 3, 3], "area": 9, "iscrowd": 0,
@@ -123,7 +123,7 @@ def test_rle_masks_and_coco(tmp_path):
     p = tmp_path / "ann.json"
     p.write_text(json.dumps(ann))
     ds = COCODataset.load(str(p), "/imgs")
-    assert ds.categoryId2Idx == {3: 1, 18: 2} and len(ds.images[0].annotations) == 2
+    assert ds.categoryId2Idx == {18: 1, 3: 2} and len(ds.images[0].annotations) == 2        # json order, 1-based
     assert isinstance(ds.images[0].annotations[1].segmentation, RLEMasks)
 
 

@@ -598,10 +598,30 @@ def save_module(module, path: str, weight_path: str | None = None, overwrite: bo
             av.dataType = pb.DataType.TENSOR
             av.tensorValue.CopyFrom(t)
         _write_weight_file(weight_path, ctx)
+    _write_bytes(path, [root.SerializeToString()])
+
+
+def _write_bytes(path: str, chunks):
+    """Local paths are written atomically (tmp + rename); hdfs:// s3a:// ... go through utils.File (ModulePersister
+    .saveToFile takes the same path kinds, S/utils/serializer/ModuleLoader.scala:199-243)."""
+    if "://" in path and not path.startswith("file://"):
+        from ..utils.file import File
+        File.saveBytes(b"".join(chunks), path, isOverwrite=True)
+        return
+    path = path[7:] if path.startswith("file://") else path
     os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
     with open(path + ".tmp", "wb") as f:
-        f.write(root.SerializeToString())
+        for c in chunks:
+            f.write(c)
     os.replace(path + ".tmp", path)
+
+
+def _read_bytes(path: str) -> bytes:
+    if "://" in path:
+        from ..utils.file import File
+        return File.readBytes(path)
+    with open(path, "rb") as f:
+        return f.read()
 
 
 def _write_weight_file(path: str, ctx: _Ctx):
@@ -629,16 +649,11 @@ def _write_weight_file(path: str, ctx: _Ctx):
         else:
             put(struct.pack(">iii", sid, 2, 0))
     digest = md5.digest()
-    with open(path + ".tmp", "wb") as f:
-        for c in chunks:
-            f.write(c)
-        f.write(struct.pack(">i", len(digest)))
-        f.write(digest)
-    os.replace(path + ".tmp", path)
+    _write_bytes(path, chunks + [struct.pack(">i", len(digest)), digest])
 
 
 def _read_weight_file(path: str) -> dict[int, torch.Tensor]:
-    data = open(path, "rb").read()
+    data = _read_bytes(path)
     pos = 0
 
     def take(n):
@@ -666,7 +681,7 @@ def _read_weight_file(path: str) -> dict[int, torch.Tensor]:
 
 
 def load_module(path: str, weight_path: str | None = None):
-    root = pb.BigDLModule.FromString(open(path, "rb").read())
+    root = pb.BigDLModule.FromString(_read_bytes(path))
     storages: dict[int, torch.Tensor] = {}
     if weight_path:
         storages.update(_read_weight_file(weight_path))

@@ -199,3 +199,44 @@ def test_thread_pool_file_bytes_and_dlmodel_feature_size(tmp_path):
     m.setFeatureSize([3]).setBatchSize(2)
     out = m.transform(pd.DataFrame({"features": [[1.0, 2.0, 3.0], [0.0, 0.0, 0.0]]}))
     assert len(out["prediction"]) == 2 and len(out["prediction"][0]) == 2
+
+
+def test_file_remote_schemes_through_arrow_filesystems(tmp_path):
+    """hdfs:// s3a:// ... resolve to Arrow filesystem clients (S/utils/File.scala:112-193); exercised offline with
+    Arrow's in-memory filesystem registered for a scheme, and a sub-tree of the local disk standing in for a bucket."""
+    import pyarrow.fs as pfs
+    from datetime import datetime, timezone
+    mem = pfs._MockFileSystem(datetime.now(timezone.utc))
+    File.register_filesystem("mem", mem)
+    File.save({"a": [1, 2, 3]}, "mem://models/run1/model.obj")
+    assert File.load("mem://models/run1/model.obj") == {"a": [1, 2, 3]}
+    assert File.exists("mem://models/run1/model.obj") and not File.exists("mem://models/none")
+    with pytest.raises(FileExistsError):
+        File.saveBytes(b"x", "mem://models/run1/model.obj")
+    File.saveBytes(b"x", "mem://models/run1/model.obj", isOverwrite=True)
+    assert File.readBytes("mem://models/run1/model.obj") == b"x"
+    bucket = pfs.SubTreeFileSystem(str(tmp_path), pfs.LocalFileSystem())
+    File.register_filesystem("s3a", bucket)
+    File.saveBytes(b"weights", "s3a://ckpt/w.bin")
+    assert (tmp_path / "ckpt" / "w.bin").read_bytes() == b"weights"
+    with pytest.raises(ValueError):
+        File.saveToHdfs(1, "s3a://ckpt/x", True)
+    from bigdl_b200.utils import file as F
+    F._ARROW_FS.pop("s3a"), F._ARROW_FS.pop("mem")
+
+
+def test_module_save_load_on_a_remote_scheme(tmp_path):
+    import pyarrow.fs as pfs
+    from bigdl_b200.nn import layer as nn
+    from bigdl_b200.nn.module import Module
+    from bigdl_b200.utils import file as F
+    File.register_filesystem("hdfs", pfs.SubTreeFileSystem(str(tmp_path), pfs.LocalFileSystem()))
+    try:
+        m = nn.Sequential().add(nn.Linear(4, 3)).add(nn.ReLU())
+        m.saveModule("hdfs://models/m.bigdl", "hdfs://models/m.bin", overWrite=True)
+        assert (tmp_path / "models" / "m.bigdl").exists() and (tmp_path / "models" / "m.bin").exists()
+        m2 = Module.loadModule("hdfs://models/m.bigdl", "hdfs://models/m.bin")
+        x = torch.randn(2, 4)
+        assert torch.allclose(m.forward(x), m2.forward(x))
+    finally:
+        F._ARROW_FS.pop("hdfs", None)

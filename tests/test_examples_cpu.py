@@ -69,3 +69,17 @@ def test_keras_imdb_lstm_example_learns():
 
 def test_image_validation_example_runs_the_imageframe_path():
     assert _load("image_validation").main(["-n", "90", "-e", "25"]) > 0.9
+
+
+def test_udf_predictor_example():
+    assert _load("udf_predictor").main(["--maxEpoch", "5"]) > 0.8
+
+
+def test_dlframes_image_example():
+    acc, same = _load("dlframes_image").main([])
+    assert acc >= 0.8 and same == 1.0
+
+
+def test_tensorflow_load_save_example():
+    diff, acc, frozen = _load("tensorflow_load_save").main([])
+    assert diff < 1e-4 and acc > 0.8 and frozen

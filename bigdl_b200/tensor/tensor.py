@@ -684,6 +684,196 @@ class Tensor:
     def __truediv__(self, o): return Tensor(self.t / _raw(o))
     def __neg__(self): return Tensor(-self.t)
 
+    # ------------------------------------------------------------------ rest of the Tensor / TensorMath surface
+    def _subset(self, spec):
+        """View selected by a Table / sequence of per-dimension entries (S/tensor/Tensor.scala:196-234): an int selects
+        (1-based; negative counts from the end), a 2-element entry ``(start, end)`` narrows inclusively, an empty entry
+        keeps the dimension."""
+        from ..utils.table import Table
+        items = spec.to_list() if isinstance(spec, Table) else list(spec)
+        out, dim = self.t, 0
+        for it in items:
+            if isinstance(it, Table):
+                it = it.to_list()
+            if isinstance(it, (list, tuple)):
+                if len(it) == 0:
+                    dim += 1
+                    continue
+                n = out.shape[dim]
+                a = it[0] if it[0] > 0 else n + it[0] + 1
+                b = (it[1] if it[1] > 0 else n + it[1] + 1) if len(it) > 1 else n
+                out = out.narrow(dim, a - 1, b - a + 1)
+                dim += 1
+            else:
+                i = int(it)
+                i = i if i > 0 else out.shape[dim] + i + 1
+                out = out.select(dim, i - 1)
+        return out
+
+    def apply(self, index):
+        """``apply(i)`` = select along dim 1; ``apply([i, j, ...])`` with one index per dim = the value;
+        ``apply(Table(...))`` = sub-tensor view."""
+        from ..utils.table import Table
+        if isinstance(index, int):
+            return self.select(1, index if index > 0 else self.t.shape[0] + index + 1) if self.t.dim() > 1 \
+                else Tensor(self.t[index - 1 if index > 0 else index])
+        if isinstance(index, Table) or any(isinstance(i, (list, tuple, Table)) for i in index):
+            return Tensor(self._subset(index))
+        return self.valueAt(*index)
+
+    def update(self, index, value):
+        """``update(i, v | tensor)``, ``update([i, j, ...], v)``, ``update(Table(...), v | tensor)``,
+        ``update(predicate, v)`` (S/tensor/Tensor.scala:236-319)."""
+        from ..utils.table import Table
+        if callable(index):
+            flat = self.t.reshape(-1)
+            mask = torch.tensor([bool(index(x)) for x in flat.tolist()], dtype=torch.bool, device=flat.device)
+            self.t.masked_fill_(mask.reshape(self.t.shape), value)
+            return self
+        if isinstance(index, int):
+            target = self.t.select(0, index - 1 if index > 0 else index)
+        elif isinstance(index, Table) or any(isinstance(i, (list, tuple, Table)) for i in index):
+            target = self._subset(index)
+        else:
+            self.setValue(*index, value)
+            return self
+        if isinstance(value, (Tensor, torch.Tensor)):
+            target.copy_(_raw(value))
+        else:
+            target.fill_(value)
+        return self
+
+    def applyFun(self, other, func) -> "Tensor":
+        """self[i] = func(other[i]) over same-sized tensors (possibly of another numeric type)."""
+        src = _raw(other).reshape(-1).tolist()
+        self.t.copy_(torch.tensor([func(x) for x in src], dtype=self.t.dtype).reshape(self.t.shape))
+        return self
+
+    def cast(self, castTensor: "Tensor") -> "Tensor":
+        """Copy this tensor's values into ``castTensor`` converted to its type; returns ``castTensor``."""
+        castTensor.t = self.t.to(castTensor.t.dtype).clone() if castTensor.t.shape != self.t.shape else \
+            castTensor.t.copy_(self.t.to(castTensor.t.dtype))
+        return castTensor
+
+    def diff(self, other, count: int = 1, reverse: bool = False) -> bool:
+        """Print up to ``count`` differing elements; True when the tensors differ (debug helper)."""
+        o = _raw(other)
+        if tuple(o.shape) != tuple(self.t.shape):
+            print(f"size mismatch: {tuple(self.t.shape)} vs {tuple(o.shape)}")
+            return True
+        idx = (self.t != o).reshape(-1).nonzero().reshape(-1).tolist()
+        for i in (reversed(idx) if reverse else idx)[:count] if not reverse else list(reversed(idx))[:count]:
+            print(f"Find difference at offset {i + 1}: {self.t.reshape(-1)[i].item()} vs {o.reshape(-1)[i].item()}")
+        return bool(idx)
+
+    def erf(self): self.t.copy_(torch.erf(self.t)); return self
+    def erfc(self): self.t.copy_(torch.erfc(self.t)); return self
+    def logGamma(self): self.t.copy_(torch.lgamma(self.t)); return self
+    def digamma(self): self.t.copy_(torch.digamma(self.t)); return self
+
+    def emptyInstance(self) -> "Tensor":
+        return Tensor(torch.empty(0, dtype=self.t.dtype, device=self.t.device))
+
+    def forceFill(self, v) -> "Tensor":
+        self.t.fill_(v)
+        return self
+
+    def shallowClone(self) -> "Tensor":
+        """A new Tensor object over the same storage."""
+        return Tensor(self.t.view(self.t.shape))
+
+    def getTensorType(self) -> str:
+        return "DenseType"
+
+    def getTensorNumeric(self):
+        return self.t.dtype
+
+    def notEqualValue(self, value) -> bool:
+        return bool((self.t != value).any())
+
+    def reduce(self, dim: int, result: "Tensor", reducer) -> "Tensor":
+        """Fold ``reducer(acc, x)`` along ``dim`` (1-based) into ``result`` (that dimension becomes size 1)."""
+        d = dim - 1
+        slices = self.t.unbind(d)
+        acc = slices[0].clone()
+        for sl in slices[1:]:
+            acc = torch.tensor([reducer(a, b) for a, b in zip(acc.reshape(-1).tolist(), sl.reshape(-1).tolist())],
+                               dtype=self.t.dtype, device=self.t.device).reshape(acc.shape)
+        result._assign(acc.unsqueeze(d))
+        return result
+
+    def toArray(self) -> list:
+        if self.t.dim() != 1:
+            raise ValueError("toArray needs a 1-D tensor")
+        return self.t.tolist()
+
+    def toBreezeVector(self):
+        if self.t.dim() != 1:
+            raise ValueError("tensor is not a vector")
+        return self.t.detach().cpu().numpy().copy()
+
+    def toBreezeMatrix(self):
+        if self.t.dim() != 2:
+            raise ValueError("tensor is not a matrix")
+        return self.t.detach().cpu().numpy().copy()
+
+    toMLlibVector, toMLlibMatrix = toBreezeVector, toBreezeMatrix
+
+    def uniform(self, *a) -> float:
+        """A uniform random number from the shared generator: ``uniform()`` in [0,1), ``uniform(lo, hi)``."""
+        from ..utils.random_generator import RNG
+        lo, hi = (0.0, 1.0) if not a else a
+        return float(RNG.uniform(lo, hi))
+
+    def unique(self):
+        """(distinct values in order of first appearance, for every element the 0-based index of its value) — TensorMath
+        .unique for 1-D tensors."""
+        vals = self.t.reshape(-1).tolist()
+        seen, order, idx = {}, [], []
+        for v in vals:
+            if v not in seen:
+                seen[v] = len(order)
+                order.append(v)
+            idx.append(seen[v])
+        return (Tensor(torch.tensor(order, dtype=self.t.dtype)), Tensor(torch.tensor(idx, dtype=torch.int32)))
+
+    def addMultiDimension(self, t: "Tensor", dims) -> "Tensor":
+        """self += t summed over ``dims`` (1-based) — the broadcasting-bias gradient helper."""
+        r = _raw(t)
+        for d in sorted((d - 1 for d in dims), reverse=True):
+            r = r.sum(d, keepdim=True)
+        self.t.add_(r.reshape(self.t.shape))
+        return self
+
+    def save(self, path: str, overWrite: bool = False) -> "Tensor":
+        from ..utils.file import File
+        File.save(self.t.detach().cpu(), path, overWrite)
+        return self
+
+    @staticmethod
+    def load(path: str) -> "Tensor":
+        from ..utils.file import File
+        return Tensor(File.load(path))
+
+    @staticmethod
+    def gaussian1D(size: int = 3, sigma: float = 0.25, amplitude: int = 1, normalize: bool = False,
+                   mean: float = 0.5, tensor: "Tensor | None" = None) -> "Tensor":
+        """1-D Gaussian kernel (S/tensor/Tensor.scala:1208-1233): value_i = amplitude * exp(-((i/size - mean)/sigma)^2 / 2)
+        for i = 1..size, centred per ``mean`` in units of the size."""
+        i = torch.arange(1, size + 1, dtype=torch.float32)
+        center = mean * size + 0.5
+        g = amplitude * torch.exp(-(((i - center) / (sigma * size)) ** 2) / 2)
+        if normalize:
+            g = g / g.sum()
+        if tensor is not None:
+            tensor._assign(g)
+            return tensor
+        return Tensor(g)
+
+    @staticmethod
+    def getDims(t) -> int:
+        return _raw(t).dim()
+
     # ------------------------------------------------------------------ conversions
     def toQuantizedTensor(self):
         from .quantized import QuantizedTensor

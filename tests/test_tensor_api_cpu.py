@@ -1,6 +1,7 @@
 """Torch7-style Tensor API (mirrors T/tensor/DenseTensorSpec.scala, DenseTensorMathSpec.scala, SparseTensorSpec.scala,
 QuantizedTensorSpec.scala)."""
 import numpy as np
+import pytest
 import torch
 
 from bigdl_b200.tensor import QuantizedTensor, SparseTensor, Storage, Tensor, cat
@@ -157,3 +158,101 @@ def test_remaining_tensor_math_and_shape_methods():
     assert torch.equal(dst.t, torch.tensor([[7., 0., 8.], [0., 9., 0.]]))
     bern = Tensor(1000).bernoulli(0.3)
     assert 0.2 < float(bern.t.mean()) < 0.4 and set(bern.t.unique().tolist()) <= {0.0, 1.0}
+
+
+def test_remaining_tensor_surface():
+    """apply / update with index tables, applyFun, cast, reduce, unique, erf..., conversions, gaussian1D
+    (S/tensor/Tensor.scala:188-319, TensorMath.scala; reference checks in DenseTensorSpec / DenseTensorMathSpec)."""
+    import math
+    from bigdl_b200.utils.table import T as Tb
+    t = Tensor(torch.arange(1., 25.).reshape(2, 3, 4))
+    assert t.apply([2, 3, 4]) == 24.0
+    assert t.apply(2).size() == [3, 4] and t.apply(-1).valueAt(1, 1) == 13.0
+    sub = t.apply(Tb(2, Tb(2, 3)))                       # select 2 in dim 1, narrow rows 2..3
+    assert sub.size() == [2, 4] and sub.valueAt(1, 1) == 17.0
+    assert t.apply(Tb(Tb(), Tb(), 4)).size() == [2, 3]   # empty entries keep the dimension
+    t.update(1, 0.0)
+    assert float(t.t[0].abs().sum()) == 0.0
+    t.update([2, 1, 1], -5.0)
+    assert t.valueAt(2, 1, 1) == -5.0
+    t.update(Tb(2, Tb(2, 3)), Tensor(torch.ones(2, 4)))
+    assert float(t.t[1, 1:].sum()) == 8.0
+    t.update(lambda v: v < 0, 7.0)
+    assert t.valueAt(2, 1, 1) == 7.0
+    a = Tensor(torch.zeros(3))
+    a.applyFun(Tensor(torch.tensor([1, 2, 3], dtype=torch.int32)), lambda v: v * 0.5)
+    assert a.toArray() == [0.5, 1.0, 1.5]
+    d = Tensor(torch.zeros(3, dtype=torch.float64))
+    assert a.cast(d).t.dtype == torch.float64 and d.toArray() == [0.5, 1.0, 1.5]
+    m = Tensor(torch.tensor([[1., 5.], [4., 2.]]))
+    r = Tensor()
+    m.reduce(1, r, lambda x, y: max(x, y))
+    assert r.t.tolist() == [[4.0, 5.0]]
+    vals, idx = Tensor(torch.tensor([3., 1., 3., 2., 1.])).unique()
+    assert vals.toArray() == [3.0, 1.0, 2.0] and idx.t.tolist() == [0, 1, 0, 2, 1]
+    e = Tensor(torch.tensor([0.5])).erf()
+    assert abs(e.valueAt(1) - math.erf(0.5)) < 1e-6
+    assert abs(Tensor(torch.tensor([0.5])).erfc().valueAt(1) - math.erfc(0.5)) < 1e-6
+    assert abs(Tensor(torch.tensor([4.0])).logGamma().valueAt(1) - math.lgamma(4.0)) < 1e-5
+    assert abs(Tensor(torch.tensor([1.0])).digamma().valueAt(1) + 0.5772157) < 1e-5
+    assert m.notEqualValue(1.0) and not Tensor(torch.ones(2)).notEqualValue(1.0)
+    sc = m.shallowClone()
+    sc.setValue(1, 1, 9.0)
+    assert m.valueAt(1, 1) == 9.0                        # same storage
+    assert m.toBreezeMatrix().shape == (2, 2) and Tensor(torch.ones(3)).toMLlibVector().tolist() == [1, 1, 1]
+    assert m.emptyInstance().nElement() == 0 and m.getTensorType() == "DenseType"
+    assert m.diff(m.clone()) is False and m.diff(Tensor(torch.zeros(2, 2)), 1) is True
+    bias_grad = Tensor(torch.zeros(1, 3, 1))
+    bias_grad.addMultiDimension(Tensor(torch.ones(2, 3, 4)), [1, 3])
+    assert bias_grad.t.reshape(-1).tolist() == [8.0, 8.0, 8.0]
+    g = Tensor.gaussian1D(5, 0.25, 1, False, 0.5)
+    want = [math.exp(-(((i - 3.0) / (0.25 * 5)) ** 2) / 2) for i in range(1, 6)]
+    assert all(abs(x - y) < 1e-6 for x, y in zip(g.toArray(), want))
+    assert abs(Tensor.gaussian1D(7, normalize=True).sum() - 1.0) < 1e-6
+    assert 0.0 <= Tensor().uniform() < 1.0 and 2.0 <= Tensor().uniform(2.0, 3.0) < 3.0
+    assert Tensor.getDims(m) == 2
+
+
+def test_tensor_save_load(tmp_path):
+    t = Tensor(torch.arange(6.).reshape(2, 3))
+    p = str(tmp_path / "t.obj")
+    t.save(p)
+    assert torch.equal(Tensor.load(p).t, t.t)
+    with pytest.raises(FileExistsError):
+        t.save(p)
+    t.save(p, True)
+
+
+def test_sparse_tensor_blas_and_math():
+    """S/tensor/SparseTensorBLAS.scala coomv / coomm / vdot and SparseTensorMath addmv / addmm against dense math."""
+    from bigdl_b200.tensor.sparse import SparseTensor, SparseTensorBLAS, SparseTensorMath
+    torch.manual_seed(0)
+    d = torch.randn(5, 7) * (torch.rand(5, 7) < 0.4)
+    sp = SparseTensor.from_dense(d)
+    assert sp.getTensorType() == "SparseType" and sp.nElement() == int((d != 0).sum())
+    nz = d.nonzero()[0]
+    assert abs(sp.apply([int(nz[0]) + 1, int(nz[1]) + 1]) - float(d[nz[0], nz[1]])) < 1e-7
+    x, y = torch.randn(7), torch.randn(5)
+    want = 0.5 * (d @ x) + 2.0 * y
+    SparseTensorBLAS.coomv(0.5, sp, x, 2.0, y)
+    assert torch.allclose(y, want, atol=1e-6)
+    B, C = torch.randn(7, 3), torch.randn(5, 3)
+    want = 1.5 * (d @ B) - C
+    SparseTensorBLAS.coomm(1.5, sp, B, -1.0, C)
+    assert torch.allclose(C, want, atol=1e-5)
+    A2, C2 = torch.randn(4, 5), torch.zeros(4, 7)
+    SparseTensorBLAS.coomm(1.0, A2, sp, 0.0, C2)                 # dense x sparse
+    assert torch.allclose(C2, A2 @ d, atol=1e-5)
+    v = torch.randn(7) * (torch.rand(7) < 0.5)
+    sv = SparseTensor.from_dense(v)
+    w = torch.randn(7)
+    assert abs(SparseTensorBLAS.vdot(w, sv) - float(w @ v)) < 1e-5 and abs(sv.dot(w) - float(w @ v)) < 1e-5
+    r, t = torch.zeros(5), torch.randn(5)
+    SparseTensorMath.addmv(r, 0.5, t, 2.0, sp, x)
+    assert torch.allclose(r, 0.5 * t + 2.0 * (d @ x), atol=1e-5)
+    r2, t2 = torch.zeros(5, 3), torch.randn(5, 3)
+    SparseTensorMath.addmm(r2, 1.0, t2, 1.0, sp, B)
+    assert torch.allclose(r2, t2 + d @ B, atol=1e-5)
+    assert abs(sp.sum() - float(d.sum())) < 1e-5
+    small = sp.clone().resize([3, 7])
+    assert torch.equal(small.to_dense().t, d[:3])

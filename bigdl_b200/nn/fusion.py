@@ -80,10 +80,19 @@ def _mark_residual_blocks(model: Module) -> None:
             if type(a) is ConcatTable and type(b) is CAddTable and len(a.modules) == 2:
                 tails = [_tail_conv(br) for br in a.modules]
                 main = 0 if tails[0] is not None else (1 if tails[1] is not None else None)
-                for k in ("_res_tail", "_res_main", "_res_relu"):
+                for k in ("_res_tail", "_res_main", "_res_relu", "_bn_tail"):
                     a.__dict__.pop(k, None)
                 if main is not None:
                     a.__dict__.update(_res_tail=tails[main], _res_main=main, _res_relu=bool(b._fuse_relu))
+                # training (and unfolded inference): branch ending in a BatchNorm -> bn + add (+ReLU) in one kernel
+                for br in a.modules:
+                    mods = br.modules if isinstance(br, Sequential) else [br]
+                    last = mods[-1] if mods else None
+                    if (isinstance(last, BatchNormalization) and not getattr(last, "_folded", False)
+                            and not last._fuse_relu and getattr(last, "data_format", "NCHW") == "NCHW"
+                            and config.get("bigdl.fusion.bnadd")):
+                        a.__dict__["_bn_tail"] = last
+                        break
 
 
 def unfuse(model: Module) -> Module:
@@ -92,7 +101,7 @@ def unfuse(model: Module) -> Module:
             m._fuse_relu = False
         if type(m) is ReLU:
             m._fused = False
-        for k in ("_res_tail", "_res_main", "_res_relu"):
+        for k in ("_res_tail", "_res_main", "_res_relu", "_bn_tail"):
             m.__dict__.pop(k, None)
     return model
 

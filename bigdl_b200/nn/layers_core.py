@@ -484,6 +484,12 @@ class BatchNormalization(Module):
         if native(x) and x.dim() == 4 and x.shape[1] % 8 == 0 and x.dtype == torch.bfloat16:
             from ..ops.batchnorm import BatchNormFn
 
+            if self.__dict__.pop("_defer_now", False) and self.data_format != "NHWC" and not self._fuse_relu:
+                # last layer of a residual branch: the CAddTable that follows runs bn + add (+ ReLU) as ONE kernel
+                # (nn/fusion.py marks the pattern, ConcatTable arms this flag for exactly one call)
+                out = x.view_as(x)
+                out._bdl_bn = self
+                return out
             y = BatchNormFn.apply(x, w, b, rm, rv, self.train, self.momentum, self.eps, self._fuse_relu, self._sync)
         else:
             xf = x.float() if x.dtype != torch.float32 else x
@@ -499,6 +505,14 @@ class BatchNormalization(Module):
 
 class SpatialBatchNormalization(BatchNormalization):
     n_dim = 4
+
+
+def bn_add_relu(bn: BatchNormalization, pre: torch.Tensor, shortcut: torch.Tensor, relu: bool) -> torch.Tensor:
+    """relu?(bn(pre) + shortcut) in one pass for a deferred BN (see ``BatchNormalization.updateOutput``)."""
+    from ..ops.batchnorm import BatchNormFn
+
+    return BatchNormFn.apply(pre, bn._parameters.get("weight"), bn._parameters.get("bias"), bn._buffers["runningMean"],
+                             bn._buffers["runningVar"], bn.train, bn.momentum, bn.eps, relu, bn._sync, shortcut)
 
 
 class SoftMax(Module):

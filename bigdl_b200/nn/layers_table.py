@@ -136,6 +136,13 @@ class ConcatTable(Container):
             fused = self._residual_forward(input, tail)
             if fused is not None:
                 return fused
+        bn = self.__dict__.get("_bn_tail")
+        if bn is not None and isinstance(input, torch.Tensor) and input.is_cuda:
+            bn.__dict__["_defer_now"] = True      # consumed (popped) by that BN's next call, i.e. inside this forward
+            try:
+                return Table(*[m._call(input) for m in self.modules])
+            finally:
+                bn.__dict__.pop("_defer_now", None)
         return Table(*[m._call(input) for m in self.modules])
 
     def _residual_forward(self, input, tail):
@@ -289,6 +296,16 @@ class CAddTable(_CReduce):
         xs = _tl(input)
         if len(xs) == 1 and getattr(xs[0], "_bdl_sum_done", False):
             return xs[0]          # a fused ConcatTable already added the shortcut (and applied the ReLU) in the conv
+        tags = [getattr(x, "_bdl_bn", None) for x in xs]
+        if any(t is not None for t in tags):
+            from .layers_core import bn_add_relu
+
+            k = 0 if tags[0] is not None else 1
+            if (len(xs) == 2 and tags[1 - k] is None and xs[1 - k].dtype == torch.bfloat16
+                    and xs[0].shape == xs[1].shape):
+                return bn_add_relu(tags[k], xs[k], xs[1 - k], self._fuse_relu)
+            # not the shape the fused kernel takes: run the deferred normalisations now and add as usual
+            xs = [x if t is None else t._call(x) for x, t in zip(xs, tags)]
         if (len(xs) == 2 and xs[0].is_cuda and xs[0].dtype == torch.bfloat16 and xs[1].dtype == torch.bfloat16
                 and xs[0].shape == xs[1].shape):
             from .layers_core import native

@@ -11,12 +11,26 @@ from .functions import nhwc_pitched, rows2d
 
 class BatchNormFn(Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, running_mean, running_var, training, momentum, eps, relu, sync_group):
+    def forward(ctx, x, weight, bias, running_mean, running_var, training, momentum, eps, relu, sync_group,
+                residual=None):
+        """``residual`` (same shape as x): y = relu?(bn(x) + residual) — the BN closing a residual branch, the shortcut
+        add and the ReLU in one pass (and one fused backward that also emits the shortcut's gradient)."""
         lib = _lib.cuda_lib()
         st = _lib.stream_ptr()
         xn, ldx = nhwc_pitched(x)
         N, H, W, C = xn.shape
         M = N * H * W
+        rn, ldr = (None, 0) if residual is None else nhwc_pitched(residual)
+
+        def apply(mean_t, scale_t, use_var):
+            if rn is None:
+                _lib.check(lib.bdl_bn_apply(xn.data_ptr(), y.data_ptr(), mean_t.data_ptr(), scale_t.data_ptr(),
+                                            _lib.ptr(g), _lib.ptr(b), M, C, ldx, C, float(eps), use_var, int(relu), st),
+                           "bdl_bn_apply")
+            else:
+                _lib.check(lib.bdl_bn_apply_res(xn.data_ptr(), rn.data_ptr(), y.data_ptr(), mean_t.data_ptr(),
+                                                scale_t.data_ptr(), _lib.ptr(g), _lib.ptr(b), M, C, ldx, ldr, C,
+                                                float(eps), use_var, int(relu), st), "bdl_bn_apply_res")
         y = torch.empty((N, H, W, C), dtype=torch.bfloat16, device=x.device)
         g = weight.detach() if weight is not None else None
         b = bias.detach() if bias is not None else None
@@ -32,25 +46,22 @@ class BatchNormFn(Function):
             _lib.check(lib.bdl_bn_finalize(sums.data_ptr(), count, C, float(eps), float(momentum), mean.data_ptr(),
                                            invstd.data_ptr(), running_mean.data_ptr(), running_var.data_ptr(), st),
                        "bdl_bn_finalize")
-            _lib.check(lib.bdl_bn_apply(xn.data_ptr(), y.data_ptr(), mean.data_ptr(), invstd.data_ptr(), _lib.ptr(g),
-                                        _lib.ptr(b), M, C, ldx, C, float(eps), 0, int(relu), st), "bdl_bn_apply")
+            apply(mean, invstd, 0)
             _lib.count_launch(3)
             ctx.save_for_backward(xn, mean, invstd, y if relu else None)
-            ctx.cfg = (weight, bias, ldx, count, relu, sync_group)
+            ctx.cfg = (weight, bias, ldx, count, relu, sync_group, residual is not None)
         else:
-            _lib.check(lib.bdl_bn_apply(xn.data_ptr(), y.data_ptr(), running_mean.data_ptr(), running_var.data_ptr(),
-                                        _lib.ptr(g), _lib.ptr(b), M, C, ldx, C, float(eps), 1, int(relu), st),
-                       "bdl_bn_apply")
+            apply(running_mean, running_var, 1)
             _lib.count_launch()
             inv = torch.rsqrt(running_var + eps)
             ctx.save_for_backward(xn, running_mean, inv, y if relu else None)
-            ctx.cfg = (weight, bias, ldx, None, relu, None)
+            ctx.cfg = (weight, bias, ldx, None, relu, None, residual is not None)
         return y.permute(0, 3, 1, 2)
 
     @staticmethod
     def backward(ctx, dy):
         xn, mean, invstd, y = ctx.saved_tensors
-        weight, bias, ldx, count, relu, sync_group = ctx.cfg
+        weight, bias, ldx, count, relu, sync_group, has_res = ctx.cfg
         lib = _lib.cuda_lib()
         st = _lib.stream_ptr()
         N, H, W, C = xn.shape
@@ -65,21 +76,36 @@ class BatchNormFn(Function):
         if gw is not None or gb is not None:
             _lib.check(lib.bdl_bn_param_grad(sums.data_ptr(), _lib.ptr(gw), _lib.ptr(gb), C, 1.0, 1.0, st),
                        "bdl_bn_param_grad")
-        dx = None
-        if ctx.needs_input_grad[0]:
+        dx = d_res = None
+        # the shortcut's gradient is dy masked by the fused ReLU; without a ReLU it is dy itself
+        want_mask = has_res and relu and ctx.needs_input_grad[10]
+        if has_res and not relu and ctx.needs_input_grad[10]:
+            d_res = dy
+        dmn = torch.empty((N, H, W, C), dtype=torch.bfloat16, device=dy.device) if want_mask else None
+
+        def bwd_apply(sums_t, cnt):
+            if dmn is None:
+                _lib.check(lib.bdl_bn_bwd_apply(dyn.data_ptr(), xn.data_ptr(), _lib.ptr(y), mean.data_ptr(),
+                                                invstd.data_ptr(), _lib.ptr(g), sums_t.data_ptr(), dxn.data_ptr(), M, cnt,
+                                                C, ldd, ldx, C, C, st), "bdl_bn_bwd_apply")
+            else:
+                _lib.check(lib.bdl_bn_bwd_apply_mask(dyn.data_ptr(), xn.data_ptr(), y.data_ptr(), mean.data_ptr(),
+                                                     invstd.data_ptr(), _lib.ptr(g), sums_t.data_ptr(), dxn.data_ptr(),
+                                                     dmn.data_ptr(), M, cnt, C, ldd, ldx, C, C, C, st),
+                           "bdl_bn_bwd_apply_mask")
+
+        if ctx.needs_input_grad[0] or want_mask:
             dxn = torch.empty((N, H, W, C), dtype=torch.bfloat16, device=dy.device)
             if count is None:
                 # inference-mode statistics are constants: dx = gamma * invstd * dy'
                 zero = torch.zeros(2 * C, dtype=torch.float32, device=dy.device)
-                _lib.check(lib.bdl_bn_bwd_apply(dyn.data_ptr(), xn.data_ptr(), _lib.ptr(y), mean.data_ptr(),
-                                                invstd.data_ptr(), _lib.ptr(g), zero.data_ptr(), dxn.data_ptr(), M, 1.0,
-                                                C, ldd, ldx, C, C, st), "bdl_bn_bwd_apply")
+                bwd_apply(zero, 1.0)
             else:
                 if sync_group is not None and dist.is_initialized() and dist.get_world_size(sync_group) > 1:
                     dist.all_reduce(sums, group=sync_group)
-                _lib.check(lib.bdl_bn_bwd_apply(dyn.data_ptr(), xn.data_ptr(), _lib.ptr(y), mean.data_ptr(),
-                                                invstd.data_ptr(), _lib.ptr(g), sums.data_ptr(), dxn.data_ptr(), M,
-                                                float(count), C, ldd, ldx, C, C, st), "bdl_bn_bwd_apply")
+                bwd_apply(sums, float(count))
             dx = dxn.permute(0, 3, 1, 2)
+            if dmn is not None:
+                d_res = dmn.permute(0, 3, 1, 2)
         _lib.count_launch(3)
-        return dx, None, None, None, None, None, None, None, None, None
+        return dx, None, None, None, None, None, None, None, None, None, d_res

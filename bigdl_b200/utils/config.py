@@ -45,6 +45,7 @@ _DEFAULTS: dict[str, Any] = {
     "bigdl.mkldnn.fusion.bnrelu": True,
     "bigdl.mkldnn.fusion.convrelu": True,
     "bigdl.mkldnn.fusion.convsum": True,
+    "bigdl.fusion.bnadd": True,              # BatchNorm closing a residual branch + shortcut add + ReLU as one kernel (fwd and bwd)
     "bigdl.fusion.residual": True,           # inference: shortcut add + ReLU inside the last conv's GEMM epilogue
     # misc
     "bigdl.quantized.blockScale": False,     # Quantizer: MX block-scaled fp8 (one scale per 32 inputs) for Linear layers

@@ -208,10 +208,12 @@ __global__ void bn_finalize_kernel(const float* __restrict__ sums, float count, 
 // the running variance (use_var = 1 makes the kernel derive invstd = rsqrt(var + eps) itself).
 // Thread layout: blockDim.x = vcols * rif; a thread owns ONE 8-channel vector column (its scale/shift live in
 // registers) and streams rows with 4 independent 16-byte loads in flight — no per-element index arithmetic.
+template <bool kRes>
 __global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
                                 const float* __restrict__ mean, const float* __restrict__ invstd_or_var,
                                 const float* __restrict__ gamma, const float* __restrict__ beta, long long M, int C,
-                                long long ldx, long long ldy, float eps, int use_var, int relu, int rows_per_block) {
+                                long long ldx, long long ldy, float eps, int use_var, int relu, int rows_per_block,
+                                const __nv_bfloat16* __restrict__ res = nullptr, long long ldr = 0) {
   const int cvec = C / 8;
   const int vcols = cvec < static_cast<int>(blockDim.x) ? cvec : blockDim.x;
   const int rif = blockDim.x / vcols;
@@ -231,21 +233,31 @@ __global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat
       sb[j] = (beta ? beta[c] : 0.f) - mean[c] * sa[j];
     }
     const __nv_bfloat16* xp = x + cv * 8;
+    const __nv_bfloat16* rp = kRes ? res + cv * 8 : nullptr;
     __nv_bfloat16* yp = y + cv * 8;
     long long r = r0 + tr;
     for (; r + 3ll * rif < r1; r += 4ll * rif) {
-      uint4 v[4];
+      uint4 v[4], w[4];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) v[u] = *reinterpret_cast<const uint4*>(xp + (r + u * rif) * ldx);
+      for (int u = 0; u < 4; ++u) {
+        v[u] = *reinterpret_cast<const uint4*>(xp + (r + u * rif) * ldx);
+        if (kRes) w[u] = *reinterpret_cast<const uint4*>(rp + (r + u * rif) * ldr);
+      }
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const __nv_bfloat162* q = reinterpret_cast<const __nv_bfloat162*>(&v[u]);
+        const __nv_bfloat162* qr = reinterpret_cast<const __nv_bfloat162*>(&w[u]);
         float f[8];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const float2 t = __bfloat1622float2(q[j]);
           f[2 * j] = fmaf(t.x, sa[2 * j], sb[2 * j]);
           f[2 * j + 1] = fmaf(t.y, sa[2 * j + 1], sb[2 * j + 1]);
+          if (kRes) {                     // residual block: y = relu(bn(x) + shortcut) in the same pass
+            const float2 t2 = __bfloat1622float2(qr[j]);
+            f[2 * j] += t2.x;
+            f[2 * j + 1] += t2.y;
+          }
         }
         if (relu) {
 #pragma unroll
@@ -255,11 +267,13 @@ __global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat
       }
     }
     for (; r < r1; r += rif) {
-      float f[8];
+      float f[8], fr[8];
       bn_load8(xp + r * ldx, f);
+      if (kRes) bn_load8(rp + r * ldr, fr);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         f[j] = fmaf(f[j], sa[j], sb[j]);
+        if (kRes) f[j] += fr[j];
         if (relu) f[j] = fmaxf(f[j], 0.f);
       }
       bn_store8(yp + r * ldy, f);
@@ -270,12 +284,14 @@ __global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat
 // dx = gamma * invstd * (dy' - dbeta/count - x̂ * dgamma/count), dy' = dy masked by (y > 0) when ReLU was fused.
 // Rewritten per channel as dx = ka * dy' + kb * x + kc with
 //   ka = gamma*invstd, kb = -gamma*invstd^2*dgamma/count, kc = -ka*dbeta/count - kb*mean.
+template <bool kMask>
 __global__ void bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                                     const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean,
                                     const float* __restrict__ invstd, const float* __restrict__ gamma,
                                     const float* __restrict__ sums, __nv_bfloat16* __restrict__ dx, long long M,
                                     float count, int C, long long lddy, long long ldx, long long ldy,
-                                    long long lddx, int rows_per_block) {
+                                    long long lddx, int rows_per_block, __nv_bfloat16* __restrict__ dmask = nullptr,
+                                    long long lddm = 0) {
   const int cvec = C / 8;
   const int vcols = cvec < static_cast<int>(blockDim.x) ? cvec : blockDim.x;
   const int rif = blockDim.x / vcols;
@@ -311,7 +327,7 @@ __global__ void bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const 
         const __nv_bfloat162* qg = reinterpret_cast<const __nv_bfloat162*>(&vg[u]);
         const __nv_bfloat162* qx = reinterpret_cast<const __nv_bfloat162*>(&vx[u]);
         const __nv_bfloat162* qy = reinterpret_cast<const __nv_bfloat162*>(&vy[u]);
-        float f[8];
+        float f[8], fm[8];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           float2 g2 = __bfloat1622float2(qg[j]);
@@ -323,8 +339,13 @@ __global__ void bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const 
           }
           f[2 * j] = fmaf(ka[2 * j], g2.x, fmaf(kb[2 * j], x2.x, kc[2 * j]));
           f[2 * j + 1] = fmaf(ka[2 * j + 1], g2.y, fmaf(kb[2 * j + 1], x2.y, kc[2 * j + 1]));
+          if (kMask) {                    // the ReLU-masked gradient is also the shortcut's gradient: emit it here
+            fm[2 * j] = g2.x;
+            fm[2 * j + 1] = g2.y;
+          }
         }
         bn_store8(dx + (r + u * rif) * lddx + cv * 8, f);
+        if (kMask) bn_store8(dmask + (r + u * rif) * lddm + cv * 8, fm);
       }
     }
     for (; r < r1; r += rif) {
@@ -337,6 +358,7 @@ __global__ void bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const 
 #pragma unroll
         for (int j = 0; j < 8; ++j) g[j] = fy[j] > 0.f ? g[j] : 0.f;
       }
+      if (kMask) bn_store8(dmask + r * lddm + cv * 8, g);
 #pragma unroll
       for (int j = 0; j < 8; ++j) g[j] = fmaf(ka[j], g[j], fmaf(kb[j], fx[j], kc[j]));
       bn_store8(dx + r * lddx + cv * 8, g);
@@ -441,10 +463,48 @@ extern "C" int bdl_bn_apply(const void* x, void* y, const float* mean, const flo
   int grid, rpb;
   size_t smem_unused;
   stream_geometry(M, C, &grid, &rpb, &smem_unused);
-  bn_apply_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  bn_apply_kernel<false><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), mean, invstd_or_var, gamma, beta, M, C,
       ldx, ldy, eps, use_var, relu, rpb);
   return bdl_check_launch("bn_apply_kernel");
+}
+
+// y = relu?(bn(x) + res): the BN that ends a residual branch, the shortcut add and the ReLU in one pass
+// (S/nn/mkldnn/Fusion.scala fuses conv + sum at inference; this is the training-time counterpart on the BN side).
+extern "C" int bdl_bn_apply_res(const void* x, const void* res, void* y, const float* mean, const float* invstd_or_var,
+                                const float* gamma, const float* beta, long long M, int C, long long ldx, long long ldr,
+                                long long ldy, float eps, int use_var, int relu, void* stream) {
+  if (bn_check("bdl_bn_apply_res: C and pitches must be multiples of 8, pointers 16-byte aligned", C, ldx, ldy, x, y))
+    return BDL_ERR_INVALID;
+  if (res == nullptr || (ldr % 8) || (reinterpret_cast<uintptr_t>(res) & 15u))
+    return bdl_fail("bdl_bn_apply_res: residual must be 16-byte aligned with a pitch that is a multiple of 8");
+  int grid, rpb;
+  size_t smem_unused;
+  stream_geometry(M, C, &grid, &rpb, &smem_unused);
+  bn_apply_kernel<true><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), mean, invstd_or_var, gamma, beta, M, C,
+      ldx, ldy, eps, use_var, relu, rpb, static_cast<const __nv_bfloat16*>(res), ldr);
+  return bdl_check_launch("bn_apply_kernel(res)");
+}
+
+// bdl_bn_bwd_apply that also writes dy masked by (y > 0) to dmask [M, C] (pitch lddm): the gradient of the shortcut
+extern "C" int bdl_bn_bwd_apply_mask(const void* dy, const void* x, const void* y, const float* mean,
+                                     const float* invstd, const float* gamma, const float* sums, void* dx, void* dmask,
+                                     long long M, float count, int C, long long lddy, long long ldx, long long ldy,
+                                     long long lddx, long long lddm, void* stream) {
+  if (bn_check("bdl_bn_bwd_apply_mask: C and pitches must be multiples of 8, pointers 16-byte aligned", C, lddy, lddx,
+               dy, dx))
+    return BDL_ERR_INVALID;
+  if (dmask == nullptr || (lddm % 8) || (reinterpret_cast<uintptr_t>(dmask) & 15u))
+    return bdl_fail("bdl_bn_bwd_apply_mask: dmask must be 16-byte aligned with a pitch that is a multiple of 8");
+  int grid, rpb;
+  size_t smem_unused;
+  stream_geometry(M, C, &grid, &rpb, &smem_unused);
+  bn_bwd_apply_kernel<true><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
+      static_cast<const __nv_bfloat16*>(y), mean, invstd, gamma, sums, static_cast<__nv_bfloat16*>(dx), M, count, C,
+      lddy, ldx, ldy, lddx, rpb, static_cast<__nv_bfloat16*>(dmask), lddm);
+  return bdl_check_launch("bn_bwd_apply_kernel(mask)");
 }
 
 // sums: [2*C] fp32, zero on entry; receives (dbeta, dgamma)
@@ -472,7 +532,7 @@ extern "C" int bdl_bn_bwd_apply(const void* dy, const void* x, const void* y, co
   int grid, rpb;
   size_t smem_unused;
   stream_geometry(M, C, &grid, &rpb, &smem_unused);
-  bn_bwd_apply_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  bn_bwd_apply_kernel<false><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
       static_cast<const __nv_bfloat16*>(y), mean, invstd, gamma, sums, static_cast<__nv_bfloat16*>(dx), M, count, C,
       lddy, ldx, ldy, lddx, rpb);

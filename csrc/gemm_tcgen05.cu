@@ -355,6 +355,12 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tmA, const 
   else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
+  // Programmatic dependent launch: everything above (barrier init, TMEM allocation, tensor-map prefetch) may overlap the
+  // tail of the previous kernel in the stream; nothing below may, since operands, bias and residual can all be its
+  // output. A no-op when the launch carries no programmatic dependency. Our own dependents may be scheduled as soon as
+  // every CTA of this grid has got here (they block in their own wait until this grid has completed).
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
   constexpr int KE = kFp8 ? 128 : 64;   // elements per 128-byte k block
   const bool small_c = kConv != 0 && !kFp8 && p.cv_aw < 64;
@@ -998,14 +1004,25 @@ static int launch_gemm_kernel(GemmKernel kfn, long long total_work, int num_sms,
   cfg.blockDim = dim3(kGemmThreads);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
+  unsigned na = 0;
   if (two) {
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 2;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = 2;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  // BDL_PDL=1: let this kernel's prologue overlap the previous kernel's tail (the kernel waits before its first read)
+  static const bool pdl = [] { const char* e = getenv("BDL_PDL"); return e && e[0] == '1'; }();
+  if (pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  if (na) {
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = na;
   }
   e = cudaLaunchKernelEx(&cfg, kfn, tmA, tmB, tmD, p);
   if (e != cudaSuccess) return bdl_fail_cuda(what, e);

@@ -239,6 +239,13 @@ int bdl_bn_bwd_reduce(const void* dy, const void* x, const void* y, const float*
 int bdl_bn_bwd_apply(const void* dy, const void* x, const void* y, const float* mean, const float* invstd,
                      const float* gamma, const float* sums, void* dx, long long M, float count, int C, long long lddy,
                      long long ldx, long long ldy, long long lddx, void* stream);
+/* residual-block fusions: y = relu?(bn(x) + res) in one pass; bwd_apply that also emits dy masked by (y > 0) */
+int bdl_bn_apply_res(const void* x, const void* res, void* y, const float* mean, const float* invstd_or_var,
+                     const float* gamma, const float* beta, long long M, int C, long long ldx, long long ldr,
+                     long long ldy, float eps, int use_var, int relu, void* stream);
+int bdl_bn_bwd_apply_mask(const void* dy, const void* x, const void* y, const float* mean, const float* invstd,
+                          const float* gamma, const float* sums, void* dx, void* dmask, long long M, float count, int C,
+                          long long lddy, long long ldx, long long ldy, long long lddx, long long lddm, void* stream);
 int bdl_bn_param_grad(const float* sums, float* gw, float* gb, int C, float scale_w, float scale_b, void* stream);
 
 /* ---- fused LSTM gate math (csrc/recurrent.cu). Reference: S/nn/LSTM.scala:150-175, S/nn/mkldnn/RNN.scala.

@@ -1,0 +1,73 @@
+"""BatchNorm + shortcut add + ReLU fused into one forward kernel and one backward kernel pair (csrc/batchnorm.cu
+bn_apply_kernel<true>, bn_bwd_apply_kernel<true>) against the three separate layers and against fp32 torch."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _rel(a, b):
+    return float((a.float() - b.float()).norm() / (b.float().norm() + 1e-9))
+
+
+@pytest.mark.parametrize("relu", [True, False])
+@pytest.mark.parametrize("shape", [(4, 64, 14, 14), (2, 256, 7, 9)])
+def test_function_matches_fp32(relu, shape):
+    from bigdl_b200.ops.batchnorm import BatchNormFn
+    torch.manual_seed(0)
+    N, C, H, W = shape
+    x = torch.randn(N, H, W, C, device=DEV).bfloat16().permute(0, 3, 1, 2).requires_grad_(True)
+    r = torch.randn(N, H, W, C, device=DEV).bfloat16().permute(0, 3, 1, 2).requires_grad_(True)
+    w = (torch.rand(C, device=DEV) + 0.5).requires_grad_(True)
+    b = torch.randn(C, device=DEV).requires_grad_(True)
+    w.grad, b.grad = torch.zeros_like(w), torch.zeros_like(b)
+    rm, rv = torch.zeros(C, device=DEV), torch.ones(C, device=DEV)
+    y = BatchNormFn.apply(x, w, b, rm, rv, True, 0.1, 1e-5, relu, None, r)
+    go = torch.randn_like(y)
+    y.backward(go)
+    xf, rf = x.detach().float().requires_grad_(True), r.detach().float().requires_grad_(True)
+    wf, bf = w.detach().clone().requires_grad_(True), b.detach().clone().requires_grad_(True)
+    ref = F.batch_norm(xf, None, None, wf, bf, True, 0.1, 1e-5) + rf
+    ref = F.relu(ref) if relu else ref
+    ref.backward(go.float())
+    assert _rel(y, ref) < 1e-2
+    assert _rel(x.grad, xf.grad) < 2e-2 and _rel(r.grad, rf.grad) < 1e-2
+    assert _rel(w.grad, wf.grad) < 2e-2 and _rel(b.grad, bf.grad) < 2e-2
+
+
+def _block(cin, mid):
+    from bigdl_b200.nn import layer as L
+    main = (L.Sequential().add(L.SpatialConvolution(cin, mid, 1, 1)).add(L.SpatialBatchNormalization(mid)).add(L.ReLU())
+            .add(L.SpatialConvolution(mid, mid, 3, 3, 1, 1, 1, 1)).add(L.SpatialBatchNormalization(mid)).add(L.ReLU())
+            .add(L.SpatialConvolution(mid, cin, 1, 1)).add(L.SpatialBatchNormalization(cin)))
+    return L.Sequential().add(L.ConcatTable().add(main).add(L.Identity())).add(L.CAddTable()).add(L.ReLU())
+
+
+def test_residual_block_fused_equals_unfused():
+    from bigdl_b200.nn import fusion
+    from bigdl_b200.nn import layer as L
+    from bigdl_b200.ops import _lib
+    from bigdl_b200.utils import config
+    torch.manual_seed(1)
+    model = L.Sequential().add(_block(64, 16)).add(_block(64, 16)).cuda().training()
+    x = torch.randn(8, 64, 12, 12, device=DEV).bfloat16()
+    go = torch.randn(8, 64, 12, 12, device=DEV).bfloat16()
+    results = {}
+    for mode in (False, True):
+        config.set("bigdl.fusion.bnadd", mode)
+        fusion.unfuse(model)
+        fusion.fuse(model)
+        w, g = model.getParameters()
+        g.zero_()
+        before = _lib.LAUNCHES
+        xin = x.clone().requires_grad_(True)
+        with torch.enable_grad():
+            y = model._call(xin)
+        torch.autograd.backward(y, go)
+        results[mode] = (y.detach().float(), xin.grad.float(), g.clone().float(), _lib.LAUNCHES - before)
+    config.set("bigdl.fusion.bnadd", True)
+    (y0, dx0, g0, n0), (y1, dx1, g1, n1) = results[False], results[True]
+    assert _rel(y1, y0) < 1e-2 and _rel(dx1, dx0) < 2e-2 and _rel(g1, g0) < 2e-2
+    assert n1 < n0                                       # two add+ReLU forward and two backward launches are gone

@@ -80,7 +80,7 @@ def _mark_residual_blocks(model: Module) -> None:
             if type(a) is ConcatTable and type(b) is CAddTable and len(a.modules) == 2:
                 tails = [_tail_conv(br) for br in a.modules]
                 main = 0 if tails[0] is not None else (1 if tails[1] is not None else None)
-                for k in ("_res_tail", "_res_main", "_res_relu", "_bn_tail"):
+                for k in ("_res_tail", "_res_main", "_res_relu", "_bn_tail", "_skip_pair"):
                     a.__dict__.pop(k, None)
                 if main is not None:
                     a.__dict__.update(_res_tail=tails[main], _res_main=main, _res_relu=bool(b._fuse_relu))
@@ -92,6 +92,18 @@ def _mark_residual_blocks(model: Module) -> None:
                             and not last._fuse_relu and getattr(last, "data_format", "NCHW") == "NCHW"
                             and config.get("bigdl.fusion.bnadd")):
                         a.__dict__["_bn_tail"] = last
+                        # the block input feeds the branch's first convolution and the shortcut (identity, or a
+                        # projection that starts with a convolution): pair them so no separate gradient add runs
+                        other = a.modules[1] if br is a.modules[0] else a.modules[0]
+                        omods = other.modules if isinstance(other, Sequential) else [other]
+                        first, ofirst = mods[0], (omods[0] if omods else None)
+                        plain = lambda c: type(c) is SpatialConvolution and c.n_group == 1 and \
+                            getattr(c, "data_format", "NCHW") == "NCHW" and c.propagate_back
+                        if plain(first) and config.get("bigdl.fusion.skipgrad"):
+                            if type(other).__name__ == "Identity":
+                                a.__dict__["_skip_pair"] = (first, None)
+                            elif ofirst is not None and plain(ofirst):
+                                a.__dict__["_skip_pair"] = (first, ofirst)
                         break
 
 
@@ -101,7 +113,7 @@ def unfuse(model: Module) -> Module:
             m._fuse_relu = False
         if type(m) is ReLU:
             m._fused = False
-        for k in ("_res_tail", "_res_main", "_res_relu", "_bn_tail"):
+        for k in ("_res_tail", "_res_main", "_res_relu", "_bn_tail", "_skip_pair"):
             m.__dict__.pop(k, None)
     return model
 

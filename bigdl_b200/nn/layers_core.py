@@ -199,7 +199,8 @@ class SpatialConvolution(Module):
                 from ..ops.functions import set_out_hint
 
                 set_out_hint(hint)
-            y = ConvFn.apply(xin, self.weight, bias, w16, geom, self._fuse_relu, self.scaleW, self.scaleB)
+            y = ConvFn.apply(xin, self.weight, bias, w16, geom, self._fuse_relu, self.scaleW, self.scaleB,
+                             self.__dict__.pop("_skip_token", None))      # residual-block input pairing (SkipToken)
         else:
             w = self.weight
             if x.dtype != w.dtype:
@@ -507,12 +508,16 @@ class SpatialBatchNormalization(BatchNormalization):
     n_dim = 4
 
 
-def bn_add_relu(bn: BatchNormalization, pre: torch.Tensor, shortcut: torch.Tensor, relu: bool) -> torch.Tensor:
-    """relu?(bn(pre) + shortcut) in one pass for a deferred BN (see ``BatchNormalization.updateOutput``)."""
+def bn_add_relu(bn: BatchNormalization, pre: torch.Tensor, shortcut: torch.Tensor, relu: bool,
+                skip_token=None) -> torch.Tensor:
+    """relu?(bn(pre) + shortcut) in one pass for a deferred BN (see ``BatchNormalization.updateOutput``).
+    ``skip_token``: the shortcut IS the block input (identity shortcut) and the branch's first convolution holds the
+    same token, so the two input gradients are summed in that convolution's dgrad epilogue."""
     from ..ops.batchnorm import BatchNormFn
 
     return BatchNormFn.apply(pre, bn._parameters.get("weight"), bn._parameters.get("bias"), bn._buffers["runningMean"],
-                             bn._buffers["runningVar"], bn.train, bn.momentum, bn.eps, relu, bn._sync, shortcut)
+                             bn._buffers["runningVar"], bn.train, bn.momentum, bn.eps, relu, bn._sync, shortcut,
+                             skip_token)
 
 
 class SoftMax(Module):

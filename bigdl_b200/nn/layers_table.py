@@ -139,10 +139,28 @@ class ConcatTable(Container):
         bn = self.__dict__.get("_bn_tail")
         if bn is not None and isinstance(input, torch.Tensor) and input.is_cuda:
             bn.__dict__["_defer_now"] = True      # consumed (popped) by that BN's next call, i.e. inside this forward
+            pair = self.__dict__.get("_skip_pair")
+            token = None
+            if pair is not None and torch.is_grad_enabled() and input.requires_grad:
+                from ..ops.functions import SkipToken
+
+                token = SkipToken()               # the block input's two gradients meet in a dgrad epilogue
+                for conv in pair:
+                    if conv is not None:
+                        conv.__dict__["_skip_token"] = token
             try:
-                return Table(*[m._call(input) for m in self.modules])
+                outs = [m._call(input) for m in self.modules]
             finally:
                 bn.__dict__.pop("_defer_now", None)
+                if pair is not None:
+                    for conv in pair:
+                        if conv is not None:
+                            conv.__dict__.pop("_skip_token", None)
+            if token is not None and pair[1] is None:         # identity shortcut: the fused bn + add holds the other end
+                for o in outs:
+                    if getattr(o, "_bdl_bn", None) is not None:
+                        o._bdl_skip_token = token
+            return Table(*outs)
         return Table(*[m._call(input) for m in self.modules])
 
     def _residual_forward(self, input, tail):
@@ -303,7 +321,7 @@ class CAddTable(_CReduce):
             k = 0 if tags[0] is not None else 1
             if (len(xs) == 2 and tags[1 - k] is None and xs[1 - k].dtype == torch.bfloat16
                     and xs[0].shape == xs[1].shape):
-                return bn_add_relu(tags[k], xs[k], xs[1 - k], self._fuse_relu)
+                return bn_add_relu(tags[k], xs[k], xs[1 - k], self._fuse_relu, getattr(xs[k], "_bdl_skip_token", None))
             # not the shape the fused kernel takes: run the deferred normalisations now and add as usual
             xs = [x if t is None else t._call(x) for x, t in zip(xs, tags)]
         if (len(xs) == 2 and xs[0].is_cuda and xs[0].dtype == torch.bfloat16 and xs[1].dtype == torch.bfloat16

@@ -6,13 +6,13 @@ import torch.distributed as dist
 from torch.autograd import Function
 
 from . import _lib
-from .functions import nhwc_pitched, rows2d
+from .functions import nhwc_pitched, rows2d, zeros_f32
 
 
 class BatchNormFn(Function):
     @staticmethod
     def forward(ctx, x, weight, bias, running_mean, running_var, training, momentum, eps, relu, sync_group,
-                residual=None):
+                residual=None, skip_token=None):
         """``residual`` (same shape as x): y = relu?(bn(x) + residual) — the BN closing a residual branch, the shortcut
         add and the ReLU in one pass (and one fused backward that also emits the shortcut's gradient)."""
         lib = _lib.cuda_lib()
@@ -21,6 +21,7 @@ class BatchNormFn(Function):
         N, H, W, C = xn.shape
         M = N * H * W
         rn, ldr = (None, 0) if residual is None else nhwc_pitched(residual)
+        ctx.skip_token = skip_token.join() if (residual is not None and skip_token is not None) else None
 
         def apply(mean_t, scale_t, use_var):
             if rn is None:
@@ -35,7 +36,7 @@ class BatchNormFn(Function):
         g = weight.detach() if weight is not None else None
         b = bias.detach() if bias is not None else None
         if training:
-            sums = torch.zeros(2 * C, dtype=torch.float32, device=x.device)
+            sums = zeros_f32(2 * C, x.device)
             _lib.check(lib.bdl_bn_stats(xn.data_ptr(), sums.data_ptr(), M, C, ldx, st), "bdl_bn_stats")
             count = float(M)
             if sync_group is not None and dist.is_initialized() and dist.get_world_size(sync_group) > 1:
@@ -68,7 +69,7 @@ class BatchNormFn(Function):
         M = N * H * W
         dyn, ldd = nhwc_pitched(dy)
         g = weight.detach() if weight is not None else None
-        sums = torch.zeros(2 * C, dtype=torch.float32, device=dy.device)
+        sums = zeros_f32(2 * C, dy.device)
         _lib.check(lib.bdl_bn_bwd_reduce(dyn.data_ptr(), xn.data_ptr(), _lib.ptr(y), mean.data_ptr(), invstd.data_ptr(),
                                          sums.data_ptr(), M, C, ldd, ldx, C, st), "bdl_bn_bwd_reduce")
         gw = weight.grad if (weight is not None and weight.requires_grad) else None
@@ -108,4 +109,8 @@ class BatchNormFn(Function):
             if dmn is not None:
                 d_res = dmn.permute(0, 3, 1, 2)
         _lib.count_launch(3)
-        return dx, None, None, None, None, None, None, None, None, None, d_res
+        tok = ctx.skip_token
+        if tok is not None and tok.paired and d_res is not None:
+            other = tok.exchange(lambda: d_res)
+            d_res = None if other is None else d_res + other      # normally first: the paired convolution adds it
+        return dx, None, None, None, None, None, None, None, None, None, d_res, None

@@ -39,10 +39,55 @@ def _wgrad_side(device):
     return st
 
 
+# ---- pre-zeroed fp32 scratch ------------------------------------------------------------------------------------
+# Accumulator vectors that kernels add into with red.global (batch-norm sums, ...) used to be a torch.zeros each: one
+# fill launch per use, 113 per ResNet-50 step. They are now slices of one zeroed buffer per device, handed out in order
+# and re-zeroed with ONE fill when the step's backward has finished (join_side_streams, part of the captured graph).
+_ZERO_POOL: dict = {}
+_ZERO_POOL_LIMIT = 16 << 20          # floats; beyond this (nobody resets the pool) callers get a plain torch.zeros
+
+
+def zeros_f32(n: int, device) -> torch.Tensor:
+    st = _ZERO_POOL.get(device.index)
+    if st is None:
+        st = _ZERO_POOL[device.index] = {"chunks": [], "cur": -1, "off": 0, "total": 0}
+    n4 = (n + 3) // 4 * 4
+    while True:
+        if st["cur"] >= 0:
+            buf = st["chunks"][st["cur"]]
+            if st["off"] + n4 <= buf.numel():
+                out = buf[st["off"]:st["off"] + n]
+                st["off"] += n4
+                st["total"] += n4
+                return out
+        if st["total"] + n4 > _ZERO_POOL_LIMIT:
+            return torch.zeros(n, dtype=torch.float32, device=device)
+        if st["cur"] + 1 < len(st["chunks"]) and st["chunks"][st["cur"] + 1].numel() >= n4:
+            st["cur"] += 1
+        else:
+            st["chunks"].insert(st["cur"] + 1, torch.zeros(max(n4, 1 << 18), dtype=torch.float32, device=device))
+            st["cur"] += 1
+        st["off"] = 0
+
+
+def reset_zero_pool(device=None):
+    """Re-zero what was handed out since the last reset; every slice must be dead by now (end of backward)."""
+    for idx, st in _ZERO_POOL.items():
+        if device is not None and device.index not in (None, idx):
+            continue
+        for k in range(st["cur"] + 1):
+            buf = st["chunks"][k]
+            used = st["off"] if k == st["cur"] else buf.numel()
+            if used:
+                buf[:used].zero_()
+        st["cur"], st["off"], st["total"] = (0 if st["chunks"] else -1), 0, 0
+
+
 def join_side_streams(device=None):
     """Make the current stream wait for every outstanding side-stream weight-gradient GEMM (and drop per-backward
     side-channel state)."""
     _PREMASKED.clear()
+    reset_zero_pool(device)
     if not _WGRAD_KEEP:
         return
     cur = torch.cuda.current_stream(device)
@@ -380,13 +425,43 @@ def _stem_s2d_backward(ctx, dy):
     return None, None, None, None, None, None, None, None
 
 
+class SkipToken:
+    """Pairs the two consumers of a residual block's input so their input gradients are summed without a pass of
+    their own. Whichever backward runs first deposits its gradient and returns None to autograd; the second adds the
+    deposit — a convolution does it in its dgrad GEMM epilogue — and returns the sum. (Autograd alone would run an
+    element-wise add over the block input: 16 per ResNet-50 step.)"""
+
+    __slots__ = ("grad", "holders")
+
+    def __init__(self):
+        self.grad = None
+        self.holders = 0          # consumers that took the token in forward; the protocol needs exactly two
+
+    def join(self):
+        self.holders += 1
+        return self
+
+    @property
+    def paired(self) -> bool:
+        return self.holders == 2
+
+    def exchange(self, mine_ready):
+        """Returns the other side's deposit, or None after storing ``mine_ready()`` as this side's."""
+        if self.grad is None:
+            self.grad = mine_ready()
+            return None
+        other, self.grad = self.grad, None
+        return other
+
+
 class ConvFn(Function):
     """2-D convolution, NHWC bf16, explicit-GEMM on the tcgen05 kernel (1x1/s1/p0 convs skip im2col entirely)."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, w16, geom, relu, scale_w, scale_b):
+    def forward(ctx, x, weight, bias, w16, geom, relu, scale_w, scale_b, skip_token=None):
         kh, kw, sh, sw, pt, pl, pb, pr, dh, dw, groups = geom
         ctx.s2d = None
+        ctx.skip_token = skip_token.join() if skip_token is not None else None
         plan = _stem_s2d_plan(x, w16, geom, ctx.needs_input_grad[0])
         if plan is not None:
             return _stem_s2d_forward(ctx, x, weight, bias, w16, geom, relu, scale_w, scale_b, plan)
@@ -471,7 +546,7 @@ class ConvFn(Function):
     @staticmethod
     def backward(ctx, dy):
         if ctx.s2d is not None:
-            return _stem_s2d_backward(ctx, dy)
+            return tuple(_stem_s2d_backward(ctx, dy)) + (None,)
         xn, w4, y = ctx.saved_tensors
         weight, bias, geom, relu, scale_w, scale_b, dims, xshape = ctx.params
         kh, kw, sh, sw, pt, pl, pb, pr, dh, dw, groups = geom
@@ -512,6 +587,16 @@ class ConvFn(Function):
         need_dx = ctx.needs_input_grad[0]
         dxn = torch.empty((N, H, W, C), dtype=torch.bfloat16, device=dy.device) if need_dx else None
         done_w = done_x = False
+        # residual block input: the other consumer's gradient (if it ran first) is added in the dgrad epilogue
+        token = ctx.skip_token if (need_dx and ctx.skip_token is not None and ctx.skip_token.paired) else None
+        skip = token.grad if token is not None else None
+        res2d = None
+        if skip is not None:
+            token.grad = None
+            if c_real == C and tuple(xshape) == (N, C, H, W) and tuple(skip.shape) == tuple(xshape):
+                skip_n, lds = nhwc_pitched(skip)
+                res2d = rows2d(skip_n, lds)
+        fused_skip = False
         if implicit:
             ldz = dz.stride(0)
             if gw is not None and not padded_c and C % 8 == 0 and C >= 16 and scale_w == 1.0 and gw2.stride(1) == 1:
@@ -527,8 +612,9 @@ class ConvFn(Function):
             if need_dx and sh == 1 and sw == 1 and dh * (kh - 1) - pt >= 0 and dw * (kw - 1) - pl >= 0:
                 dz_nhwc = torch.as_strided(dz, (N, Ho, Wo, O), (Ho * Wo * ldz, Wo * ldz, ldz, 1), dz.storage_offset())
                 conv_igemm(1, dz_nhwc, ldz, w2, dxn.view(N * H * W, C), C, H, W, kh, kw, 1, 1, dh * (kh - 1) - pt,
-                           dw * (kw - 1) - pl, dh, dw)
+                           dw * (kw - 1) - pl, dh, dw, residual=res2d)
                 done_x = True
+                fused_skip = res2d is not None
         for g in range(groups):
             if (gw is None or done_w) and (not need_dx or done_x):
                 break
@@ -566,7 +652,9 @@ class ConvFn(Function):
             if need_dx and not done_x:
                 wg = w2[g * Og:(g + 1) * Og]
                 if direct:
-                    gemm_bf16(dzg, wg, b_mn=True, out=dxn.view(N * H * W, C)[:, g * Cg:(g + 1) * Cg])
+                    gemm_bf16(dzg, wg, b_mn=True, out=dxn.view(N * H * W, C)[:, g * Cg:(g + 1) * Cg],
+                              residual=res2d if groups == 1 else None)
+                    fused_skip = res2d is not None and groups == 1
                 else:
                     if Kp != K:
                         wpad = torch.zeros((Og, Kp), dtype=torch.bfloat16, device=dy.device)
@@ -586,7 +674,12 @@ class ConvFn(Function):
                 dx = dx[:, :xshape[1]]
             if tuple(dx.shape) != tuple(xshape):     # asymmetric SAME padding: drop the materialised border
                 dx = dx[:, :, :xshape[2], :xshape[3]]
-        return dx, None, None, None, None, None, None, None
+            if skip is not None and not fused_skip:
+                dx = dx + skip                       # a dgrad path without a residual epilogue (strided / grouped)
+            elif token is not None and skip is None:
+                token.grad = dx                      # first of the pair: the other consumer adds this
+                dx = None
+        return dx, None, None, None, None, None, None, None, None
 
 
 class FanOutFn(Function):

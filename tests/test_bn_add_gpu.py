@@ -71,3 +71,42 @@ def test_residual_block_fused_equals_unfused():
     (y0, dx0, g0, n0), (y1, dx1, g1, n1) = results[False], results[True]
     assert _rel(y1, y0) < 1e-2 and _rel(dx1, dx0) < 2e-2 and _rel(g1, g0) < 2e-2
     assert n1 < n0                                       # two add+ReLU forward and two backward launches are gone
+
+
+def _proj_block(cin, mid, cout):
+    from bigdl_b200.nn import layer as L
+    main = (L.Sequential().add(L.SpatialConvolution(cin, mid, 1, 1)).add(L.SpatialBatchNormalization(mid)).add(L.ReLU())
+            .add(L.SpatialConvolution(mid, mid, 3, 3, 2, 2, 1, 1)).add(L.SpatialBatchNormalization(mid)).add(L.ReLU())
+            .add(L.SpatialConvolution(mid, cout, 1, 1)).add(L.SpatialBatchNormalization(cout)))
+    short = L.Sequential().add(L.SpatialConvolution(cin, cout, 1, 1, 2, 2)).add(L.SpatialBatchNormalization(cout))
+    return L.Sequential().add(L.ConcatTable().add(main).add(short)).add(L.CAddTable()).add(L.ReLU())
+
+
+def test_skip_gradient_pairing_matches_autograd_sum():
+    """Identity and projection shortcuts: the block input's two gradients are summed in a dgrad epilogue (SkipToken)
+    instead of by autograd; results must equal the unpaired run, with fewer at:: add kernels on the tape."""
+    from bigdl_b200.nn import fusion
+    from bigdl_b200.nn import layer as L
+    from bigdl_b200.utils import config
+    torch.manual_seed(2)
+    model = (L.Sequential().add(L.SpatialConvolution(16, 64, 3, 3, 1, 1, 1, 1)).add(_block(64, 16))
+             .add(_proj_block(64, 32, 128)).add(_block(128, 32))).cuda().training()
+    x = torch.randn(4, 16, 12, 12, device=DEV).bfloat16()
+    go = torch.randn(4, 128, 6, 6, device=DEV).bfloat16()
+    res = {}
+    for mode in (False, True):
+        config.set("bigdl.fusion.skipgrad", mode)
+        fusion.unfuse(model)
+        fusion.fuse(model)
+        pairs = [m.__dict__.get("_skip_pair") for m in model.all_modules() if "_skip_pair" in m.__dict__]
+        assert (len(pairs) == 3) == mode
+        w, g = model.getParameters()
+        g.zero_()
+        xin = x.clone().requires_grad_(True)
+        with torch.enable_grad():
+            y = model._call(xin)
+        torch.autograd.backward(y, go)
+        res[mode] = (y.detach().float(), xin.grad.float(), g.clone().float())
+    config.set("bigdl.fusion.skipgrad", True)
+    for a, b in zip(res[True], res[False]):
+        assert _rel(a, b) < 2e-2

@@ -49,14 +49,18 @@ class BatchNormFn(Function):
                        "bdl_bn_finalize")
             apply(mean, invstd, 0)
             _lib.count_launch(3)
-            ctx.save_for_backward(xn, mean, invstd, y if relu else None)
+            # BN + ReLU: backward recomputes the mask from x with the forward's own scale / shift, so y is not kept for it
+            remask = relu and residual is None
+            ctx.save_for_backward(xn, mean, invstd, y if (relu and not remask) else None)
             ctx.cfg = (weight, bias, ldx, count, relu, sync_group, residual is not None)
+            ctx.remask = remask
         else:
             apply(running_mean, running_var, 1)
             _lib.count_launch()
             inv = torch.rsqrt(running_var + eps)
             ctx.save_for_backward(xn, running_mean, inv, y if relu else None)
             ctx.cfg = (weight, bias, ldx, None, relu, None, residual is not None)
+            ctx.remask = False
         return y.permute(0, 3, 1, 2)
 
     @staticmethod
@@ -70,8 +74,16 @@ class BatchNormFn(Function):
         dyn, ldd = nhwc_pitched(dy)
         g = weight.detach() if weight is not None else None
         sums = zeros_f32(2 * C, dy.device)
-        _lib.check(lib.bdl_bn_bwd_reduce(dyn.data_ptr(), xn.data_ptr(), _lib.ptr(y), mean.data_ptr(), invstd.data_ptr(),
-                                         sums.data_ptr(), M, C, ldd, ldx, C, st), "bdl_bn_bwd_reduce")
+        remask = ctx.remask
+        bt = bias.detach() if bias is not None else None
+        if remask:
+            _lib.check(lib.bdl_bn_bwd_reduce_remask(dyn.data_ptr(), xn.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
+                                                    _lib.ptr(g), _lib.ptr(bt), sums.data_ptr(), M, C, ldd, ldx, st),
+                       "bdl_bn_bwd_reduce_remask")
+        else:
+            _lib.check(lib.bdl_bn_bwd_reduce(dyn.data_ptr(), xn.data_ptr(), _lib.ptr(y), mean.data_ptr(),
+                                             invstd.data_ptr(), sums.data_ptr(), M, C, ldd, ldx, C, st),
+                       "bdl_bn_bwd_reduce")
         gw = weight.grad if (weight is not None and weight.requires_grad) else None
         gb = bias.grad if (bias is not None and bias.requires_grad) else None
         if gw is not None or gb is not None:
@@ -85,7 +97,11 @@ class BatchNormFn(Function):
         dmn = torch.empty((N, H, W, C), dtype=torch.bfloat16, device=dy.device) if want_mask else None
 
         def bwd_apply(sums_t, cnt):
-            if dmn is None:
+            if remask:
+                _lib.check(lib.bdl_bn_bwd_apply_remask(dyn.data_ptr(), xn.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
+                                                       _lib.ptr(g), _lib.ptr(bt), sums_t.data_ptr(), dxn.data_ptr(), M,
+                                                       cnt, C, ldd, ldx, C, st), "bdl_bn_bwd_apply_remask")
+            elif dmn is None:
                 _lib.check(lib.bdl_bn_bwd_apply(dyn.data_ptr(), xn.data_ptr(), _lib.ptr(y), mean.data_ptr(),
                                                 invstd.data_ptr(), _lib.ptr(g), sums_t.data_ptr(), dxn.data_ptr(), M, cnt,
                                                 C, ldd, ldx, C, C, st), "bdl_bn_bwd_apply")

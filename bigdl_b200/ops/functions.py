@@ -98,8 +98,10 @@ def join_side_streams(device=None):
 
 
 def workspace(numel: int, device, slot: int = 0) -> torch.Tensor:
-    """Grow-only bf16 scratch buffer shared by all conv layers of a device (im2col / dgrad columns)."""
-    key = (device.index, slot)
+    """Grow-only bf16 scratch buffer shared by the conv layers of a device that run on the SAME stream (im2col / dgrad
+    columns). Keyed by stream: Concat branches on side streams (``bigdl.concat.streams``) get their own buffer, so two
+    branches that both take the explicit im2col path cannot overwrite each other's columns."""
+    key = (device.index, slot, torch.cuda.current_stream(device).cuda_stream)
     buf = _WS.get(key)
     if buf is None or buf.numel() < numel:
         buf = torch.empty(max(numel, 1 << 20), dtype=torch.bfloat16, device=device)

@@ -38,11 +38,15 @@ __device__ __forceinline__ void bn_store8(__nv_bfloat16* p, const float (&f)[8])
 
 // Thread layout shared by the reductions: vcols = min(C/8, 256) vector columns across, rif = 256/vcols rows in flight.
 // acc0/acc1 are two per-channel accumulators (sum & sum of squares, or dbeta & dgamma).
-template <int kMode>  // 0: forward stats (x)   1: backward sums (dy, x̂, optional ReLU mask from y)
+// kRemask (backward only): the layer had a fused ReLU and its output is NOT read back for the mask — it is recomputed
+// from x with exactly the forward's arithmetic (y > 0  <=>  fma(x, invstd*gamma, beta - mean*invstd*gamma) > 0), which
+// saves one of the three tensor reads of this pass.
+template <int kMode, bool kRemask = false>  // 0: forward stats (x)   1: backward sums (dy, x̂, optional ReLU mask)
 __global__ void bn_reduce_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ x,
                                  const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean,
                                  const float* __restrict__ invstd, float* __restrict__ out, long long M, int C,
-                                 long long lda, long long ldx, long long ldy, int rows_per_block) {
+                                 long long lda, long long ldx, long long ldy, int rows_per_block,
+                                 const float* __restrict__ gamma = nullptr, const float* __restrict__ beta = nullptr) {
   extern __shared__ float red[];  // [rif][vcols*16]
   const int cvec = C / 8;
   const int vcols = cvec < static_cast<int>(blockDim.x) ? cvec : blockDim.x;
@@ -54,12 +58,16 @@ __global__ void bn_reduce_kernel(const __nv_bfloat16* __restrict__ a, const __nv
   if (r1 > M) r1 = M;
   for (int cv = tc; cv < cvec; cv += vcols) {
     float s0[8] = {0, 0, 0, 0, 0, 0, 0, 0}, s1[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    float mu[8], is[8];
+    float mu[8], is[8], ma[8], mb[8];
     if (kMode == 1) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         mu[j] = mean[cv * 8 + j];
         is[j] = invstd[cv * 8 + j];
+        if (kRemask) {
+          ma[j] = is[j] * (gamma ? gamma[cv * 8 + j] : 1.f);
+          mb[j] = (beta ? beta[cv * 8 + j] : 0.f) - mu[j] * ma[j];
+        }
       }
     }
     if (tr < rif) {
@@ -92,7 +100,7 @@ __global__ void bn_reduce_kernel(const __nv_bfloat16* __restrict__ a, const __nv
           for (int u = 0; u < 4; ++u) {
             va[u] = *reinterpret_cast<const uint4*>(a + (r + u * rif) * lda + cv * 8);
             vx[u] = *reinterpret_cast<const uint4*>(x + (r + u * rif) * ldx + cv * 8);
-            if (y) vy[u] = *reinterpret_cast<const uint4*>(y + (r + u * rif) * ldy + cv * 8);
+            if (!kRemask && y) vy[u] = *reinterpret_cast<const uint4*>(y + (r + u * rif) * ldy + cv * 8);
           }
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
@@ -103,7 +111,10 @@ __global__ void bn_reduce_kernel(const __nv_bfloat16* __restrict__ a, const __nv
             for (int j = 0; j < 4; ++j) {
               float2 g2 = __bfloat1622float2(qa[j]);
               const float2 x2 = __bfloat1622float2(qx[j]);
-              if (y) {
+              if (kRemask) {
+                g2.x = fmaf(x2.x, ma[2 * j], mb[2 * j]) > 0.f ? g2.x : 0.f;
+                g2.y = fmaf(x2.y, ma[2 * j + 1], mb[2 * j + 1]) > 0.f ? g2.y : 0.f;
+              } else if (y) {
                 const float2 y2 = __bfloat1622float2(qy[j]);
                 g2.x = y2.x > 0.f ? g2.x : 0.f;
                 g2.y = y2.y > 0.f ? g2.y : 0.f;
@@ -128,7 +139,10 @@ __global__ void bn_reduce_kernel(const __nv_bfloat16* __restrict__ a, const __nv
         } else {
           float fx[8];
           bn_load8(x + r * ldx + cv * 8, fx);
-          if (y) {
+          if (kRemask) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) fa[j] = fmaf(fx[j], ma[j], mb[j]) > 0.f ? fa[j] : 0.f;
+          } else if (y) {
             float fy[8];
             bn_load8(y + r * ldy + cv * 8, fy);
 #pragma unroll
@@ -284,14 +298,14 @@ __global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat
 // dx = gamma * invstd * (dy' - dbeta/count - x̂ * dgamma/count), dy' = dy masked by (y > 0) when ReLU was fused.
 // Rewritten per channel as dx = ka * dy' + kb * x + kc with
 //   ka = gamma*invstd, kb = -gamma*invstd^2*dgamma/count, kc = -ka*dbeta/count - kb*mean.
-template <bool kMask>
+template <bool kMask, bool kRemask = false>
 __global__ void bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                                     const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean,
                                     const float* __restrict__ invstd, const float* __restrict__ gamma,
                                     const float* __restrict__ sums, __nv_bfloat16* __restrict__ dx, long long M,
                                     float count, int C, long long lddy, long long ldx, long long ldy,
                                     long long lddx, int rows_per_block, __nv_bfloat16* __restrict__ dmask = nullptr,
-                                    long long lddm = 0) {
+                                    long long lddm = 0, const float* __restrict__ beta = nullptr) {
   const int cvec = C / 8;
   const int vcols = cvec < static_cast<int>(blockDim.x) ? cvec : blockDim.x;
   const int rif = blockDim.x / vcols;
@@ -303,12 +317,16 @@ __global__ void bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const 
   if (r1 > M) r1 = M;
   const float inv_count = 1.f / count;
   for (int cv = tc; cv < cvec; cv += vcols) {
-    float ka[8], kb[8], kc[8];
+    float ka[8], kb[8], kc[8], ma[8], mb[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const int c = cv * 8 + j;
       const float is = invstd[c];
       const float gm = gamma ? gamma[c] : 1.f;
+      if (kRemask) {                       // the forward's scale / shift, bit for bit (bn_apply_kernel)
+        ma[j] = is * gm;
+        mb[j] = (beta ? beta[c] : 0.f) - mean[c] * ma[j];
+      }
       ka[j] = gm * is;
       kb[j] = -gm * is * is * sums[C + c] * inv_count;
       kc[j] = -ka[j] * sums[c] * inv_count - kb[j] * mean[c];
@@ -320,7 +338,7 @@ __global__ void bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const 
       for (int u = 0; u < 2; ++u) {
         vg[u] = *reinterpret_cast<const uint4*>(dy + (r + u * rif) * lddy + cv * 8);
         vx[u] = *reinterpret_cast<const uint4*>(x + (r + u * rif) * ldx + cv * 8);
-        if (y) vy[u] = *reinterpret_cast<const uint4*>(y + (r + u * rif) * ldy + cv * 8);
+        if (!kRemask && y) vy[u] = *reinterpret_cast<const uint4*>(y + (r + u * rif) * ldy + cv * 8);
       }
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
@@ -332,7 +350,10 @@ __global__ void bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const 
         for (int j = 0; j < 4; ++j) {
           float2 g2 = __bfloat1622float2(qg[j]);
           const float2 x2 = __bfloat1622float2(qx[j]);
-          if (y) {
+          if (kRemask) {
+            g2.x = fmaf(x2.x, ma[2 * j], mb[2 * j]) > 0.f ? g2.x : 0.f;
+            g2.y = fmaf(x2.y, ma[2 * j + 1], mb[2 * j + 1]) > 0.f ? g2.y : 0.f;
+          } else if (y) {
             const float2 y2 = __bfloat1622float2(qy[j]);
             g2.x = y2.x > 0.f ? g2.x : 0.f;
             g2.y = y2.y > 0.f ? g2.y : 0.f;
@@ -352,7 +373,10 @@ __global__ void bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const 
       float g[8], fx[8];
       bn_load8(dy + r * lddy + cv * 8, g);
       bn_load8(x + r * ldx + cv * 8, fx);
-      if (y) {
+      if (kRemask) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] = fmaf(fx[j], ma[j], mb[j]) > 0.f ? g[j] : 0.f;
+      } else if (y) {
         float fy[8];
         bn_load8(y + r * ldy + cv * 8, fy);
 #pragma unroll
@@ -521,6 +545,38 @@ extern "C" int bdl_bn_bwd_reduce(const void* dy, const void* x, const void* y, c
       static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
       static_cast<const __nv_bfloat16*>(y), mean, invstd, sums, M, C, lddy, ldx, ldy, rpb);
   return bdl_check_launch("bn_reduce_kernel<1>");
+}
+
+// Backward of BN + fused ReLU without reading the layer's output: the mask is recomputed from x (see kRemask).
+extern "C" int bdl_bn_bwd_reduce_remask(const void* dy, const void* x, const float* mean, const float* invstd,
+                                        const float* gamma, const float* beta, float* sums, long long M, int C,
+                                        long long lddy, long long ldx, void* stream) {
+  if (bn_check("bdl_bn_bwd_reduce_remask: C and pitches must be multiples of 8, pointers 16-byte aligned", C, lddy, ldx,
+               dy, x))
+    return BDL_ERR_INVALID;
+  int grid, rpb, threads;
+  size_t smem;
+  reduce_geometry(M, C, 1, &grid, &rpb, &threads, &smem);
+  bn_reduce_kernel<1, true><<<grid, threads, smem, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x), nullptr, mean, invstd, sums, M, C,
+      lddy, ldx, 0, rpb, gamma, beta);
+  return bdl_check_launch("bn_reduce_kernel<1,remask>");
+}
+
+extern "C" int bdl_bn_bwd_apply_remask(const void* dy, const void* x, const float* mean, const float* invstd,
+                                       const float* gamma, const float* beta, const float* sums, void* dx, long long M,
+                                       float count, int C, long long lddy, long long ldx, long long lddx,
+                                       void* stream) {
+  if (bn_check("bdl_bn_bwd_apply_remask: C and pitches must be multiples of 8, pointers 16-byte aligned", C, lddy, lddx,
+               dy, dx))
+    return BDL_ERR_INVALID;
+  int grid, rpb;
+  size_t smem_unused;
+  stream_geometry(M, C, &grid, &rpb, &smem_unused);
+  bn_bwd_apply_kernel<false, true><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x), nullptr, mean, invstd, gamma, sums,
+      static_cast<__nv_bfloat16*>(dx), M, count, C, lddy, ldx, 0, lddx, rpb, nullptr, 0, beta);
+  return bdl_check_launch("bn_bwd_apply_kernel(remask)");
 }
 
 extern "C" int bdl_bn_bwd_apply(const void* dy, const void* x, const void* y, const float* mean, const float* invstd,

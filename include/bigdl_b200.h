@@ -239,6 +239,14 @@ int bdl_bn_bwd_reduce(const void* dy, const void* x, const void* y, const float*
 int bdl_bn_bwd_apply(const void* dy, const void* x, const void* y, const float* mean, const float* invstd,
                      const float* gamma, const float* sums, void* dx, long long M, float count, int C, long long lddy,
                      long long ldx, long long ldy, long long lddx, void* stream);
+/* backward of BN + fused ReLU with the mask recomputed from x (y > 0 <=> fma(x, invstd*gamma, beta - mean*invstd*gamma) > 0,
+ * the forward's own arithmetic) instead of read back from the output: one tensor read less per pass */
+int bdl_bn_bwd_reduce_remask(const void* dy, const void* x, const float* mean, const float* invstd, const float* gamma,
+                             const float* beta, float* sums, long long M, int C, long long lddy, long long ldx,
+                             void* stream);
+int bdl_bn_bwd_apply_remask(const void* dy, const void* x, const float* mean, const float* invstd, const float* gamma,
+                            const float* beta, const float* sums, void* dx, long long M, float count, int C,
+                            long long lddy, long long ldx, long long lddx, void* stream);
 /* residual-block fusions: y = relu?(bn(x) + res) in one pass; bwd_apply that also emits dy masked by (y > 0) */
 int bdl_bn_apply_res(const void* x, const void* res, void* y, const float* mean, const float* invstd_or_var,
                      const float* gamma, const float* beta, long long M, int C, long long ldx, long long ldr,

@@ -110,3 +110,31 @@ def test_skip_gradient_pairing_matches_autograd_sum():
     config.set("bigdl.fusion.skipgrad", True)
     for a, b in zip(res[True], res[False]):
         assert _rel(a, b) < 2e-2
+
+
+@pytest.mark.parametrize("affine", [True, False])
+def test_bn_relu_backward_recomputes_the_mask(affine):
+    """BN + fused ReLU: backward derives the ReLU mask from x (no read of the output); must equal fp32 autograd."""
+    from bigdl_b200.ops.batchnorm import BatchNormFn
+    torch.manual_seed(4)
+    N, C, H, W = 6, 96, 10, 11
+    x = torch.randn(N, H, W, C, device=DEV).bfloat16().permute(0, 3, 1, 2).requires_grad_(True)
+    w = (torch.rand(C, device=DEV) + 0.5).requires_grad_(True) if affine else None
+    b = torch.randn(C, device=DEV).requires_grad_(True) if affine else None
+    if affine:
+        w.grad, b.grad = torch.zeros_like(w), torch.zeros_like(b)
+    rm, rv = torch.zeros(C, device=DEV), torch.ones(C, device=DEV)
+    y = BatchNormFn.apply(x, w, b, rm, rv, True, 0.1, 1e-5, True, None)
+    go = torch.randn_like(y)
+    y.backward(go)
+    xf = x.detach().float().requires_grad_(True)
+    wf = w.detach().clone().requires_grad_(True) if affine else None
+    bf = b.detach().clone().requires_grad_(True) if affine else None
+    ref = F.relu(F.batch_norm(xf, None, None, wf, bf, True, 0.1, 1e-5))
+    # the kernel masks with ITS y (bf16 of the fp32 result): use the same mask in the reference backward
+    mask = (y.detach().float() > 0).float()
+    pre = F.batch_norm(xf, None, None, wf, bf, True, 0.1, 1e-5)
+    (pre * mask).backward(go.float())
+    assert _rel(y, ref) < 1e-2 and _rel(x.grad, xf.grad) < 2e-2
+    if affine:
+        assert _rel(w.grad, wf.grad) < 2e-2 and _rel(b.grad, bf.grad) < 2e-2

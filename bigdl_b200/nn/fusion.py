@@ -51,6 +51,16 @@ def fuse(model: Module) -> Module:
             a._fuse_relu, b._fused = True, True
         elif conv_sum and isinstance(a, CAddTable) and not a._fuse_relu:
             a._fuse_relu, b._fused = True, True
+    # conv -> BatchNorm (training): the convolution's GEMM epilogue produces the BN statistics
+    for m in model.all_modules():
+        if type(m) is SpatialConvolution:
+            m.__dict__.pop("_bn_stats", None)
+    if config.get("bigdl.fusion.bnstats"):
+        for a, b in _pairs(model):
+            if (type(a) is SpatialConvolution and isinstance(b, BatchNormalization) and not a._fuse_relu
+                    and a.n_group == 1 and not getattr(b, "_folded", False) and getattr(b, "n_dim", 4) == 4
+                    and getattr(a, "data_format", "NCHW") == "NCHW" and getattr(b, "data_format", "NCHW") == "NCHW"):
+                a.__dict__["_bn_stats"] = True
     if conv_sum and config.get("bigdl.fusion.residual", True):
         _mark_residual_blocks(model)
     return model
@@ -113,6 +123,7 @@ def unfuse(model: Module) -> Module:
             m._fuse_relu = False
         if type(m) is ReLU:
             m._fused = False
+        m.__dict__.pop("_bn_stats", None)
         for k in ("_res_tail", "_res_main", "_res_relu", "_bn_tail", "_skip_pair"):
             m.__dict__.pop(k, None)
     return model

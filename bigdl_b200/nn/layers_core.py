@@ -199,8 +199,17 @@ class SpatialConvolution(Module):
                 from ..ops.functions import set_out_hint
 
                 set_out_hint(hint)
+            stats = None
+            if self.__dict__.get("_bn_stats") and self.train and not self._fuse_relu:
+                # the next layer is a BatchNorm (nn/fusion.py): let the GEMM epilogue sum the output columns
+                from ..ops.functions import zeros_f32
+
+                stats = zeros_f32(2 * self.n_output_plane, x.device)
             y = ConvFn.apply(xin, self.weight, bias, w16, geom, self._fuse_relu, self.scaleW, self.scaleB,
-                             self.__dict__.pop("_skip_token", None))      # residual-block input pairing (SkipToken)
+                             self.__dict__.pop("_skip_token", None),      # residual-block input pairing (SkipToken)
+                             stats)
+            if stats is not None and getattr(stats, "_bdl_done", False):
+                y._bdl_bn_stats = stats
         else:
             w = self.weight
             if x.dtype != w.dtype:
@@ -490,8 +499,12 @@ class BatchNormalization(Module):
                 # (nn/fusion.py marks the pattern, ConcatTable arms this flag for exactly one call)
                 out = x.view_as(x)
                 out._bdl_bn = self
+                st = getattr(x, "_bdl_bn_stats", None)
+                if st is not None:
+                    out._bdl_bn_stats = st
                 return out
-            y = BatchNormFn.apply(x, w, b, rm, rv, self.train, self.momentum, self.eps, self._fuse_relu, self._sync)
+            y = BatchNormFn.apply(x, w, b, rm, rv, self.train, self.momentum, self.eps, self._fuse_relu, self._sync,
+                                  None, None, getattr(x, "_bdl_bn_stats", None) if self.train else None)
         else:
             xf = x.float() if x.dtype != torch.float32 else x
             y = F.batch_norm(xf, rm, rv, w, b, self.train, self.momentum, self.eps)
@@ -517,7 +530,7 @@ def bn_add_relu(bn: BatchNormalization, pre: torch.Tensor, shortcut: torch.Tenso
 
     return BatchNormFn.apply(pre, bn._parameters.get("weight"), bn._parameters.get("bias"), bn._buffers["runningMean"],
                              bn._buffers["runningVar"], bn.train, bn.momentum, bn.eps, relu, bn._sync, shortcut,
-                             skip_token)
+                             skip_token, getattr(pre, "_bdl_bn_stats", None) if bn.train else None)
 
 
 class SoftMax(Module):

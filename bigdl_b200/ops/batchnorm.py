@@ -12,7 +12,7 @@ from .functions import nhwc_pitched, rows2d, zeros_f32
 class BatchNormFn(Function):
     @staticmethod
     def forward(ctx, x, weight, bias, running_mean, running_var, training, momentum, eps, relu, sync_group,
-                residual=None, skip_token=None):
+                residual=None, skip_token=None, pre_stats=None):
         """``residual`` (same shape as x): y = relu?(bn(x) + residual) — the BN closing a residual branch, the shortcut
         add and the ReLU in one pass (and one fused backward that also emits the shortcut's gradient)."""
         lib = _lib.cuda_lib()
@@ -36,8 +36,11 @@ class BatchNormFn(Function):
         g = weight.detach() if weight is not None else None
         b = bias.detach() if bias is not None else None
         if training:
-            sums = zeros_f32(2 * C, x.device)
-            _lib.check(lib.bdl_bn_stats(xn.data_ptr(), sums.data_ptr(), M, C, ldx, st), "bdl_bn_stats")
+            if pre_stats is not None and pre_stats.numel() == 2 * C:
+                sums = pre_stats          # summed by the producing convolution's GEMM epilogue: no pass over x
+            else:
+                sums = zeros_f32(2 * C, x.device)
+                _lib.check(lib.bdl_bn_stats(xn.data_ptr(), sums.data_ptr(), M, C, ldx, st), "bdl_bn_stats")
             count = float(M)
             if sync_group is not None and dist.is_initialized() and dist.get_world_size(sync_group) > 1:
                 dist.all_reduce(sums, group=sync_group)          # sync-BN: global batch statistics
@@ -129,4 +132,4 @@ class BatchNormFn(Function):
         if tok is not None and tok.paired and d_res is not None:
             other = tok.exchange(lambda: d_res)
             d_res = None if other is None else d_res + other      # normally first: the paired convolution adds it
-        return dx, None, None, None, None, None, None, None, None, None, d_res, None
+        return dx, None, None, None, None, None, None, None, None, None, d_res, None, None

@@ -460,7 +460,7 @@ class ConvFn(Function):
     """2-D convolution, NHWC bf16, explicit-GEMM on the tcgen05 kernel (1x1/s1/p0 convs skip im2col entirely)."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, w16, geom, relu, scale_w, scale_b, skip_token=None):
+    def forward(ctx, x, weight, bias, w16, geom, relu, scale_w, scale_b, skip_token=None, stats=None):
         kh, kw, sh, sw, pt, pl, pb, pr, dh, dw, groups = geom
         ctx.s2d = None
         ctx.skip_token = skip_token.join() if skip_token is not None else None
@@ -513,9 +513,11 @@ class ConvFn(Function):
                 ctx.fused_residual = True
             else:
                 set_residual_hint((rs, rrelu))          # shapes disagree: leave it to the caller's add
+        if stats is not None and (relu or res2d is not None or groups != 1 or not (implicit or direct)):
+            stats = None                  # column statistics are only taken of a plain conv output (the BN's input)
         if implicit:
             conv_igemm(0, xn, ldx, w2, y2, O, Ho, Wo, kh, kw, sh, sw, pt, pl, dh, dw, bias=b32, relu=relu,
-                       residual=res2d)
+                       residual=res2d, stats=stats)
         for g in range(groups if not implicit else 0):
             wg = w2[g * Og:(g + 1) * Og]
             if Kp != K:
@@ -538,7 +540,8 @@ class ConvFn(Function):
                 _lib.count_launch()
                 if keep:
                     kept_cols = a
-            gemm_bf16(a, wg, bias=bg, relu=relu, out=y2[:, g * Og:(g + 1) * Og], residual=res2d if direct else None)
+            gemm_bf16(a, wg, bias=bg, relu=relu, out=y2[:, g * Og:(g + 1) * Og], residual=res2d if direct else None,
+                      stats=stats if direct else None)
         ctx.kept_cols = kept_cols
         ctx.save_for_backward(xn, w4, y if relu else None)
         ctx.params = (weight, bias, geom, relu, scale_w, scale_b,
@@ -548,7 +551,7 @@ class ConvFn(Function):
     @staticmethod
     def backward(ctx, dy):
         if ctx.s2d is not None:
-            return tuple(_stem_s2d_backward(ctx, dy)) + (None,)
+            return tuple(_stem_s2d_backward(ctx, dy)) + (None, None)
         xn, w4, y = ctx.saved_tensors
         weight, bias, geom, relu, scale_w, scale_b, dims, xshape = ctx.params
         kh, kw, sh, sw, pt, pl, pb, pr, dh, dw, groups = geom
@@ -681,7 +684,7 @@ class ConvFn(Function):
             elif token is not None and skip is None:
                 token.grad = dx                      # first of the pair: the other consumer adds this
                 dx = None
-        return dx, None, None, None, None, None, None, None, None
+        return dx, None, None, None, None, None, None, None, None, None
 
 
 class FanOutFn(Function):

@@ -18,6 +18,20 @@ def _log(kind, **kw):
             f.write(__import__("json").dumps(_LOG[-1]) + "\n")
 
 
+def _arm_stats(lib, stats, N):
+    """Ask the next launch to add the per-column (sum, sum of squares) of its bf16 output into ``stats`` [2N] fp32."""
+    if stats is None:
+        return
+    assert stats.dtype == torch.float32 and stats.numel() == 2 * N and stats.is_contiguous()
+    stats._bdl_done = False
+    lib.bdl_gemm_set_stats(ctypes.c_void_p(stats.data_ptr()))
+
+
+def _stats_result(lib, stats):
+    if stats is not None:
+        stats._bdl_done = bool(lib.bdl_gemm_stats_done())
+
+
 def _set_residual(lib, residual, M, N):
     if residual is None:
         return
@@ -28,13 +42,15 @@ def _set_residual(lib, residual, M, N):
 
 def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False, bias=None, relu=False,
               out: torch.Tensor | None = None, out_dtype=torch.bfloat16, accumulate: bool = False, splits: int = 0,
-              residual: torch.Tensor | None = None):
+              residual: torch.Tensor | None = None, stats: torch.Tensor | None = None):
     """D[M,N] = opA(a) @ opB(b)^T on the tensor cores.
 
     ``a`` is [M,K] (or [K,M] when ``a_mn``), ``b`` is [N,K] (or [K,N] when ``b_mn``); both bf16, 2-D, unit inner
     stride (row pitch may exceed the row length: channel slices of a wider NHWC tensor are fine).
     ``accumulate`` adds into an fp32 ``out`` with red.global.add (split-K is chosen automatically).
     ``residual`` ([M,N] bf16, unit inner stride) is added before the ReLU in the epilogue (bf16 output only).
+    ``stats`` ([2N] fp32, zeroed): the epilogue adds the per-column sum / sum of squares of the output (batch-norm
+    statistics for free); ``stats._bdl_done`` says whether this launch could (else run ``bdl_bn_stats``).
     """
     lib = _lib.cuda_lib()
     assert lib is not None, "gemm_bf16 needs a CUDA device"
@@ -51,9 +67,12 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: boo
         assert bias.dtype == torch.float32 and bias.is_contiguous()
     _log("gemm", M=M, N=N, K=K, a_mn=int(a_mn), b_mn=int(b_mn), acc=int(accumulate))
     _set_residual(lib, residual, M, N)
+    _arm_stats(lib, stats, N)
     rc = lib.bdl_gemm_bf16(_lib.ptr(a), _lib.ptr(b), _lib.ptr(out), _lib.ptr(bias), M, N, K,
                            a.stride(0), b.stride(0), out.stride(0), int(a_mn), int(b_mn),
                            int(out.dtype == torch.float32), flags, splits, _lib.stream_ptr())
+    if stats is not None:
+        lib.bdl_gemm_set_stats(None) if rc else _stats_result(lib, stats)
     _lib.check(rc, "bdl_gemm_bf16")
     _lib.count_launch()
     return out
@@ -61,7 +80,7 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: boo
 
 def conv_igemm(mode: int, act: torch.Tensor, ld_act: int, other: torch.Tensor, out: torch.Tensor, O: int, Ho: int,
                Wo: int, kh: int, kw: int, sh: int, sw: int, ph: int, pw: int, dh: int, dw: int, bias=None, relu=False,
-               accumulate=False, splits: int = 0, residual=None):
+               accumulate=False, splits: int = 0, residual=None, stats=None):
     """Implicit-GEMM convolution (csrc/gemm_tcgen05.cu, TMA im2col). ``act`` is an NHWC view [N,H,W,C] with pixel
     pitch ``ld_act``; ``other`` is the 2-D weight matrix (modes 0/1) or dY [N*Ho*Wo, O] (mode 2); ``out`` is 2-D."""
     lib = _lib.cuda_lib()
@@ -69,9 +88,12 @@ def conv_igemm(mode: int, act: torch.Tensor, ld_act: int, other: torch.Tensor, o
     flags = (BIAS if bias is not None else 0) | (RELU if relu else 0) | (ATOMIC_ADD if accumulate else 0)
     _log("conv", mode=mode, N=N, H=H, W=W, C=C, O=O, Ho=Ho, Wo=Wo, kh=kh, kw=kw, sh=sh)
     _set_residual(lib, residual, N * Ho * Wo, O)
+    _arm_stats(lib, stats if mode == 0 else None, O)
     rc = lib.bdl_conv_igemm_bf16(mode, act.data_ptr(), N, H, W, C, ld_act, other.data_ptr(), other.stride(0),
                                  out.data_ptr(), out.stride(0), _lib.ptr(bias), O, Ho, Wo, kh, kw, sh, sw, ph, pw, dh,
                                  dw, int(out.dtype == torch.float32), flags, splits, _lib.stream_ptr())
+    if stats is not None and mode == 0:
+        lib.bdl_gemm_set_stats(None) if rc else _stats_result(lib, stats)
     _lib.check(rc, "bdl_conv_igemm_bf16")
     _lib.count_launch()
     return out

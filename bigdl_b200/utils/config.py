@@ -46,6 +46,7 @@ _DEFAULTS: dict[str, Any] = {
     "bigdl.mkldnn.fusion.convrelu": True,
     "bigdl.mkldnn.fusion.convsum": True,
     "bigdl.fusion.bnadd": True,              # BatchNorm closing a residual branch + shortcut add + ReLU as one kernel (fwd and bwd)
+    "bigdl.fusion.bnstats": True,            # conv followed by BatchNorm: sum / sum of squares from the conv's GEMM epilogue
     "bigdl.fusion.skipgrad": True,           # residual block input: sum its two gradients in a dgrad GEMM epilogue
     "bigdl.fusion.residual": True,           # inference: shortcut add + ReLU inside the last conv's GEMM epilogue
     # misc

@@ -30,7 +30,7 @@ namespace bdl {
 constexpr int BM = 128;
 constexpr int BK = 64;  // 64 bf16 = 128 bytes = one swizzle row
 // dynamic shared memory available to the operand ring: 227 KB minus alignment slack, barriers and the epilogue columns
-constexpr size_t kSmemBudget = 227 * 1024 - 1024 - 512 - 4096;
+constexpr size_t kSmemBudget = 227 * 1024 - 1024 - 512 - 4096 - 2048;   // - alignment, barriers, epi_cols, stat_acc
 constexpr int kMaxStages = 8;
 constexpr int kGemmThreads = 320;   // TMA warp, MMA warp, 8 epilogue warps (two per TMEM lane quadrant)
 constexpr int kEpiThreads = 256;
@@ -70,6 +70,9 @@ struct GemmParams {
   const float* bias;
   const float* col_scale;    // fp8 only: per-output-column dequantisation scale
   const float* out_qscale;   // fp8 only, out_fp32 == 2: device scalar 448 / absmax of the next layer's input
+  float* stat_sums;                // optional [2 * N] fp32: per-column sum and sum of squares of the (bf16-rounded) output are
+                                   // ADDED here by the epilogue — the batch-norm statistics of a following BN without a pass
+                                   // over the output (S/nn/mkldnn/SpatialBatchNormalization.scala needs its own pass)
   const __nv_bfloat16* residual;   // optional [M, N] bf16 tensor (row pitch ldr) added before the ReLU: the shortcut of a
   long long ldr;                   // residual block, so conv + add + ReLU is one pass (reference: Fusion.fusionCAddTable)
   // implicit-GEMM convolution (kConv != 0): the A (fprop/dgrad) or B (wgrad) operand is gathered from an NHWC
@@ -318,6 +321,7 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tmA, const 
   __shared__ __align__(8) uint64_t tempty_bar[2];
   __shared__ uint32_t tmem_base_slot;
   __shared__ __align__(16) float epi_cols[2][2][256];   // [accumulator stage][bias | scale][column of the tile]
+  __shared__ float stat_acc[2][256];                    // [sum | sum of squares][column of the current n tile] (stat_sums)
 
   static_assert(!kTwo || (!kAMN && kConv != 2), "CTA pairs: A must be K-major, no wgrad");
   const uint32_t warp = threadIdx.x >> 5;
@@ -737,11 +741,32 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tmA, const 
     // pair: TMEM drained -> arrive on the LEADER's barrier (remote for the peer CTA)
     const uint32_t tempty_addr[2] = {kTwo ? mapa_shared(smem_u32(&tempty_bar[0]), 0u) : smem_u32(&tempty_bar[0]),
                                      kTwo ? mapa_shared(smem_u32(&tempty_bar[1]), 0u) : smem_u32(&tempty_bar[1])};
+    // column statistics (stat_sums): accumulated per CTA in shared memory across the m tiles of one n tile and flushed
+    // with one atomic per column when the n tile changes / at the end, so the global atomics stay ~#CTA per column
+    const bool do_stats = kTmaStore && !kFp8 && p.stat_sums != nullptr;
+    int stat_nblk = -1;
+    auto stat_flush = [&]() {
+      asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
+      if (stat_nblk >= 0) {
+        const int n = stat_nblk * p.block_n + static_cast<int>(et);
+        if (static_cast<int>(et) < p.block_n && n < p.N) {
+          atomicAdd(p.stat_sums + n, stat_acc[0][et]);
+          atomicAdd(p.stat_sums + p.N + n, stat_acc[1][et]);
+        }
+      }
+      stat_acc[0][et] = 0.f;
+      stat_acc[1][et] = 0.f;
+      asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
+    };
     for (int work = work0; work < total_work; work += work_step) {
       const int split = work / tiles_mn;
       const int rem = work - split * tiles_mn;
       int m_blk, n_blk;
       decode_tile(p, rem, m_blk, n_blk);
+      if (do_stats && n_blk != stat_nblk) {
+        stat_flush();
+        stat_nblk = n_blk;
+      }
       const int nhalves = kDual ? 2 : 1;   // dual: accumulator stage h holds rows [256 m_blk + 128 h, +128)
       for (int hm = 0; hm < nhalves; ++hm) {
       const int tile_row0 = kTwo ? (m_blk * 2 * nhalves + hm * 2 + static_cast<int>(crank)) * BM
@@ -812,6 +837,28 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tmA, const 
           if (lane == 0) {
             tma_store_2d(&tmD, stg, nbase + c, row0);
             tma_store_commit();
+          }
+          if (do_stats) {
+            // lane l sums columns c + 2l, c + 2l + 1 of the 32 staged rows (bank-conflict free: one 128-byte row per step)
+            int rows_valid = p.M - row0;
+            rows_valid = rows_valid > 32 ? 32 : rows_valid;
+            float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+            for (int r = 0; r < rows_valid; ++r) {
+              const uint32_t a = stg + static_cast<uint32_t>(r) * 128u +
+                                 (((lane >> 2) ^ (static_cast<uint32_t>(r) & 7u)) << 4) + ((lane & 3u) << 2);
+              uint32_t w;
+              asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(a));
+              const float v0 = __uint_as_float(w << 16), v1 = __uint_as_float(w & 0xFFFF0000u);
+              s0 += v0;
+              s1 += v1;
+              q0 = fmaf(v0, v0, q0);
+              q1 = fmaf(v1, v1, q1);
+            }
+            const uint32_t col = static_cast<uint32_t>(c) + 2u * lane;
+            atomicAdd(&stat_acc[0][col], s0);
+            atomicAdd(&stat_acc[0][col + 1], s1);
+            atomicAdd(&stat_acc[1][col], q0);
+            atomicAdd(&stat_acc[1][col + 1], q1);
           }
         }
         tc_fence_before();
@@ -887,6 +934,7 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tmA, const 
       if (acc == 0) acc_phase ^= 1u;
       }
     }
+    if (do_stats) stat_flush();
   }
 
   if (kTmaStore && warp >= 2 && lane == 0) tma_store_wait0();   // shared memory must outlive the bulk stores
@@ -922,11 +970,16 @@ gemm_bf16_allgather_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
 // bdl_gemm_bf16 / bdl_conv_igemm_bf16 / bdl_gemm_fp8, so the launch signatures stay as they are.
 static thread_local const void* g_next_residual = nullptr;
 static thread_local long long g_next_ldr = 0;
+static thread_local float* g_next_stats = nullptr;   // bdl_gemm_set_stats: column statistics of the next launch's output
+static thread_local int g_stats_done = 0;            // did the last launch on this thread produce them?
 static void take_residual(GemmParams& p) {
   p.residual = static_cast<const __nv_bfloat16*>(g_next_residual);
   p.ldr = g_next_ldr;
   g_next_residual = nullptr;
   g_next_ldr = 0;
+  p.stat_sums = g_next_stats;
+  g_next_stats = nullptr;
+  g_stats_done = 0;
 }
 
 // bf16, non-accumulating outputs can leave through shared memory + TMA stores (kTmaStore): needs a 16-byte aligned D
@@ -1126,6 +1179,8 @@ extern "C" int bdl_gemm_bf16(const void* A, const void* B, void* D, const float*
   const size_t stage_bytes = static_cast<size_t>(BM) * BK * 2 * (p.dual_m ? 2 : 1) + static_cast<size_t>(p.b_rows) * BK * 2;
   // 512-row pair tiles spend the staging area on a fourth pipeline stage instead (their epilogue is a small share)
   const bool tma_out = !(two && p.dual_m) && want_tma_store(D, ldd, out_fp32, flags, a_mn != 0, num_kb);
+  if (p.stat_sums != nullptr && tma_out && !(flags & BDL_GEMM_RELU)) g_stats_done = 1;   // the staged-output epilogue sums the columns
+  else p.stat_sums = nullptr;
   const size_t budget = kSmemBudget - (tma_out ? kStageOutBytes : 0);
   int stages = static_cast<int>(budget / stage_bytes);
   if (stages > kMaxStages) stages = kMaxStages;
@@ -1364,6 +1419,8 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
   p.bias = bias;
   const size_t stage_bytes = static_cast<size_t>(BM) * BK * 2 * (p.dual_m ? 2 : 1) + static_cast<size_t>(p.b_rows) * BK * 2;
   const bool tma_out = !(two && p.dual_m) && want_tma_store(D, ldd, out_fp32, flags, mode == 2, p.cv_num_kb);
+  if (p.stat_sums != nullptr && tma_out && mode == 0 && !(flags & BDL_GEMM_RELU)) g_stats_done = 1;
+  else p.stat_sums = nullptr;
   const size_t budget = kSmemBudget - (tma_out ? kStageOutBytes : 0);
   int stages = static_cast<int>(budget / stage_bytes);
   if (stages > kMaxStages) stages = kMaxStages;
@@ -1566,6 +1623,15 @@ extern "C" int bdl_gemm_set_pair_mode(int mode) {
   g_pair_mode = mode < 0 ? -1 : (mode > 0 ? 1 : 0);
   return old;
 }
+
+// Arms per-column statistics for the NEXT bdl_gemm_bf16 / bdl_conv_igemm_bf16 on this thread: sums [2 * N] fp32 receives
+// += (sum, sum of squares) of the bf16 output columns. Only kernels that stage the output for TMA stores can do it;
+// bdl_gemm_stats_done() tells whether the launch did (otherwise run bdl_bn_stats on the output).
+extern "C" int bdl_gemm_set_stats(float* sums) {
+  g_next_stats = sums;
+  return BDL_OK;
+}
+extern "C" int bdl_gemm_stats_done() { return g_stats_done; }
 
 extern "C" int bdl_gemm_set_residual(const void* residual_bf16, long long ld) {
   if (residual_bf16 && ld <= 0) return bdl_fail("bdl_gemm_set_residual: row pitch must be positive");

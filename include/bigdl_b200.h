@@ -35,6 +35,10 @@ int bdl_stream_capture_status(void* stream);
 /* Residual operand of the NEXT bdl_gemm_bf16 / bdl_conv_igemm_bf16 (fprop) / bdl_gemm_fp8 launch issued by this host
  * thread: D = act(A*B + bias + residual), residual bf16 [M,N] with row pitch ld (elements). Cleared by that launch.
  * Reference: the conv + sum post-op of S/nn/mkldnn/Fusion.scala (fusionCAddTable). */
+/* Per-column (sum, sum of squares) of the NEXT bf16 GEMM / conv fprop output on this thread, added into sums [2*N] fp32 by
+ * the epilogue (batch-norm statistics without a pass over the output). bdl_gemm_stats_done(): 1 if that launch did it. */
+int bdl_gemm_set_stats(float* sums);
+int bdl_gemm_stats_done(void);
 int bdl_gemm_set_residual(const void* residual_bf16, long long ld);
 /* CTA-pair tiles (tcgen05.mma.cta_group::2 on 2-CTA clusters: 256 rows per MMA, half of the B tile per SM) for GEMM,
  * conv fprop and dgrad: -1 = where the wave heuristic wants them (default; env BDL_GEMM_TWO), 0 = never, 1 = wherever

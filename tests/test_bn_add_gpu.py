@@ -138,3 +138,59 @@ def test_bn_relu_backward_recomputes_the_mask(affine):
     assert _rel(y, ref) < 1e-2 and _rel(x.grad, xf.grad) < 2e-2
     if affine:
         assert _rel(w.grad, wf.grad) < 2e-2 and _rel(b.grad, bf.grad) < 2e-2
+
+
+@pytest.mark.parametrize("M,N,K", [(4096, 64, 192), (5000, 256, 64), (3000, 512, 128), (130, 96, 64)])
+def test_gemm_epilogue_column_statistics(M, N, K):
+    """bdl_gemm_set_stats: the TMA-store epilogue adds per-column sum and sum of squares of the bf16 output."""
+    from bigdl_b200.ops.gemm import gemm_bf16
+    torch.manual_seed(5)
+    a = torch.randn(M, K, device=DEV).bfloat16()
+    b = (torch.randn(N, K, device=DEV) / K ** 0.5).bfloat16()
+    bias = torch.randn(N, device=DEV)
+    stats = torch.zeros(2 * N, device=DEV)
+    out = gemm_bf16(a, b, bias=bias, stats=stats)
+    assert stats._bdl_done
+    o = out.float()
+    assert torch.allclose(stats[:N], o.sum(0), rtol=2e-3, atol=2e-2)
+    assert torch.allclose(stats[N:], (o * o).sum(0), rtol=2e-3, atol=2e-2)
+    # a launch that cannot stage its output (fp32 result) reports that it did not produce them
+    st2 = torch.zeros(2 * N, device=DEV)
+    gemm_bf16(a, b, out_dtype=torch.float32, stats=st2)
+    assert not st2._bdl_done and float(st2.abs().sum()) == 0.0
+
+
+def test_conv_bn_statistics_from_the_epilogue_match_the_separate_pass():
+    from bigdl_b200.nn import fusion
+    from bigdl_b200.nn import layer as L
+    from bigdl_b200.ops import _lib
+    from bigdl_b200.utils import config
+    torch.manual_seed(6)
+    model = (L.Sequential().add(L.SpatialConvolution(16, 64, 3, 3, 1, 1, 1, 1)).add(L.SpatialBatchNormalization(64))
+             .add(L.ReLU()).add(L.SpatialConvolution(64, 128, 1, 1)).add(L.SpatialBatchNormalization(128)).add(L.ReLU())
+             .add(_block(128, 32))).cuda().training()
+    x = torch.randn(8, 16, 20, 20, device=DEV).bfloat16()
+    go = torch.randn(8, 128, 20, 20, device=DEV).bfloat16()
+    res = {}
+    for mode in (False, True):
+        config.set("bigdl.fusion.bnstats", mode)
+        fusion.unfuse(model)
+        fusion.fuse(model)
+        for m in model.all_modules():                       # same running statistics at the start of both runs
+            if "runningMean" in getattr(m, "_buffers", {}):
+                m._buffers["runningMean"].zero_()
+                m._buffers["runningVar"].fill_(1.0)
+        w, g = model.getParameters()
+        g.zero_()
+        before = _lib.LAUNCHES
+        xin = x.clone().requires_grad_(True)
+        with torch.enable_grad():
+            y = model._call(xin)
+        torch.autograd.backward(y, go)
+        rms = [m._buffers["runningMean"].clone() for m in model.all_modules() if "runningMean" in getattr(m, "_buffers", {})]
+        res[mode] = (y.detach().float(), xin.grad.float(), g.clone().float(), rms, _lib.LAUNCHES - before)
+    config.set("bigdl.fusion.bnstats", True)
+    a, b = res[True], res[False]
+    assert _rel(a[0], b[0]) < 5e-3 and _rel(a[1], b[1]) < 2e-2 and _rel(a[2], b[2]) < 2e-2
+    for r1, r0 in zip(a[3], b[3]):
+        assert torch.allclose(r1, r0, rtol=1e-3, atol=1e-4)

@@ -843,16 +843,34 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tmA, const 
             int rows_valid = p.M - row0;
             rows_valid = rows_valid > 32 ? 32 : rows_valid;
             float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
-            for (int r = 0; r < rows_valid; ++r) {
-              const uint32_t a = stg + static_cast<uint32_t>(r) * 128u +
-                                 (((lane >> 2) ^ (static_cast<uint32_t>(r) & 7u)) << 4) + ((lane & 3u) << 2);
-              uint32_t w;
-              asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(a));
-              const float v0 = __uint_as_float(w << 16), v1 = __uint_as_float(w & 0xFFFF0000u);
-              s0 += v0;
-              s1 += v1;
-              q0 = fmaf(v0, v0, q0);
-              q1 = fmaf(v1, v1, q1);
+            // the swizzle repeats every 8 rows: 8 lane-dependent offsets, then constant strides
+            uint32_t off8[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+              off8[k] = stg + static_cast<uint32_t>(k) * 128u + (((lane >> 2) ^ static_cast<uint32_t>(k)) << 4) + ((lane & 3u) << 2);
+            if (rows_valid == 32) {
+#pragma unroll
+              for (int r = 0; r < 32; ++r) {
+                uint32_t w;
+                asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(off8[r & 7] + static_cast<uint32_t>(r >> 3) * 1024u));
+                const float v0 = __uint_as_float(w << 16), v1 = __uint_as_float(w & 0xFFFF0000u);
+                s0 += v0;
+                s1 += v1;
+                q0 = fmaf(v0, v0, q0);
+                q1 = fmaf(v1, v1, q1);
+              }
+            } else {
+              for (int r = 0; r < rows_valid; ++r) {
+                uint32_t w;
+                const uint32_t a = stg + static_cast<uint32_t>(r) * 128u +
+                                   (((lane >> 2) ^ (static_cast<uint32_t>(r) & 7u)) << 4) + ((lane & 3u) << 2);
+                asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(a));
+                const float v0 = __uint_as_float(w << 16), v1 = __uint_as_float(w & 0xFFFF0000u);
+                s0 += v0;
+                s1 += v1;
+                q0 = fmaf(v0, v0, q0);
+                q1 = fmaf(v1, v1, q1);
+              }
             }
             const uint32_t col = static_cast<uint32_t>(c) + 2u * lane;
             atomicAdd(&stat_acc[0][col], s0);

@@ -132,7 +132,8 @@ def test_bucketed_plane_on_real_peers(world):
         assert r["buckets"] >= 3 and r["overlapped"] > 0, r           # the exchange really ran from inside backward
         # all-gather fused into the Linear forward == rows pushed by their owners (up to the arrival order of the split-K
         # red.adds of that 4096-deep GEMM, ~1e-4)
-        assert r["gathered_gemms"] > 0 and r["gather_vs_push"] <= 1e-3, r
+        # (a rank must own at least one whole 128-row tile of the 512-row weight for the fused gather to engage: world <= 4)
+        assert (r["gathered_gemms"] > 0 or world > 4) and r["gather_vs_push"] <= 1e-3, r
         assert r["ranks_identical"] and r["masters_identical"] and r["multi_ranks_identical"], r
         assert r["master_matches_compute"] == 0.0, r
         # same kernels, same order: replaying the captured graph and issuing the step eagerly agree up to the arrival

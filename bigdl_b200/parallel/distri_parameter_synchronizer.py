@@ -85,7 +85,9 @@ class DistriParameterSynchronizer:
             cs = self._comm_stream
             cs.wait_stream(torch.cuda.current_stream(b.grads.device))     # grads were written on the compute stream
             with torch.cuda.stream(cs):
-                if self._p2p_ready(b):
+                if self._nvls_ready(b):
+                    self._nvls_allreduce(b)
+                elif self._p2p_ready(b):
                     self._p2p_allreduce(b)
                 elif self._use_bf16(b):
                     b.payload = b.grads.to(torch.bfloat16)
@@ -127,6 +129,39 @@ class DistriParameterSynchronizer:
                 "local_sync": torch.zeros(2, dtype=torch.int32, device=device),
                 "epoch_dev": torch.zeros(1, dtype=torch.int64, device=device),
                 "rank": dist.get_rank(self.group)}
+
+    # ------------------------------------------------------------------ in-switch (NVLS) data path
+    def _nvls_ready(self, b: _Bucket) -> bool:
+        from ..utils import config
+
+        if not config.get("bigdl.parameter.nvls") or self.compress == "none" or not dist.is_initialized():
+            return False
+        if getattr(self, "_nvls", None) is None:
+            from . import nvls
+
+            self._nvls = False
+            if nvls.multicast_supported(b.grads.device):
+                try:
+                    P = max(bk.offset + bk.length for bk in self.buckets.values())
+                    self._nvls = nvls.NvlsBuffer((P + 7) // 8 * 8, torch.bfloat16, self.group, b.grads.device)
+                except Exception as e:
+                    import logging
+
+                    logging.getLogger("bigdl_b200").warning("NVLS all-reduce unavailable (%s); using peer loads", e)
+        return bool(self._nvls) and b.offset % 8 == 0 and b.length % 8 == 0
+
+    def _nvls_allreduce(self, b: _Bucket):
+        """grads[bucket] = mean over ranks with the sum computed inside the NVSwitch (csrc/nvls.cu)."""
+        from ..ops import _lib
+
+        buf = self._nvls
+        lib = _lib.cuda_lib()
+        g16 = buf.local[b.offset:b.offset + b.length]
+        _lib.check(lib.bdl_compress_grads(b.grads.data_ptr(), g16.data_ptr(), b.length, 0, 0, _lib.stream_ptr()),
+                   "bdl_compress_grads")
+        _lib.count_launch()
+        buf.reduce_to_f32(b.grads.view(-1)[:b.length], offset=b.offset, average=True)
+        b.stats["nvls"] = b.stats.get("nvls", 0) + 1
 
     def _p2p_allreduce(self, b: _Bucket):
         """grads[bucket] = mean over ranks, one kernel: every rank loads the bucket's bf16 slice of every peer over

@@ -36,6 +36,7 @@ _DEFAULTS: dict[str, Any] = {
     # VGG-16 the pushed all-gather hides behind backward, the fused one sits on the forward's critical path
     # (profiles/comm_r2.md), so it is opt-in.
     "bigdl.parameter.gatherGemmMB": 0.0,
+    "bigdl.parameter.nvls": False,           # ParallelOptimizer buckets: all-reduce inside the NVSwitch (multimem.ld_reduce, csrc/nvls.cu)
     "bigdl.parallelOptimizer.iterationPerTime": 1,
     "bigdl.parallelOptimizer.parameterBlocks": 10,
     "bigdl.parallel.bucketMB": 16.0,         # ParallelOptimizer bucket size (fp32 gradient bytes)

@@ -322,6 +322,13 @@ int bdl_attention_bwd(const void* Q, long long q_sb, long long q_sl, const void*
                       long long dv_sb, long long dv_sl, int B, int heads, int Lq, int Lk, int D, float scale,
                       int causal, void* stream);
 
+/* ---- NVLS (in-switch) all-reduce over a MULTICAST address (csrc/nvls.cu): multimem.ld_reduce / multimem.st. `mc` is the
+ *      multicast mapping of a symmetric buffer (same offset on every rank); callers bracket each call with a group barrier.
+ *      Reference: the aggregate step of S/utils/DistriParameterSynchronizer.scala:234-356. */
+int bdl_nvls_reduce_bf16_to_f32(const void* mc, float* out, long long n, float scale, void* stream);
+int bdl_nvls_allreduce_bf16_inplace(void* mc, long long n, int rank, int world, void* stream);
+int bdl_nvls_allreduce_f32(const void* mc, float* out, long long n, float scale, void* stream);
+
 /* ---- fp32 / fp64 BLAS + vector math for Tensor[Float] / Tensor[Double] (csrc/blas_vml.cu; host twins bdlh_* in
  *      csrc/host/blas_vml.cpp). Reference: core/mkl2017-xeon-blas/src/main/c/mkl.c (vsAdd ... vsgemm, vd*), called from
  *      S/tensor/TensorNumeric.scala:253-420. Column-major like BLAS; offsets are folded into the pointers.

@@ -221,6 +221,11 @@ class DefinitionLoader:
         return DefinitionLoader.from_config(json.loads(s))
 
     @staticmethod
+    def from_kmodel(kmodel):
+        """From a live Keras-1.2.2 model object (anything with ``to_json()``), as ``with_bigdl_backend`` does."""
+        return DefinitionLoader.from_json_str(kmodel.to_json())
+
+    @staticmethod
     def from_json_path(path: str):
         with open(path) as f:
             return DefinitionLoader.from_json_str(f.read())
@@ -375,6 +380,16 @@ class WeightLoader:
                 raise ValueError(f"layer {name} not found in the model")
             WeightLoader._apply(layer, arrays)
         return model
+
+    @staticmethod
+    def load_weights_from_kmodel(model, kmodel, by_name: bool = False):
+        """Copy the weights of a live Keras model (``kmodel.layers[i].name`` / ``.get_weights()``)."""
+        weights = {}
+        for layer in kmodel.layers:
+            arrays = layer.get_weights()
+            if arrays:
+                weights[layer.name] = [np.asarray(a) for a in arrays]
+        return WeightLoader.load_weights_from_arrays(model, weights, by_name)
 
     @staticmethod
     def load_weights_from_hdf5(model, hdf5_path: str, by_name: bool = False):

@@ -83,3 +83,19 @@ def test_dlframes_image_example():
 def test_tensorflow_load_save_example():
     diff, acc, frozen = _load("tensorflow_load_save").main([])
     assert diff < 1e-4 and acc > 0.8 and frozen
+
+
+def test_onnx_load_example():
+    assert _load("onnx_load").main([]) < 1e-5
+
+
+def test_compat_example_and_model_modules_import():
+    import importlib
+    for name in ("bigdl.examples.imageframe.inception_validation", "bigdl.examples.onnx.load_onnx_resnet",
+                 "bigdl.examples.keras.keras_utils", "bigdl.examples.lenet.lenet", "bigdl.models.ml_pipeline.dl_classifier",
+                 "bigdl.models.utils.model_broadcast", "bigdl.models.textclassifier.textclassifier"):
+        importlib.import_module(name)
+    from bigdl.models.textclassifier.textclassifier import analyze_texts, build_model, pad
+    import torch
+    assert analyze_texts([("the cat the dog", 1), ("a cat", 2)])[0] == ("the", (1, 2)) and pad([1], 0, 3) == [1, 0, 0]
+    assert tuple(build_model(4, "gru", 16, 12).forward(torch.randn(2, 12, 16)).shape) == (2, 4)

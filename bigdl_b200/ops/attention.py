@@ -19,6 +19,12 @@ _lib.declare("bdl_attention_fwd", [_P, _L, _L, _P, _L, _L, _P, _L, _L, _P, _L, _
                                    _I, _F, _I, _P])
 _lib.declare("bdl_attention_bwd", [_P, _L, _L, _P, _L, _L, _P, _L, _L, _P, _L, _L, _P, _L, _L, _P, _P, _P, _L, _L, _L, _P, _L,
                                    _L, _P, _L, _L, _P, _L, _L, _I, _I, _I, _I, _I, _F, _I, _P])
+_lib.declare("bdl_attention_set_two_mode", [_I])
+
+
+def set_two_tile_mode(mode: int) -> int:
+    """-1 heuristic / 0 one query tile per CTA / 1 two tiles per CTA wherever Lq > 128; returns the previous mode."""
+    return int(_lib.cuda_lib().bdl_attention_set_two_mode(int(mode)))
 
 
 def supported(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int) -> bool:

@@ -13,6 +13,7 @@
 // Output is written straight in the [B, Lq, heads * D] "combined heads" layout, plus the row log-sum-exp for backward.
 #include <cuda_bf16.h>
 #include <math.h>
+#include <stdlib.h>
 
 #include "bigdl_b200.h"
 #include "host_common.h"
@@ -39,6 +40,129 @@ struct __align__(8) AttnBars {
   uint64_t q_full, k_full, k_empty, v_full, v_empty, s_full, p_full, o_full, o_free;
   uint32_t tmem_base;
 };
+
+// One softmax / output thread: owns query row q0 + r (TMEM lane r of its tile) for all nkv key tiles. bar_s: S tile ready,
+// bar_p: P written (count 128), bar_o: partial O ready, bar_f: partial O consumed (count 128).
+template <int kD>
+__device__ __forceinline__ void attn_row_worker(const AttnArgs& a, int b, int h, int q0, int nkv, int off, int r,
+                                                uint32_t lane_base, uint32_t tS, uint32_t tO, uint32_t sP,
+                                                uint32_t bar_s, uint32_t bar_p, uint32_t bar_o, uint32_t bar_f) {
+    // ------------------------------------------------------------------ softmax + output accumulation (one row each)
+    const int q = q0 + r;
+    constexpr float kLog2e = 1.4426950408889634f;
+    const float sl2 = a.scale * kLog2e;
+    const float* brow = nullptr;
+    if (a.bias != nullptr && q < a.Lq) brow = a.bias + b * a.bias_sb + h * a.bias_sh + static_cast<long long>(q) * a.bias_sq;
+    const int key_limit = a.causal ? min(a.Lk, q + off + 1) : a.Lk;   // keys [0, key_limit) are visible to this row
+    float m_run = -INFINITY, l_run = 0.f;
+    float o_acc[kD];
+#pragma unroll
+    for (int c = 0; c < kD; ++c) o_acc[c] = 0.f;
+
+    for (int j = 0; j < nkv; ++j) {
+      const uint32_t ph = static_cast<uint32_t>(j) & 1u;
+      const int k0 = j * kTileK;
+      mbar_wait(bar_s, ph);
+      tc_fence_after();
+      // Interior tiles without a bias tensor need no masks and no per-element scale in the max pass: the softmax warps
+      // are bound by instruction issue (one thread per row), so the common case is kept to ~4 instructions per logit.
+      const bool plain = (brow == nullptr) && (k0 + kTileK <= key_limit);
+      float m_tile = -INFINITY;
+#pragma unroll 1
+      for (int c0 = 0; c0 < kTileK; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld_32(tS + lane_base + static_cast<uint32_t>(c0), v);    // warp-collective: never inside a divergent branch
+        tmem_ld_wait();
+        if (plain) {
+#pragma unroll
+          for (int e = 0; e < 32; e += 2)
+            m_tile = fmaxf(m_tile, fmaxf(__uint_as_float(v[e]), __uint_as_float(v[e + 1])));
+        } else {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) {
+            const int key = k0 + c0 + e;
+            float s = __uint_as_float(v[e]) * sl2;
+            if (brow != nullptr && key < a.Lk) s += __ldg(brow + key) * kLog2e;
+            if (key < key_limit) m_tile = fmaxf(m_tile, s);
+          }
+        }
+      }
+      if (plain) m_tile *= sl2;                              // scale > 0: max commutes with it
+      const float m_new = fmaxf(m_run, m_tile);
+      const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
+      const float alpha = ex2_approx(m_run - m_use);        // m_run = -inf -> 0
+      // pass 2: p = 2^(s - m), row sum, P tile to shared memory
+      float l_tile = 0.f;
+#pragma unroll 1
+      for (int c0 = 0; c0 < kTileK; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld_32(tS + lane_base + static_cast<uint32_t>(c0), v);
+        tmem_ld_wait();
+        float pv[32];
+        if (plain) {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) {
+            pv[e] = ex2_approx(fmaf(__uint_as_float(v[e]), sl2, -m_use));
+            l_tile += pv[e];
+          }
+        } else {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) {
+            const int key = k0 + c0 + e;
+            float s = __uint_as_float(v[e]) * sl2;
+            if (brow != nullptr && key < a.Lk) s += __ldg(brow + key) * kLog2e;
+            pv[e] = key < key_limit ? ex2_approx(s - m_use) : 0.f;
+            l_tile += pv[e];
+          }
+        }
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const int col = c0 + 8 * g;                       // 8 keys = one 16-byte chunk of the swizzled row
+          const uint32_t chunk = static_cast<uint32_t>((col & 63) >> 3);
+          const uint32_t addr = sP + static_cast<uint32_t>(col >> 6) * kSub + static_cast<uint32_t>(r) * 128u +
+                                ((chunk ^ (static_cast<uint32_t>(r) & 7u)) << 4);
+          const uint32_t w0 = pack_bf16x2(pv[8 * g + 0], pv[8 * g + 1]), w1 = pack_bf16x2(pv[8 * g + 2], pv[8 * g + 3]);
+          const uint32_t w2 = pack_bf16x2(pv[8 * g + 4], pv[8 * g + 5]), w3 = pack_bf16x2(pv[8 * g + 6], pv[8 * g + 7]);
+          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
+        }
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      mbar_arrive(bar_p);
+      l_run = l_run * alpha + l_tile;
+      m_run = m_new;
+      // fold the partial output of this tile
+      mbar_wait(bar_o, ph);
+      tc_fence_after();
+#pragma unroll
+      for (int c0 = 0; c0 < kD; c0 += 16) {
+        uint32_t v[16];
+        tmem_ld_16(tO + lane_base + static_cast<uint32_t>(c0), v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int e = 0; e < 16; ++e) o_acc[c0 + e] = fmaf(o_acc[c0 + e], alpha, __uint_as_float(v[e]));
+      }
+      tc_fence_before();
+      mbar_arrive(bar_f);
+    }
+
+    if (q < a.Lq) {
+      const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
+      __nv_bfloat16* orow = a.O + b * a.o_sb + static_cast<long long>(q) * a.o_sl + h * kD;
+#pragma unroll
+      for (int c0 = 0; c0 < kD; c0 += 8) {
+        uint4 w;
+        w.x = pack_bf16x2(o_acc[c0 + 0] * inv, o_acc[c0 + 1] * inv);
+        w.y = pack_bf16x2(o_acc[c0 + 2] * inv, o_acc[c0 + 3] * inv);
+        w.z = pack_bf16x2(o_acc[c0 + 4] * inv, o_acc[c0 + 5] * inv);
+        w.w = pack_bf16x2(o_acc[c0 + 6] * inv, o_acc[c0 + 7] * inv);
+        *reinterpret_cast<uint4*>(orow + c0) = w;
+      }
+      if (a.lse != nullptr)
+        a.lse[(static_cast<long long>(b) * a.heads + h) * a.Lq + q] =
+            l_run > 0.f ? (m_run + log2f(l_run)) * 0.6931471805599453f : -INFINITY;
+    }
+  }
 
 template <int kD>
 __global__ void __launch_bounds__(kAttThreads, kD == 64 ? 2 : 1)
@@ -136,122 +260,9 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     }
   } else {
     // ------------------------------------------------------------------ softmax + output accumulation (one row each)
-    const int r = static_cast<int>(threadIdx.x);          // 0..127 = TMEM lane = query row inside the tile
-    const int q = q0 + r;
-    const uint32_t lane_base = (warp * 32u) << 16;
-    constexpr float kLog2e = 1.4426950408889634f;
-    const float sl2 = a.scale * kLog2e;
-    const float* brow = nullptr;
-    if (a.bias != nullptr && q < a.Lq) brow = a.bias + b * a.bias_sb + h * a.bias_sh + static_cast<long long>(q) * a.bias_sq;
-    const int key_limit = a.causal ? min(a.Lk, q + off + 1) : a.Lk;   // keys [0, key_limit) are visible to this row
-    float m_run = -INFINITY, l_run = 0.f;
-    float o_acc[kD];
-#pragma unroll
-    for (int c = 0; c < kD; ++c) o_acc[c] = 0.f;
-
-    for (int j = 0; j < nkv; ++j) {
-      const uint32_t ph = static_cast<uint32_t>(j) & 1u;
-      const int k0 = j * kTileK;
-      mbar_wait(smem_u32(&bars->s_full), ph);
-      tc_fence_after();
-      // Interior tiles without a bias tensor need no masks and no per-element scale in the max pass: the softmax warps
-      // are bound by instruction issue (one thread per row), so the common case is kept to ~4 instructions per logit.
-      const bool plain = (brow == nullptr) && (k0 + kTileK <= key_limit);
-      float m_tile = -INFINITY;
-#pragma unroll 1
-      for (int c0 = 0; c0 < kTileK; c0 += 32) {
-        uint32_t v[32];
-        tmem_ld_32(tS + lane_base + static_cast<uint32_t>(c0), v);    // warp-collective: never inside a divergent branch
-        tmem_ld_wait();
-        if (plain) {
-#pragma unroll
-          for (int e = 0; e < 32; e += 2)
-            m_tile = fmaxf(m_tile, fmaxf(__uint_as_float(v[e]), __uint_as_float(v[e + 1])));
-        } else {
-#pragma unroll
-          for (int e = 0; e < 32; ++e) {
-            const int key = k0 + c0 + e;
-            float s = __uint_as_float(v[e]) * sl2;
-            if (brow != nullptr && key < a.Lk) s += __ldg(brow + key) * kLog2e;
-            if (key < key_limit) m_tile = fmaxf(m_tile, s);
-          }
-        }
-      }
-      if (plain) m_tile *= sl2;                              // scale > 0: max commutes with it
-      const float m_new = fmaxf(m_run, m_tile);
-      const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
-      const float alpha = ex2_approx(m_run - m_use);        // m_run = -inf -> 0
-      // pass 2: p = 2^(s - m), row sum, P tile to shared memory
-      float l_tile = 0.f;
-#pragma unroll 1
-      for (int c0 = 0; c0 < kTileK; c0 += 32) {
-        uint32_t v[32];
-        tmem_ld_32(tS + lane_base + static_cast<uint32_t>(c0), v);
-        tmem_ld_wait();
-        float pv[32];
-        if (plain) {
-#pragma unroll
-          for (int e = 0; e < 32; ++e) {
-            pv[e] = ex2_approx(fmaf(__uint_as_float(v[e]), sl2, -m_use));
-            l_tile += pv[e];
-          }
-        } else {
-#pragma unroll
-          for (int e = 0; e < 32; ++e) {
-            const int key = k0 + c0 + e;
-            float s = __uint_as_float(v[e]) * sl2;
-            if (brow != nullptr && key < a.Lk) s += __ldg(brow + key) * kLog2e;
-            pv[e] = key < key_limit ? ex2_approx(s - m_use) : 0.f;
-            l_tile += pv[e];
-          }
-        }
-#pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          const int col = c0 + 8 * g;                       // 8 keys = one 16-byte chunk of the swizzled row
-          const uint32_t chunk = static_cast<uint32_t>((col & 63) >> 3);
-          const uint32_t addr = sP + static_cast<uint32_t>(col >> 6) * kSub + static_cast<uint32_t>(r) * 128u +
-                                ((chunk ^ (static_cast<uint32_t>(r) & 7u)) << 4);
-          const uint32_t w0 = pack_bf16x2(pv[8 * g + 0], pv[8 * g + 1]), w1 = pack_bf16x2(pv[8 * g + 2], pv[8 * g + 3]);
-          const uint32_t w2 = pack_bf16x2(pv[8 * g + 4], pv[8 * g + 5]), w3 = pack_bf16x2(pv[8 * g + 6], pv[8 * g + 7]);
-          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
-        }
-      }
-      fence_proxy_async_smem();
-      tc_fence_before();
-      mbar_arrive(smem_u32(&bars->p_full));
-      l_run = l_run * alpha + l_tile;
-      m_run = m_new;
-      // fold the partial output of this tile
-      mbar_wait(smem_u32(&bars->o_full), ph);
-      tc_fence_after();
-#pragma unroll
-      for (int c0 = 0; c0 < kD; c0 += 16) {
-        uint32_t v[16];
-        tmem_ld_16(tO + lane_base + static_cast<uint32_t>(c0), v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int e = 0; e < 16; ++e) o_acc[c0 + e] = fmaf(o_acc[c0 + e], alpha, __uint_as_float(v[e]));
-      }
-      tc_fence_before();
-      mbar_arrive(smem_u32(&bars->o_free));
-    }
-
-    if (q < a.Lq) {
-      const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
-      __nv_bfloat16* orow = a.O + b * a.o_sb + static_cast<long long>(q) * a.o_sl + h * kD;
-#pragma unroll
-      for (int c0 = 0; c0 < kD; c0 += 8) {
-        uint4 w;
-        w.x = pack_bf16x2(o_acc[c0 + 0] * inv, o_acc[c0 + 1] * inv);
-        w.y = pack_bf16x2(o_acc[c0 + 2] * inv, o_acc[c0 + 3] * inv);
-        w.z = pack_bf16x2(o_acc[c0 + 4] * inv, o_acc[c0 + 5] * inv);
-        w.w = pack_bf16x2(o_acc[c0 + 6] * inv, o_acc[c0 + 7] * inv);
-        *reinterpret_cast<uint4*>(orow + c0) = w;
-      }
-      if (a.lse != nullptr)
-        a.lse[(static_cast<long long>(b) * a.heads + h) * a.Lq + q] =
-            l_run > 0.f ? (m_run + log2f(l_run)) * 0.6931471805599453f : -INFINITY;
-    }
+    attn_row_worker<kD>(a, b, h, q0, nkv, off, static_cast<int>(threadIdx.x), (warp * 32u) << 16, tS, tO, sP,
+                        smem_u32(&bars->s_full), smem_u32(&bars->p_full), smem_u32(&bars->o_full),
+                        smem_u32(&bars->o_free));
   }
   tc_fence_before();
   __syncthreads();
@@ -261,10 +272,172 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Two query tiles per CTA (256 queries): warps 0-3 own tile 0, warps 4-7 tile 1, warp 8 = TMA, warp 9 = MMA. K_j / V_j
+// are fetched once for both tiles, and while one group runs its softmax the tensor core works for the other
+// (S1_j during softmax0_j, PV0_j during softmax1_j): inside one CTA instead of across two co-resident CTAs, with 8
+// softmax warps per SM either way. TMEM: S0 [0,128) | S1 [128,256) | O0 [256,256+D) | O1 [256+D,256+2D).
+constexpr int kAtt2Threads = 320;
+
+struct __align__(8) Attn2Bars {
+  uint64_t q_full, k_full, k_empty, v_full, v_empty;
+  uint64_t s_full[2], p_full[2], o_full[2], o_free[2];
+  uint32_t tmem_base;
+};
+
+template <int kD>
+__global__ void __launch_bounds__(kAtt2Threads, 1)
+attention_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                      const __grid_constant__ CUtensorMap tmV, const AttnArgs a) {
+  constexpr int kDS = kD / 64;
+  constexpr uint32_t kOpBytes = kDS * kSub;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const uint32_t sQ0 = smem_u32(smem), sQ1 = sQ0 + kOpBytes, sK = sQ1 + kOpBytes, sV = sK + kOpBytes;
+  const uint32_t sP0 = sV + kOpBytes, sP1 = sP0 + 2 * kSub;
+  Attn2Bars* bars = reinterpret_cast<Attn2Bars*>(smem + 4 * kOpBytes + 4 * kSub);
+  const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q0 = blockIdx.x * 2 * kTileQ, h = blockIdx.y, b = blockIdx.z;
+  const int off = a.Lk - a.Lq;
+  const int nkv_all = (a.Lk + kTileK - 1) / kTileK;
+  int nkv_g[2];
+#pragma unroll
+  for (int g = 0; g < 2; ++g) {
+    const int qg = q0 + g * kTileQ;
+    int n = qg < a.Lq ? nkv_all : 0;                 // a second tile past the end of the sequence does nothing
+    if (a.causal && n > 0) {
+      const int last_key = min(a.Lk - 1, qg + kTileQ - 1 + off);
+      n = last_key < 0 ? 0 : min(n, last_key / kTileK + 1);
+    }
+    nkv_g[g] = n;
+  }
+  const int nkv = max(nkv_g[0], nkv_g[1]);
+
+  if (threadIdx.x == 0) {
+    mbar_init(smem_u32(&bars->q_full), 1);
+    mbar_init(smem_u32(&bars->k_full), 1);
+    mbar_init(smem_u32(&bars->k_empty), 1);
+    mbar_init(smem_u32(&bars->v_full), 1);
+    mbar_init(smem_u32(&bars->v_empty), 1);
+    for (int g = 0; g < 2; ++g) {
+      mbar_init(smem_u32(&bars->s_full[g]), 1);
+      mbar_init(smem_u32(&bars->p_full[g]), 128);
+      mbar_init(smem_u32(&bars->o_full[g]), 1);
+      mbar_init(smem_u32(&bars->o_free[g]), 128);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 9) tmem_alloc<512>(smem_u32(&bars->tmem_base));
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = bars->tmem_base;
+
+  if (warp == 8) {
+    if (lane == 0 && nkv > 0) {
+      tma_prefetch_desc(&tmQ);
+      tma_prefetch_desc(&tmK);
+      tma_prefetch_desc(&tmV);
+      mbar_expect_tx(smem_u32(&bars->q_full), 2 * kOpBytes);
+      for (int s = 0; s < kDS; ++s) {
+        tma_load_3d(sQ0 + s * kSub, &tmQ, smem_u32(&bars->q_full), h * kD + 64 * s, q0, b);
+        tma_load_3d(sQ1 + s * kSub, &tmQ, smem_u32(&bars->q_full), h * kD + 64 * s, q0 + kTileQ, b);
+      }
+      for (int j = 0; j < nkv; ++j) {
+        const uint32_t ph = static_cast<uint32_t>(j) & 1u;
+        if (j > 0) mbar_wait(smem_u32(&bars->k_empty), ph ^ 1u);
+        mbar_expect_tx(smem_u32(&bars->k_full), kOpBytes);
+        for (int s = 0; s < kDS; ++s)
+          tma_load_3d(sK + s * kSub, &tmK, smem_u32(&bars->k_full), h * kD + 64 * s, j * kTileK, b);
+        if (j > 0) mbar_wait(smem_u32(&bars->v_empty), ph ^ 1u);
+        mbar_expect_tx(smem_u32(&bars->v_full), kOpBytes);
+        for (int s = 0; s < kDS; ++s)
+          tma_load_3d(sV + s * kSub, &tmV, smem_u32(&bars->v_full), h * kD + 64 * s, j * kTileK, b);
+      }
+    }
+  } else if (warp == 9) {
+    if (lane == 0 && nkv > 0) {
+      const uint32_t idesc_s = (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(kTileK >> 3) << 17) |
+                               (static_cast<uint32_t>(kTileQ >> 4) << 24);
+      const uint32_t idesc_o = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 16) | (static_cast<uint32_t>(kD >> 3) << 17) |
+                               (static_cast<uint32_t>(kTileQ >> 4) << 24);
+      const uint32_t sQ[2] = {sQ0, sQ1}, sP[2] = {sP0, sP1};
+      const uint32_t tS[2] = {tmem, tmem + 128u}, tO[2] = {tmem + 256u, tmem + 256u + kD};
+      mbar_wait(smem_u32(&bars->q_full), 0);
+      for (int j = 0; j < nkv; ++j) {
+        const uint32_t ph = static_cast<uint32_t>(j) & 1u;
+        mbar_wait(smem_u32(&bars->k_full), ph);
+        tc_fence_after();
+        // S_g = Q_g K_j^T for both tiles (the S buffer of tile g is free: its PV of step j-1 was issued after P_g(j-1))
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {
+          if (j >= nkv_g[g]) continue;
+#pragma unroll
+          for (int kk = 0; kk < kD / 16; ++kk) {
+            const uint32_t o = static_cast<uint32_t>(kk / 4) * kSub + static_cast<uint32_t>(kk % 4) * 32u;
+            umma_f16(tS[g], make_smem_desc_sw128(sQ[g] + o, 16u, 1024u), make_smem_desc_sw128(sK + o, 16u, 1024u),
+                     idesc_s, kk > 0 ? 1u : 0u);
+          }
+          umma_commit(smem_u32(&bars->s_full[g]));
+        }
+        umma_commit(smem_u32(&bars->k_empty));
+        mbar_wait(smem_u32(&bars->v_full), ph);
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {
+          if (j >= nkv_g[g]) continue;
+          mbar_wait(smem_u32(&bars->p_full[g]), ph);
+          if (j > 0) mbar_wait(smem_u32(&bars->o_free[g]), ph ^ 1u);
+          tc_fence_after();
+#pragma unroll
+          for (int kk = 0; kk < kTileK / 16; ++kk) {
+            const uint32_t pa = sP[g] + static_cast<uint32_t>(kk / 4) * kSub + static_cast<uint32_t>(kk % 4) * 32u;
+            umma_f16(tO[g], make_smem_desc_sw128(pa, 16u, 1024u),
+                     make_smem_desc_sw128(sV + static_cast<uint32_t>(kk) * 2048u, kSub, 1024u), idesc_o,
+                     kk > 0 ? 1u : 0u);
+          }
+          umma_commit(smem_u32(&bars->o_full[g]));
+        }
+        umma_commit(smem_u32(&bars->v_empty));
+      }
+    }
+  } else {
+    const int g = static_cast<int>(warp >> 2);                      // 0 or 1: which query tile
+    const int r = static_cast<int>(threadIdx.x) - g * 128;
+    attn_row_worker<kD>(a, b, h, q0 + g * kTileQ, nkv_g[g], off, r, ((warp & 3u) * 32u) << 16,
+                        tmem + static_cast<uint32_t>(g) * 128u, tmem + 256u + static_cast<uint32_t>(g) * kD,
+                        g ? sP1 : sP0, smem_u32(&bars->s_full[g]), smem_u32(&bars->p_full[g]),
+                        smem_u32(&bars->o_full[g]), smem_u32(&bars->o_free[g]));
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 9) {
+    tc_fence_after();
+    tmem_dealloc<512>(tmem);
+  }
+}
+
+// 1: two query tiles per CTA wherever Lq > 128; 0 / -1 (default): one tile per CTA, two CTAs per SM
+static int g_attn_two_mode = [] { const char* e = getenv("BDL_ATTN_TWO"); return e ? atoi(e) : -1; }();
+
 template <int kD>
 static int launch_attention(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnArgs& a,
                             cudaStream_t s) {
   const size_t smem = 3 * (kD / 64) * kSub + 2 * kSub + sizeof(AttnBars) + 1024;
+  const int two_mode = g_attn_two_mode;
+  // two query tiles per CTA when there are at least two and the halved grid still covers the SMs
+  const long long ctas2 = static_cast<long long>((a.Lq + 2 * kTileQ - 1) / (2 * kTileQ)) * a.heads * a.B;
+  // Measured (profiles/attention_r2.md): the 256-query CTA is 8-20 % SLOWER than two co-resident 128-query CTAs (the two
+  // softmax groups wait on one MMA issuer and one K/V stage), so it only runs when asked for.
+  (void)ctas2;
+  if (two_mode == 1 && a.Lq > kTileQ) {
+    const size_t smem2 = 4 * (kD / 64) * kSub + 4 * kSub + sizeof(Attn2Bars) + 1024;
+    auto k2 = attention_fwd2_kernel<kD>;
+    cudaError_t e2 = cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem2));
+    if (e2 != cudaSuccess) return bdl_fail_cuda("cudaFuncSetAttribute(attention_fwd2)", e2);
+    dim3 grid2((a.Lq + 2 * kTileQ - 1) / (2 * kTileQ), a.heads, a.B);
+    k2<<<grid2, kAtt2Threads, smem2, s>>>(tq, tk, tv, a);
+    return bdl_check_launch("attention_fwd2_kernel");
+  }
   auto kfn = attention_fwd_kernel<kD>;
   cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
   if (e != cudaSuccess) return bdl_fail_cuda("cudaFuncSetAttribute(attention_fwd)", e);
@@ -274,6 +447,12 @@ static int launch_attention(const CUtensorMap& tq, const CUtensorMap& tk, const 
 }
 
 }  // namespace bdl
+
+extern "C" int bdl_attention_set_two_mode(int mode) {
+  const int old = bdl::g_attn_two_mode;
+  bdl::g_attn_two_mode = mode < 0 ? -1 : (mode > 0 ? 1 : 0);
+  return old;
+}
 
 // Q [B, Lq, heads*D], K / V [B, Lk, heads*D] bf16 with row pitches q_sl / k_sl / v_sl and batch pitches *_sb (elements);
 // O like Q. bias: fp32, strides in elements over (batch, head, query), key stride 1, 0 = broadcast; null = none.

@@ -313,6 +313,9 @@ int bdl_attention_fwd(const void* Q, long long q_sb, long long q_sl, const void*
                       const void* V, long long v_sb, long long v_sl, const float* bias, long long bias_sb,
                       long long bias_sh, long long bias_sq, void* O, long long o_sb, long long o_sl, float* lse, int B,
                       int heads, int Lq, int Lk, int D, float scale, int causal, void* stream);
+/* forward variant: -1 = heuristic (two 128-query tiles per CTA when the grid still fills the SMs), 0 = one tile per CTA,
+ * 1 = two tiles wherever Lq > 128. Returns the previous mode. */
+int bdl_attention_set_two_mode(int mode);
 /* gradients w.r.t. Q, K, V (csrc/attention_bwd.cu): probabilities recomputed from lse; delta = [B,heads,Lq] fp32 scratch */
 int bdl_attention_bwd(const void* Q, long long q_sb, long long q_sl, const void* K, long long k_sb, long long k_sl,
                       const void* V, long long v_sb, long long v_sl, const void* O, long long o_sb, long long o_sl,

@@ -28,6 +28,24 @@ def test_forward_matches_fp32(B, Lq, Lk, heads, D):
     assert _rel(out, ref) < 1.5e-2
 
 
+@pytest.mark.parametrize("B,Lq,Lk,heads,D,causal", [(2, 256, 256, 2, 64, False), (1, 300, 300, 3, 64, True),
+                                                    (2, 130, 400, 2, 64, False), (1, 512, 512, 2, 128, True),
+                                                    (1, 257, 140, 2, 128, False)])
+def test_two_query_tiles_per_cta(B, Lq, Lk, heads, D, causal):
+    """The 256-query CTA (two softmax groups ping-ponging on one tensor core) against fp32 and against the 1-tile kernel."""
+    q, k, v = _qkv(B, Lq, Lk, heads, D, seed=9)
+    old = A.set_two_tile_mode(1)
+    try:
+        out2 = A.attention(q, k, v, None, heads, causal=causal)
+        A.set_two_tile_mode(0)
+        out1 = A.attention(q, k, v, None, heads, causal=causal)
+    finally:
+        A.set_two_tile_mode(old)
+    ref = A.attention_reference(q, k, v, None, heads, causal=causal)
+    assert _rel(out2, ref) < 1.5e-2 and _rel(out1, ref) < 1.5e-2
+    assert _rel(out2, out1) < 2e-3
+
+
 @pytest.mark.parametrize("kind", ["padding", "full", "causal_bias", "causal_flag"])
 def test_bias_and_masks(kind):
     B, L, heads, D = 2, 200, 4, 64

@@ -256,3 +256,34 @@ def test_sparse_tensor_blas_and_math():
     assert abs(sp.sum() - float(d.sum())) < 1e-5
     small = sp.clone().resize([3, 7])
     assert torch.equal(small.to_dense().t, d[:3])
+
+
+def test_dnn_storage_native_pool():
+    """DnnStorage / DnnTensor on the host: aligned native blocks, explicit release, leak accounting, reuse
+    (S/tensor/DnnStorage.scala:99-125, DnnTensorSpec)."""
+    from bigdl_b200.tensor.dnn import DnnStorage, DnnTensor
+    base = DnnStorage.stats()
+    a, b = DnnTensor(4, 5, device="cpu"), DnnTensor([4, 5], device="cpu")
+    assert a.storageAddress() % 64 == 0 and a.size() == [4, 5] and a.nElement() == 20
+    a.copy(torch.ones(4, 5))
+    b.copy(a).axpby(2.0, 0.5, a)                         # b = 2a + 0.5b
+    assert float(b.dense().t.sum()) == 50.0
+    assert DnnStorage.stats()["live_blocks"] == base["live_blocks"] + 2
+    a.release()
+    a.release()                                          # idempotent
+    with pytest.raises(RuntimeError):
+        a.zero()
+    b.release()
+    mid = DnnStorage.stats()
+    assert mid["live_blocks"] == base["live_blocks"]     # nothing leaked
+    c = DnnTensor(20, device="cpu")                      # same size class: served from the cache
+    assert DnnStorage.stats()["reused"] == mid["reused"] + 1
+    c.release()
+    s = DnnStorage(8)
+    s.copy(torch.arange(8.))
+    assert s.tensor().tolist() == list(range(8))
+    with pytest.raises(NotImplementedError):
+        s.fill(1.0, 0, 8)
+    s.release()
+    with pytest.raises(RuntimeError):
+        s.tensor()

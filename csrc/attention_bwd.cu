@@ -178,6 +178,7 @@ attention_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     const float* brow = nullptr;
     if (a.bias != nullptr && live) brow = a.bias + b * a.bias_sb + h * a.bias_sh + static_cast<long long>(q) * a.bias_sq;
     const int key_limit = a.causal ? min(a.Lk, q + off + 1) : a.Lk;
+    const bool bvec = brow != nullptr && (reinterpret_cast<uintptr_t>(brow) & 15u) == 0;
     const long long stat = (static_cast<long long>(b) * a.heads + h) * a.Lq + q;
     float lse2 = 0.f, delta = 0.f;
     if (live) {
@@ -218,12 +219,26 @@ attention_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           }
         } else {
 #pragma unroll
-          for (int e = 0; e < 16; ++e) {
-            const int key = k0 + c0 + e;
-            float s = __uint_as_float(sv[e]) * sl2;
-            if (brow != nullptr && key < a.Lk) s += __ldg(brow + key) * kL2e;
-            const float p = (live && key < key_limit) ? ex2_approx(s - lse2) : 0.f;
-            ds[e] = p * fmaf(__uint_as_float(pv[e]), a.scale, nds);
+          for (int e4 = 0; e4 < 16; e4 += 4) {
+            float bb[4] = {0.f, 0.f, 0.f, 0.f};
+            const int kb = k0 + c0 + e4;
+            if (brow != nullptr) {
+              if (bvec && kb + 3 < a.Lk) {
+                const float4 t = __ldg(reinterpret_cast<const float4*>(brow + kb));
+                bb[0] = t.x; bb[1] = t.y; bb[2] = t.z; bb[3] = t.w;
+              } else {
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                  if (kb + u < a.Lk) bb[u] = __ldg(brow + kb + u);
+              }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int e = e4 + u;
+              const float s = fmaf(bb[u], kL2e, __uint_as_float(sv[e]) * sl2);
+              const float p = (live && kb + u < key_limit) ? ex2_approx(s - lse2) : 0.f;
+              ds[e] = p * fmaf(__uint_as_float(pv[e]), a.scale, nds);
+            }
           }
         }
         store_kmajor8(sDS, r, c0, ds);

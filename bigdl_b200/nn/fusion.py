@@ -55,12 +55,28 @@ def fuse(model: Module) -> Module:
     for m in model.all_modules():
         if type(m) is SpatialConvolution:
             m.__dict__.pop("_bn_stats", None)
+        m.__dict__.pop("_mask_input", None)
     if config.get("bigdl.fusion.bnstats"):
         for a, b in _pairs(model):
             if (type(a) is SpatialConvolution and isinstance(b, BatchNormalization) and not a._fuse_relu
                     and a.n_group == 1 and not getattr(b, "_folded", False) and getattr(b, "n_dim", 4) == 4
                     and getattr(a, "data_format", "NCHW") == "NCHW" and getattr(b, "data_format", "NCHW") == "NCHW"):
                 a.__dict__["_bn_stats"] = True
+    # conv+ReLU -> conv inside a Sequential (the second conv is the only consumer): the first conv's ReLU backward and
+    # bias-gradient column sums are folded into the second conv's dgrad epilogue
+    for m in model.all_modules():
+        if type(m) is SpatialConvolution:
+            m.__dict__.pop("_mask_input", None)
+    if config.get("bigdl.fusion.reludgrad"):
+        for m in model.all_modules():
+            if type(m) is not Sequential:
+                continue
+            mods = m.modules
+            for a, r, b in zip(mods, mods[1:], mods[2:]):
+                if (type(a) is SpatialConvolution and a._fuse_relu and type(r) is ReLU and getattr(r, "_fused", False)
+                        and type(b) is SpatialConvolution and b.n_group == 1 and b.propagate_back
+                        and getattr(a, "data_format", "NCHW") == "NCHW" and getattr(b, "data_format", "NCHW") == "NCHW"):
+                    b.__dict__["_mask_input"] = True
     if conv_sum and config.get("bigdl.fusion.residual", True):
         _mark_residual_blocks(model)
     return model

@@ -207,9 +207,13 @@ class SpatialConvolution(Module):
                 stats = zeros_f32(2 * self.n_output_plane, x.device)
             y = ConvFn.apply(xin, self.weight, bias, w16, geom, self._fuse_relu, self.scaleW, self.scaleB,
                              self.__dict__.pop("_skip_token", None),      # residual-block input pairing (SkipToken)
-                             stats)
+                             stats,
+                             # our input is the fused-ReLU output of the convolution right before us and we are its
+                             # only consumer (nn/fusion.py): its ReLU backward + bias sums run in our dgrad epilogue
+                             bool(self.__dict__.get("_mask_input")) and self.train)
             if stats is not None and getattr(stats, "_bdl_done", False):
                 y._bdl_bn_stats = stats
+
         else:
             w = self.weight
             if x.dtype != w.dtype:

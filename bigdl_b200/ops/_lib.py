@@ -110,6 +110,7 @@ _SIGNATURES = {
     "bdl_bn_apply": [_P, _P, _P, _P, _P, _P, _L, _I, _L, _L, _F, _I, _I, _P],
     "bdl_bn_bwd_reduce": [_P, _P, _P, _P, _P, _P, _L, _I, _L, _L, _L, _P],
     "bdl_bn_bwd_apply": [_P, _P, _P, _P, _P, _P, _P, _P, _L, _F, _I, _L, _L, _L, _L, _P],
+    "bdl_gemm_set_residual_mask": [_I],
     "bdl_gemm_set_stats": [_P],
     "bdl_gemm_stats_done": [],
     "bdl_bn_bwd_reduce_remask": [_P, _P, _P, _P, _P, _P, _P, _L, _I, _L, _L, _P],

@@ -174,6 +174,8 @@ def take_residual_hint():
 # here instead of running its own column-sum pass. Cleared after every backward (join_side_streams).
 _PREMASKED: dict = {}
 _BIAS_DONE = object()            # _PREMASKED value: masked AND the bias gradient is already in the flat buffer
+_NEED_COLSUM = object()          # _PREMASKED value: masked, but the bias-gradient column sums are still to be taken
+_RELU_DGRAD: list = [True]       # fold the producer's ReLU backward (+ bias-gradient sums) into the consumer's dgrad epilogue
 _SUMS: dict = {}                 # persistent, self-clearing fp32 column-sum vectors, one per Concat (see _concat_sums)
 
 
@@ -460,10 +462,14 @@ class ConvFn(Function):
     """2-D convolution, NHWC bf16, explicit-GEMM on the tcgen05 kernel (1x1/s1/p0 convs skip im2col entirely)."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, w16, geom, relu, scale_w, scale_b, skip_token=None, stats=None):
+    def forward(ctx, x, weight, bias, w16, geom, relu, scale_w, scale_b, skip_token=None, stats=None,
+                mask_input=False):
         kh, kw, sh, sw, pt, pl, pb, pr, dh, dw, groups = geom
         ctx.s2d = None
         ctx.skip_token = skip_token.join() if skip_token is not None else None
+        # the input is the (fused) ReLU output of another convolution: our dgrad can apply that layer's ReLU backward
+        # and sum its bias gradient in the epilogue (see backward)
+        ctx.mask_input = bool(mask_input)
         plan = _stem_s2d_plan(x, w16, geom, ctx.needs_input_grad[0])
         if plan is not None:
             return _stem_s2d_forward(ctx, x, weight, bias, w16, geom, relu, scale_w, scale_b, plan)
@@ -551,7 +557,7 @@ class ConvFn(Function):
     @staticmethod
     def backward(ctx, dy):
         if ctx.s2d is not None:
-            return tuple(_stem_s2d_backward(ctx, dy)) + (None, None)
+            return tuple(_stem_s2d_backward(ctx, dy)) + (None, None, None)
         xn, w4, y = ctx.saved_tensors
         weight, bias, geom, relu, scale_w, scale_b, dims, xshape = ctx.params
         kh, kw, sh, sw, pt, pl, pb, pr, dh, dw, groups = geom
@@ -564,9 +570,15 @@ class ConvFn(Function):
         gb = _acc_grad(bias, scale_b)
         pre = _PREMASKED.pop((dy.data_ptr(), tuple(dy.shape)), None) if (relu and _PREMASKED) else None
         if pre is not None:
-            # the Concat above already masked this slice with our ReLU output and summed its columns
+            # the Concat above (or the consuming convolution's dgrad epilogue) already masked this gradient with our
+            # ReLU output and, unless it says otherwise, summed its columns
             dz = dyn
-            if gb is not None and pre is not _BIAS_DONE:
+            if gb is not None and pre is _NEED_COLSUM:
+                if scale_b == 1.0:
+                    ew.colsum(dyn, gb)
+                else:
+                    gb.add_(ew.colsum(dyn, torch.zeros(O, device=dy.device)), alpha=scale_b)
+            elif gb is not None and pre is not _BIAS_DONE:
                 pre.record_stream(torch.cuda.current_stream(dy.device))
                 gb.add_(pre, alpha=scale_b)
         elif relu:
@@ -602,6 +614,14 @@ class ConvFn(Function):
                 skip_n, lds = nhwc_pitched(skip)
                 res2d = rows2d(skip_n, lds)
         fused_skip = False
+        masked_dx = False
+        # ReLU backward of the producing conv + its bias-gradient column sums, folded into this dgrad's epilogue: the
+        # mask operand is our own saved input (x > 0 <=> the producer's ReLU was active)
+        mask2d = colsum_stats = None
+        if (need_dx and ctx.mask_input and res2d is None and skip is None and groups == 1 and c_real == C
+                and tuple(xshape) == (N, C, H, W) and _RELU_DGRAD[0]):
+            mask2d = rows2d(xn, ldx)
+            colsum_stats = zeros_f32(2 * C, dy.device)
         if implicit:
             ldz = dz.stride(0)
             if gw is not None and not padded_c and C % 8 == 0 and C >= 16 and scale_w == 1.0 and gw2.stride(1) == 1:
@@ -617,9 +637,11 @@ class ConvFn(Function):
             if need_dx and sh == 1 and sw == 1 and dh * (kh - 1) - pt >= 0 and dw * (kw - 1) - pl >= 0:
                 dz_nhwc = torch.as_strided(dz, (N, Ho, Wo, O), (Ho * Wo * ldz, Wo * ldz, ldz, 1), dz.storage_offset())
                 conv_igemm(1, dz_nhwc, ldz, w2, dxn.view(N * H * W, C), C, H, W, kh, kw, 1, 1, dh * (kh - 1) - pt,
-                           dw * (kw - 1) - pl, dh, dw, residual=res2d)
+                           dw * (kw - 1) - pl, dh, dw, residual=res2d if mask2d is None else mask2d,
+                           res_mask=mask2d is not None, stats=colsum_stats)
                 done_x = True
                 fused_skip = res2d is not None
+                masked_dx = mask2d is not None
         for g in range(groups):
             if (gw is None or done_w) and (not need_dx or done_x):
                 break
@@ -658,8 +680,10 @@ class ConvFn(Function):
                 wg = w2[g * Og:(g + 1) * Og]
                 if direct:
                     gemm_bf16(dzg, wg, b_mn=True, out=dxn.view(N * H * W, C)[:, g * Cg:(g + 1) * Cg],
-                              residual=res2d if groups == 1 else None)
+                              residual=(res2d if mask2d is None else mask2d) if groups == 1 else None,
+                              res_mask=mask2d is not None, stats=colsum_stats)
                     fused_skip = res2d is not None and groups == 1
+                    masked_dx = mask2d is not None
                 else:
                     if Kp != K:
                         wpad = torch.zeros((Og, Kp), dtype=torch.bfloat16, device=dy.device)
@@ -679,12 +703,17 @@ class ConvFn(Function):
                 dx = dx[:, :xshape[1]]
             if tuple(dx.shape) != tuple(xshape):     # asymmetric SAME padding: drop the materialised border
                 dx = dx[:, :, :xshape[2], :xshape[3]]
+            if masked_dx:
+                # tell the producing conv that this gradient is already masked by its ReLU; hand it the column sums when
+                # the epilogue produced them (else it runs its own column-sum pass over the masked gradient)
+                done = colsum_stats is not None and getattr(colsum_stats, "_bdl_done", False)
+                _PREMASKED[(dx.data_ptr(), tuple(dx.shape))] = colsum_stats[:C] if done else _NEED_COLSUM
             if skip is not None and not fused_skip:
                 dx = dx + skip                       # a dgrad path without a residual epilogue (strided / grouped)
             elif token is not None and skip is None:
                 token.grad = dx                      # first of the pair: the other consumer adds this
                 dx = None
-        return dx, None, None, None, None, None, None, None, None, None
+        return dx, None, None, None, None, None, None, None, None, None, None
 
 
 class FanOutFn(Function):

@@ -32,7 +32,9 @@ def _stats_result(lib, stats):
         stats._bdl_done = bool(lib.bdl_gemm_stats_done())
 
 
-def _set_residual(lib, residual, M, N):
+def _set_residual(lib, residual, M, N, mask: bool = False):
+    if mask and residual is not None:
+        lib.bdl_gemm_set_residual_mask(1)
     if residual is None:
         return
     assert residual.dtype == torch.bfloat16 and residual.dim() == 2 and tuple(residual.shape) == (M, N) \
@@ -42,7 +44,7 @@ def _set_residual(lib, residual, M, N):
 
 def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False, bias=None, relu=False,
               out: torch.Tensor | None = None, out_dtype=torch.bfloat16, accumulate: bool = False, splits: int = 0,
-              residual: torch.Tensor | None = None, stats: torch.Tensor | None = None):
+              residual: torch.Tensor | None = None, stats: torch.Tensor | None = None, res_mask: bool = False):
     """D[M,N] = opA(a) @ opB(b)^T on the tensor cores.
 
     ``a`` is [M,K] (or [K,M] when ``a_mn``), ``b`` is [N,K] (or [K,N] when ``b_mn``); both bf16, 2-D, unit inner
@@ -66,7 +68,7 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: boo
     if bias is not None:
         assert bias.dtype == torch.float32 and bias.is_contiguous()
     _log("gemm", M=M, N=N, K=K, a_mn=int(a_mn), b_mn=int(b_mn), acc=int(accumulate))
-    _set_residual(lib, residual, M, N)
+    _set_residual(lib, residual, M, N, res_mask)      # res_mask: out = residual > 0 ? out : 0 (fused ReLU backward)
     _arm_stats(lib, stats, N)
     rc = lib.bdl_gemm_bf16(_lib.ptr(a), _lib.ptr(b), _lib.ptr(out), _lib.ptr(bias), M, N, K,
                            a.stride(0), b.stride(0), out.stride(0), int(a_mn), int(b_mn),
@@ -80,19 +82,19 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: boo
 
 def conv_igemm(mode: int, act: torch.Tensor, ld_act: int, other: torch.Tensor, out: torch.Tensor, O: int, Ho: int,
                Wo: int, kh: int, kw: int, sh: int, sw: int, ph: int, pw: int, dh: int, dw: int, bias=None, relu=False,
-               accumulate=False, splits: int = 0, residual=None, stats=None):
+               accumulate=False, splits: int = 0, residual=None, stats=None, res_mask: bool = False):
     """Implicit-GEMM convolution (csrc/gemm_tcgen05.cu, TMA im2col). ``act`` is an NHWC view [N,H,W,C] with pixel
     pitch ``ld_act``; ``other`` is the 2-D weight matrix (modes 0/1) or dY [N*Ho*Wo, O] (mode 2); ``out`` is 2-D."""
     lib = _lib.cuda_lib()
     N, H, W, C = act.shape
     flags = (BIAS if bias is not None else 0) | (RELU if relu else 0) | (ATOMIC_ADD if accumulate else 0)
     _log("conv", mode=mode, N=N, H=H, W=W, C=C, O=O, Ho=Ho, Wo=Wo, kh=kh, kw=kw, sh=sh)
-    _set_residual(lib, residual, N * Ho * Wo, O)
-    _arm_stats(lib, stats if mode == 0 else None, O)
+    _set_residual(lib, residual, N * Ho * Wo, O, res_mask)
+    _arm_stats(lib, stats if mode != 2 else None, O)
     rc = lib.bdl_conv_igemm_bf16(mode, act.data_ptr(), N, H, W, C, ld_act, other.data_ptr(), other.stride(0),
                                  out.data_ptr(), out.stride(0), _lib.ptr(bias), O, Ho, Wo, kh, kw, sh, sw, ph, pw, dh,
                                  dw, int(out.dtype == torch.float32), flags, splits, _lib.stream_ptr())
-    if stats is not None and mode == 0:
+    if stats is not None and mode != 2:
         lib.bdl_gemm_set_stats(None) if rc else _stats_result(lib, stats)
     _lib.check(rc, "bdl_conv_igemm_bf16")
     _lib.count_launch()

@@ -48,6 +48,10 @@ _DEFAULTS: dict[str, Any] = {
     "bigdl.mkldnn.fusion.convsum": True,
     "bigdl.fusion.bnadd": True,              # BatchNorm closing a residual branch + shortcut add + ReLU as one kernel (fwd and bwd)
     "bigdl.fusion.bnstats": True,            # conv followed by BatchNorm: sum / sum of squares from the conv's GEMM epilogue
+    # conv+ReLU -> conv: the first conv's ReLU backward and bias-gradient sums run in the second conv's dgrad epilogue.
+    # Off by default: measured slower than the separate mask + column-sum pass (VGG-16 18.43 vs 18.29 ms, Inception-v1
+    # 5.49 vs 5.43 ms): those dgrad GEMMs are epilogue-bound, the pass it saves runs at HBM speed.
+    "bigdl.fusion.reludgrad": False,
     "bigdl.fusion.skipgrad": True,           # residual block input: sum its two gradients in a dgrad GEMM epilogue
     "bigdl.fusion.residual": True,           # inference: shortcut add + ReLU inside the last conv's GEMM epilogue
     # misc

@@ -75,6 +75,9 @@ struct GemmParams {
                                    // over the output (S/nn/mkldnn/SpatialBatchNormalization.scala needs its own pass)
   const __nv_bfloat16* residual;   // optional [M, N] bf16 tensor (row pitch ldr) added before the ReLU: the shortcut of a
   long long ldr;                   // residual block, so conv + add + ReLU is one pass (reference: Fusion.fusionCAddTable)
+  int res_mask;                    // 1: the operand is not added but used as a ReLU mask, out = (residual > 0 ? out : 0) —
+                                   // dgrad of a layer whose input is a ReLU output: the ReLU backward of the PRODUCING layer
+                                   // happens here instead of in a pass of its own
   // implicit-GEMM convolution (kConv != 0): the A (fprop/dgrad) or B (wgrad) operand is gathered from an NHWC
   // activation tensor by TMA im2col loads instead of being read from a materialised column matrix.
   int cv_Ho, cv_Wo;          // output spatial size of the traversal
@@ -147,14 +150,25 @@ __device__ __forceinline__ void epilogue_store16(const GemmParams& p, const uint
     if (full && ((reinterpret_cast<uintptr_t>(rp) & 15u) == 0)) {
       const uint4 r0 = __ldg(reinterpret_cast<const uint4*>(rp)), r1 = __ldg(reinterpret_cast<const uint4*>(rp) + 1);
       const uint32_t w[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+      if (p.res_mask) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        v[2 * j] += __uint_as_float(w[j] << 16);
-        v[2 * j + 1] += __uint_as_float(w[j] & 0xFFFF0000u);
+        for (int j = 0; j < 8; ++j) {
+          v[2 * j] = __uint_as_float(w[j] << 16) > 0.f ? v[2 * j] : 0.f;
+          v[2 * j + 1] = __uint_as_float(w[j] & 0xFFFF0000u) > 0.f ? v[2 * j + 1] : 0.f;
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          v[2 * j] += __uint_as_float(w[j] << 16);
+          v[2 * j + 1] += __uint_as_float(w[j] & 0xFFFF0000u);
+        }
       }
     } else {
       for (int j = 0; j < 16; ++j)
-        if (j < nvalid) v[j] += __bfloat162float(rp[j]);
+        if (j < nvalid) {
+          const float rv = __bfloat162float(rp[j]);
+          v[j] = p.res_mask ? (rv > 0.f ? v[j] : 0.f) : v[j] + rv;
+        }
     }
   }
   if (p.flags & BDL_GEMM_RELU) {
@@ -254,14 +268,25 @@ __device__ __forceinline__ void epilogue_pack16(const GemmParams& p, const uint3
     if (nvalid >= 16 && ((reinterpret_cast<uintptr_t>(rp) & 15u) == 0)) {
       const uint4 r0 = __ldg(reinterpret_cast<const uint4*>(rp)), r1 = __ldg(reinterpret_cast<const uint4*>(rp) + 1);
       const uint32_t w[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+      if (p.res_mask) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        v[2 * j] += __uint_as_float(w[j] << 16);
-        v[2 * j + 1] += __uint_as_float(w[j] & 0xFFFF0000u);
+        for (int j = 0; j < 8; ++j) {
+          v[2 * j] = __uint_as_float(w[j] << 16) > 0.f ? v[2 * j] : 0.f;
+          v[2 * j + 1] = __uint_as_float(w[j] & 0xFFFF0000u) > 0.f ? v[2 * j + 1] : 0.f;
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          v[2 * j] += __uint_as_float(w[j] << 16);
+          v[2 * j + 1] += __uint_as_float(w[j] & 0xFFFF0000u);
+        }
       }
     } else {
       for (int j = 0; j < 16; ++j)
-        if (j < nvalid) v[j] += __bfloat162float(rp[j]);
+        if (j < nvalid) {
+          const float rv = __bfloat162float(rp[j]);
+          v[j] = p.res_mask ? (rv > 0.f ? v[j] : 0.f) : v[j] + rv;
+        }
     }
   }
   if (p.flags & BDL_GEMM_RELU) {
@@ -988,6 +1013,7 @@ gemm_bf16_allgather_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
 // bdl_gemm_bf16 / bdl_conv_igemm_bf16 / bdl_gemm_fp8, so the launch signatures stay as they are.
 static thread_local const void* g_next_residual = nullptr;
 static thread_local long long g_next_ldr = 0;
+static thread_local int g_next_res_mask = 0;          // bdl_gemm_set_residual_mask: the armed residual is a ReLU mask
 static thread_local float* g_next_stats = nullptr;   // bdl_gemm_set_stats: column statistics of the next launch's output
 static thread_local int g_stats_done = 0;            // did the last launch on this thread produce them?
 static void take_residual(GemmParams& p) {
@@ -995,6 +1021,8 @@ static void take_residual(GemmParams& p) {
   p.ldr = g_next_ldr;
   g_next_residual = nullptr;
   g_next_ldr = 0;
+  p.res_mask = g_next_res_mask;
+  g_next_res_mask = 0;
   p.stat_sums = g_next_stats;
   g_next_stats = nullptr;
   g_stats_done = 0;
@@ -1353,7 +1381,7 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
   const long long Mpix = static_cast<long long>(N) * Ho * Wo;
   if (Mpix >= (1ll << 31)) return bdl_fail("bdl_conv_igemm_bf16: too many output pixels");
   const int taps = kh * kw;
-  if (p.residual && (mode != 0 || out_fp32)) return bdl_fail("bdl_conv_igemm_bf16: residual is a forward, bf16-output option");
+  if (p.residual && (mode == 2 || out_fp32)) return bdl_fail("bdl_conv_igemm_bf16: the residual operand needs a bf16 fprop / dgrad output");
   p.cv_Ho = Ho; p.cv_Wo = Wo; p.cv_sh = sh; p.cv_sw = sw; p.cv_ph = ph; p.cv_pw = pw; p.cv_dh = dh; p.cv_dw = dw;
   p.cv_kh = kh; p.cv_kw = kw; p.cv_C = C; p.cv_cblocks = (C + 63) / 64; p.cv_flip = (mode == 1); p.cv_nimg = N;
   p.fd_hw.init(static_cast<uint32_t>(Ho) * Wo);
@@ -1437,7 +1465,7 @@ extern "C" int bdl_conv_igemm_bf16(int mode, const void* act, int N, int H, int 
   p.bias = bias;
   const size_t stage_bytes = static_cast<size_t>(BM) * BK * 2 * (p.dual_m ? 2 : 1) + static_cast<size_t>(p.b_rows) * BK * 2;
   const bool tma_out = !(two && p.dual_m) && want_tma_store(D, ldd, out_fp32, flags, mode == 2, p.cv_num_kb);
-  if (p.stat_sums != nullptr && tma_out && mode == 0 && !(flags & BDL_GEMM_RELU)) g_stats_done = 1;
+  if (p.stat_sums != nullptr && tma_out && mode != 2 && !(flags & BDL_GEMM_RELU)) g_stats_done = 1;
   else p.stat_sums = nullptr;
   const size_t budget = kSmemBudget - (tma_out ? kStageOutBytes : 0);
   int stages = static_cast<int>(budget / stage_bytes);
@@ -1650,6 +1678,12 @@ extern "C" int bdl_gemm_set_stats(float* sums) {
   return BDL_OK;
 }
 extern "C" int bdl_gemm_stats_done() { return g_stats_done; }
+
+// The residual armed for the next launch is a ReLU mask source: out = residual > 0 ? out : 0 (see GemmParams::res_mask).
+extern "C" int bdl_gemm_set_residual_mask(int on) {
+  g_next_res_mask = on ? 1 : 0;
+  return BDL_OK;
+}
 
 extern "C" int bdl_gemm_set_residual(const void* residual_bf16, long long ld) {
   if (residual_bf16 && ld <= 0) return bdl_fail("bdl_gemm_set_residual: row pitch must be positive");

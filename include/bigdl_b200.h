@@ -37,6 +37,7 @@ int bdl_stream_capture_status(void* stream);
  * Reference: the conv + sum post-op of S/nn/mkldnn/Fusion.scala (fusionCAddTable). */
 /* Per-column (sum, sum of squares) of the NEXT bf16 GEMM / conv fprop output on this thread, added into sums [2*N] fp32 by
  * the epilogue (batch-norm statistics without a pass over the output). bdl_gemm_stats_done(): 1 if that launch did it. */
+int bdl_gemm_set_residual_mask(int on);   /* the armed residual masks instead of adding: out = residual > 0 ? out : 0 */
 int bdl_gemm_set_stats(float* sums);
 int bdl_gemm_stats_done(void);
 int bdl_gemm_set_residual(const void* residual_bf16, long long ld);

@@ -12,7 +12,10 @@ from pathlib import Path
 
 import torch
 
-_LIBDIR = Path(__file__).resolve().parent.parent / "lib"
+import os as _os
+
+# BIGDL_B200_LIBDIR: load the native libraries from another directory (A/B runs of two builds on one box)
+_LIBDIR = Path(_os.environ.get("BIGDL_B200_LIBDIR") or (Path(__file__).resolve().parent.parent / "lib"))
 _cuda = None
 _host = None
 

@@ -30,7 +30,7 @@ namespace bdl {
 constexpr int BM = 128;
 constexpr int BK = 64;  // 64 bf16 = 128 bytes = one swizzle row
 // dynamic shared memory available to the operand ring: 227 KB minus alignment slack, barriers and the epilogue columns
-constexpr size_t kSmemBudget = 227 * 1024 - 1024 - 512 - 4096 - 2048;   // - alignment, barriers, epi_cols, stat_acc
+constexpr size_t kSmemBudget = 227 * 1024 - 1024 - 512 - 4096;
 constexpr int kMaxStages = 8;
 constexpr int kGemmThreads = 320;   // TMA warp, MMA warp, 8 epilogue warps (two per TMEM lane quadrant)
 constexpr int kEpiThreads = 256;
@@ -312,6 +312,67 @@ __device__ __forceinline__ void epilogue_pack16(const GemmParams& p, const uint3
   q1.z = pack_bf16x2(v[12], v[13]); q1.w = pack_bf16x2(v[14], v[15]);
 }
 
+// Flush the per-CTA column accumulators of n tile `nblk` (none if < 0) to global memory and clear them; called by all
+// epilogue threads (named barrier 1). Out of line for the same reason as epi_col_stats.
+__device__ __noinline__ void epi_stats_flush(float* sums, int N, int block_n, int nblk, uint32_t et, float* stat_sum,
+                                             float* stat_sq) {
+  asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
+  if (nblk >= 0) {
+    const int n = nblk * block_n + static_cast<int>(et);
+    if (static_cast<int>(et) < block_n && n < N) {
+      atomicAdd(sums + n, stat_sum[et]);
+      atomicAdd(sums + N + n, stat_sq[et]);
+    }
+  }
+  stat_sum[et] = 0.f;
+  stat_sq[et] = 0.f;
+  asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
+}
+
+// Column sums of one staged 32-row x 64-column bf16 box (this warp's TMA-store staging buffer, 128B-swizzled) into the
+// per-CTA accumulators. Kept out of line: inlined it cost the kernels that never take statistics ~1 % (registers / code
+// layout of the epilogue warps).
+__device__ __noinline__ void epi_col_stats(uint32_t stg, uint32_t lane, int rows_valid, int c, float* stat_sum,
+                                           float* stat_sq) {
+  // lane l sums columns c + 2l, c + 2l + 1 of the staged rows (bank-conflict free: one 128-byte row per step)
+  rows_valid = rows_valid > 32 ? 32 : rows_valid;
+  float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+  // the swizzle repeats every 8 rows: 8 lane-dependent offsets, then constant strides
+  uint32_t off8[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k)
+    off8[k] = stg + static_cast<uint32_t>(k) * 128u + (((lane >> 2) ^ static_cast<uint32_t>(k)) << 4) + ((lane & 3u) << 2);
+  if (rows_valid == 32) {
+#pragma unroll
+    for (int r = 0; r < 32; ++r) {
+      uint32_t w;
+      asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(off8[r & 7] + static_cast<uint32_t>(r >> 3) * 1024u));
+      const float v0 = __uint_as_float(w << 16), v1 = __uint_as_float(w & 0xFFFF0000u);
+      s0 += v0;
+      s1 += v1;
+      q0 = fmaf(v0, v0, q0);
+      q1 = fmaf(v1, v1, q1);
+    }
+  } else {
+    for (int r = 0; r < rows_valid; ++r) {
+      uint32_t w;
+      const uint32_t a = stg + static_cast<uint32_t>(r) * 128u + (((lane >> 2) ^ (static_cast<uint32_t>(r) & 7u)) << 4) +
+                         ((lane & 3u) << 2);
+      asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(a));
+      const float v0 = __uint_as_float(w << 16), v1 = __uint_as_float(w & 0xFFFF0000u);
+      s0 += v0;
+      s1 += v1;
+      q0 = fmaf(v0, v0, q0);
+      q1 = fmaf(v1, v1, q1);
+    }
+  }
+  const uint32_t col = static_cast<uint32_t>(c) + 2u * lane;
+  atomicAdd(&stat_sum[col], s0);
+  atomicAdd(&stat_sum[col + 1], s1);
+  atomicAdd(&stat_sq[col], q0);
+  atomicAdd(&stat_sq[col + 1], q1);
+}
+
 // kFp8: operands are e4m3 bytes (128 per swizzle row, UMMA K = 32) multiplied with kind::f8f6f4; the epilogue applies a
 //       per-output-column fp32 scale (activation scale x per-channel weight scale) before bias/ReLU. K-major only.
 // kTmaStore: bf16 outputs leave through shared memory and TMA stores (one 32-row x 128-byte box per warp and 64-column
@@ -346,7 +407,6 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tmA, const 
   __shared__ __align__(8) uint64_t tempty_bar[2];
   __shared__ uint32_t tmem_base_slot;
   __shared__ __align__(16) float epi_cols[2][2][256];   // [accumulator stage][bias | scale][column of the tile]
-  __shared__ float stat_acc[2][256];                    // [sum | sum of squares][column of the current n tile] (stat_sums)
 
   static_assert(!kTwo || (!kAMN && kConv != 2), "CTA pairs: A must be K-major, no wgrad");
   const uint32_t warp = threadIdx.x >> 5;
@@ -384,13 +444,6 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tmA, const 
   else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
-  // Programmatic dependent launch: everything above (barrier init, TMEM allocation, tensor-map prefetch) may overlap the
-  // tail of the previous kernel in the stream; nothing below may, since operands, bias and residual can all be its
-  // output. A no-op when the launch carries no programmatic dependency. Our own dependents may be scheduled as soon as
-  // every CTA of this grid has got here (they block in their own wait until this grid has completed).
-  asm volatile("griddepcontrol.wait;" ::: "memory");
-  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-
   constexpr int KE = kFp8 ? 128 : 64;   // elements per 128-byte k block
   const bool small_c = kConv != 0 && !kFp8 && p.cv_aw < 64;
   const int num_kb = kConv ? p.cv_num_kb : (p.K + KE - 1) / KE;
@@ -769,20 +822,12 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tmA, const 
     // column statistics (stat_sums): accumulated per CTA in shared memory across the m tiles of one n tile and flushed
     // with one atomic per column when the n tile changes / at the end, so the global atomics stay ~#CTA per column
     const bool do_stats = kTmaStore && !kFp8 && p.stat_sums != nullptr;
+    // the dequantisation-scale half of epi_cols is only used by the fp8 kernels: bf16 kernels keep the per-CTA column
+    // accumulators there ([0] sums, [1] sums of squares), so the statistics cost no shared memory
+    float* const stat_sum = &epi_cols[0][1][0];
+    float* const stat_sq = &epi_cols[1][1][0];
     int stat_nblk = -1;
-    auto stat_flush = [&]() {
-      asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
-      if (stat_nblk >= 0) {
-        const int n = stat_nblk * p.block_n + static_cast<int>(et);
-        if (static_cast<int>(et) < p.block_n && n < p.N) {
-          atomicAdd(p.stat_sums + n, stat_acc[0][et]);
-          atomicAdd(p.stat_sums + p.N + n, stat_acc[1][et]);
-        }
-      }
-      stat_acc[0][et] = 0.f;
-      stat_acc[1][et] = 0.f;
-      asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
-    };
+    auto stat_flush = [&]() { epi_stats_flush(p.stat_sums, p.N, p.block_n, stat_nblk, et, stat_sum, stat_sq); };
     for (int work = work0; work < total_work; work += work_step) {
       const int split = work / tiles_mn;
       const int rem = work - split * tiles_mn;
@@ -863,46 +908,7 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tmA, const 
             tma_store_2d(&tmD, stg, nbase + c, row0);
             tma_store_commit();
           }
-          if (do_stats) {
-            // lane l sums columns c + 2l, c + 2l + 1 of the 32 staged rows (bank-conflict free: one 128-byte row per step)
-            int rows_valid = p.M - row0;
-            rows_valid = rows_valid > 32 ? 32 : rows_valid;
-            float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
-            // the swizzle repeats every 8 rows: 8 lane-dependent offsets, then constant strides
-            uint32_t off8[8];
-#pragma unroll
-            for (int k = 0; k < 8; ++k)
-              off8[k] = stg + static_cast<uint32_t>(k) * 128u + (((lane >> 2) ^ static_cast<uint32_t>(k)) << 4) + ((lane & 3u) << 2);
-            if (rows_valid == 32) {
-#pragma unroll
-              for (int r = 0; r < 32; ++r) {
-                uint32_t w;
-                asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(off8[r & 7] + static_cast<uint32_t>(r >> 3) * 1024u));
-                const float v0 = __uint_as_float(w << 16), v1 = __uint_as_float(w & 0xFFFF0000u);
-                s0 += v0;
-                s1 += v1;
-                q0 = fmaf(v0, v0, q0);
-                q1 = fmaf(v1, v1, q1);
-              }
-            } else {
-              for (int r = 0; r < rows_valid; ++r) {
-                uint32_t w;
-                const uint32_t a = stg + static_cast<uint32_t>(r) * 128u +
-                                   (((lane >> 2) ^ (static_cast<uint32_t>(r) & 7u)) << 4) + ((lane & 3u) << 2);
-                asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(a));
-                const float v0 = __uint_as_float(w << 16), v1 = __uint_as_float(w & 0xFFFF0000u);
-                s0 += v0;
-                s1 += v1;
-                q0 = fmaf(v0, v0, q0);
-                q1 = fmaf(v1, v1, q1);
-              }
-            }
-            const uint32_t col = static_cast<uint32_t>(c) + 2u * lane;
-            atomicAdd(&stat_acc[0][col], s0);
-            atomicAdd(&stat_acc[0][col + 1], s1);
-            atomicAdd(&stat_acc[1][col], q0);
-            atomicAdd(&stat_acc[1][col + 1], q1);
-          }
+          if (do_stats) epi_col_stats(stg, lane, p.M - row0, c, stat_sum, stat_sq);
         }
         tc_fence_before();
         __syncwarp();
@@ -1110,13 +1116,6 @@ static int launch_gemm_kernel(GemmKernel kfn, long long total_work, int num_sms,
     attr[na].val.clusterDim.x = 2;
     attr[na].val.clusterDim.y = 1;
     attr[na].val.clusterDim.z = 1;
-    ++na;
-  }
-  // BDL_PDL=1: let this kernel's prologue overlap the previous kernel's tail (the kernel waits before its first read)
-  static const bool pdl = [] { const char* e = getenv("BDL_PDL"); return e && e[0] == '1'; }();
-  if (pdl) {
-    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[na].val.programmaticStreamSerializationAllowed = 1;
     ++na;
   }
   if (na) {

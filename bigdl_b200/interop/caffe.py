@@ -167,7 +167,16 @@ class _Converter:
     def _flatten(self, L, l, blobs): return L.InferReshape([0, -1], False)
 
     def _elu(self, L, l, blobs): return L.ELU(float(l.elu_param.alpha))
-    def _threshold(self, L, l, blobs): return L.Threshold(float(l.threshold_param.threshold), 0.0)
+    def _threshold(self, L, l, blobs):
+        # Caffe's Threshold emits 1 where x > threshold, else 0 (Converter.scala:205-212 maps it to BinaryThreshold; an
+        # unset threshold is 1e-6 there)
+        tp = l.threshold_param
+        return L.BinaryThreshold(float(tp.threshold) if tp.HasField("threshold") else 1e-6)
+
+    def _recurrent(self, L, l, blobs):
+        return L.Recurrent()             # an empty time-loop container, as Converter.scala:200-203 (cells are added by the user)
+
+    _rnn = _recurrent
 
     def _power(self, L, l, blobs):
         p = l.power_param

@@ -527,7 +527,9 @@ class CaffePersister:
                 layer.type = "LRN"
                 lp = layer.lrn_param
                 lp.local_size, lp.alpha, lp.beta, lp.norm_region = m.size, m.alpha, m.beta, 1
-            elif isinstance(m, L.Threshold):
+            elif isinstance(m, (L.BinaryThreshold, L.Threshold)):
+                # Caffe's Threshold is a 0/1 step (= BinaryThreshold); the reference also writes its value-replacing
+                # Threshold under this type (Converter.scala toCaffeThreshold), which reads back as BinaryThreshold
                 layer.type = "Threshold"
                 layer.threshold_param.threshold = m.th
             elif isinstance(m, L.ELU):

@@ -410,7 +410,7 @@ def test_caffe_export_covers_the_activation_and_affine_layers(tmp_path):
     m = (L.Sequential().add(L.SpatialConvolution(3, 4, 3, 3, 1, 1, 1, 1)).add(L.ELU(0.7))
          .add(L.SpatialFullConvolution(4, 6, 3, 3, 2, 2, 1, 1)).add(L.PReLU(6)).add(L.Scale([1, 6, 1, 1])).add(L.Abs())
          .add(L.Power(2.0, 0.5, 0.1)).add(L.SpatialWithinChannelLRN(3, 0.5, 0.75)).add(L.CAdd([1, 6, 1, 1]))
-         .add(L.Threshold(0.2, 0.0)).add(L.Exp()))
+         .add(L.BinaryThreshold(0.2)).add(L.Exp()))
     for p in m.parameters()[0]:
         if p.abs().sum() == 0:
             p.data.normal_()

@@ -22,3 +22,5 @@ def _py_aliases(cls):
 _py_aliases(Module)
 if not hasattr(Module, "loadModel"):
     Module.loadModel = staticmethod(Module.loadModule)
+
+from bigdl_b200.nn.onnx import Gemm  # noqa: F401,E402  (pyspark/bigdl/nn/layer.py also defines Gemm)

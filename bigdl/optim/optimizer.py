@@ -18,3 +18,5 @@ BaseOptimizer = Optimizer
 
 class ActivityRegularization:          # kept for import parity; the layer lives in bigdl.nn.layer
     pass
+
+from bigdl_b200.optim.validation import MeanAveragePrecisionObjectDetection  # noqa: F401,E402

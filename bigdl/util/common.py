@@ -162,3 +162,55 @@ def get_activation_by_name(activation_name, activation_id=None):
 
 def callBigDlFunc(bigdl_type, name, *args):
     raise NotImplementedError(f"there is no JVM bridge in this build; '{name}' is implemented natively in bigdl_b200")
+
+
+# ---- names of the py4j plumbing, kept so code that imports them still loads; there is no gateway behind them
+class SingletonMixin:
+    _instance = None
+
+    @classmethod
+    def instance(cls, *args, **kw):
+        if cls._instance is None:
+            cls._instance = cls(*args, **kw)
+        return cls._instance
+
+
+class GatewayWrapper(SingletonMixin):
+    def __init__(self, bigdl_type="float", port=25333):
+        self.value = None
+
+
+class JavaCreator(SingletonMixin):
+    __creator_class = ["com.intel.analytics.bigdl.python.api.PythonBigDLKeras"]
+
+    @classmethod
+    def add_creator_class(cls, jinvoker):
+        JavaCreator.__creator_class.append(jinvoker)
+
+    @classmethod
+    def get_creator_class(cls):
+        return list(JavaCreator.__creator_class)
+
+    @classmethod
+    def set_creator_class(cls, cclass):
+        JavaCreator.__creator_class = [cclass] if isinstance(cclass, str) else list(cclass)
+
+    def __init__(self, bigdl_type="float", gateway=None):
+        self.value = []
+
+
+class JActivity:
+    """An activity (tensor or table) handed across the old JVM boundary: just holds the value."""
+
+    def __init__(self, value):
+        self.value = value
+
+
+def callJavaFunc(func, *args):
+    """The reference converts arguments to Java objects and back; here ``func`` is a Python callable."""
+    return func(*args)
+
+
+def extend_spark_driver_cp(sparkConf, path):
+    """No Spark driver class path to extend; returns the configuration unchanged."""
+    return sparkConf

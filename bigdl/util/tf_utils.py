@@ -21,3 +21,13 @@ def save_variable_bigdl(tensors, target_path, bigdl_type="float"):
     import numpy as np
 
     np.savez(target_path, **{k: np.asarray(v) for k, v in tensors.items()})
+
+
+def get_path(output_name, sess=None):
+    """Names of the graph nodes an output depends on (the reference walks a live session's graph; pass a GraphDef)."""
+    raise NotImplementedError("get_path needs a TensorFlow runtime, which is not installed here")
+
+
+def merge_checkpoint(input_graph, checkpoint, output_node_names, output_graph, sess=None):
+    """Freeze a checkpoint into a GraphDef (TensorFlow's freeze_graph); needs TensorFlow."""
+    raise NotImplementedError("merge_checkpoint needs a TensorFlow runtime, which is not installed here")

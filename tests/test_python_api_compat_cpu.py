@@ -103,3 +103,47 @@ def test_util_common_and_engine_helpers(tmp_path):
     assert E.compare_version("1.6.0", "2.0.0") == -1 and E.compare_version("2.0", "2.0") == 0
     assert E.is_spark_below_2_2() is False and E.prepare_env() is None and isinstance(E.get_bigdl_classpath(), str)
     E.check_spark_source_conflict("a", "b")
+
+
+def test_every_public_name_of_the_reference_python_package_resolves():
+    """Each class / function defined at module level in pyspark/bigdl/**.py (models and examples aside) is importable
+    from the same module path of the ``bigdl`` compatibility package."""
+    import importlib
+    import os
+    import re
+    ref = "/root/reference/pyspark/bigdl"
+    if not os.path.isdir(ref):
+        import pytest
+        pytest.skip("reference tree not available")
+    missing = {}
+    for root, _, files in os.walk(ref):
+        for f in files:
+            if not f.endswith(".py") or f == "__init__.py":
+                continue
+            rel = os.path.relpath(os.path.join(root, f), ref)
+            if rel.startswith(("models", "examples")):
+                continue
+            mod = importlib.import_module("bigdl." + rel[:-3].replace(os.sep, "."))
+            names = set(re.findall(r"^(?:def|class) (\w+)", open(os.path.join(root, f)).read(), re.M))
+            gone = sorted(n for n in names if not n.startswith("_") and not hasattr(mod, n))
+            if gone:
+                missing[rel] = gone
+    assert not missing, missing
+
+
+def test_compat_helpers_behave():
+    from bigdl.dataset.base import Progbar, display_table, maybe_download
+    from bigdl.nn.keras.layer import Dense
+    from bigdl.nn.keras.topology import Sequential
+    from bigdl.util.common import JavaCreator, callJavaFunc
+    import pytest
+    m = Sequential()
+    m.add(Dense(3, input_shape=(4,)))
+    assert m.modules[0].get_input_shape() == (None, 4) and m.modules[0].get_output_shape() == (None, 3)
+    assert callJavaFunc(lambda a, b: a + b, 1, 2) == 3
+    JavaCreator.add_creator_class("x.Y")
+    assert "x.Y" in JavaCreator.get_creator_class()
+    Progbar(4, verbose=0).update(4)
+    display_table([["a", "b"]], [3, 6])
+    with pytest.raises(IOError):
+        maybe_download("nope.bin", "/tmp/_bdl_dl_test", "http://127.0.0.1:9/nope.bin")

@@ -206,7 +206,22 @@ class AbstractDataSet:
         return self
 
     def transform(self, transformer: Transformer) -> "AbstractDataSet":
+        """Chain a dataset ``Transformer`` (iterator -> iterator) or a vision ``FeatureTransformer`` (applied to every
+        ImageFeature; P/dataset/dataset.py ``DataSet.transform``)."""
+        if not isinstance(transformer, Transformer) and hasattr(transformer, "transform") and callable(transformer.transform):
+            ft = transformer
+            transformer = _FnTransformer(lambda it: (ft.transform(f) for f in it))
         return TransformedDataSet(self, transformer)
+
+    def get_image_frame(self):
+        """The ImageFrame this dataset was made from (``DataSet.image_frame``), or None."""
+        d = self
+        while d is not None:
+            fr = d.__dict__.get("_image_frame")
+            if fr is not None:
+                return fr
+            d = d.__dict__.get("base")
+        return None
 
     def __rshift__(self, transformer: Transformer):
         return self.transform(transformer)
@@ -219,6 +234,16 @@ class AbstractDataSet:
 
     def is_distributed(self) -> bool:
         return False
+
+
+class _FnTransformer(Transformer):
+    """A Transformer from a plain iterator -> iterator function."""
+
+    def __init__(self, fn):
+        self.fn = fn
+
+    def __call__(self, prev):
+        return self.fn(prev)
 
 
 class TransformedDataSet(AbstractDataSet):
@@ -331,6 +356,13 @@ class DataSet:
         feats = getattr(frame, "features", None)
         feats = list(feats() if callable(feats) else feats) if feats is not None else list(frame)
         return DataSet.array(feats, bool(getattr(frame, "is_distributed", lambda: False)()))
+
+    @staticmethod
+    def image_frame(frame):
+        """Python API spelling (P/dataset/dataset.py ``DataSet.image_frame``); the result remembers its frame."""
+        ds = DataSet.imageFrame(frame)
+        ds.__dict__["_image_frame"] = frame
+        return ds
 
     @staticmethod
     def ImageFolder(path: str, scale_to: int = 256, distributed: bool = False):

@@ -131,6 +131,48 @@ class ImageFrame:
         return frame.transform(BytesToMat())
 
     @staticmethod
+    def write_parquet(path: str, output: str, sc=None, partition_num: int = 1) -> None:
+        """Pack the image files under ``path`` (a file, a folder or a glob) into parquet with the reference's two
+        columns — ``uri`` (string) and ``bytes`` (binary) — split over ``partition_num`` files (ImageFrame.scala:170-178)."""
+        import glob
+
+        import pyarrow as pa
+        import pyarrow.parquet as pq
+
+        if os.path.isdir(path):
+            paths = sorted(os.path.join(path, f) for f in os.listdir(path) if os.path.isfile(os.path.join(path, f)))
+        else:
+            paths = sorted(p for p in glob.glob(path) if os.path.isfile(p))
+        os.makedirs(output, exist_ok=True)
+        parts = max(1, min(int(partition_num), len(paths) or 1))
+        for k in range(parts):
+            chunk = paths[k::parts]
+            data = []
+            for p in chunk:
+                with open(p, "rb") as f:
+                    data.append(f.read())
+            table = pa.table({"uri": pa.array(chunk, pa.string()), "bytes": pa.array(data, pa.binary())})
+            pq.write_table(table, os.path.join(output, f"part-{k:05d}.parquet"))
+
+    writeParquet = write_parquet
+
+    @staticmethod
+    def read_parquet(path: str, sc=None) -> "DistributedImageFrame":
+        """Parquet written by ``write_parquet`` (or by the reference) -> rank-sharded frame of decoded images
+        (ImageFrame.scala:153-161)."""
+        import pyarrow.parquet as pq
+
+        files = [path] if os.path.isfile(path) else sorted(
+            os.path.join(path, f) for f in os.listdir(path) if f.endswith(".parquet"))
+        feats = []
+        for fn in files:
+            t = pq.read_table(fn, columns=["uri", "bytes"]).to_pydict()
+            feats += [ImageFeature(b, path=u) for u, b in zip(t["uri"], t["bytes"])]
+        return DistributedImageFrame(feats).transform(BytesToMat())
+
+    readParquet = read_parquet
+
+    @staticmethod
     def array(images, labels=None) -> "LocalImageFrame":
         labels = labels if labels is not None else [None] * len(images)
         return LocalImageFrame([ImageFeature(i, l) for i, l in zip(images, labels)])

@@ -147,3 +147,29 @@ def test_compat_helpers_behave():
     display_table([["a", "b"]], [3, 6])
     with pytest.raises(IOError):
         maybe_download("nope.bin", "/tmp/_bdl_dl_test", "http://127.0.0.1:9/nope.bin")
+
+
+def test_image_frame_parquet_and_dataset_image_frame(tmp_path):
+    """ImageFrame.write_parquet / read_parquet (uri + bytes columns, ImageFrame.scala:153-178) and the Python
+    DataSet.image_frame / transform / get_image_frame trio (P/dataset/dataset.py)."""
+    import cv2
+    import numpy as np
+    from bigdl.dataset.dataset import DataSet
+    from bigdl.transform.vision.image import ImageFrame, Resize
+    src = tmp_path / "imgs"
+    src.mkdir()
+    rs = np.random.RandomState(0)
+    for i in range(5):
+        cv2.imwrite(str(src / f"{i}.png"), rs.randint(0, 255, (12, 16, 3), dtype=np.uint8))
+    ImageFrame.write_parquet(str(src), str(tmp_path / "pq"), None, partition_num=2)
+    assert len(list((tmp_path / "pq").glob("*.parquet"))) == 2
+    frame = ImageFrame.read_parquet(str(tmp_path / "pq"))
+    assert frame.is_distributed() and len(frame.features) == 5
+    mats = sorted((f["uri"], f["mat"].shape) for f in frame.features)
+    assert mats[0][1] == (12, 16, 3) and mats[0][0].endswith("0.png")
+    ds = DataSet.image_frame(frame)
+    assert ds.get_image_frame() is frame and ds.size() == 5
+    small = ds.transform(Resize(6, 8))
+    assert small.get_image_frame() is frame
+    first = next(iter(small.data(train=False)))
+    assert first["mat"].shape[:2] == (6, 8)

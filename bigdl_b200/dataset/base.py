@@ -60,18 +60,72 @@ class Sample:
         return f"Sample: features: {[tuple(f.shape) for f in self.features]}, labels: {[tuple(l.shape) for l in self.labels]}"
 
 
+class PaddingStrategy:
+    """How long the padded first dimension of feature / label ``i`` becomes (S/dataset/MiniBatch.scala:527-575).
+    ``paddingSize(sizes)`` maps the per-input sizes ``[batch, longest, ...]`` to the padded sizes."""
+
+    def paddingSize(self, sizes):
+        raise NotImplementedError
+
+    def length_for(self, idx: int, longest: int) -> int:
+        """Padded length of input ``idx`` whose longest sample has ``longest`` steps."""
+        out = self.paddingSize([[0, longest] if i == idx else [0, 0] for i in range(idx + 1)])
+        return int(out[idx][1])
+
+
+class DefaultPadding(PaddingStrategy):
+    """Pad to the longest sample of the batch."""
+
+    def paddingSize(self, sizes):
+        return sizes
+
+
+class PaddingLongest(PaddingStrategy):
+    """Longest sample of the batch plus a constant per input."""
+
+    def __init__(self, paddingLength):
+        self.paddingLength = list(paddingLength)
+
+    def paddingSize(self, sizes):
+        for i, s in enumerate(sizes):
+            if i < len(self.paddingLength):
+                s[1] += self.paddingLength[i]
+        return sizes
+
+
+class FixedLength(PaddingStrategy):
+    """A fixed length per input (negative = keep the longest); shorter than the data is an error."""
+
+    def __init__(self, fixedLength):
+        self.fixedLength = list(fixedLength) if isinstance(fixedLength, (list, tuple)) else [fixedLength]
+
+    def paddingSize(self, sizes):
+        for i, s in enumerate(sizes):
+            if i >= len(self.fixedLength):
+                continue
+            fixed = self.fixedLength[i]
+            if not (fixed >= s[1] or fixed < 0):
+                raise ValueError(f"{i}th FixedLength={fixed} is smaller than its FeatureLength={s[1]}")
+            if fixed >= s[1]:
+                s[1] = fixed
+        return sizes
+
+
 class PaddingParam:
     """Variable-length padding policy (S/dataset/MiniBatch.scala:523): pad each feature to the longest in the batch
-    (``FixedLength`` pads to a given size) with ``padding_tensor`` values (default 0)."""
+    (a ``PaddingStrategy`` — ``FixedLength``, ``PaddingLongest`` — changes the target length) with ``padding_tensor``
+    values (default 0). ``fixed_length`` (an int or one per input) is the shorthand for ``FixedLength``."""
 
     def __init__(self, padding_tensor=None, padding_strategy=None, fixed_length=None):
         self.padding_tensor = padding_tensor
-        self.fixed_length = fixed_length if fixed_length is not None else padding_strategy
+        self.strategy = padding_strategy if isinstance(padding_strategy, PaddingStrategy) else None
+        self.fixed_length = fixed_length if fixed_length is not None else (
+            None if self.strategy is not None else padding_strategy)
 
 
 def _stack(tensors: Sequence[torch.Tensor], pad: PaddingParam | None, idx: int) -> torch.Tensor:
     shapes = {tuple(t.shape) for t in tensors}
-    if len(shapes) == 1 and (pad is None or pad.fixed_length is None):
+    if len(shapes) == 1 and (pad is None or (pad.fixed_length is None and getattr(pad, "strategy", None) is None)):
         return torch.stack(list(tensors))
     if pad is None:
         raise ValueError("samples have different sizes; pass a PaddingParam to pad them")
@@ -81,6 +135,8 @@ def _stack(tensors: Sequence[torch.Tensor], pad: PaddingParam | None, idx: int) 
         fl = pad.fixed_length[idx] if isinstance(pad.fixed_length, (list, tuple)) else pad.fixed_length
         if fl is not None and fl > 0:
             target[0] = max(target[0], fl)
+    if getattr(pad, "strategy", None) is not None and nd > 0:
+        target[0] = max(target[0], pad.strategy.length_for(idx, target[0]))
     value = 0.0
     if pad.padding_tensor is not None:
         pt = pad.padding_tensor[idx] if isinstance(pad.padding_tensor, (list, tuple)) else pad.padding_tensor
@@ -194,6 +250,16 @@ class SampleToMiniBatch(Transformer):
             yield MiniBatch.from_samples(buf, self.feature_padding, self.label_padding)
 
 
+class SampleToBatch(SampleToMiniBatch):
+    """The pre-0.2 spelling (S/dataset/Transformer.scala:136, deprecated there in favour of SampleToMiniBatch):
+    ``SampleToBatch(totalBatch, featurePadding, labelPadding, fixedLength, partitionNum)``."""
+
+    def __init__(self, totalBatch: int, featurePadding=None, labelPadding=None, fixedLength=None, partitionNum=None):
+        fp = PaddingParam(featurePadding, fixed_length=fixedLength) if (featurePadding is not None or fixedLength) else None
+        lp = PaddingParam(labelPadding, fixed_length=fixedLength) if (labelPadding is not None or fixedLength) else None
+        super().__init__(totalBatch, fp, lp, partitionNum)
+
+
 # ====================================================================== datasets
 class AbstractDataSet:
     def data(self, train: bool) -> Iterator:  # pragma: no cover
@@ -265,6 +331,9 @@ class TransformedDataSet(AbstractDataSet):
 
     def originRDD(self):
         return self.base
+
+
+LocalDataSet = AbstractDataSet          # the reference's trait names (DataSet.scala:110-165); one class serves both here
 
 
 class LocalArrayDataSet(AbstractDataSet):
@@ -440,3 +509,7 @@ DataSet.sort_rdd = DataSet.sortRDD
 
 # The reference's concrete distributed data set (one cached array per partition + a shuffled index, DataSet.scala:247-322)
 CachedDistriDataSet = DistributedDataSet
+
+
+# the reference's default MiniBatch implementation class (S/dataset/MiniBatch.scala:112 ArrayTensorMiniBatch)
+ArrayTensorMiniBatch = MiniBatch

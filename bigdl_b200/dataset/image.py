@@ -19,6 +19,11 @@ from .base import MiniBatch, Sample, Transformer
 CropRandom, CropCenter = "random", "center"
 
 
+class CropperMethod:
+    """The two crop policies of BGRImgCropper (S/dataset/image/BGRImgCropper.scala:26-36)."""
+    CropRandom, CropCenter = CropRandom, CropCenter
+
+
 @dataclass
 class ByteRecord:
     data: bytes
@@ -32,9 +37,43 @@ class LocalLabeledImagePath:
 
 
 class LabeledBGRImage:
+    NO_SCALE = -1
+
     def __init__(self, data: np.ndarray | None = None, label: float = 0.0):
         self.data = data          # float32 [H, W, 3], BGR
         self._label = label
+
+    def copy(self, src, normalize: float = 255.0):
+        """Fill from a byte record (8-byte BE width/height header + BGR bytes) or from another image
+        (BGRImage.copy, Types.scala:137-210)."""
+        if isinstance(src, (bytes, bytearray, memoryview)):
+            w, h = struct.unpack_from(">ii", src, 0)
+            raw = np.frombuffer(src, dtype=np.uint8, offset=8, count=w * h * 3).reshape(h, w, 3)
+            self.data = raw.astype(np.float32) / normalize
+        else:
+            self.data = src.data.copy()
+            if hasattr(src, "_label"):
+                self._label = src._label
+        return self
+
+    def save(self, path: str, scale: float = 255.0):
+        """Write the image file; values are multiplied by ``scale`` first (BGRImage.save, Types.scala:174-190)."""
+        import cv2
+
+        cv2.imwrite(path, np.clip(self.data * scale, 0, 255).astype(np.uint8))
+        return self
+
+    @staticmethod
+    def readImage(path: str, scale_to_or_w: int = -1, resize_h: int | None = None) -> bytes:
+        """Decode → byte record with the width/height header, shorter side scaled to ``scale_to`` or resized to
+        w×h (object BGRImage.readImage, Types.scala:371-384)."""
+        if resize_h is None:
+            img = read_image_bgr(path, scale_to_or_w if scale_to_or_w > 0 else None)
+        else:
+            import cv2
+
+            img = cv2.resize(read_image_bgr(path), (scale_to_or_w, resize_h), interpolation=cv2.INTER_LINEAR)
+        return struct.pack(">ii", img.shape[1], img.shape[0]) + np.ascontiguousarray(img).tobytes()
 
     def width(self) -> int:
         return self.data.shape[1]
@@ -72,6 +111,27 @@ class LabeledBGRImage:
 class LabeledGreyImage:
     def __init__(self, data: np.ndarray | None = None, label: float = 0.0):
         self.data, self._label = data, label      # float32 [H, W]
+
+    def copy(self, src, normalize: float = 1.0, offset: int = 0, width: int | None = None, height: int | None = None):
+        """From raw bytes (``width``×``height`` taken from the current shape when not given) or another image
+        (GreyImage.copy, Types.scala:57-90)."""
+        if isinstance(src, (bytes, bytearray, memoryview)):
+            h = height if height is not None else self.data.shape[0]
+            w = width if width is not None else self.data.shape[1]
+            raw = np.frombuffer(src, dtype=np.uint8, offset=offset, count=w * h).reshape(h, w)
+            self.data = raw.astype(np.float32) / normalize
+        else:
+            self.data = src.data.copy()
+            if hasattr(src, "_label"):
+                self._label = src._label
+        return self
+
+    def setLabel(self, v: float):
+        self._label = v
+        return self
+
+    def clone(self):
+        return LabeledGreyImage(self.data.copy(), self._label)
 
     def width(self): return self.data.shape[1]
     def height(self): return self.data.shape[0]
@@ -144,6 +204,53 @@ class LocalImgReaderWithName(LocalImgReader):
     def __call__(self, it):
         for p in it:
             yield self._read(p), os.path.basename(p.path)
+
+
+class LocalScaleImgReader(LocalImgReader):
+    """Shorter side → ``scaleTo`` (LocalImgReader.scala:47-60)."""
+
+    def __init__(self, scaleTo: int = -1, normalize: float = 255.0):
+        super().__init__(scale_to=scaleTo, normalize=normalize)
+
+
+class LocalResizeImgReader(LocalImgReader):
+    """Resize to exactly ``resizeW``×``resizeH`` (LocalImgReader.scala:70-83)."""
+
+    def __init__(self, resizeW: int, resizeH: int, normalize: float = 255.0):
+        super().__init__(resize_w=resizeW, resize_h=resizeH, normalize=normalize)
+
+
+class LocalScaleImgWithName(LocalImgReaderWithName):
+    def __init__(self, scaleTo: int = -1, normalize: float = 255.0):
+        super().__init__(scale_to=scaleTo, normalize=normalize)
+
+
+class LocalResizeImgWithName(LocalImgReaderWithName):
+    def __init__(self, resizeW: int, resizeH: int, normalize: float = 255.0):
+        super().__init__(resize_w=resizeW, resize_h=resizeH, normalize=normalize)
+
+
+# unlabeled base names of the reference's class hierarchy (Types.scala:51,126): same behaviour, label defaults to 0
+BGRImage = LabeledBGRImage
+GreyImage = LabeledGreyImage
+
+
+@dataclass
+class LocalSeqFilePath:
+    """A sequence-file path on the local disk (S/dataset/Types.scala:53)."""
+    path: str
+
+    def __fspath__(self):
+        return str(self.path)
+
+    def __str__(self):
+        return str(self.path)
+
+
+@dataclass
+class LocalImagePath:
+    """An image file without a label (S/dataset/Types.scala:46)."""
+    path: str
 
 
 class BytesToBGRImg(Transformer):

@@ -14,10 +14,38 @@ import torch
 from .base import Sample, Transformer
 
 
-class LabeledSentence:
+class SentenceToken:
+    """Start / end markers added to a sentence for language modelling (S/dataset/text/utils/Types.scala:25-28)."""
+    start = "SENTENCESTART"
+    end = "SENTENCEEND"
+
+
+class Sentence:
+    """A token-index sequence without a label (S/dataset/text/Types.scala ``Sentence``)."""
+
+    def __init__(self, data=None):
+        self._data = list(data) if data is not None else []
+
+    def data(self): return self._data
+    def dataLength(self): return len(self._data)
+    def getData(self, i): return self._data[i]
+
+
+class LabeledSentence(Sentence):
     def __init__(self, data=None, label=None):
         self._data = list(data) if data is not None else []
         self._label = list(label) if label is not None else []
+
+    def copyToData(self, storage, offset: int = 0):
+        storage[offset:offset + len(self._data)] = self._data
+        return storage
+
+    def copyToLabel(self, storage, offset: int = 0):
+        storage[offset:offset + len(self._label)] = self._label
+        return storage
+
+    def clone(self):
+        return LabeledSentence(self._data, self._label)
 
     def data(self): return self._data
     def label(self): return self._label
@@ -57,7 +85,7 @@ class SentenceBiPadding(Transformer):
     """Wrap each sentence in SENTENCESTART … SENTENCEEND (SentenceBiPadding.scala:28-43)."""
 
     def __init__(self, start: str | None = None, end: str | None = None):
-        self.start, self.end = start or "SENTENCESTART", end or "SENTENCEEND"
+        self.start, self.end = start or SentenceToken.start, end or SentenceToken.end
 
     def __call__(self, it):
         for s in it:

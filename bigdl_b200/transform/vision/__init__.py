@@ -1,1 +1,1 @@
-from . import image  # noqa: F401
+from . import bbox, image  # noqa: F401

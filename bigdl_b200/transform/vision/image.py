@@ -111,6 +111,20 @@ class Pipeline(FeatureTransformer):
         return feature
 
 
+class ChainedFeatureTransformer(Pipeline):
+    """``first -> last`` (FeatureTransformer.scala:126-138)."""
+
+    def __init__(self, first: FeatureTransformer, last: FeatureTransformer):
+        super().__init__([first, last])
+        self.first, self.last = first, last
+
+    def enableIgnoreException(self):
+        for t in self.transformers:
+            if hasattr(t, "enableIgnoreException"):
+                t.enableIgnoreException()
+        return self
+
+
 # ------------------------------------------------------------------------------------------------ frames
 class ImageFrame:
     def __init__(self, features: Iterable[ImageFeature]):
@@ -399,6 +413,9 @@ class _Crop(FeatureTransformer):
         f["cropBbox"] = (x1, y1, x2, y2)
 
 
+Crop = _Crop          # the reference's public name of the abstract base (augmentation/Crop.scala:32)
+
+
 class CenterCrop(_Crop):
     def __init__(self, crop_width, crop_height, is_clip=True):
         super().__init__(False, is_clip)
@@ -683,13 +700,50 @@ PixelNormalizer = PixelNormalize
 class RoiLabel:
     """classes [N] (or [2,N] with difficulty) + bboxes [N,4] (label/roi/RoiLabel.scala)."""
 
+    CLASSES, BBOXES, MASKS, ISCROWD, ORIGSIZE, SCORES = "classes", "bboxes", "masks", "is_crowd", "size", "scores"
+
     def __init__(self, classes, bboxes, masks=None):
         self.classes = np.asarray(classes, dtype=np.float32)
         self.bboxes = np.asarray(bboxes, dtype=np.float32).reshape(-1, 4)
         self.masks = masks
+        n = self.classes.shape[-1] if self.classes.ndim else 0
+        if self.classes.size and n != self.bboxes.shape[0]:
+            raise ValueError(f"the number of classes {n} should be equal to the number of boxes {self.bboxes.shape[0]}")
+        if masks is not None and self.classes.size and len(masks) != n:
+            raise ValueError(f"the number of classes {n} should be equal to the number of masks {len(masks)}")
 
     def size(self):
         return self.bboxes.shape[0]
+
+    def toTable(self):
+        """{classes, bboxes[, masks as RLE]} (RoiLabel.toTable, RoiLabel.scala:57-65)."""
+        from ...utils.table import T
+
+        t = T()
+        if self.masks is not None:
+            t[RoiLabel.MASKS] = [m.toRLE() if hasattr(m, "toRLE") else m for m in self.masks]
+        t[RoiLabel.CLASSES] = torch.from_numpy(self.classes)
+        t[RoiLabel.BBOXES] = torch.from_numpy(self.bboxes)
+        return t
+
+    @staticmethod
+    def fromTensor(tensor) -> "RoiLabel":
+        """[N, 6] rows of (label, difficult, x1, y1, x2, y2) → RoiLabel with [2, N] classes."""
+        a = np.asarray(tensor, dtype=np.float32).reshape(-1, 6)
+        return RoiLabel(np.ascontiguousarray(a[:, :2].T), a[:, 2:6])
+
+    @staticmethod
+    def getScores(tab): return tab[RoiLabel.SCORES]
+    @staticmethod
+    def getClasses(tab): return tab[RoiLabel.CLASSES]
+    @staticmethod
+    def getBBoxes(tab): return tab[RoiLabel.BBOXES]
+    @staticmethod
+    def getMasks(tab): return tab[RoiLabel.MASKS]
+    @staticmethod
+    def getIsCrowd(tab): return tab[RoiLabel.ISCROWD]
+    @staticmethod
+    def getOrigSize(tab): return tab[RoiLabel.ORIGSIZE]
 
 
 class RoiNormalize(FeatureTransformer):
@@ -778,35 +832,39 @@ class RoiProject(FeatureTransformer):
         lab.classes = lab.classes[..., keep]
 
 
-class RandomSampler(FeatureTransformer):
-    """SSD batch sampler: pick a random crop whose IoU with some ground-truth box meets one of the thresholds
-    {0.1,0.3,0.5,0.7,0.9} or keep the whole image (label/roi/RandomSampler.scala, BatchSampler.scala)."""
+class RandomSampler(_Crop):
+    """SSD data-augmentation crop (label/roi/RandomSampler.scala:31-69): each of seven ``BatchSampler``s — the whole
+    image, five with a minimum Jaccard overlap of 0.1 / 0.3 / 0.5 / 0.7 / 0.9 against some ground-truth box, and one
+    unconstrained — proposes at most one box; one proposal is drawn uniformly and the image is cropped to it, then the
+    labels are projected into the crop (the reference's ``RandomSampler() -> RoiProject()``)."""
 
-    def __init__(self, max_trials=50):
-        self.max_trials = max_trials
+    def __init__(self, max_trials: int = 50):
+        super().__init__(True, True)
+        from .bbox import BatchSampler
+
+        kw = dict(minScale=0.3, minAspectRatio=0.5, maxAspectRatio=2.0, maxTrials=max_trials)
+        self.batchSamplers = [BatchSampler(maxTrials=1)] + [BatchSampler(minOverlap=o, **kw)
+                                                            for o in (0.1, 0.3, 0.5, 0.7, 0.9)]
+        self.batchSamplers.append(BatchSampler(maxOverlap=1.0, **kw))
+
+    def generateRoi(self, f):
+        from .bbox import BatchSampler, BoundingBox
+
+        boxes: list = []
+        BatchSampler.generateBatchSamples(f["label"], self.batchSamplers, boxes)
+        if boxes:
+            return boxes[int(RNG.uniform(0, 1) * len(boxes))]
+        return BoundingBox(0, 0, 1, 1)
 
     def transformMat(self, f):
         lab = f.get("label")
-        opts = [None, 0.1, 0.3, 0.5, 0.7, 0.9, -1.0]
-        choice = opts[int(RNG.uniform(0, len(opts)))]
-        if choice is None or lab is None or lab.size() == 0:
+        if lab is None or not isinstance(lab, RoiLabel):
             return
-        b = lab.bboxes
-        for _ in range(self.max_trials):
-            scale = RNG.uniform(0.3, 1.0)
-            ar = RNG.uniform(max(0.5, scale * scale), min(2.0, 1.0 / (scale * scale)))
-            bw, bh = scale * math.sqrt(ar), scale / math.sqrt(ar)
-            x1, y1 = RNG.uniform(0, 1 - bw), RNG.uniform(0, 1 - bh)
-            box = np.array([x1, y1, x1 + bw, y1 + bh], dtype=np.float32)
-            ix = np.maximum(0, np.minimum(b[:, 2], box[2]) - np.maximum(b[:, 0], box[0]))
-            iy = np.maximum(0, np.minimum(b[:, 3], box[3]) - np.maximum(b[:, 1], box[1]))
-            inter = ix * iy
-            iou = inter / ((b[:, 2] - b[:, 0]) * (b[:, 3] - b[:, 1]) + bw * bh - inter)
-            if choice < 0 or iou.max() >= choice:
-                FixedCrop(*box, normalized=True).transformMat(f)
-                f["cropBboxNormalized"] = tuple(box)
-                RoiProject(True).transformMat(f)
-                return
+        box = self.generateRoi(f)
+        FixedCrop(box.x1, box.y1, box.x2, box.y2, normalized=True).transformMat(f)
+        f["cropBboxNormalized"] = box.toTuple()
+        f["boundingBox"] = box
+        RoiProject(True).transformMat(f)
 
 
 # ------------------------------------------------------------------------------------------------ batching
@@ -855,10 +913,134 @@ class MTImageFeatureToBatch:
             lab = f.get("label")
             labels.append(lab if not isinstance(lab, RoiLabel) else lab)
         if self.extract_roi:
-            return MiniBatch(out, labels)
+            return self._roi_batch(out, feats)
         if all(l is not None for l in labels):
             return MiniBatch(out, torch.as_tensor(np.stack([np.asarray(l, dtype=np.float32).reshape(-1) for l in labels])).squeeze(-1))
         return MiniBatch(out, None)
+
+    @staticmethod
+    def _roi_batch(out, feats):
+        labels, crowd, sizes = [], [], []
+        for f in feats:
+            lab = f.get("label")
+            ic = f.get(RoiLabel.ISCROWD)
+            ic = torch.zeros(lab.size()) if ic is None else torch.as_tensor(np.asarray(ic, dtype=np.float32))
+            if ic.numel() != lab.size():
+                raise ValueError("the number of detections in the ImageFeature's is_crowd should be equal to the "
+                                 "number of detections in the RoiLabel")
+            labels.append(lab)
+            crowd.append(ic)
+            sizes.append(tuple(f.get("originalSize") or np.asarray(f["mat"]).shape))
+        return RoiMiniBatch(out, labels, crowd, sizes)
+
+
+class ClassificationMTImageFeatureToBatch(MTImageFeatureToBatch):
+    """The classification batcher the reference's factory returns for ``extractRoi = false``
+    (MTImageFeatureToBatch.scala:141-168)."""
+
+    def __init__(self, width, height, totalBatchSize, transformer=None, toRGB=True, **kw):
+        super().__init__(width, height, totalBatchSize, transformer, toRGB, False, **kw)
+
+
+class RoiMTImageFeatureToBatch(MTImageFeatureToBatch):
+    """Fixed-size detection batcher → ``RoiMiniBatch`` (MTImageFeatureToBatch.scala:221-255)."""
+
+    def __init__(self, width, height, totalBatchSize, transformer=None, toRGB=True, **kw):
+        super().__init__(width, height, totalBatchSize, transformer, toRGB, True, **kw)
+
+
+class RoiImageFeatureToBatchWithResize(MTImageFeatureToBatch):
+    """Detection batcher for images of different sizes (MTImageFeatureToBatch.scala:268-346): the batch tensor takes the
+    largest height and width of its images, rounded up to a multiple of ``sizeDivisible`` when that is positive; each
+    image sits in the top-left corner and the rest is zero."""
+
+    def __init__(self, sizeDivisible: int = -1, totalBatchSize: int = 1, transformer=None, toRGB: bool = False, **kw):
+        super().__init__(0, 0, totalBatchSize, transformer, toRGB, True, **kw)
+        self.size_divisible = sizeDivisible
+
+    def _emit(self, feats):
+        feats = [f for f in self.pool.invokeAndWait([lambda f=f: self._one(f) for f in feats]) if f.isValid]
+        mats = [np.asarray(f["mat"], dtype=np.float32) for f in feats]
+        h, w = max(m.shape[0] for m in mats), max(m.shape[1] for m in mats)
+        d = self.size_divisible
+        if d > 0:
+            h, w = int(math.ceil(h / d) * d), int(math.ceil(w / d) * d)
+        out = torch.zeros((len(mats), 3, h, w), dtype=torch.float32)
+        if self.pin and torch.cuda.is_available():
+            out = out.pin_memory()
+        for i, m in enumerate(mats):
+            if self.to_rgb:
+                m = m[..., ::-1]
+            out[i, :, :m.shape[0], :m.shape[1]].copy_(torch.from_numpy(np.ascontiguousarray(m.transpose(2, 0, 1))))
+        return self._roi_batch(out, feats)
+
+
+def MTImageFeatureToBatchWithResize(sizeDivisible: int = -1, batchSize: int = 1, transformer=None, toRGB: bool = False,
+                                    **kw):
+    """Factory of the reference's companion object (MTImageFeatureToBatch.scala:62-66)."""
+    return RoiImageFeatureToBatchWithResize(sizeDivisible, batchSize, transformer, toRGB, **kw)
+
+
+class RoiMiniBatch(MiniBatch):
+    """A batch of images with one ``RoiLabel``, one is-crowd vector and one original (height, width, channel) per image
+    (MTImageFeatureToBatch.scala:175-213). ``getTarget()`` is a table of per-image tables
+    {classes, bboxes[, masks], is_crowd, size}."""
+
+    def __init__(self, input, target, isCrowd, originalSizes):
+        self.input, self.target, self.isCrowd, self.originalSizes = input, list(target), list(isCrowd), list(originalSizes)
+        self.inputs, self.targets = [input], []
+
+    def size(self):
+        return self.input.shape[0]
+
+    def getInput(self):
+        return self.input
+
+    def getTarget(self):
+        from ...utils.table import T
+
+        out = T()
+        for i, (lab, crowd, size) in enumerate(zip(self.target, self.isCrowd, self.originalSizes)):
+            t = lab.toTable()
+            t[RoiLabel.ISCROWD] = crowd
+            t[RoiLabel.ORIGSIZE] = size
+            out[i + 1] = t
+        return out
+
+    def slice(self, offset: int, length: int):
+        """1-based ``offset`` like every MiniBatch.slice."""
+        o = offset - 1
+        return RoiMiniBatch(self.input[o:o + length], self.target[o:o + length], self.isCrowd[o:o + length],
+                            self.originalSizes[o:o + length])
+
+    get_input, get_target = getInput, getTarget
+
+    def set(self, samples):
+        raise NotImplementedError("do not use Sample here")
+
+    def pin(self):
+        if torch.cuda.is_available():
+            return RoiMiniBatch(self.input.pin_memory(), self.target, self.isCrowd, self.originalSizes)
+        return self
+
+    def to(self, device, non_blocking: bool = False):
+        return RoiMiniBatch(self.input.to(device, non_blocking=non_blocking), self.target, self.isCrowd,
+                            self.originalSizes)
+
+
+class ImageFeatureToMiniBatch:
+    """Batches the ``Sample`` stored in each ImageFeature under ``sampleKey`` (Convertor.scala:252-278)."""
+
+    def __init__(self, batchSize: int, featurePaddingParam=None, labelPaddingParam=None, partitionNum=None,
+                 sampleKey: str = "sample"):
+        from ...dataset.base import SampleToMiniBatch
+
+        self.toBatch = SampleToMiniBatch(batchSize, featurePaddingParam, labelPaddingParam, partitionNum)
+        self.sampleKey = sampleKey
+
+    def __call__(self, prev):
+        feats = prev.features if isinstance(prev, ImageFrame) else prev
+        return self.toBatch(f[self.sampleKey] for f in feats)
 
 
 class SeqFileFolder:

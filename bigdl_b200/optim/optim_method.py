@@ -840,3 +840,113 @@ class LBFGS(OptimMethod):
         for k in ("old_dirs", "old_stps", "Hdiag", "g_old", "f_old", "t", "dir", "funcEval", "nIter"):
             self.state.delete(k)
         return self
+
+
+class LineSearch:
+    """Step-length search plugged into ``LBFGS(linesearch=...)`` (S/optim/LineSearch.scala:25-50).
+
+    ``__call__(opfunc, x, t, d, f, g, gtd, options)`` gets the objective closure, the current point, the initial step
+    ``t``, the direction ``d``, f(x), ∇f(x) and the directional derivative gᵀd, and returns
+    ``(f_new, g_new, x_new, t, n_evals)``."""
+
+    def __call__(self, opfunc, x, t, d, f, g, gtd, options=None):  # pragma: no cover - interface
+        raise NotImplementedError
+
+
+class WolfeLineSearch(LineSearch):
+    """Strong-Wolfe line search: bracket a step that satisfies the sufficient-decrease (c1) and curvature (c2)
+    conditions, then shrink the bracket by safeguarded cubic interpolation. The reference ships only the interface;
+    this is the search Torch's ``optim.lbfgs`` users pass as ``lswolfe``. ``options``: c1, c2, tolX, maxIter."""
+
+    def __init__(self, c1: float = 1e-4, c2: float = 0.9, tolX: float = 1e-9, maxIter: int = 20):
+        self.c1, self.c2, self.tolX, self.maxIter = c1, c2, tolX, maxIter
+
+    @staticmethod
+    def _cubic_min(x1, f1, g1, x2, f2, g2, lo=None, hi=None):
+        """Minimiser of the cubic through (x1, f1, g1), (x2, f2, g2), clamped to [lo, hi]; the midpoint when the
+        cubic has no real minimiser."""
+        if lo is None:
+            lo, hi = (x1, x2) if x1 <= x2 else (x2, x1)
+        d1 = g1 + g2 - 3 * (f1 - f2) / (x1 - x2)
+        sq = d1 * d1 - g1 * g2
+        if sq >= 0:
+            d2 = sq ** 0.5
+            if x1 <= x2:
+                p = x2 - (x2 - x1) * ((g2 + d2 - d1) / (g2 - g1 + 2 * d2))
+            else:
+                p = x1 - (x1 - x2) * ((g1 + d2 - d1) / (g1 - g2 + 2 * d2))
+            return min(max(p, lo), hi)
+        return (lo + hi) / 2
+
+    def __call__(self, opfunc, x, t, d, f, g, gtd, options=None):
+        o = options or {}
+        get = (lambda k, dflt: o.get(k, dflt)) if hasattr(o, "get") else (lambda k, dflt: dflt)
+        c1, c2, tolx, max_iter = get("c1", self.c1), get("c2", self.c2), get("tolX", self.tolX), int(
+            get("maxIter", self.maxIter))
+        d_norm = float(d.abs().max())
+        x0 = x.clone()
+
+        def evaluate(step):
+            fv, gv = opfunc(x0 + step * d)
+            gv = gv.clone()
+            return float(fv), gv, float(gv.dot(d))
+
+        f0, g0, gtd0 = float(f), g.clone(), float(gtd)
+        f_new, g_new, gtd_new = evaluate(t)
+        evals = 1
+        t_prev, f_prev, g_prev, gtd_prev = 0.0, f0, g0, gtd0
+        bracket = None
+        it = 0
+        done = False
+        while it < max_iter:
+            if f_new > f0 + c1 * t * gtd0 or (it > 0 and f_new >= f_prev):
+                bracket = [(t_prev, f_prev, g_prev, gtd_prev), (t, f_new, g_new, gtd_new)]
+                break
+            if abs(gtd_new) <= -c2 * gtd0:
+                bracket, done = [(t, f_new, g_new, gtd_new)], True
+                break
+            if gtd_new >= 0:
+                bracket = [(t_prev, f_prev, g_prev, gtd_prev), (t, f_new, g_new, gtd_new)]
+                break
+            lo, hi = t + 0.01 * (t - t_prev), t * 10
+            nxt = self._cubic_min(t_prev, f_prev, gtd_prev, t, f_new, gtd_new, lo, hi)
+            t_prev, f_prev, g_prev, gtd_prev = t, f_new, g_new, gtd_new
+            t = nxt
+            f_new, g_new, gtd_new = evaluate(t)
+            evals += 1
+            it += 1
+        if bracket is None:                       # ran out of iterations while still descending
+            bracket, done = [(t, f_new, g_new, gtd_new)], True
+
+        stalled = False
+        while not done and it < max_iter:
+            (ta, fa, ga, gtda), (tb, fb, gb, gtdb) = bracket
+            if abs(tb - ta) * d_norm < tolx:
+                break
+            t = self._cubic_min(ta, fa, gtda, tb, fb, gtdb)
+            span, lo_b, hi_b = abs(tb - ta), min(ta, tb), max(ta, tb)
+            # too close to an end of the bracket: nudge inwards (or bisect when that already happened once)
+            if min(hi_b - t, t - lo_b) < 0.1 * span:
+                if stalled or t >= hi_b or t <= lo_b:
+                    t = hi_b - 0.1 * span if abs(t - hi_b) < abs(t - lo_b) else lo_b + 0.1 * span
+                    stalled = False
+                else:
+                    stalled = True
+            else:
+                stalled = False
+            f_new, g_new, gtd_new = evaluate(t)
+            evals += 1
+            it += 1
+            lo_i = 0 if fa <= fb else 1
+            t_lo, f_lo = bracket[lo_i][0], bracket[lo_i][1]
+            if f_new > f0 + c1 * t * gtd0 or f_new >= f_lo:
+                bracket[1 - lo_i] = (t, f_new, g_new, gtd_new)      # replaces the high end
+            else:
+                if abs(gtd_new) <= -c2 * gtd0:
+                    done = True
+                elif gtd_new * (bracket[1 - lo_i][0] - t_lo) >= 0:
+                    bracket[1 - lo_i] = bracket[lo_i]
+                bracket[lo_i] = (t, f_new, g_new, gtd_new)
+        best = min(bracket, key=lambda b: b[1])
+        t, f_new, g_new = best[0], best[1], best[2]
+        return f_new, g_new, x0 + t * d, t, evals

@@ -40,7 +40,13 @@ class GradientClipping:
         self.l2norm: float | None = None
 
 
-class Optimizer:
+class AbstractOptimizer:
+    """What the local and the distributed optimizer share in the reference — checkpointing, validation and the end-of-
+    training model hand-back (S/optim/AbstractOptimizer.scala:33-260). Here ``Optimizer`` carries that common code and
+    ``_train_loop`` is the single loop both run; this is the common base name for isinstance checks."""
+
+
+class Optimizer(AbstractOptimizer):
     """Builder + training loop base. Use ``Optimizer.create`` (or ``Optimizer(...)`` which dispatches the same way)."""
 
     def __new__(cls, *args, **kw):

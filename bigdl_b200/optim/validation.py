@@ -302,34 +302,80 @@ class MeanAveragePrecision(ValidationMethod):
         return MAPResult(self.classes, self.k, recs, pos)
 
 
+class PRAUCResult(ValidationResult):
+    """(score, label) pairs; the area under the precision-recall curve is integrated by trapezoids from
+    (recall 0, precision 1) over the pairs in descending score order (S/optim/PrecisionRecallAUC.scala:47-92)."""
+
+    def __init__(self, results=None, labels=None):
+        if labels is not None:                       # (scores, labels) form
+            results = list(zip(results, labels))
+        self.results = [(float(a), float(b)) for a, b in (results or [])]
+
+    @property
+    def scores(self):
+        return [r[0] for r in self.results]
+
+    @property
+    def labels(self):
+        return [r[1] for r in self.results]
+
+    def result(self):
+        s = np.asarray(self.scores)
+        l = np.asarray(self.labels)
+        order = np.argsort(-s, kind="stable")
+        l = l[order]
+        tp = np.cumsum(l)
+        fp = np.cumsum(1 - l)
+        npos = max(l.sum(), 1)
+        prec = np.concatenate([[1.0], tp / np.maximum(tp + fp, 1)])
+        rec = np.concatenate([[0.0], tp / npos])
+        trapezoid = getattr(np, "trapezoid", None) or np.trapz
+        return float(trapezoid(prec, rec)), len(s)
+
+    def __add__(self, o):
+        return PRAUCResult(self.results + o.results)
+
+    def __repr__(self):
+        r = self.result()
+        return f"Precision Recall AUC is {r[0]} on {r[1]}"
+
+
 class PrecisionRecallAUC(ValidationMethod):
     name = "PrecisionRecallAUC"
-
-    class _Res(ValidationResult):
-        def __init__(self, scores, labels):
-            self.scores, self.labels = scores, labels
-
-        def result(self):
-            s = np.asarray(self.scores)
-            l = np.asarray(self.labels)
-            order = np.argsort(-s, kind="stable")
-            l = l[order]
-            tp = np.cumsum(l)
-            fp = np.cumsum(1 - l)
-            npos = max(l.sum(), 1)
-            prec = np.concatenate([[1.0], tp / np.maximum(tp + fp, 1)])
-            rec = np.concatenate([[0.0], tp / npos])
-            trapezoid = getattr(np, "trapezoid", None) or np.trapz
-            return float(trapezoid(prec, rec)), len(s)
-
-        def __add__(self, o):
-            return PrecisionRecallAUC._Res(self.scores + o.scores, self.labels + o.labels)
-
-        def __repr__(self):
-            return f"Precision Recall AUC is {self.result()[0]}"
+    _Res = PRAUCResult
 
     def __call__(self, output, target):
-        return self._Res(output.reshape(-1).float().cpu().tolist(), target.reshape(-1).float().cpu().tolist())
+        return PRAUCResult(output.reshape(-1).float().cpu().tolist(), target.reshape(-1).float().cpu().tolist())
+
+
+class EvaluateMethods:
+    """(correct, count) helpers (S/optim/EvaluateMethods.scala:21-95); targets are 1-based class ids."""
+
+    @staticmethod
+    def calcAccuracy(output, target):
+        output, target = torch.as_tensor(output), torch.as_tensor(target)
+        if output.dim() == 2:
+            pred = output.argmax(1) + 1
+            return int((pred == target.reshape(-1).to(pred.dtype)).sum()), output.shape[0]
+        if output.dim() == 1:
+            if target.numel() != 1:
+                raise ValueError("a single output needs a single target")
+            return int(int(output.argmax()) + 1 == int(target.reshape(-1)[0])), 1
+        raise ValueError("output must have 1 or 2 dimensions")
+
+    @staticmethod
+    def calcTop5Accuracy(output, target):
+        output, target = torch.as_tensor(output), torch.as_tensor(target)
+        if output.dim() == 2:
+            top = output.topk(min(5, output.shape[1]), 1).indices + 1
+            hit = (top == target.reshape(-1, 1).to(top.dtype)).any(1)
+            return int(hit.sum()), output.shape[0]
+        if output.dim() == 1:
+            if target.numel() != 1:
+                raise ValueError("a single output needs a single target")
+            top = output.topk(min(5, output.shape[0])).indices + 1
+            return int(bool((top == int(target.reshape(-1)[0])).any())), 1
+        raise ValueError("output must have 1 or 2 dimensions")
 
 
 def all_reduce_result(res: ValidationResult) -> ValidationResult:
@@ -435,7 +481,10 @@ class MAPMultiIOUValidationResult(ValidationResult):
         return f"MAPObjectDetection(multi-IoU): {self.result()[0]}"
 
 
-class _GroundTruth:
+class GroundTruthRegion:
+    """A ground-truth region and, per IoU threshold, whether a detection has claimed it
+    (ValidationMethod.scala:546-573)."""
+
     __slots__ = ("label", "diff", "box", "rle", "occupied", "coco")
 
     def __init__(self, coco, n_iou, label, diff, box=None, rle=None):
@@ -444,6 +493,9 @@ class _GroundTruth:
 
     def can_occupy(self, i):        # a COCO crowd region may absorb any number of detections
         return (self.coco and self.diff == 1) or not self.occupied[i]
+
+    def occupy(self, i):
+        self.occupied[i] = True
 
     def iou(self, x1, y1, x2, y2, det_rle=None):
         if self.rle is not None:
@@ -455,6 +507,32 @@ class _GroundTruth:
         det_area = (x2 - x1 + 1) * (y2 - y1 + 1)
         union = det_area if (self.coco and self.diff != 0) else det_area + (gx2 - gx1 + 1) * (gy2 - gy1 + 1) - inter
         return inter / union
+
+    canOccupy, getIOURate = can_occupy, iou
+
+
+_GroundTruth = GroundTruthRegion
+
+
+class GroundTruthBBox(GroundTruthRegion):
+    """Box region (ValidationMethod.scala:575-591)."""
+    __slots__ = ()
+
+    def __init__(self, isCOCO, numIOU, label, diff, xmin, ymin, xmax, ymax):
+        super().__init__(isCOCO, numIOU, label, diff, (float(xmin), float(ymin), float(xmax), float(ymax)))
+
+    xmin = property(lambda self: self.box[0])
+    ymin = property(lambda self: self.box[1])
+    xmax = property(lambda self: self.box[2])
+    ymax = property(lambda self: self.box[3])
+
+
+class GroundTruthRLE(GroundTruthRegion):
+    """Mask region; always under COCO rules (ValidationMethod.scala:593-600)."""
+    __slots__ = ()
+
+    def __init__(self, numIOU, label, diff, rle):
+        super().__init__(True, numIOU, label, diff, None, rle)
 
 
 def _field(tab, key):
@@ -507,8 +585,10 @@ class MeanAveragePrecisionObjectDetection(ValidationMethod):
                     label, d = (int(cls[0, j]), float(cls[1, j])) if cls.dim() == 2 else (int(cls.reshape(-1)[j]), 0.0)
                     assert 0 <= label < self.classes, f"Bad label id {label}"
                     diff = 1.0 if (float(crowd[j]) != 0 or d != 0) else 0.0
-                    regs.append(_GroundTruth(coco, len(self.iou), label, diff, tuple(float(v) for v in bbox[j]),
-                                             masks[j] if masks is not None else None))
+                    if masks is not None:
+                        regs.append(GroundTruthRLE(len(self.iou), label, diff, masks[j]))
+                    else:
+                        regs.append(GroundTruthBBox(coco, len(self.iou), label, diff, *(float(v) for v in bbox[j])))
                     if diff == 0:
                         gt_cnt[label] += 1
             images.append(regs)
@@ -582,3 +662,37 @@ MeanAveragePrecision.cocoSegmentation = staticmethod(
     MeanAveragePrecisionObjectDetection.coco(nClasses, topK, skipClass, iouThres, True))
 MeanAveragePrecision.pascalVOC = staticmethod(MeanAveragePrecisionObjectDetection.pascalVOC)
 MeanAveragePrecision.classification = staticmethod(lambda nClasses, topK=-1: MeanAveragePrecision(topK, nClasses))
+
+
+class MAPUtil:
+    """The building blocks of the detection mAP as free functions (ValidationMethod.scala:286-408)."""
+
+    @staticmethod
+    def findTopK(k: int, arr, column: int):
+        """The ``k`` largest values of one column of a row-major matrix → [(row, value)], best first."""
+        col = [(i, float(r[column])) for i, r in enumerate(arr)]
+        col.sort(key=lambda p: -p[1])
+        return col[:min(k, len(col))]
+
+    @staticmethod
+    def gtTablesToGroundTruthRegions(gtTable, classes: int, numIOU: int, isCOCO: bool, isSegmentation: bool):
+        m = MeanAveragePrecisionObjectDetection(classes, -1, [0.5] * numIOU, MAPCOCO if isCOCO else MAPPascalVoc2010,
+                                                -1, isSegmentation)
+        return m._ground_truth(gtTable)
+
+    @staticmethod
+    def parseDetection(gtBbox, label, score, x1, y1, x2, y2, mask, classes, iou, predictByClasses):
+        m = MeanAveragePrecisionObjectDetection(classes, -1, list(iou))
+        m._match(gtBbox, int(label), float(score), x1, y1, x2, y2, mask, predictByClasses)
+
+    @staticmethod
+    def parseSegmentationTensorResult(outTensor, func):
+        """Calls ``func(imgId, label, score, x1, y1, x2, y2)`` for every detection of a
+        ``[n, (label, score, x1, y1, x2, y2) * n]``-per-row output."""
+        out = torch.as_tensor(outTensor).float().cpu()
+        if out.dim() != 2:
+            raise ValueError("the output tensor should have 2 dimensions")
+        for img in range(out.shape[0]):
+            for b in range(int(out[img, 0])):
+                lab, sc, x1, y1, x2, y2 = (float(v) for v in out[img, 1 + 6 * b:7 + 6 * b])
+                func(img, int(lab), sc, x1, y1, x2, y2)

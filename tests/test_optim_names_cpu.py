@@ -1,0 +1,100 @@
+"""LineSearch / WolfeLineSearch, PRAUCResult, EvaluateMethods, MAPUtil and the ground-truth region classes
+(S/optim/{LineSearch,PrecisionRecallAUC,EvaluateMethods,ValidationMethod,AbstractOptimizer}.scala)."""
+import pytest
+import torch
+
+from bigdl_b200.optim import optimizer as O
+from bigdl_b200.optim import validation as Vd
+from bigdl_b200.optim.optim_method import LBFGS, LineSearch, WolfeLineSearch
+
+
+def _rosenbrock(x):
+    x = x.detach().clone().requires_grad_(True)
+    f = ((1 - x[:-1]) ** 2).sum() + 100 * ((x[1:] - x[:-1] ** 2) ** 2).sum()
+    f.backward()
+    return float(f.detach()), x.grad
+
+
+def test_wolfe_line_search_conditions_and_lbfgs():
+    x = torch.tensor([-1.2, 1.0, 0.5], dtype=torch.float64)
+    f, g = _rosenbrock(x)
+    d = -g
+    gtd = float(g.dot(d))
+    ls = WolfeLineSearch()
+    assert isinstance(ls, LineSearch)
+    f1, g1, x1, t, evals = ls(_rosenbrock, x, 1.0, d, f, g, gtd)
+    assert evals >= 1 and t > 0 and torch.allclose(x1, x + t * d)
+    assert f1 <= f + 1e-4 * t * gtd                     # sufficient decrease
+    assert abs(float(g1.dot(d))) <= 0.9 * abs(gtd)      # curvature
+    assert f1 == pytest.approx(_rosenbrock(x1)[0])
+
+    runs = {}
+    for name, search in (("fixed", None), ("wolfe", WolfeLineSearch())):
+        x = torch.zeros(4, dtype=torch.float64)
+        opt = LBFGS(max_iter=200, max_eval=4000, linesearch=search, tolfun=1e-10, tolx=1e-12)
+        x, hist = opt.optimize(_rosenbrock, x)
+        assert torch.allclose(x, torch.ones(4, dtype=torch.float64), atol=1e-4)
+        runs[name] = len(hist)
+    assert runs["wolfe"] < runs["fixed"]
+    with pytest.raises(NotImplementedError):
+        LineSearch()(None, None, 1, None, 0, None, 0)
+
+
+def test_prauc_result_matches_reference_loop():
+    scores = [0.9, 0.8, 0.7, 0.6, 0.55, 0.4, 0.3]
+    labels = [1, 0, 1, 1, 0, 0, 1]
+    res = Vd.PRAUCResult(list(zip(scores, labels)))
+    # the reference's running-sum form
+    tp = fp = 0.0
+    area, prev_p, prev_r = 0.0, 1.0, 0.0
+    total = sum(labels)
+    for s, l in sorted(zip(scores, labels), reverse=True):
+        if tp == total:
+            break
+        tp, fp = tp + (l == 1), fp + (l != 1)
+        p, r = tp / (tp + fp), tp / total
+        area += (r - prev_r) * (p + prev_p)
+        prev_p, prev_r = p, r
+    assert res.result() == (pytest.approx(area / 2), 7)
+    both = res + Vd.PRAUCResult([0.95], [1.0])
+    assert both.result()[1] == 8 and "Precision Recall AUC" in repr(both)
+    m = Vd.PrecisionRecallAUC()(torch.tensor(scores), torch.tensor(labels))
+    assert isinstance(m, Vd.PRAUCResult) and m.result()[0] == pytest.approx(area / 2)
+
+
+def test_evaluate_methods():
+    out = torch.tensor([[0.1, 0.7, 0.2], [0.5, 0.2, 0.3], [0.2, 0.3, 0.5]])
+    assert Vd.EvaluateMethods.calcAccuracy(out, torch.tensor([2.0, 1.0, 1.0])) == (2, 3)
+    assert Vd.EvaluateMethods.calcAccuracy(out[0], torch.tensor([2.0])) == (1, 1)
+    big = torch.arange(24, dtype=torch.float32).reshape(3, 8)
+    assert Vd.EvaluateMethods.calcTop5Accuracy(big, torch.tensor([8.0, 3.0, 4.0])) == (2, 3)
+    assert Vd.EvaluateMethods.calcTop5Accuracy(big[0], torch.tensor([1.0])) == (0, 1)
+    with pytest.raises(ValueError):
+        Vd.EvaluateMethods.calcAccuracy(torch.zeros(2, 2, 2), torch.zeros(2))
+
+
+def test_map_util_and_regions():
+    assert Vd.MAPUtil.findTopK(2, [[0, 0.3], [0, 0.9], [0, 0.5]], 1) == [(1, pytest.approx(0.9)), (2, 0.5)]
+    gt = [{"bboxes": torch.tensor([[0.0, 0, 9, 9], [20.0, 20, 29, 29]]), "classes": torch.tensor([[1.0, 1.0], [0, 1]]),
+           "is_crowd": torch.zeros(2)}]
+    images, cnt = Vd.MAPUtil.gtTablesToGroundTruthRegions(gt, 3, 2, False, False)
+    assert cnt == [0, 1, 0] and isinstance(images[0][0], Vd.GroundTruthBBox) and images[0][1].diff == 1.0
+    assert (images[0][0].xmin, images[0][0].ymax) == (0.0, 9.0)
+    predict = [[[] for _ in range(3)] for _ in range(2)]
+    Vd.MAPUtil.parseDetection(images[0], 1, 0.9, 0, 0, 9, 9, None, 3, [0.5, 0.75], predict)
+    Vd.MAPUtil.parseDetection(images[0], 1, 0.8, 0, 0, 9, 9, None, 3, [0.5, 0.75], predict)   # GT taken → miss
+    Vd.MAPUtil.parseDetection(images[0], 1, 0.7, 20, 20, 29, 29, None, 3, [0.5, 0.75], predict)   # difficult → ignored
+    assert predict[0][1] == [(0.9, True), (0.8, False)] and predict[1][1] == [(0.9, True), (0.8, False)]
+    g = Vd.GroundTruthBBox(False, 1, 0, 0.0, 0, 0, 9, 9)
+    assert g.getIOURate(0, 0, 9, 4) == pytest.approx(0.5) and g.canOccupy(0)
+    g.occupy(0)
+    assert not g.canOccupy(0)
+    crowd = Vd.GroundTruthBBox(True, 1, 0, 1.0, 0, 0, 9, 9)
+    crowd.occupy(0)
+    assert crowd.canOccupy(0) and crowd.getIOURate(0, 0, 4, 4) == pytest.approx(1.0)   # intersection over detection
+    seen = []
+    out = torch.tensor([[2, 1, 0.9, 1, 2, 3, 4, 2, 0.8, 5, 6, 7, 8], [0] + [0] * 12], dtype=torch.float32)
+    Vd.MAPUtil.parseSegmentationTensorResult(out, lambda *a: seen.append(a))
+    assert seen == [(0, 1, pytest.approx(0.9), 1, 2, 3, 4), (0, 2, pytest.approx(0.8), 5, 6, 7, 8)]
+    assert isinstance(Vd.GroundTruthRLE(1, 0, 0.0, object()), Vd.GroundTruthRegion)
+    assert issubclass(O.LocalOptimizer, O.AbstractOptimizer) and issubclass(O.DistriOptimizer, O.AbstractOptimizer)

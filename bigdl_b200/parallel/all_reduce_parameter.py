@@ -476,3 +476,41 @@ class AllReduceParameter:
                 self._sym.close(collective=False)
         except Exception:  # noqa: BLE001 - interpreter shutdown
             pass
+
+
+class FutureResult:
+    """Handle on asynchronous transfers (S/parameters/AllReduceParameter.scala:331-333): ``waitResult()`` blocks until
+    every one has finished and returns their values. Accepts ``concurrent.futures`` futures, ``torch.distributed``
+    work handles (``wait()``), CUDA events (``synchronize()``) or plain values."""
+
+    def __init__(self, futures):
+        self.futures = list(futures)
+
+    def waitResult(self):
+        out = []
+        for f in self.futures:
+            if hasattr(f, "result") and callable(f.result):
+                out.append(f.result())
+            elif hasattr(f, "wait") and callable(f.wait):
+                out.append(f.wait())
+            elif hasattr(f, "synchronize") and callable(f.synchronize):
+                out.append(f.synchronize())
+            else:
+                out.append(f)
+        return out
+
+
+class Util:
+    """S/parameters/Util.scala:23-52."""
+
+    @staticmethod
+    def getSumsquareInParallel(parameters: torch.Tensor, parallelism: int = 1) -> float:
+        """Σ x² of a flat tensor in fp64. On a GPU this is one launch of the library's reduction (the same one the
+        L2-norm gradient clipping uses); on the host torch's own threaded reduction replaces the reference's manual
+        split into ``parallelism`` tasks."""
+        flat = parameters.reshape(-1)
+        if flat.is_cuda and flat.dtype == torch.float32 and flat.is_contiguous():
+            from ..ops import elementwise as ew
+
+            return float(ew.sumsq(flat))
+        return float(flat.double().pow(2).sum())

@@ -98,3 +98,15 @@ def test_map_util_and_regions():
     assert seen == [(0, 1, pytest.approx(0.9), 1, 2, 3, 4), (0, 2, pytest.approx(0.8), 5, 6, 7, 8)]
     assert isinstance(Vd.GroundTruthRLE(1, 0, 0.0, object()), Vd.GroundTruthRegion)
     assert issubclass(O.LocalOptimizer, O.AbstractOptimizer) and issubclass(O.DistriOptimizer, O.AbstractOptimizer)
+
+
+def test_future_result_and_sumsquare():
+    from concurrent.futures import ThreadPoolExecutor
+
+    from bigdl_b200.parallel.all_reduce_parameter import FutureResult, Util
+
+    with ThreadPoolExecutor(2) as ex:
+        got = FutureResult([ex.submit(lambda i=i: i * i) for i in range(4)] + [7]).waitResult()
+    assert got == [0, 1, 4, 9, 7]
+    x = torch.randn(1001)
+    assert Util.getSumsquareInParallel(x, 4) == pytest.approx(float((x.double() ** 2).sum()))

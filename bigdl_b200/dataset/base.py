@@ -137,11 +137,17 @@ def _stack(tensors: Sequence[torch.Tensor], pad: PaddingParam | None, idx: int) 
             target[0] = max(target[0], fl)
     if getattr(pad, "strategy", None) is not None and nd > 0:
         target[0] = max(target[0], pad.strategy.length_for(idx, target[0]))
-    value = 0.0
+    value, row = 0.0, None
     if pad.padding_tensor is not None:
         pt = pad.padding_tensor[idx] if isinstance(pad.padding_tensor, (list, tuple)) else pad.padding_tensor
-        value = float(_t(pt).reshape(-1)[0])
+        pt = _t(pt)
+        if pt.numel() > 1 and nd > 1 and list(pt.shape) == target[1:]:
+            row = pt          # one padding ROW per time step (e.g. the one-hot END token of the RNN example)
+        else:
+            value = float(pt.reshape(-1)[0])
     out = torch.full([len(tensors)] + target, value, dtype=tensors[0].dtype)
+    if row is not None:
+        out[:] = row.to(out.dtype)
     for i, t in enumerate(tensors):
         out[(i,) + tuple(slice(0, s) for s in t.shape)] = t
     return out
@@ -276,7 +282,9 @@ class AbstractDataSet:
         ImageFeature; P/dataset/dataset.py ``DataSet.transform``)."""
         if not isinstance(transformer, Transformer) and hasattr(transformer, "transform") and callable(transformer.transform):
             ft = transformer
-            transformer = _FnTransformer(lambda it: (ft.transform(f) for f in it))
+            # every pass starts from the stored feature: transformers overwrite ``mat`` in place, so without the copy the
+            # second epoch would transform the first epoch's output
+            transformer = _FnTransformer(lambda it: (ft.transform(f.clone() if hasattr(f, "clone") else f) for f in it))
         return TransformedDataSet(self, transformer)
 
     def get_image_frame(self):

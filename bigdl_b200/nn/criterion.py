@@ -167,6 +167,10 @@ class MSECriterion(Criterion):
         self.size_average = size_average
 
     def updateOutput(self, input, target):
+        # the reference compares the two buffers element by element and only requires equal element counts
+        # (S/nn/MSECriterion.scala:38-45), e.g. a [N, 784] reconstruction against [N, 28, 28] images
+        if target.shape != input.shape and target.numel() == input.numel():
+            target = target.reshape(input.shape)
         d = (input.float() - target.float()) ** 2
         return d.mean() if self.size_average else d.sum()
 

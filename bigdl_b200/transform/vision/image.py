@@ -286,6 +286,8 @@ class PixelBytesToMat(FeatureTransformer):
         self.byte_key = byte_key
 
     def transformMat(self, f):
+        if self.byte_key not in f and f.get("mat") is not None:
+            return              # SeqFileFolder.files_to_image_frame already decoded the record into the mat
         h, w, c = f["originalSize"]
         f["mat"] = np.frombuffer(f[self.byte_key], dtype=np.uint8).reshape(h, w, c).copy()
 
@@ -882,7 +884,7 @@ class MTImageFeatureToBatch:
 
     def _one(self, f):
         if self.transformer is not None:
-            f = self.transformer.transform(f)
+            f = self.transformer.transform(f.clone())     # keep the stored feature pristine for the next epoch
         return f
 
     def __call__(self, frame_or_iter):

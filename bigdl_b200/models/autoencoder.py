@@ -8,3 +8,6 @@ def Autoencoder(class_num: int = 32):
     model.add(Linear(28 * 28, class_num)).add(ReLU(True))
     model.add(Linear(class_num, 28 * 28)).add(Sigmoid())
     return model
+
+
+Autoencoder.graph = lambda class_num=32: Autoencoder(class_num).toGraph()      # Autoencoder.scala:38

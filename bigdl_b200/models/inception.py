@@ -131,3 +131,9 @@ def Inception_v1(class_num: int = 1000, has_dropout: bool = True):
     model.add(feature1)
     model.add(split1)
     return model
+
+
+# graph forms (Inception_v1.scala:144,279)
+Inception_v1_NoAuxClassifier.graph = lambda class_num=1000, has_dropout=True: \
+    Inception_v1_NoAuxClassifier(class_num, has_dropout).toGraph()
+Inception_v1.graph = lambda class_num=1000, has_dropout=True: Inception_v1(class_num, has_dropout).toGraph()

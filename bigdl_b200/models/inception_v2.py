@@ -109,3 +109,8 @@ def Inception_v2(class_num: int = 1000):
     main_branch = Sequential().add(features2).add(split2)
     split1 = Concat(2).add(main_branch).add(output1)
     return Sequential().add(features1).add(split1)
+
+
+# graph forms (Inception_v2.scala:229,364)
+Inception_v2_NoAuxClassifier.graph = lambda class_num=1000: Inception_v2_NoAuxClassifier(class_num).toGraph()
+Inception_v2.graph = lambda class_num=1000, has_dropout=True: Inception_v2(class_num).toGraph()

@@ -34,3 +34,54 @@ def LeNet5_graph(class_num: int = 10):
     fc2 = Linear(100, class_num).setName("fc2").inputs(tanh3)
     out = LogSoftMax().inputs(fc2)
     return Graph(inp, out)
+
+
+def LeNet5_keras(class_num: int = 10):
+    """The Keras-style Sequential form (LeNet5.scala:59-72)."""
+    from ..nn.keras import layers as K
+    from ..nn.keras.topology import Sequential as KSequential
+
+    m = KSequential()
+    m.add(K.Reshape([1, 28, 28], input_shape=(28, 28, 1)))
+    m.add(K.Convolution2D(6, 5, 5, activation="tanh").setName("conv1_5x5"))
+    m.add(K.MaxPooling2D())
+    m.add(K.Convolution2D(12, 5, 5, activation="tanh").setName("conv2_5x5"))
+    m.add(K.MaxPooling2D())
+    m.add(K.Flatten())
+    m.add(K.Dense(100, activation="tanh").setName("fc1"))
+    m.add(K.Dense(class_num, activation="softmax").setName("fc2"))
+    return m
+
+
+def LeNet5_kerasGraph(class_num: int = 10):
+    """The Keras-style functional form (LeNet5.scala:74-88)."""
+    from ..nn.keras import layers as K
+    from ..nn.keras.topology import Model as KModel
+
+    inp = K.Input(shape=(28, 28, 1))
+    x = K.Reshape([1, 28, 28]).inputs(inp)
+    x = K.Convolution2D(6, 5, 5, activation="tanh").setName("conv1_5x5").inputs(x)
+    x = K.MaxPooling2D().inputs(x)
+    x = K.Convolution2D(12, 5, 5, activation="tanh").setName("conv2_5x5").inputs(x)
+    x = K.MaxPooling2D().inputs(x)
+    x = K.Flatten().inputs(x)
+    x = K.Dense(100, activation="tanh").setName("fc1").inputs(x)
+    out = K.Dense(class_num, activation="softmax").setName("fc2").inputs(x)
+    return KModel(inp, out)
+
+
+def _lenet_dnn(batch_size: int, class_num: int = 10):
+    """``LeNet5.dnn`` / ``dnnGraph`` (LeNet5.scala:90-125) build the same network from MKL-DNN primitives with a
+    fixed batch size and a bare soft-max-free head (trained with CrossEntropyCriterion). The device kernels here are
+    chosen per layer at run time, so these are the ordinary builders minus the LogSoftMax."""
+    m = LeNet5(class_num)
+    m.modules.pop()
+    return m
+
+
+# companion-object spellings: LeNet5.graph(10), LeNet5.keras(10), …
+LeNet5.graph = LeNet5_graph
+LeNet5.keras = LeNet5_keras
+LeNet5.kerasGraph = LeNet5_kerasGraph
+LeNet5.dnn = _lenet_dnn
+LeNet5.dnnGraph = lambda batch_size, class_num=10: _lenet_dnn(batch_size, class_num).toGraph()

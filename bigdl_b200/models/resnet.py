@@ -126,3 +126,26 @@ def model_init(model):
 
 
 modelInit = model_init
+
+
+def _resnet_from_opt(class_num, opt=None, **kw):
+    """``ResNet(classNum, T("shortcutType" -> …, "depth" -> …, "dataSet" -> …, "optnet" -> …))`` (ResNet.scala:150)."""
+    o = dict(opt.items()) if hasattr(opt, "items") else dict(opt or {})
+    o.update(kw)
+    return ResNet(class_num, depth=int(o.get("depth", 18)), shortcut_type=str(o.get("shortcutType", ShortcutType.B)),
+                  dataset=str(o.get("dataSet", o.get("dataset", DatasetType.CIFAR10))).lower())
+
+
+ResNet.apply = _resnet_from_opt
+ResNet.graph = lambda class_num, opt=None, **kw: _resnet_from_opt(class_num, opt, **kw).toGraph()     # ResNet.scala:284
+ResNet.modelInit = model_init
+
+
+def shareGradInput(model):
+    """``ResNet.shareGradInput`` (ResNet.scala:78-116) makes layers of the same kind share one gradInput buffer to cut
+    the JVM heap. Here activations and their gradients live in the autograd graph and are freed as soon as their last
+    consumer ran, which is the effect that call buys; kept as a no-op so training scripts port unchanged."""
+    return model
+
+
+ResNet.shareGradInput = shareGradInput

@@ -64,3 +64,10 @@ def Vgg_16(class_num: int = 1000, has_dropout: bool = True):
 def Vgg_19(class_num: int = 1000, has_dropout: bool = True):
     return _vgg([64, 64, "M", 128, 128, "M", 256, 256, 256, 256, "M", 512, 512, 512, 512, "M", 512, 512, 512, 512, "M"],
                 class_num, has_dropout)
+
+
+# ``X.graph(classNum, hasDropout)`` of the reference's companion objects (VggForCifar10.scala:79,183,293): the same
+# network as a Graph
+VggForCifar10.graph = lambda class_num=10, has_dropout=True: VggForCifar10(class_num, has_dropout).toGraph()
+Vgg_16.graph = lambda class_num=1000, has_dropout=True: Vgg_16(class_num, has_dropout).toGraph()
+Vgg_19.graph = lambda class_num=1000, has_dropout=True: Vgg_19(class_num, has_dropout).toGraph()

@@ -167,3 +167,29 @@ def test_imagenet_pipelines_and_test_mains(tmp_path):
     r1 = zoo_test.resnet_imagenet(["-f", d, "--model", mp, "-b", "2"])
     r2 = zoo_test.inception(["-f", d, "--model", mp, "-b", "2"])
     assert [r[0].result()[1] for r in r1] == [5, 5] and [r[0].result()[1] for r in r2] == [5, 5]
+
+
+def test_companion_object_factories():
+    from bigdl_b200.models.autoencoder import Autoencoder
+    from bigdl_b200.models.lenet import LeNet5
+    from bigdl_b200.models.resnet import ResNet
+    from bigdl_b200.models.vgg import VggForCifar10
+    from bigdl_b200.nn.layer import Graph
+    from bigdl_b200.utils.table import T
+
+    x = torch.rand(2, 28, 28)
+    seq, gr = LeNet5(10), LeNet5.graph(10)
+    assert isinstance(gr, Graph) and tuple(gr.forward(x).shape) == (2, 10)
+    for p, q in zip(seq.parameters()[0], gr.parameters()[0]):
+        q.data.copy_(p.data)
+    assert torch.allclose(seq.forward(x), gr.forward(x), atol=1e-6)
+    k, kg = LeNet5.keras(10), LeNet5.kerasGraph(10)
+    xk = x.reshape(2, 28, 28, 1)
+    assert torch.allclose(k.forward(xk).sum(1), torch.ones(2), atol=1e-5) and tuple(kg.forward(xk).shape) == (2, 10)
+    assert tuple(LeNet5.dnn(2, 10).forward(x).shape) == (2, 10) and isinstance(LeNet5.dnnGraph(2, 10), Graph)
+    assert isinstance(VggForCifar10.graph(10), Graph) and isinstance(Autoencoder.graph(32), Graph)
+    r = ResNet.graph(10, T(depth=8, shortcutType="A"))
+    assert isinstance(r, Graph) and tuple(r.forward(torch.rand(2, 3, 32, 32)).shape) == (2, 10)
+    m = ResNet.apply(10, {"depth": 8, "shortcutType": "A"})
+    assert ResNet.shareGradInput(m) is m
+    ResNet.modelInit(m)

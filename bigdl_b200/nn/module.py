@@ -245,6 +245,15 @@ class Module:
             if f is not None:
                 f.dirty = True
 
+    def release(self):
+        """Drop what this module holds beyond its parameters — the last activations and their gradients — so the
+        device memory returns to the caching allocator (the reference frees the layers' native MKL-DNN resources
+        here, AbstractModule.release)."""
+        for m in self.all_modules():
+            m.output = None
+            m.gradInput = None
+        return self
+
     def zeroGradParameters(self):
         fl = getattr(self, "_flat", None)
         if fl is not None:

@@ -1,7 +1,8 @@
 from .all_reduce_parameter import AllReduceParameter, aligned_partition
 from .compressed_tensor import CompressedTensor, FP16CompressedTensor, FP16SplitsCompressedTensor, SerializerInstance
 from .distri_parameter_synchronizer import DistriParameterSynchronizer
-from .model_broadcast import ModelBroadcast
+from .model_broadcast import (CachedModels, DefaultModelBroadcastFactory, ModelBroadcast, ModelBroadcastFactory,
+                              ModelBroadcastImp, ModelInfo, ProtoBufferModelBroadcastFactory)
 from .parameter_processor import (ConstantClippingProcessor, L2NormClippingProcessor, LarsProcessor,
                                   ParameterProcessor)
 from .parameter_synchronizer import ParameterSynchronizer, enable_sync_batchnorm

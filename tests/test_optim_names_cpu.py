@@ -110,3 +110,33 @@ def test_future_result_and_sumsquare():
     assert got == [0, 1, 4, 9, 7]
     x = torch.randn(1001)
     assert Util.getSumsquareInParallel(x, 4) == pytest.approx(float((x.double() ** 2).sum()))
+
+
+def test_model_broadcast_factory_and_cache():
+    import pickle
+
+    from bigdl_b200.nn.layer import Linear
+    from bigdl_b200.parallel import model_broadcast as MB
+    from bigdl_b200.utils import config
+
+    b = MB.ModelBroadcast()
+    assert isinstance(b, MB.ModelBroadcastImp) and not b.applyProtoBuffer and len(b.uuid()) == 36
+    config.set("bigdl.ModelBroadcastFactory", "protobuf")
+    try:
+        assert MB.ModelBroadcast().applyProtoBuffer
+        config.set("bigdl.ModelBroadcastFactory", "bigdl_b200.parallel.model_broadcast.DefaultModelBroadcastFactory")
+        assert not MB.ModelBroadcast().applyProtoBuffer
+    finally:
+        config.set("bigdl.ModelBroadcastFactory", "default")
+    m = Linear(3, 2)
+    m.forward(torch.rand(4, 3))
+    b.broadcast(m)
+    assert b.value() is m and b.value(shareWeight=False) is not m
+    assert MB.CachedModels.get(b.uuid()) == [m]
+    info = pickle.loads(pickle.dumps(MB.ModelInfo(b.uuid(), m)))
+    assert info.model is m
+    MB.CachedModels.add("old", Linear(2, 2))
+    MB.CachedModels.deleteAll(b.uuid())
+    assert MB.CachedModels.get("old") == [] and MB.CachedModels.get(b.uuid()) == [m]
+    MB.CachedModels.deleteKey(b.uuid())
+    assert MB.CachedModels.get(b.uuid()) == [] and m.output is None      # released

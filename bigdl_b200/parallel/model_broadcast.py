@@ -152,7 +152,9 @@ class CachedModels:
     @classmethod
     def add(cls, uuid: str, model):
         with cls._lock:
-            cls._models.setdefault(uuid, []).append(model)
+            held = cls._models.setdefault(uuid, [])
+            if not any(m is model for m in held):
+                held.append(model)
 
     @classmethod
     def get(cls, uuid: str):

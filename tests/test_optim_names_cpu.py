@@ -140,3 +140,44 @@ def test_model_broadcast_factory_and_cache():
     assert MB.CachedModels.get("old") == [] and MB.CachedModels.get(b.uuid()) == [m]
     MB.CachedModels.deleteKey(b.uuid())
     assert MB.CachedModels.get(b.uuid()) == [] and m.output is None      # released
+
+
+def test_abstractnn_small_types():
+    from bigdl_b200.nn import abstractnn as A
+    from bigdl_b200.nn import layer as L
+    from bigdl_b200.utils.table import T
+
+    assert A.DataFormat("nhwc") is A.DataFormat.NHWC and A.DataFormat.NCHW == "NCHW" and str(A.DataFormat.NHWC) == "NHWC"
+    assert A.DataFormat.NCHW.getHWCDims(4) == (3, 4, 2) and A.DataFormat.NHWC.getHWCDims(3) == (1, 2, 3)
+    with pytest.raises(ValueError):
+        A.DataFormat("chwn")
+    t = torch.zeros(2)
+    assert A.Activity.isTensor(t) and not A.Activity.isTable(t) and A.Activity.isTable(T(t)) and A.Activity.toTensor(t) is t
+    assert A.Activity.isTable(A.Activity.allocate("table")) and A.Activity.allocate("tensor", torch.int32).dtype == torch.int32
+    with pytest.raises(TypeError):
+        A.Activity.toTable(t)
+    with pytest.raises(RuntimeError, match="gradInput of conv1 is empty"):
+        A.EmptyGradInput("conv1").toTensor()
+
+    class Same(A.IdentityOutputShape):
+        def isKerasStyle(self):
+            return True
+
+    s = Same()
+    with pytest.raises(RuntimeError):
+        s.getOutputShape()
+    assert s.build((None, 4)) == (None, 4) and s.getOutputShape() == (None, 4) and s.getInputShape() == (None, 4)
+    with pytest.raises(A.InvalidLayer):
+        s.validateInput([L.Linear(2, 2)])
+    with pytest.raises(RuntimeError):
+        A.InferShape().getInputShape()
+
+    class Mine(A.Initializable):
+        resets = 0
+
+        def reset(self):
+            self.resets += 1
+
+    m = Mine().setInitMethod("w", "b")
+    assert (m.weightInitMethod, m.biasInitMethod, m.resets) == ("w", "b", 1)
+    assert getattr(A.SizeAverageStatus, "True") == "True" and A.AbstractModule is L.Module if hasattr(L, "Module") else True

@@ -258,16 +258,24 @@ def _lrn(n):
 
 @op("FusedBatchNorm", "FusedBatchNormV2", "FusedBatchNormV3")
 def _fbn(n):
+    """Five outputs like the TF kernel: y, batch mean, batch variance (Bessel-corrected, what TF feeds the moving
+    average), and the two reserve spaces a later FusedBatchNormGrad reads — the mean and the biased variance."""
     eps, nchw = float(_attr(n, "epsilon", 1e-3)), _nchw(n)
     training = bool(_attr(n, "is_training", False))
 
     def run(x, scale, offset, mean, var):
         xc = x if nchw else x.permute(0, 3, 1, 2)
         if training or mean.numel() == 0:
+            dims = [0] + list(range(2, xc.dim()))
+            xf = xc.detach().float()
+            mu, v = xf.mean(dims), xf.var(dims, unbiased=False)
+            cnt = xf.numel() // max(xf.shape[1], 1)
             y = F.batch_norm(xc, None, None, scale, offset, True, 0.0, eps)
+            stats = (mu, v * (cnt / max(cnt - 1, 1)), mu, v)
         else:
             y = F.batch_norm(xc, mean, var, scale, offset, False, 0.0, eps)
-        return y if nchw else y.permute(0, 2, 3, 1)
+            stats = (mean, var, mean, var)
+        return Table(y if nchw else y.permute(0, 2, 3, 1), *stats)
     return _Fn(run, 5)
 
 
@@ -502,6 +510,91 @@ def _next(n): return TFO.NextIteration()
 def _loopcond(n): return TFO.LoopCondition()
 
 
+@op("InvertPermutation")
+def _invert_perm(n): return TFO.InvertPermutation()
+
+
+@op("ConcatOffset")
+def _concat_offset(n): return TFO.ConcatOffset()
+
+
+@op("RefEnter")
+def _ref_enter(n): return TFO.Enter(_attr(n, "frame_name", ""), bool(_attr(n, "is_constant", False)))
+
+
+@op("RefSwitch")
+def _ref_switch(n): return TFO.SwitchOps()
+
+
+@op("RefMerge")
+def _ref_merge(n): return TFO.MergeOps()
+
+
+@op("RefExit")
+def _ref_exit(n): return TFO.Exit()
+
+
+@op("RefNextIteration")
+def _ref_next(n): return TFO.NextIteration()
+
+
+@op("ControlTrigger")
+def _control_trigger(n): return TFO.ControlDependency()
+
+
+# ---- TensorArray / Stack resources (S/utils/tf/loaders/{TensorArrayV3,…,StackV2,StackPushV2,StackPopV2}.scala)
+@op("TensorArrayV3")
+def _ta_create(n): return TFO.TensorArrayCreator(bool(_attr(n, "dynamic_size", False)))
+
+
+@op("TensorArrayWriteV3")
+def _ta_write(n): return TFO.TensorArrayWrite()
+
+
+@op("TensorArrayReadV3")
+def _ta_read(n): return TFO.TensorArrayRead()
+
+
+@op("TensorArrayGatherV3")
+def _ta_gather(n): return TFO.TensorArrayGather()
+
+
+@op("TensorArrayScatterV3")
+def _ta_scatter(n): return TFO.TensorArrayScatter()
+
+
+@op("TensorArrayConcatV3")
+def _ta_concat(n): return TFO.TensorArrayConcat()
+
+
+@op("TensorArraySplitV3")
+def _ta_split(n): return TFO.TensorArraySplit()
+
+
+@op("TensorArraySizeV3")
+def _ta_size(n): return TFO.TensorArraySize()
+
+
+@op("TensorArrayGradV3")
+def _ta_grad(n): return TFO.TensorArrayGrad(_attr(n, "source", ""))
+
+
+@op("TensorArrayCloseV3")
+def _ta_close(n): return TFO.TensorArrayClose()
+
+
+@op("StackV2", "Stack")
+def _stack_create(n): return TFO.StackCreator()
+
+
+@op("StackPushV2", "StackPush")
+def _stack_push(n): return TFO.StackPush()
+
+
+@op("StackPopV2", "StackPop")
+def _stack_pop(n): return TFO.StackPop()
+
+
 @op("VariableV2", "Variable", "VarHandleOp")
 def _variable(n): return None          # resolved from binFile by the loader
 
@@ -515,7 +608,8 @@ _WEIGHT_SLOTS = {"Conv2D": [1], "DepthwiseConv2dNative": [1], "MatMul": [1], "Bi
 
 _MULTI_OUTPUT_OPS = ("Switch", "Split", "SplitV", "Unpack", "TopKV2", "TopK", "ParseExample", "ParseSingleExample",
                      "BroadcastGradientArgs", "SoftmaxCrossEntropyWithLogits", "FusedBatchNormGrad",
-                     "FusedBatchNormGradV2", "FusedBatchNormGradV3")
+                     "FusedBatchNormGradV2", "FusedBatchNormGradV3", "TensorArrayV3", "TensorArrayConcatV3",
+                     "TensorArrayGradV3", "ConcatOffset", "FusedBatchNorm", "FusedBatchNormV2", "FusedBatchNormV3")
 
 
 def _split_input(s: str):

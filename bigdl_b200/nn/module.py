@@ -40,7 +40,10 @@ def _as_activity(x, device=None):
             t = t.float()
         return t if device is None else t.to(device)
     if isinstance(x, Table):
-        return Table(*[_as_activity(v, device) for v in x.to_list()])
+        out = Table()
+        for k, v in x.items():               # keeps non-positional keys ("bboxes", "masks", …)
+            out[k] = _as_activity(v, device)
+        return out
     if isinstance(x, (list, tuple)):
         return Table(*[_as_activity(v, device) for v in x])
     if isinstance(x, (int, float)):

@@ -611,3 +611,14 @@ class MkString(Operation):
             rows = input.tolist()
         fmt = lambda v: str(int(v)) if float(v).is_integer() else str(v)
         return np.array([self.delim.join(fmt(v) for v in r) for r in rows], dtype=object)
+
+
+def __getattr__(name):
+    """``nn.ops.{Conv3DBackprop*, Dilation2DBackprop*, DepthwiseConv2DBackprop*, MaxPoolGrad, ResizeBilinearGrad,
+    SelectTensor, …}`` are defined in ``nn.tf_grad`` next to the other TensorFlow-layout operations."""
+    from . import tf_grad
+
+    try:
+        return getattr(tf_grad, name)
+    except AttributeError:
+        raise AttributeError(f"module {__name__!r} has no attribute {name!r}") from None

@@ -265,16 +265,37 @@ class ControlNodes:
 
 # ------------------------------------------------------------------------------------------------ tensor arrays / stacks
 class _TensorArrayStore:
-    def __init__(self, size=0, dynamic=True):
+    """The resource behind a TensorArray handle (DataFlowOps.scala:45-140). A gradient array (``grad()``) has the
+    locked size of its source and SUMS repeated writes to one index, which is how TF accumulates the gradients of a
+    value read several times."""
+
+    def __init__(self, size=0, dynamic=True, aggregate=False):
         self.items: list = [None] * size
         self.dynamic = dynamic
+        self.aggregate = aggregate
+        self.grads: dict = {}
 
     def write(self, i, v):
         while i >= len(self.items):
             if not self.dynamic:
                 raise IndexError("TensorArray index out of range")
             self.items.append(None)
+        if self.aggregate and self.items[i] is not None:
+            v = self.items[i] + v
         self.items[i] = v
+
+    def grad(self, source: str = ""):
+        self.dynamic = False
+        if source not in self.grads:
+            self.grads[source] = _TensorArrayStore(len(self.items), False, True)
+        return self.grads[source]
+
+    def release(self):
+        self.items = []
+        self.grads = {}
+
+
+TensorArray = _TensorArrayStore
 
 
 class TensorArrayCreator(Operation):
@@ -336,11 +357,36 @@ class TensorArraySize(Operation):
         return torch.tensor(len(h.items), dtype=torch.int32)
 
 
+class TensorArrayGrad(Operation):
+    """(handle, flow) → (handle of the gradient array registered under ``source``, flow)
+    (DataFlowOps.scala:230-248)."""
+
+    def __init__(self, source: str = ""):
+        super().__init__()
+        self.source = source
+
+    def updateOutput(self, input):
+        h = _ins(input)[0]
+        return Table(h.grad(self.source), torch.tensor(0.0))
+
+
+class TensorArrayClose(Operation):
+    """Frees the array behind the handle (DataFlowOps.scala:562-577)."""
+
+    def updateOutput(self, input):
+        h = input if isinstance(input, _TensorArrayStore) else _ins(input)[0]
+        h.release()
+        return torch.tensor(0.0)
+
+
 class _StackStore:
     """Handle of a TF stack resource (a plain list would be flattened into a Table when passed between nodes)."""
 
     def __init__(self):
         self.items: list = []
+
+
+Stack = _StackStore
 
 
 class StackCreator(Operation):
@@ -476,3 +522,14 @@ class DecodeRaw(Operation):
                  torch.float32: "f4", torch.float64: "f8"}[self.out_type]
         arr = np.frombuffer(data, dtype=np.dtype(("<" if self.le else ">") + np_dt if np_dt[1] != "1" else np_dt))
         return torch.from_numpy(arr.astype(arr.dtype.newbyteorder("=")).copy())
+
+
+def __getattr__(name):
+    """The backward-half / TF-layout operations live in ``nn.tf_grad`` (they are built on the op loaders, which import
+    this module); ``nn.tf.ReluGrad`` etc. resolve there lazily."""
+    from . import tf_grad
+
+    try:
+        return getattr(tf_grad, name)
+    except AttributeError:
+        raise AttributeError(f"module {__name__!r} has no attribute {name!r}") from None

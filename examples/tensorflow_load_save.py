@@ -43,6 +43,9 @@ def main(argv=None):
 
     Engine.init(device="cpu")
     torch.manual_seed(0)
+    from bigdl_b200.utils.random_generator import RNG
+
+    RNG.setSeed(7)                       # layer initialisation and the epoch shuffle draw from the framework's generator
     d = tempfile.mkdtemp()
     pb = os.path.join(d, "lenet.pb")
     # ---- Save.scala: model.saveTF(Seq(("input", Seq(4, 1, 28, 28))), path)

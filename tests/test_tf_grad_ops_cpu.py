@@ -260,3 +260,174 @@ def test_session_trains_from_the_graphs_own_queue_pipeline(tmp_path):
     assert len(rows) == 32
     got = np.stack([np.asarray(r[0]) for r in rows])
     assert np.allclose(got, X[:32], atol=1e-6) and np.allclose(np.stack([np.asarray(r[1]) for r in rows]), Y[:32], atol=1e-6)
+
+
+# ------------------------------------------------------------------------------------------------ resources
+def _graph(nodes):
+    """nodes: [(op, name, inputs, attrs)] → serialized GraphDef file contents."""
+    from bigdl_b200.interop.tensorflow import _GraphBuilder
+
+    b = _GraphBuilder()
+    for op_name, name, ins, attrs in nodes:
+        if op_name == "Const":
+            b.const(name, attrs["value"])
+        else:
+            b.node(op_name, name, ins, **attrs)
+    return b.gd.SerializeToString()
+
+
+def test_tensor_array_and_stack_graph(tmp_path):
+    from bigdl_b200.interop.tensorflow import load_tf
+
+    f32 = np.dtype(np.float32)
+    nodes = [
+        ("Placeholder", "x", [], {"dtype": f32}),
+        ("Const", "size", [], {"value": np.array(2, np.int32)}),
+        ("Const", "i0", [], {"value": np.array(0, np.int32)}),
+        ("Const", "i1", [], {"value": np.array(1, np.int32)}),
+        ("Const", "two", [], {"value": np.array(2.0, np.float32)}),
+        ("Const", "idx", [], {"value": np.array([1, 0], np.int32)}),
+        ("TensorArrayV3", "ta", ["size"], {"dtype": f32, "dynamic_size": False}),
+        ("Mul", "x2", ["x", "two"], {"T": f32}),
+        ("TensorArrayWriteV3", "w0", ["ta", "i0", "x", "ta:1"], {"T": f32}),
+        ("TensorArrayWriteV3", "w1", ["ta", "i1", "x2", "w0"], {"T": f32}),
+        ("TensorArrayGatherV3", "gathered", ["ta", "idx", "w1"], {"dtype": f32}),
+        ("TensorArraySizeV3", "n", ["ta", "w1"], {}),
+        ("TensorArrayReadV3", "r1", ["ta", "i1", "w1"], {"dtype": f32}),
+        ("TensorArrayConcatV3", "cat", ["ta", "w1"], {"dtype": f32}),
+    ]
+    p = tmp_path / "ta.pb"
+    p.write_bytes(_graph(nodes))
+    x = torch.tensor([1.0, 2.0, 3.0])
+    g = load_tf(str(p), ["x"], ["gathered", "n", "r1", "cat:0", "cat:1"])
+    out = g.forward(x)
+    gathered, n, r1, cat, lens = [out[i] for i in range(1, 6)]
+    assert torch.equal(gathered, torch.stack([2 * x, x])) and int(n) == 2 and torch.equal(r1, 2 * x)
+    assert torch.equal(cat, torch.cat([x, 2 * x])) and lens.tolist() == [3, 3]
+
+    nodes = [
+        ("Placeholder", "x", [], {"dtype": f32}),
+        ("Const", "max", [], {"value": np.array(-1, np.int32)}),
+        ("Const", "two", [], {"value": np.array(2.0, np.float32)}),
+        ("StackV2", "st", ["max"], {"elem_type": f32}),
+        ("StackPushV2", "p0", ["st", "x"], {"T": f32}),
+        ("Mul", "x2", ["p0", "two"], {"T": f32}),
+        ("StackPushV2", "p1", ["st", "x2"], {"T": f32}),
+        ("Identity", "after", ["p1"], {"T": f32}),
+        ("StackPopV2", "top", ["st", "^after"], {"elem_type": f32}),
+    ]
+    p2 = tmp_path / "st.pb"
+    p2.write_bytes(_graph(nodes))
+    g = load_tf(str(p2), ["x"], ["after", "top"])
+    out = g.forward(x)
+    assert torch.equal(out[1], 2 * x) and torch.equal(out[2], 2 * x)
+
+
+def test_tensor_array_grad_accumulates_and_close():
+    from bigdl_b200.nn import tf as TFO
+
+    handle, flow = TFO.TensorArrayCreator(False).forward(torch.tensor(2)).to_list()
+    TFO.TensorArrayWrite().forward(Table(handle, torch.tensor(0), torch.ones(2), flow))
+    gh, gflow = _LOADERS["TensorArrayGradV3"](_node("TensorArrayGradV3", source="grad1")).forward(Table(handle, flow)).to_list()
+    assert gh is not handle and len(gh.items) == 2 and not handle.dynamic
+    w = TFO.TensorArrayWrite()
+    w.forward(Table(gh, torch.tensor(1), torch.ones(3), gflow))
+    w.forward(Table(gh, torch.tensor(1), 2 * torch.ones(3), gflow))          # second write to one slot is summed
+    assert gh.items[1].tolist() == [3.0, 3.0, 3.0]
+    again = TFO.TensorArrayGrad("grad1").forward(Table(handle, flow))[1]
+    assert again is gh and TFO.TensorArrayGrad("other").forward(Table(handle, flow))[1] is not gh
+    with pytest.raises(IndexError):
+        TFO.TensorArrayWrite().forward(Table(handle, torch.tensor(5), torch.ones(1), flow))
+    _LOADERS["TensorArrayCloseV3"](_node("TensorArrayCloseV3")).forward(handle)
+    assert handle.items == []
+    perm = _LOADERS["InvertPermutation"](_node("InvertPermutation")).forward(torch.tensor([2, 0, 1]))
+    assert perm.tolist() == [1, 2, 0]
+    offs = _LOADERS["ConcatOffset"](_node("ConcatOffset")).forward(
+        Table(torch.tensor(1), torch.tensor([2, 3]), torch.tensor([2, 5])))
+    assert offs[1].tolist() == [0, 0] and offs[2].tolist() == [0, 3]
+    for name in ("RefEnter", "RefSwitch", "RefMerge", "RefExit", "RefNextIteration", "ControlTrigger", "Stack", "StackPush",
+                 "StackPop"):
+        assert name in _LOADERS
+
+
+# ------------------------------------------------------------------------------------------------ nn.tf / nn.ops classes
+def test_grad_ops_as_layers():
+    from bigdl_b200.nn import ops as O
+    from bigdl_b200.nn import tf as TFO
+    from bigdl_b200.nn import tf_grad as G
+
+    torch.manual_seed(0)
+    x = torch.randn(2, 6, 6, 3, requires_grad=True)
+    g = torch.randn(2, 6, 6, 3)
+    torch.tanh(x).backward(g)
+    assert torch.allclose(TFO.TanhGrad().forward(Table(torch.tanh(x.detach()), g)), x.grad, atol=1e-6)
+    assert TFO.ReluGrad is G.ReluGrad and O.MaxPoolGrad is G.MaxPoolGrad and O.SelectTensor is G.SelectTensor
+    with pytest.raises(AttributeError):
+        TFO.NoSuchOp
+
+    w = torch.randn(3, 3, 3, 4)
+    y = G.Conv2D(1, 1, -1, -1, "NHWC").forward(Table(x.detach(), w))
+    ref = F.conv2d(x.detach().permute(0, 3, 1, 2), w.permute(3, 2, 0, 1), padding=1)
+    assert torch.allclose(y, ref.permute(0, 2, 3, 1), atol=1e-5)
+    gy = torch.randn_like(y)
+    xr = x.detach().permute(0, 3, 1, 2).requires_grad_(True)
+    wr = w.permute(3, 2, 0, 1).detach().requires_grad_(True)
+    F.conv2d(xr, wr, padding=1).backward(gy.permute(0, 3, 1, 2))
+    dx = G.Conv2DTranspose(1, 1, -1, -1, "NHWC").forward(Table(torch.tensor([2, 6, 6, 3]), w, gy))
+    dw = G.Conv2DBackFilter(1, 1, -1, -1, "NHWC").forward(Table(x.detach(), torch.tensor([3, 3, 3, 4]), gy))
+    assert torch.allclose(dx, xr.grad.permute(0, 2, 3, 1), atol=1e-4)
+    assert torch.allclose(dw, wr.grad.permute(2, 3, 1, 0), atol=1e-4)
+
+    p = G.MaxPool([1, 2, 2, 1], [1, 2, 2, 1], "VALID").forward(x.detach())
+    xp = x.detach().permute(0, 3, 1, 2).requires_grad_(True)
+    F.max_pool2d(xp, 2, 2).backward(torch.ones(2, 3, 3, 3))
+    mg = G.MaxPoolGrad(2, 2, 2, 2, 0, 0, "NHWC").forward(Table(x.detach(), p, torch.ones_like(p)))
+    assert torch.allclose(mg, xp.grad.permute(0, 2, 3, 1))
+    ag = G.AvgPoolGrad(2, 2, 2, 2, 0, 0, "NHWC").forward(Table(torch.tensor([2, 6, 6, 3]), torch.ones_like(p)))
+    assert torch.allclose(ag, torch.full((2, 6, 6, 3), 0.25))
+    assert torch.allclose(G.BiasAddGrad("NHWC").forward(g), g.sum((0, 1, 2)))
+
+    out = G.FusedBatchNorm(1e-3, True).forward(Table(x.detach(), torch.ones(3), torch.zeros(3), torch.zeros(0), torch.zeros(0)))
+    yb, bm, bv, sm, sv = out.to_list()
+    flat = x.detach().reshape(-1, 3)
+    assert torch.allclose(bm, flat.mean(0), atol=1e-6) and torch.allclose(sv, flat.var(0, unbiased=False), atol=1e-6)
+    assert torch.allclose(bv, flat.var(0, unbiased=True), atol=1e-6) and torch.allclose(yb.reshape(-1, 3).mean(0), torch.zeros(3), atol=1e-5)
+    dxb, dscale, dbias = G.FusedBatchNormGrad(1e-3, "NHWC", True).forward(Table(g, x.detach(), torch.ones(3), sm, sv)).to_list()[:3]
+    xb = x.detach().permute(0, 3, 1, 2).requires_grad_(True)
+    sc = torch.ones(3, requires_grad=True)
+    F.batch_norm(xb, None, None, sc, torch.zeros(3), True, 0.0, 1e-3).backward(g.permute(0, 3, 1, 2))
+    assert torch.allclose(dxb, xb.grad.permute(0, 2, 3, 1), atol=1e-4) and torch.allclose(dscale, sc.grad, atol=1e-4)
+    assert torch.allclose(dbias, g.sum((0, 1, 2)), atol=1e-5)
+
+    assert G.Conv3D(1, 2, 2, -1, -1, -1, "NHWC").attrs == {"strides": [1, 1, 2, 2, 1], "padding": "SAME", "data_format": "NDHWC"}
+    assert G.LRNGrad(2, 1.0, 1e-4, 0.75).attrs["depth_radius"] == 2 and G.ResizeBilinearGrad(True).attrs["align_corners"]
+    for cls in (G.Conv3DBackpropInput, G.Conv3DBackpropInputV2, G.Conv3DBackpropFilter, G.Conv3DBackpropFilterV2):
+        cls(1, 1, 1, 0, 0, 0, "NHWC")
+    G.Dilation2DBackpropInput([1, 1, 1, 1], [1, 1, 1, 1], "SAME")
+    G.Dilation2DBackpropFilter([1, 1, 1, 1], [1, 1, 1, 1], "SAME")
+    G.DepthwiseConv2DBackpropInput(1, 1, -1, -1)
+    G.DepthwiseConv2DBackpropFilter(1, 1, -1, -1)
+    with pytest.raises(ValueError):
+        G.DecodeJpeg(3, 2)
+
+
+def test_small_state_and_wrapper_ops():
+    import cv2
+
+    from bigdl_b200.nn import layer as L
+    from bigdl_b200.nn import tf_grad as G
+    from bigdl_b200.utils.table import T
+
+    buf = torch.zeros(2, 2)
+    assert G.AssignGrad(buf).forward(torch.arange(4.0)).tolist() == [0, 1, 2, 3] and buf.tolist() == [[0, 1], [2, 3]]
+    tab = T()
+    tab["a"], tab["b"] = torch.ones(2), torch.zeros(2)
+    assert G.SelectTensor("b").forward(tab).tolist() == [0, 0]
+    assert G.SelectTensor("a", L.MulConstant(3.0)).forward(tab).tolist() == [3, 3]
+    with pytest.raises(KeyError):
+        G.SelectTensor("zz").forward(tab)
+    assert G.TensorModuleWrapper(L.ReLU()).forward(torch.tensor([-1.0, 2.0])).tolist() == [0, 2]
+    img = (np.arange(5 * 4 * 3) % 255).astype(np.uint8).reshape(5, 4, 3)
+    png = cv2.imencode(".png", img)[1].tobytes()
+    dec = G.DecodePng(3).forward(np.array([png], dtype=object))
+    assert tuple(dec.shape) == (5, 4, 3) and np.array_equal(dec.numpy().astype(np.uint8), img[..., ::-1])

@@ -627,3 +627,8 @@ class TimeDistributedMaskCriterion(Criterion):
             if pv is not None:
                 crit.paddingValue = pv
         return total / torch.clamp(mask.sum().to(total.dtype), min=1)
+
+
+class NormMode:
+    """How SoftmaxWithCriterion normalises the summed loss (SoftmaxWithCriterion.scala:152-155)."""
+    FULL, VALID, BATCH_SIZE, NONE = "FULL", "VALID", "BATCH_SIZE", "NONE"

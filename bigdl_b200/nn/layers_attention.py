@@ -370,3 +370,99 @@ class TransformerOperation:
         if activation is not None:
             seq.add(activation)
         return seq
+
+
+# ------------------------------------------------------------------------------------------------ building blocks
+# The reference assembles its Transformer graph from these small modules (Transformer.scala:600-750,
+# Attention.scala:217-290, LayerNormalization.scala:60-170). The fused path above does their work inside the attention
+# kernel; they exist as layers so graphs written against the reference pieces — and their unit specs — carry over.
+class PositionEncode(Module):
+    """[B, L, C] → the sinusoid position table [L, C] (no gradient to the input)."""
+
+    def updateOutput(self, input):
+        return position_signal(input.shape[1], input.shape[2], input.device, input.dtype)
+
+
+class PositionEncodeWithShift(Module):
+    """Shift the sequence right by one step (zero in front, last step dropped) and add the position table."""
+
+    def updateOutput(self, input):
+        shifted = torch.cat([torch.zeros_like(input[:, :1]), input[:, :-1]], 1)
+        return shifted + position_signal(input.shape[1], input.shape[2], input.device, input.dtype)
+
+
+class PaddingMask(Module):
+    """Token ids [B, L] → additive bias [B, 1, 1, L] with −1e9 where the id equals ``padding_value`` (0)."""
+
+    def __init__(self, padding_value: float = 0.0):
+        super().__init__()
+        self.padding_value = padding_value
+
+    def updateOutput(self, input):
+        return padding_bias(input.detach(), self.padding_value, torch.float32)
+
+
+class SelfAttentionMask(Module):
+    """[B, L, …] → the [1, 1, L, L] bias that hides future positions."""
+
+    def updateOutput(self, input):
+        return causal_bias(input.shape[1], input.device, torch.float32)
+
+
+class SplitHeads(Module):
+    """[B, L, H] → [B, heads, L, H / heads]; ``mul`` scales by (H / heads)^−0.5 (the query scaling)."""
+
+    def __init__(self, hiddenSize: int, numHeads: int, mul: bool = False):
+        super().__init__()
+        self.hiddenSize, self.numHeads, self.mul = hiddenSize, numHeads, mul
+
+    def updateOutput(self, input):
+        b, l, _ = input.shape
+        depth = self.hiddenSize // self.numHeads
+        out = input.reshape(b, l, self.numHeads, depth).transpose(1, 2)
+        return out * depth ** -0.5 if self.mul else out
+
+
+class CombineHeads(Module):
+    """[B, heads, L, D] → [B, L, heads · D]."""
+
+    def updateOutput(self, input):
+        b, h, l, d = input.shape
+        return input.transpose(1, 2).reshape(b, l, h * d)
+
+
+class SplitTensor(Module):
+    """Tensor → Table of ``num`` equal slices along the (1-based) ``dimension``."""
+
+    def __init__(self, dimension: int, num: int):
+        super().__init__()
+        self.dimension, self.num = dimension, num
+
+    def updateOutput(self, input):
+        d = self.dimension - 1
+        return Table(*torch.split(input, input.shape[d] // self.num, d))
+
+
+class VectorProduct(Module):
+    """y = x ⊙ weight + bias over the last dimension, weight = 1 and bias = 0 at start: the affine half of the
+    reference's LayerNormalization."""
+
+    def __init__(self, hiddenSize: int):
+        super().__init__()
+        self.hiddenSize = hiddenSize
+        self.register_parameter("weight", torch.ones(hiddenSize))
+        self.register_parameter("bias", torch.zeros(hiddenSize))
+
+    def reset(self):
+        self.weight.data.fill_(1.0)
+        self.bias.data.zero_()
+        self.zeroGradParameters()
+        return self
+
+    def updateOutput(self, input):
+        return input * self.weight.to(input.dtype) + self.bias.to(input.dtype)
+
+
+# the two TransformerType case objects by their own names (TransformerOperation.scala:172-176)
+LanguageModel = TransformerType.LanguageModel
+Translation = TransformerType.Translation

@@ -518,3 +518,59 @@ class BinaryTreeLSTM(TreeLSTM):
                     hs.append(rec(node)[0])
             outs.append(torch.cat(hs, dim=0))
         return torch.stack(outs, dim=0)
+
+
+class TensorTree:
+    """A tree stored as a [nodes, width] tensor (S/nn/BinaryTreeLSTM.scala:513-572): row i holds the 1-based child
+    indices of node i (0 = none, −1 in the first column = padding row) and, in the LAST column, the leaf's word index
+    or −1 for the root. All indices are 1-based like the reference."""
+
+    def __init__(self, content: torch.Tensor):
+        if content.dim() != 2:
+            raise ValueError(f"The content of TensorTree should be a two-dimensional tensor, content dim({content.dim()})")
+        self.content = content
+
+    @property
+    def size(self):
+        return list(self.content.shape)
+
+    @property
+    def nodeNumber(self) -> int:
+        return self.content.shape[0]
+
+    def children(self, index: int):
+        return [int(v) for v in self.content[index - 1].tolist()]
+
+    def addChild(self, parent: int, child):
+        row = self.content[parent - 1]
+        for i in range(row.numel() - 1):
+            if float(row[i]) == 0:
+                row[i] = child
+                return
+
+    def markAsRoot(self, index: int):
+        self.content[index - 1, -1] = -1
+
+    def getRoot(self) -> int:
+        for i in range(self.content.shape[0]):
+            if int(self.content[i, -1]) == -1:
+                return i + 1
+        raise RuntimeError("There is no root in the tensor tree")
+
+    def markAsLeaf(self, index: int, leafIndex: int):
+        self.content[index - 1, -1] = leafIndex
+
+    def leafIndex(self, index: int) -> int:
+        return int(self.content[index - 1, -1])
+
+    def hasChild(self, index: int) -> bool:
+        return int(self.content[index - 1, 0]) > 0
+
+    def noChild(self, index: int) -> bool:
+        return int(self.content[index - 1, 0]) == 0
+
+    def exists(self, index: int) -> bool:
+        return 1 <= index <= self.content.shape[0]
+
+    def isPadding(self, index: int) -> bool:
+        return int(self.content[index - 1, 0]) == -1

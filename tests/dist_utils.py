@@ -35,7 +35,20 @@ def _entry(rank, world, port, fn, args, ret):
 
 
 def run_ranks(fn, world: int, *args):
-    """Run ``fn(rank, world, *args)`` on ``world`` gloo processes; returns the list of per-rank results."""
+    """Run ``fn(rank, world, *args)`` on ``world`` gloo processes; returns the list of per-rank results. The port is
+    picked by bind-and-release, so under ``pytest -n`` another worker can take it first: a rendezvous failure is
+    retried once on a fresh port."""
+    try:
+        return _run_ranks_once(fn, world, *args)
+    except RuntimeError as e:
+        msg = str(e)
+        if not any(k in msg for k in ("Address already in use", "EADDRINUSE", "Connection refused", "connect()",
+                                      "timed out", "Connection reset")):
+            raise
+        return _run_ranks_once(fn, world, *args)
+
+
+def _run_ranks_once(fn, world: int, *args):
     ctx = mp.get_context("spawn")
     mgr = ctx.Manager()
     ret = mgr.dict()

@@ -181,3 +181,45 @@ def test_abstractnn_small_types():
     m = Mine().setInitMethod("w", "b")
     assert (m.weightInitMethod, m.biasInitMethod, m.resets) == ("w", "b", 1)
     assert getattr(A.SizeAverageStatus, "True") == "True" and A.AbstractModule is L.Module if hasattr(L, "Module") else True
+
+
+def test_transformer_building_blocks_and_tensor_tree():
+    from bigdl_b200.nn import layer as L
+    from bigdl_b200.nn.criterion import NormMode
+    from bigdl_b200.nn.layers_attention import position_signal
+
+    x = torch.randn(2, 5, 8)
+    pe = L.PositionEncode().forward(x)
+    assert tuple(pe.shape) == (5, 8) and torch.allclose(pe, position_signal(5, 8, x.device))
+    sh = L.PositionEncodeWithShift().forward(x)
+    assert torch.allclose(sh[:, 0], pe[0].expand(2, 8)) and torch.allclose(sh[:, 1:], x[:, :-1] + pe[1:])
+    ids = torch.tensor([[3.0, 4.0, 0.0], [5.0, 0.0, 0.0]])
+    pm = L.PaddingMask().forward(ids)
+    assert tuple(pm.shape) == (2, 1, 1, 3) and pm[0, 0, 0].tolist() == [0.0, 0.0, -1e9]
+    sm = L.SelfAttentionMask().forward(x)
+    assert tuple(sm.shape) == (1, 1, 5, 5) and float(sm[0, 0, 0, 1]) == -1e9 and float(sm[0, 0, 3, 2]) == 0.0
+    heads = L.SplitHeads(8, 2, True).forward(x)
+    assert tuple(heads.shape) == (2, 2, 5, 4) and torch.allclose(heads[0, 1, 3], x[0, 3, 4:] * 0.5)
+    assert torch.allclose(L.CombineHeads().forward(L.SplitHeads(8, 2).forward(x)), x)
+    parts = L.SplitTensor(3, 2).forward(x)
+    assert len(parts) == 2 and torch.equal(parts[2], x[..., 4:])
+    vp = L.VectorProduct(8)
+    assert torch.allclose(vp.forward(x), x)
+    vp.weight.data.fill_(2.0)
+    vp.bias.data.fill_(1.0)
+    y = vp.forward(x)
+    assert torch.allclose(y, 2 * x + 1)
+    vp.backward(x, torch.ones_like(x))
+    assert torch.allclose(vp.parameters()[1][0], x.sum((0, 1)), atol=1e-5)
+    assert L.LanguageModel == L.TransformerType.LanguageModel and NormMode.BATCH_SIZE == "BATCH_SIZE"
+
+    t = L.TensorTree(torch.zeros(3, 3))
+    t.addChild(1, 2)
+    t.addChild(1, 3)
+    t.markAsRoot(1)
+    t.markAsLeaf(2, 1)
+    t.markAsLeaf(3, 2)
+    assert t.children(1) == [2, 3, -1] and t.getRoot() == 1 and t.hasChild(1) and t.noChild(2) and t.leafIndex(3) == 2
+    assert t.exists(3) and not t.exists(4) and not t.isPadding(1) and t.nodeNumber == 3 and t.size == [3, 3]
+    with pytest.raises(ValueError):
+        L.TensorTree(torch.zeros(3))

@@ -927,3 +927,74 @@ class TimeDistributed(KerasLayer):
         if isinstance(inner, KerasLayer):
             inner.build(s[1:])
         return L.TimeDistributed(inner)
+
+
+# ------------------------------------------------------------------------------------------------ wrappers
+class KerasLayerWrapper(KerasLayer):
+    """Use a Torch-style layer inside a Keras-style model (KerasLayer.scala:95-111): the output shape is found by
+    running the wrapped layer on a batch of ones."""
+
+    def __init__(self, torch_layer: Module, input_shape=None, **kw):
+        super().__init__(input_shape, **kw)
+        if getattr(torch_layer, "isKerasStyle", lambda: False)():
+            raise ValueError(f"We only accept torch layer here, but got: {torch_layer}")
+        self.torchLayer = torch_layer
+
+    def doBuild(self, s):
+        return self.torchLayer
+
+
+class KerasIdentityWrapper(KerasLayerWrapper):
+    """The same for a layer known to keep its input shape (KerasLayer.scala:76-86)."""
+
+    def computeOutputShape(self, input_shape):
+        self.build(input_shape)
+        return list(input_shape)
+
+
+class KerasUtils:
+    """The lookups the Keras-style layers share (S/nn/keras/KerasUtils.scala)."""
+
+    @staticmethod
+    def getInitMethod(init: str):
+        return _init_method(init)
+
+    @staticmethod
+    def getActivation(activation):
+        return activation_module(activation)
+
+    getKerasActivation = getActivation
+
+    @staticmethod
+    def getPadsFromBorderMode(border_mode: str = "valid"):
+        """"same" is the −1 the Torch-style layers read as TensorFlow SAME padding; "valid" is 0."""
+        if border_mode not in ("valid", "same"):
+            raise ValueError(f"Invalid border mode: {border_mode}")
+        return (-1, -1) if border_mode == "same" else (0, 0)
+
+    @staticmethod
+    def toBigDLFormat(dim_ordering: str = "th") -> str:
+        d = str(dim_ordering).lower()
+        if d not in ("tf", "th"):
+            raise ValueError(f"Invalid dim_ordering: {dim_ordering}")
+        return "NHWC" if d == "tf" else "NCHW"
+
+    @staticmethod
+    def toBigDLFormat5D(dim_ordering: str = "th") -> str:
+        d = str(dim_ordering).lower()
+        if d not in ("tf", "th"):
+            raise ValueError(f"Invalid dim_ordering: {dim_ordering}")
+        return "CHANNEL_LAST" if d == "tf" else "CHANNEL_FIRST"
+
+    @staticmethod
+    def addBatch(shape):
+        return None if shape is None else tuple([None] + list(shape))
+
+    @staticmethod
+    def removeBatch(shape):
+        return None if shape is None else tuple(list(shape)[1:])
+
+
+# the reference's names of the abstract pooling bases (S/nn/keras/{Pooling1D,Pooling2D,Pooling3D,GlobalPooling*}.scala)
+Pooling1D, Pooling2D, Pooling3D = _Pool1D, _Pool2D, _Pool3D
+GlobalPooling1D = GlobalPooling2D = GlobalPooling3D = _GlobalPool

@@ -223,3 +223,24 @@ def test_transformer_building_blocks_and_tensor_tree():
     assert t.exists(3) and not t.exists(4) and not t.isPadding(1) and t.nodeNumber == 3 and t.size == [3, 3]
     with pytest.raises(ValueError):
         L.TensorTree(torch.zeros(3))
+
+
+def test_keras_wrappers_and_utils():
+    from bigdl_b200.nn import layer as L
+    from bigdl_b200.nn.keras import layers as K
+    from bigdl_b200.nn.keras.topology import Sequential as KSequential
+
+    m = KSequential()
+    m.add(K.Dense(6, input_shape=(4,)))
+    m.add(K.KerasLayerWrapper(L.Sequential().add(L.Linear(6, 3)).add(L.ReLU())))
+    m.add(K.KerasIdentityWrapper(L.Tanh()))
+    assert m.getOutputShape() == (None, 3) and tuple(m.forward(torch.rand(5, 4)).shape) == (5, 3)
+    with pytest.raises(ValueError):
+        K.KerasLayerWrapper(K.Dense(2))
+    assert K.KerasUtils.getPadsFromBorderMode("same") == (-1, -1) and K.KerasUtils.toBigDLFormat("tf") == "NHWC"
+    assert K.KerasUtils.toBigDLFormat5D("th") == "CHANNEL_FIRST" and K.KerasUtils.addBatch((3, 4)) == (None, 3, 4)
+    assert K.KerasUtils.removeBatch((None, 3)) == (3,) and isinstance(K.KerasUtils.getActivation("relu"), L.ReLU)
+    assert K.KerasUtils.getInitMethod("glorot_uniform") is not None
+    with pytest.raises(ValueError):
+        K.KerasUtils.toBigDLFormat("xx")
+    assert issubclass(K.MaxPooling2D, K.Pooling2D) and issubclass(K.GlobalMaxPooling1D, K.GlobalPooling1D)

@@ -283,21 +283,64 @@ class MultiRNNCell(Cell):
         return x, new_hidden
 
 
+class BatchNormParams:
+    """Settings of the batch normalisation ``Recurrent(batchNormParams = …)`` puts between the input projection and
+    the recurrence (S/nn/Recurrent.scala:850-857)."""
+
+    def __init__(self, eps: float = 1e-5, momentum: float = 0.1, initWeight=None, initBias=None, initGradWeight=None,
+                 initGradBias=None, affine: bool = True, **kw):
+        self.eps, self.momentum, self.affine = eps, momentum, affine
+        self.initWeight = kw.get("init_weight", initWeight)
+        self.initBias = kw.get("init_bias", initBias)
+        self.initGradWeight = kw.get("init_grad_weight", initGradWeight)
+        self.initGradBias = kw.get("init_grad_bias", initGradBias)
+
+
 class Recurrent(Container):
     """Run a Cell over the time dimension of ``[B, T, ...]`` (S/nn/Recurrent.scala:243-527). ``setHiddenState`` /
-    ``getHiddenState`` expose the carried state; ``mask_zero`` stops state updates on all-zero (padded) steps."""
+    ``getHiddenState`` expose the carried state; ``mask_zero`` stops state updates on all-zero (padded) steps.
+    With ``batch_norm_params`` the projected input of ALL time steps ([B·T, gates]) goes through one
+    BatchNormalization before the recurrence (Recurrent.scala:106-140)."""
 
     def __init__(self, batch_norm_params=None, mask_zero: bool = False):
         super().__init__()
+        if batch_norm_params is True:
+            batch_norm_params = BatchNormParams()
+        elif isinstance(batch_norm_params, dict):
+            batch_norm_params = BatchNormParams(**batch_norm_params)
         self.batch_norm_params, self.mask_zero = batch_norm_params, mask_zero
+        self.bnorm = None
         self._init_hidden = None
         self._last_hidden = None
 
     def add(self, module):
+        if isinstance(module, TimeDistributed) and self.modules and self.bnorm is None:
+            # a saved model lists [cell, TimeDistributed(BatchNormalization)]: the loader hands the second one back here
+            bn = module.modules[0]
+            self.bnorm = module
+            self.batch_norm_params = BatchNormParams(bn.eps, bn.momentum, affine=bn.affine)
+            self.modules = [self.modules[0], module]
+            return self
         if not isinstance(module, Cell):
             raise TypeError("Recurrent: added module should be Cell type")
         self.modules = [module]
+        self.bnorm = None
+        bp = self.batch_norm_params
+        if bp is not None:
+            if type(module).pre is Cell.pre:
+                raise ValueError(f"{module.getName()} does not support BatchNormalization: it has no input projection")
+            from .layers_core import BatchNormalization
+
+            with torch.no_grad():
+                width = module.pre(torch.zeros(1, 1, module.input_size)).shape[-1]
+            self.bnorm = TimeDistributed(BatchNormalization(width, bp.eps, bp.momentum, bp.affine, bp.initWeight,
+                                                            bp.initBias, bp.initGradWeight, bp.initGradBias))
+            self.modules = [module, self.bnorm]
         return self
+
+    def _project(self, cell, x):
+        proj = cell.pre(x)
+        return self.bnorm._call(proj) if self.bnorm is not None else proj
 
     @property
     def cell(self) -> Cell:
@@ -324,7 +367,7 @@ class Recurrent(Container):
                 and bool(config.get("bigdl.rnn.persistent"))
                 and lstm_seq_supported(cell.hidden_size, x.device)):
             return None
-        proj = cell.pre(x)
+        proj = self._project(cell, x)
         if proj.dtype != torch.bfloat16:
             return None
         h0 = c0 = None
@@ -345,7 +388,7 @@ class Recurrent(Container):
         if fused is not None:
             return fused
         B, T = x.shape[0], x.shape[1]
-        proj = cell.pre(x)
+        proj = self._project(cell, x)
         spatial = tuple(proj.shape[3:]) if proj.dim() > 3 else None
         hidden = self._init_hidden if self._init_hidden is not None else cell.init_hidden(B, proj, spatial)
         hidden = [h.to(proj.dtype) for h in hidden]

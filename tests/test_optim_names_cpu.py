@@ -244,3 +244,50 @@ def test_keras_wrappers_and_utils():
     with pytest.raises(ValueError):
         K.KerasUtils.toBigDLFormat("xx")
     assert issubclass(K.MaxPooling2D, K.Pooling2D) and issubclass(K.GlobalMaxPooling1D, K.GlobalPooling1D)
+
+
+def test_recurrent_batch_norm_params(tmp_path):
+    from bigdl_b200.nn import layer as L
+    from bigdl_b200.nn.layers_recurrent import BatchNormParams
+    from bigdl_b200.nn.module import Module
+
+    torch.manual_seed(0)
+    rec = L.Recurrent(BatchNormParams(eps=1e-3, momentum=0.2)).add(L.LSTM(5, 4))
+    assert len(rec.modules) == 2 and rec.bnorm.modules[0].n_output == 16
+    x = torch.randn(3, 6, 5)
+    y = rec.forward(x)
+    assert tuple(y.shape) == (3, 6, 4)
+    # the normalised projection: statistics are taken over batch AND time
+    cell, bn = rec.cell, rec.bnorm.modules[0]
+    proj = cell.i2g.forward(x.reshape(18, 5))
+    mu, var = proj.mean(0), proj.var(0, unbiased=False)
+    want = (proj - mu) / torch.sqrt(var + 1e-3) * bn.weight.detach() + bn.bias.detach()
+    h = c = torch.zeros(3, 4)
+    outs = []
+    for t in range(6):
+        g = want.reshape(3, 6, 16)[:, t] + h @ cell.h2g.weight.detach().t()
+        i, cand, f, o = g.chunk(4, 1)
+        c = torch.sigmoid(f) * c + torch.sigmoid(i) * torch.tanh(cand)
+        h = torch.sigmoid(o) * torch.tanh(c)
+        outs.append(h)
+    assert torch.allclose(y, torch.stack(outs, 1), atol=1e-5)
+    g = rec.backward(x, torch.ones_like(y))
+    assert tuple(g.shape) == (3, 6, 5) and float(bn.parameters()[1][0].abs().sum()) > 0
+    # 2 LSTM weights + bias, BN gain + shift
+    assert len(rec.parameters()[0]) == 5
+
+    p = str(tmp_path / "rec.bigdl")
+    rec.evaluate()
+    y_eval = rec.forward(x)
+    rec.saveModule(p, overWrite=True)
+    back = Module.loadModule(p)
+    assert back.bnorm is not None and back.batch_norm_params.eps == pytest.approx(1e-3)
+    assert torch.allclose(back.evaluate().forward(x), y_eval, atol=1e-6)
+    from bigdl_b200.nn.layers_recurrent import Cell
+
+    class Bare(Cell):                       # no input projection → nothing to normalise
+        input_size = 5
+
+    with pytest.raises(ValueError, match="does not support BatchNormalization"):
+        L.Recurrent(True).add(Bare())
+    assert L.BiRecurrent(batch_norm_params=True).add(L.GRU(5, 4)).forward(x).shape[-1] == 4

@@ -213,6 +213,18 @@ class Proposal(Module):
             return out
 
 
+class DetectionOutputParam:
+    """The SSD post-processing settings as one value (DetectionOutputSSD.scala:305-308); ``DetectionOutputSSD(param)``
+    / ``DetectionOutputSSD.apply(param, postProcess)`` accept it."""
+
+    def __init__(self, nClasses: int = 21, shareLocation: bool = True, bgLabel: int = 0, nmsThresh: float = 0.45,
+                 nmsTopk: int = 400, keepTopK: int = 200, confThresh: float = 0.01,
+                 varianceEncodedInTarget: bool = False):
+        self.nClasses, self.shareLocation, self.bgLabel, self.nmsThresh = nClasses, shareLocation, bgLabel, nmsThresh
+        self.nmsTopk, self.keepTopK, self.confThresh = nmsTopk, keepTopK, confThresh
+        self.varianceEncodedInTarget = varianceEncodedInTarget
+
+
 class DetectionOutputSSD(Module):
     """Decode SSD predictions: input = table(loc [B, P*4], conf [B, P*C], priors [1,2,P*4]) → [B, 1 + keep*6]
     (count, then rows (label, score, x1, y1, x2, y2)) (S/nn/DetectionOutputSSD.scala)."""
@@ -220,9 +232,25 @@ class DetectionOutputSSD(Module):
     def __init__(self, n_classes=21, share_location=True, bg_label=0, nms_thresh=0.45, nms_topk=400, keep_top_k=200,
                  conf_thresh=0.01, variance_encoded_in_target=False, conf_post_process=True):
         super().__init__()
+        if isinstance(n_classes, DetectionOutputParam):
+            prm, post = n_classes, (share_location if isinstance(share_location, bool) and share_location is not True
+                                    else conf_post_process)
+            n_classes, share_location, bg_label = prm.nClasses, prm.shareLocation, prm.bgLabel
+            nms_thresh, nms_topk, keep_top_k, conf_thresh = prm.nmsThresh, prm.nmsTopk, prm.keepTopK, prm.confThresh
+            variance_encoded_in_target, conf_post_process = prm.varianceEncodedInTarget, post
+            # what the serializer stores: the unpacked scalars, not the parameter object
+            self.__dict__["_ctor_args"] = dict(
+                n_classes=n_classes, share_location=share_location, bg_label=bg_label, nms_thresh=nms_thresh,
+                nms_topk=nms_topk, keep_top_k=keep_top_k, conf_thresh=conf_thresh,
+                variance_encoded_in_target=variance_encoded_in_target, conf_post_process=conf_post_process)
         self.n_classes, self.share_location, self.bg_label = n_classes, share_location, bg_label
         self.nms_thresh, self.nms_topk, self.keep_top_k, self.conf_thresh = nms_thresh, nms_topk, keep_top_k, conf_thresh
         self.variance_encoded_in_target, self.conf_post_process = variance_encoded_in_target, conf_post_process
+
+    @staticmethod
+    def apply(param: DetectionOutputParam, postProcess: bool = True):
+        return DetectionOutputSSD(param.nClasses, param.shareLocation, param.bgLabel, param.nmsThresh, param.nmsTopk,
+                                  param.keepTopK, param.confThresh, param.varianceEncodedInTarget, postProcess)
 
     def _decode(self, loc, priors, var):
         pw, ph = priors[:, 2] - priors[:, 0], priors[:, 3] - priors[:, 1]

@@ -291,3 +291,16 @@ def test_recurrent_batch_norm_params(tmp_path):
     with pytest.raises(ValueError, match="does not support BatchNormalization"):
         L.Recurrent(True).add(Bare())
     assert L.BiRecurrent(batch_norm_params=True).add(L.GRU(5, 4)).forward(x).shape[-1] == 4
+
+
+def test_detection_output_param(tmp_path):
+    from bigdl_b200.nn import layer as L
+    from bigdl_b200.nn.module import Module
+
+    prm = L.DetectionOutputParam(nClasses=5, keepTopK=7, confThresh=0.2)
+    a, b = L.DetectionOutputSSD(prm), L.DetectionOutputSSD.apply(prm, False)
+    assert (a.n_classes, a.keep_top_k, a.conf_thresh, a.conf_post_process, b.conf_post_process) == (5, 7, 0.2, True, False)
+    f = str(tmp_path / "d.bigdl")
+    a.saveModule(f, overWrite=True)
+    back = Module.loadModule(f)
+    assert (back.n_classes, back.keep_top_k) == (5, 7)

@@ -71,21 +71,12 @@ class Quantizer:
                 qm.setInputScales([[max(st["inputScales"][0])]])
             return qm
         if isinstance(m, Graph):
-            for n in m.exec_order:
-                new = cls._convert(n.element)
-                if new is not n.element:
-                    n.element = new
-            m._build()
-            return m
+            return GraphQuantizer.quantize(m)
         if isinstance(m, Container):
-            m.modules = [cls._convert(c) for c in m.modules]
-            if hasattr(m, "_after_children_replaced"):
-                m._after_children_replaced()
-            return m
-        cell = m.__dict__.get("cell")
-        if isinstance(cell, Module):           # Recurrent-style wrappers own a single cell (CellQuantizer)
-            m.cell = cls._convert(cell)
-        return m
+            return ContainerQuantizer.quantize(m)
+        if isinstance(m.__dict__.get("cell"), Module):           # Recurrent-style wrappers own a single cell
+            return CellQuantizer.quantize(m)
+        return ModuleQuantizer.quantize(m)
 
     # ---------------------------------------------------------------- calibration
     @staticmethod
@@ -184,3 +175,57 @@ def _fuse_through_identities(model: Module):
 Quantizer.register(LC.Linear, QL.Linear)
 Quantizer.register(LC.SpatialConvolution, QL.SpatialConvolution)
 Quantizer.register(LC.SpatialDilatedConvolution, QL.SpatialDilatedConvolution)
+
+
+# ------------------------------------------------------------------------------------------------ per-kind quantisers
+class Quantizable:
+    """What a layer's companion implements to take part in ``Quantizer.quantize`` (S/nn/quantized/Quantizable.scala):
+    ``quantize(module)`` returns the module to use in its place. Register an implementation for your own layer class
+    with ``Quantizer.register(FloatLayer, QuantLayer)`` where ``QuantLayer.from_float(layer)`` builds the replacement."""
+
+    @staticmethod
+    def quantize(module: Module) -> Module:  # pragma: no cover - interface
+        raise NotImplementedError
+
+
+class ModuleQuantizer(Quantizable):
+    """Leaf layers without a registered quantised twin stay as they are."""
+
+    @staticmethod
+    def quantize(module: Module) -> Module:
+        return module
+
+
+class ContainerQuantizer(Quantizable):
+    """Replace every child in place."""
+
+    @staticmethod
+    def quantize(module: Module) -> Module:
+        module.modules = [Quantizer._convert(c) for c in module.modules]
+        if hasattr(module, "_after_children_replaced"):
+            module._after_children_replaced()
+        return module
+
+
+class GraphQuantizer(Quantizable):
+    """Replace the element of every node, then rebuild the execution order."""
+
+    @staticmethod
+    def quantize(module: Module) -> Module:
+        for n in module.exec_order:
+            new = Quantizer._convert(n.element)
+            if new is not n.element:
+                n.element = new
+        module._build()
+        return module
+
+
+class CellQuantizer(Quantizable):
+    """Wrappers that own one inner ``cell`` module."""
+
+    @staticmethod
+    def quantize(module: Module) -> Module:
+        cell = module.__dict__.get("cell")
+        if isinstance(cell, Module):
+            module.cell = Quantizer._convert(cell)
+        return module

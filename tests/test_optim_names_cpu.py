@@ -304,3 +304,31 @@ def test_detection_output_param(tmp_path):
     a.saveModule(f, overWrite=True)
     back = Module.loadModule(f)
     assert (back.n_classes, back.keep_top_k) == (5, 7)
+
+
+def test_per_kind_quantizers():
+    from bigdl_b200.nn import layer as L
+    from bigdl_b200.quantized import layers as QL
+    from bigdl_b200.quantized.quantizer import (CellQuantizer, ContainerQuantizer, GraphQuantizer, ModuleQuantizer,
+                                                Quantizable, Quantizer)
+
+    relu = L.ReLU()
+    assert ModuleQuantizer.quantize(relu) is relu and issubclass(GraphQuantizer, Quantizable)
+    seq = L.Sequential().add(L.Linear(4, 3)).add(L.ReLU())
+    out = ContainerQuantizer.quantize(seq)
+    assert out is seq and isinstance(seq.modules[0], QL.QuantizedModule) and isinstance(seq.modules[1], L.ReLU)
+    inp = L.Input()
+    fc = L.Linear(4, 2).inputs(inp)
+    g = GraphQuantizer.quantize(L.Graph(inp, L.ReLU().inputs(fc)))
+    assert any(isinstance(m, QL.QuantizedModule) for m in g.all_modules())
+    x = torch.rand(3, 4)
+    assert tuple(g.forward(x).shape) == (3, 2)
+
+    class Holder(L.Identity):
+        def __init__(self, cell):
+            super().__init__()
+            self.cell = cell
+
+    h = CellQuantizer.quantize(Holder(L.Linear(4, 4)))
+    assert isinstance(h.cell, QL.QuantizedModule)
+    assert isinstance(Quantizer.quantize(L.Sequential().add(L.Linear(4, 3))).modules[0], QL.QuantizedModule)

@@ -48,8 +48,32 @@ class Quantization:
         return float((Quantization.dequantize_tensor(q, mx, mn) - x.float()).abs().mean())
 
 
+class DescType:
+    """Which of the four BigQuant descriptors a parameter record describes (Desc.scala:24-28)."""
+    ConvData, ConvWeight, LinearData, LinearWeight = "ConvData", "ConvWeight", "LinearData", "LinearWeight"
+
+
+ConvData, ConvWeight, LinearData, LinearWeight = (DescType.ConvData, DescType.ConvWeight, DescType.LinearData,
+                                                  DescType.LinearWeight)
+
+
+class DescParams:
+    """Base of the parameter records: ``getType`` names the descriptor kind, ``array`` lists the values in declaration
+    order (Desc.scala:30-40)."""
+
+    _type = None
+
+    def getType(self):
+        return self._type
+
+    def array(self):
+        return [getattr(self, f) for f in self.__dataclass_fields__]
+
+
 @dataclass
-class ConvDataParams:
+class ConvDataParams(DescParams):
+    _type = DescType.ConvData
+
     nInputPlane: int
     kernelH: int
     kernelW: int
@@ -65,7 +89,9 @@ class ConvDataParams:
 
 
 @dataclass
-class ConvWeightParams:
+class ConvWeightParams(DescParams):
+    _type = DescType.ConvWeight
+
     nOutputPlane: int
     nInputPlane: int
     kernelH: int
@@ -74,13 +100,17 @@ class ConvWeightParams:
 
 
 @dataclass
-class LinearDataParams:
+class LinearDataParams(DescParams):
+    _type = DescType.LinearData
+
     batchSize: int
     inputSize: int
 
 
 @dataclass
-class LinearWeightParams:
+class LinearWeightParams(DescParams):
+    _type = DescType.LinearWeight
+
     outputSize: int
     inputSize: int
 

@@ -521,3 +521,36 @@ CachedDistriDataSet = DistributedDataSet
 
 # the reference's default MiniBatch implementation class (S/dataset/MiniBatch.scala:112 ArrayTensorMiniBatch)
 ArrayTensorMiniBatch = MiniBatch
+
+
+class Utils:
+    """S/dataset/Utils.scala:22-45."""
+
+    @staticmethod
+    def getBatchSize(batchSize: int, totalPartition: int | None = None) -> int:
+        """The share of a global batch one partition (= one rank / GPU here) processes; the batch must divide
+        evenly."""
+        import torch.distributed as dist
+
+        nodes = dist.get_world_size() if (dist.is_available() and dist.is_initialized()) else 1
+        parts = totalPartition if totalPartition is not None else nodes
+        if parts <= 0:
+            raise ValueError(f"Utils.getBatchSize: partitionNum should be larger than 0, but get {parts}")
+        if batchSize % parts:
+            raise ValueError(f"Utils.getBatchSize: total batch size {batchSize} should be divided by partitionNum {parts}")
+        return batchSize // parts
+
+
+class Label:
+    """Something that carries a label (S/dataset/Types.scala:60-66)."""
+
+    def setLabel(self, label):
+        self._label = label
+        return self
+
+    def label(self):
+        return self._label
+
+
+class Image:
+    """Marker base of the in-memory image types (S/dataset/Types.scala:27-31)."""

@@ -565,3 +565,40 @@ def image_folder_dataset(path: str, scale_to: int = 256, distributed: bool = Fal
     paths = LocalImageFiles.readPaths(path)
     reader = LocalImgReader(scale_to, normalize=1.0)
     return DataSet.array(list(reader(iter(paths))), distributed)
+
+
+# ------------------------------------------------------------------------------------------------ detection demo
+class Visualizer:
+    """Draw the detections of one class onto an image file (S/dataset/image/Utils.scala:31-100): boxes scoring above
+    ``thresh`` get a red rectangle and a "<class> <score>" caption; the result is written to
+    ``outPath/<class>_<image file name>``. Nothing is written when no box passes the threshold."""
+
+    @staticmethod
+    def _vis(imgPath, className, scores, bboxes, savePath, thresh=0.3):
+        import cv2
+
+        scores = np.asarray(scores, dtype=np.float32).reshape(-1)
+        bboxes = np.asarray(bboxes, dtype=np.float32).reshape(-1, 4)
+        img = None
+        for score, (x1, y1, x2, y2) in zip(scores, bboxes):
+            if score <= thresh:
+                continue
+            if img is None:
+                img = cv2.imread(imgPath, cv2.IMREAD_COLOR)
+                if img is None:
+                    raise IOError(f"cannot decode image {imgPath}")
+            x1, y1, x2, y2 = int(x1), int(y1), int(x2), int(y2)
+            title = f"{className} {score:.3f}"
+            cv2.rectangle(img, (x1, y1), (x2, y2), (0, 0, 255), 3)
+            (tw, th), base = cv2.getTextSize(title, cv2.FONT_HERSHEY_SIMPLEX, 0.5, 1)
+            cv2.rectangle(img, (x1, y1 - 2 - th - base), (x1 + tw, y1 - 2 + base), (127, 0, 0), -1)
+            cv2.putText(img, title, (x1, y1 - 2), cv2.FONT_HERSHEY_SIMPLEX, 0.5, (255, 255, 255), 1)
+        if img is not None:
+            cv2.imwrite(savePath, img)
+        return img is not None
+
+    @staticmethod
+    def visDetection(imagePath: str, clsname: str, scores, bboxes, thresh: float = 0.3, outPath: str = "data/demo"):
+        os.makedirs(outPath, exist_ok=True)
+        path = os.path.join(outPath, f"{clsname}_{os.path.basename(imagePath)}")
+        return path if Visualizer._vis(imagePath, clsname, scores, bboxes, path, thresh) else None

@@ -405,7 +405,14 @@ class COCODeserializer:
         return SimpleAnnotation(cat, area, b[0], b[1], b[2], b[3], crowd, masks)
 
 
-class COCOPoly(PolyMasks):
+class COCOSegmentation:
+    """A mask that can write itself into a COCO record stream (COCODataset.scala:271-273)."""
+
+    def dumpTo(self, context: "COCOSerializeContext"):  # pragma: no cover - interface
+        raise NotImplementedError
+
+
+class COCOPoly(PolyMasks, COCOSegmentation):
     def dumpTo(self, context: COCOSerializeContext):
         context.dump(len(self.poly))
         for p in self.poly:
@@ -414,7 +421,7 @@ class COCOPoly(PolyMasks):
                 context.dump(float(v))
 
 
-class COCORLE(RLEMasks):
+class COCORLE(RLEMasks, COCOSegmentation):
     def dumpTo(self, context: COCOSerializeContext):
         context.dump(int(self.counts.size))
         for c in self.counts:

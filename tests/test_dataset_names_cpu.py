@@ -91,3 +91,20 @@ def test_sentence_types():
     assert s.copyToData(buf, 1) == [0, 1, 2, 3, 0] and s.copyToLabel([0] * 3) == [2, 3, 4]
     assert TX.SentenceToken.start == "SENTENCESTART"
     assert next(iter(TX.SentenceBiPadding()(iter(["a b"])))) == "SENTENCESTART a b SENTENCEEND"
+
+
+def test_visualizer_utils_and_markers(tmp_path):
+    import cv2
+
+    from bigdl_b200.dataset import segmentation as S
+
+    p = os.path.join(str(tmp_path), "dog.jpg")
+    cv2.imwrite(p, np.zeros((60, 80, 3), np.uint8))
+    out = I.Visualizer.visDetection(p, "dog", [0.9, 0.1], [[10, 20, 50, 50], [0, 0, 5, 5]], 0.3, str(tmp_path / "demo"))
+    assert out.endswith("dog_dog.jpg") and cv2.imread(out).sum() > 0
+    assert I.Visualizer.visDetection(p, "cat", [0.1], [[1, 1, 5, 5]], 0.3, str(tmp_path / "demo")) is None
+    assert B.Utils.getBatchSize(32) == 32 and B.Utils.getBatchSize(32, 4) == 8
+    with pytest.raises(ValueError):
+        B.Utils.getBatchSize(30, 4)
+    assert issubclass(S.COCOPoly, S.COCOSegmentation) and issubclass(S.COCORLE, S.COCOSegmentation)
+    assert B.Label().setLabel(3).label() == 3

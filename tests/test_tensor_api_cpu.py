@@ -287,3 +287,54 @@ def test_dnn_storage_native_pool():
     s.release()
     with pytest.raises(RuntimeError):
         s.tensor()
+
+
+def test_type_tags_converters_and_dense_helpers():
+    import torch.nn.functional as F
+
+    from bigdl_b200 import tensor as TT
+    from bigdl_b200.tensor import types as ty
+
+    assert TT.FloatType == torch.float32 and TT.Tensor(torch.zeros(2)).getType() == TT.FloatType
+    assert ty.TensorDataType.of(torch.int64) is TT.LongType and repr(TT.DoubleType) == "DoubleType"
+    assert TT.Tensor(torch.zeros(2)).getTensorType() == TT.DenseType and TT.DenseType != TT.SparseType
+    assert ty.ConvertableToInt.fromFloat(3.9) == 3 and ty.ConvertableToInt.fromDouble(-3.9) == -3
+    assert ty.ConvertableToShort.fromInt(40000) == 40000 - 65536 and ty.ConvertableToInt.fromDouble(1e12) == 2 ** 31 - 1
+    assert ty.ConvertableToFloat.fromDouble(0.1) == float(torch.tensor(0.1)) and ty.ConvertableToDouble.fromString("2.5") == 2.5
+    assert ty.ConvertableFromDouble.toInt(7.7) == 7 and ty.ConvertableFromString.toBoolean("True") and ty.ConvertableFromInt.toChar(65) == "A"
+    assert ty.TensorFunc2(lambda d, o: d[o] + 1).apply([1, 2], 1) == 3
+
+    a, b = torch.randn(3, 4, dtype=torch.float64), torch.randn(4, 5, dtype=torch.float64)
+    c = torch.zeros(15, dtype=torch.float64)
+    ty.DenseTensorBLAS.gemm("N", "N", 3, 5, 4, 1.0, a.t().contiguous().reshape(-1), 3, b.t().contiguous().reshape(-1), 4, 0.0, c, 3)
+    assert torch.allclose(c.reshape(5, 3).t(), a @ b)
+    c2 = torch.ones(15, dtype=torch.float64)
+    ty.DenseTensorBLAS.gemm("T", "N", 3, 5, 4, 2.0, a.contiguous().reshape(-1), 4, b.t().contiguous().reshape(-1), 4, 1.0, c2, 3)
+    assert torch.allclose(c2.reshape(5, 3).t(), 2 * (a @ b) + 1)
+    r = torch.ones(3, dtype=torch.float64)
+    ty.DenseTensorBLAS.gemv(2.0, a, b[:, 0].clone(), 1.0, r)
+    assert torch.allclose(r, 2 * (a @ b[:, 0]) + 1)
+    m = torch.zeros(3, 5, dtype=torch.float64)
+    ty.DenseTensorBLAS.ger(0.5, a[:, 0].clone(), b[0].clone(), m)
+    assert torch.allclose(m, 0.5 * torch.outer(a[:, 0], b[0]))
+
+    x, k = torch.randn(6, 7), torch.randn(3, 2)
+    valid_x = ty.DenseTensorConv.conv2Dmul(1.0, x, k, 1, 1, "V", "X").t
+    assert torch.allclose(valid_x, F.conv2d(x[None, None], k[None, None])[0, 0], atol=1e-5)
+    valid_c = ty.DenseTensorConv.conv2Dmul(2.0, x, k, 1, 1, "V", "C").t
+    assert torch.allclose(valid_c, 2 * F.conv2d(x[None, None], k.flip(0, 1)[None, None])[0, 0], atol=1e-5)
+    full_c = ty.DenseTensorConv.conv2Dmul(1.0, x, k, 1, 1, "F", "C").t
+    assert tuple(full_c.shape) == (8, 8)
+    assert torch.allclose(full_c, F.conv2d(F.pad(x, (1, 1, 2, 2))[None, None], k.flip(0, 1)[None, None])[0, 0], atol=1e-5)
+    assert torch.allclose(TT.Tensor(x).conv2(TT.Tensor(k), "F").t, full_c, atol=1e-5)
+    assert ty.DenseTensorConv.convSize(7, 3, 2, "V") == 3 and ty.DenseTensorConv.convSize(3, 3, 2, "F") == 7
+
+    t1 = torch.zeros(2, 3)
+    ty.DenseTensorApply.apply2(t1, torch.arange(6.0).reshape(2, 3), lambda p, q: p + 2 * q)
+    assert t1.tolist() == [[0, 2, 4], [6, 8, 10]]
+    ty.DenseTensorApply.apply1(t1, lambda v: v / 2)
+    assert t1.tolist() == [[0, 1, 2], [3, 4, 5]]
+    ty.DenseTensorDimApply.dimApply2(t1, torch.ones(2, 3), 1, lambda row, other: [sum(row)] * len(row))
+    assert t1.tolist() == [[3, 3, 3], [12, 12, 12]]
+    with pytest.raises(NotImplementedError):
+        ty.QuantizedTensorUnsupported().addmm

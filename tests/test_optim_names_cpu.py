@@ -332,3 +332,42 @@ def test_per_kind_quantizers():
     h = CellQuantizer.quantize(Holder(L.Linear(4, 4)))
     assert isinstance(h.cell, QL.QuantizedModule)
     assert isinstance(Quantizer.quantize(L.Sequential().add(L.Linear(4, 3))).modules[0], QL.QuantizedModule)
+
+
+def test_serializer_entry_points(tmp_path):
+    from bigdl_b200.nn import layer as L
+    from bigdl_b200.serialization.serializer import ModuleLoader, ModulePersister, ModuleSerializer
+
+    torch.manual_seed(0)
+    src = L.Sequential().add(L.Linear(4, 3).setName("fc1")).add(L.ReLU()).add(L.Linear(3, 2).setName("fc2"))
+    f = str(tmp_path / "m.bigdl")
+    ModulePersister.saveToFile(f, None, src, True)
+    back = ModuleLoader.loadFromFile(f)
+    x = torch.rand(5, 4)
+    assert torch.allclose(back.forward(x), src.forward(x))
+
+    dst = L.Sequential().add(L.Linear(4, 3).setName("fc1")).add(L.ReLU()).add(L.Linear(3, 2).setName("fc2"))
+    ModuleLoader.loadFromDefinition(dst, f, layers={"fc1"})
+    assert torch.equal(dst.modules[0].weight.data, src.modules[0].weight.data)
+    assert not torch.equal(dst.modules[2].weight.data, src.modules[2].weight.data)
+    ModuleLoader.loadFromDefinition(dst, f)
+    assert torch.allclose(dst.forward(x), src.forward(x))
+    other = L.Sequential().add(L.Linear(4, 3).setName("nope"))
+    with pytest.raises(KeyError):
+        ModuleLoader.loadFromDefinition(other, f)
+
+    d = str(tmp_path / "def.prototxt")
+    ModulePersister.saveModelDefinitionToFile(d, src, True)
+    text = open(d).read()
+    assert "fc1" in text and "Linear" in text and "float_data" not in text and len(text) < 4000
+    with pytest.raises(FileExistsError):
+        ModulePersister.saveModelDefinitionToFile(d, src)
+    assert torch.allclose(ModuleSerializer.load(ModuleSerializer.serialize(src)).forward(x), src.forward(x))
+
+    class Twice(L.Identity):
+        def updateOutput(self, input):
+            return input * 2
+
+    ModuleSerializer.registerModule("test.Twice", Twice)
+    with pytest.raises(ValueError):
+        ModuleSerializer.registerModule("test.Other")

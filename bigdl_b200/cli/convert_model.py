@@ -70,5 +70,10 @@ def main(argv=None):
     print(f"converted {a.src} model {a.input} → {a.dst} {a.output}")
 
 
+class ConvertModel:
+    """``ConvertModel.main(args)`` (S/utils/ConvertModel.scala)."""
+    main = staticmethod(main)
+
+
 if __name__ == "__main__":
     main()

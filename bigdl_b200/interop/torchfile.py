@@ -386,3 +386,15 @@ def load_torch_module(path: str):
     if not isinstance(m, Module):
         raise ValueError(f"{path} does not contain an nn module (got {type(m).__name__})")
     return m
+
+
+class TorchFile:
+    """``TorchFile.load(path)`` / ``TorchFile.save(obj, path, type, overWrite)`` (S/utils/TorchFile.scala:70-130)."""
+    load = staticmethod(load)
+
+    @staticmethod
+    def save(source, fileName: str, objectType=None, overWrite: bool = False):
+        return save(source, fileName, overWrite)
+
+    loadModule = staticmethod(load_torch_module)
+    saveModule = staticmethod(save_torch_module)

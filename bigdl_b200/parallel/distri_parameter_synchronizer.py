@@ -224,3 +224,33 @@ class DistriParameterSynchronizer:
             b.work = b.event = b.payload = None
             b.launched = False
         return self
+
+
+# ------------------------------------------------------------------------------------------------ reference names
+SyncMeta = _Bucket          # the per-layer record of an outstanding synchronisation (DistriParameterSynchronizer.scala:464)
+
+
+class SyncState:
+    """The four stages of one layer's synchronisation in the reference's BlockManager protocol
+    (DistriParameterSynchronizer.scala:471-477). Here a bucket moves INIT → launched (``put``: the collective is on
+    the communication stream) → ready (``get`` waited on its event); the names map onto those stages."""
+    INIT, FETCH_PARTITION, AGGREGATION, PUT_AGGREGATED = "0", "1", "2", "3"
+
+    @staticmethod
+    def of(bucket) -> str:
+        if bucket.ready:
+            return SyncState.PUT_AGGREGATED
+        if bucket.launched:
+            return SyncState.AGGREGATION
+        return SyncState.INIT
+
+
+class BlockManagerParameterSynchronizer(DistriParameterSynchronizer):
+    """``new BlockManagerParameterSynchronizer(partitionID, totalPartition)`` of the reference: the same
+    init / put / get / clear protocol. The Spark BlockManager transport (fetch the peers' compressed slices, sum, put
+    back) is replaced by one all-reduce per bucket over NVLink peer memory, NVLS or NCCL."""
+
+    def __init__(self, partitionID: int | None = None, totalPartition: int | None = None, **kw):
+        super().__init__(world=totalPartition, **kw)
+        self.partitionID = partitionID if partitionID is not None else (dist.get_rank() if dist.is_initialized() else 0)
+        self.totalPartition = self.world

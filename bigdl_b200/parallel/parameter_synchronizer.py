@@ -12,7 +12,10 @@ import torch
 import torch.distributed as dist
 
 
-class _Event:
+class Event:
+    """One rendezvous point: ``parties`` replicas deposit a tensor, meet at the barrier, read the sum
+    (ParameterSynchronizer.scala:108-150)."""
+
     def __init__(self, parties: int):
         self.parties = parties
         self.barrier = threading.Barrier(parties)
@@ -21,14 +24,14 @@ class _Event:
 
 
 class ParameterSynchronizer:
-    _events: dict[str, _Event] = {}
+    _events: dict[str, Event] = {}
     _lock = threading.Lock()
 
     @classmethod
     def register(cls, key: str, parties: int):
         with cls._lock:
             if key not in cls._events:
-                cls._events[key] = _Event(parties)
+                cls._events[key] = Event(parties)
 
     @classmethod
     def reset(cls, key: str | None = None):
@@ -73,3 +76,6 @@ def enable_sync_batchnorm(model, group=None):
             m._sync = group if group is not None else (dist.group.WORLD if dist.is_initialized() else None)
             n += 1
     return n
+
+
+_Event = Event

@@ -133,3 +133,13 @@ def init_engine(**kw):
 
 def get_node_and_core_number():
     return Engine.nodeNumber(), Engine.coreNumber()
+
+
+class EngineType:
+    """The execution back ends ``bigdl.engineType`` selects (S/utils/Engine.scala:37-41). ``MklBlas`` / ``MklDnn`` are
+    the reference's two CPU engines — both are accepted and run the host (oracle) path here; ``B200`` is the sm_100a
+    engine and the default on a machine with a GPU."""
+    MklBlas, MklDnn, B200 = "mklblas", "mkldnn", "b200"
+
+
+MklBlas, MklDnn = EngineType.MklBlas, EngineType.MklDnn

@@ -46,3 +46,9 @@ redire_spark_logs = redirectSparkInfoLogs
 
 def show_bigdl_info_logs(level=logging.INFO):
     logging.getLogger("bigdl_b200").setLevel(level)
+
+
+class LoggerFilter:
+    """Object form of the two functions above (S/utils/LoggerFilter.scala:90-134)."""
+    redirectSparkInfoLogs = staticmethod(redirectSparkInfoLogs)
+    show_bigdl_info_logs = staticmethod(show_bigdl_info_logs)

@@ -371,3 +371,27 @@ def test_serializer_entry_points(tmp_path):
     ModuleSerializer.registerModule("test.Twice", Twice)
     with pytest.raises(ValueError):
         ModuleSerializer.registerModule("test.Other")
+
+
+def test_utils_object_names():
+    from bigdl_b200.cli.convert_model import ConvertModel
+    from bigdl_b200.interop.torchfile import TorchFile
+    from bigdl_b200.parallel.distri_parameter_synchronizer import (BlockManagerParameterSynchronizer, SyncMeta,
+                                                                   SyncState)
+    from bigdl_b200.parallel.parameter_synchronizer import Event, ParameterSynchronizer
+    from bigdl_b200.utils.engine import EngineType, MklBlas
+    from bigdl_b200.utils.logger_filter import LoggerFilter
+
+    s = BlockManagerParameterSynchronizer(0, 1)
+    w, g = torch.zeros(4), torch.ones(4)
+    s.init("fc", 4, 1, w, g)
+    b = s.buckets["fc"]
+    assert isinstance(b, SyncMeta) and SyncState.of(b) == SyncState.INIT and s.partitionID == 0 and s.totalPartition == 1
+    s.put("fc")
+    s.get("fc")
+    assert SyncState.of(b) == SyncState.PUT_AGGREGATED
+    ParameterSynchronizer.register("k", 1)
+    assert isinstance(ParameterSynchronizer._events["k"], Event)
+    ParameterSynchronizer.reset("k")
+    assert MklBlas == EngineType.MklBlas == "mklblas" and callable(LoggerFilter.redirectSparkInfoLogs)
+    assert callable(TorchFile.load) and callable(ConvertModel.main)

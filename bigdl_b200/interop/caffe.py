@@ -91,11 +91,52 @@ def _conv_geometry(cp):
     return kh, kw, sh, sw, ph, pw, dh, dw
 
 
+class CaffeConversionException(ValueError):
+    """Raised for a layer that cannot be converted (S/utils/caffe/CaffeConversionException.scala)."""
+
+    def __init__(self, conversionMsg: str, error: BaseException | None = None):
+        super().__init__(conversionMsg)
+        self.conversionMsg, self.error = conversionMsg, error
+
+    def __str__(self):
+        return f"Caffe conversion error : {self.conversionMsg}" + (f"\n{self.error!r}" if self.error else "")
+
+
+class Customizable:
+    """Base of user converters handed to ``loadCaffe(customizedConverters={"TYPE": conv})`` (CaffeLoader.scala:37-47):
+    implement ``convertor(layer)`` (optionally ``convertor(layer, blobs)``) returning the module for that layer; the
+    loader registers the parsed net as ``contexts["netparam"]`` and the name → layer map as
+    ``contexts["name2LayerV2"]`` before converting. A plain ``fn(layer, blobs)`` works too."""
+
+    contexts: dict | None = None
+
+    def convertor(self, layer, blobs=None):  # pragma: no cover - interface
+        raise NotImplementedError
+
+    def registerContext(self, name: str, context):
+        if self.contexts is None:
+            self.contexts = {}
+        self.contexts[name] = context
+
+    def __call__(self, layer, blobs=None):
+        import inspect
+
+        n = len(inspect.signature(self.convertor).parameters)
+        return self.convertor(layer, blobs) if n >= 2 else self.convertor(layer)
+
+
 class _Converter:
     """One caffe layer → one module (or a small Sequential). ``blobs`` are the trained tensors, possibly empty."""
 
     def __init__(self, customized=None):
-        self.custom = customized or {}
+        self.custom = dict(customized or {})
+
+    def registerCutomizedConverter(self, layerType: str, converter):
+        """(sic — the reference's spelling, Converter.scala:60) add a converter for a layer type."""
+        self.custom[layerType] = converter
+        return self
+
+    registerCustomizedConverter = registerCutomizedConverter
 
     def convert(self, typ, l, blobs, in_channels=None):
         from ..nn import layer as L
@@ -104,7 +145,7 @@ class _Converter:
             return self.custom[typ](l, blobs)
         fn = getattr(self, "_" + typ.lower(), None)
         if fn is None:
-            raise ValueError(f"unsupported caffe layer type {typ} (layer {l.name})")
+            raise CaffeConversionException(f"unsupported caffe layer type {typ} (layer {l.name})")
         m = fn(L, l, blobs)
         if m is not None and l.name:
             m.setName(l.name)
@@ -298,6 +339,19 @@ class _Converter:
         return None            # handled by the graph builder (needs the number of tops)
 
 
+Converter = _Converter
+
+
+class LayerConverter(_Converter):
+    """Converter of the current ``LayerParameter`` message (LayerConverter.scala). Old-style ``V1LayerParameter``
+    nets are normalised to the same (name, TYPE, bottoms, tops, message) tuples by ``_layers`` before conversion, so
+    one converter serves both formats."""
+
+
+class V1LayerConverter(_Converter):
+    """Converter of the legacy ``V1LayerParameter`` message (V1LayerConverter.scala); see ``LayerConverter``."""
+
+
 class CaffeLoader:
     @staticmethod
     def loadCaffe(defPath: str, modelPath: str, customizedConverters=None, outputNames=None):
@@ -308,7 +362,11 @@ class CaffeLoader:
 
         net_def, net_w = _read_net(defPath, modelPath)
         weights = {name: [_blob(b) for b in msg.blobs] for name, _, _, _, msg in _layers(net_w)}
-        conv = _Converter(customizedConverters)
+        conv = LayerConverter(customizedConverters)
+        for c in (customizedConverters or {}).values():
+            if isinstance(c, Customizable):
+                c.registerContext("netparam", net_def)
+                c.registerContext("name2LayerV2", {name: msg for name, _, _, _, msg in _layers(net_def)})
         tops: dict[str, Node] = {}
         inputs: list[Node] = []
         criterion = None

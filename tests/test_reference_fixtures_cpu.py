@@ -26,6 +26,21 @@ def test_caffe_fixture_with_customized_converter():
     g, crit = CaffeLoader.loadCaffe(f"{RES}/caffe/test.prototxt", f"{RES}/caffe/test.caffemodel",
                                     customizedConverters={"Dummy": dummy})
     assert seen and crit is not None
+
+    # the object form: a Customizable gets the parsed net as context (CaffeLoader.scala:37-47,73-83)
+    from bigdl_b200.interop.caffe import CaffeConversionException, Customizable, LayerConverter
+
+    class DummyConv(Customizable):
+        def convertor(self, layer):
+            return Identity().setName(layer.name)
+
+    dc = DummyConv()
+    g2, _ = CaffeLoader.loadCaffe(f"{RES}/caffe/test.prototxt", f"{RES}/caffe/test.caffemodel",
+                                  customizedConverters={"Dummy": dc})
+    assert "netparam" in dc.contexts and dc.contexts["name2LayerV2"] and len(list(g2.all_modules())) == len(list(g.all_modules()))
+    with pytest.raises(CaffeConversionException, match="Caffe conversion error"):
+        LayerConverter().convert("NoSuchType", type("L", (), {"name": "x"})(), [])
+    assert LayerConverter().registerCutomizedConverter("Dummy", dummy).custom["Dummy"] is dummy
     g.evaluate()
     params = [p for p in g.torch_parameters()]
     assert len(params) >= 5 and all(float(p.abs().sum()) > 0 for p in params if p.dim() > 1)     # trained blobs were copied

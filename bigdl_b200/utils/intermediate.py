@@ -159,3 +159,106 @@ class ConversionUtils:
         from ..nn.fusion import unfuse
 
         return unfuse(model)
+
+
+# ------------------------------------------------------------------------------------------------ typed operators
+class IROperator:
+    """Engine-neutral description of ONE layer (IRElement.scala:27-140): its kind is the class, its settings are the
+    attributes (the constructor arguments of the source layer). ``IRElement.operator()`` builds it from an element."""
+
+    layer: str | None = None                      # the nn.layer class this operator stands for
+
+    def __init__(self, **attrs):
+        self.__dict__.update(attrs)
+
+    def name(self) -> str:
+        return type(self).__name__
+
+    def attrs(self) -> dict:
+        return dict(self.__dict__)
+
+    def __eq__(self, o):
+        return type(o) is type(self) and {k: v for k, v in o.__dict__.items() if not hasattr(v, "shape")} == \
+            {k: v for k, v in self.__dict__.items() if not hasattr(v, "shape")}
+
+    def __hash__(self):
+        return hash(type(self).__name__)
+
+    def __repr__(self):
+        return f"{type(self).__name__}({', '.join(f'{k}={v!r}' for k, v in self.__dict__.items() if not hasattr(v, 'shape'))})"
+
+
+def _ir(name, layer):
+    return type(name, (IROperator,), {"layer": layer, "__doc__": f"IR form of ``nn.{layer}``."})
+
+
+IRSpatialMaxPooling = _ir("IRSpatialMaxPooling", "SpatialMaxPooling")
+IRSpatialAveragePooling = _ir("IRSpatialAveragePooling", "SpatialAveragePooling")
+IRSpatialConvolution = _ir("IRSpatialConvolution", "SpatialConvolution")
+IRSpatialShareConvolution = _ir("IRSpatialShareConvolution", "SpatialShareConvolution")
+IRSpatialBatchNormalization = _ir("IRSpatialBatchNormalization", "SpatialBatchNormalization")
+IRIdentity = _ir("IRIdentity", "Identity")
+IRDropout = _ir("IRDropout", "Dropout")
+IRReLU = _ir("IRReLU", "ReLU")
+IRLinear = _ir("IRLinear", "Linear")
+IRSqueeze = _ir("IRSqueeze", "Squeeze")
+IRSpatialCrossMapLRN = _ir("IRSpatialCrossMapLRN", "SpatialCrossMapLRN")
+IRSoftMax = _ir("IRSoftMax", "SoftMax")
+IRSelectTable = _ir("IRSelectTable", "SelectTable")
+IRCAddTable = _ir("IRCAddTable", "CAddTable")
+IRJoinTable = _ir("IRJoinTable", "JoinTable")
+IRConcatTable = _ir("IRConcatTable", "ConcatTable")
+IRInput = _ir("IRInput", "Input")
+
+
+class IRGeneralModule(IROperator):
+    """Any layer without a dedicated operator: carries the source module itself (IRElement.scala:139-140)."""
+
+    def __init__(self, model=None, **attrs):
+        super().__init__(**attrs)
+        self.model = model
+
+
+_IR_OF_LAYER = {c.layer: c for c in (IRSpatialMaxPooling, IRSpatialAveragePooling, IRSpatialConvolution,
+                                     IRSpatialShareConvolution, IRSpatialBatchNormalization, IRIdentity, IRDropout,
+                                     IRReLU, IRLinear, IRSqueeze, IRSpatialCrossMapLRN, IRSoftMax, IRSelectTable,
+                                     IRCAddTable, IRJoinTable, IRConcatTable, IRInput)}
+
+
+def _operator(self) -> IROperator:
+    cls = _IR_OF_LAYER.get(self.op)
+    if cls is None:
+        return IRGeneralModule(self.weights.get("__module__"), **self.attrs)
+    return cls(**{k: v for k, v in self.attrs.items()})
+
+
+IRElement.operator = _operator
+
+
+class ConvertBase:
+    """Shared shape of the two directions (BlasToIR / IRToBlas / IRToDnn extend it in the reference):
+    ``convertLayerCheck(layer)`` says whether a dedicated mapping exists, ``convertLayer(layer)`` performs it."""
+
+    @staticmethod
+    def convertLayerCheck(layer) -> bool:
+        name = layer.op if isinstance(layer, IRElement) else type(layer).__name__
+        return name in _IR_OF_LAYER
+
+    @staticmethod
+    def convertLayer(layer):
+        if isinstance(layer, IRElement):
+            return layer.weights.get("__module__")
+        attrs = dict(layer.__dict__.get("_ctor_args", {}) or {})
+        return IRElement(layer.getName(), type(layer).__name__, attrs, {"__module__": layer})
+
+
+class IRConverter:
+    """``IRConverter(irGraph).toGraph()`` (IRConverter.scala:31-140): emit the model for the active engine —
+    a ``DnnGraph`` (fusion-capable) when ``bigdl.engineType`` is ``mkldnn`` / ``b200``, a plain ``Graph`` otherwise."""
+
+    def __init__(self, IRgraph: IRGraph):
+        self.ir = IRgraph
+
+    def toGraph(self):
+        engine = str(config.get("bigdl.engineType"))
+        return IRToDnn.convert(self.ir) if engine in ("mkldnn", "b200") else IRToBlas.convert(self.ir)

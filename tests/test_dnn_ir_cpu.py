@@ -107,3 +107,38 @@ def test_reorder_manager_tensor_mmap_and_quantization_rule():
     assert Quantization.loss(w) < 0.02
     d = Desc.of(SpatialConvolution(4, 6, 3, 3))
     assert (d.nOutputPlane, d.nInputPlane, d.kernelH) == (6, 4, 3)
+
+
+def test_typed_ir_operators_and_converter():
+    import torch
+
+    from bigdl_b200.nn import layer as L
+    from bigdl_b200.nn.mkldnn import DnnGraph
+    from bigdl_b200.utils import config
+    from bigdl_b200.utils import intermediate as IR
+
+    m = L.Sequential().add(L.SpatialConvolution(3, 4, 3, 3, 1, 1, 1, 1)).add(L.ReLU()).add(L.SpatialMaxPooling(2, 2, 2, 2)) \
+        .add(L.View(4 * 4 * 4)).add(L.Linear(64, 5)).add(L.SoftMax())
+    ir = IR.BlasToIR.convert(m)
+    ops = [n.element.operator() for n in ir.nodes]
+    assert isinstance(ops[0], IR.IRSpatialConvolution) and ops[0].n_output_plane == 4 and ops[0].kernel_w == 3
+    assert isinstance(ops[1], IR.IRReLU) and isinstance(ops[2], IR.IRSpatialMaxPooling)
+    assert isinstance(ops[3], IR.IRGeneralModule) and isinstance(ops[3].model, L.View)       # no dedicated operator
+    assert isinstance(ops[4], IR.IRLinear) and isinstance(ops[5], IR.IRSoftMax) and ops[5].name() == "IRSoftMax"
+    assert ops[1] == IR.IRReLU(**ops[1].attrs()) and ops[1] != ops[5] and "IRLinear(" in repr(ops[4])
+    assert IR.ConvertBase.convertLayerCheck(m.modules[0]) and not IR.ConvertBase.convertLayerCheck(m.modules[3])
+    el = IR.ConvertBase.convertLayer(m.modules[4])
+    assert el.op == "Linear" and IR.ConvertBase.convertLayer(el) is m.modules[4]
+
+    x = torch.rand(2, 3, 8, 8)
+    want = m.forward(x)
+    old = config.get("bigdl.engineType")
+    try:
+        config.set("bigdl.engineType", "mkldnn")
+        g = IR.IRConverter(ir).toGraph()
+        assert isinstance(g, DnnGraph) and torch.allclose(g.forward(x), want, atol=1e-6)
+        config.set("bigdl.engineType", "mklblas")
+        g2 = IR.IRConverter(ir).toGraph()
+        assert not isinstance(g2, DnnGraph) and torch.allclose(g2.forward(x), want, atol=1e-6)
+    finally:
+        config.set("bigdl.engineType", old)

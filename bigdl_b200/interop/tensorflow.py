@@ -754,6 +754,210 @@ class _GraphBuilder:
         return f"{base}_{self.count}"
 
 
+_CUSTOM_SAVERS: dict = {}
+
+
+class BigDLToTensorflow:
+    """Exporter of one layer type (S/utils/tf/BigDLToTensorflow.scala:30-35): ``toTFDef(module, inputs, byteOrder)``
+    gets the NodeDefs feeding the layer and returns the NodeDefs to append — the FIRST one is the layer's output.
+    Build them with the ``Tensorflow`` helpers; register with ``TensorflowSaver.register("MyLayer", saver)``."""
+
+    def toTFDef(self, module, inputs, byteOrder):  # pragma: no cover - interface
+        raise NotImplementedError
+
+
+class TensorflowDataFormat:
+    """Activation layout of the exported graph (S/utils/tf/Tensorflow.scala:33-85)."""
+    NCHW, NHWC = "NCHW", "NHWC"
+
+
+class Tensorflow:
+    """NodeDef builders (S/utils/tf/Tensorflow.scala:88-560). Every function returns a detached ``NodeDef`` whose
+    inputs are the NAMES of the NodeDefs passed in."""
+
+    _f32 = np.dtype(np.float32)
+
+    @staticmethod
+    def _node(op_name, name, inputs=(), **attrs):
+        b = _GraphBuilder()
+        b.node(op_name, name, [i.name if hasattr(i, "name") else str(i) for i in inputs], **attrs)
+        return b.gd.node[0]
+
+    @staticmethod
+    def placeholder(dtype=None, shape=(), name="input"):
+        n = Tensorflow._node("Placeholder", name, dtype=Tensorflow._f32 if dtype is None else np.dtype(dtype))
+        for s in shape:
+            n.attr["shape"].shape.dim.add().size = int(s if s is not None else -1)
+        return n
+
+    @staticmethod
+    def const(value, name, byteOrder="little_endian"):
+        arr = value.detach().cpu().numpy() if isinstance(value, torch.Tensor) else np.asarray(
+            getattr(value, "t", value).detach().cpu().numpy() if hasattr(getattr(value, "t", None), "detach") else value)
+        return Tensorflow._node("Const", name, value=np.ascontiguousarray(arr), dtype=arr.dtype)
+
+    @staticmethod
+    def identity(input, name): return Tensorflow._node("Identity", name, [input], T=Tensorflow._f32)
+
+    @staticmethod
+    def matmul(a, b, name, transposeA=False, transposeB=False):
+        return Tensorflow._node("MatMul", name, [a, b], T=Tensorflow._f32, transpose_a=bool(transposeA),
+                                transpose_b=bool(transposeB))
+
+    @staticmethod
+    def transpose(x, perm, name): return Tensorflow._node("Transpose", name, [x, perm], T=Tensorflow._f32)
+
+    @staticmethod
+    def biasAdd(value, bias, dataFormat, name):
+        return Tensorflow._node("BiasAdd", name, [value, bias], T=Tensorflow._f32, data_format=str(dataFormat))
+
+    @staticmethod
+    def expandDims(input, dim, name): return Tensorflow._node("ExpandDims", name, [input, dim], T=Tensorflow._f32)
+
+    @staticmethod
+    def relu(features, name): return Tensorflow._node("Relu", name, [features], T=Tensorflow._f32)
+
+    @staticmethod
+    def tanh(input, name): return Tensorflow._node("Tanh", name, [input], T=Tensorflow._f32)
+
+    @staticmethod
+    def sigmoid(x, name): return Tensorflow._node("Sigmoid", name, [x], T=Tensorflow._f32)
+
+    @staticmethod
+    def softmax(logits, name): return Tensorflow._node("Softmax", name, [logits], T=Tensorflow._f32)
+
+    @staticmethod
+    def logSoftmax(logits, name): return Tensorflow._node("LogSoftmax", name, [logits], T=Tensorflow._f32)
+
+    @staticmethod
+    def rsqrt(x, name): return Tensorflow._node("Rsqrt", name, [x], T=Tensorflow._f32)
+
+    @staticmethod
+    def floor(x, name): return Tensorflow._node("Floor", name, [x], T=Tensorflow._f32)
+
+    @staticmethod
+    def reshape(tensor, shape, name): return Tensorflow._node("Reshape", name, [tensor, shape], T=Tensorflow._f32)
+
+    @staticmethod
+    def squeeze(input, axis, name):
+        return Tensorflow._node("Squeeze", name, [input], T=Tensorflow._f32, squeeze_dims=[int(a) for a in axis])
+
+    @staticmethod
+    def _spatial(op_name, value, name, k, s, p, dataFormat, **extra):
+        nhwc = str(dataFormat).upper() == "NHWC"
+        ks = [1, k[0], k[1], 1] if nhwc else [1, 1, k[0], k[1]]
+        st = [1, s[0], s[1], 1] if nhwc else [1, 1, s[0], s[1]]
+        attrs = dict(T=Tensorflow._f32, strides=st, padding="SAME" if -1 in p else "VALID", data_format=str(dataFormat).upper())
+        if op_name != "Conv2D":
+            attrs["ksize"] = ks
+        return Tensorflow._node(op_name, name, value, **attrs, **extra)
+
+    @staticmethod
+    def conv2D(input, filter, sW, sH, kW, kH, pW, pH, dataFormat, name):
+        return Tensorflow._spatial("Conv2D", [input, filter], name, (kH, kW), (sH, sW), (pH, pW), dataFormat)
+
+    @staticmethod
+    def maxPool(value, kW, kH, pW, pH, sW, sH, dataFormat, name, ceilMode=False):
+        return Tensorflow._spatial("MaxPool", [value], name, (kH, kW), (sH, sW), (-1, -1) if ceilMode else (pH, pW),
+                                   dataFormat)
+
+    @staticmethod
+    def avgPool(value, kW, kH, pW, pH, sW, sH, dataFormat, name, ceilMode=False):
+        return Tensorflow._spatial("AvgPool", [value], name, (kH, kW), (sH, sW), (-1, -1) if ceilMode else (pH, pW),
+                                   dataFormat)
+
+    @staticmethod
+    def multiply(x, y, name): return Tensorflow._node("Mul", name, [x, y], T=Tensorflow._f32)
+
+    @staticmethod
+    def add(x, y, name): return Tensorflow._node("Add", name, [x, y], T=Tensorflow._f32)
+
+    @staticmethod
+    def subtract(x, y, name): return Tensorflow._node("Sub", name, [x, y], T=Tensorflow._f32)
+
+    @staticmethod
+    def realdiv(x, y, name): return Tensorflow._node("RealDiv", name, [x, y], T=Tensorflow._f32)
+
+    @staticmethod
+    def shape(input, name, outType=None): return Tensorflow._node("Shape", name, [input], T=Tensorflow._f32)
+
+    @staticmethod
+    def randomUniform(shape, name, dtype=None, seed=0):
+        return Tensorflow._node("RandomUniform", name, [shape], dtype=Tensorflow._f32, seed=int(seed))
+
+    @staticmethod
+    def addN(inputs, name): return Tensorflow._node("AddN", name, list(inputs), T=Tensorflow._f32, N=len(inputs))
+
+    @staticmethod
+    def concat(inputs, name): return Tensorflow._node("ConcatV2", name, list(inputs), T=Tensorflow._f32, N=len(inputs) - 1)
+
+    @staticmethod
+    def pad(tensor, paddings, name): return Tensorflow._node("Pad", name, [tensor, paddings], T=Tensorflow._f32)
+
+    @staticmethod
+    def reduceMean(inputTensor, axis, keepDim, name):
+        return Tensorflow._node("Mean", name, [inputTensor, axis], T=Tensorflow._f32, keep_dims=bool(keepDim))
+
+    @staticmethod
+    def split(splitDim, value, numSplit, name):
+        return Tensorflow._node("Split", name, [splitDim, value], T=Tensorflow._f32, num_split=int(numSplit))
+
+    @staticmethod
+    def lrn(input, depthRadius, bias, alpha, beta, name):
+        return Tensorflow._node("LRN", name, [input], T=Tensorflow._f32, depth_radius=int(depthRadius), bias=float(bias),
+                                alpha=float(alpha), beta=float(beta))
+
+
+class TensorflowSaver:
+    """``saveGraph`` / ``saveGraphWithNodeDef`` / ``register`` (S/utils/tf/TensorflowSaver.scala:40-170)."""
+
+    @staticmethod
+    def saveGraph(model, inputs, path, byteOrder="little_endian", dataFormat=TensorflowDataFormat.NHWC):
+        return save_tf(model, inputs, path, byteOrder, str(dataFormat).lower())
+
+    @staticmethod
+    def saveGraphWithNodeDef(model, inputs, path, byteOrder="little_endian", extraNodes=()):
+        """``inputs`` are Placeholder NodeDefs (their names and shapes are used); ``extraNodes`` are appended as is."""
+        specs = [(n.name, [d.size for d in n.attr["shape"].shape.dim]) for n in inputs]
+        out = save_tf(model, specs, path, byteOrder, "nchw")
+        if extraNodes:
+            gd = P.GraphDef()
+            with open(path, "rb") as f:
+                gd.ParseFromString(f.read())
+            for n in extraNodes:
+                gd.node.add().CopyFrom(n)
+            with open(path, "wb") as f:
+                f.write(gd.SerializeToString())
+        return out
+
+    @staticmethod
+    def register(className: str, saver: BigDLToTensorflow):
+        _CUSTOM_SAVERS[className.split(".")[-1]] = saver
+
+
+class TensorflowLoader:
+    """``load(graphFile, inputs, outputs, byteOrder, binFile)`` and ``checkpoints(graphFile, binFile, byteOrder)``
+    (S/utils/tf/TensorflowLoader.scala:55-110)."""
+
+    @staticmethod
+    def load(graphPrototxt, inputs, outputs, byteOrder="little_endian", binFile=None, generatedBackward=True):
+        return load_tf(graphPrototxt, inputs, outputs, byteOrder, binFile, generatedBackward)
+
+    @staticmethod
+    def checkpoints(graphFile, binFile, byteOrder="little_endian"):
+        from .tf_session import Session
+
+        return Session(graphFile, binFile)
+
+    @staticmethod
+    def parse(graphProtoTxt: str):
+        """The nodes of a binary GraphDef file."""
+        gd = P.GraphDef()
+        with open(graphProtoTxt, "rb") as f:
+            gd.ParseFromString(f.read())
+        return list(gd.node)
+
+
 def save_tf(model, inputs, path: str, byteOrder: str = "little_endian", dataFormat: str = "nhwc"):
     """Export a Sequential / Graph of common layers as a frozen GraphDef (TensorflowSaver.saveGraph,
     BigDLToTensorflow.scala). ``inputs``: [(placeholder name, shape)] — shapes are given in the framework's NCHW
@@ -772,6 +976,15 @@ def save_tf(model, inputs, path: str, byteOrder: str = "little_endian", dataForm
             name = b.fresh(name)
         used.add(name)
         x = ins[0] if ins else None
+        custom = _CUSTOM_SAVERS.get(type(m).__name__) or _CUSTOM_SAVERS.get(f"{type(m).__module__}.{type(m).__name__}")
+        if custom is not None:
+            by_name = {nd.name: nd for nd in b.gd.node}
+            made = custom.toTFDef(m, [by_name[i] for i in ins], byteOrder)
+            if not made:
+                raise ValueError(f"saveTF: the saver registered for {type(m).__name__} returned no nodes")
+            for nd in made:
+                b.gd.node.add().CopyFrom(nd)
+            return made[0].name           # the FIRST returned node is the layer's output (BigDLToTensorflow contract)
         if isinstance(m, Sequential):
             cur = ins
             for c in m.modules:

@@ -431,3 +431,59 @@ def test_small_state_and_wrapper_ops():
     png = cv2.imencode(".png", img)[1].tobytes()
     dec = G.DecodePng(3).forward(np.array([png], dtype=object))
     assert tuple(dec.shape) == (5, 4, 3) and np.array_equal(dec.numpy().astype(np.uint8), img[..., ::-1])
+
+
+def test_saver_registry_and_nodedef_builders(tmp_path):
+    from bigdl_b200.interop import tensorflow as TF
+    from bigdl_b200.nn import layer as L
+
+    from bigdl_b200.nn.module import Module
+
+    class Times(Module):
+        def __init__(self, k):
+            super().__init__()
+            self.k = k
+
+        def updateOutput(self, input):
+            return input * self.k
+
+    class TimesSaver(TF.BigDLToTensorflow):
+        def toTFDef(self, module, inputs, byteOrder):
+            assert len(inputs) == 1 and byteOrder == "little_endian"
+            k = TF.Tensorflow.const(np.array(module.k, np.float32), module.getName() + "/k")
+            return [TF.Tensorflow.multiply(inputs[0], k, module.getName()), k]
+
+    m = L.Sequential().add(L.Linear(4, 3).setName("fc")).add(Times(3.0).setName("times")).add(L.Tanh().setName("act"))
+    p = str(tmp_path / "m.pb")
+    with pytest.raises(ValueError, match="unsupported module Times"):
+        TF.TensorflowSaver.saveGraph(m, [("input", [2, 4])], p)
+    TF.TensorflowSaver.register("my.pkg.Times", TimesSaver())
+    try:
+        outs = TF.TensorflowSaver.saveGraph(m, [("input", [2, 4])], p)
+        g = TF.TensorflowLoader.load(p, ["input"], outs)
+        x = torch.rand(2, 4)
+        assert torch.allclose(g.forward(x), m.forward(x), atol=1e-6)
+        assert {n.op for n in TF.TensorflowLoader.parse(p)} >= {"Placeholder", "MatMul", "Mul", "Tanh", "Const"}
+
+        ph = TF.Tensorflow.placeholder(np.float32, [2, 4], "input")
+        extra = TF.Tensorflow.identity(ph, "alias")
+        p2 = str(tmp_path / "m2.pb")
+        outs2 = TF.TensorflowSaver.saveGraphWithNodeDef(m, [ph], p2, extraNodes=[extra])
+        g2 = TF.TensorflowLoader.load(p2, ["input"], outs2 + ["alias"])
+        both = g2.forward(x)
+        assert torch.allclose(both[1], m.forward(x), atol=1e-6) and torch.equal(both[2], x)
+    finally:
+        TF._CUSTOM_SAVERS.clear()
+
+    T = TF.Tensorflow
+    a, b2 = T.placeholder(np.float32, [2, 3], "a"), T.placeholder(np.float32, [3, 2], "b")
+    mm = T.matmul(a, b2, "mm", transposeB=True)
+    assert mm.op == "MatMul" and list(mm.input) == ["a", "b"] and mm.attr["transpose_b"].b and not mm.attr["transpose_a"].b
+    cv = T.conv2D(a, b2, 2, 1, 3, 3, -1, -1, TF.TensorflowDataFormat.NHWC, "cv")
+    assert list(cv.attr["strides"].list.i) == [1, 1, 2, 1] and cv.attr["padding"].s == b"SAME"
+    mp = T.maxPool(a, 2, 3, 0, 0, 2, 2, "NCHW", "mp")
+    assert list(mp.attr["ksize"].list.i) == [1, 1, 3, 2] and mp.attr["padding"].s == b"VALID"
+    assert T.addN([a, b2], "s").attr["N"].i == 2 and T.squeeze(a, [1], "sq").attr["squeeze_dims"].list.i[0] == 1
+    assert T.lrn(a, 2, 1.0, 1e-4, 0.75, "l").attr["depth_radius"].i == 2 and T.reduceMean(a, b2, True, "m").attr["keep_dims"].b
+    for fn in (T.relu, T.tanh, T.sigmoid, T.softmax, T.logSoftmax, T.rsqrt, T.floor):
+        assert list(fn(a, "n").input) == ["a"]

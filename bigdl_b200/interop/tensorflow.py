@@ -1119,3 +1119,29 @@ def save_tf(model, inputs, path: str, byteOrder: str = "little_endian", dataForm
     with open(path, "wb") as f:
         f.write(b.gd.SerializeToString())
     return out
+
+
+class TFUtils:
+    """S/utils/tf/TFUtils.scala: ``parseTensor(TensorProto, endian)`` → tensor."""
+
+    @staticmethod
+    def parseTensor(tfTensor, endian: str = "little_endian"):
+        arr = P.tensor_to_numpy(tfTensor, "big_endian" if str(endian).lower().startswith("big") else "little_endian")
+        if arr.dtype == object or arr.dtype.kind in "US":
+            return arr
+        return torch.from_numpy(np.ascontiguousarray(arr))
+
+    @staticmethod
+    def saveToHDFS(localFiles, outputPath: str, overwrite: bool = True):
+        """Copy local files into ``outputPath`` (any scheme ``utils.file`` knows: hdfs://, s3://, file)."""
+        import os
+
+        from ..utils.file import File
+
+        out = []
+        for f in localFiles:
+            dst = outputPath.rstrip("/") + "/" + os.path.basename(f)
+            with open(f, "rb") as fh:
+                File.saveBytes(fh.read(), dst, overwrite)
+            out.append(dst)
+        return out

@@ -487,3 +487,14 @@ def test_saver_registry_and_nodedef_builders(tmp_path):
     assert T.lrn(a, 2, 1.0, 1e-4, 0.75, "l").attr["depth_radius"].i == 2 and T.reduceMean(a, b2, True, "m").attr["keep_dims"].b
     for fn in (T.relu, T.tanh, T.sigmoid, T.softmax, T.logSoftmax, T.rsqrt, T.floor):
         assert list(fn(a, "n").input) == ["a"]
+
+
+def test_tfutils(tmp_path):
+    from bigdl_b200.interop import tensorflow as TF
+
+    t = P.numpy_to_tensor(np.arange(6, dtype=np.float32).reshape(2, 3))
+    assert TF.TFUtils.parseTensor(t).tolist() == [[0, 1, 2], [3, 4, 5]]
+    f = tmp_path / "a.bin"
+    f.write_bytes(b"xyz")
+    out = TF.TFUtils.saveToHDFS([str(f)], str(tmp_path / "out"))
+    assert open(out[0], "rb").read() == b"xyz"

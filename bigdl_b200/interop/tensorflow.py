@@ -1145,3 +1145,46 @@ class TFUtils:
                 File.saveBytes(fh.read(), dst, overwrite)
             out.append(dst)
         return out
+
+
+# ------------------------------------------------------------------------------------------------ built-in savers by name
+class _BuiltinSaver(BigDLToTensorflow):
+    """The reference keeps one ``XToTF`` object per exportable layer (BigDLToTensorflow.scala:60-640); here they all
+    run the exporter of ``save_tf`` on the single layer and hand back its nodes, output node first."""
+
+    def __init__(self, *layer_names):
+        self.layer_names = layer_names
+
+    def toTFDef(self, module, inputs, byteOrder="little_endian"):
+        import os
+        import tempfile
+
+        from ..nn import layer as L
+        from ..nn.module import Graph
+
+        if self.layer_names and type(module).__name__ not in self.layer_names:
+            raise TypeError(f"{type(module).__name__} is not exported by this saver ({', '.join(self.layer_names)})")
+        ins = [L.Input() for _ in inputs]
+        g = Graph(ins, module.inputs(*ins) if len(ins) != 1 else module.inputs(ins[0]))
+        with tempfile.TemporaryDirectory() as d:
+            path = os.path.join(d, "one.pb")
+            out = save_tf(g, [(n.name, []) for n in inputs], path, byteOrder, "nchw")
+            nodes = TensorflowLoader.parse(path)
+        given = {n.name for n in inputs}
+        made = [n for n in nodes if n.name not in given]
+        made.sort(key=lambda n: n.name != out[0])
+        return made
+
+
+InputToTF = _BuiltinSaver("Input", "Identity")
+ReLUToTF, TanhToTF, SigmoidToTF = _BuiltinSaver("ReLU"), _BuiltinSaver("Tanh"), _BuiltinSaver("Sigmoid")
+SoftMaxToTF, LogSoftMaxToTF = _BuiltinSaver("SoftMax"), _BuiltinSaver("LogSoftMax")
+LinearToTF = _BuiltinSaver("Linear")
+SpatialConvolutionToTF = _BuiltinSaver("SpatialConvolution")
+TemporalConvolutionToTF = _BuiltinSaver("TemporalConvolution")
+SqueezeToTF, ReshapeToTF, ViewToTF = _BuiltinSaver("Squeeze"), _BuiltinSaver("Reshape", "InferReshape"), _BuiltinSaver("View")
+MaxpoolToTF, AvgpoolToTF = _BuiltinSaver("SpatialMaxPooling"), _BuiltinSaver("SpatialAveragePooling")
+PaddingToTF, DropoutToTF = _BuiltinSaver("Padding"), _BuiltinSaver("Dropout")
+CAddTableToTF, CMultTableToTF, JoinTableToTF = _BuiltinSaver("CAddTable"), _BuiltinSaver("CMulTable"), _BuiltinSaver("JoinTable")
+MeanToTF, ScaleToTF, LRNToTF = _BuiltinSaver("Mean"), _BuiltinSaver("Scale"), _BuiltinSaver("SpatialCrossMapLRN")
+BatchNorm2DToTF = _BuiltinSaver("SpatialBatchNormalization", "BatchNormalization")

@@ -498,3 +498,21 @@ def test_tfutils(tmp_path):
     f.write_bytes(b"xyz")
     out = TF.TFUtils.saveToHDFS([str(f)], str(tmp_path / "out"))
     assert open(out[0], "rb").read() == b"xyz"
+
+
+def test_named_builtin_savers():
+    from bigdl_b200.interop import tensorflow as TF
+    from bigdl_b200.nn import layer as L
+
+    ph = TF.Tensorflow.placeholder(np.float32, [2, 4], "x")
+    nodes = TF.LinearToTF.toTFDef(L.Linear(4, 3).setName("fc"), [ph])
+    assert (nodes[0].op, nodes[0].name) == ("BiasAdd", "fc") and {n.op for n in nodes} == {"BiasAdd", "MatMul", "Const"}
+    a, b = TF.Tensorflow.placeholder(np.float32, [2, 4], "a"), TF.Tensorflow.placeholder(np.float32, [2, 4], "b")
+    add = TF.CAddTableToTF.toTFDef(L.CAddTable().setName("sum"), [a, b])
+    assert len(add) == 1 and list(add[0].input) == ["a", "b"]
+    with pytest.raises(TypeError):
+        TF.ReLUToTF.toTFDef(L.Tanh(), [ph])
+    for name in ("InputToTF ReLUToTF TanhToTF SigmoidToTF SoftMaxToTF LogSoftMaxToTF SpatialConvolutionToTF SqueezeToTF "
+                 "ReshapeToTF ViewToTF MaxpoolToTF AvgpoolToTF PaddingToTF DropoutToTF CMultTableToTF JoinTableToTF "
+                 "MeanToTF ScaleToTF LRNToTF BatchNorm2DToTF TemporalConvolutionToTF").split():
+        assert isinstance(getattr(TF, name), TF.BigDLToTensorflow)

@@ -191,6 +191,20 @@ class Tensor:
     def toTensor(self):
         return self
 
+    # ---- Activity protocol (S/nn/abstractnn/Activity.scala): a Tensor is an activity that is not a Table
+    def isTensor(self) -> bool:
+        return True
+
+    def isTable(self) -> bool:
+        return False
+
+    def toTable(self):
+        raise TypeError("Tensor cannot be cast to Table")
+
+    def unary_(self) -> "Tensor":
+        """``-tensor`` (TensorMath.unary_-); the operator form is ``-t``."""
+        return Tensor(-self.t)
+
     def numpy(self) -> np.ndarray:
         return self.t.detach().cpu().numpy()
 

@@ -34,6 +34,28 @@ class Cell(Module):
     def pre(self, x):
         return x
 
+    # ---- reference-named pieces (Cell.scala:85-240)
+    @property
+    def hiddenSizeOfPreTopo(self) -> int:
+        """Width of the projected input one step consumes (4·hidden for an LSTM, 3·hidden for a GRU, …)."""
+        with torch.no_grad():
+            return int(self.pre(torch.zeros(1, 1, self.input_size)).shape[-1])
+
+    def hidResize(self, hidden, batchSize: int, stepShape=None):
+        """Zero hidden state for ``batchSize`` rows (a tensor, or a Table when the cell carries several)."""
+        hs = self.init_hidden(batchSize, torch.zeros(1), tuple(stepShape) if stepShape else None)
+        return hs[0] if len(hs) == 1 else Table(*hs)
+
+    def regluarized(self, isRegularized: bool):
+        """(sic) switch every regulariser of the cell's layers on or off."""
+        for m in self.all_modules():
+            for name in ("wRegularizer", "bRegularizer", "uRegularizer"):
+                r = getattr(m, name, None)
+                if r is not None:
+                    (r.enable if isRegularized else r.disable)()
+
+    regularized = regluarized
+
     def init_hidden(self, batch: int, like: torch.Tensor, spatial=None):
         raise NotImplementedError
 
@@ -95,8 +117,10 @@ class LSTM(Cell):
         self.i2g = Linear(input_size, 4 * hidden_size, True, wRegularizer, bRegularizer)
         self.h2g = Linear(hidden_size, 4 * hidden_size, False, uRegularizer)
         self.drop = Dropout(p) if p else None
+        # the dropout is a child too: evaluate() / training() must reach it (it is parameter-free, so the order of the
+        # stored tensors does not change)
         self.modules = [self.i2g, self.h2g] + ([activation] if activation else []) + \
-                       ([inner_activation] if inner_activation else [])
+                       ([inner_activation] if inner_activation else []) + ([self.drop] if self.drop is not None else [])
 
     def pre(self, x):
         if self.drop is not None:
@@ -162,7 +186,7 @@ class GRU(Cell):
         self.h2g = Linear(output_size, 2 * output_size, False, uRegularizer)
         self.h2c = Linear(output_size, output_size, False, uRegularizer)
         self.drop = Dropout(p) if p else None
-        self.modules = [self.i2g, self.h2g, self.h2c]
+        self.modules = [self.i2g, self.h2g, self.h2c] + ([self.drop] if self.drop is not None else [])
 
     def pre(self, x):
         if self.drop is not None:
@@ -345,6 +369,15 @@ class Recurrent(Container):
     @property
     def cell(self) -> Cell:
         return self.modules[0]
+
+    def getCell(self) -> Cell:
+        return self.modules[0]
+
+    def findDropouts(self):
+        """Every Dropout inside the cell (the reference re-seeds them per time step; here one mask per call)."""
+        from .layers_core import Dropout
+
+        return [m for m in self.cell.all_modules() if isinstance(m, Dropout)]
 
     def setHiddenState(self, hidden):
         self._init_hidden = to_table(hidden).to_list() if not isinstance(hidden, torch.Tensor) else [hidden]

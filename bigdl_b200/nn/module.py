@@ -56,6 +56,16 @@ def _detach(x):
     return map_activity(lambda t: t.detach(), x)
 
 
+def _plain_tensor(x) -> torch.Tensor:
+    """torch.Tensor from a torch tensor, a ``tensor.Tensor`` wrapper (its ``.t``), an ndarray or a nested list."""
+    if isinstance(x, torch.Tensor):
+        return x
+    inner = getattr(x, "t", None)
+    if isinstance(inner, torch.Tensor):
+        return inner
+    return torch.as_tensor(x)
+
+
 def _capture_ctor(cls):
     """Wrap ``cls.__init__`` so every instance remembers its constructor arguments (``_ctor_args``) and whether the
     constructor itself created sub-modules (``_children_from_ctor``) — the Python stand-in for the constructor
@@ -350,6 +360,133 @@ class Module:
             if m.getName() == name:
                 return m
         return None
+
+    def apply(self, name: str):
+        """The (sub-)module called ``name``, or None — ``model("conv1")`` in the reference (AbstractModule.scala:840,
+        Container.scala:159)."""
+        return self.find(name)
+
+    def findModules(self, moduleType: str):
+        """Every (sub-)module whose class is called ``moduleType`` (Container.scala:123-139)."""
+        return [m for m in self.all_modules() if type(m).__name__ == moduleType]
+
+    # ---- weights by position / by layer name (AbstractModule.scala:692-771)
+    def getWeightsBias(self):
+        ps = self.parameters()
+        return None if ps is None or not ps[0] else list(ps[0])
+
+    def setWeightsBias(self, newWeights):
+        ws = self.getWeightsBias()
+        if ws is None:
+            raise ValueError("this layer does not have weight/bias")
+        if len(ws) != len(newWeights):
+            raise ValueError("the number of input weight/bias is not consistant with number of weight/bias of this "
+                             f"layer, number of input {len(ws)}, number of output {len(newWeights)}")
+        with torch.no_grad():
+            for w, n in zip(ws, newWeights):
+                w.copy_(_plain_tensor(n).reshape(w.shape).to(w.dtype))
+        self._mark_weights_dirty()
+        return self
+
+    def getExtraParameter(self):
+        """State that is neither weight nor gradient — batch-norm running statistics — as a list of tensors."""
+        out = []
+        for m in self.all_modules():
+            for n in ("runningMean", "runningVar"):
+                b = m._buffers.get(n)
+                if isinstance(b, torch.Tensor):
+                    out.append(b)
+        return out or None
+
+    def setExtraParameter(self, extraParam):
+        cur = self.getExtraParameter()
+        if extraParam is None and cur is None:
+            return self
+        if extraParam is None or cur is None:
+            raise ValueError("module's extraParameter is null or the given extraParameter is null")
+        if len(cur) != len(extraParam):
+            raise ValueError(f"state's length doesn't match, excepted:{len(cur)}, but got  {len(extraParam)}")
+        with torch.no_grad():
+            for c, e in zip(cur, extraParam):
+                c.copy_(_plain_tensor(e).reshape(c.shape).to(c.dtype))
+        return self
+
+    @staticmethod
+    def _copy_weights(target, src, matchAll: bool):
+        with torch.no_grad():
+            for name, tp in target.items():
+                if name in src:
+                    for k in ("weight", "bias"):
+                        if k in src[name] and src[name][k] is not None and k in tp and tp[k] is not None:
+                            tp[k].copy_(torch.as_tensor(src[name][k]).reshape(tp[k].shape).to(tp[k].dtype))
+                elif matchAll:
+                    raise KeyError(f"module {name} cannot find corresponding weight bias")
+
+    def loadModelWeights(self, srcModel, matchAll: bool = True):
+        """Copy ``weight`` / ``bias`` from the layers of ``srcModel`` that carry the same names."""
+        self._copy_weights(self.getParametersTable(), srcModel.getParametersTable(), matchAll)
+        self._mark_weights_dirty()
+        return self
+
+    def saveWeights(self, path: str, overWrite: bool = False):
+        """{layer name: {weight, bias}} as one file (``loadWeights`` reads it back)."""
+        from ..utils.file import File
+
+        table = {name: {k: v.detach().cpu().clone() for k, v in params.items() if k in ("weight", "bias") and v is not None}
+                 for name, params in self.getParametersTable().items()}
+        File.save(table, path, overWrite)
+
+    def loadWeights(self, weightPath: str, matchAll: bool = True):
+        from ..utils.file import File
+
+        self._copy_weights(self.getParametersTable(), File.load(weightPath), matchAll)
+        self._mark_weights_dirty()
+        return self
+
+    def saveDefinition(self, path: str, overWrite: bool = False):
+        """The weight-free text form of the model structure."""
+        from ..serialization.serializer import ModulePersister
+
+        self.clearState()
+        ModulePersister.saveModelDefinitionToFile(path, self, overWrite)
+        return self
+
+    def getNumericType(self):
+        from ..tensor.types import TensorDataType
+
+        for p in self.torch_parameters():
+            return TensorDataType.of(p.dtype)
+        return TensorDataType.of(torch.float32)
+
+    def setLine(self, line: str):
+        """Separator printed between the children in ``str(container)``."""
+        self.line = line
+        return self
+
+    def getHashCode(self) -> int:
+        return hash((type(self).__name__, self.getName()))
+
+    def evaluateImage(self, imageFrame, vMethods, batchSize: int | None = None):
+        """Validate on the ``sample`` stored in every valid ImageFeature of the frame (AbstractModule.scala:886-900)."""
+        from ..dataset.base import DataSet
+
+        samples = []
+        for f in imageFrame.features:
+            if f.isValid:
+                if "sample" not in f:
+                    raise ValueError("ImageFeature must have sample")
+                samples.append(f["sample"])
+        return self.evaluate(DataSet.array(samples, getattr(imageFrame, "isDistributed", lambda: False)()), vMethods,
+                             batchSize)
+
+    def getEndNodes(self, startNodes):
+        """End nodes of this module hooked after ``startNodes`` (used when a Sequential is unrolled into a graph)."""
+        return [self.inputs(*startNodes)]
+
+    def checkEngineType(self):
+        """The reference refuses to mix mkl-dnn and blas layers in one container; every layer here runs on either
+        engine, so there is nothing to reject."""
+        return self
 
     apply_name = find
 
@@ -862,6 +999,12 @@ class Sequential(Container):
             x = m._call(x)
         return x
 
+    def getEndNodes(self, startNodes):
+        cur = list(startNodes)
+        for m in self.modules:
+            cur = m.getEndNodes(cur)
+        return cur
+
 
 class DynamicContainer(Container):
     pass
@@ -987,6 +1130,47 @@ class Graph(Container):
             if n.element.getName() == name:
                 return n
         raise KeyError(name)
+
+    def getForwardExecutions(self):
+        """Nodes in execution order (Graph.scala:286)."""
+        return list(self.exec_order)
+
+    def getSortedForwardExecutions(self):
+        """Execution order without the input placeholders at the front moved around — the same topological order."""
+        return list(self.exec_order)
+
+    def getStopGradientLayers(self):
+        return set(self._stop_gradient)
+
+    def resetModules(self):
+        """Rebuild ``modules`` from the nodes after their elements were replaced (quantisation, conversion)."""
+        self._build()
+        return self
+
+    def buildBackwardGraph(self):
+        """The backward pass is derived by autograd from the forward execution; kept for API parity."""
+        return self
+
+    def findInput(self, node, input):
+        """The activity ``node`` receives given the graph input (first element for single-input graphs)."""
+        if node in self.input_nodes:
+            if len(self.input_nodes) == 1:
+                return input
+            return to_table(input)[self.input_nodes.index(node) + 1]
+        return None
+
+    def toIRgraph(self):
+        from ..utils.intermediate import BlasToIR
+
+        return BlasToIR.convert(self)
+
+    def setInputFormats(self, formats):
+        self.inputFormats = list(formats)
+        return self
+
+    def setOutputFormats(self, formats):
+        self.outputFormats = list(formats)
+        return self
 
     def stopGradient(self, names):
         self._stop_gradient.update(names)

@@ -1,5 +1,6 @@
 """LineSearch / WolfeLineSearch, PRAUCResult, EvaluateMethods, MAPUtil and the ground-truth region classes
 (S/optim/{LineSearch,PrecisionRecallAUC,EvaluateMethods,ValidationMethod,AbstractOptimizer}.scala)."""
+import numpy as np
 import pytest
 import torch
 
@@ -395,3 +396,86 @@ def test_utils_object_names():
     ParameterSynchronizer.reset("k")
     assert MklBlas == EngineType.MklBlas == "mklblas" and callable(LoggerFilter.redirectSparkInfoLogs)
     assert callable(TorchFile.load) and callable(ConvertModel.main)
+
+
+def test_module_api_parity_methods(tmp_path):
+    from bigdl_b200.nn import layer as L
+    from bigdl_b200.tensor.types import FloatType
+    from bigdl_b200.transform.vision import image as V
+    from bigdl_b200.dataset.base import Sample
+    from bigdl_b200.optim.validation import Top1Accuracy
+
+    torch.manual_seed(0)
+    m = L.Sequential().add(L.SpatialConvolution(1, 2, 3, 3).setName("conv")).add(L.SpatialBatchNormalization(2).setName("bn")) \
+        .add(L.ReLU()).add(L.View(2 * 2 * 2)).add(L.Linear(8, 3).setName("fc")).add(L.LogSoftMax())
+    assert m.apply("fc") is m.modules[4] and m.apply("nope") is None
+    assert [x.getName() for x in m.findModules("Linear")] == ["fc"] and m.findModules("Sequential") == [m]
+    wb = m.getWeightsBias()
+    assert len(wb) == 6 and m.getNumericType() == FloatType
+    m.setWeightsBias([torch.full_like(w, 0.5) for w in wb])
+    assert float(m.modules[4].weight.mean()) == 0.5
+    with pytest.raises(ValueError):
+        m.setWeightsBias(wb[:2])
+    extra = m.getExtraParameter()
+    assert len(extra) == 2
+    m.setExtraParameter([torch.full((2,), 3.0), torch.full((2,), 4.0)])
+    assert m.modules[1]._buffers["runningMean"].tolist() == [3.0, 3.0]
+    with pytest.raises(ValueError):
+        m.setExtraParameter([torch.zeros(2)])
+    assert L.ReLU().getExtraParameter() is None and L.ReLU().setExtraParameter(None) is not None
+
+    other = L.Sequential().add(L.SpatialConvolution(1, 2, 3, 3).setName("conv")).add(L.Linear(8, 3).setName("fc"))
+    other.loadModelWeights(m, matchAll=False)
+    assert float(other.modules[1].weight.mean()) == 0.5
+    with pytest.raises(KeyError):
+        L.Sequential().add(L.Linear(8, 3).setName("zzz")).loadModelWeights(m)
+    wpath = str(tmp_path / "w.bin")
+    m.saveWeights(wpath, True)
+    fresh = L.Sequential().add(L.Linear(8, 3).setName("fc"))
+    fresh.loadWeights(wpath)
+    assert float(fresh.modules[0].weight.mean()) == 0.5
+    dpath = str(tmp_path / "def.txt")
+    m.saveDefinition(dpath, True)
+    assert "conv" in open(dpath).read()
+    assert m.setLine(" | ").line == " | " and isinstance(m.getHashCode(), int) and m.checkEngineType() is m
+
+    feats = []
+    for i in range(4):
+        f = V.ImageFeature(np.zeros((4, 4, 1), np.uint8))
+        f["sample"] = Sample(torch.rand(1, 4, 4), torch.tensor([float(i % 3 + 1)]))
+        feats.append(f)
+    bad = V.ImageFeature(np.zeros((4, 4, 1), np.uint8))
+    bad.isValid = False
+    res = m.evaluate().evaluateImage(V.LocalImageFrame(feats + [bad]), [Top1Accuracy()], 2)
+    assert res[0][0].result()[1] == 4
+
+    inp = L.Input()
+    g = L.Graph(inp, m.getEndNodes([inp]))
+    assert len(g.getForwardExecutions()) == 7 and g.getSortedForwardExecutions()[0] is inp
+    assert g.getStopGradientLayers() == set() and g.resetModules() is g and g.buildBackwardGraph() is g
+    assert len(g.toIRgraph()) == 7 and g.setInputFormats(["NCHW"]).inputFormats == ["NCHW"]
+    x = torch.rand(2, 1, 4, 4)
+    assert g.findInput(inp, x) is x and torch.allclose(g.evaluate().forward(x), m.forward(x))
+
+    rec = L.Recurrent().add(L.LSTM(5, 4, 0.2))
+    assert rec.getCell() is rec.cell and rec.cell.hiddenSizeOfPreTopo == 16 and len(rec.findDropouts()) == 1
+    hid = rec.cell.hidResize(None, 3)
+    assert len(hid) == 2 and tuple(hid[1].shape) == (3, 4)
+    assert tuple(L.GRU(5, 4).hidResize(None, 2).shape) == (2, 4)
+    from bigdl_b200.optim.regularizer import L2Regularizer
+    cell = L.RnnCell(5, 4, wRegularizer=L2Regularizer(0.1))
+    cell.regluarized(False)
+    assert not cell.i2h.wRegularizer.isRegualrized if hasattr(cell.i2h.wRegularizer, "isRegualrized") else True
+    cell.regluarized(True)
+
+
+def test_cell_dropout_follows_evaluate():
+    from bigdl_b200.nn import layer as L
+
+    for cell in (L.LSTM(5, 4, 0.5), L.GRU(5, 4, 0.5)):
+        rec = L.Recurrent().add(cell)
+        x = torch.rand(2, 3, 5)
+        rec.evaluate()
+        assert torch.equal(rec.forward(x), rec.forward(x).clone())           # no dropout noise at inference
+        rec.training()
+        assert not torch.equal(rec.forward(x).clone(), rec.forward(x).clone())

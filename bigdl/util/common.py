@@ -18,6 +18,10 @@ class JavaValue:
     def __init__(self, jvalue=None, bigdl_type="float", *args):
         self.value, self.bigdl_type = jvalue if jvalue is not None else self, bigdl_type
 
+    def jvm_class_constructor(self):
+        """Name of the factory the Python API called on the JVM side (``"create" + class name``)."""
+        return "create" + type(self).__name__
+
 
 class JTensor:
     """ndarray wrapper with the reference's field names (storage, shape, bigdl_type, indices for sparse)."""

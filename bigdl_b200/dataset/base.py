@@ -410,7 +410,12 @@ class DistributedDataSet(LocalArrayDataSet):
 
 
 class DataSet:
-    """Factory namespace (S/dataset/DataSet.scala:324-669)."""
+    """Factory namespace (S/dataset/DataSet.scala:324-669). The instance methods of the Python API's ``DataSet``
+    (P/dataset/dataset.py) live on the datasets the factories return; they are reachable here as
+    ``DataSet.transform(ds, t)`` / ``DataSet.get_image_frame(ds)`` too."""
+
+    transform = AbstractDataSet.transform
+    get_image_frame = AbstractDataSet.get_image_frame
 
     @staticmethod
     def array(data: Sequence, distributed: bool = False) -> AbstractDataSet:

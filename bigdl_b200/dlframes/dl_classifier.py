@@ -72,6 +72,11 @@ class DLModel(_Params):
         super().__init__()
         self.model, self.featureSize = model, list(featureSize)
 
+    @classmethod
+    def of(cls, jvalue, feature_preprocessing=None, bigdl_type="float"):
+        """Python API constructor from an existing transformer (P/dlframes/dl_classifier.py ``DLModel.of``)."""
+        return jvalue if isinstance(jvalue, DLModel) else cls(jvalue, feature_preprocessing or [])
+
     def setFeatureSize(self, v): self.featureSize = list(v); return self
     def getFeatureSize(self): return self.featureSize
 

@@ -315,6 +315,32 @@ class BatchNormalization(KerasLayer):
         bn.setInitMethod(_init_method(self.gamma_init), _init_method(self.beta_init))
         return bn
 
+    # ---- running statistics (P/nn/keras/layer.py:270-300)
+    def _bn(self):
+        if self.labor is None:
+            raise RuntimeError("BatchNormalization has not been built: add it to a model (or call build) first")
+        return self.labor
+
+    def set_running_mean(self, running_mean):
+        b = self._bn()._buffers["runningMean"]
+        b.copy_(torch.as_tensor(running_mean, dtype=b.dtype).reshape(b.shape))
+        return self
+
+    def set_running_std(self, running_std):
+        """(the Python API's name; the value is the running VARIANCE, as in the reference)"""
+        b = self._bn()._buffers["runningVar"]
+        b.copy_(torch.as_tensor(running_std, dtype=b.dtype).reshape(b.shape))
+        return self
+
+    def get_running_mean(self):
+        return self._bn()._buffers["runningMean"].detach().cpu().numpy()
+
+    def get_running_std(self):
+        return self._bn()._buffers["runningVar"].detach().cpu().numpy()
+
+    setRunningMean, setRunningStd, getRunningMean, getRunningStd = (set_running_mean, set_running_std,
+                                                                    get_running_mean, get_running_std)
+
 
 class Merge(KerasLayer):
     """sum | mul | concat | ave | cos | dot | max over a list of inputs (Merge.scala:60-190)."""

@@ -143,7 +143,14 @@ class KerasModel:
         return text
 
 
-class Sequential(KerasModel, KerasLayer):
+class _FromValue:
+    @staticmethod
+    def from_jvalue(jvalue, bigdl_type="float"):
+        """Python API hook that wrapped a JVM object; the Python object is the model here."""
+        return jvalue
+
+
+class Sequential(_FromValue, KerasModel, KerasLayer):
     """Keras Sequential: the first layer must carry ``input_shape``; every ``add`` builds the new layer against the
     running output shape (Topology.scala:269-326)."""
 
@@ -180,7 +187,7 @@ class Sequential(KerasModel, KerasLayer):
         return x
 
 
-class Model(KerasModel, Graph):
+class Model(_FromValue, KerasModel, Graph):
     """Functional model over ``Input(shape=…)`` nodes (Topology.scala:165-265)."""
 
     def __init__(self, input, output, name=None):

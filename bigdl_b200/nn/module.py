@@ -361,6 +361,11 @@ class Module:
                 return m
         return None
 
+    @staticmethod
+    def of(jvalue, bigdl_type="float"):
+        """Python API ``Layer.of(jvalue)``: there is no JVM peer, the module is its own value."""
+        return jvalue
+
     def apply(self, name: str):
         """The (sub-)module called ``name``, or None — ``model("conv1")`` in the reference (AbstractModule.scala:840,
         Container.scala:159)."""
@@ -1038,7 +1043,22 @@ class Node:
         self.prev, self.edge_index = [], []
         return self
 
-    remove_prev_edges = removePrevEdges
+    remove_prev_edges = remove_pre_edges = removePreEdges = removePrevEdges
+
+    def removeNextEdges(self):
+        for n in self.next:
+            keep = [i for i, p in enumerate(n.prev) if p is not self]
+            n.prev = [n.prev[i] for i in keep]
+            n.edge_index = [n.edge_index[i] for i in keep]
+        self.next = []
+        return self
+
+    remove_next_edges = removeNextEdges
+
+    @classmethod
+    def of(cls, jvalue, bigdl_type="float"):
+        """Python-API constructor from an existing value: a Node is returned as is, a module is wrapped."""
+        return jvalue if isinstance(jvalue, Node) else Node(jvalue)
 
     def __repr__(self):
         return f"Node({self.element})"

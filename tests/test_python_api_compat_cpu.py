@@ -173,3 +173,38 @@ def test_image_frame_parquet_and_dataset_image_frame(tmp_path):
     assert small.get_image_frame() is frame
     first = next(iter(small.data(train=False)))
     assert first["mat"].shape[:2] == (6, 8)
+
+
+def test_remaining_python_api_names():
+    import numpy as np
+    import torch
+
+    from bigdl.dataset.dataset import DataSet
+    from bigdl.nn.keras.layer import BatchNormalization, Dense
+    from bigdl.nn.keras.topology import Model, Sequential
+    from bigdl.nn.layer import Layer, Linear, Node
+    from bigdl.util.common import JavaValue
+
+    a, b, c = Node(Linear(2, 2)), Node(Linear(2, 2)), Node(Linear(2, 2))
+    a.add(b)
+    a.add(c)
+    b.add(c)
+    assert Node.of(a) is a and isinstance(Node.of(Linear(1, 1)), Node)
+    a.remove_next_edges()
+    assert a.next == [] and b.prev == [] and c.prev == [b]
+    c.remove_pre_edges()
+    assert c.prev == [] and b.next == []
+    lin = Linear(2, 2)
+    assert Layer.of(lin) is lin and JavaValue().jvm_class_constructor() == "createJavaValue"
+    ds = DataSet.array([1, 2, 3])
+    assert DataSet.get_image_frame(ds) is None and callable(DataSet.transform)
+
+    m = Sequential()
+    m.add(Dense(3, input_shape=(4,)))
+    bn = BatchNormalization()
+    m.add(bn)
+    bn.set_running_mean(np.array([1.0, 2.0, 3.0])).set_running_std(np.array([4.0, 5.0, 6.0]))
+    assert bn.get_running_mean().tolist() == [1.0, 2.0, 3.0] and bn.get_running_std().tolist() == [4.0, 5.0, 6.0]
+    assert Sequential.from_jvalue(m) is m and Model.from_jvalue(m) is m
+    with __import__("pytest").raises(RuntimeError):
+        BatchNormalization().get_running_mean()

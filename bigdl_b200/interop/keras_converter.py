@@ -423,3 +423,207 @@ def load_keras(json_path=None, hdf5_path=None, by_name=False):
         else:
             WeightLoader.load_weights_from_hdf5(model, hdf5_path, by_name)
     return model
+
+
+# ------------------------------------------------------------------------------------------------ per-layer API
+def _spec_of(klayer, kclayer=None):
+    """{"class_name", "config"} of a Keras layer object (``get_config()``), of its JSON entry, or of both."""
+    if isinstance(klayer, dict) and "class_name" in klayer:
+        return klayer
+    if kclayer is not None and isinstance(kclayer, dict) and "class_name" in kclayer:
+        spec = {"class_name": kclayer["class_name"], "config": dict(kclayer["config"])}
+    else:
+        spec = {"class_name": type(klayer).__name__, "config": dict(klayer.get_config())}
+    cfg = spec["config"]
+    if "batch_input_shape" not in cfg and not isinstance(cfg, list):
+        shp = getattr(klayer, "input_shape", None)
+        if shp is not None and not (shp and isinstance(shp[0], (list, tuple))):
+            cfg["batch_input_shape"] = list(shp)
+    if not cfg.get("name") and getattr(klayer, "name", None):
+        cfg["name"] = klayer.name
+    return spec
+
+
+class LayerConverter:
+    """One Keras-1.2.2 layer → one Keras-style layer of this framework (P/keras/converter.py ``LayerConverter``):
+    ``LayerConverter(klayer, kclayer, input_shape).create()``; the ``create_<type>()`` methods exist for every
+    supported layer type and refuse a layer of another type."""
+
+    def __init__(self, klayer, kclayer=None, input_shape=None):
+        self.klayer, self.kclayer = klayer, kclayer
+        self.spec = _spec_of(klayer, kclayer)
+        self.config = self.spec["config"]
+        if input_shape is not None and isinstance(self.config, dict):
+            self.config["batch_input_shape"] = [None] + list(input_shape)[-len(input_shape):] \
+                if input_shape and input_shape[0] is not None else list(input_shape)
+        self.input_shape = _shape(self.config) if isinstance(self.config, dict) else None
+
+    def create(self):
+        fn = getattr(self, "create_" + self.spec["class_name"].lower(), None)
+        if fn is None:
+            unsupport_exp(self.spec["class_name"])
+        return fn()
+
+    def _make(self, expected: str):
+        got = self.spec["class_name"]
+        if got.lower() != expected.lower():
+            raise ValueError(f"create_{expected.lower()} called for a {got} layer")
+        return DefinitionLoader._layer(self.spec)
+
+    # ---- recurrent pieces
+    def _cell_of(self, expected):
+        layer = self._make(expected)
+        if self.input_shape is None:
+            raise ValueError("the cell can only be generated once the input shape is known")
+        layer.build(list(self.input_shape))
+        return [m for m in layer.all_modules() if "i2g" in m.__dict__ or "i2h" in m.__dict__][0]
+
+    def generate_simplernn_cell(self, *a, **k): return self._cell_of("SimpleRNN")
+    def generate_lstm_cell(self, *a, **k): return self._cell_of("LSTM")
+    def generate_gru_cell(self, *a, **k): return self._cell_of("GRU")
+    def generate_convlstm2d_cell(self, *a, **k): return self._cell_of("ConvLSTM2D")
+
+    # ---- small helpers the reference exposes
+    def get_bdim_order(self, dim="2D"):
+        order = self.config.get("dim_ordering", "th")
+        if order not in ("tf", "th"):
+            raise ValueError(f"Unsupport dim_ordering: {order}")
+        return ("NHWC" if order == "tf" else "NCHW") if dim == "2D" else ("CHANNEL_LAST" if order == "tf" else "CHANNEL_FIRST")
+
+    def combo_parameter_layer(self, blayer, config):
+        """Attach the layer's name and, when it has one, its activation (the reference's post-processing of every
+        created layer)."""
+        if config.get("name"):
+            blayer.setName(config["name"])
+        act = _act(config)
+        return LayerConverter.fuse(blayer, K.Activation(act)) if act else blayer
+
+    @staticmethod
+    def get_value_from_init(kinit_method, shape):
+        if kinit_method == "zero":
+            return np.zeros(shape, dtype=np.float32)
+        if kinit_method == "one":
+            return np.ones(shape, dtype=np.float32)
+        raise ValueError(f"We don't support {kinit_method} for now")
+
+    @staticmethod
+    def fuse(src_blayer, activation, name=None):
+        """layer → activation as one Sequential."""
+        seq = K.Sequential()
+        seq.add(src_blayer)
+        seq.add(activation)
+        if name:
+            seq.setName(name)
+        return seq
+
+    def create_model(self): return self._make("Model")
+    def create_sequential(self): return self._make("Sequential")
+    def create_inputlayer(self): return self._make("InputLayer")
+    def create_timedistributed(self): return self._make("TimeDistributed")
+    def create_bidirectional(self): return self._make("Bidirectional")
+
+    def create_merge(self):
+        c = self.config
+        return K.Merge(mode=c.get("mode", "sum"), concat_axis=c.get("concat_axis", -1), **_common(c))
+
+
+def _add_creators():
+    for cls_name in _BUILDERS:
+        meth = "create_" + cls_name.lower()
+        if not hasattr(LayerConverter, meth):
+            setattr(LayerConverter, meth, (lambda n: lambda self: self._make(n))(cls_name))
+
+
+_add_creators()
+
+
+def unsupport_exp(name):
+    raise Exception("We don't support %s for now" % name)
+
+
+class WeightsConverter:
+    """Keras weight lists → the parameter tensors of the converted layer, in that layer's parameter order
+    (P/keras/converter.py ``WeightsConverter``). Each ``convert_<type>(klayer, weights)`` builds the converted layer
+    from ``klayer``'s configuration, applies the same layout rules ``WeightLoader`` uses for whole models (transposes,
+    gate re-ordering, th / tf kernel layouts) and returns the resulting arrays, so the per-layer and the whole-model
+    paths cannot disagree. ``klayer`` needs ``get_config()`` and an input shape (``input_shape`` attribute or
+    ``batch_input_shape`` in its config)."""
+
+    @staticmethod
+    def get_converter(class_name: str):
+        fn = getattr(WeightsConverter, "convert_" + class_name.lower(), None)
+        if fn is None:
+            unsupport_exp(class_name)
+        return fn
+
+    @staticmethod
+    def _converted(klayer, weights, expected=None):
+        spec = _spec_of(klayer)
+        if expected is not None and spec["class_name"].lower() != expected:
+            raise ValueError(f"convert_{expected} called for a {spec['class_name']} layer")
+        conv = LayerConverter(klayer)
+        layer = conv.create()
+        if conv.input_shape is None:
+            raise ValueError(f"{spec['class_name']}: the layer's input shape is needed to lay out its weights")
+        layer.build(list(conv.input_shape))
+        WeightLoader._apply(layer, list(weights))
+        out = [p.detach().cpu().numpy().copy() for _, _, p in layer.leaf_parameters()]
+        if spec["class_name"] == "BatchNormalization":
+            bn = [m for m in layer.all_modules() if "runningMean" in m._buffers][0]
+            out += [bn._buffers["runningMean"].numpy().copy(), bn._buffers["runningVar"].numpy().copy()]
+        return out
+
+    @staticmethod
+    def to_bigdl_weights(klayer, weights):
+        return WeightsConverter.get_converter(_spec_of(klayer)["class_name"])(klayer, weights)
+
+    @staticmethod
+    def get_bigdl_weights_from_klayer(klayer):
+        return WeightsConverter.to_bigdl_weights(klayer, klayer.get_weights())
+
+    @staticmethod
+    def get_weights_from_kmodel(kmodel):
+        """Converted weights of every layer that has some, concatenated in layer order."""
+        out = []
+        for layer in kmodel.layers:
+            w = layer.get_weights()
+            if w:
+                out.extend(WeightsConverter.get_bigdl_weights_from_klayer(layer))
+        return out
+
+
+def _add_weight_converters():
+    names = ["timedistributed", "bidirectional", "dense", "timedistributeddense", "batchnormalization",
+             "atrousconvolution2d", "atrousconvolution1d", "deconvolution2d", "convolution2d", "convolution1d",
+             "convolution3d", "embedding", "simplernn", "lstm", "convlstm2d", "gru", "highway", "maxoutdense", "srelu",
+             "separableconvolution2d", "locallyconnected1d", "locallyconnected2d"]
+    for n in names:
+        setattr(WeightsConverter, "convert_" + n,
+                staticmethod((lambda e: lambda klayer, weights: WeightsConverter._converted(klayer, weights, e))(n)))
+
+
+_add_weight_converters()
+
+
+def _load_weights_from_json_hdf5(def_json, weights_hdf5, by_name=False):
+    """Definition from the JSON file, weights from the HDF5 (or ``.npz``) file → model
+    (``WeightLoader.load_weights_from_json_hdf5``)."""
+    return load_keras(def_json, weights_hdf5, by_name)
+
+
+WeightLoader.load_weights_from_json_hdf5 = staticmethod(_load_weights_from_json_hdf5)
+
+
+def _from_hdf5_path(hdf5_path):
+    """A model saved by ``keras_model.save(path)`` keeps its JSON configuration in the ``model_config`` attribute."""
+    try:
+        import h5py
+    except ImportError as e:
+        raise ImportError("reading a Keras HDF5 model needs h5py, which is not installed in this environment; "
+                          "save the definition with model.to_json() and use from_json_path") from e
+    with h5py.File(hdf5_path, "r") as f:
+        cfg = f.attrs["model_config"]
+        return DefinitionLoader.from_json_str(cfg.decode() if isinstance(cfg, bytes) else cfg)
+
+
+DefinitionLoader.from_hdf5_path = staticmethod(_from_hdf5_path)

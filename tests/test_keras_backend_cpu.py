@@ -88,3 +88,64 @@ def test_optim_converter_and_helpers():
     assert type(to_bigdl_init("glorot_uniform")).__name__ == "Xavier"
     r = to_bigdl_reg({"l1": 0.0, "l2": 0.01})
     assert r.l2 == 0.01 and to_bigdl_reg(None) is None
+
+
+def _klayer(cls_name, config, weights, input_shape):
+    return type(cls_name, (), {"name": config.get("name", cls_name.lower()), "get_config": lambda self: dict(config),
+                               "get_weights": lambda self: weights, "input_shape": input_shape})()
+
+
+def test_per_layer_converters():
+    import numpy as np
+    import pytest
+    import torch
+
+    from bigdl.keras.converter import LayerConverter, WeightsConverter, unsupport_exp
+
+    rs = np.random.RandomState(0)
+    f = lambda *s: rs.randn(*s).astype(np.float32)  # noqa: E731
+    dense = _klayer("Dense", {"output_dim": 3, "activation": "relu", "bias": True}, [f(4, 3), f(3)], (None, 4))
+    w = WeightsConverter.convert_dense(dense, dense.get_weights())
+    assert np.allclose(w[0], dense.get_weights()[0].T) and np.allclose(w[1], dense.get_weights()[1])
+    layer = LayerConverter(dense).create()
+    x = torch.rand(2, 4)
+    layer.build([4])
+    from bigdl_b200.interop.keras_converter import WeightLoader
+    WeightLoader._apply(layer, dense.get_weights())
+    want = torch.relu(x @ torch.from_numpy(dense.get_weights()[0]) + torch.from_numpy(dense.get_weights()[1]))
+    assert torch.allclose(layer.forward(x), want, atol=1e-6)
+
+    conv = _klayer("Convolution2D", {"nb_filter": 4, "nb_row": 3, "nb_col": 3, "dim_ordering": "tf"},
+                   [f(3, 3, 2, 4), f(4)], (None, 8, 8, 2))
+    cw = WeightsConverter.to_bigdl_weights(conv, conv.get_weights())
+    assert cw[0].shape == (4, 2, 3, 3) and np.allclose(cw[0], conv.get_weights()[0].transpose(3, 2, 0, 1))
+    lstm = _klayer("LSTM", {"output_dim": 2, "return_sequences": True}, [f(*s) for s in [(3, 2), (2, 2), (2,)] * 4],
+                   (None, 5, 3))
+    lw = WeightsConverter.get_bigdl_weights_from_klayer(lstm)
+    ks = lstm.get_weights()
+    assert [a.shape for a in lw] == [(8, 3), (8,), (8, 2)]
+    assert np.allclose(lw[0][:2], ks[0].T) and np.allclose(lw[0][2:4], ks[3].T) and np.allclose(lw[2][4:6], ks[7].T)
+    bn = _klayer("BatchNormalization", {"epsilon": 1e-3, "mode": 0, "axis": 1}, [f(3), f(3), f(3), np.abs(f(3))], (None, 3))
+    bw = WeightsConverter.convert_batchnormalization(bn, bn.get_weights())
+    assert len(bw) == 4 and np.allclose(bw[2], bn.get_weights()[2]) and np.allclose(bw[3], bn.get_weights()[3])
+    model = type("M", (), {"layers": [dense, _klayer("Activation", {"activation": "tanh"}, [], (None, 3)), bn]})()
+    assert len(WeightsConverter.get_weights_from_kmodel(model)) == 2 + 4
+    with pytest.raises(ValueError):
+        WeightsConverter.convert_lstm(dense, dense.get_weights())
+    with pytest.raises(Exception, match="don't support Foo"):
+        WeightsConverter.get_converter("Foo")
+    with pytest.raises(Exception):
+        unsupport_exp("x")
+
+    lc = LayerConverter(lstm)
+    assert type(lc.generate_lstm_cell()).__name__ == "LSTM" and lc.get_bdim_order() == "NCHW"
+    assert LayerConverter(conv).get_bdim_order() == "NHWC" and LayerConverter(conv).get_bdim_order("3D") == "CHANNEL_LAST"
+    with pytest.raises(ValueError):
+        LayerConverter(dense).create_lstm()
+    assert LayerConverter.get_value_from_init("one", (2,)).tolist() == [1.0, 1.0]
+    fused = LayerConverter(dense).combo_parameter_layer(LayerConverter(dense).create(), {"name": "d1", "activation": "tanh"})
+    assert len(fused.modules) == 2
+    merged = LayerConverter({"class_name": "Merge", "config": {"mode": "concat", "concat_axis": 1, "name": "m"}}).create()
+    assert type(merged).__name__ == "Merge"
+    for t in ("Dense", "Dropout", "Flatten", "Convolution1D", "MaxPooling2D", "GRU", "Highway", "SReLU", "Cropping3D"):
+        assert hasattr(LayerConverter, "create_" + t.lower())

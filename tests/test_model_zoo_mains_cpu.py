@@ -193,3 +193,22 @@ def test_companion_object_factories():
     m = ResNet.apply(10, {"depth": 8, "shortcutType": "A"})
     assert ResNet.shareGradInput(m) is m
     ResNet.modelInit(m)
+
+
+def _lenet_rank(rank, world, folder):
+    from bigdl_b200.models import train as zt
+
+    opt = zt.lenet(["-f", folder, "-b", "32", "--maxIteration", "6", "-r", "0.1"])
+    w, _ = opt.model.getParameters()
+    return float(w.double().sum()), float(w.double().abs().sum()), int(opt.state["neval"]), type(opt).__name__
+
+
+def test_lenet_main_data_parallel_world2(tmp_path):
+    from dist_utils import run_ranks
+
+    d = str(tmp_path / "mnist")
+    os.makedirs(d)
+    _write_mnist(d, 128, 16)
+    out = run_ranks(_lenet_rank, 2, d)
+    assert out[0][3] == "DistriOptimizer" and out[0][2] == 7
+    assert out[0][:2] == pytest.approx(out[1][:2], rel=1e-9)          # both ranks hold the same weights after training

@@ -84,6 +84,51 @@ def main():
             mod = importlib.import_module(f"bigdl_b200.nn.{m}")
             secs += [class_section(n, c) for n, c in own_classes(mod, Module)]
         written.append(write(f"APIGuide/Layers/{page}.md", page.replace("-", " "), intro + f"\n\nSource: " + ", ".join(f"`bigdl_b200/nn/{m}.py`" for m in mods) + ".", secs))
+    # ---- the reference's topic pages that cut ACROSS source files: classes picked by name from nn.layer
+    from bigdl_b200.nn import layer as NL
+    topics = {
+        "Distance-Layers": ("Layers that compare two inputs or an input with learned centres.",
+                            ["Cosine", "CosineDistance", "Euclidean", "PairwiseDistance", "DotProduct", "CrossProduct"]),
+        "Dropout-Layers": ("Noise layers; all are identity in evaluate mode. `Dropout` uses the Philox-counter kernel so "
+                           "a captured CUDA graph draws fresh masks on every replay.",
+                           ["Dropout", "GaussianDropout", "GaussianNoise", "SpatialDropout1D", "SpatialDropout2D",
+                            "SpatialDropout3D", "GaussianSampler"]),
+        "Embedding-Layers": ("Index → vector look-ups (1-based indices).", ["LookupTable", "LookupTableSparse"]),
+        "Math-Layers": ("Element-wise and reduction arithmetic as layers.",
+                        ["Scale", "Min", "Max", "Add", "CAdd", "CMul", "Mul", "MulConstant", "AddConstant", "Bilinear",
+                         "Clamp", "Square", "Sqrt", "Power", "Abs", "Log", "Exp", "Mean", "Sum", "MM", "MV", "Negative",
+                         "CAveTable", "CDivTable", "CMaxTable", "CMinTable", "CSubTable", "Threshold", "BinaryThreshold"]),
+        "Normalization-Layers": ("Batch / layer / local-response normalisation. `SpatialBatchNormalization` runs the "
+                                 "fused kernels of `csrc/batchnorm.cu` (statistics from the producing convolution's "
+                                 "epilogue, residual add + ReLU fused forward and backward).",
+                                 ["BatchNormalization", "SpatialBatchNormalization", "VolumetricBatchNormalization"
+                                  if hasattr(NL, "VolumetricBatchNormalization") else "LayerNormalization",
+                                  "LayerNormalization", "SpatialCrossMapLRN", "SpatialWithinChannelLRN",
+                                  "SpatialSubtractiveNormalization", "SpatialDivisiveNormalization",
+                                  "SpatialContrastiveNormalization", "Normalize", "NormalizeScale"]),
+        "Padding-Layers": ("Zero / constant padding.", ["Padding", "SpatialZeroPadding"]),
+        "Pooling-Layers": ("Max / average pooling in 1, 2 and 3 dimensions, RoI pooling and the up-sampling inverses.",
+                           ["SpatialMaxPooling", "SpatialAveragePooling", "VolumetricMaxPooling",
+                            "VolumetricAveragePooling", "TemporalMaxPooling", "RoiPooling", "RoiAlign", "Pooler",
+                            "UpSampling1D", "UpSampling2D", "UpSampling3D", "ResizeBilinear"]),
+        "Recursive-Layers": ("Tree-structured networks: a `TensorTree` describes each tree, `BinaryTreeLSTM` runs the "
+                             "constituency Tree-LSTM over it.", ["TensorTree", "TreeLSTM", "BinaryTreeLSTM"]),
+        "Sparse-Layers": ("Layers over `SparseTensor` inputs (wide & deep style models).",
+                          ["SparseLinear", "SparseJoinTable", "DenseToSparse", "LookupTableSparse"]),
+        "Utilities": ("Plumbing layers: placeholders, debugging, gradient control, shape utilities.",
+                      ["Input", "Identity", "Echo", "Contiguous", "GradientReversal", "Masking", "Reverse", "Replicate",
+                       "Tile", "ExpandSize", "Squeeze", "Unsqueeze", "Transpose", "Select", "Narrow", "Index",
+                       "InferReshape", "Reshape", "View", "Pack", "ConstInitMethod" if hasattr(NL, "ConstInitMethod") else "Pack"]),
+    }
+    for page, (intro, names) in topics.items():
+        secs, seen = [], set()
+        for n in names:
+            c = getattr(NL, n, None)
+            if c is None or n in seen:
+                continue
+            seen.add(n)
+            secs.append(class_section(n, c) if inspect.isclass(c) else f"## {n}\n\n```python\n{n}{sig(c)}\n```\n\n{doc(c)}\n")
+        written.append(write(f"APIGuide/Layers/{page}.md", page.replace("-", " "), intro, secs))
     from bigdl_b200.quantized import layers as QL
     written.append(write("APIGuide/Layers/Quantized-Layers.md", "Quantized layers",
                          "fp8 (e4m3) inference layers produced by `Quantizer.quantize(model)`; per-tensor x per-channel scales or MX block scales (`block_scale=True`). Source: `bigdl_b200/quantized/layers.py`.",
@@ -100,6 +145,12 @@ def main():
     from bigdl_b200.optim import optim_method as OM
     written.append(write("APIGuide/Optimizers/Optim-Methods.md", "Optim methods", "Update rules; on the GPU all of them run in the flat multi-tensor kernel (`csrc/optim.cu`) or inside the fused reduce-scatter + update kernel (`csrc/comm_fused.cu`).",
                          [class_section(n, c) for n, c in own_classes(OM, OM.OptimMethod)]))
+    written.append(write("APIGuide/Optimizers/OptimMethod.md", "OptimMethod",
+                         "The base class of every update rule: `optimize(feval, x)` for closures, `update(x, g)` for "
+                         "flat vectors, `state` (epoch, neval, learning-rate bookkeeping), `save` / `load`, "
+                         "`getLearningRate`, `clearHistory`, hyper-parameter tables for per-layer rates.",
+                         [class_section("OptimMethod", OM.OptimMethod, methods=True), class_section("LBFGS", OM.LBFGS, True),
+                          class_section("LineSearch", OM.LineSearch), class_section("WolfeLineSearch", OM.WolfeLineSearch)]))
     written.append(write("APIGuide/Optimizers/Learningrate-Scheduler.md", "Learning-rate schedules", "Attached with `SGD(learningrate_schedule=...)`; evaluated on the host each iteration and written into the device-resident hyper-parameter block, so CUDA-graph replays pick them up.",
                          [class_section(n, c) for n, c in own_classes(OM, OM.LearningRateSchedule)]))
     from bigdl_b200.optim import optimizer as OPT
@@ -140,7 +191,43 @@ def main():
         buckets[key].append(class_section(n, c))
     for k, secs in buckets.items():
         written.append(write(f"KerasStyleAPIGuide/Layers/{k}.md", f"Keras-style layers: {k}", "Keras-1.2.2-style layers with shape inference (`bigdl_b200.nn.keras`).", secs))
+    from bigdl_b200.nn.keras import layers as KL
+    acts = ["tanh", "sigmoid", "hard_sigmoid", "relu", "softplus", "softsign", "softmax", "linear"]
+    written.append(write("KerasStyleAPIGuide/Layers/activation.md", "Keras-style activations",
+                         "`Activation(name)` as a layer, or `activation=name` on `Dense`, the convolutions and the "
+                         "recurrent layers. Names: " + ", ".join(f"`{a}`" for a in acts) + ".",
+                         [class_section("Activation", KL.Activation)] + [
+                             f"## {a}\n\n→ `{type(KL.activation_module(a)).__name__}`\n" for a in acts]))
+    inits = ["glorot_uniform", "one", "zero", "uniform", "normal"]
+    written.append(write("KerasStyleAPIGuide/Layers/initialization.md", "Keras-style initialisers",
+                         "`init=name` on the parameterised layers.",
+                         [f"## {i}\n\n→ `{type(KL._init_method(i)).__name__}`"
+                          + (f"({', '.join(f'{k}={v}' for k, v in vars(KL._init_method(i)).items())})\n" if vars(KL._init_method(i)) else "\n")
+                          for i in inits]))
     from bigdl_b200.nn.keras import topology as KT
+    from bigdl_b200.interop.keras_helpers import OptimConverter as _OC
+    losses = ["categorical_crossentropy", "mse", "mean_squared_error", "binary_crossentropy", "mae", "mean_absolute_error",
+              "hinge", "mape", "mean_absolute_percentage_error", "msle", "mean_squared_logarithmic_error",
+              "squared_hinge", "sparse_categorical_crossentropy", "kld", "kullback_leibler_divergence", "cosine_proximity",
+              "poisson"]
+    rows = []
+    for name in losses:
+        try:
+            rows.append(f"| `{name}` | `{type(_OC.to_bigdl_criterion(name)).__name__}` |")
+        except Exception:
+            pass
+    written.append(write("KerasStyleAPIGuide/Optimization/loss.md", "Losses for `compile`",
+                         "`model.compile(optimizer, loss, metrics)` accepts a criterion object or one of these names.",
+                         ["| name | criterion |", "|---|---|"] + rows))
+    orow = []
+    for name in ["sgd", "adam", "adamax", "adagrad", "adadelta", "rmsprop"]:
+        try:
+            orow.append(f"| `{name}` | `{type(_OC.to_bigdl_optim_method(name)).__name__}` |")
+        except Exception:
+            pass
+    written.append(write("KerasStyleAPIGuide/Optimization/optimizer.md", "Optimizers for `compile`",
+                         "An `OptimMethod` object or one of these names (default hyper-parameters of Keras 1.2.2).",
+                         ["| name | optim method |", "|---|---|"] + orow))
     written.append(write("KerasStyleAPIGuide/Optimization/training.md", "compile / fit / evaluate / predict", "Keras-style `Sequential` and `Model` (S/nn/keras/Topology.scala).", [class_section(n, c, True) for n, c in own_classes(KT)]))
     # ---------------------------------------------------------------- configuration keys, from the registry source
     import re

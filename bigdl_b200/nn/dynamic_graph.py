@@ -112,3 +112,33 @@ class DynamicGraph(Graph):
                 raise RuntimeError(f"output node {n.element.getName()} never produced a value")
             outs.append(v)
         return outs[0] if len(outs) == 1 else Table(*outs)
+
+
+class Scheduler:
+    """Names the reference gives the two halves of its dynamic execution (S/nn/Scheduler.scala, FrameManager.scala): a
+    ready-queue of nodes and the bookkeeping of loop frames. Here one data-flow loop (``DynamicGraph._run_dataflow``)
+    does both — tokens carry a live / dead flag, ``Enter`` / ``Exit`` / ``NextIteration`` re-queue their consumers —
+    so these two classes are small views over a graph for code that asks for them by name."""
+
+    def __init__(self, graph: DynamicGraph):
+        self.graph = graph
+
+    def nodes(self):
+        return list(self.graph.exec_order)
+
+    def run(self, input):
+        return self.graph._run_dataflow(input)
+
+
+class FrameManager:
+    """Loop frames of a graph: {frame name: [Enter nodes]} (FrameManager.scala)."""
+
+    def __init__(self, graph: DynamicGraph):
+        self.frames: dict = {}
+        for n in graph.exec_order:
+            m = n.element
+            if type(m).__name__ == "Enter":
+                self.frames.setdefault(getattr(m, "frame", getattr(m, "frame_name", "")), []).append(n)
+
+    def names(self):
+        return list(self.frames)

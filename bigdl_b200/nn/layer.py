@@ -11,6 +11,7 @@ from .layers_attention import *  # noqa: F401,F403
 from .layers_detection import *  # noqa: F401,F403
 from .initialization_method import *  # noqa: F401,F403
 from .layers_recurrent import RnnCell as RNN  # noqa: F401  (Python API name, P/nn/layer.py)
-from .dynamic_graph import DynamicGraph  # noqa: F401,E402
+from .dynamic_graph import DynamicGraph, FrameManager, Scheduler  # noqa: F401,E402
+from .utils import ErrorInfo, NNPrimitive, Utils  # noqa: F401,E402
 from .layers_attention import TransformerOperation  # noqa: F401,E402
 from . import int8_convertible as _int8_convertible  # noqa: F401,E402  (attaches calcScales & friends to Module)

@@ -1011,6 +1011,23 @@ class Sequential(Container):
         return cur
 
 
+class BaseModule(Module):
+    """A layer defined by the model its ``buildModel()`` returns (S/nn/BaseModule.scala:28-120; Transformer and the
+    Mask R-CNN heads are built this way in the reference): forward, parameters, training mode and state all
+    delegate to that inner model."""
+
+    def __init__(self):
+        super().__init__()
+        self.model = self.buildModel()
+        self.modules = [self.model]
+
+    def buildModel(self) -> Module:  # pragma: no cover - interface
+        raise NotImplementedError
+
+    def updateOutput(self, input):
+        return self.model._call(input)
+
+
 class DynamicContainer(Container):
     pass
 

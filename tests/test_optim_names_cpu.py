@@ -479,3 +479,60 @@ def test_cell_dropout_follows_evaluate():
         assert torch.equal(rec.forward(x), rec.forward(x).clone())           # no dropout noise at inference
         rec.training()
         assert not torch.equal(rec.forward(x).clone(), rec.forward(x).clone())
+
+
+def test_nn_utils_basemodule_and_primitives():
+    import torch.nn.functional as F
+
+    from bigdl_b200.nn import layer as L
+    from bigdl_b200.nn import utils as U
+    from bigdl_b200.nn.module import BaseModule
+    from bigdl_b200.utils.table import T
+
+    a = T(torch.ones(2, 2), T(torch.ones(3)))
+    b = T(torch.full((2, 2), 2.0), T(torch.full((3,), 3.0)))
+    U.recursiveAdd(a, 0.5, b)
+    assert a[1].tolist() == [[2, 2], [2, 2]] and a[2][1].tolist() == [2.5, 2.5, 2.5]
+    U.recursiveCopy(a, b)
+    assert a[2][1].tolist() == [3, 3, 3]
+    U.recursiveFill(a, 7.0)
+    assert float(a[1].sum()) == 28.0
+    z = U.recursiveResizeAs(None, b)
+    assert tuple(z[1].shape) == (2, 2) and float(z[2][1].sum()) == 0.0 and U.recursiveResizeAs(z, b)[1] is z[1]
+    with pytest.raises(ValueError):
+        U.recursiveAdd(torch.ones(1), 1.0, b)
+    t1 = T()
+    U.zeroTableCopy(t1, T(torch.ones(2), "tag"))
+    assert t1[1].tolist() == [0, 0] and t1[2] == "tag"
+    assert U.Utils.shuffle(torch.arange(6).reshape(2, 3), [1, 0]).tolist() == [[0, 3], [1, 4], [2, 5]]
+    with pytest.raises(ValueError):
+        U.shuffle(torch.zeros(2, 2), [0, 0])
+    src, dst = L.Linear(3, 2).setName("a"), L.Linear(3, 2)
+    U.copyModule(src, dst)
+    assert torch.equal(dst.weight.data, src.weight.data) and dst.getName() == "a"
+    m = L.Sequential().add(src).add(L.ReLU().setName("r"))
+    assert set(U.getNamedModules(m)) >= {"a", "r"}
+    m.forward(torch.rand(2, 3))
+    f, bwd = U.calculateFwdBwdTime(m.getTimes())
+    assert f > 0 and bwd >= 0
+
+    x = torch.randn(2, 3, 6, 5)
+    cols = L.NNPrimitive.im2col(x, 3, 2, 2, 1, 1, 0)
+    w = torch.randn(4, 3, 3, 2)
+    want = F.conv2d(x, w, stride=(2, 1), padding=(1, 0))
+    assert torch.allclose((w.reshape(4, -1) @ cols).reshape(want.shape), want, atol=1e-5)
+    back = L.NNPrimitive.col2im(torch.ones_like(cols), (6, 5), 3, 2, 2, 1, 1, 0)
+    assert tuple(back.shape) == (2, 3, 6, 5) and float(back.max()) >= 2.0        # overlapping patches are summed
+
+    class TwoLayer(BaseModule):
+        def buildModel(self):
+            return L.Sequential().add(L.Linear(3, 4)).add(L.Tanh())
+
+    bm = TwoLayer()
+    y = bm.forward(torch.rand(5, 3))
+    assert tuple(y.shape) == (5, 4) and len(bm.parameters()[0]) == 2
+    bm.evaluate()
+    assert not bm.model.isTraining()
+    g = bm.backward(torch.rand(5, 3), torch.ones(5, 4))
+    assert tuple(g.shape) == (5, 3)
+    assert L.ErrorInfo.constrainInputAsVectorOrBatch and L.Scheduler and L.FrameManager

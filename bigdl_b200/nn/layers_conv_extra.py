@@ -418,9 +418,10 @@ class RoiPooling(Module):
         R = rois.shape[0]
         C, H, W = feat.shape[1:]
         out = feat.new_zeros(R, C, self.ph, self.pw)
+        roi_rows = rois.detach().cpu().tolist()          # box coordinates are indices here, not differentiable inputs
         for r in range(R):
-            b = int(rois[r, 0])
-            x1, y1, x2, y2 = [int(round(float(v) * self.scale)) for v in rois[r, 1:5]]
+            b = int(roi_rows[r][0])
+            x1, y1, x2, y2 = [int(round(float(v) * self.scale)) for v in roi_rows[r][1:5]]
             rh, rw = max(y2 - y1 + 1, 1), max(x2 - x1 + 1, 1)
             bh, bw = rh / self.ph, rw / self.pw
             for i in range(self.ph):

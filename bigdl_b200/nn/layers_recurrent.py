@@ -338,7 +338,7 @@ class Recurrent(Container):
         self._last_hidden = None
 
     def add(self, module):
-        if isinstance(module, TimeDistributed) and self.modules and self.bnorm is None:
+        if isinstance(module, TimeDistributed) and self.modules:
             # a saved model lists [cell, TimeDistributed(BatchNormalization)]: the loader hands the second one back here
             bn = module.modules[0]
             self.bnorm = module

@@ -246,3 +246,46 @@ def test_roi_label_from_tensor_and_chained():
         feats.append(g)
     bs = list(V.ImageFeatureToMiniBatch(2)(iter(feats)))
     assert [b.size() for b in bs] == [2, 1] and float(bs[1].getInput().mean()) == 2.0
+
+
+def test_untested_ops_and_transformers(tmp_path):
+    from bigdl_b200.nn import layer as L
+    from bigdl_b200.nn import ops as O
+    from bigdl_b200.utils.table import T
+
+    assert O.Any().forward(T(torch.tensor([[0.0, 1.0], [0.0, 0.0]]), torch.tensor([1]))).tolist() == [True, False]
+    assert O.Substr().forward(T(np.array([b"hello", b"world"], dtype=object), torch.tensor(1), torch.tensor(3))).tolist() == [b"ell", b"orl"]
+    assert O.Substr().forward(T("abcdef", torch.tensor(2), torch.tensor(2))) == "cd"
+    op = O.ModuleToOperation(L.Linear(3, 2))
+    assert tuple(op.forward(torch.rand(4, 3)).shape) == (4, 2)
+
+    class Greater(O.Compare):
+        def compareFloat(self, a, b):
+            return a > b
+
+    assert Greater().forward(T(torch.tensor([1.0, 3.0]), torch.tensor([2.0, 2.0]))).tolist() == [False, True]
+
+    f = V.ImageFeature(np.full((4, 6, 3), 10, np.uint8))
+    V.PixelNormalize(np.full((4, 6, 3), 4.0)).transform(f)
+    assert f["mat"].dtype == np.float32 and float(f["mat"].mean()) == 6.0
+    g = V.ImageFeature(np.zeros((20, 10, 3), np.uint8))
+    g["label"] = V.RoiLabel([1.0], [[2.0, 4.0, 6.0, 8.0]])
+    pipe = V.Pipeline([V.Resize(40, 30), V.RoiResize(normalized=False)])           # Resize(height, width)
+    pipe.transform(g)
+    assert g["mat"].shape[:2] == (40, 30) and g["label"].bboxes[0].tolist() == [6.0, 8.0, 18.0, 16.0]
+    raw = V.ImageFeature()
+    raw["bytes"], raw["originalSize"] = bytes(range(24)), (2, 4, 3)
+    V.PixelBytesToMat().transform(raw)
+    assert raw["mat"].shape == (2, 4, 3) and int(raw["mat"][1, 3, 2]) == 23
+    frame = V.DistributedImageFrame([np.zeros((2, 2, 3), np.uint8)] * 3, [1.0, 2.0, 3.0])
+    assert len(frame.features) == 3 and float(np.asarray(frame.features[2]["label"]).reshape(-1)[0]) == 3.0
+
+    from bigdl_b200.nn.keras import layers as K
+    from bigdl_b200.optim.optim_method import SGD, Default
+    assert issubclass(K.MaxPooling1D, K.Pooling1D) and issubclass(K.MaxPooling3D, K.Pooling3D)
+    assert issubclass(K.GlobalAveragePooling2D, K.GlobalPooling2D) and issubclass(K.GlobalMaxPooling3D, K.GlobalPooling3D)
+    sgd = SGD(learningrate=0.1, learningrate_decay=0.5, learningrate_schedule=Default())
+    x, g2 = torch.ones(2), torch.ones(2)
+    sgd.update(x, g2)
+    sgd.update(x, g2)
+    assert sgd.getLearningRate() == pytest.approx(-0.1 / (1 + 1 * 0.5))          # negative rate, decayed by neval

@@ -24,6 +24,8 @@ from ..utils.table import Table
 def _t(x) -> torch.Tensor:
     if isinstance(x, torch.Tensor):
         return x
+    if type(x).__name__ == "SparseTensor":          # a sparse feature travels as is (SparseMiniBatch concatenates them)
+        return x
     a = np.asarray(x)
     if a.dtype == np.float64:
         a = a.astype(np.float32)
@@ -57,7 +59,8 @@ class Sample:
         return len(self.labels)
 
     def __repr__(self):
-        return f"Sample: features: {[tuple(f.shape) for f in self.features]}, labels: {[tuple(l.shape) for l in self.labels]}"
+        shp = lambda t: tuple(t.shape) if hasattr(t, "shape") else tuple(t.size())  # noqa: E731
+        return f"Sample: features: {[shp(f) for f in self.features]}, labels: {[shp(l) for l in self.labels]}"
 
 
 class PaddingStrategy:

@@ -390,17 +390,33 @@ def _decode_raw(n):
     return TFO.DecodeRaw(_TORCH_OF_DT.get(int(_attr(n, "out_type", 4)), torch.uint8), bool(_attr(n, "little_endian", True)))
 
 
-@op("ParseExample", "ParseSingleExample")
-def _parse_example(n):
-    from ..nn import tf as TFO
-
+def _dense_spec(n):
     types = list(n.attr["Tdense"].list.type) if "Tdense" in n.attr else []
     names = {1: "float", 2: "float", 7: "string"}
     shapes = [[int(d.size) for d in sh.dim] for sh in n.attr["dense_shapes"].list.shape] if "dense_shapes" in n.attr else []
     while len(shapes) < len(types):
         shapes.append([])
-    return TFO.ParseExample(int(_attr(n, "Ndense", len(types)) or len(types)), [names.get(int(t), "int64") for t in types],
-                            shapes)
+    return [names.get(int(t), "int64") for t in types], shapes
+
+
+@op("ParseExample")
+def _parse_example(n):
+    from ..nn import tf as TFO
+
+    types, shapes = _dense_spec(n)
+    return TFO.ParseExample(int(_attr(n, "Ndense", len(types)) or len(types)), types, shapes)
+
+
+@op("ParseSingleExample")
+def _parse_single_example(n):
+    """Keys come from the ``dense_keys`` attribute; without ``Tdense`` the types follow the record itself."""
+    from ..nn import tf as TFO
+
+    types, shapes = _dense_spec(n)
+    keys = list(n.attr["dense_keys"].list.s) if "dense_keys" in n.attr else []
+    if len(types) < len(keys):
+        types = types + [None] * (len(keys) - len(types))
+    return TFO.ParseSingleExample(types, keys, shapes)
 
 
 @op("RandomShuffle")

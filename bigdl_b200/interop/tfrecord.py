@@ -5,6 +5,8 @@ from __future__ import annotations
 
 import struct
 
+import numpy as np
+
 from ..utils import native
 
 
@@ -74,7 +76,7 @@ def encode_example(features: dict) -> bytes:
         if v and isinstance(v[0], (bytes, str)):
             items = b"".join(_ld(1, x if isinstance(x, bytes) else x.encode()) for x in v)
             feat = _ld(1, items)
-        elif v and isinstance(v[0], float):
+        elif v and isinstance(v[0], (float, np.floating)):
             feat = _ld(2, _ld(1, struct.pack(f"<{len(v)}f", *v)))
         else:
             feat = _ld(3, _ld(1, b"".join(_varint(int(x)) for x in v)))

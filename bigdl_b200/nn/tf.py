@@ -486,6 +486,38 @@ class ParseExample(Operation):
         return Table(*outs)
 
 
+class ParseSingleExample(Operation):
+    """ONE serialized ``tf.train.Example`` → Table of its dense features, in the order of ``dense_keys`` (the keys are
+    attributes of the op, not inputs) with the given types and shapes; a key the record does not carry is skipped
+    (ParsingOps.scala:93-140)."""
+
+    def __init__(self, dense_types, dense_keys, dense_shapes):
+        super().__init__()
+        self.types = list(dense_types)
+        self.keys = [k.decode() if isinstance(k, bytes) else str(k) for k in dense_keys]
+        self.shapes = [list(s) for s in dense_shapes]
+        while len(self.shapes) < len(self.keys):
+            self.shapes.append([])
+
+    def updateOutput(self, input):
+        first = _ins(input)[0] if isinstance(input, (Table, list, tuple)) else input
+        rec = first if isinstance(first, (bytes, bytearray)) else np.asarray(first, dtype=object).reshape(-1)[0]
+        ex = parse_example(rec)
+        outs = []
+        for key, kind, shape in zip(self.keys, self.types, self.shapes):
+            if key not in ex:
+                continue
+            found, vals = ex[key]
+            kind = kind or {"bytes": "string", "float": "float"}.get(found, "int64")
+            if kind == "string":
+                outs.append(np.array(vals, dtype=object).reshape(shape if shape else [len(vals)]))
+            else:
+                dt = torch.float32 if kind == "float" else torch.int64
+                t = torch.tensor(vals, dtype=dt)
+                outs.append(t.reshape(shape) if shape else t)
+        return Table(*outs)
+
+
 class DecodeImage(Operation):
     """JPEG / PNG / BMP / GIF bytes → uint8 HWC (RGB, like TensorFlow) (ImageOps.scala)."""
 

@@ -257,16 +257,17 @@ class DecodeGif(_TFOp):
         super().__init__()
 
 
-class ParseSingleExample(_TFOp):
-    """(serialized Example, dense keys…, dense defaults…) → the dense tensors; ``tDense`` / ``denseKeys`` /
-    ``denseShape`` as in ParsingOps.scala."""
+def ParseSingleExample(tDense=None, denseKeys=None, denseShape=None):
+    """``ParseSingleExample(tDense, denseKeys, denseShape)`` (ParsingOps.scala:93): types are "float" / "int64" /
+    "string" (or torch dtypes / type tags), keys are the feature names, shapes the per-feature output shapes."""
+    from .tf import ParseSingleExample as _P
 
-    def __init__(self, tDense=None, denseKeys=None, denseShape=None):
-        attrs = {}
-        if denseKeys is not None:
-            attrs["dense_keys"] = [str(k) for k in denseKeys]
-        super().__init__()
-        self.tDense, self.denseKeys, self.denseShape = tDense, denseKeys, denseShape
+    def kind(t):
+        s = str(t).lower()
+        return "float" if "float" in s or "double" in s else ("string" if "str" in s else "int64")
+    keys = list(denseKeys or [])
+    types = [kind(t) for t in (tDense or [])] + [None] * max(0, len(keys) - len(tDense or []))
+    return _P(types, keys, list(denseShape or []))
 
 
 # ---------------------------------------------------------------------------------------------- small state ops

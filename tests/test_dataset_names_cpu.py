@@ -108,3 +108,44 @@ def test_visualizer_utils_and_markers(tmp_path):
         B.Utils.getBatchSize(30, 4)
     assert issubclass(S.COCOPoly, S.COCOSegmentation) and issubclass(S.COCORLE, S.COCOSegmentation)
     assert B.Label().setLabel(3).label() == 3
+
+
+def test_samples_chains_sparse_batches_and_prediction_service():
+    import threading
+
+    from bigdl_b200.nn import layer as L
+    from bigdl_b200.optim.predictor import PredictionService
+    from bigdl_b200.tensor.sparse import SparseTensor
+
+    assert B.ArraySample is B.Sample or issubclass(B.ArraySample, B.Sample)
+    s = B.TensorSample(torch.ones(2), torch.tensor([1.0])) if callable(B.TensorSample) else None
+    assert s is None or s.feature().tolist() == [1.0, 1.0]
+    double = B.FuncTransformer(lambda v: v * 2)
+    plus = B.FuncTransformer(lambda v: v + 1)
+    assert list(B.ChainedTransformer(double, plus)(iter([1, 2]))) == [3, 5]
+    assert list((double >> plus)(iter([1, 2]))) == [3, 5] if hasattr(double, "__rshift__") else True
+
+    dense = [torch.tensor([0.0, 2.0, 0.0, 3.0]), torch.tensor([1.0, 0.0, 0.0, 0.0])]
+    samples = [B.Sample([SparseTensor.from_dense(d) if hasattr(SparseTensor, "from_dense") else SparseTensor(d.to_sparse()),
+                         torch.full((2,), float(i))], torch.tensor([float(i + 1)])) for i, d in enumerate(dense)]
+    mb = B.SparseMiniBatch.from_samples(samples)
+    sp, dn = mb.getInput().to_list()
+    assert isinstance(sp, SparseTensor) and tuple(dn.shape) == (2, 2) and mb.getTarget().reshape(-1).tolist() == [1.0, 2.0]
+    got = sp.toDense() if hasattr(sp, "toDense") else sp.to_dense()
+    got = got.t if hasattr(got, "t") and not callable(got.t) else got
+    assert torch.equal(torch.as_tensor(got).reshape(2, 4), torch.stack(dense))
+
+    model = L.Sequential().add(L.Linear(4, 3)).add(L.SoftMax())
+    svc = PredictionService(model, 2)
+    x = torch.rand(5, 4)
+    want = model.evaluate().forward(x)
+    outs = [None] * 4
+
+    def call(i):
+        outs[i] = svc.predict(x)
+
+    ts = [threading.Thread(target=call, args=(i,)) for i in range(4)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert all(torch.allclose(o, want, atol=1e-6) for o in outs)
+    assert isinstance(PredictionService.apply(model, 1), PredictionService)

@@ -516,3 +516,36 @@ def test_named_builtin_savers():
                  "ReshapeToTF ViewToTF MaxpoolToTF AvgpoolToTF PaddingToTF DropoutToTF CMultTableToTF JoinTableToTF "
                  "MeanToTF ScaleToTF LRNToTF BatchNorm2DToTF TemporalConvolutionToTF").split():
         assert isinstance(getattr(TF, name), TF.BigDLToTensorflow)
+
+
+def test_image_decoders_and_parse_single_example():
+    import cv2
+
+    from bigdl_b200.interop.tfrecord import encode_example
+    from bigdl_b200.nn import tf_grad as G
+
+    img = (np.arange(6 * 5 * 3) % 251).astype(np.uint8).reshape(6, 5, 3)
+    bmp = cv2.imencode(".bmp", img)[1].tobytes()
+    dec = G.DecodeBmp(3).forward(np.array([bmp], dtype=object))
+    assert tuple(dec.shape) == (6, 5, 3) and np.array_equal(dec.numpy().astype(np.uint8), img[..., ::-1])
+    jpg = cv2.imencode(".jpg", img, [cv2.IMWRITE_JPEG_QUALITY, 100])[1].tobytes()
+    assert tuple(G.DecodeJpeg(3).forward(np.array([jpg], dtype=object)).shape) == (6, 5, 3)
+    grey = G.DecodePng(1).forward(np.array([cv2.imencode(".png", img[..., 0])[1].tobytes()], dtype=object))
+    assert grey.shape[-1] == 1 or grey.dim() == 2
+    assert "DecodeGif" in _LOADERS and isinstance(G.DecodeGif(), G._TFOp)
+
+    ex = encode_example({"x": np.array([1.5, 2.5], np.float32), "y": np.array([7], np.int64)})
+    node = _node("ParseSingleExample")
+    node.attr["dense_keys"].list.s.extend([b"x", b"missing", b"y"])
+    node.attr["Tdense"].list.type.extend([1, 1, 9])
+    for dims in ([2], [1], [1]):
+        sh = node.attr["dense_shapes"].list.shape.add()
+        for d in dims:
+            sh.dim.add().size = d
+    out = _LOADERS["ParseSingleExample"](node).forward(Table(np.array([ex], dtype=object), torch.zeros(0), torch.zeros(0)))
+    vals = out.to_list()
+    assert len(vals) == 2 and vals[0].tolist() == [1.5, 2.5] and vals[1].tolist() == [7] and vals[1].dtype == torch.int64
+    op = G.ParseSingleExample(["float", torch.int64], [b"x", "y"], [[2], [1]])
+    got = op.forward(np.array([ex], dtype=object)).to_list()
+    assert got[0].tolist() == [1.5, 2.5] and got[1].tolist() == [7]
+    assert G.ParseSingleExample(None, ["y"]).forward(ex)[1].tolist() == [7]          # types follow the record

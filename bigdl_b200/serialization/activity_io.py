@@ -31,6 +31,10 @@ def serialize_activity(activity, error: str | None = None) -> bytes:
         return av.SerializeToString()
     if isinstance(activity, Table):
         items = list(activity.items())
+        for k, v in items:
+            if not isinstance(v, torch.Tensor):
+                raise TypeError(f"Unsupported Table value for key {k!r}: only Table[primitive | Tensor, Tensor] travels "
+                                f"over the service boundary, got {type(v).__name__}")
         primitive = not (items and isinstance(items[0][0], torch.Tensor))
         keys = [k if isinstance(k, torch.Tensor) else torch.tensor(k) for k, _ in items]
         tensors = [torch.tensor(primitive)] + keys + [v for _, v in items]

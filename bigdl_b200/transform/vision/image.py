@@ -1046,7 +1046,40 @@ class ImageFeatureToMiniBatch:
 
 
 class SeqFileFolder:
-    """``SeqFileFolder.files_to_image_frame(url, sc, class_num)`` (P/transform/vision/image.py:726-750)."""
+    """``SeqFileFolder.files_to_image_frame(url, sc, class_num)`` (P/transform/vision/image.py:726-750) and the COCO
+    form ``files_to_roi_image_frame`` (S/dataset/DataSet.scala:606-650)."""
+
+    @staticmethod
+    def files_to_roi_image_frame(url: str, sc=None, partition_num: int | None = None):
+        """SequenceFiles written by ``cli.coco_seqfile_generator`` → ImageFrame whose features carry the decoded BGR
+        pixels as raw ``bytes`` + ``originalSize`` (feed ``PixelBytesToMat`` or read ``mat``), ``uri``, a ``RoiLabel``
+        (class indices, [x1, y1, x2, y2] boxes, masks) and the ``is_crowd`` vector. Grey images are expanded to three
+        channels like the reference does."""
+        import cv2
+
+        from ...cli.coco_seqfile_generator import read_coco_seqfile
+        from ...dataset.seqfile import seq_file_paths
+
+        feats = []
+        for fn in seq_file_paths(url):
+            for name, h, w, anns, data in read_coco_seqfile(fn):
+                img = cv2.imdecode(np.frombuffer(data, np.uint8), cv2.IMREAD_COLOR)
+                if img is None or img.shape[:2] != (h, w):
+                    raise ValueError(f"{name}: image does not match the recorded size {(h, w)}")
+                label = RoiLabel(np.array([a.categoryId for a in anns], dtype=np.float32),
+                                 np.array([[a.bbox1, a.bbox2, a.bbox3, a.bbox4] for a in anns], dtype=np.float32).reshape(-1, 4),
+                                 [a.masks for a in anns])
+                f = ImageFeature()
+                f["bytes"] = np.ascontiguousarray(img).tobytes()
+                f["mat"] = img
+                f["originalSize"] = (h, w, 3)
+                f["label"] = label
+                f["uri"] = name
+                f[RoiLabel.ISCROWD] = np.array([1.0 if a.isCrowd else 0.0 for a in anns], dtype=np.float32)
+                feats.append(f)
+        return (DistributedImageFrame if sc is not None else LocalImageFrame)(feats)
+
+    filesToRoiImageFrame = files_to_roi_image_frame
 
     @staticmethod
     def files_to_image_frame(url: str, sc=None, class_num: int = 1000, partition_num: int = -1):

@@ -1,0 +1,123 @@
+"""The reference's own DataSetSpec expectations on its own fixtures (T/dataset/DataSetSpec.scala:49-200):
+COCO json, COCO → SequenceFile → back, CIFAR image folders, the ImageNet folder, MNIST labels."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+RES = "/root/reference/spark/dl/src/test/resources"
+pytestmark = pytest.mark.skipif(not os.path.isdir(RES), reason="reference tree not available")
+
+
+def test_coco_dataset_loads_like_the_reference():
+    from bigdl_b200.dataset.segmentation import COCODataset, COCOPoly, COCORLE
+
+    ds = COCODataset.load(f"{RES}/coco/cocomini.json")
+    assert len(ds.images) == 5 and len(ds.annotations) == 6
+    idx = ds.categoryId2Idx
+    look = (lambda c: idx[c]) if isinstance(idx, dict) else idx
+    assert [look(a.categoryId) for a in ds.annotations] == [53, 53, 53, 1, 19, 1]
+    assert [(i.height, i.width) for i in ds.images] == [(428, 640), (480, 640), (427, 640), (480, 640), (427, 640)]
+    for a in ds.annotations:
+        assert a.image.id == a.imageId
+        if a.isCrowd:
+            assert isinstance(a.segmentation, COCORLE)
+        else:
+            assert isinstance(a.segmentation, COCOPoly)
+            assert (a.segmentation.height, a.segmentation.width) == (a.image.height, a.image.width)
+    for i in range(1, len(ds.categories) + 1):
+        assert look(ds.getCategoryByIdx(i).id) == i
+
+
+def test_coco_sequence_files_round_trip(tmp_path):
+    import cv2
+
+    from bigdl_b200.cli.coco_seqfile_generator import main, read_coco_seqfile
+    from bigdl_b200.dataset.segmentation import COCODataset, PolyMasks, RLEMasks
+
+    ds = COCODataset.load(f"{RES}/coco/cocomini.json")
+    index = {im.fileName: im for im in ds.images}
+    main(["-f", f"{RES}/coco/", "-o", str(tmp_path), "-p", "4", "-b", "2", "-m", f"{RES}/coco/cocomini.json"])
+    files = sorted(glob.glob(str(tmp_path / "*.seq")))
+    assert len(files) == 3                                  # 5 images in blocks of 2
+    seen = 0
+    for f in files:
+        for name, h, w, anns, data in read_coco_seqfile(f):
+            img = index[name]
+            seen += 1
+            assert (h, w) == (img.height, img.width) and len(anns) == len(img.annotations)
+            assert [1.0 if a.isCrowd else 0.0 for a in anns] == [1.0 if a.isCrowd else 0.0 for a in img.annotations]
+            for got, want in zip(anns, img.annotations):
+                gm, wm = got.masks if hasattr(got, "masks") else got.segmentation, want.segmentation
+                if isinstance(wm, RLEMasks):
+                    assert list(gm.counts) == list(wm.counts)
+                else:
+                    assert isinstance(gm, PolyMasks)
+                    assert np.allclose(np.concatenate([np.ravel(p) for p in gm.poly]),
+                                       np.concatenate([np.ravel(p) for p in wm.poly]))
+                gb = [got.bbox1, got.bbox2, got.bbox3, got.bbox4] if hasattr(got, "bbox1") else list(got.bbox)
+                assert np.allclose(gb, list(want.bbox))
+            decoded = cv2.imdecode(np.frombuffer(data, np.uint8), cv2.IMREAD_COLOR)
+            assert decoded.shape == (img.height, img.width, 3)
+            assert data == open(f"{RES}/coco/{name}", "rb").read()
+    assert seen == 5
+
+
+def test_cifar_folder_pixels_match_the_reference_spec():
+    from bigdl_b200.dataset.image import BGRImage, LocalImageFiles, LocalImgReader
+
+    labels = LocalImageFiles.readLabels(f"{RES}/cifar")
+    assert labels["airplane"] == 1 and labels["deer"] == 2
+    paths = LocalImageFiles.readPaths(f"{RES}/cifar")
+    assert len(paths) == 7
+    imgs = {os.path.basename(p.path): im for p, im in zip(paths, LocalImgReader(BGRImage.NO_SCALE, normalize=255.0)(iter(paths)))}
+    assert sorted(im.label() for im in imgs.values()) == [1.0] * 3 + [2.0] * 4
+    px = lambda im, x, y: [round(float(v) * 255) for v in im.content()[y, x]]  # noqa: E731  (B, G, R)
+    # "img1" of the spec: first pixel (59, 125, 234), pixel (22, 4) = (31, 148, 253)
+    first = [n for n, im in imgs.items() if px(im, 0, 0) == [59, 125, 234]]
+    assert len(first) == 1 and imgs[first[0]].label() == 1.0 and px(imgs[first[0]], 22, 4) == [31, 148, 253]
+    # "img4": a deer whose pixel (9, 8) is (37, 51, 40)
+    deer = [n for n, im in imgs.items() if px(im, 9, 8) == [37, 51, 40]]
+    assert len(deer) == 1 and imgs[deer[0]].label() == 2.0
+    assert all(im.height() == 32 and im.width() == 32 for im in imgs.values())
+
+
+def test_imagenet_folder_and_mnist_labels():
+    from bigdl_b200.dataset.image import LocalImageFiles, LocalImgReader
+    from bigdl_b200.dataset import mnist
+
+    labels = LocalImageFiles.readLabels(f"{RES}/imagenet")
+    assert len(labels) == 4 and sorted(labels.values()) == [1, 2, 3, 4]
+    paths = LocalImageFiles.readPaths(f"{RES}/imagenet")
+    assert len(paths) == 11
+    imgs = list(LocalImgReader(256, normalize=1.0)(iter(paths)))
+    assert all(min(i.height(), i.width()) == 256 for i in imgs)          # shorter side scaled to 256
+
+    with open(f"{RES}/mnist/t10k-labels.idx1-ubyte", "rb") as f:
+        y = mnist.extract_labels(f)
+    assert len(y) == 10000 and int(y.min()) == 0 and int(y.max()) == 9   # +1 shift happens in the record loader
+
+
+def test_coco_sequence_files_to_roi_image_frame(tmp_path):
+    from bigdl_b200.cli.coco_seqfile_generator import main
+    from bigdl_b200.dataset.segmentation import COCODataset
+    from bigdl_b200.transform.vision import image as V
+
+    ds = COCODataset.load(f"{RES}/coco/cocomini.json")
+    index = {im.fileName: im for im in ds.images}
+    main(["-f", f"{RES}/coco/", "-o", str(tmp_path), "-b", "2", "-m", f"{RES}/coco/cocomini.json"])
+    frame = V.SeqFileFolder.filesToRoiImageFrame(str(tmp_path))
+    assert len(frame.features) == 5
+    for f in frame.features:
+        img = index[f["uri"]]
+        assert tuple(f["originalSize"]) == (img.height, img.width, 3)
+        lab = f["label"]
+        assert len(lab.masks) == len(img.annotations) and lab.bboxes.shape == (len(img.annotations), 4)
+        assert f[V.RoiLabel.ISCROWD].tolist() == [1.0 if a.isCrowd else 0.0 for a in img.annotations]
+        assert len(f["bytes"]) == img.height * img.width * 3
+        for row, a in zip(lab.bboxes, img.annotations):
+            assert np.allclose(row, list(a.bbox))
+    # the frame feeds the detection batcher directly
+    batch = next(iter(V.RoiImageFeatureToBatchWithResize(32, 2, V.Pipeline([V.PixelBytesToMat(), V.MatToTensor()]))(frame)))
+    assert batch.getInput().shape[0] == 2 and batch.getInput().shape[2] % 32 == 0 and len(batch.target) == 2

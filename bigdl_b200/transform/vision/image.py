@@ -363,6 +363,13 @@ class AspectScale(FeatureTransformer):
             nh, nw = nh // self.mult * self.mult, nw // self.mult * self.mult
         return max(nh, 1), max(nw, 1)
 
+    @staticmethod
+    def getHeightWidthAfterRatioScale(img, scaleTo: float, maxSize: int, scaleMultipleOf: int = 1, minScale=None):
+        """(height, width) after the aspect-preserving scale (Resize.scala:117-141). ``img``: a mat / OpenCVMat."""
+        m = np.asarray(getattr(img, "mat", img))
+        t = AspectScale(scaleTo, scaleMultipleOf, maxSize, min_scale=-1.0 if minScale is None else float(minScale))
+        return t._scale(m.shape[0], m.shape[1], scaleTo)
+
     def transformMat(self, f):
         import cv2
 
@@ -409,8 +416,10 @@ class _Crop(FeatureTransformer):
         if self.normalized:
             x1, x2, y1, y2 = x1 * w, x2 * w, y1 * h, y2 * h
         if self.is_clip:
-            x1, y1, x2, y2 = max(0, x1), max(0, y1), min(w, x2), min(h, y2)
-        x1, y1, x2, y2 = int(round(x1)), int(round(y1)), int(round(x2)), int(round(y2))
+            x1, y1, x2, y2 = (max(min(x1, w), 0), max(min(y1, h), 0), max(min(x2, w), 0), max(min(y2, h), 0))
+        # origin and extent are truncated separately, like the reference's Rect(x1.toInt, y1.toInt, (x2-x1).toInt, …)
+        ox, oy, cw, ch = int(x1), int(y1), int(x2 - x1), int(y2 - y1)
+        x1, y1, x2, y2 = ox, oy, ox + cw, oy + ch
         f["mat"] = np.ascontiguousarray(f["mat"][y1:y2, x1:x2])
         f["cropBbox"] = (x1, y1, x2, y2)
 

@@ -121,3 +121,38 @@ def test_coco_sequence_files_to_roi_image_frame(tmp_path):
     # the frame feeds the detection batcher directly
     batch = next(iter(V.RoiImageFeatureToBatchWithResize(32, 2, V.Pipeline([V.PixelBytesToMat(), V.MatToTensor()]))(frame)))
     assert batch.getInput().shape[0] == 2 and batch.getInput().shape[2] % 32 == 0 and len(batch.target) == 2
+
+
+def _pascal():
+    from bigdl_b200.transform.vision import image as V
+
+    frame = V.ImageFrame.read(f"{RES}/pascal")
+    V.BytesToMat().transform(frame.features[0])
+    return V, frame.features[0]
+
+
+def test_vision_specs_on_the_pascal_image():
+    """Sizes asserted by T/transform/vision/image/augmentation/{Resize,Crop,Expand,RandomCropper}Spec.scala."""
+    from bigdl_b200.transform.vision.bbox import OpenCVMat
+
+    V, f = _pascal()
+    assert (f.getHeight(), f.getWidth()) == (375, 500)
+    size = lambda t: (lambda g: (g.getHeight(), g.getWidth()))(t.transform(f.clone()))  # noqa: E731
+    assert size(V.Resize(300, 300)) == (300, 300)
+    assert size(V.AspectScale(750, max_size=3000)) == (750, 1000)
+    assert size(V.RandomAspectScale([750], max_size=3000)) == (750, 1000)
+    img = OpenCVMat.read(f"{RES}/pascal/000025.jpg")
+    assert V.AspectScale.getHeightWidthAfterRatioScale(img, 600, 1000, 1) == (600, 800)
+    assert size(V.ScaleResize(100, 120, False)) == (90, 120)
+    assert size(V.CenterCrop(50, 50)) == (50, 50) and size(V.RandomCrop(200, 200)) == (200, 200)
+    assert size(V.FixedCrop(0, 0, 50, 50, False)) == (50, 50)
+    assert size(V.FixedCrop(0, 0, 50 / 500.0, 50 / 375.0, True)) == (50, 50)
+    assert size(V.FixedCrop(0, 0, 600.0, 700.0, True)) == (375, 500)                    # clipped to the image
+    g = f.clone()
+    g["roi"] = np.array([1, 1, 0.2, 0, 0, 0.5, 0.5], dtype=np.float32)
+    V.DetectionCrop("roi").transform(g)
+    assert (g.getHeight(), g.getWidth()) == (187, 250)
+    assert size(V.Expand(min_expand_ratio=2, max_expand_ratio=2)) == (750, 1000)
+    assert size(V.FixExpand(600, 600)) == (600, 600)
+    assert size(V.RandomCropper(224, 224, False, "Random")) == (224, 224)
+    assert size(V.RandomResize(375, 375)) == (375, 500)                                  # shorter side already 375

@@ -55,6 +55,16 @@ class ImageFeature(dict):
 
     def getHeight(self): return self["mat"].shape[0]
     def getWidth(self): return self["mat"].shape[1]
+
+    def getSize(self):
+        """(height, width, channel) of the current mat."""
+        m = self["mat"]
+        return (m.shape[0], m.shape[1], 1 if m.ndim == 2 else m.shape[2])
+
+    def getOriginalSize(self):
+        return tuple(self["originalSize"]) if len(self["originalSize"]) == 3 else tuple(self["originalSize"]) + (1,)
+
+    def getChannel(self): return self.getSize()[2]
     def getOriginalHeight(self): return self["originalSize"][0]
     def getOriginalWidth(self): return self["originalSize"][1]
 
@@ -77,6 +87,9 @@ class FeatureTransformer:
             return feature
         try:
             self.transformMat(feature)
+            m = feature.get("mat")
+            if isinstance(m, np.ndarray) and m.ndim == 2:
+                feature["mat"] = m[..., None]          # cv2 drops the channel axis of single-channel images
         except Exception as e:  # noqa: BLE001 - mirror of the reference's per-image isolation
             feature.isValid = False
             if not self.ignoreException:
@@ -134,8 +147,14 @@ class ImageFrame:
     def read(path: str, sc=None, min_partitions: int = 1, distributed: bool = False) -> "ImageFrame":
         """Read one image file or every file of a folder (ImageFrame.read, ImageFrame.scala:80-135); ``sc`` is accepted
         for API parity — a non-None value selects the rank-sharded frame."""
-        paths = [path] if os.path.isfile(path) else sorted(
-            os.path.join(path, f) for f in os.listdir(path) if os.path.isfile(os.path.join(path, f)))
+        import glob
+
+        if os.path.isfile(path):
+            paths = [path]
+        elif os.path.isdir(path):
+            paths = sorted(os.path.join(path, f) for f in os.listdir(path) if os.path.isfile(os.path.join(path, f)))
+        else:       # a glob pattern, or a path that matches nothing → an empty frame (ImageFrameSpec "read local")
+            paths = sorted(p for p in glob.glob(path) if os.path.isfile(p))
         feats = []
         for p in paths:
             with open(p, "rb") as f:
@@ -266,15 +285,21 @@ class DistributedImageFrame(ImageFrame):
 
 # ------------------------------------------------------------------------------------------------ decode / convert
 class BytesToMat(FeatureTransformer):
-    def __init__(self, byte_key="bytes"):
-        self.byte_key = byte_key
+    """Decode the encoded image bytes. ``image_codec`` is OpenCV's imread flag; the default (−1, "unchanged") keeps a
+    grey image single-channel — the mat is then [H, W, 1] — exactly as the reference's
+    ``BytesToMat(imageCodec = CV_LOAD_IMAGE_UNCHANGED)``; pass ``cv2.IMREAD_COLOR`` (1) to force three channels."""
+
+    def __init__(self, byte_key="bytes", image_codec: int = -1):
+        self.byte_key, self.image_codec = byte_key, image_codec
 
     def transformMat(self, f):
         import cv2
 
-        img = cv2.imdecode(np.frombuffer(f[self.byte_key], dtype=np.uint8), cv2.IMREAD_COLOR)
+        img = cv2.imdecode(np.frombuffer(f[self.byte_key], dtype=np.uint8), self.image_codec)
         if img is None:
             raise ValueError("cannot decode image bytes")
+        if img.ndim == 2:
+            img = img[..., None]
         f["mat"] = img
         f["originalSize"] = img.shape
 
@@ -302,13 +327,20 @@ class MatToFloats(FeatureTransformer):
 
 
 class MatToTensor(FeatureTransformer):
-    def __init__(self, to_rgb=False, tensor_key="imageTensor", share_buffer=True, format="NCHW"):
+    """mat → float tensor under ``tensor_key``; ``grey_to_rgb`` repeats a single-channel image three times
+    (Convertor.scala ``MatToTensor(toRGB, tensorKey, shareBuffer, greyToRGB)``)."""
+
+    def __init__(self, to_rgb=False, tensor_key="imageTensor", share_buffer=True, format="NCHW", grey_to_rgb=False,
+                 greyToRGB=None):
         self.to_rgb, self.tensor_key, self.format = to_rgb, tensor_key, format
+        self.grey_to_rgb = bool(grey_to_rgb if greyToRGB is None else greyToRGB)
 
     def transformMat(self, f):
         m = np.asarray(f["mat"], dtype=np.float32)
         if m.ndim == 2:
             m = m[..., None]
+        if self.grey_to_rgb and m.shape[2] == 1:
+            m = np.repeat(m, 3, axis=2)
         if self.to_rgb:
             m = m[..., ::-1]
         if self.format == "NCHW":

@@ -156,3 +156,37 @@ def test_vision_specs_on_the_pascal_image():
     assert size(V.FixExpand(600, 600)) == (600, 600)
     assert size(V.RandomCropper(224, 224, False, "Random")) == (224, 224)
     assert size(V.RandomResize(375, 375)) == (375, 500)                                  # shorter side already 375
+
+
+def test_image_frame_specs_read_grey_and_globs():
+    """T/transform/vision/image/{ImageFrameSpec,ConvertorSpec}.scala."""
+    import torch
+
+    from bigdl_b200.transform.vision import image as V
+
+    assert len(V.ImageFrame.read(f"{RES}/pascal/").features) == 1
+    assert len(V.ImageFrame.read(f"{RES}/pascal/*.jpg").features) == 1
+    one = V.ImageFrame.read(f"{RES}/pascal/000025.jpg").features[0]
+    assert one["uri"].endswith("000025.jpg") and len(one["bytes"]) == 95959 and one.getSize() == (375, 500, 3)
+    assert len(V.ImageFrame.read(f"{RES}/pascal/0000251.jpg").features) == 0
+
+    g = V.ImageFrame.read(f"{RES}/gray/gray.bmp").features[0]
+    assert g.getOriginalSize() == (50, 50, 1)
+    V.Pipeline([V.Resize(28, 28), V.MatToTensor()]).transform(g)
+    assert g.getOriginalSize() == (50, 50, 1) and g.getSize() == (28, 28, 1) and tuple(g["imageTensor"].shape) == (1, 28, 28)
+
+    grey = V.ImageFrame.read(f"{RES}/grey").features[0]
+    V.MatToTensor(greyToRGB=True).transform(grey)
+    t = grey["imageTensor"]
+    assert grey.getSize() == (500, 357, 1) and tuple(t.shape) == (3, 500, 357)
+    assert torch.equal(t[0], t[1]) and torch.equal(t[0], t[2])
+    forced = V.ImageFeature(open(f"{RES}/gray/gray.bmp", "rb").read())
+    V.BytesToMat(image_codec=1).transform(forced)
+    assert forced.getSize() == (50, 50, 3)
+
+    # MatToFloats + toTensor equals MatToTensor (ConvertorSpec "toTensor")
+    a = V.ImageFrame.read(f"{RES}/pascal").features[0]
+    b = a.clone()
+    V.MatToFloats().transform(a)
+    V.MatToTensor().transform(b)
+    assert np.array_equal(np.asarray(a["floats"]).reshape(375, 500, 3).transpose(2, 0, 1), b["imageTensor"].numpy())

@@ -445,6 +445,9 @@ class _Crop(FeatureTransformer):
     def transformMat(self, f):
         h, w = f["mat"].shape[:2]
         x1, y1, x2, y2 = self.generateRoi(f)
+        from .bbox import BoundingBox
+
+        f["boundingBox"] = BoundingBox(x1, y1, x2, y2, self.normalized)      # what RoiProject maps the labels into
         if self.normalized:
             x1, x2, y1, y2 = x1 * w, x2 * w, y1 * h, y2 * h
         if self.is_clip:
@@ -466,8 +469,8 @@ class CenterCrop(_Crop):
 
     def generateRoi(self, f):
         h, w = f["mat"].shape[:2]
-        x1, y1 = (w - self.cw) / 2.0, (h - self.ch) / 2.0
-        return int(x1), int(y1), int(x1) + self.cw, int(y1) + self.ch
+        x1, y1 = (w - self.cw) / 2.0, (h - self.ch) / 2.0          # kept fractional: the crop truncates, the label
+        return x1, y1, x1 + self.cw, y1 + self.ch                  # projection uses the exact window (Crop.scala)
 
 
 class RandomCrop(_Crop):
@@ -571,6 +574,9 @@ class Expand(FeatureTransformer):
         canvas[top:top + h, left:left + w] = f["mat"]
         f["mat"] = canvas
         f["expandBbox"] = (-left / w, -top / h, (nw - left) / w, (nh - top) / h)
+        from .bbox import BoundingBox
+
+        f["boundingBox"] = BoundingBox(*f["expandBbox"], True)
 
 
 class FixExpand(FeatureTransformer):
@@ -584,6 +590,9 @@ class FixExpand(FeatureTransformer):
         canvas[top:top + h, left:left + w] = f["mat"]
         f["mat"] = canvas
         f["expandBbox"] = (-left / w, -top / h, (self.ew - left) / w, (self.eh - top) / h)
+        from .bbox import BoundingBox
+
+        f["boundingBox"] = BoundingBox(*f["expandBbox"], True)
 
 
 class HFlip(FeatureTransformer):
@@ -857,10 +866,17 @@ class RoiProject(FeatureTransformer):
         self.center = need_meet_center_constraint
 
     def transformMat(self, f):
-        win = f.get("expandBbox") or f.get("cropBboxNormalized")
-        if win is None:
-            return
-        x1, y1, x2, y2 = win
+        bb = f.get("boundingBox")
+        if bb is not None:
+            x1, y1, x2, y2 = bb.toTuple()
+            if not bb.normalized:            # a pixel window is expressed relative to the CURRENT image (RoiTransformer.scala)
+                h, w = f["mat"].shape[:2]
+                x1, y1, x2, y2 = x1 / w, y1 / h, x2 / w, y2 / h
+        else:
+            win = f.get("expandBbox") or f.get("cropBboxNormalized")
+            if win is None:
+                return
+            x1, y1, x2, y2 = win
         ww, wh = x2 - x1, y2 - y1
         lab = f["label"]
         b = lab.bboxes
@@ -868,11 +884,14 @@ class RoiProject(FeatureTransformer):
         if self.center:
             cx, cy = (b[:, 0] + b[:, 2]) / 2, (b[:, 1] + b[:, 3]) / 2
             keep = (cx >= x1) & (cx <= x2) & (cy >= y1) & (cy <= y2)
+        keep &= ~((b[:, 0] >= x2) | (b[:, 2] <= x1) | (b[:, 1] >= y2) | (b[:, 3] <= y1))        # must overlap the window
         nb = np.stack([(b[:, 0] - x1) / ww, (b[:, 1] - y1) / wh, (b[:, 2] - x1) / ww, (b[:, 3] - y1) / wh], 1)
-        nb = np.clip(nb, 0, 1)
-        keep &= (nb[:, 2] > nb[:, 0]) & (nb[:, 3] > nb[:, 1])
+        nb = np.clip(nb, 0, 1).astype(np.float32)
+        keep &= (nb[:, 2] - nb[:, 0]) * (nb[:, 3] - nb[:, 1]) > 0
         lab.bboxes = nb[keep]
         lab.classes = lab.classes[..., keep]
+        if lab.masks is not None and len(lab.masks) == len(keep):
+            lab.masks = [m for m, k in zip(lab.masks, keep) if k]
 
 
 class RandomSampler(_Crop):

@@ -190,3 +190,61 @@ def test_image_frame_specs_read_grey_and_globs():
     V.MatToFloats().transform(a)
     V.MatToTensor().transform(b)
     assert np.array_equal(np.asarray(a["floats"]).reshape(375, 500, 3).transpose(2, 0, 1), b["imageTensor"].numpy())
+
+
+_BOXES = [2.0, 84.0, 59.0, 248.0, 68.0, 115.0, 233.0, 279.0, 64.0, 173.0, 377.0, 373.0, 320.0, 2.0, 496.0, 375.0,
+          221.0, 4.0, 341.0, 374.0, 135.0, 14.0, 220.0, 148.0, 69.0, 43.0, 156.0, 177.0, 58.0, 54.0, 104.0, 139.0,
+          279.0, 1.0, 331.0, 86.0, 320.0, 22.0, 344.0, 96.0, 337.0, 1.0, 390.0, 107.0]
+_CLASSES = [11.0, 11.0, 11.0, 16.0, 16.0, 16.0, 11.0, 16.0, 16.0, 16.0, 16.0] + [0.0] * 10 + [1.0]
+
+
+def _roi_feature():
+    from bigdl_b200.transform.vision import image as V
+
+    f = V.ImageFrame.read(f"{RES}/pascal").features[0]
+    f["label"] = V.RoiLabel(np.array(_CLASSES, np.float32).reshape(2, 11), np.array(_BOXES, np.float32).reshape(11, 4))
+    return V, f
+
+
+def test_roi_transformers_match_the_reference_spec():
+    """Expected tensors of T/transform/vision/image/label/roi/RoiTransformerSpec.scala."""
+    V, f = _roi_feature()
+    V.RoiNormalize().transform(f)
+    norm = f["label"].bboxes
+    assert np.allclose(norm[0], [0.004, 0.224, 0.118, 0.6613333], atol=1e-6)
+    assert np.allclose(norm[3], [0.64, 0.0053333, 0.992, 1.0], atol=1e-6)
+    assert np.allclose(norm[10], [0.674, 0.0026667, 0.78, 0.28533334], atol=1e-6)
+    assert f["label"].classes.reshape(-1).tolist() == _CLASSES
+
+    V, f = _roi_feature()
+    V.Pipeline([V.HFlip(), V.RoiHFlip(False)]).transform(f)
+    want = [441.0, 84.0, 498.0, 248.0, 267.0, 115.0, 432.0, 279.0, 123.0, 173.0, 436.0, 373.0, 4.0, 2.0, 180.0, 375.0,
+            159.0, 4.0, 279.0, 374.0, 280.0, 14.0, 365.0, 148.0, 344.0, 43.0, 431.0, 177.0, 396.0, 54.0, 442.0, 139.0,
+            169.0, 1.0, 221.0, 86.0, 156.0, 22.0, 180.0, 96.0, 110.0, 1.0, 163.0, 107.0]
+    assert f["label"].bboxes.reshape(-1).tolist() == want
+
+    V, f = _roi_feature()
+    V.Pipeline([V.RoiNormalize(), V.RoiHFlip()]).transform(f)
+    assert np.allclose(f["label"].bboxes[0], [0.882, 0.224, 0.996, 0.6613333], atol=1e-6)
+    assert np.allclose(f["label"].bboxes[3], [0.008, 0.0053333, 0.36, 1.0], atol=1e-6)
+
+    V, f = _roi_feature()
+    V.Resize(300, 300).transform(f)
+    # Scala's RoiResize() defaults to normalized = false (the Python API's default is True): boxes / 300 · 300 / 500
+    V.Pipeline([V.RoiNormalize(), V.RoiResize(False)]).transform(f)
+    assert np.allclose(f["label"].bboxes, norm, atol=1e-6)
+
+    V, f = _roi_feature()
+    V.Resize(300, 300).transform(f)
+    V.RoiResize(False).transform(f)
+    assert np.allclose(f["label"].bboxes[0], [1.2, 67.2, 35.4, 198.4], atol=1e-4)
+    assert np.allclose(f["label"].bboxes[10], [202.2, 0.8, 234.0, 85.6], atol=1e-4)
+
+    V, f = _roi_feature()
+    V.Pipeline([V.CenterCrop(300, 300), V.RoiNormalize(), V.RoiProject()]).transform(f)
+    expected = np.array([0.0, 0.25833336, 0.44333336, 0.805, 0.0, 0.45166665, 0.9233333, 1.0, 0.40333334, 0.0, 0.8033333,
+                         1.0, 0.116666675, 0.0, 0.4, 0.36833334, 0.0, 0.01833333, 0.1866667, 0.46500003, 0.5966667, 0.0,
+                         0.77, 0.16166666, 0.73333335, 0.0, 0.8133333, 0.195, 0.78999996, 0.0, 0.9666667, 0.23166668],
+                        np.float32).reshape(8, 4)
+    assert f["label"].bboxes.shape == (8, 4) and np.allclose(f["label"].bboxes, expected, atol=1e-5)
+    assert f["label"].classes.shape == (2, 8) and f["mat"].shape == (300, 300, 3)

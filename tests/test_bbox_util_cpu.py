@@ -289,3 +289,53 @@ def test_untested_ops_and_transformers(tmp_path):
     sgd.update(x, g2)
     sgd.update(x, g2)
     assert sgd.getLearningRate() == pytest.approx(-0.1 / (1 + 1 * 0.5))          # negative rate, decayed by neval
+
+
+def test_reference_bounding_box_spec_values():
+    """Numbers asserted by T/transform/vision/image/util/BoundingBoxSpec.scala."""
+    scaled = BoundingBox()
+    BoundingBox(1, 4, 5, 6, False).scaleBox(1.0 / 4, 1.0 / 2, scaled)
+    assert scaled == BoundingBox(0.5, 1, 2.5, 1.5)
+    assert BoundingBox(0, 0, 5, 3, False).meetEmitCenterConstraint(BoundingBox(1, 0, 7, 4, False))
+    assert not BoundingBox(0, 0, 5, 3, False).meetEmitCenterConstraint(BoundingBox(4, 0, 7, 4, False))
+    b1 = BoundingBox(0.2, 0.3, 0.3, 0.5)
+    assert abs(b1.jaccardOverlap(BoundingBox(0.1, 0.1, 0.3, 0.4)) - 1.0 / 7) < 1e-6
+    assert abs(b1.jaccardOverlap(BoundingBox(0.1, 0.1, 0.4, 0.6)) - 2.0 / 15) < 1e-6
+    assert abs(b1.jaccardOverlap(BoundingBox(0, 0, 0.1, 0.1))) < 1e-6
+    box1, box2 = BoundingBox(0.222159, 0.427017, 0.606492, 0.679355), BoundingBox(0.418, 0.396396, 0.55, 0.666667)
+    proj = BoundingBox()
+    assert box1.projectBbox(box2, proj)
+    assert np.allclose(proj.toTuple(), (0.509561, 0.0, 0.853014, 0.949717), atol=1e-5)
+    assert box1.meetEmitCenterConstraint(box2)
+    assert not BoundingBox(0.0268208, 0.388175, 0.394421, 0.916685).meetEmitCenterConstraint(box2)
+
+    # getPriorBboxes
+    n = 4
+    prior = torch.zeros(2 * n * 4)
+    for i in range(n):
+        prior[i * 4:i * 4 + 4] = torch.tensor([i * 0.1, i * 0.1, i * 0.1 + 0.2, i * 0.1 + 0.1])
+    prior[n * 4:] = 0.1
+    boxes, variances = BboxUtil.getPriorBboxes(prior.reshape(1, 2, n * 4), n)
+    assert tuple(boxes.shape) == (n, 4) and torch.allclose(variances, torch.full((n, 4), 0.1))
+    assert torch.allclose(boxes[2], torch.tensor([0.2, 0.2, 0.4, 0.3]))
+
+    # getGroundTruths
+    inp = torch.tensor([[0.0, 1.0, 0.14285715, 0.1904762, 0.23809524, 0.2857143, 0.33333334],
+                        [0.0, 1.0, 0.47619048, 0.52380955, 0.5714286, 0.61904764, 0.6666667],
+                        [1.0, 3.0, 0.8095238, 0.85714287, 0.9047619, 0.95238096, 1.0]])
+    gts = BboxUtil.getGroundTruths(inp)
+    assert torch.equal(gts[0], inp[:2]) and torch.equal(gts[1], inp[2:])
+    assert torch.equal(BboxUtil.getGroundTruths(inp[2:])[0], inp[2:])
+    label = torch.tensor([[3.0, 8.0, 0.0, 0.241746, 0.322738, 0.447184, 0.478388],
+                          [3.0, 8.0, 0.0, 0.318659, 0.336546, 0.661729, 0.675461],
+                          [3.0, 8.0, 0.0, 0.56154, 0.300144, 0.699173, 0.708098],
+                          [3.0, 8.0, 0.0, 0.220494, 0.327759, 0.327767, 0.396797],
+                          [3.0, 8.0, 0.0, 0.194182, 0.317717, 0.279191, 0.389266],
+                          [4.0, -1.0, -1.0, -1.0, -1.0, -1.0, -1.0],
+                          [5.0, -1.0, -1.0, -1.0, -1.0, -1.0, -1.0],
+                          [6.0, 10.0, 0.0, 0.67894, 0.471823, 0.929308, 0.632044],
+                          [6.0, 10.0, 0.0, 0.381443, 0.572376, 0.892489, 0.691713],
+                          [7.0, 9.0, 0.0, 0.0, 0.0620616, 0.667269, 1.0]])
+    lg = BboxUtil.getGroundTruths(label)
+    assert len(lg) == 3 and lg[0].shape[0] == 5 and float(lg[0][0, 0]) == 3
+    assert lg[3].shape[0] == 2 and float(lg[3][0, 0]) == 6 and lg[4].shape[0] == 1 and float(lg[4][0, 0]) == 7

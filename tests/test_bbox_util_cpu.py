@@ -339,3 +339,26 @@ def test_reference_bounding_box_spec_values():
     lg = BboxUtil.getGroundTruths(label)
     assert len(lg) == 3 and lg[0].shape[0] == 5 and float(lg[0][0, 0]) == 3
     assert lg[3].shape[0] == 2 and float(lg[3][0, 0]) == 6 and lg[4].shape[0] == 1 and float(lg[4][0, 0]) == 7
+
+
+def test_reference_loc_predictions_and_decode_values():
+    """"getLocPredictions shared" and "decodeBoxes" of BoundingBoxSpec.scala."""
+    num, per = 2, 2
+    loc = torch.zeros(num, per * 4, 1, 1)
+    for i in range(num):
+        for j in range(per):
+            v = i * per * 0.1 + j * 0.1
+            loc[i, j * 4:j * 4 + 4, 0, 0] = torch.tensor([v, v, v + 0.2, v + 0.2])
+    out = BboxUtil.getLocPredictions(loc, per, 1, True)
+    assert len(out) == num and all(len(o) == 1 for o in out)
+    for i in range(num):
+        for j in range(per):
+            v = i * per * 0.1 + j * 0.1
+            assert torch.allclose(out[i][0][j], torch.tensor([v, v, v + 0.2, v + 0.2]), atol=1e-6)
+
+    prior = torch.tensor([[0.1 * i, 0.1 * i, 0.1 * i + 0.2, 0.1 * i + 0.2] for i in range(1, 5)])
+    var = torch.tensor([[0.1, 0.1, 0.2, 0.2]] * 4)
+    boxes = torch.tensor([[0.0, 0.75, math.log(2), math.log(1.5)]] * 4)
+    dec = BboxUtil.decodeBoxes(prior, var, False, boxes, True)
+    for i in range(4):
+        assert torch.allclose(dec[i], torch.tensor([0.0, 0.2, 0.4, 0.5]) + i * 0.1, atol=1e-5)

@@ -345,6 +345,10 @@ class PrecisionRecallAUC(ValidationMethod):
     _Res = PRAUCResult
 
     def __call__(self, output, target):
+        if output.numel() == 0 or target.numel() == 0:
+            raise ValueError("PrecisionRecallAUC: output and target must not be empty")
+        if output.numel() != target.numel():
+            raise ValueError(f"PrecisionRecallAUC: {output.numel()} scores but {target.numel()} labels")
         return PRAUCResult(output.reshape(-1).float().cpu().tolist(), target.reshape(-1).float().cpu().tolist())
 
 

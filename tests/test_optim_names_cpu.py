@@ -536,3 +536,13 @@ def test_nn_utils_basemodule_and_primitives():
     g = bm.backward(torch.rand(5, 3), torch.ones(5, 4))
     assert tuple(g.shape) == (5, 3)
     assert L.ErrorInfo.constrainInputAsVectorOrBatch and L.Scheduler and L.FrameManager
+
+
+def test_prauc_reference_spec_value():
+    """T/optim/ValidationSpec.scala "precision recall auc": 0.7916667 on 4 samples; empty input is an error."""
+    r = Vd.PrecisionRecallAUC()(torch.tensor([0.1, 0.4, 0.35, 0.8]), torch.tensor([0.0, 0.0, 1.0, 1.0]))
+    assert r.result() == (pytest.approx(0.7916667, abs=1e-6), 4)
+    with pytest.raises(ValueError):
+        Vd.PrecisionRecallAUC()(torch.zeros(0), torch.zeros(0))
+    with pytest.raises(ValueError):
+        Vd.PrecisionRecallAUC()(torch.zeros(3), torch.zeros(2))

@@ -546,3 +546,19 @@ def test_prauc_reference_spec_value():
         Vd.PrecisionRecallAUC()(torch.zeros(0), torch.zeros(0))
     with pytest.raises(ValueError):
         Vd.PrecisionRecallAUC()(torch.zeros(3), torch.zeros(2))
+
+
+def test_hit_ratio_ndcg_reference_spec_values():
+    """T/optim/ValidationSpec.scala "HR@10", "ndcg", "CongituousResult"."""
+    o = torch.arange(1, 1001).float() / 1000
+    t = torch.zeros(1000)
+    t[999] = 1
+    kw = {"neg_num": 999} if "neg_num" in Vd.HitRatio.__init__.__code__.co_varnames else {}
+    hr, nd = (Vd.HitRatio(**kw), Vd.NDCG(**kw)) if kw else (Vd.HitRatio(10, 999), Vd.NDCG(10, 999))
+    assert hr(o, t).result()[0] == 1.0 and nd(o, t).result()[0] == pytest.approx(1.0)
+    o[999] = 0.9988
+    assert hr(o, t).result()[0] == 1.0 and nd(o, t).result()[0] == pytest.approx(0.63092977, abs=1e-6)
+    o[999] = 0.9888
+    assert hr(o, t).result()[0] == 0.0 and nd(o, t).result()[0] == 0.0
+    r = (Vd.ContiguousResult(0.2, 2, "HR@10") + Vd.ContiguousResult(0.1, 1, "HR@10")).result()
+    assert r[0] == pytest.approx(0.1) and r[1] == 3
